@@ -1,0 +1,209 @@
+/*
+ * mpmc_b200.h -- C ABI of the B200-native energy engine for MPMC's per-step
+ * energy hot path (LJ + Ewald + iterative Thole polarization).
+ *
+ * Plain pointers and sizes only; no torch / CUDA types appear in any signature,
+ * so the library can be bound from C (the reference's host language), ctypes,
+ * cgo, JNI...  All arithmetic is IEEE fp64.  Units follow the reference:
+ * energies in K, lengths in Angstrom, charges in sqrt(K*A) (e * 408.7816,
+ * reference src/include/defines.h:45), polarizabilities in A^3.
+ *
+ * Which reference interface each entry point replaces (paths relative to the
+ * reference tree):
+ *
+ *   mpmc_b200_set_params     system_t scalar options read by the hot path
+ *                            (src/include/structs.h:347-513) and pbc_t
+ *                            (structs.h:100-105)
+ *   mpmc_b200_set_atoms      the molecule_t -> atom_t linked lists as walked by
+ *                            rebuild_arrays() (src/energy/pairs.c:12-38); the
+ *                            per-pair pair_t list (structs.h:21-37) is NOT
+ *                            materialised
+ *   mpmc_b200_set_positions  atom_t.pos[] after an MC move
+ *                            (src/mc/mc_moves.c:567-741)
+ *   mpmc_b200_energy         energy()            (src/energy/energy.c:67-226)
+ *                            = pairs()           (src/energy/pairs.c:293-361)
+ *                            + polar()           (src/energy/polar.c:31-135)
+ *                            + lj()              (src/energy/lj.c:165-276)
+ *                            + coulombic()       (src/energy/coulombic.c:22-39)
+ *   mpmc_b200_polar          polar() alone       (src/energy/polar.c:31-135)
+ *   mpmc_b200_get_atom_arrays  the per-atom fields polar() writes back:
+ *                            mu, ef_static, ef_induced, ef_induced_change,
+ *                            dipole_rrms (structs.h:47-49), rank_metric
+ *
+ * The drop-in `double energy(system_t*)` / `double polar(system_t*)` symbols of
+ * the reference (src/include/function_prototypes.h:5,193) are provided by the
+ * shim in mpmc_b200/shim/ on top of this ABI; see INTEGRATION.md.
+ *
+ * Error convention: every function returns 0 on success, non-zero on failure;
+ * mpmc_b200_last_error() returns a static, human-readable message.  CUDA errors
+ * are never swallowed.  There is NO CPU fallback: without a CUDA device
+ * mpmc_b200_create() fails.
+ */
+#ifndef MPMC_B200_H
+#define MPMC_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPMC_B200_ABI_VERSION 1
+
+/* damp_type: src/include/defines.h DAMPING_* enum */
+enum { MPMC_DAMP_OFF = 0, MPMC_DAMP_LINEAR = 1, MPMC_DAMP_EXPONENTIAL = 2 };
+/* LJ mixing rule (src/energy/pairs.c:84-211) */
+enum { MPMC_MIX_LORENTZ_BERTHELOT = 0, MPMC_MIX_WALDMAN_HAGLER = 1, MPMC_MIX_HALGREN = 2, MPMC_MIX_C6 = 3 };
+
+/* Scalar options of system_t / pbc_t that the hot path reads. */
+typedef struct mpmc_b200_params {
+    /* pbc_t (structs.h:100-105): basis[q][p] = component p of lattice vector q */
+    double basis[3][3];
+    double reciprocal_basis[3][3];
+    double cutoff;
+    double volume;
+    /* Ewald (structs.h:424-427) */
+    double ewald_alpha;
+    int ewald_kmax;
+    /* Feynman-Hibbs (structs.h:442) */
+    int feynman_hibbs;
+    int feynman_hibbs_order;
+    double temperature;
+    /* repulsion / dispersion */
+    int rd_lrc;  /* structs.h:444 */
+    int mixing;  /* MPMC_MIX_* */
+    int rd_only; /* structs.h:418: skip electrostatics and polarization */
+    /* cavity_autoreject_absolute (structs.h:395,406; energy.c:49-64) */
+    int cavity_autoreject_absolute;
+    double cavity_autoreject_scale;
+    /* Thole polarization (structs.h:429-435) */
+    int polarization;
+    int polar_iterative;
+    int damp_type;
+    double polar_damp;
+    int polar_max_iter;
+    double polar_precision;
+    double polar_gamma;
+    int polar_gs, polar_gs_ranked;
+    int polar_sor, polar_esor;
+    int polar_palmo, polar_rrms, polar_zodid;
+    int polar_ewald, polar_ewald_full, polar_wolf, polar_wolf_full;
+    int polar_wolf_alpha_lookup;
+    double polar_wolf_alpha;
+    double polar_wolf_alpha_lookup_cutoff;
+    double polar_ewald_alpha;
+} mpmc_b200_params;
+
+/* What energy() puts into observables_t (structs.h:152-162) plus its parts. */
+typedef struct mpmc_b200_energies {
+    double total;       /* observables->energy */
+    double rd;          /* observables->rd_energy  (pair LJ [+FH] + LRC pair + LRC self) */
+    double coulombic;   /* observables->coulombic_energy = real + reciprocal + self */
+    double polar;       /* observables->polarization_energy */
+    double rd_pair;     /* sum over in-cutoff pairs only */
+    double rd_lrc;      /* pair + self long-range correction */
+    double es_real;     /* coulombic_real(): erfc pairs [+FH] - intramolecular erf term */
+    double es_recip;    /* coulombic_reciprocal() */
+    double es_self;     /* coulombic_self() */
+    double dipole_rrms; /* observables->dipole_rrms (get_dipole_rrms, polar.c:13-28) */
+    double min_intermolecular_r; /* smallest r_img between atoms of different molecules */
+    int polar_iterations;        /* nodestats->polarization_iterations */
+    int iter_success;            /* system->iter_success: 1 = solver failed to converge */
+    int autorejected;            /* 1 = cavity_autoreject_absolute fired; total = 1e40 */
+    int reserved;
+} mpmc_b200_energies;
+
+/* Work counters of the last evaluation (for Gpair/s and roofline arithmetic). */
+typedef struct mpmc_b200_counters {
+    double pairs_tested;      /* unordered pairs whose geometry was evaluated by the pair kernel */
+    double pairs_lj;          /* pairs inside the cutoff contributing an LJ term */
+    double pairs_es;          /* pairs inside the cutoff contributing an erfc term */
+    double pairs_field;       /* unordered pairs contributing to the static field */
+    double pairs_dipole;      /* ordered polarizable pairs per contraction */
+    double contractions;      /* dipole-tensor contractions done (iterations [+1 palmo]) */
+    double kvectors;          /* reciprocal vectors */
+    double recip_atoms;       /* atoms in the structure factor */
+    int n_atoms, n_polarizable;
+    int kernel_launches;      /* kernels of THIS library launched by the last evaluation */
+    int reserved;
+} mpmc_b200_counters;
+
+typedef struct mpmc_b200_ctx mpmc_b200_ctx;
+
+int mpmc_b200_abi_version(void);
+const char *mpmc_b200_last_error(void);
+
+/* device = CUDA ordinal.  Fails (non-zero) when no CUDA device is usable. */
+int mpmc_b200_create(mpmc_b200_ctx **ctx, int device);
+void mpmc_b200_destroy(mpmc_b200_ctx *ctx);
+
+/* Optional: run on a caller-owned cudaStream_t (passed as void*). NULL = own stream. */
+int mpmc_b200_set_stream(mpmc_b200_ctx *ctx, void *cuda_stream);
+
+int mpmc_b200_set_params(mpmc_b200_ctx *ctx, const mpmc_b200_params *p);
+
+/*
+ * Full (re)definition of the atom set, in the reference's list order
+ * (molecule list order, then atom list order: pairs.c:28-34).  HOST pointers.
+ *   pos[3*n]       atom_t.pos
+ *   charge[n]      atom_t.charge          polarizability[n] atom_t.polarizability
+ *   epsilon[n]     atom_t.epsilon         sigma[n]          atom_t.sigma
+ *   mol_mass[n]    molecule_t.mass of the atom's molecule (Feynman-Hibbs reduced mass)
+ *   mol_id[n]      index of the atom's molecule (same molecule <=> same id)
+ *   frozen[n]      atom_t.frozen
+ */
+int mpmc_b200_set_atoms(mpmc_b200_ctx *ctx, int n, const double *pos, const double *charge,
+                        const double *polarizability, const double *epsilon, const double *sigma,
+                        const double *mol_mass, const int *mol_id, const int *frozen);
+
+/* Overwrite positions of atoms [first, first+count) -- one MC displacement.  HOST pointer. */
+int mpmc_b200_set_positions(mpmc_b200_ctx *ctx, int first, int count, const double *pos);
+
+/*
+ * Row sharding for multi-GPU runs: this context computes only its share of the
+ * pair tiles, field rows, dipole rows and k-vector/atom chunks.  rank in
+ * [0, world).  Partial results are combined by the caller (allreduce of
+ * mpmc_b200_energies fields; allgather of dipole rows, see *_polar_stage).
+ */
+int mpmc_b200_set_shard(mpmc_b200_ctx *ctx, int rank, int world);
+
+/* energy(): all kernels + device->host copy of the scalars; synchronous. */
+int mpmc_b200_energy(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
+/* polar() alone: static field + solver + U_pol; synchronous. */
+int mpmc_b200_polar(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
+
+/* Enqueue energy() on the stream without any host synchronisation or copy
+ * (fixed-iteration solver modes only); pair with mpmc_b200_energy_finish(). */
+int mpmc_b200_energy_enqueue(mpmc_b200_ctx *ctx);
+int mpmc_b200_energy_finish(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
+
+/* Staged polarization for sharded runs (each returns after enqueueing):
+ *   stage 0: static field for own rows + mu0 for own rows
+ *   stage 1: one contraction + update for own rows (Jacobi family), writes own rows of mu_new
+ *   stage 2: finish: U_pol partial over own rows
+ * Between stages the caller all-gathers the dipole buffer (see device_buffer). */
+int mpmc_b200_polar_stage(mpmc_b200_ctx *ctx, int stage, int iteration);
+/* Raw device pointer + element count of an internal buffer, for collectives
+ * issued by the caller on the same stream.  which: 0 = packed dipoles mu
+ * [3][n_pol_padded] (SoA), 1 = packed new dipoles, 2 = convergence scalar. */
+int mpmc_b200_device_buffer(mpmc_b200_ctx *ctx, int which, void **dev_ptr, long long *n_doubles);
+/* rows [begin,end) of the packed polarizable index space owned by this shard */
+int mpmc_b200_shard_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_pol, int *n_pol_padded);
+
+/* Copy per-atom results back (HOST pointers, any may be NULL), reference list order:
+ * mu, ef_static, ef_induced, ef_induced_change : [3*n] ; dipole_rrms, rank_metric : [n] */
+int mpmc_b200_get_atom_arrays(mpmc_b200_ctx *ctx, double *mu, double *ef_static, double *ef_induced,
+                              double *ef_induced_change, double *dipole_rrms, double *rank_metric);
+
+int mpmc_b200_get_counters(mpmc_b200_ctx *ctx, mpmc_b200_counters *out);
+
+/* Measured device time (ms, CUDA events on the library's stream) of the named
+ * phase in the last evaluation: "pair", "recip", "field", "dipole", "total". */
+int mpmc_b200_phase_ms(mpmc_b200_ctx *ctx, const char *phase, double *ms);
+
+/* fp64 FMA throughput probe (dependent-chain DFMA kernel), TFLOP/s; used as the
+ * roofline denominator because MEASURED_PEAKS.json carries no fp64 figure. */
+int mpmc_b200_measure_fp64_peak(mpmc_b200_ctx *ctx, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPMC_B200_H */

@@ -1,0 +1,69 @@
+"""Loader for tests/golden/*.npz (written by oracle/make_golden.py from the unmodified reference)."""
+import glob
+import json
+import os
+
+import numpy as np
+
+from mpmc_b200.api import System
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def case_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLD, "*.npz")))
+
+
+def load(name):
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    s = System.from_arrays(z, name)
+    exp = json.loads(str(z["expected_json"]))
+    for k in z.files:
+        if k.startswith("exp_"):
+            exp[k[4:]] = z[k]
+    return s, exp
+
+
+# Tolerances.  BASELINE.json north_star: LJ / Ewald / polarization energies <= 1e-10 relative.
+# rd, polar, and each Ewald piece (real, reciprocal, self) are held to that against their own
+# magnitude.  The Ewald TOTAL is a difference of pieces 1e3-1e5 times larger than itself (the
+# intramolecular erf term cancels the point self energy), so merely re-associating the
+# reference's own sum moves it by ~3e-15 of the largest piece (measured: co2_fluid_375, row
+# partials vs one running sum).  Its tolerance is therefore 1e-10 of itself PLUS a conditioning
+# floor of 1e-13 of the largest piece; the same floor carries into the grand total.
+RTOL = 1e-10
+COND_FLOOR = 1e-13
+
+
+def assert_energies(got: dict, exp: dict, rtol=RTOL, label="", floor=COND_FLOOR):
+    def close(a, b, k="", extra=0.0):
+        tol = rtol * abs(b) + extra
+        assert abs(a - b) <= tol, f"{label} {k}: got {a!r} expected {b!r} |diff| {abs(a - b):.3e} > tol {tol:.3e}"
+
+    if exp.get("total", 0) >= 1e40 or got.get("autorejected"):
+        assert got["total"] == exp["total"], f"{label} autoreject: {got['total']} vs {exp['total']}"
+        return
+    close(got["rd"], exp["rd"], k="rd")
+    close(got["polar"], exp["polar"], k="polar")
+    es_floor = 0.0
+    if "es_real" in exp:
+        for k in ("es_real", "es_recip", "es_self"):
+            close(got[k], exp[k], k=k)
+        es_floor = floor * max(abs(exp["es_real"]), abs(exp["es_self"]), abs(exp["es_recip"]))
+        close(got["coulombic"], exp["coulombic"], k="coulombic", extra=es_floor)
+    close(got["total"], exp["total"], k="total", extra=es_floor + rtol * (abs(exp["rd"]) + abs(exp["polar"])))
+    assert int(got["polar_iterations"]) == int(exp["polar_iterations"]), f"{label} iterations"
+    assert int(got["iter_success"]) == int(exp["iter_success"]), f"{label} iter_success"
+
+
+def assert_atom_arrays(got: dict, exp: dict, s: System, rtol=1e-10, label=""):
+    for k in ("ef_static", "mu", "ef_induced", "ef_induced_change"):
+        scale = max(np.abs(exp[k]).max(), 1e-300)
+        if k == "ef_induced_change":
+            # a difference of two O(|ef_induced|) sums: compare on that scale
+            scale = max(scale, np.abs(exp["ef_induced"]).max())
+        err = np.abs(got[k] - exp[k]).max() / scale
+        assert err <= rtol, f"{label} {k}: max err / max |ref| = {err:.3e}"
+    err = np.abs(got["dipole_rrms"] - exp["dipole_rrms"]).max()
+    assert err <= 1e-8 * max(1.0, np.abs(exp["dipole_rrms"]).max()), f"{label} dipole_rrms {err:.3e}"
+    assert np.array_equal(got["rank_metric"], exp["rank_metric"]), f"{label} rank_metric"
