@@ -1,0 +1,93 @@
+// common.cuh -- shared device helpers of the mpmc_b200 energy engine (sm_100a, fp64).
+//
+// Geometry follows the reference's minimum_image() (src/energy/pairs.c:230-290):
+//   img[p] = rint( sum_q reciprocal_basis[q][p] * d[q] ),  dimg[p] = d[p] - sum_q basis[q][p] * img[q]
+// evaluated in registers for every pair, every time (the reference's pair_t cache is not kept).
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "mpmc_b200.h"
+
+namespace mpmc {
+
+constexpr int TILE = 128;  // atoms per tile == threads per CTA in the pair / field / dipole kernels
+
+// reference src/include/defines.h
+constexpr double kHBAR2 = 1.11211999e-68;
+constexpr double kHBAR4 = 1.23681087e-136;
+constexpr double kKB = 1.3806503e-23;
+constexpr double kKB2 = 1.90619525e-46;
+constexpr double kM2A2 = 1.0e20;
+constexpr double kM2A4 = 1.0e40;
+constexpr double kAMU2KG = 1.66053873e-27;
+constexpr double kDEBYE2SKA = 85.10597636;
+constexpr double kMAXVALUE = 1.0e40;
+constexpr double kSMALL_dR = 1.0e-12;
+constexpr int kMAX_ITERATION_COUNT = 128;
+
+// Scalars every kernel needs, passed by value (lands in the constant bank).
+struct Cell {
+    double B[3][3];  // basis[q][p]
+    double R[3][3];  // reciprocal_basis[q][p]
+    double cutoff;
+    double volume;
+};
+
+__device__ __forceinline__ double rint_magic(double x) {
+    // round-half-even like rint() for |x| < 2^51; two DADDs instead of a conversion-pipe op
+    const double m = 6755399441055744.0;  // 1.5 * 2^52
+    return __dadd_rn(__dadd_rn(x, m), -m);
+}
+
+template <bool ORTHO>
+__device__ __forceinline__ void min_image(const Cell& c, double& dx, double& dy, double& dz) {
+    if (ORTHO) {
+        dx -= c.B[0][0] * rint_magic(c.R[0][0] * dx);
+        dy -= c.B[1][1] * rint_magic(c.R[1][1] * dy);
+        dz -= c.B[2][2] * rint_magic(c.R[2][2] * dz);
+    } else {
+        double i0 = rint_magic(c.R[0][0] * dx + c.R[1][0] * dy + c.R[2][0] * dz);
+        double i1 = rint_magic(c.R[0][1] * dx + c.R[1][1] * dy + c.R[2][1] * dz);
+        double i2 = rint_magic(c.R[0][2] * dx + c.R[1][2] * dy + c.R[2][2] * dz);
+        dx -= c.B[0][0] * i0 + c.B[1][0] * i1 + c.B[2][0] * i2;
+        dy -= c.B[0][1] * i0 + c.B[1][1] * i1 + c.B[2][1] * i2;
+        dz -= c.B[0][2] * i0 + c.B[1][2] * i1 + c.B[2][2] * i2;
+    }
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_down_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_down_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Fixed-order block reduction (deterministic run to run): warp shuffles, then warp 0 adds the
+// per-warp partials in warp order.  Result valid in thread 0.  `scratch` holds >= 32 doubles.
+template <int OP>  // 0 sum, 1 min, 2 max
+__device__ __forceinline__ double block_reduce(double v, double* scratch) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = OP == 0 ? warp_sum(v) : OP == 1 ? warp_min(v) : warp_max(v);
+    __syncthreads();
+    if (lane == 0) scratch[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        double ident = OP == 0 ? 0.0 : OP == 1 ? 1.0e300 : -1.0e300;
+        v = lane < nw ? scratch[lane] : ident;
+        v = OP == 0 ? warp_sum(v) : OP == 1 ? warp_min(v) : warp_max(v);
+    }
+    return v;
+}
+
+}  // namespace mpmc

@@ -1,0 +1,1316 @@
+// engine.cu -- host side of libmpmc_b200: device-resident system image, evaluation pipeline and
+// the C ABI of include/mpmc_b200.h.
+//
+// The pipeline mirrors energy() (reference src/energy/energy.c:67-226):
+//   pairs()+lj()+coulombic_real()  -> K1 pair tiles            (pair_kernel.cu)
+//   coulombic_reciprocal()         -> K2 structure factor      (recip_kernel.cu)
+//   coulombic_self(), LRC          -> O(N) / O(types^2) on the host, identical formulas
+//   polar(): thole_field()         -> K3 static field          (field_kernel.cu)
+//            thole_iterative()     -> K4 contraction + K5 update, or the blocked GS sweep
+//                                                              (dipole_kernel.cu)
+// The O(N^2) pair_t lists and the 3N x 3N A matrix are never built: device memory is O(N).
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <numeric>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "kernels.h"
+
+using namespace mpmc;
+
+static thread_local std::string g_err = "";
+
+#define CU(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e__ = (call);                                                                     \
+        if (e__ != cudaSuccess) {                                                                     \
+            char b__[512];                                                                            \
+            snprintf(b__, sizeof(b__), "CUDA error %s at %s:%d (%s)", cudaGetErrorString(e__), __FILE__, __LINE__, #call); \
+            g_err = b__;                                                                              \
+            return 10;                                                                                \
+        }                                                                                             \
+    } while (0)
+
+#define FAIL(code, msg) \
+    do {                \
+        g_err = (msg);  \
+        return (code);  \
+    } while (0)
+
+namespace {
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n) {
+        if (n <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 4 + 256;
+        if (cudaMalloc(&p, want * sizeof(T)) != cudaSuccess) return 1;
+        cap = want;
+        return 0;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct Subset {
+    std::vector<int> idx;  // atom indices, ascending
+    int n = 0, n_pad = 0;
+    DevBuf<double> x, y, z, q, alpha, aux;
+    DevBuf<int> mol, flags, didx;
+    SubsetDev dev() const {
+        SubsetDev d;
+        d.n = n;
+        d.n_pad = n_pad;
+        d.x = x.p;
+        d.y = y.p;
+        d.z = z.p;
+        d.q = q.p;
+        d.alpha = alpha.p;
+        d.aux = aux.p;
+        d.mol = mol.p;
+        d.flags = flags.p;
+        d.idx = didx.p;
+        return d;
+    }
+    void release() {
+        x.release(), y.release(), z.release(), q.release(), alpha.release(), aux.release();
+        mol.release(), flags.release(), didx.release();
+    }
+};
+
+enum Phase { PH_PAIR = 0, PH_RECIP, PH_FIELD, PH_DIPOLE, PH_TOTAL, PH_COUNT };
+
+// device scalar slots
+enum Slot {
+    S_PAIR = 0,    // 8 doubles: rd, es, intra, min_r, n_tested, n_lj, n_es
+    S_RECIP = 8,   // 1
+    S_POLAR = 9,   // 3: sum mu.Es, sum mu.eic, sum rrms
+    S_ERR = 12,    // max err^2 bits (as unsigned long long)
+    S_FIELDCNT = 13,
+    S_COUNT = 16
+};
+
+}  // namespace
+
+struct mpmc_b200_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    mpmc_b200_params P{};
+    bool have_params = false, have_atoms = false;
+    int rank = 0, world = 1;
+
+    // host copy (list order)
+    int n = 0, n_pad = 0;
+    std::vector<double> hx, hy, hz, hq, halpha, heps, hsig, hmm;
+    std::vector<int> hmol, hfrozen;
+
+    // device image
+    DevBuf<double> x, y, z, q, eps, sig, molmass, alpha;
+    DevBuf<int> mol, flags;
+    Subset charged, recip, pol, gs;  // gs: polarizable atoms permuted into Gauss-Seidel order
+    DevBuf<int2> tiles;
+    int ntiles = 0;
+    DevBuf<double> pair_part;
+    int pair_stride = 0;
+
+    // reciprocal space
+    DevBuf<int> kl;
+    DevBuf<double> kweight, kweight_field, kvec, sf_partial, sf;
+    int nk = 0;
+    bool kdirty = true;
+    int recip_chunks = 0, recip_apc = 0;
+
+    // polarization
+    DevBuf<double> ef_static;  // [3][n_pad]
+    DevBuf<double> epart;      // max(field, dipole) partials
+    DevBuf<double> es, mu, mu_old, mu_new, eind, eic, rrms, rank_packed, rmin_part, field_cnt;
+    DevBuf<double> g_es, g_mu, g_mu_old, g_mu_new, g_eind, g_eic, g_rrms;  // GS space
+    DevBuf<int> perm;
+    std::vector<int> hperm;
+    DevBuf<double> wolf_table;
+    int wolf_table_max = 0;
+    double wolf_table_alpha = -1.0, wolf_table_cut = -1.0;
+    int field_jsplits = 1, dipole_jsplits = 1;
+
+    DevBuf<double> scalars;
+    double* h_scalars = nullptr;  // pinned
+    double* h_stage = nullptr;    // pinned staging for positions
+    size_t h_stage_cap = 0;
+
+    // host-side analytic terms
+    double lrc_pair = 0, lrc_self = 0, es_self = 0;
+    bool analytic_dirty = true;
+    bool subsets_stale = false;
+
+    cudaEvent_t ev[PH_COUNT][2];
+    bool ev_used[PH_COUNT] = {false, false, false, false, false};
+    float phase_ms[PH_COUNT] = {0, 0, 0, 0, 0};
+
+    mpmc_b200_counters cnt{};
+    int launches = 0;
+    int pending_iterations = 0, pending_iter_success = 0;
+    bool pending = false;
+    bool last_had_polar = false;
+};
+
+typedef mpmc_b200_ctx Ctx;
+
+// ------------------------------------------------------------------------------------------------
+// small device helpers defined here
+// ------------------------------------------------------------------------------------------------
+__global__ void gather_positions_kernel(const double* __restrict__ x, const double* __restrict__ y,
+                                        const double* __restrict__ z, const int* __restrict__ idx, int n,
+                                        double* __restrict__ sx, double* __restrict__ sy, double* __restrict__ sz) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int g = idx[k];
+    sx[k] = x[g];
+    sy[k] = y[g];
+    sz[k] = z[g];
+}
+
+// dst[c][k] = src[c][perm[k]] (forward) or dst[c][perm[k]] = src[c][k] (inverse), k < n
+__global__ void permute_kernel(const double* __restrict__ src, double* __restrict__ dst, const int* __restrict__ perm, int n,
+                               int np, int ncomp, int inverse) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int pk = perm[k];
+    for (int c = 0; c < ncomp; c++) {
+        if (inverse)
+            dst[c * np + pk] = src[c * np + k];
+        else
+            dst[c * np + k] = src[c * np + pk];
+    }
+}
+__global__ void permute_int_kernel(const int* __restrict__ src, int* __restrict__ dst, const int* __restrict__ perm, int n) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) dst[k] = src[perm[k]];
+}
+
+// GS convergence / rrms on (mu_new - mu_old), same arithmetic as dipole_update_kernel
+__global__ void gs_check_kernel(int n, int np, const double* __restrict__ mu_new, const double* __restrict__ mu_old,
+                                int do_rrms, double* __restrict__ rrms, unsigned long long* __restrict__ max_err2_bits) {
+    __shared__ double red[32];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double worst = 0.0;
+    if (i < n) {
+        double num = 0.0, den = 0.0;
+        for (int c = 0; c < 3; c++) {
+            const double nw = mu_new[c * np + i], d = nw - mu_old[c * np + i];
+            worst = fmax(worst, d * d);
+            num += d * d;
+            den += nw * nw;
+        }
+        if (do_rrms) {
+            double v = sqrt(num / den);
+            if (!isfinite(v)) v = 0.0;
+            rrms[i] = v;
+        }
+    }
+    worst = block_reduce<2>(worst, red);
+    if (threadIdx.x == 0) atomicMax(max_err2_bits, (unsigned long long)__double_as_longlong(worst));
+}
+
+__global__ void __launch_bounds__(1024) sum_reduce_kernel(const double* __restrict__ in, int n, double* __restrict__ out) {
+    __shared__ double red[32];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) acc += in[i];
+    acc = block_reduce<0>(acc, red);
+    if (threadIdx.x == 0) out[0] = acc;
+}
+
+// failure path of thole_iterative (src/polarization/thole_iterative.c:199-210): mu = alpha E_s, eic = 0
+__global__ void reset_dipoles_kernel(int n, int np, const double* __restrict__ alpha, const double* __restrict__ es,
+                                     double* __restrict__ mu, double* __restrict__ eic) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int c = 0; c < 3; c++) {
+        mu[c * np + i] = alpha[i] * es[c * np + i];
+        eic[c * np + i] = 0.0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host helpers
+// ------------------------------------------------------------------------------------------------
+static int round_up(int n, int m) { return ((n + m - 1) / m) * m; }
+
+static bool is_ortho(const mpmc_b200_params& P) {
+    for (int a = 0; a < 3; a++)
+        for (int b = 0; b < 3; b++)
+            if (a != b && (P.basis[a][b] != 0.0 || P.reciprocal_basis[a][b] != 0.0)) return false;
+    return true;
+}
+
+static Cell make_cell(const mpmc_b200_params& P) {
+    Cell c;
+    for (int a = 0; a < 3; a++)
+        for (int b = 0; b < 3; b++) {
+            c.B[a][b] = P.basis[a][b];
+            c.R[a][b] = P.reciprocal_basis[a][b];
+        }
+    c.cutoff = P.cutoff;
+    c.volume = P.volume;
+    return c;
+}
+
+template <typename T>
+static int upload(DevBuf<T>& b, const std::vector<T>& h, cudaStream_t s) {
+    if (b.ensure(h.size() ? h.size() : 1)) FAIL(11, "cudaMalloc failed");
+    if (!h.empty()) CU(cudaMemcpyAsync(b.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s));
+    return 0;
+}
+
+// mixed LJ parameters on the host for the analytic long-range correction (pairs.c:84-211)
+static void host_mix(int mixing, double ei, double si, double ej, double sj, double& eps, double& sigma) {
+    eps = 0.0;
+    sigma = 0.0;
+    switch (mixing) {
+        case MPMC_MIX_WALDMAN_HAGLER: {
+            double si3 = si * si * si, si6 = si3 * si3, sj3 = sj * sj * sj, sj6 = sj3 * sj3;
+            if (si < 0.0 || sj < 0.0)
+                sigma = pow(0.5 * (si6 + sj6), 1. / 6.);
+            else if (si == 0 || sj == 0)
+                eps = sqrt(ei * ej);
+            else {
+                sigma = pow(0.5 * (si6 + sj6), 1. / 6.);
+                eps = sqrt(ei * ej) * 2.0 * si3 * sj3 / (si6 + sj6);
+            }
+        } break;
+        case MPMC_MIX_HALGREN:
+            if (si > 0.0 && sj > 0.0) sigma = (si * si * si + sj * sj * sj) / (si * si + sj * sj);
+            if (ei > 0.0 && ej > 0.0) eps = 4 * ei * ej / pow(sqrt(ei) + sqrt(ej), 2);
+            break;
+        case MPMC_MIX_C6:
+            sigma = 0.5 * (si + sj);
+            if (sigma != 0.0) eps = 64.0 * sqrt(ei * ej) * pow(si, 3.0) * pow(sj, 3.0) / pow(si + sj, 6.0);
+            break;
+        default:
+            if (si < 0.0 || sj < 0.0)
+                sigma = 0.5 * (fabs(si) + fabs(sj));
+            else if (si == 0 || sj == 0)
+                eps = sqrt(ei * ej);
+            else {
+                sigma = 0.5 * (si + sj);
+                eps = sqrt(ei * ej);
+            }
+    }
+}
+
+static double lrc_value(double eps, double sigma, double cutoff, double volume) {
+    // lj_lrc_corr / lj_lrc_self (src/energy/lj.c:69-80, 92-103)
+    double sig_cut = fabs(sigma) / cutoff;
+    double sig3 = fabs(sigma);
+    sig3 *= sig3 * sig3;
+    double sig_cut3 = sig_cut * sig_cut * sig_cut;
+    double sig_cut9 = sig_cut3 * sig_cut3 * sig_cut3;
+    return ((16.0 / 3.0) * M_PI * eps * sig3) * ((1.0 / 3.0) * sig_cut9 - sig_cut3) / volume;
+}
+
+// LRC and Ewald self term.  The reference adds one LRC value per unordered pair that is not
+// frozen-frozen and has non-zero mixed parameters -- intramolecular and beyond-cutoff pairs
+// included (lj.c:62-65,188,256).  The value depends only on the two (eps, sigma) types, so the sum is
+// pair-count(type a, type b) * value(a, b): O(N) + O(types^2) instead of O(N^2).
+static void compute_analytic(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    c->lrc_pair = c->lrc_self = c->es_self = 0.0;
+    if (P.rd_lrc) {
+        struct TypeCount {
+            double eps, sig;
+            double total = 0, frozen = 0;
+        };
+        std::map<std::pair<double, double>, int> index;
+        std::vector<TypeCount> types;
+        for (int i = 0; i < c->n; i++) {
+            auto key = std::make_pair(c->heps[i], c->hsig[i]);
+            auto it = index.find(key);
+            int t;
+            if (it == index.end()) {
+                t = (int)types.size();
+                index[key] = t;
+                TypeCount tc;
+                tc.eps = c->heps[i];
+                tc.sig = c->hsig[i];
+                types.push_back(tc);
+            } else
+                t = it->second;
+            types[t].total += 1;
+            if (c->hfrozen[i]) types[t].frozen += 1;
+        }
+        double pair_sum = 0.0, self_sum = 0.0;
+        for (size_t a = 0; a < types.size(); a++) {
+            for (size_t b = a; b < types.size(); b++) {
+                double eps, sigma;
+                host_mix(P.mixing, types[a].eps, types[a].sig, types[b].eps, types[b].sig, eps, sigma);
+                if (!(eps != 0 && sigma != 0)) continue;
+                double npairs;
+                if (a == b)
+                    npairs = 0.5 * types[a].total * (types[a].total - 1) - 0.5 * types[a].frozen * (types[a].frozen - 1);
+                else
+                    npairs = types[a].total * types[b].total - types[a].frozen * types[b].frozen;
+                if (npairs > 0) pair_sum += npairs * lrc_value(eps, sigma, P.cutoff, P.volume);
+            }
+            if (types[a].sig != 0 && types[a].eps != 0) {
+                double mobile = types[a].total - types[a].frozen;
+                if (mobile > 0) self_sum += mobile * lrc_value(types[a].eps, types[a].sig, P.cutoff, P.volume);
+            }
+        }
+        c->lrc_pair = pair_sum;
+        c->lrc_self = self_sum;
+    }
+    if (!P.rd_only) {  // coulombic_self (src/energy/coulombic.c:97-112), same accumulation order
+        double self_potential = 0.0;
+        const double alpha = P.ewald_alpha;
+        for (int i = 0; i < c->n; i++) {
+            if (c->hfrozen[i]) continue;
+            self_potential -= alpha * c->hq[i] * c->hq[i] / sqrt(M_PI);
+        }
+        c->es_self = self_potential;
+    }
+    c->analytic_dirty = false;
+}
+
+// hemisphere of reciprocal vectors, reference enumeration order (coulombic.c:56-60)
+static int build_kvectors(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    const int kmax = P.ewald_kmax;
+    if (kmax + 1 > 16) FAIL(3, "ewald_kmax > 15 not supported");
+    std::vector<int> l0, l1, l2;
+    for (int a = 0; a <= kmax; a++)
+        for (int b = (!a ? 0 : -kmax); b <= kmax; b++)
+            for (int d = ((!a && !b) ? 1 : -kmax); d <= kmax; d++) {
+                if (a * a + b * b + d * d > kmax * kmax) continue;
+                l0.push_back(a);
+                l1.push_back(b);
+                l2.push_back(d);
+            }
+    const int nk = (int)l0.size();
+    if (nk > 2048) FAIL(3, "too many reciprocal vectors (nk > 2048)");
+    std::vector<int> l(3 * (size_t)std::max(nk, 1));
+    std::vector<double> w(std::max(nk, 1)), wf(std::max(nk, 1)), kv(3 * (size_t)std::max(nk, 1));
+    for (int ik = 0; ik < nk; ik++) {
+        int ll[3] = {l0[ik], l1[ik], l2[ik]};
+        double k[3];
+        for (int p = 0; p < 3; p++) {
+            k[p] = 0;
+            for (int q = 0; q < 3; q++) k[p] += 2.0 * M_PI * P.reciprocal_basis[p][q] * ll[q];
+        }
+        const double k2 = k[0] * k[0] + k[1] * k[1] + k[2] * k[2];
+        w[ik] = exp(-k2 / (4.0 * P.ewald_alpha * P.ewald_alpha)) / k2;                  // coulombic.c:86
+        wf[ik] = exp(-k2 / (4.0 * P.polar_ewald_alpha * P.polar_ewald_alpha)) / k2;     // polar_ewald.c:101-103
+        for (int p = 0; p < 3; p++) {
+            l[p * nk + ik] = ll[p];
+            kv[p * nk + ik] = k[p];
+        }
+    }
+    c->nk = nk;
+    if (upload(c->kl, l, c->stream) || upload(c->kweight, w, c->stream) || upload(c->kweight_field, wf, c->stream) ||
+        upload(c->kvec, kv, c->stream))
+        return 11;
+    if (c->sf.ensure(2 * (size_t)std::max(nk, 1))) FAIL(11, "cudaMalloc failed");
+    c->kdirty = false;
+    return 0;
+}
+
+static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_multiple, bool with_aux) {
+    const mpmc_b200_params& P = c->P;
+    s.idx = idx;
+    s.n = (int)idx.size();
+    s.n_pad = std::max(round_up(s.n, pad_multiple), pad_multiple);
+    std::vector<double> x(s.n_pad, 0.0), y(s.n_pad, 0.0), z(s.n_pad, 0.0), q(s.n_pad, 0.0), al(s.n_pad, 0.0), aux(s.n_pad, 0.0);
+    std::vector<int> mol(s.n_pad, -1), fl(s.n_pad, 0), di(s.n_pad, 0);
+    for (int k = 0; k < s.n; k++) {
+        const int g = idx[k];
+        x[k] = c->hx[g];
+        y[k] = c->hy[g];
+        z[k] = c->hz[g];
+        q[k] = c->hq[g];
+        al[k] = c->halpha[g];
+        mol[k] = c->hmol[g];
+        fl[k] = F_VALID | (c->hfrozen[g] ? F_FROZEN : 0);
+        di[k] = g;
+        if (with_aux) aux[k] = (P.damp_type == MPMC_DAMP_LINEAR) ? pow(c->halpha[g], 1.0 / 6.0) : c->hq[g];
+    }
+    if (with_aux && P.damp_type == MPMC_DAMP_LINEAR)
+        for (int k = s.n; k < s.n_pad; k++) aux[k] = 1.0;
+    // distinct pad positions far from each other are not needed: pad sources carry mu = 0 / q = 0 and
+    // every loop over a padded tile is bounded by n
+    cudaStream_t st = c->stream;
+    if (upload(s.x, x, st) || upload(s.y, y, st) || upload(s.z, z, st) || upload(s.q, q, st) || upload(s.alpha, al, st) ||
+        upload(s.aux, aux, st) || upload(s.mol, mol, st) || upload(s.flags, fl, st) || upload(s.didx, di, st))
+        return 11;
+    return 0;
+}
+
+static int repack(Ctx* c) {
+    const int n = c->n;
+    cudaStream_t st = c->stream;
+    c->n_pad = std::max(round_up(n, TILE), TILE);
+    const int np = c->n_pad;
+    auto padded = [&](const std::vector<double>& h) {
+        std::vector<double> v(np, 0.0);
+        std::copy(h.begin(), h.end(), v.begin());
+        return v;
+    };
+    std::vector<int> mol(np, -1), fl(np, 0);
+    for (int i = 0; i < n; i++) {
+        mol[i] = c->hmol[i];
+        fl[i] = F_VALID | (c->hfrozen[i] ? F_FROZEN : 0);
+    }
+    if (upload(c->x, padded(c->hx), st) || upload(c->y, padded(c->hy), st) || upload(c->z, padded(c->hz), st) ||
+        upload(c->q, padded(c->hq), st) || upload(c->eps, padded(c->heps), st) || upload(c->sig, padded(c->hsig), st) ||
+        upload(c->molmass, padded(c->hmm), st) || upload(c->alpha, padded(c->halpha), st) || upload(c->mol, mol, st) ||
+        upload(c->flags, fl, st))
+        return 11;
+
+    // subsets
+    std::vector<int> charged, recip, pol;
+    for (int i = 0; i < n; i++) {
+        if (c->hq[i] != 0.0) {
+            charged.push_back(i);
+            if (!c->hfrozen[i]) recip.push_back(i);  // coulombic.c:74-75
+        }
+        if (c->halpha[i] != 0.0) pol.push_back(i);
+    }
+    const int polpad = TILE * std::max(c->world, 1);
+    if (pack_subset(c, c->charged, charged, TILE, false) || pack_subset(c, c->recip, recip, TILE, false) ||
+        pack_subset(c, c->pol, pol, polpad, true))
+        return 11;
+    c->hperm.assign(c->pol.n_pad, 0);
+    std::iota(c->hperm.begin(), c->hperm.end(), 0);
+
+    // tile pairs of the upper triangle, skipping tile pairs in which every atom is frozen
+    const int nt = np / TILE;
+    std::vector<char> all_frozen(nt, 1);
+    for (int t = 0; t < nt; t++)
+        for (int k = t * TILE; k < std::min(n, (t + 1) * TILE); k++)
+            if (!c->hfrozen[k]) all_frozen[t] = 0;
+    std::vector<int2> tiles;
+    tiles.reserve((size_t)nt * (nt + 1) / 2);
+    // interleave short (near-diagonal-first) ordering is irrelevant: every tile pair costs the same
+    for (int I = 0; I < nt; I++)
+        for (int J = I; J < nt; J++) {
+            if (all_frozen[I] && all_frozen[J]) continue;
+            tiles.push_back(make_int2(I, J));
+        }
+    c->ntiles = (int)tiles.size();
+    if (tiles.empty()) tiles.push_back(make_int2(0, 0));
+    if (upload(c->tiles, tiles, st)) return 11;
+    c->pair_stride = round_up(std::max(c->ntiles, 1), 32);
+    if (c->pair_part.ensure((size_t)PAIR_NPART * c->pair_stride)) FAIL(11, "cudaMalloc failed");
+
+    // reciprocal chunks: about two CTAs per SM
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    const int target = 2 * sms;
+    c->recip_apc = std::max(64, round_up((std::max(c->charged.n, 1) + target - 1) / target, 64));
+    // (chunking is computed per use from the subset actually summed)
+
+    // polarization buffers
+    const int pp = c->pol.n_pad;
+    const int ptiles = pp / TILE;
+    // j-splits so that (row tiles / world) x splits is a few waves of CTAs
+    int rows_tiles = std::max(1, ptiles / std::max(c->world, 1));
+    int js = std::max(1, std::min(ptiles, (4 * sms + rows_tiles - 1) / rows_tiles));
+    c->dipole_jsplits = js;
+    const int ctiles = c->charged.n_pad / TILE;
+    int frows = std::max(1, (np / TILE) / std::max(c->world, 1));
+    c->field_jsplits = std::max(1, std::min(ctiles, (4 * sms + frows - 1) / frows));
+    const size_t gs_splits = (size_t)std::min(ptiles, 148);
+    size_t epart_need = std::max({(size_t)c->field_jsplits * 3 * np, (size_t)c->dipole_jsplits * 3 * pp, gs_splits * 3 * pp});
+    if (c->ef_static.ensure((size_t)3 * np) || c->epart.ensure(epart_need) || c->es.ensure((size_t)3 * pp) ||
+        c->mu.ensure((size_t)3 * pp) || c->mu_old.ensure((size_t)3 * pp) || c->mu_new.ensure((size_t)3 * pp) ||
+        c->eind.ensure((size_t)3 * pp) || c->eic.ensure((size_t)3 * pp) || c->rrms.ensure(pp) ||
+        c->rank_packed.ensure(pp) || c->rmin_part.ensure(ptiles + 8) ||
+        c->field_cnt.ensure((size_t)c->field_jsplits * (np / TILE) + 8))
+        FAIL(11, "cudaMalloc failed");
+    CU(cudaMemsetAsync(c->ef_static.p, 0, sizeof(double) * 3 * np, st));
+    for (DevBuf<double>* b : {&c->es, &c->mu, &c->mu_old, &c->mu_new, &c->eind, &c->eic})
+        CU(cudaMemsetAsync(b->p, 0, sizeof(double) * 3 * pp, st));
+    CU(cudaMemsetAsync(c->rrms.p, 0, sizeof(double) * pp, st));
+    CU(cudaMemsetAsync(c->rank_packed.p, 0, sizeof(double) * pp, st));
+    c->analytic_dirty = true;
+    c->subsets_stale = false;
+    c->have_atoms = true;
+    return 0;
+}
+
+static void shard_range(int total_units, int rank, int world, int& b, int& e) {
+    b = (int)((long long)total_units * rank / world);
+    e = (int)((long long)total_units * (rank + 1) / world);
+}
+
+static void phase_begin(Ctx* c, Phase p) {
+    cudaEventRecord(c->ev[p][0], c->stream);
+    c->ev_used[p] = true;
+}
+static void phase_end(Ctx* c, Phase p) { cudaEventRecord(c->ev[p][1], c->stream); }
+
+static int refresh_subsets(Ctx* c) {
+    if (!c->subsets_stale) return 0;
+    for (Subset* s : {&c->charged, &c->recip, &c->pol}) {
+        if (s->n <= 0) continue;
+        gather_positions_kernel<<<(s->n + 255) / 256, 256, 0, c->stream>>>(c->x.p, c->y.p, c->z.p, s->didx.p, s->n, s->x.p,
+                                                                          s->y.p, s->z.p);
+        c->launches++;
+    }
+    c->subsets_stale = false;
+    return 0;
+}
+
+static AtomsDev atoms_dev(Ctx* c) {
+    AtomsDev a;
+    a.n = c->n;
+    a.n_pad = c->n_pad;
+    a.x = c->x.p;
+    a.y = c->y.p;
+    a.z = c->z.p;
+    a.q = c->q.p;
+    a.eps = c->eps.p;
+    a.sig = c->sig.p;
+    a.molmass = c->molmass.p;
+    a.alpha = c->alpha.p;
+    a.mol = c->mol.p;
+    a.flags = c->flags.p;
+    return a;
+}
+
+static int check_supported(const mpmc_b200_params& P) {
+    if (P.polarization && !P.rd_only) {
+        if (P.polar_ewald_full) FAIL(3, "polar_ewald_full is not implemented in the B200 engine yet (SURVEY 8f f1)");
+        if (!P.polar_iterative && !P.polar_zodid)
+            FAIL(3, "matrix-inversion polarization (polar_iterative off) is out of scope: O(N^3) dense LU");
+        if (!P.polar_zodid && P.polar_precision == 0.0 && P.polar_max_iter <= 0)
+            FAIL(3, "polar_max_iter must be > 0 when polar_precision is 0");
+        if (P.damp_type < 0 || P.damp_type > 2) FAIL(3, "unknown damp_type");
+    }
+    if (P.feynman_hibbs && !(P.temperature > 0.0)) FAIL(3, "feynman_hibbs needs temperature > 0");
+    return 0;
+}
+
+// ---- reciprocal sum over a subset; leaves S(k) in c->sf and (optionally) the energy in a scalar slot
+static int run_structure_factor(Ctx* c, const Subset& sub, const DevBuf<double>& weight, double scale, double* energy_slot,
+                                bool sharded) {
+    KVecDev kv;
+    kv.nk = c->nk;
+    kv.kmax = c->P.ewald_kmax;
+    kv.l = c->kl.p;
+    kv.weight = weight.p;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    const int target = 2 * sms;
+    const int apc = std::max(64, round_up((std::max(sub.n, 1) + target - 1) / target, 64));
+    const int nchunks = std::max(1, (sub.n + apc - 1) / apc);
+    int cb = 0, ce = nchunks;
+    if (sharded) shard_range(nchunks, c->rank, c->world, cb, ce);
+    const int mine = std::max(ce - cb, 0);
+    if (c->sf_partial.ensure((size_t)std::max(mine, 1) * 2 * std::max(c->nk, 1))) FAIL(11, "cudaMalloc failed");
+    if (c->nk > 0 && sub.n > 0 && mine > 0) {
+        launch_recip_sf(make_cell(c->P), sub.dev(), kv, cb, ce, apc, c->sf_partial.p, c->stream);
+        c->launches++;
+    }
+    launch_recip_finish(kv, c->sf_partial.p, (c->nk > 0 && sub.n > 0) ? mine : 0, scale, c->sf.p, energy_slot, c->stream);
+    c->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// ---- polar(): static field + solver + energy.  Enqueue only (precision mode syncs per iteration).
+static int enqueue_polar(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    const Cell cell = make_cell(P);
+    const bool ortho = is_ortho(P);
+    const AtomsDev a = atoms_dev(c);
+    const int np = c->n_pad, pp = c->pol.n_pad;
+    SubsetDev pol = c->pol.dev();
+    unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
+
+    c->pending_iterations = 0;
+    c->pending_iter_success = 0;
+    c->cnt.contractions = 0;
+    c->cnt.n_polarizable = c->pol.n;
+    c->cnt.pairs_dipole = (double)c->pol.n * std::max(c->pol.n - 1, 0);
+
+    // row ranges of this shard (tile aligned)
+    int fb, fe, pb, pe;
+    {
+        int tb, te;
+        shard_range(np / TILE, c->rank, c->world, tb, te);
+        fb = tb * TILE;
+        fe = std::min(te * TILE, c->n);
+        shard_range(pp / TILE, c->rank, c->world, tb, te);
+        pb = tb * TILE;
+        pe = te * TILE;
+    }
+
+    // ---------------- static field: thole_field() (thole_field.c:14-36) ----------------
+    phase_begin(c, PH_FIELD);
+    CU(cudaMemsetAsync(c->ef_static.p, 0, sizeof(double) * 3 * np, st));
+    FieldOpts fo;
+    fo.table = nullptr;
+    fo.table_max = 0;
+    fo.cutoffterm = 0.0;
+    fo.a = 0.0;
+    bool accumulate = false;
+    if (P.polar_ewald) {
+        fo.mode = FIELD_EWALD_REAL;
+        fo.a = P.polar_ewald_alpha;
+        // recip_term(): S(k) over ALL atoms (polar_ewald.c:104-108); zero-charge atoms add exact zeros
+        if (run_structure_factor(c, c->charged, c->kweight_field, 0.0, nullptr, false)) return 10;
+        KVecDev kv;
+        kv.nk = c->nk;
+        kv.kmax = P.ewald_kmax;
+        kv.l = c->kl.p;
+        kv.weight = c->kweight_field.p;
+        launch_recip_field(cell, a, kv, c->kvec.p, c->sf.p, 8.0 * M_PI / P.volume, fb, fe, c->ef_static.p, st);
+        c->launches++;
+        accumulate = true;
+    } else if (P.polar_wolf || P.polar_wolf_full) {
+        const double aa = P.polar_wolf_alpha, R = P.cutoff, rR = 1.0 / R;
+        fo.a = aa;
+        fo.cutoffterm = (erfc(aa * R) * rR * rR + 2.0 * aa * 0.56418958354 * exp(-aa * aa * R * R) * rR);
+        if (aa == 0.0)
+            fo.mode = FIELD_WOLF_A0;
+        else if (P.polar_wolf_alpha_lookup) {
+            fo.mode = FIELD_WOLF_LOOKUP;
+            if (c->wolf_table_alpha != aa || c->wolf_table_cut != P.polar_wolf_alpha_lookup_cutoff) {
+                // polar_wolf_alpha_lookup_init(): src/polarization/polar_wolf_lookup.c:8-26
+                const int tmax = (int)(ceil(P.polar_wolf_alpha_lookup_cutoff) * 1000);
+                std::vector<double> tab(std::max(tmax, 1), 0.0);
+                for (int i = 1; i < tmax; i++) {
+                    double r = (double)i / 1000., rr = 1.0 / r;
+                    tab[i] = erfc(aa * r) * rr * rr + 2.0 * aa * 0.56418958354 * exp(-aa * aa * r * r) * rr;
+                }
+                if (tmax > 1) tab[0] = tab[1];
+                if (upload(c->wolf_table, tab, st)) return 11;
+                c->wolf_table_max = tmax;
+                c->wolf_table_alpha = aa;
+                c->wolf_table_cut = P.polar_wolf_alpha_lookup_cutoff;
+            }
+            fo.table = c->wolf_table.p;
+            fo.table_max = c->wolf_table_max;
+        } else
+            fo.mode = FIELD_WOLF;
+    } else
+        fo.mode = FIELD_NOPBC;
+    if (c->charged.n > 0 && fe > fb) {
+        const int gx = (fe - fb + TILE - 1) / TILE;
+        launch_static_field(cell, ortho, a, c->charged.dev(), fo, fb, fe, c->field_jsplits, c->epart.p, c->field_cnt.p, st);
+        launch_field_reduce(c->epart.p, c->field_jsplits, np, fb, fe, accumulate, c->ef_static.p, st);
+        // work counter: per-CTA counts of (row, charged source) contributions -> one scalar
+        sum_reduce_kernel<<<1, 1024, 0, st>>>(c->field_cnt.p, gx * c->field_jsplits, c->scalars.p + S_FIELDCNT);
+        c->launches += 3;
+    }
+    phase_end(c, PH_FIELD);
+    CU(cudaGetLastError());
+
+    // ---------------- solver: thole_iterative() (thole_iterative.c:168-259) ----------------
+    phase_begin(c, PH_DIPOLE);
+    const double gscale = (!P.polar_sor && !P.polar_esor) ? P.polar_gamma : 1.0;
+    launch_dipole_init(pol, c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st);
+    c->launches++;
+    const bool want_rrms = P.polar_rrms || P.polar_precision > 0;
+    if (!want_rrms) CU(cudaMemsetAsync(c->rrms.p, 0, sizeof(double) * pp, st));
+    CU(cudaMemsetAsync(c->eind.p, 0, sizeof(double) * 3 * pp, st));
+    CU(cudaMemsetAsync(c->eic.p, 0, sizeof(double) * 3 * pp, st));
+    CU(cudaMemsetAsync(c->mu_new.p, 0, sizeof(double) * 3 * pp, st));
+
+    DipoleOpts dop;
+    dop.damp_type = P.damp_type;
+    dop.wolf_full = P.polar_wolf_full;
+    dop.damp = P.polar_damp;
+    UpdateOpts uo;
+    uo.sor = P.polar_sor;
+    uo.esor = P.polar_esor;
+    uo.gamma = P.polar_gamma;
+    uo.save_old = (P.polar_rrms || P.polar_precision > 0 || P.polar_sor || P.polar_esor) ? 1 : 0;
+    uo.do_rrms = want_rrms ? 1 : 0;
+    const bool gs = P.polar_gs || P.polar_gs_ranked;
+    const double allowed = P.polar_precision * P.polar_precision * kDEBYE2SKA * kDEBYE2SKA;
+    const int js = c->dipole_jsplits;
+
+    if (!P.polar_zodid && c->pol.n > 0) {
+        if (gs && c->world > 1) FAIL(3, "Gauss-Seidel polarization is single-GPU only (sequential dependency)");
+        // ---- Gauss-Seidel working set (processing order = hperm) ----
+        SubsetDev g = pol;
+        bool permuted = false;
+        std::vector<double> hrank;
+        if (gs) {
+            std::iota(c->hperm.begin(), c->hperm.end(), 0);
+            if (P.polar_gs_ranked) {
+                // rank metric (pairs.c:337-360) -> host, stable descending order (update_ranking,
+                // thole_iterative.c:143-164: stable bubble sort over all atoms; non-polarizable atoms
+                // are skipped by contract_dipoles so only the relative order of polarizable ones matters)
+                launch_rank_metric(cell, ortho, pol, c->rmin_part.p, c->rank_packed.p, st);
+                c->launches += 3;
+                hrank.resize(pp);
+                CU(cudaMemcpyAsync(hrank.data(), c->rank_packed.p, sizeof(double) * pp, cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+            }
+            if (c->gs.x.ensure(pp) || c->gs.y.ensure(pp) || c->gs.z.ensure(pp) || c->gs.q.ensure(pp) ||
+                c->gs.alpha.ensure(pp) || c->gs.aux.ensure(pp) || c->gs.mol.ensure(pp) || c->gs.flags.ensure(pp) ||
+                c->gs.didx.ensure(pp) || c->perm.ensure(pp) || c->g_es.ensure(3 * (size_t)pp) ||
+                c->g_mu.ensure(3 * (size_t)pp) || c->g_mu_old.ensure(3 * (size_t)pp) || c->g_mu_new.ensure(3 * (size_t)pp) ||
+                c->g_eind.ensure(3 * (size_t)pp) || c->g_eic.ensure(3 * (size_t)pp) || c->g_rrms.ensure(pp))
+                FAIL(11, "cudaMalloc failed");
+        }
+        auto to_gs_space = [&](bool first) -> int {
+            // (re)build the permuted working set from the packed-order arrays
+            if (upload(c->perm, c->hperm, st)) return 11;
+            const int nb = (c->pol.n + 255) / 256;
+            const int n = c->pol.n;
+            permute_kernel<<<nb, 256, 0, st>>>(c->pol.x.p, c->gs.x.p, c->perm.p, n, pp, 1, 0);
+            permute_kernel<<<nb, 256, 0, st>>>(c->pol.y.p, c->gs.y.p, c->perm.p, n, pp, 1, 0);
+            permute_kernel<<<nb, 256, 0, st>>>(c->pol.z.p, c->gs.z.p, c->perm.p, n, pp, 1, 0);
+            permute_kernel<<<nb, 256, 0, st>>>(c->pol.q.p, c->gs.q.p, c->perm.p, n, pp, 1, 0);
+            permute_kernel<<<nb, 256, 0, st>>>(c->pol.alpha.p, c->gs.alpha.p, c->perm.p, n, pp, 1, 0);
+            permute_kernel<<<nb, 256, 0, st>>>(c->pol.aux.p, c->gs.aux.p, c->perm.p, n, pp, 1, 0);
+            permute_int_kernel<<<nb, 256, 0, st>>>(c->pol.mol.p, c->gs.mol.p, c->perm.p, n);
+            permute_kernel<<<nb, 256, 0, st>>>(c->es.p, c->g_es.p, c->perm.p, n, pp, 3, 0);
+            permute_kernel<<<nb, 256, 0, st>>>(c->mu.p, c->g_mu.p, c->perm.p, n, pp, 3, 0);
+            if (!first) {
+                permute_kernel<<<nb, 256, 0, st>>>(c->mu_old.p, c->g_mu_old.p, c->perm.p, n, pp, 3, 0);
+                permute_kernel<<<nb, 256, 0, st>>>(c->mu_new.p, c->g_mu_new.p, c->perm.p, n, pp, 3, 0);
+            }
+            c->launches += first ? 9 : 11;
+            g = pol;
+            g.x = c->gs.x.p;
+            g.y = c->gs.y.p;
+            g.z = c->gs.z.p;
+            g.q = c->gs.q.p;
+            g.alpha = c->gs.alpha.p;
+            g.aux = c->gs.aux.p;
+            g.mol = c->gs.mol.p;
+            CU(cudaGetLastError());
+            return 0;
+        };
+        auto from_gs_space = [&]() -> int {
+            const int nb = (c->pol.n + 255) / 256, n = c->pol.n;
+            permute_kernel<<<nb, 256, 0, st>>>(c->g_mu.p, c->mu.p, c->perm.p, n, pp, 3, 1);
+            permute_kernel<<<nb, 256, 0, st>>>(c->g_mu_old.p, c->mu_old.p, c->perm.p, n, pp, 3, 1);
+            permute_kernel<<<nb, 256, 0, st>>>(c->g_mu_new.p, c->mu_new.p, c->perm.p, n, pp, 3, 1);
+            permute_kernel<<<nb, 256, 0, st>>>(c->g_eind.p, c->eind.p, c->perm.p, n, pp, 3, 1);
+            permute_kernel<<<nb, 256, 0, st>>>(c->g_eic.p, c->eic.p, c->perm.p, n, pp, 3, 1);
+            permute_kernel<<<nb, 256, 0, st>>>(c->g_rrms.p, c->rrms.p, c->perm.p, n, pp, 1, 1);
+            c->launches += 6;
+            CU(cudaGetLastError());
+            return 0;
+        };
+        if (gs) {
+            CU(cudaMemsetAsync(c->g_mu_old.p, 0, sizeof(double) * 3 * pp, st));
+            CU(cudaMemsetAsync(c->g_mu_new.p, 0, sizeof(double) * 3 * pp, st));
+            CU(cudaMemsetAsync(c->g_eind.p, 0, sizeof(double) * 3 * pp, st));
+            CU(cudaMemsetAsync(c->g_eic.p, 0, sizeof(double) * 3 * pp, st));
+            CU(cudaMemsetAsync(c->g_rrms.p, 0, sizeof(double) * pp, st));
+            if (to_gs_space(true)) return 10;
+            permuted = true;
+        }
+
+        int it = 0;
+        bool keep = true;
+        while (keep) {
+            it++;
+            if (it >= kMAX_ITERATION_COUNT && P.polar_precision != 0.0) {  // divergence bail-out (:199-210)
+                if (gs)
+                    reset_dipoles_kernel<<<(c->pol.n + 255) / 256, 256, 0, st>>>(c->pol.n, pp, g.alpha, c->g_es.p, c->g_mu.p,
+                                                                                c->g_eic.p);
+                else
+                    reset_dipoles_kernel<<<(c->pol.n + 255) / 256, 256, 0, st>>>(c->pol.n, pp, pol.alpha, c->es.p, c->mu.p,
+                                                                                c->eic.p);
+                c->launches++;
+                c->pending_iter_success = 1;
+                break;
+            }
+            uo.iteration = it;
+            const bool precision_mode = P.polar_precision != 0.0;
+            if (precision_mode) CU(cudaMemsetAsync(errbits, 0, sizeof(unsigned long long), st));
+            if (gs) {
+                if (uo.save_old) CU(cudaMemcpyAsync(c->g_mu_old.p, c->g_mu.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToDevice, st));
+                launch_gs_sweep(cell, ortho, g, dop, nullptr, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->epart.p, st);
+                c->launches += 2 * (pp / TILE);
+                if (want_rrms || precision_mode) {
+                    gs_check_kernel<<<(c->pol.n + 255) / 256, 256, 0, st>>>(c->pol.n, pp, c->g_mu_new.p, c->g_mu_old.p,
+                                                                          uo.do_rrms, c->g_rrms.p, errbits);
+                    c->launches++;
+                }
+            } else {
+                launch_dipole_contract(cell, ortho, pol, dop, c->mu.p, pb, pe, js, c->epart.p, st);
+                launch_dipole_update(pol, uo, c->epart.p, js, c->es.p, c->mu.p, c->mu_old.p, c->mu_new.p, c->eind.p,
+                                     c->rrms.p, precision_mode ? errbits : nullptr, pb, pe, st);
+                c->launches += 2;
+            }
+            c->cnt.contractions += 1;
+            CU(cudaGetLastError());
+
+            if (!precision_mode)
+                keep = (it != P.polar_max_iter);
+            else {
+                CU(cudaMemcpyAsync(c->h_scalars + S_ERR, c->scalars.p + S_ERR, sizeof(double), cudaMemcpyDeviceToHost, st));
+                CU(cudaStreamSynchronize(st));
+                double worst;
+                memcpy(&worst, c->h_scalars + S_ERR, sizeof(double));
+                keep = worst > allowed;
+            }
+
+            if (P.polar_palmo && !keep) {  // palmo_contraction (:119-141) with the CURRENT mu
+                if (gs) {
+                    launch_dipole_contract(cell, ortho, g, dop, c->g_mu.p, 0, pp, js, c->epart.p, st);
+                    launch_palmo_finish(g, c->epart.p, js, c->g_eind.p, c->g_eic.p, 0, pp, st);
+                } else {
+                    launch_dipole_contract(cell, ortho, pol, dop, c->mu.p, pb, pe, js, c->epart.p, st);
+                    launch_palmo_finish(pol, c->epart.p, js, c->eind.p, c->eic.p, pb, pe, st);
+                }
+                c->launches += 2;
+                c->cnt.contractions += 1;
+            }
+
+            if (gs && P.polar_gs_ranked && keep && it == 1) {
+                // update_ranking (:143-164): from the second sweep on, atoms are processed in stable
+                // descending rank order (the metric is constant within one energy() call)
+                if (from_gs_space()) return 10;
+                std::vector<int> order(c->pol.n);
+                std::iota(order.begin(), order.end(), 0);
+                std::stable_sort(order.begin(), order.end(), [&](int u, int v) { return hrank[u] > hrank[v]; });
+                std::copy(order.begin(), order.end(), c->hperm.begin());
+                if (to_gs_space(false)) return 10;
+            }
+
+            // save the dipoles for the next pass (:242-252)
+            if (gs) {
+                if (uo.sor || uo.esor) {
+                    launch_dipole_commit(g, uo, c->g_mu_old.p, c->g_mu_new.p, c->g_mu.p, 0, pp, st);
+                    c->launches++;
+                }  // else mu already equals new_mu
+            } else {
+                launch_dipole_commit(pol, uo, c->mu_old.p, c->mu_new.p, c->mu.p, pb, pe, st);
+                c->launches++;
+            }
+        }
+        c->pending_iterations = it;
+        if (permuted)
+            if (from_gs_space()) return 10;
+    }
+    phase_end(c, PH_DIPOLE);
+
+    // ---------------- U_pol (polar.c:108-116) and dipole_rrms (polar.c:13-28) ----------------
+    launch_polar_energy(pol, c->mu.p, c->es.p, P.polar_palmo ? c->eic.p : nullptr, c->rrms.p, pb, std::min(pe, c->pol.n),
+                        c->scalars.p + S_POLAR, st);
+    c->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
+    if (!c->have_params) FAIL(2, "mpmc_b200_set_params has not been called");
+    if (!c->have_atoms) FAIL(2, "mpmc_b200_set_atoms has not been called");
+    if (check_supported(c->P)) return 3;
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    CU(cudaSetDevice(c->device));
+    if (c->kdirty)
+        if (build_kvectors(c)) return 10;
+    if (c->analytic_dirty) compute_analytic(c);
+    refresh_subsets(c);
+    c->launches = 0;
+    for (int p = 0; p < PH_COUNT; p++) c->ev_used[p] = false;
+    memset(&c->cnt, 0, sizeof(c->cnt));
+    c->cnt.n_atoms = c->n;
+    c->pending_iterations = 0;
+    c->pending_iter_success = 0;
+    CU(cudaMemsetAsync(c->scalars.p, 0, sizeof(double) * 32, st));
+    phase_begin(c, PH_TOTAL);
+    const Cell cell = make_cell(P);
+    const bool ortho = is_ortho(P);
+
+    if (with_pair_part) {
+        phase_begin(c, PH_PAIR);
+        PairOpts po;
+        po.ewald_alpha = P.ewald_alpha;
+        po.temperature = P.temperature;
+        po.fh_order = P.feynman_hibbs ? (P.feynman_hibbs_order == 2 ? 2 : 4) : 0;
+        po.mixing = P.mixing;
+        po.rd_only = P.rd_only;
+        int tb, te;
+        shard_range(c->ntiles, c->rank, c->world, tb, te);
+        if (te > tb) {
+            launch_pair_energy(cell, ortho, atoms_dev(c), po, c->tiles.p + tb, te - tb, c->pair_part.p, c->pair_stride, st);
+            c->launches++;
+        }
+        launch_pair_reduce(c->pair_part.p, std::max(te - tb, 0), c->pair_stride, c->scalars.p + S_PAIR, st);
+        c->launches++;
+        phase_end(c, PH_PAIR);
+        CU(cudaGetLastError());
+
+        if (P.cavity_autoreject_absolute) {  // energy.c:99-102: a bad contact skips every other term
+            CU(cudaMemcpyAsync(c->h_scalars, c->scalars.p, sizeof(double) * 8, cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            if (c->h_scalars[S_PAIR + 3] < P.cavity_autoreject_scale && c->world == 1) {
+                c->pending = true;
+                c->last_had_polar = false;
+                phase_end(c, PH_TOTAL);
+                return 0;
+            }
+        }
+        if (!P.rd_only) {
+            phase_begin(c, PH_RECIP);
+            c->cnt.kvectors = c->nk;
+            c->cnt.recip_atoms = c->recip.n;
+            if (run_structure_factor(c, c->recip, c->kweight, 4.0 * M_PI / P.volume, c->scalars.p + S_RECIP, true)) return 10;
+            phase_end(c, PH_RECIP);
+        }
+    }
+    c->last_had_polar = false;
+    if (with_polar_part && P.polarization && !P.rd_only) {
+        if (enqueue_polar(c)) return 10;
+        c->last_had_polar = true;
+    }
+    phase_end(c, PH_TOTAL);
+    c->pending = true;
+    return 0;
+}
+
+static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
+    if (!c->pending) FAIL(2, "no evaluation pending");
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->h_scalars, c->scalars.p, sizeof(double) * 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    c->pending = false;
+    for (int p = 0; p < PH_COUNT; p++) {
+        c->phase_ms[p] = 0.f;
+        if (c->ev_used[p]) cudaEventElapsedTime(&c->phase_ms[p], c->ev[p][0], c->ev[p][1]);
+    }
+    const double* h = c->h_scalars;
+    memset(out, 0, sizeof(*out));
+    const bool lead = (c->rank == 0);  // host-side analytic terms are added once (rank 0) in sharded runs
+    out->min_intermolecular_r = h[S_PAIR + 3];
+    c->cnt.pairs_tested = h[S_PAIR + 4];
+    c->cnt.pairs_lj = h[S_PAIR + 5];
+    c->cnt.pairs_es = h[S_PAIR + 6];
+    c->cnt.kernel_launches = c->launches;
+    c->cnt.pairs_field = 0.5 * h[S_FIELDCNT];
+    if (P.cavity_autoreject_absolute && c->world == 1 && h[S_PAIR + 3] < P.cavity_autoreject_scale) {
+        out->autorejected = 1;
+        out->total = kMAXVALUE;
+        return 0;
+    }
+    out->rd_pair = h[S_PAIR + 0];
+    out->rd_lrc = lead ? (c->lrc_pair + c->lrc_self) : 0.0;
+    out->rd = (out->rd_pair + (lead ? c->lrc_pair : 0.0)) + (lead ? c->lrc_self : 0.0);
+    if (!P.rd_only) {
+        out->es_real = h[S_PAIR + 1] - h[S_PAIR + 2];
+        out->es_recip = h[S_RECIP];
+        out->es_self = lead ? c->es_self : 0.0;
+        out->coulombic = out->es_real + out->es_recip + out->es_self;
+    }
+    if (c->last_had_polar) {
+        double pot = h[S_POLAR + 0];
+        if (P.polar_palmo) pot += h[S_POLAR + 1];
+        out->polar = -0.5 * pot;
+        out->dipole_rrms = c->n ? h[S_POLAR + 2] / c->n : 0.0;
+        out->polar_iterations = c->pending_iterations;
+        out->iter_success = c->pending_iter_success;
+    }
+    out->total = out->rd + out->coulombic + out->polar;  // energy.c:194
+    return 0;
+}
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+int mpmc_b200_abi_version(void) { return MPMC_B200_ABI_VERSION; }
+const char* mpmc_b200_last_error(void) { return g_err.c_str(); }
+
+int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
+    if (!out) FAIL(1, "null ctx pointer");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) FAIL(20, "no CUDA device available (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) FAIL(20, "CUDA device ordinal out of range");
+    CU(cudaSetDevice(device));
+    Ctx* c = new Ctx();
+    c->device = device;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->own_stream = true;
+    for (int p = 0; p < PH_COUNT; p++) {
+        CU(cudaEventCreate(&c->ev[p][0]));
+        CU(cudaEventCreate(&c->ev[p][1]));
+    }
+    if (c->scalars.ensure(64)) FAIL(11, "cudaMalloc failed");
+    CU(cudaMallocHost(&c->h_scalars, sizeof(double) * 64));
+    *out = c;
+    return 0;
+}
+
+void mpmc_b200_destroy(mpmc_b200_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (int p = 0; p < PH_COUNT; p++) {
+        cudaEventDestroy(c->ev[p][0]);
+        cudaEventDestroy(c->ev[p][1]);
+    }
+    for (DevBuf<double>* b : {&c->x, &c->y, &c->z, &c->q, &c->eps, &c->sig, &c->molmass, &c->alpha, &c->pair_part, &c->kweight,
+                              &c->kweight_field, &c->kvec, &c->sf_partial, &c->sf, &c->ef_static, &c->epart, &c->es, &c->mu,
+                              &c->mu_old, &c->mu_new, &c->eind, &c->eic, &c->rrms, &c->rank_packed, &c->rmin_part,
+                              &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms,
+                              &c->wolf_table, &c->scalars})
+        b->release();
+    for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();
+    c->tiles.release();
+    c->charged.release();
+    c->recip.release();
+    c->pol.release();
+    c->gs.release();
+    if (c->h_scalars) cudaFreeHost(c->h_scalars);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int mpmc_b200_set_stream(mpmc_b200_ctx* c, void* cuda_stream) {
+    if (!c) FAIL(1, "null ctx");
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    if (cuda_stream) {
+        c->stream = (cudaStream_t)cuda_stream;
+        c->own_stream = false;
+    } else {
+        CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        c->own_stream = true;
+    }
+    return 0;
+}
+
+int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
+    if (!c || !p) FAIL(1, "null argument");
+    const bool repack_needed = c->have_atoms && (p->damp_type != c->P.damp_type);
+    c->P = *p;
+    c->have_params = true;
+    c->kdirty = true;
+    c->analytic_dirty = true;
+    if (check_supported(c->P)) return 3;
+    if (repack_needed) {
+        CU(cudaSetDevice(c->device));
+        if (repack(c)) return 10;
+    }
+    return 0;
+}
+
+int mpmc_b200_set_atoms(mpmc_b200_ctx* c, int n, const double* pos, const double* charge, const double* polarizability,
+                        const double* epsilon, const double* sigma, const double* mol_mass, const int* mol_id,
+                        const int* frozen) {
+    if (!c) FAIL(1, "null ctx");
+    if (!c->have_params) FAIL(2, "call mpmc_b200_set_params before mpmc_b200_set_atoms");
+    if (n < 0 || (n > 0 && (!pos || !charge || !polarizability || !epsilon || !sigma || !mol_mass || !mol_id || !frozen)))
+        FAIL(1, "bad atom arrays");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    c->n = n;
+    c->hx.resize(n), c->hy.resize(n), c->hz.resize(n), c->hq.resize(n), c->halpha.resize(n), c->heps.resize(n);
+    c->hsig.resize(n), c->hmm.resize(n), c->hmol.resize(n), c->hfrozen.resize(n);
+    for (int i = 0; i < n; i++) {
+        c->hx[i] = pos[3 * i];
+        c->hy[i] = pos[3 * i + 1];
+        c->hz[i] = pos[3 * i + 2];
+        c->hq[i] = charge[i];
+        c->halpha[i] = polarizability[i];
+        c->heps[i] = epsilon[i];
+        c->hsig[i] = sigma[i];
+        c->hmm[i] = mol_mass[i];
+        c->hmol[i] = mol_id[i];
+        c->hfrozen[i] = frozen[i] ? 1 : 0;
+    }
+    if (repack(c)) return 10;
+    CU(cudaStreamSynchronize(c->stream));  // uploads read from temporaries
+    return 0;
+}
+
+int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double* pos) {
+    if (!c || !pos) FAIL(1, "null argument");
+    if (!c->have_atoms) FAIL(2, "mpmc_b200_set_atoms has not been called");
+    if (first < 0 || count < 0 || first + count > c->n) FAIL(1, "position range out of bounds");
+    if (count == 0) return 0;
+    CU(cudaSetDevice(c->device));
+    if (c->h_stage_cap < (size_t)3 * count) {
+        if (c->h_stage) {
+            CU(cudaStreamSynchronize(c->stream));
+            cudaFreeHost(c->h_stage);
+        }
+        c->h_stage_cap = (size_t)3 * count + 1024;
+        CU(cudaMallocHost(&c->h_stage, sizeof(double) * c->h_stage_cap));
+    } else {
+        CU(cudaStreamSynchronize(c->stream));  // staging buffer reuse
+    }
+    double *sx = c->h_stage, *sy = sx + count, *sz = sy + count;
+    for (int k = 0; k < count; k++) {
+        sx[k] = c->hx[first + k] = pos[3 * k];
+        sy[k] = c->hy[first + k] = pos[3 * k + 1];
+        sz[k] = c->hz[first + k] = pos[3 * k + 2];
+    }
+    CU(cudaMemcpyAsync(c->x.p + first, sx, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->y.p + first, sy, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->z.p + first, sz, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
+    c->subsets_stale = true;
+    return 0;
+}
+
+int mpmc_b200_set_shard(mpmc_b200_ctx* c, int rank, int world) {
+    if (!c) FAIL(1, "null ctx");
+    if (world < 1 || rank < 0 || rank >= world) FAIL(1, "bad shard");
+    const bool changed = (world != c->world);
+    c->rank = rank;
+    c->world = world;
+    if (changed && c->have_atoms) {
+        CU(cudaSetDevice(c->device));
+        if (repack(c)) return 10;
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    return 0;
+}
+
+int mpmc_b200_energy(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
+    if (!c || !out) FAIL(1, "null argument");
+    if (c->world > 1) FAIL(2, "sharded contexts are driven with mpmc_b200_energy_enqueue / mpmc_b200_polar_stage");
+    int rc = enqueue_energy(c, true, true);
+    if (rc) return rc;
+    return finish_energy(c, out);
+}
+
+int mpmc_b200_polar(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
+    if (!c || !out) FAIL(1, "null argument");
+    if (c->world > 1) FAIL(2, "sharded contexts are driven with mpmc_b200_polar_stage");
+    int rc = enqueue_energy(c, false, true);
+    if (rc) return rc;
+    rc = finish_energy(c, out);
+    if (!rc) {
+        out->rd = out->rd_pair = out->rd_lrc = out->coulombic = out->es_real = out->es_recip = out->es_self = 0.0;
+        out->total = out->polar;
+    }
+    return rc;
+}
+
+int mpmc_b200_energy_enqueue(mpmc_b200_ctx* c) {
+    if (!c) FAIL(1, "null ctx");
+    if (c->world > 1) return enqueue_energy(c, true, false);  // polar part is staged by the caller
+    return enqueue_energy(c, true, true);
+}
+
+int mpmc_b200_energy_finish(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
+    if (!c || !out) FAIL(1, "null argument");
+    return finish_energy(c, out);
+}
+
+int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
+    (void)iteration;
+    if (!c) FAIL(1, "null ctx");
+    (void)stage;
+    FAIL(3, "mpmc_b200_polar_stage: staged multi-GPU polarization is not wired yet");
+}
+
+int mpmc_b200_device_buffer(mpmc_b200_ctx* c, int which, void** dev_ptr, long long* n_doubles) {
+    if (!c || !dev_ptr || !n_doubles) FAIL(1, "null argument");
+    if (!c->have_atoms) FAIL(2, "no atoms");
+    switch (which) {
+        case 0: *dev_ptr = c->mu.p; *n_doubles = 3LL * c->pol.n_pad; break;
+        case 1: *dev_ptr = c->mu_new.p; *n_doubles = 3LL * c->pol.n_pad; break;
+        case 2: *dev_ptr = c->scalars.p; *n_doubles = 32; break;
+        case 3: *dev_ptr = c->ef_static.p; *n_doubles = 3LL * c->n_pad; break;
+        default: FAIL(1, "unknown buffer");
+    }
+    return 0;
+}
+
+int mpmc_b200_shard_rows(mpmc_b200_ctx* c, int* begin, int* end, int* n_pol, int* n_pol_padded) {
+    if (!c) FAIL(1, "null ctx");
+    if (!c->have_atoms) FAIL(2, "no atoms");
+    int tb, te;
+    shard_range(c->pol.n_pad / TILE, c->rank, c->world, tb, te);
+    if (begin) *begin = tb * TILE;
+    if (end) *end = te * TILE;
+    if (n_pol) *n_pol = c->pol.n;
+    if (n_pol_padded) *n_pol_padded = c->pol.n_pad;
+    return 0;
+}
+
+int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, double* ef_induced,
+                              double* ef_induced_change, double* dipole_rrms, double* rank_metric) {
+    if (!c) FAIL(1, "null ctx");
+    if (!c->have_atoms) FAIL(2, "no atoms");
+    CU(cudaSetDevice(c->device));
+    const int n = c->n, np = c->n_pad, pp = c->pol.n_pad;
+    std::vector<double> buf((size_t)3 * std::max(np, pp));
+    auto scatter3 = [&](const DevBuf<double>& d, double* out) -> int {
+        if (!out) return 0;
+        CU(cudaMemcpyAsync(buf.data(), d.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        std::fill(out, out + 3 * (size_t)n, 0.0);
+        for (int k = 0; k < c->pol.n; k++) {
+            const int g = c->pol.idx[k];
+            for (int d3 = 0; d3 < 3; d3++) out[3 * g + d3] = buf[(size_t)d3 * pp + k];
+        }
+        return 0;
+    };
+    if (scatter3(c->mu, mu) || scatter3(c->eind, ef_induced) || scatter3(c->eic, ef_induced_change)) return 10;
+    if (ef_static) {
+        CU(cudaMemcpyAsync(buf.data(), c->ef_static.p, sizeof(double) * 3 * np, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        for (int i = 0; i < n; i++)
+            for (int d3 = 0; d3 < 3; d3++) ef_static[3 * i + d3] = buf[(size_t)d3 * np + i];
+    }
+    auto scatter1 = [&](const DevBuf<double>& d, double* out) -> int {
+        if (!out) return 0;
+        CU(cudaMemcpyAsync(buf.data(), d.p, sizeof(double) * pp, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        std::fill(out, out + n, 0.0);
+        for (int k = 0; k < c->pol.n; k++) out[c->pol.idx[k]] = buf[k];
+        return 0;
+    };
+    if (scatter1(c->rrms, dipole_rrms) || scatter1(c->rank_packed, rank_metric)) return 10;
+    return 0;
+}
+
+int mpmc_b200_get_counters(mpmc_b200_ctx* c, mpmc_b200_counters* out) {
+    if (!c || !out) FAIL(1, "null argument");
+    *out = c->cnt;
+    return 0;
+}
+
+int mpmc_b200_phase_ms(mpmc_b200_ctx* c, const char* phase, double* ms) {
+    if (!c || !phase || !ms) FAIL(1, "null argument");
+    static const char* names[PH_COUNT] = {"pair", "recip", "field", "dipole", "total"};
+    for (int p = 0; p < PH_COUNT; p++)
+        if (!strcmp(phase, names[p])) {
+            *ms = c->phase_ms[p];
+            return 0;
+        }
+    FAIL(1, "unknown phase");
+}
+
+int mpmc_b200_measure_fp64_peak(mpmc_b200_ctx* c, double* tflops) {
+    if (!c || !tflops) FAIL(1, "null argument");
+    CU(cudaSetDevice(c->device));
+    *tflops = measure_fp64_peak_tflops(c->stream);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

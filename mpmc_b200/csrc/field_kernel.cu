@@ -1,0 +1,150 @@
+// field_kernel.cu -- K3: static electric field at every atom from the permanent charges.
+//
+// Row-owned: thread t of CTA (bx, by) keeps atom i = row_begin + bx*128 + t in registers and walks
+// the by-th slice of the compacted CHARGED-atom list staged through shared memory; partial fields go
+// to epart[by][c][i] and are added in slice order by field_reduce (no atomics => deterministic).
+//
+// Reference loops replaced (relative to the reference tree):
+//   thole_field_nopbc()  src/polarization/thole_field.c:39-68
+//   thole_field_wolf()   src/polarization/thole_field.c:71-124 (+ polar_wolf_lookup.c:8-32)
+//   real_term()          src/polarization/polar_ewald.c:38-74
+// For the unordered pair (i<j) the reference adds q_j f(r) d to E_i and subtracts q_i f(r) d from
+// E_j with d = r_i - r_j imaged; per row that is E_i = sum_j q_j f(r_ij) (r_i - r_j)_img.
+#include "kernels.h"
+
+namespace mpmc {
+
+constexpr double kOneOverSqrtPiField = 0.56418958354;  // thole_field.c:10 (truncated constant, kept)
+constexpr double kOneOverSqrtPiEwald = 0.5641895835477562869480794515607725858440506293289988;  // polar_ewald.c:6
+
+template <bool ORTHO, int MODE>
+__global__ void __launch_bounds__(TILE) static_field_kernel(Cell c, AtomsDev a, SubsetDev ch, FieldOpts o, int row_begin,
+                                                            int row_end, int tiles_per_split,
+                                                            double* __restrict__ epart, double* __restrict__ count_part) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], sq[TILE];
+    __shared__ int smol[TILE], sfl[TILE];
+    __shared__ double red[32];
+    const int tid = threadIdx.x;
+    const int i = row_begin + blockIdx.x * TILE + tid;
+    const bool live = i < row_end;
+    const int ii = live ? i : row_begin;
+    const double xi = a.x[ii], yi = a.y[ii], zi = a.z[ii], qi = a.q[ii];
+    const int moli = a.mol[ii], fli = live ? a.flags[ii] : 0;
+
+    double ex = 0.0, ey = 0.0, ez = 0.0;
+    int cnt = 0;
+    const int ntiles = ch.n_pad / TILE;
+    const int t0 = blockIdx.y * tiles_per_split, t1 = min(t0 + tiles_per_split, ntiles);
+    for (int jt = t0; jt < t1; jt++) {
+        __syncthreads();
+        {
+            const int j = jt * TILE + tid;
+            sx[tid] = ch.x[j];
+            sy[tid] = ch.y[j];
+            sz[tid] = ch.z[j];
+            sq[tid] = ch.q[j];
+            smol[tid] = ch.mol[j];
+            sfl[tid] = ch.flags[j];
+        }
+        __syncthreads();
+        for (int jj = 0; jj < TILE; jj++) {
+            const int fj = sfl[jj];
+            if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) continue;  // thole_field.c:49, polar_ewald.c:49
+            const bool same = (moli == smol[jj]);
+            if (MODE != FIELD_EWALD_REAL && same) continue;  // thole_field.c:50
+            double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
+            if (MODE == FIELD_EWALD_REAL && same && dx == 0.0 && dy == 0.0 && dz == 0.0) continue;  // the atom itself
+            min_image<ORTHO>(c, dx, dy, dz);
+            const double r2 = dx * dx + dy * dy + dz * dz;
+            const double r = sqrt(r2);
+            double f;  // E_i += q_j * f * d
+            if (MODE == FIELD_EWALD_REAL) {
+                if ((r > c.cutoff) || (r == 0.0)) continue;  // polar_ewald.c:51
+                const bool excluded = same || (qi == 0.0);   // pair es_excluded (pairs.c:61-77); q_j != 0 by construction
+                const double g = 2.0 * o.a * kOneOverSqrtPiEwald * exp(-o.a * o.a * r2) * r;
+                f = excluded ? (g - erf(o.a * r)) / (r * r2) : (g + erfc(o.a * r)) / (r2 * r);
+            } else {
+                if (!((r - kSMALL_dR < c.cutoff) && (r != 0.0))) continue;  // thole_field.c:55
+                if (MODE == FIELD_NOPBC) {
+                    f = 1.0 / (r * r * r);
+                } else {
+                    const double rr = 1.0 / r;
+                    if (MODE == FIELD_WOLF_A0) {
+                        const double rR = 1.0 / c.cutoff;
+                        f = (rr * rr - rR * rR) * rr;
+                    } else {
+                        double bigmess;
+                        if (MODE == FIELD_WOLF_LOOKUP) {  // polar_wolf_lookup.c:28-32 (truncating index)
+                            const int kx = (int)(r * 1000);
+                            bigmess = (kx >= o.table_max) ? 0.0 : o.table[kx];
+                        } else {
+                            bigmess = erfc(o.a * r) * rr * rr + 2.0 * o.a * kOneOverSqrtPiField * exp(-o.a * o.a * r * r) * rr;
+                        }
+                        f = (bigmess - o.cutoffterm) * rr;
+                    }
+                }
+            }
+            const double qf = sq[jj] * f;
+            ex += qf * dx;
+            ey += qf * dy;
+            ez += qf * dz;
+            cnt++;
+        }
+    }
+    if (live) {
+        double* e = epart + (size_t)blockIdx.y * 3 * a.n_pad;
+        e[0 * a.n_pad + i] = ex;
+        e[1 * a.n_pad + i] = ey;
+        e[2 * a.n_pad + i] = ez;
+    }
+    if (count_part) {
+        double v = block_reduce<0>((double)cnt, red);
+        if (tid == 0) count_part[blockIdx.y * gridDim.x + blockIdx.x] = v;
+    }
+}
+
+__global__ void field_reduce_kernel(const double* __restrict__ epart, int jsplits, int n_pad, int row_begin, int row_end,
+                                    int accumulate, double* __restrict__ ef) {
+    const int i = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= row_end) return;
+    for (int cdim = 0; cdim < 3; cdim++) {
+        double acc = accumulate ? ef[cdim * n_pad + i] : 0.0;
+        for (int js = 0; js < jsplits; js++) acc += epart[((size_t)js * 3 + cdim) * n_pad + i];
+        ef[cdim * n_pad + i] = acc;
+    }
+}
+
+void launch_static_field(const Cell& c, bool ortho, const AtomsDev& a, const SubsetDev& charged, const FieldOpts& o,
+                         int row_begin, int row_end, int jsplits, double* epart, double* count_part, cudaStream_t s) {
+    const int rows = row_end - row_begin;
+    if (rows <= 0) return;
+    const int ntiles = charged.n_pad / TILE;
+    const int tps = (ntiles + jsplits - 1) / jsplits;
+    dim3 grid((rows + TILE - 1) / TILE, jsplits);
+#define LAUNCH(ORTHO, MODE)                                                                                         \
+    static_field_kernel<ORTHO, MODE><<<grid, TILE, 0, s>>>(c, a, charged, o, row_begin, row_end, tps, epart, count_part)
+#define DISPATCH(ORTHO)                                     \
+    switch (o.mode) {                                       \
+        case FIELD_NOPBC: LAUNCH(ORTHO, FIELD_NOPBC); break; \
+        case FIELD_WOLF_A0: LAUNCH(ORTHO, FIELD_WOLF_A0); break; \
+        case FIELD_WOLF: LAUNCH(ORTHO, FIELD_WOLF); break;  \
+        case FIELD_WOLF_LOOKUP: LAUNCH(ORTHO, FIELD_WOLF_LOOKUP); break; \
+        default: LAUNCH(ORTHO, FIELD_EWALD_REAL);           \
+    }
+    if (ortho) {
+        DISPATCH(true)
+    } else {
+        DISPATCH(false)
+    }
+#undef DISPATCH
+#undef LAUNCH
+}
+
+void launch_field_reduce(const double* epart, int jsplits, int n_pad, int row_begin, int row_end, bool accumulate,
+                         double* ef, cudaStream_t s) {
+    const int rows = row_end - row_begin;
+    if (rows <= 0) return;
+    field_reduce_kernel<<<(rows + 255) / 256, 256, 0, s>>>(epart, jsplits, n_pad, row_begin, row_end, accumulate ? 1 : 0, ef);
+}
+
+}  // namespace mpmc

@@ -1,0 +1,120 @@
+// kernels.h -- host-callable launchers of the sm_100a kernels (one per reference loop).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "common.cuh"
+
+namespace mpmc {
+
+enum : int { F_FROZEN = 1, F_VALID = 2 };
+
+// All atoms, reference list order, padded to a multiple of TILE (pad atoms have flags == 0).
+struct AtomsDev {
+    int n, n_pad;
+    double *x, *y, *z, *q, *eps, *sig, *molmass, *alpha;
+    int *mol, *flags;
+};
+
+// A compacted subset of atoms (charged atoms for the static field, charged mobile atoms for the
+// structure factor, polarizable atoms for the dipole solve), padded to a multiple of TILE.
+struct SubsetDev {
+    int n, n_pad;
+    double *x, *y, *z, *q, *alpha;
+    double *aux;  // dipole kernels: alpha^(1/6) for linear damping, the charge for damping off
+    int *mol, *flags, *idx;  // idx = index in AtomsDev
+};
+
+// ---- K1: fused LJ(+FH) + Ewald real(+FH) + intramolecular erf + min distance ------------------
+// replaces pair_exclusions/minimum_image (src/energy/pairs.c:56-290), the pair loops of lj()
+// (src/energy/lj.c:181-260) and coulombic_real() (src/energy/coulombic.c:159-191), and
+// cavity_absolute_check() (src/energy/energy.c:49-64).
+struct PairOpts {
+    double ewald_alpha, temperature;
+    int fh_order;  // 0 = off, 2, 4
+    int mixing;
+    int rd_only;
+};
+constexpr int PAIR_NPART = 8;  // rd, es, intra, min_r, n_tested, n_lj, n_es, (unused)
+void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const int2* tiles, int ntiles,
+                        double* partial /*[PAIR_NPART][ntiles_stride]*/, int stride, cudaStream_t s);
+void launch_pair_reduce(const double* partial, int ntiles, int stride, double* out /*[PAIR_NPART]*/, cudaStream_t s);
+
+// ---- K2: reciprocal-space structure factor -----------------------------------------------------
+// replaces coulombic_reciprocal() (src/energy/coulombic.c:42-95)
+struct KVecDev {
+    int nk, kmax;
+    int* l;          // [3][nk]
+    double* weight;  // exp(-k^2/4a^2)/k^2
+};
+void launch_recip_sf(const Cell& c, const SubsetDev& atoms, const KVecDev& kv, int chunk_begin, int chunk_end,
+                     int atoms_per_chunk, double* sf_partial /*[nchunks][2][nk]*/, cudaStream_t s);
+void launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale,
+                         double* sf /*[2][nk]*/, double* energy_out, cudaStream_t s);
+// recip_term() of the Ewald static field (src/polarization/polar_ewald.c:78-132)
+void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, const double* kvec /*[3][nk]*/,
+                        const double* sf, double scale, int row_begin, int row_end, double* ef /*[3][n_pad]*/,
+                        cudaStream_t s);
+
+// ---- K3: static field --------------------------------------------------------------------------
+// replaces thole_field_nopbc / thole_field_wolf (src/polarization/thole_field.c:39-124) and
+// real_term() (src/polarization/polar_ewald.c:38-74)
+enum : int { FIELD_NOPBC = 0, FIELD_WOLF_A0 = 1, FIELD_WOLF = 2, FIELD_WOLF_LOOKUP = 3, FIELD_EWALD_REAL = 4 };
+struct FieldOpts {
+    int mode;
+    double a;           // polar_wolf_alpha or polar_ewald_alpha
+    double cutoffterm;  // wolf: value of the kernel at R_c
+    const double* table;
+    int table_max;
+};
+void launch_static_field(const Cell& c, bool ortho, const AtomsDev& a, const SubsetDev& charged, const FieldOpts& o,
+                         int row_begin, int row_end, int jsplits, double* epart /*[jsplits][3][n_pad]*/,
+                         double* count_part, cudaStream_t s);
+// ef[c][i] (+)= sum_js epart[js][c][i]
+void launch_field_reduce(const double* epart, int jsplits, int n_pad, int row_begin, int row_end, bool accumulate,
+                         double* ef, cudaStream_t s);
+
+// ---- K4/K5: matrix-free dipole field tensor contraction and dipole update -----------------------
+// replaces thole_amatrix() (src/polarization/thole_matrix.c:38-146) and contract_dipoles(),
+// palmo_contraction() (src/polarization/thole_iterative.c:27-59,119-141)
+struct DipoleOpts {
+    int damp_type;
+    int wolf_full;
+    double damp;  // polar_damp
+};
+void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu /*[3][n_pad]*/,
+                            int row_begin, int row_end, int jsplits, double* epart /*[jsplits][3][n_pad]*/,
+                            cudaStream_t s);
+struct UpdateOpts {
+    int sor, esor, save_old, do_rrms;
+    double gamma;
+    int iteration;
+};
+// E_ind = sum_js epart; new_mu = alpha (E_s + E_ind); max (new-old)^2; rrms.  Does not touch mu.
+void launch_dipole_update(const SubsetDev& pol, const UpdateOpts& o, const double* epart, int jsplits, const double* es,
+                          const double* mu, double* mu_old, double* mu_new, double* eind, double* rrms,
+                          unsigned long long* max_err2_bits, int row_begin, int row_end, cudaStream_t s);
+// mu = new_mu | SOR | ESOR mix (src/polarization/thole_iterative.c:242-252)
+void launch_dipole_commit(const SubsetDev& pol, const UpdateOpts& o, const double* mu_old, const double* mu_new,
+                          double* mu, int row_begin, int row_end, cudaStream_t s);
+// mu0 = gamma alpha E_s (init_dipoles, thole_iterative.c:13-25); also gathers E_s into packed order
+void launch_dipole_init(const SubsetDev& pol, const double* ef_static /*[3][atoms n_pad]*/, int atoms_n_pad,
+                        double gamma_scale, double* es /*[3][pol n_pad]*/, double* mu, int row_begin, int row_end,
+                        cudaStream_t s);
+// ef_induced_change = -ef_induced + sum_js epart (palmo)
+void launch_palmo_finish(const SubsetDev& pol, const double* epart, int jsplits, const double* eind, double* eic,
+                         int row_begin, int row_end, cudaStream_t s);
+// out[0] = sum mu.E_s, out[1] = sum mu.eic, out[2] = sum finite rrms   (fixed-order, one CTA)
+void launch_polar_energy(const SubsetDev& pol, const double* mu, const double* es, const double* eic, const double* rrms,
+                         int row_begin, int row_end, double* out, cudaStream_t s);
+
+// Gauss-Seidel sweep (polar_gs / polar_gs_ranked): blocked forward substitution in `order`.
+void launch_gs_sweep(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const int* order,
+                     const double* es, double* mu, double* mu_new, double* eind, double* scratch, cudaStream_t s);
+// rank metric of pairs() (src/energy/pairs.c:337-360)
+void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank /*[pol n_pad]*/,
+                        cudaStream_t s);
+
+// fp64 FMA throughput probe
+double measure_fp64_peak_tflops(cudaStream_t s);
+
+}  // namespace mpmc

@@ -32,12 +32,15 @@ CO2_LIKE = [
     ("O", +1.16, 15.999, -0.35, 0.0, 79.0, 3.05),
     ("O", -1.16, 15.999, -0.35, 0.0, 79.0, 3.05),
 ]
-# framework "elements" (name, mass, alpha, epsilon, sigma): typical PHAST/UFF-like values
+# framework "elements" (name, mass, alpha, epsilon, sigma): UFF-like LJ values; polarizabilities are
+# the usual C/O/H/Cu point polarizabilities (1.2886, 0.852, 0.4138, 2.1963 A^3) halved, which makes the
+# synthetic scaffold's Thole iteration matrix contractive (spectral radius ~0.73, so the Jacobi solve
+# of the reference converges; with the full values on this artificial geometry it diverges).
 FRAMEWORK_TYPES = [
-    ("C", 12.011, 1.28860, 52.84, 3.431),
-    ("O", 15.999, 0.85200, 30.19, 3.118),
-    ("H", 1.008, 0.41380, 22.14, 2.571),
-    ("CU", 63.546, 2.19630, 2.516, 3.114),
+    ("C", 12.011, 0.64430, 52.84, 3.431),
+    ("O", 15.999, 0.42600, 30.19, 3.118),
+    ("H", 1.008, 0.20690, 22.14, 2.571),
+    ("CU", 63.546, 1.09815, 2.516, 3.114),
 ]
 
 
@@ -109,48 +112,36 @@ def co2_fluid(n_mol: int = 4096, seed: int = SEED + 1) -> System:
     return _assemble([part], p, f"co2_fluid_{n_mol * 3}")
 
 
-def mof_h2(cells=(6, 6, 2), cell_edge: float = 21.398, n_h2: Optional[int] = None, seed: int = SEED + 2,
+def mof_h2(cells=(9, 9, 3), cell_edge: float = 21.398 * 2.0 / 3.0, n_h2: Optional[int] = None, seed: int = SEED + 2,
            cutoff: float = 8.0, polar_max_iter: int = 10, polar_precision: float = 0.0) -> System:
-    """M4-like synthetic MOF supercell + H2: a frozen, neutral, polarizable rod-and-node scaffold
-    (one frozen molecule, listed first, as MOF PQR files do) filled with H2-BSSP molecules.
-    Defaults give N = 63,360 atoms in a 128.388 x 128.388 x 42.796 A box (18,000 frozen atoms,
-    9,072 H2 => 45,216 polarizable sites), options of sample_configs_gpu/3_PCN61/iter.inp
-    (FH4, exponential damping 2.1304, pbc_cutoff 8.0, Jacobi, bare-Coulomb static field)."""
+    """M4-like synthetic MOF supercell + H2: a frozen, neutral, polarizable open scaffold (one frozen
+    molecule, listed first, as MOF PQR files do) filled with H2-BSSP molecules.  Defaults give
+    N ~ 63k atoms in a 128.388 x 128.388 x 42.796 A box (~18k frozen atoms, 9,072 H2 => ~45k
+    polarizable sites), options of sample_configs_gpu/3_PCN61/iter.inp (FH4, exponential damping
+    2.1304, pbc_cutoff 8.0, Jacobi, bare-Coulomb static field)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     cells = np.asarray(cells)
     box = cells * cell_edge
-    # --- scaffold: for every cell, three rods (x,y,z edges) of 4 chains x 15 atoms + a 70-atom node cluster
-    pts, kinds = [], []
-    chain_off = 0.95
-    for ix in range(cells[0]):
-        for iy in range(cells[1]):
-            for iz in range(cells[2]):
-                origin = np.array([ix, iy, iz]) * cell_edge
-                for ax in range(3):
-                    u = np.zeros(3)
-                    u[ax] = 1.0
-                    v = np.roll(u, 1)
-                    w = np.roll(u, 2)
-                    t = 3.4 + np.arange(15) * ((cell_edge - 6.8) / 14.0)
-                    for sv, sw in ((1, 1), (1, -1), (-1, 1), (-1, -1)):
-                        p = origin + t[:, None] * u + chain_off * (sv * v + sw * w)
-                        pts.append(p)
-                        kinds.append(np.where(np.arange(15) % 3 == 2, 2, 0) if sv == sw else np.where(
-                            np.arange(15) % 4 == 1, 1, 0))
-                # node: 70 atoms on two shells around the vertex, min separation enforced below
-                shell = _random_unit_vectors(rng, 400)
-                rad = np.where(np.arange(400) % 2 == 0, 1.9, 3.0)
-                cand = origin + shell * rad[:, None]
-                chosen = []
-                for cpt in cand:
-                    if all(np.linalg.norm(cpt - o) > 1.35 for o in chosen):
-                        chosen.append(cpt)
-                    if len(chosen) == 70:
-                        break
-                chosen = np.array(chosen)
-                pts.append(chosen)
-                k = np.where(np.arange(len(chosen)) % 9 == 0, 3, np.where(np.arange(len(chosen)) % 2 == 0, 1, 0))
-                kinds.append(k)
+    # --- scaffold: sites of a simple-cubic grid (spacing = cell_edge/10 ~ 1.43 A, a bonded distance).
+    # Every cell edge carries a hollow rod of three single-file chains, 2.85 A apart, so an atom has
+    # two bonded neighbours (more only where rods cross) -- a dense solid rod makes the Thole
+    # iteration matrix expansive (Jacobi diverges), a chain-like one does not.  Sites are jittered
+    # by < 0.1 A.
+    m = 10
+    ag = cell_edge / m
+    gi = np.stack(np.meshgrid(np.arange(cells[0] * m), np.arange(cells[1] * m), np.arange(cells[2] * m),
+                              indexing="ij"), -1).reshape(-1, 3)
+    loc = gi % m
+    off = np.where(loc > m // 2, loc - m, loc)  # signed offset from the nearest lower/upper cell face
+    keep = np.zeros(gi.shape[0], dtype=bool)
+    for ax in range(3):
+        o1, o2 = off[:, (ax + 1) % 3], off[:, (ax + 2) % 3]
+        keep |= ((np.abs(o1) == 1) & (np.abs(o2) == 1)) & ~((o1 == -1) & (o2 == -1))  # 3 of the 4 corner chains
+    gi = gi[keep]
+    h = (gi[:, 0] * 73856093) ^ (gi[:, 1] * 19349663) ^ (gi[:, 2] * 83492791)
+    kind = np.select([h % 20 == 0, h % 20 < 5, h % 20 < 12], [3, 1, 2], default=0)  # 5% Cu, 20% O, 35% H, 40% C
+    pts = [gi * ag + rng.uniform(-0.07, 0.07, size=gi.shape)]
+    kinds = [kind]
     fpos = np.concatenate(pts)
     fkind = np.concatenate(kinds).astype(int)
     fpos = fpos - 0.5 * box  # centre the box on the origin
@@ -168,7 +159,7 @@ def mof_h2(cells=(6, 6, 2), cell_edge: float = 21.398, n_h2: Optional[int] = Non
     from scipy.spatial import cKDTree
 
     if n_h2 is None:
-        n_h2 = int(round(9072 * np.prod(cells) / 72.0))
+        n_h2 = int(round(9072 * np.prod(cells) / 243.0))
     wrap = lambda x: (x + 0.5 * box) % box
     ftree = cKDTree(wrap(fpos), boxsize=box)
     centres = np.zeros((0, 3))

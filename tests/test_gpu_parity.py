@@ -1,0 +1,120 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libmpmc_b200.so via ctypes), against
+(a) fixtures generated from the unmodified reference and (b) the CPU oracle on the same seeded
+inputs, plus size-independent properties at BASELINE.json's full sizes."""
+import numpy as np
+import pytest
+
+from mpmc_b200 import systems
+from tests import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+
+CASES = gu.case_names()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_cuda_matches_reference_fixture(engine, name):
+    s, exp = gu.load(name)
+    engine.set_system(s)
+    got = engine.energy()
+    gu.assert_energies(got.to_dict(), exp, rtol=1e-10, label=name)
+    if s.params.polarization and not s.params.rd_only and not got.autorejected:
+        arr = engine.atom_arrays()
+        gu.assert_atom_arrays(arr, exp, s, rtol=1e-10, label=name)
+    assert engine.counters().kernel_launches > 0
+
+
+@pytest.mark.parametrize("builder,kw", [
+    (systems.h2_fluid, dict(n_atoms=4000)),
+    (systems.co2_fluid, dict(n_mol=1500)),
+    (systems.mof_h2, dict(cells=(3, 3, 1))),
+])
+def test_cuda_matches_oracle_midsize(engine, builder, kw):
+    from oracle import oracle
+
+    s = builder(**kw)
+    engine.set_system(s)
+    got = engine.energy()
+    exp, _, oarr = oracle.energy(s, nthreads=0)
+    gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=s.name)
+    if s.params.polarization:
+        gu.assert_atom_arrays(engine.atom_arrays(), oarr, s, rtol=1e-10, label=s.name)
+
+
+def test_polar_entry_point(engine):
+    s, exp = gu.load("mixed_default")
+    engine.set_system(s)
+    got = engine.polar()
+    assert abs(got.polar - exp["polar"]) <= 1e-10 * abs(exp["polar"])
+    assert got.total == got.polar and got.rd == 0.0
+
+
+def test_determinism_and_partial_update(engine):
+    """Same inputs => bit-identical outputs; moving one molecule through set_positions equals a
+    full re-upload of the moved system."""
+    s = systems.h2_fluid(2000)
+    engine.set_system(s)
+    a = engine.energy().to_dict()
+    b = engine.energy().to_dict()
+    assert a == b
+    moved = s.copy()
+    moved.pos[35:40] += np.array([0.11, -0.07, 0.05])
+    engine.set_positions(35, moved.pos[35:40])
+    c = engine.energy().to_dict()
+    engine.set_system(moved)
+    d = engine.energy().to_dict()
+    assert c == d and c != a
+    engine.set_positions(35, s.pos[35:40])
+    engine.set_system(s)
+    assert engine.energy().to_dict() == a
+
+
+def test_lattice_translation_invariance_full_size(engine):
+    """BASELINE config 4 size (63k atoms, polarizable): translating every atom by a lattice vector,
+    or one molecule by a lattice vector, leaves every energy term unchanged (minimum image +
+    periodic structure factor), to rounding."""
+    s = systems.mof_h2(polar_max_iter=3)
+    assert s.n > 60000
+    engine.set_system(s)
+    e0 = engine.energy()
+    shifted = s.copy()
+    basis = np.array(s.params.to_dict()["basis"])
+    shifted.pos[-5:] += basis[1]  # last H2 molecule moved by one lattice vector
+    engine.set_system(shifted)
+    e1 = engine.energy()
+    for k in ("rd", "polar", "es_recip"):
+        a, b = getattr(e0, k), getattr(e1, k)
+        assert abs(a - b) <= 1e-9 * abs(a), (k, a, b)
+    floor = 1e-12 * abs(e0.es_real)
+    assert abs(e0.coulombic - e1.coulombic) <= 1e-9 * abs(e0.coulombic) + floor
+    assert e0.polar_iterations == 3 and e0.polar < 0
+    c = engine.counters()
+    assert c.n_polarizable > 45000 and c.pairs_dipole == float(c.n_polarizable) * (c.n_polarizable - 1)
+
+
+def test_edge_cases(engine):
+    from mpmc_b200.api import System, default_params
+
+    # two atoms, no charges, no polarizability: pure LJ (reference lenard_jones test geometry)
+    p = default_params(np.eye(3) * 20.0)
+    p.rd_lrc = 0
+    s = System(p, [[0, 0, 0], [5, 5, 5]], [0, 0], [0, 0], [128.326802, 128.326802], [3.371914, 3.371914], [39.948, 39.948],
+               [0, 1], [0, 0])
+    engine.set_system(s)
+    e = engine.energy()
+    assert f"{e.rd:.5f}" == "-1.78212"  # mpmc_testing/tests/lenard_jones_test.txt
+    assert e.coulombic == 0.0 and e.polar == 0.0
+    # a single atom: no pairs at all
+    s1 = System(p, [[1, 2, 3]], [0.5], [0.0], [10.0], [3.0], [1.0], [0], [0])
+    engine.set_system(s1)
+    e = engine.energy()
+    assert e.rd == 0.0 and np.isfinite(e.total)
+    # exactly one full tile and one tile + 1 atom (padding boundaries)
+    for n in (640, 645):
+        sN = systems.h2_fluid(n)
+        from oracle import oracle
+
+        engine.set_system(sN)
+        got = engine.energy()
+        exp, _, _ = oracle.energy(sN, nthreads=0)
+        gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=f"n={n}")
