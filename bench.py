@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py -- the per-MC-step energy hot path (LJ + Ewald + iterative Thole) on B200.
+
+One "step" = one full energy() evaluation of the workload (what one MC trial move costs in the
+reference: src/mc/mc.c:302 calls energy() once per step and energy() recomputes everything).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+Own arm (default): the CUDA engine behind the C ABI (mpmc_b200/lib/libmpmc_b200.so).
+  value  : Gpair-interactions/s, device-timed (CUDA events), system resident in HBM
+  e2e    : same metric through the reference-facing call with HOST buffers: every step copies all
+           atom positions host->device, evaluates, and reads energies + per-atom mu / fields back
+  roofline: the dominant kernel (K4 dipole-tensor contraction), algorithmic fp64 flops per launch
+           (126 flop per ordered polarizable pair) / mean launch time (CUDA events on the
+           launching stream) against the fp64 FMA peak measured on this GPU in the same run
+  cpu_baseline: the unmodified reference (oracle/_ref) or the oracle port, on the host cores
+Reference arm (--impl reference): the reference's own CPU energy() on the host cores.
+
+The oracle/ directory is used ONLY for cpu_baseline and --impl reference (it is the thing timed
+there, never a fallback for the CUDA path).  Nothing here reads /root/reference at run time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "pair_interactions_per_second"
+UNIT = "Gpair/s"
+
+# algorithmic fp64 flops per unit of work
+FLOP_GEOM, FLOP_PAIR_FH4, FLOP_PAIR, FLOP_FIELD, FLOP_DIPOLE, FLOP_RECIP = 51.0, 369.0, 153.0, 81.0, 126.0, 49.0
+
+
+def build_workload(name: str):
+    """Synthetic systems of BASELINE.json's configs."""
+    from mpmc_b200 import systems
+
+    if name == "mof_h2_63k":  # config 4: MOF supercell + H2, ~63k atoms, full polarizable energy, Jacobi x10
+        return systems.mof_h2()
+    if name == "mof_h2_42k":
+        return systems.mof_h2(cells=(9, 6, 3))
+    if name == "mof_h2_7k":
+        return systems.mof_h2(cells=(3, 3, 3))
+    if name == "co2_fluid_12k":  # config 2
+        return systems.co2_fluid(4096)
+    if name.startswith("h2_fluid_"):  # config 5 sweep
+        return systems.h2_fluid(int(name.split("_")[-1]))
+    raise SystemExit(f"unknown workload {name}")
+
+
+def pair_interactions(cnt) -> float:
+    """the pair terms the reference evaluates in one energy() call."""
+    return (cnt.pairs_lj + cnt.pairs_es + cnt.pairs_field + 0.5 * cnt.pairs_dipole * cnt.contractions)
+
+
+def algorithmic_flops(cnt, fh: bool) -> float:
+    per_cut = FLOP_PAIR_FH4 if fh else FLOP_PAIR
+    return (FLOP_GEOM * cnt.pairs_tested + per_cut * max(cnt.pairs_lj, cnt.pairs_es) + FLOP_FIELD * cnt.pairs_field +
+            FLOP_DIPOLE * cnt.pairs_dipole * cnt.contractions + FLOP_RECIP * cnt.kvectors * cnt.recip_atoms)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU side: the reference's own implementation (oracle/_ref) or the oracle port, on the host cores
+# ------------------------------------------------------------------------------------------------
+def _cpu_sample_system(workload: str, budget_s: float, calls: int):
+    """A bounded sample of the workload: the same generator and options on a smaller supercell, so
+    that `calls` evaluations of the O(N^2) CPU path fit in `budget_s` (2.1e-7 N^2 s per reference
+    call on one core of this class of host, from the 1,236-atom sample: 0.32 s)."""
+    from mpmc_b200 import systems
+
+    if workload.startswith("mof_h2"):
+        for cells in ((3, 3, 3), (3, 3, 2), (2, 2, 2), (2, 2, 1)):
+            n = int(round(63549 * cells[0] * cells[1] * cells[2] / 243.0))
+            if 2.1e-7 * n * n * calls <= budget_s or cells == (2, 2, 1):
+                return systems.mof_h2(cells=cells), f"mof_h2 supercell {cells[0]}x{cells[1]}x{cells[2]} of the 9x9x3 workload"
+    if workload.startswith("co2_fluid"):
+        for m in (1728, 1000, 512):
+            if 0.5e-7 * (3 * m) ** 2 * calls <= budget_s or m == 512:
+                return systems.co2_fluid(m), f"co2_fluid with {m} molecules"
+    for n in (4000, 2000, 1000):
+        if 2.1e-7 * n * n * calls <= budget_s or n == 1000:
+            return systems.h2_fluid(n), f"h2_fluid with {n} atoms"
+
+
+def _sample_pairs(sample) -> float:
+    """Pair interactions of one energy() call on the sample (oracle counters; untimed bookkeeping)."""
+    from oracle import oracle
+
+    _, cnt, _ = oracle.energy(sample, nthreads=0)
+    return pair_interactions(cnt), cnt
+
+
+def run_cpu_reference(workload: str, steps: int, warmup: int, budget_s: float = 120.0):
+    """Times energy() of the reference on the host cores.  With oracle/_ref present: the UNMODIFIED
+    reference (single-threaded C, as shipped) as `cores` independent replicas, one per host core --
+    the reference's own parallel mode (MPI replicas, src/mc/mc.c:431).  Otherwise the OpenMP oracle
+    port on all cores.  Returns dict(value Gpair/s, cores, kind, sample, ms_per_step)."""
+    from mpmc_b200 import systems
+    from oracle import oracle
+
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    sample, what = _cpu_sample_system(workload, budget_s, steps + warmup)
+    pairs, cnt = _sample_pairs(sample)
+    if os.path.exists(oracle.REF_DRIVER):
+        # memory of the reference: 200 B per pair_t + 72 N^2 B for the A matrix
+        per_proc = sample.n * sample.n * (100.0 + 72.0) + 1e9
+        try:
+            avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
+        except Exception:
+            avail = 64e9
+        nproc = int(max(1, min(cores, 0.7 * avail // per_proc)))
+        with tempfile.TemporaryDirectory(prefix="mpmc_ref_") as tmp:
+            procs = []
+            for r in range(nproc):
+                wd = os.path.join(tmp, f"r{r}")
+                inp = systems.write_reference_case(sample, wd)
+                procs.append(subprocess.Popen([oracle.REF_DRIVER, os.path.basename(inp), str(steps), str(warmup)], cwd=wd,
+                                              stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True))
+            secs = []
+            for p in procs:
+                out, _ = p.communicate()
+                t = [l for l in out.splitlines() if l.startswith("timing seconds_per_energy")]
+                if p.returncode != 0 or not t:
+                    raise RuntimeError("ref_driver failed:\n" + out[-2000:])
+                secs.append(float(t[-1].split()[2]))
+        sec = max(secs)  # replicas run concurrently: the slowest one bounds the step
+        return dict(value=nproc * pairs / sec / 1e9, cores=nproc, kind="reference", ms_per_step=sec * 1e3,
+                    sample=f"{what} (N={sample.n}, {pairs:.4g} pair interactions per energy()); {nproc} concurrent "
+                           f"single-threaded replicas of the unmodified reference, {steps} timed energy() calls each "
+                           f"after {warmup} warm-up, one molecule displaced between calls",
+                    n_atoms=sample.n)
+    nthreads = oracle.max_threads()
+    for _ in range(warmup):
+        oracle.energy(sample, nthreads=0)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle.energy(sample, nthreads=0)
+    sec = (time.perf_counter() - t0) / max(steps, 1)
+    return dict(value=pairs / sec / 1e9, cores=nthreads, kind="port", ms_per_step=sec * 1e3,
+                sample=f"{what} (N={sample.n}, {pairs:.4g} pair interactions per energy()); OpenMP oracle port "
+                       f"on {nthreads} threads, {steps} timed calls after {warmup} warm-up", n_atoms=sample.n)
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    r = run_cpu_reference(args.workload, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "cpu_sample": r["sample"]},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# own arm
+# ------------------------------------------------------------------------------------------------
+def own_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    from mpmc_b200 import Engine
+    from mpmc_b200.sharded import ShardedEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the engine has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    s = build_workload(args.workload)
+    fh = bool(s.params.feynman_hibbs)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    eng = Engine(local, stream=stream.cuda_stream)
+    sh = ShardedEngine(eng, rank, world, stream=stream)
+    sh.set_system(s)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    flush = torch.empty(256 * 1024 * 1024 // 8, dtype=torch.float64, device="cuda")  # > 126 MB L2
+
+    # ---- warm-up (untimed) ----
+    e0 = None
+    for _ in range(max(args.warmup, 0)):
+        e0 = sh.energy()
+    peak_tf = eng.measure_fp64_peak()  # DFMA-chain probe on this GPU, same run (also warms the clocks)
+
+    # ---- value: device-timed, system resident in HBM ----
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches = 0
+    contract_ms = []
+    phases = {}
+    for k in range(args.steps):
+        flush.fill_(float(k))  # L2 flush between timed iterations (untimed)
+        ev[k][0].record(stream)
+        e = sh.energy()
+        ev[k][1].record(stream)
+        launches += sh.kernel_launches()
+        contract_ms.append(eng.phase_ms("contract"))
+        for ph in ("pair", "recip", "field", "dipole", "total"):
+            phases.setdefault(ph, []).append(eng.phase_ms(ph))
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_dev = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([ms_dev], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / args.steps
+    cnt = sh.counters_total()
+    pairs = pair_interactions(cnt)
+    value = pairs / (ms_per_step * 1e-3) / 1e9
+
+    # ---- e2e: HOST buffers through the public call, copies inside the timed region ----
+    n = s.n
+    hpos = torch.from_numpy(s.pos.copy()).pin_memory()
+    hnp = hpos.numpy()
+    rng = np.random.Generator(np.random.PCG64(7))
+    h2d = n * 3 * 8
+    d2h = 32 * 8 + (4 * 3 + 2) * 8 * n if s.params.polarization else 32 * 8
+    movable = np.flatnonzero(s.frozen == 0)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        # one MC translation of one molecule (5 sites), applied on the host copy the caller owns
+        first = int(movable[0]) + 5 * int(rng.integers(0, max(1, movable.size // 5)))
+        hnp[first:first + 5] += rng.uniform(-0.05, 0.05, size=3)
+        sh.set_positions(0, hnp)           # host -> device, all positions (the drop-in does not diff)
+        e = sh.energy()                    # device -> host: energies
+        if s.params.polarization:
+            arr = sh.atom_arrays()         # device -> host: mu, ef_static, ef_induced, ... as polar() writes back
+        launches += sh.kernel_launches()
+    barrier()
+    sec = time.perf_counter() - t0
+    t = torch.tensor([sec], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = pairs / (float(t.item()) / args.steps) / 1e9
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (K4) ----
+    c_ms = float(np.mean([x for x in contract_ms if x > 0])) if any(x > 0 for x in contract_ms) else 0.0
+    own = sh.counters_own()
+    k4_flops = FLOP_DIPOLE * own.pairs_dipole_own  # ordered pairs this rank's launch covers
+    ach = k4_flops / (c_ms * 1e-3) / 1e12 if c_ms > 0 else 0.0
+    roofline = {"bound": "fp64", "kernel": "dipole_contract_kernel (K4)", "achieved": ach, "peak": peak_tf,
+                "unit": "TFLOP/s", "frac": (ach / peak_tf) if peak_tf > 0 else None, "traffic": None,
+                "peak_source": "DFMA-chain probe measured on this GPU in this run (MEASURED_PEAKS.json has no fp64 entry)",
+                "flops_per_launch": k4_flops, "ms_per_launch": c_ms,
+                "whole_eval_tflops": algorithmic_flops(cnt, fh) / (ms_per_step * 1e-3) / 1e12,
+                "phase_ms": {k: float(np.mean(v)) for k, v in phases.items()}}
+    prof = os.path.join(ROOT, "profiles", "k4_traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get(args.workload)
+        except Exception:
+            pass
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        r = run_cpu_reference(args.workload, 2, 1, budget_s=25.0)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": args.workload, "n_atoms": n, "n_polarizable": int(cnt.n_polarizable),
+                   "polar_iterations": int(e.polar_iterations), "pair_interactions_per_step": pairs,
+                   "mc_steps_per_s": 1e3 / ms_per_step, "l2": "flushed between timed iterations (256 MiB fill)",
+                   "parallelism": f"rows{world}", "energy_K": e.total},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "mc_steps_per_s": args.steps / float(t.item())},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="mof_h2_63k")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    return own_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

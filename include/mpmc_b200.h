@@ -175,15 +175,33 @@ int mpmc_b200_polar(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
 int mpmc_b200_energy_enqueue(mpmc_b200_ctx *ctx);
 int mpmc_b200_energy_finish(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
 
-/* Staged polarization for sharded runs (each returns after enqueueing):
- *   stage 0: static field for own rows + mu0 for own rows
- *   stage 1: one contraction + update for own rows (Jacobi family), writes own rows of mu_new
- *   stage 2: finish: U_pol partial over own rows
- * Between stages the caller all-gathers the dipole buffer (see device_buffer). */
+/* Staged polarization for sharded (multi-GPU) runs, Jacobi family only.  Each call enqueues on the
+ * context's stream and returns; between stages the CALLER runs the collectives (on the same
+ * stream) over the buffers returned by mpmc_b200_device_buffer():
+ *   mpmc_b200_energy_enqueue()                    pair tiles + k-sum partials of this shard
+ *   stage FIELD                                   static field for this shard's atom rows
+ *        -> all-gather ef_static rows (buffer 3, rows from mpmc_b200_shard_field_rows)
+ *   stage INIT                                    mu0 = gamma alpha E_s for all rows (replicated)
+ *   per iteration it = 1, 2, ...:
+ *     stage PASS(it)                              contraction + new_mu + residual for own rows
+ *        -> precision mode: all-reduce(max) of scalar slot 12 (buffer 2), then read it
+ *     stage PALMO                                 only on the last iteration, when polar_palmo is set
+ *     stage COMMIT(it)                            mu rows = new_mu | SOR | ESOR
+ *        -> all-gather mu rows (buffer 0, rows from mpmc_b200_shard_rows)
+ *     (stage FAIL instead, when it reaches 128 in precision mode: mu = alpha E_s, iter_success = 1)
+ *   stage ENERGY(iterations)                      U_pol partial over own rows
+ *   mpmc_b200_energy_finish()                     partial energies; the caller sums them over ranks
+ * This is thole_iterative() (src/polarization/thole_iterative.c:168-259) cut at the points where
+ * the dipole vector has to be exchanged. */
+enum { MPMC_STAGE_FIELD = 0, MPMC_STAGE_INIT = 1, MPMC_STAGE_PASS = 2, MPMC_STAGE_PALMO = 3, MPMC_STAGE_COMMIT = 4,
+       MPMC_STAGE_ENERGY = 5, MPMC_STAGE_FAIL = 6 };
 int mpmc_b200_polar_stage(mpmc_b200_ctx *ctx, int stage, int iteration);
+/* atom rows [begin,end) (padded, tile aligned) whose static field this shard computes */
+int mpmc_b200_shard_field_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_atoms_padded);
 /* Raw device pointer + element count of an internal buffer, for collectives
  * issued by the caller on the same stream.  which: 0 = packed dipoles mu
- * [3][n_pol_padded] (SoA), 1 = packed new dipoles, 2 = convergence scalar. */
+ * [3][n_pol_padded] (SoA), 1 = packed new dipoles, 2 = the 32 device scalars (slot 12 = max squared
+ * dipole change of the last pass, as a double), 3 = static field [3][n_atoms_padded]. */
 int mpmc_b200_device_buffer(mpmc_b200_ctx *ctx, int which, void **dev_ptr, long long *n_doubles);
 /* rows [begin,end) of the packed polarizable index space owned by this shard */
 int mpmc_b200_shard_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_pol, int *n_pol_padded);
@@ -196,7 +214,8 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx *ctx, double *mu, double *ef_static,
 int mpmc_b200_get_counters(mpmc_b200_ctx *ctx, mpmc_b200_counters *out);
 
 /* Measured device time (ms, CUDA events on the library's stream) of the named
- * phase in the last evaluation: "pair", "recip", "field", "dipole", "total". */
+ * phase in the last evaluation: "pair", "recip", "field", "dipole", "total"; "contract" = mean
+ * time of one dipole-tensor contraction (K4) launch. */
 int mpmc_b200_phase_ms(mpmc_b200_ctx *ctx, const char *phase, double *ms);
 
 /* fp64 FMA throughput probe (dependent-chain DFMA kernel), TFLOP/s; used as the

@@ -26,6 +26,9 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmpmc_b200.so")
 DAMP_OFF, DAMP_LINEAR, DAMP_EXPONENTIAL = 0, 1, 2
 MIX_LB, MIX_WH, MIX_HALGREN, MIX_C6 = 0, 1, 2, 3
 
+# enum of mpmc_b200_polar_stage (include/mpmc_b200.h)
+STAGE_FIELD, STAGE_INIT, STAGE_PASS, STAGE_PALMO, STAGE_COMMIT, STAGE_ENERGY, STAGE_FAIL = range(7)
+
 E2REDUCED = 408.7816  # reference src/include/defines.h:45
 DEBYE2SKA = 85.10597636  # defines.h:51
 
@@ -301,6 +304,7 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_polar_stage.argtypes = [vp, C.c_int, C.c_int]
     lib.mpmc_b200_device_buffer.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(C.c_longlong)]
     lib.mpmc_b200_shard_rows.argtypes = [vp, ip, ip, ip, ip]
+    lib.mpmc_b200_shard_field_rows.argtypes = [vp, ip, ip, ip]
     lib.mpmc_b200_get_atom_arrays.argtypes = [vp, dp, dp, dp, dp, dp, dp]
     lib.mpmc_b200_get_counters.argtypes = [vp, C.POINTER(Counters)]
     lib.mpmc_b200_phase_ms.argtypes = [vp, C.c_char_p, dp]
@@ -319,7 +323,8 @@ ABI_SYMBOLS = [
     "mpmc_b200_abi_version", "mpmc_b200_last_error", "mpmc_b200_create", "mpmc_b200_destroy", "mpmc_b200_set_stream",
     "mpmc_b200_set_params", "mpmc_b200_set_atoms", "mpmc_b200_set_positions", "mpmc_b200_set_shard",
     "mpmc_b200_energy", "mpmc_b200_polar", "mpmc_b200_energy_enqueue", "mpmc_b200_energy_finish",
-    "mpmc_b200_polar_stage", "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_get_atom_arrays",
+    "mpmc_b200_polar_stage", "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
+    "mpmc_b200_get_atom_arrays",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak",
 ]
 
@@ -404,6 +409,11 @@ class Engine:
         b, e, n, npad = C.c_int(), C.c_int(), C.c_int(), C.c_int()
         self._check(self.lib.mpmc_b200_shard_rows(self._ctx, C.byref(b), C.byref(e), C.byref(n), C.byref(npad)))
         return b.value, e.value, n.value, npad.value
+
+    def shard_field_rows(self):
+        b, e, npad = C.c_int(), C.c_int(), C.c_int()
+        self._check(self.lib.mpmc_b200_shard_field_rows(self._ctx, C.byref(b), C.byref(e), C.byref(npad)))
+        return b.value, e.value, npad.value
 
     def atom_arrays(self) -> dict:
         n = self.n

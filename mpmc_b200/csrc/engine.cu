@@ -145,6 +145,7 @@ struct mpmc_b200_ctx {
     int wolf_table_max = 0;
     double wolf_table_alpha = -1.0, wolf_table_cut = -1.0;
     int field_jsplits = 1, dipole_jsplits = 1;
+    int fb = 0, fe = 0, pb = 0, pe = 0;  // this shard's static-field rows (atom space) and dipole rows (packed space)
 
     DevBuf<double> scalars;
     double* h_scalars = nullptr;  // pinned
@@ -159,6 +160,12 @@ struct mpmc_b200_ctx {
     cudaEvent_t ev[PH_COUNT][2];
     bool ev_used[PH_COUNT] = {false, false, false, false, false};
     float phase_ms[PH_COUNT] = {0, 0, 0, 0, 0};
+
+    // per-launch timing of the dominant kernel (K4 contraction): event pairs, created on demand
+    std::vector<cudaEvent_t> kev;
+    int kev_used = 0;
+    float contract_ms_sum = 0.f;
+    int contract_launches = 0;
 
     mpmc_b200_counters cnt{};
     int launches = 0;
@@ -459,7 +466,7 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
 static int repack(Ctx* c) {
     const int n = c->n;
     cudaStream_t st = c->stream;
-    c->n_pad = std::max(round_up(n, TILE), TILE);
+    c->n_pad = std::max(round_up(n, TILE * std::max(c->world, 1)), TILE);
     const int np = c->n_pad;
     auto padded = [&](const std::vector<double>& h) {
         std::vector<double> v(np, 0.0);
@@ -560,6 +567,17 @@ static void phase_begin(Ctx* c, Phase p) {
 }
 static void phase_end(Ctx* c, Phase p) { cudaEventRecord(c->ev[p][1], c->stream); }
 
+// bracket one K4 launch with its own event pair (at most 160 per evaluation are timed)
+static void kev_mark(Ctx* c) {
+    if (c->kev_used >= 320) return;
+    if ((int)c->kev.size() <= c->kev_used) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        c->kev.push_back(e);
+    }
+    cudaEventRecord(c->kev[c->kev_used++], c->stream);
+}
+
 static int refresh_subsets(Ctx* c) {
     if (!c->subsets_stale) return 0;
     for (Subset* s : {&c->charged, &c->recip, &c->pol}) {
@@ -630,34 +648,32 @@ static int run_structure_factor(Ctx* c, const Subset& sub, const DevBuf<double>&
 }
 
 // ---- polar(): static field + solver + energy.  Enqueue only (precision mode syncs per iteration).
-static int enqueue_polar(Ctx* c) {
-    const mpmc_b200_params& P = c->P;
-    cudaStream_t st = c->stream;
-    const Cell cell = make_cell(P);
-    const bool ortho = is_ortho(P);
-    const AtomsDev a = atoms_dev(c);
+// row ranges of this shard (tile aligned) and per-evaluation counters
+static void polar_prepare(Ctx* c) {
     const int np = c->n_pad, pp = c->pol.n_pad;
-    SubsetDev pol = c->pol.dev();
-    unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
-
     c->pending_iterations = 0;
     c->pending_iter_success = 0;
     c->cnt.contractions = 0;
     c->cnt.n_polarizable = c->pol.n;
     c->cnt.pairs_dipole = (double)c->pol.n * std::max(c->pol.n - 1, 0);
+    int tb, te;
+    shard_range(np / TILE, c->rank, c->world, tb, te);
+    c->fb = tb * TILE;
+    c->fe = std::min(te * TILE, c->n);
+    shard_range(pp / TILE, c->rank, c->world, tb, te);
+    c->pb = tb * TILE;
+    c->pe = te * TILE;
+}
 
-    // row ranges of this shard (tile aligned)
-    int fb, fe, pb, pe;
-    {
-        int tb, te;
-        shard_range(np / TILE, c->rank, c->world, tb, te);
-        fb = tb * TILE;
-        fe = std::min(te * TILE, c->n);
-        shard_range(pp / TILE, c->rank, c->world, tb, te);
-        pb = tb * TILE;
-        pe = te * TILE;
-    }
-
+// thole_field() (thole_field.c:14-36) for the atom rows [fb, fe) of this shard
+static int polar_field(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    const Cell cell = make_cell(P);
+    const bool ortho = is_ortho(P);
+    const AtomsDev a = atoms_dev(c);
+    const int np = c->n_pad;
+    const int fb = c->fb, fe = c->fe;
     // ---------------- static field: thole_field() (thole_field.c:14-36) ----------------
     phase_begin(c, PH_FIELD);
     CU(cudaMemsetAsync(c->ef_static.p, 0, sizeof(double) * 3 * np, st));
@@ -718,28 +734,113 @@ static int enqueue_polar(Ctx* c) {
     }
     phase_end(c, PH_FIELD);
     CU(cudaGetLastError());
+    return 0;
+}
 
-    // ---------------- solver: thole_iterative() (thole_iterative.c:168-259) ----------------
-    phase_begin(c, PH_DIPOLE);
+static DipoleOpts dipole_opts(const mpmc_b200_params& P) {
+    DipoleOpts dop;
+    dop.damp_type = P.damp_type;
+    dop.wolf_full = P.polar_wolf_full;
+    dop.damp = P.polar_damp;
+    return dop;
+}
+static UpdateOpts update_opts(const mpmc_b200_params& P, int iteration) {
+    UpdateOpts uo;
+    uo.sor = P.polar_sor;
+    uo.esor = P.polar_esor;
+    uo.gamma = P.polar_gamma;
+    uo.save_old = (P.polar_rrms || P.polar_precision > 0 || P.polar_sor || P.polar_esor) ? 1 : 0;
+    uo.do_rrms = (P.polar_rrms || P.polar_precision > 0) ? 1 : 0;
+    uo.iteration = iteration;
+    return uo;
+}
+
+// init_dipoles (thole_iterative.c:13-25) for ALL packed rows (needs the complete static field) and
+// the per-evaluation clears
+static int polar_init(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    const int np = c->n_pad, pp = c->pol.n_pad;
     const double gscale = (!P.polar_sor && !P.polar_esor) ? P.polar_gamma : 1.0;
-    launch_dipole_init(pol, c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st);
+    launch_dipole_init(c->pol.dev(), c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st);
     c->launches++;
     const bool want_rrms = P.polar_rrms || P.polar_precision > 0;
     if (!want_rrms) CU(cudaMemsetAsync(c->rrms.p, 0, sizeof(double) * pp, st));
     CU(cudaMemsetAsync(c->eind.p, 0, sizeof(double) * 3 * pp, st));
     CU(cudaMemsetAsync(c->eic.p, 0, sizeof(double) * 3 * pp, st));
     CU(cudaMemsetAsync(c->mu_new.p, 0, sizeof(double) * 3 * pp, st));
+    CU(cudaGetLastError());
+    return 0;
+}
 
-    DipoleOpts dop;
-    dop.damp_type = P.damp_type;
-    dop.wolf_full = P.polar_wolf_full;
-    dop.damp = P.polar_damp;
-    UpdateOpts uo;
-    uo.sor = P.polar_sor;
-    uo.esor = P.polar_esor;
-    uo.gamma = P.polar_gamma;
-    uo.save_old = (P.polar_rrms || P.polar_precision > 0 || P.polar_sor || P.polar_esor) ? 1 : 0;
-    uo.do_rrms = want_rrms ? 1 : 0;
+// one Jacobi-family pass over this shard's rows: contract_dipoles + calc_dipole_rrms + the
+// are_we_done_yet residual (thole_iterative.c:27-117); mu itself is not touched
+static int polar_jacobi_pass(Ctx* c, int it) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    const SubsetDev pol = c->pol.dev();
+    unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
+    const bool precision_mode = P.polar_precision != 0.0;
+    if (precision_mode) CU(cudaMemsetAsync(errbits, 0, sizeof(unsigned long long), st));
+    kev_mark(c);
+    launch_dipole_contract(make_cell(P), is_ortho(P), pol, dipole_opts(P), c->mu.p, c->pb, c->pe, c->dipole_jsplits,
+                           c->epart.p, st);
+    kev_mark(c);
+    launch_dipole_update(pol, update_opts(P, it), c->epart.p, c->dipole_jsplits, c->es.p, c->mu.p, c->mu_old.p,
+                         c->mu_new.p, c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr, c->pb, c->pe, st);
+    c->launches += 2;
+    c->cnt.contractions += 1;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// palmo_contraction (thole_iterative.c:119-141) with the CURRENT mu, this shard's rows
+static int polar_palmo_pass(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    const SubsetDev pol = c->pol.dev();
+    launch_dipole_contract(make_cell(P), is_ortho(P), pol, dipole_opts(P), c->mu.p, c->pb, c->pe, c->dipole_jsplits,
+                           c->epart.p, c->stream);
+    launch_palmo_finish(pol, c->epart.p, c->dipole_jsplits, c->eind.p, c->eic.p, c->pb, c->pe, c->stream);
+    c->launches += 2;
+    c->cnt.contractions += 1;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// mu = new_mu | SOR | ESOR mix (thole_iterative.c:242-252), this shard's rows
+static int polar_commit(Ctx* c, int it) {
+    launch_dipole_commit(c->pol.dev(), update_opts(c->P, it), c->mu_old.p, c->mu_new.p, c->mu.p, c->pb, c->pe, c->stream);
+    c->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// U_pol partial (polar.c:108-116) and rrms partial (polar.c:13-28) over this shard's rows
+static int polar_energy_partial(Ctx* c) {
+    launch_polar_energy(c->pol.dev(), c->mu.p, c->es.p, c->P.polar_palmo ? c->eic.p : nullptr, c->rrms.p, c->pb,
+                        std::min(c->pe, c->pol.n), c->scalars.p + S_POLAR, c->stream);
+    c->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// ---- polar(): static field + solver + energy on ONE device.  Enqueue only (precision mode syncs
+// per iteration).  thole_iterative(): thole_iterative.c:168-259.
+static int enqueue_polar(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    const Cell cell = make_cell(P);
+    const bool ortho = is_ortho(P);
+    const int pp = c->pol.n_pad;
+    SubsetDev pol = c->pol.dev();
+    unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
+    polar_prepare(c);
+    if (polar_field(c)) return 10;
+    phase_begin(c, PH_DIPOLE);
+    if (polar_init(c)) return 10;
+    const bool want_rrms = P.polar_rrms || P.polar_precision > 0;
+    const DipoleOpts dop = dipole_opts(P);
+    UpdateOpts uo = update_opts(P, 0);
     const bool gs = P.polar_gs || P.polar_gs_ranked;
     const double allowed = P.polar_precision * P.polar_precision * kDEBYE2SKA * kDEBYE2SKA;
     const int js = c->dipole_jsplits;
@@ -849,12 +950,9 @@ static int enqueue_polar(Ctx* c) {
                     c->launches++;
                 }
             } else {
-                launch_dipole_contract(cell, ortho, pol, dop, c->mu.p, pb, pe, js, c->epart.p, st);
-                launch_dipole_update(pol, uo, c->epart.p, js, c->es.p, c->mu.p, c->mu_old.p, c->mu_new.p, c->eind.p,
-                                     c->rrms.p, precision_mode ? errbits : nullptr, pb, pe, st);
-                c->launches += 2;
+                if (polar_jacobi_pass(c, it)) return 10;
             }
-            c->cnt.contractions += 1;
+            if (gs) c->cnt.contractions += 1;
             CU(cudaGetLastError());
 
             if (!precision_mode)
@@ -871,12 +969,10 @@ static int enqueue_polar(Ctx* c) {
                 if (gs) {
                     launch_dipole_contract(cell, ortho, g, dop, c->g_mu.p, 0, pp, js, c->epart.p, st);
                     launch_palmo_finish(g, c->epart.p, js, c->g_eind.p, c->g_eic.p, 0, pp, st);
-                } else {
-                    launch_dipole_contract(cell, ortho, pol, dop, c->mu.p, pb, pe, js, c->epart.p, st);
-                    launch_palmo_finish(pol, c->epart.p, js, c->eind.p, c->eic.p, pb, pe, st);
-                }
-                c->launches += 2;
-                c->cnt.contractions += 1;
+                    c->launches += 2;
+                    c->cnt.contractions += 1;
+                } else if (polar_palmo_pass(c))
+                    return 10;
             }
 
             if (gs && P.polar_gs_ranked && keep && it == 1) {
@@ -896,10 +992,8 @@ static int enqueue_polar(Ctx* c) {
                     launch_dipole_commit(g, uo, c->g_mu_old.p, c->g_mu_new.p, c->g_mu.p, 0, pp, st);
                     c->launches++;
                 }  // else mu already equals new_mu
-            } else {
-                launch_dipole_commit(pol, uo, c->mu_old.p, c->mu_new.p, c->mu.p, pb, pe, st);
-                c->launches++;
-            }
+            } else if (polar_commit(c, it))
+                return 10;
         }
         c->pending_iterations = it;
         if (permuted)
@@ -907,12 +1001,7 @@ static int enqueue_polar(Ctx* c) {
     }
     phase_end(c, PH_DIPOLE);
 
-    // ---------------- U_pol (polar.c:108-116) and dipole_rrms (polar.c:13-28) ----------------
-    launch_polar_energy(pol, c->mu.p, c->es.p, P.polar_palmo ? c->eic.p : nullptr, c->rrms.p, pb, std::min(pe, c->pol.n),
-                        c->scalars.p + S_POLAR, st);
-    c->launches++;
-    CU(cudaGetLastError());
-    return 0;
+    return polar_energy_partial(c);
 }
 
 static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
@@ -928,6 +1017,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
     refresh_subsets(c);
     c->launches = 0;
     for (int p = 0; p < PH_COUNT; p++) c->ev_used[p] = false;
+    c->kev_used = 0;
     memset(&c->cnt, 0, sizeof(c->cnt));
     c->cnt.n_atoms = c->n;
     c->pending_iterations = 0;
@@ -994,6 +1084,13 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     for (int p = 0; p < PH_COUNT; p++) {
         c->phase_ms[p] = 0.f;
         if (c->ev_used[p]) cudaEventElapsedTime(&c->phase_ms[p], c->ev[p][0], c->ev[p][1]);
+    }
+    c->contract_ms_sum = 0.f;
+    c->contract_launches = c->kev_used / 2;
+    for (int k = 0; k + 1 < c->kev_used; k += 2) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->kev[k], c->kev[k + 1]);
+        c->contract_ms_sum += ms;
     }
     const double* h = c->h_scalars;
     memset(out, 0, sizeof(*out));
@@ -1068,6 +1165,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
         cudaEventDestroy(c->ev[p][0]);
         cudaEventDestroy(c->ev[p][1]);
     }
+    for (cudaEvent_t e : c->kev) cudaEventDestroy(e);
     for (DevBuf<double>* b : {&c->x, &c->y, &c->z, &c->q, &c->eps, &c->sig, &c->molmass, &c->alpha, &c->pair_part, &c->kweight,
                               &c->kweight_field, &c->kvec, &c->sf_partial, &c->sf, &c->ef_static, &c->epart, &c->es, &c->mu,
                               &c->mu_old, &c->mu_new, &c->eind, &c->eic, &c->rrms, &c->rank_packed, &c->rmin_part,
@@ -1220,10 +1318,58 @@ int mpmc_b200_energy_finish(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
 }
 
 int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
-    (void)iteration;
     if (!c) FAIL(1, "null ctx");
-    (void)stage;
-    FAIL(3, "mpmc_b200_polar_stage: staged multi-GPU polarization is not wired yet");
+    if (!c->have_params || !c->have_atoms) FAIL(2, "no system");
+    const mpmc_b200_params& P = c->P;
+    if (!P.polarization || P.rd_only) FAIL(2, "polarization is off");
+    if (P.polar_gs || P.polar_gs_ranked) FAIL(3, "Gauss-Seidel polarization is single-GPU only (sequential dependency)");
+    if (check_supported(P)) return 3;
+    CU(cudaSetDevice(c->device));
+    switch (stage) {
+        case MPMC_STAGE_FIELD:
+            polar_prepare(c);
+            if (polar_field(c)) return 10;
+            c->last_had_polar = true;
+            return 0;
+        case MPMC_STAGE_INIT:
+            phase_begin(c, PH_DIPOLE);
+            return polar_init(c) ? 10 : 0;
+        case MPMC_STAGE_PASS:
+            if (P.polar_zodid || c->pol.n <= 0) return 0;
+            return polar_jacobi_pass(c, iteration) ? 10 : 0;
+        case MPMC_STAGE_PALMO:
+            if (P.polar_zodid || c->pol.n <= 0) return 0;
+            return polar_palmo_pass(c) ? 10 : 0;
+        case MPMC_STAGE_COMMIT:
+            if (P.polar_zodid || c->pol.n <= 0) return 0;
+            return polar_commit(c, iteration) ? 10 : 0;
+        case MPMC_STAGE_FAIL:  // divergence bail-out (thole_iterative.c:199-210): mu = alpha E_s on every rank
+            reset_dipoles_kernel<<<(c->pol.n + 255) / 256, 256, 0, c->stream>>>(c->pol.n, c->pol.n_pad, c->pol.alpha.p,
+                                                                               c->es.p, c->mu.p, c->eic.p);
+            c->launches++;
+            c->pending_iter_success = 1;
+            CU(cudaGetLastError());
+            return 0;
+        case MPMC_STAGE_ENERGY:
+            phase_end(c, PH_DIPOLE);
+            c->pending_iterations = iteration;
+            if (polar_energy_partial(c)) return 10;
+            phase_end(c, PH_TOTAL);
+            c->pending = true;
+            return 0;
+        default: FAIL(1, "unknown polar stage");
+    }
+}
+
+int mpmc_b200_shard_field_rows(mpmc_b200_ctx* c, int* begin, int* end, int* n_atoms_padded) {
+    if (!c) FAIL(1, "null ctx");
+    if (!c->have_atoms) FAIL(2, "no atoms");
+    int tb, te;
+    shard_range(c->n_pad / TILE, c->rank, c->world, tb, te);
+    if (begin) *begin = tb * TILE;
+    if (end) *end = te * TILE;
+    if (n_atoms_padded) *n_atoms_padded = c->n_pad;
+    return 0;
 }
 
 int mpmc_b200_device_buffer(mpmc_b200_ctx* c, int which, void** dev_ptr, long long* n_doubles) {
@@ -1296,6 +1442,10 @@ int mpmc_b200_get_counters(mpmc_b200_ctx* c, mpmc_b200_counters* out) {
 
 int mpmc_b200_phase_ms(mpmc_b200_ctx* c, const char* phase, double* ms) {
     if (!c || !phase || !ms) FAIL(1, "null argument");
+    if (!strcmp(phase, "contract")) {  // mean device time of one K4 launch in the last evaluation
+        *ms = c->contract_launches ? c->contract_ms_sum / c->contract_launches : 0.0;
+        return 0;
+    }
     static const char* names[PH_COUNT] = {"pair", "recip", "field", "dipole", "total"};
     for (int p = 0; p < PH_COUNT; p++)
         if (!strcmp(phase, names[p])) {

@@ -8,9 +8,9 @@
  * (src/energy/energy.c:67) and prints every input the hot path reads and every
  * output it writes with %.17g, so that golden fixtures carry all 53 bits.
  *
- * usage: ref_driver <mpmc input file> [repeat]
- *   repeat > 1 re-evaluates energy() that many times and reports seconds per call
- *   (CPU baseline timing of the real reference).
+ * usage: ref_driver <mpmc input file> [repeat [warmup]]
+ *   repeat > 1 re-evaluates energy() that many times (after `warmup` untimed calls) and
+ *   reports seconds per call (CPU baseline timing of the real reference).
  * Output goes to stdout after the marker line "MPMC_SNAPSHOT 1"; the
  * reference's own chatter goes to stdout before it / stderr.
  */
@@ -43,7 +43,7 @@ static void p3x3(const char *name, double m[3][3]) {
 
 int main(int argc, char **argv) {
     system_t *s;
-    int repeat = 1, i, n, molidx;
+    int repeat = 1, warmup = 0, i, n, molidx;
     double e = 0, t0, t1;
     molecule_t *m;
     atom_t *a;
@@ -53,6 +53,8 @@ int main(int argc, char **argv) {
         return 1;
     }
     if (argc > 2) repeat = atoi(argv[2]);
+    if (argc > 3) warmup = atoi(argv[3]);
+    if (repeat < 1) repeat = 1;
     rank = 0;
     size = 1;
 
@@ -69,10 +71,18 @@ int main(int argc, char **argv) {
     s->checkpoint->observables = zalloc(sizeof(observables_t));
     if (s->polarization && !s->polar_zodid) thole_resize_matrices(s);
 
+    /* timing mode (repeat > 1 or warmup > 0): between calls the last molecule is displaced by
+     * +-1e-3 A along x, as one MC translation would, so the reference's own pair cache
+     * (src/energy/pairs.c:243-250) behaves as it does inside mc(); the snapshot printed below
+     * is then of the LAST call.  Golden fixtures are generated with repeat = 1, warmup = 0. */
     t0 = now_s();
-    for (i = 0; i < repeat; i++) {
-        /* force a full recalculation each time, as a moved system would */
-        if (i) s->observables->energy = 0.0;
+    for (i = 0; i < warmup + repeat; i++) {
+        if (i == warmup) t0 = now_s();
+        if (i) {
+            for (m = s->molecules; m->next; m = m->next)
+                ;
+            for (a = m->atoms; a; a = a->next) a->pos[0] += (i & 1) ? 1e-3 : -1e-3;
+        }
         e = energy(s);
     }
     t1 = now_s();
