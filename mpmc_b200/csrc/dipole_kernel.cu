@@ -171,6 +171,73 @@ static void contract_dispatch(const Cell& c, bool ortho, const SubsetDev& pol, c
 #undef LAUNCH
 }
 
+// Field of the dipoles at atoms that are NOT in the polarizable list (alpha == 0).  The reference's
+// palmo_contraction() (thole_iterative.c:119-141) runs over every atom, so non-polarizable atoms
+// get ef_induced_change = - sum_j T_ij mu_j as well (their rows of A exist, thole_matrix.c:73-143);
+// the values never enter an energy (mu_i = 0) but are written back to atom_t.
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(TILE) dipole_field_at_kernel(Cell c, SubsetDev rows, SubsetDev p, DipoleConsts k,
+                                                               const double* __restrict__ mu, int row_begin,
+                                                               double* __restrict__ out) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], smx[TILE], smy[TILE], smz[TILE], saux[TILE];
+    __shared__ int smol[TILE];
+    const int tid = threadIdx.x;
+    const int i = row_begin + blockIdx.x * TILE + tid;
+    const double xi = rows.x[i], yi = rows.y[i], zi = rows.z[i];
+    const double auxi = rows.aux[i];
+    const int moli = rows.mol[i];
+    const int np = p.n_pad;
+    double ex = 0.0, ey = 0.0, ez = 0.0;
+    for (int jt = 0; jt < np / TILE; jt++) {
+        __syncthreads();
+        const int j = jt * TILE + tid;
+        sx[tid] = p.x[j];
+        sy[tid] = p.y[j];
+        sz[tid] = p.z[j];
+        smx[tid] = mu[j];
+        smy[tid] = mu[np + j];
+        smz[tid] = mu[2 * np + j];
+        saux[tid] = p.aux[j];
+        smol[tid] = p.mol[j];
+        __syncthreads();
+        const int jn = min(TILE, p.n - jt * TILE);
+        for (int jj = 0; jj < jn; jj++)
+            tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[jj], yi - sy[jj], zi - sz[jj], smx[jj], smy[jj], smz[jj], auxi,
+                                          saux[jj], moli == smol[jj], ex, ey, ez);
+    }
+    const bool live = i < rows.n;
+    out[i] = live ? ex : 0.0;
+    out[rows.n_pad + i] = live ? ey : 0.0;
+    out[2 * rows.n_pad + i] = live ? ez : 0.0;
+}
+
+void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, const SubsetDev& pol, const DipoleOpts& o,
+                            const double* mu, int row_begin, int row_end, double* out, cudaStream_t s) {
+    const int n = row_end - row_begin;
+    if (n <= 0 || pol.n <= 0) return;
+    const DipoleConsts k = make_consts(c, o);
+    const int grid = n / TILE;
+#define LAUNCH(ORTHO, DAMP, WF) \
+    dipole_field_at_kernel<ORTHO, DAMP, WF><<<grid, TILE, 0, s>>>(c, rows, pol, k, mu, row_begin, out)
+#define DISPATCH(ORTHO)                                              \
+    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true); \
+        else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false);            \
+    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                    \
+        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false);                      \
+    } else {                                                         \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true);         \
+        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false);                    \
+    }
+    if (ortho) {
+        DISPATCH(true)
+    } else {
+        DISPATCH(false)
+    }
+#undef DISPATCH
+#undef LAUNCH
+}
+
 void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
                             int row_begin, int row_end, int jsplits, double* epart, cudaStream_t s) {
     contract_dispatch(c, ortho, pol, o, mu, row_begin, row_end, jsplits, -1, epart, s);

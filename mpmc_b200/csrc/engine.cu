@@ -122,6 +122,9 @@ struct mpmc_b200_ctx {
     DevBuf<double> x, y, z, q, eps, sig, molmass, alpha;
     DevBuf<int> mol, flags;
     Subset charged, recip, pol, gs;  // gs: polarizable atoms permuted into Gauss-Seidel order
+    Subset nonpol;                   // alpha == 0 atoms: rows of the palmo field that are only written back
+    DevBuf<double> eic_np;           // [3][nonpol.n_pad]
+    bool eic_np_valid = false;
     DevBuf<int2> tiles;
     int ntiles = 0;
     DevBuf<double> pair_part;
@@ -485,8 +488,9 @@ static int repack(Ctx* c) {
         return 11;
 
     // subsets
-    std::vector<int> charged, recip, pol;
+    std::vector<int> charged, recip, pol, nonpol;
     for (int i = 0; i < n; i++) {
+        if (c->halpha[i] == 0.0) nonpol.push_back(i);
         if (c->hq[i] != 0.0) {
             charged.push_back(i);
             if (!c->hfrozen[i]) recip.push_back(i);  // coulombic.c:74-75
@@ -495,8 +499,9 @@ static int repack(Ctx* c) {
     }
     const int polpad = TILE * std::max(c->world, 1);
     if (pack_subset(c, c->charged, charged, TILE, false) || pack_subset(c, c->recip, recip, TILE, false) ||
-        pack_subset(c, c->pol, pol, polpad, true))
+        pack_subset(c, c->pol, pol, polpad, true) || pack_subset(c, c->nonpol, nonpol, polpad, true))
         return 11;
+    if (c->eic_np.ensure((size_t)3 * c->nonpol.n_pad)) FAIL(11, "cudaMalloc failed");
     c->hperm.assign(c->pol.n_pad, 0);
     std::iota(c->hperm.begin(), c->hperm.end(), 0);
 
@@ -580,7 +585,7 @@ static void kev_mark(Ctx* c) {
 
 static int refresh_subsets(Ctx* c) {
     if (!c->subsets_stale) return 0;
-    for (Subset* s : {&c->charged, &c->recip, &c->pol}) {
+    for (Subset* s : {&c->charged, &c->recip, &c->pol, &c->nonpol}) {
         if (s->n <= 0) continue;
         gather_positions_kernel<<<(s->n + 255) / 256, 256, 0, c->stream>>>(c->x.p, c->y.p, c->z.p, s->didx.p, s->n, s->x.p,
                                                                           s->y.p, s->z.p);
@@ -633,15 +638,19 @@ static int run_structure_factor(Ctx* c, const Subset& sub, const DevBuf<double>&
     const int target = 2 * sms;
     const int apc = std::max(64, round_up((std::max(sub.n, 1) + target - 1) / target, 64));
     const int nchunks = std::max(1, (sub.n + apc - 1) / apc);
-    int cb = 0, ce = nchunks;
-    if (sharded) shard_range(nchunks, c->rank, c->world, cb, ce);
-    const int mine = std::max(ce - cb, 0);
+    // Every rank accumulates the complete S(k) (0.1-0.2 ms at 64k atoms; |S|^2 is not linear in
+    // atom partials); the SUM over k-vectors is what is split across ranks.
+    const int cb = 0, ce = nchunks;
+    const int mine = nchunks;
+    int kb = 0, ke = c->nk;
+    if (sharded) shard_range(c->nk, c->rank, c->world, kb, ke);
     if (c->sf_partial.ensure((size_t)std::max(mine, 1) * 2 * std::max(c->nk, 1))) FAIL(11, "cudaMalloc failed");
     if (c->nk > 0 && sub.n > 0 && mine > 0) {
         launch_recip_sf(make_cell(c->P), sub.dev(), kv, cb, ce, apc, c->sf_partial.p, c->stream);
         c->launches++;
     }
-    launch_recip_finish(kv, c->sf_partial.p, (c->nk > 0 && sub.n > 0) ? mine : 0, scale, c->sf.p, energy_slot, c->stream);
+    launch_recip_finish(kv, c->sf_partial.p, (c->nk > 0 && sub.n > 0) ? mine : 0, scale, c->sf.p, energy_slot, kb, ke,
+                        c->stream);
     c->launches++;
     CU(cudaGetLastError());
     return 0;
@@ -653,6 +662,7 @@ static void polar_prepare(Ctx* c) {
     const int np = c->n_pad, pp = c->pol.n_pad;
     c->pending_iterations = 0;
     c->pending_iter_success = 0;
+    c->eic_np_valid = false;
     c->cnt.contractions = 0;
     c->cnt.n_polarizable = c->pol.n;
     c->cnt.pairs_dipole = (double)c->pol.n * std::max(c->pol.n - 1, 0);
@@ -794,6 +804,23 @@ static int polar_jacobi_pass(Ctx* c, int it) {
     return 0;
 }
 
+// palmo rows of the non-polarizable atoms (write-back only, see dipole_field_at_kernel); `src`/`mu`
+// are the polarizable atoms and their current dipoles in any common order
+static int palmo_nonpolar_rows(Ctx* c, const SubsetDev& src, const double* mu) {
+    if (c->nonpol.n <= 0) return 0;
+    int tb, te;
+    shard_range(c->nonpol.n_pad / TILE, c->rank, c->world, tb, te);
+    CU(cudaMemsetAsync(c->eic_np.p, 0, sizeof(double) * 3 * c->nonpol.n_pad, c->stream));
+    if (te > tb) {
+        launch_dipole_field_at(make_cell(c->P), is_ortho(c->P), c->nonpol.dev(), src, dipole_opts(c->P), mu, tb * TILE,
+                               te * TILE, c->eic_np.p, c->stream);
+        c->launches++;
+    }
+    c->eic_np_valid = true;
+    CU(cudaGetLastError());
+    return 0;
+}
+
 // palmo_contraction (thole_iterative.c:119-141) with the CURRENT mu, this shard's rows
 static int polar_palmo_pass(Ctx* c) {
     const mpmc_b200_params& P = c->P;
@@ -804,7 +831,7 @@ static int polar_palmo_pass(Ctx* c) {
     c->launches += 2;
     c->cnt.contractions += 1;
     CU(cudaGetLastError());
-    return 0;
+    return palmo_nonpolar_rows(c, pol, c->mu.p);
 }
 
 // mu = new_mu | SOR | ESOR mix (thole_iterative.c:242-252), this shard's rows
@@ -971,6 +998,7 @@ static int enqueue_polar(Ctx* c) {
                     launch_palmo_finish(g, c->epart.p, js, c->g_eind.p, c->g_eic.p, 0, pp, st);
                     c->launches += 2;
                     c->cnt.contractions += 1;
+                    if (palmo_nonpolar_rows(c, g, c->g_mu.p)) return 10;
                 } else if (polar_palmo_pass(c))
                     return 10;
             }
@@ -1177,6 +1205,8 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     c->charged.release();
     c->recip.release();
     c->pol.release();
+    c->nonpol.release();
+    c->eic_np.release();
     c->gs.release();
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -1416,6 +1446,14 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
         return 0;
     };
     if (scatter3(c->mu, mu) || scatter3(c->eind, ef_induced) || scatter3(c->eic, ef_induced_change)) return 10;
+    if (ef_induced_change && c->eic_np_valid && c->nonpol.n > 0) {
+        const int qp = c->nonpol.n_pad;
+        std::vector<double> nb((size_t)3 * qp);
+        CU(cudaMemcpyAsync(nb.data(), c->eic_np.p, sizeof(double) * 3 * qp, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        for (int k = 0; k < c->nonpol.n; k++)
+            for (int d3 = 0; d3 < 3; d3++) ef_induced_change[3 * c->nonpol.idx[k] + d3] = nb[(size_t)d3 * qp + k];
+    }
     if (ef_static) {
         CU(cudaMemcpyAsync(buf.data(), c->ef_static.p, sizeof(double) * 3 * np, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));

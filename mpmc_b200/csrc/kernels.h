@@ -48,8 +48,9 @@ struct KVecDev {
 };
 void launch_recip_sf(const Cell& c, const SubsetDev& atoms, const KVecDev& kv, int chunk_begin, int chunk_end,
                      int atoms_per_chunk, double* sf_partial /*[nchunks][2][nk]*/, cudaStream_t s);
+// energy_out = scale * sum_{k in [k_begin,k_end)} w_k |S(k)|^2 : the k-vector range is this shard's share
 void launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale,
-                         double* sf /*[2][nk]*/, double* energy_out, cudaStream_t s);
+                         double* sf /*[2][nk]*/, double* energy_out, int k_begin, int k_end, cudaStream_t s);
 // recip_term() of the Ewald static field (src/polarization/polar_ewald.c:78-132)
 void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, const double* kvec /*[3][nk]*/,
                         const double* sf, double scale, int row_begin, int row_end, double* ef /*[3][n_pad]*/,
@@ -84,6 +85,9 @@ struct DipoleOpts {
 void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu /*[3][n_pad]*/,
                             int row_begin, int row_end, int jsplits, double* epart /*[jsplits][3][n_pad]*/,
                             cudaStream_t s);
+// palmo: field of the dipoles at the atoms of `rows` (the non-polarizable atoms), out[3][rows.n_pad]
+void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, const SubsetDev& pol, const DipoleOpts& o,
+                            const double* mu, int row_begin, int row_end, double* out, cudaStream_t s);
 struct UpdateOpts {
     int sor, esor, save_old, do_rrms;
     double gamma;

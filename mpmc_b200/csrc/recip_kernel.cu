@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(RC_THREADS) recip_sf_kernel(Cell c, SubsetDev 
 // then fixed-order block reduction.
 __global__ void __launch_bounds__(1024) recip_finish_kernel(KVecDev kv, const double* __restrict__ sf_partial, int nchunks,
                                                             double scale, double* __restrict__ sf,
-                                                            double* __restrict__ energy_out) {
+                                                            double* __restrict__ energy_out, int k_begin, int k_end) {
     __shared__ double red[32];
     double acc = 0.0;
     for (int ik = threadIdx.x; ik < kv.nk; ik += blockDim.x) {
@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(1024) recip_finish_kernel(KVecDev kv, const do
             sf[ik] = re;
             sf[kv.nk + ik] = im;
         }
-        acc += kv.weight[ik] * (re * re + im * im);
+        if (ik >= k_begin && ik < k_end) acc += kv.weight[ik] * (re * re + im * im);  // this shard's k-vectors
     }
     double v = block_reduce<0>(acc, red);
     if (threadIdx.x == 0 && energy_out) *energy_out = v * scale;
@@ -167,8 +167,8 @@ void launch_recip_sf(const Cell& c, const SubsetDev& atoms, const KVecDev& kv, i
 }
 
 void launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale, double* sf,
-                         double* energy_out, cudaStream_t s) {
-    recip_finish_kernel<<<1, 1024, 0, s>>>(kv, sf_partial, nchunks, scale, sf, energy_out);
+                         double* energy_out, int k_begin, int k_end, cudaStream_t s) {
+    recip_finish_kernel<<<1, 1024, 0, s>>>(kv, sf_partial, nchunks, scale, sf, energy_out, k_begin, k_end);
 }
 
 void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, const double* kvec, const double* sf,

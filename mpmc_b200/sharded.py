@@ -98,6 +98,7 @@ class ShardedEngine:
         self.eng, self.rank, self.world = engine, rank, world
         self.ex = Exchange(rank, world, group)
         self.stream = stream
+        self.device = getattr(engine, "torch_device", "cuda")
         self.system = None
         self._launches = 0
         self._last_cnt: Optional[Counters] = None
@@ -123,8 +124,11 @@ class ShardedEngine:
         import torch
 
         if which not in self._views:
-            ptr, n = self.eng.device_buffer(which)
-            self._views[which] = torch.as_tensor(_DevView(ptr, n), device="cuda")
+            if hasattr(self.eng, "buffer_tensor"):  # host stand-in used by the gloo tests
+                self._views[which] = self.eng.buffer_tensor(which)
+            else:
+                ptr, n = self.eng.device_buffer(which)
+                self._views[which] = torch.as_tensor(_DevView(ptr, n), device="cuda")
         return self._views[which]
 
     # -- evaluation ----------------------------------------------------------
@@ -151,7 +155,7 @@ class ShardedEngine:
             eng.polar_stage(api.STAGE_INIT)
             mu = self._view(0)
             if not p.polar_zodid and n_pol > 0:
-                allowed = (p.polar_precision * DEBYE2SKA) ** 2
+                allowed = p.polar_precision * p.polar_precision * DEBYE2SKA * DEBYE2SKA  # thole_iterative.c:106
                 keep = True
                 while keep:
                     iterations += 1
@@ -175,7 +179,7 @@ class ShardedEngine:
         cnt = eng.counters()
         self._launches = cnt.kernel_launches
         vals = [getattr(part, k) for k in _ENERGY_SUM_FIELDS] + [getattr(cnt, k) for k in _COUNTER_SUM_FIELDS]
-        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        t = torch.tensor(vals, dtype=torch.float64, device=self.device)
         self.ex.all_reduce(t, "sum")
         vals = t.tolist()
         out = Energies()
@@ -197,7 +201,7 @@ class ShardedEngine:
             # mu and ef_static are complete on every rank after their all-gathers; the rest is
             # valid on the owning rank's rows and zero elsewhere -> sum over ranks
             for k in ("ef_induced", "ef_induced_change", "dipole_rrms"):
-                t = torch.from_numpy(arr[k]).cuda()
+                t = torch.from_numpy(arr[k]).to(self.device)
                 self.ex.all_reduce(t, "sum")
                 arr[k] = t.cpu().numpy()
         return arr

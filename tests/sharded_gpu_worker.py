@@ -1,0 +1,84 @@
+"""Worker of tests/test_gpu_sharded.py: run under torchrun with >= 2 ranks, one GPU each.
+Every rank evaluates energy() row-sharded over the ranks (NCCL) and, on its own GPU, unsharded;
+the two must agree to rounding (only the association of the partial sums differs)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from mpmc_b200 import Engine, systems  # noqa: E402
+from mpmc_b200.sharded import ShardedEngine  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    cases = []
+    s = systems.mof_h2(cells=(3, 3, 2))
+    cases.append(("mof_jacobi10", s))
+    s = systems.h2_fluid(4000)
+    s.params.polar_max_iter, s.params.polar_precision, s.params.polar_palmo, s.params.polar_rrms = 0, 1e-6, 1, 1
+    cases.append(("h2_precision_palmo_rrms", s))
+    s = systems.mixed_small()
+    s.params.polar_ewald = 1
+    cases.append(("mixed_polar_ewald", s))
+    s = systems.mixed_small(triclinic=True)
+    s.params.polar_sor, s.params.polar_gamma = 1, 0.8
+    cases.append(("mixed_tri_sor", s))
+    cases.append(("co2_nopolar", systems.co2_fluid(500)))
+    ok = True
+    for name, s in cases:
+        one = Engine(local, stream=stream.cuda_stream)
+        one.set_system(s)
+        ref = one.energy()
+        ref_arr = one.atom_arrays() if s.params.polarization else None
+        one.close()
+        eng = Engine(local, stream=stream.cuda_stream)
+        sh = ShardedEngine(eng, rank, world, stream=stream)
+        sh.set_system(s)
+        got = sh.energy()
+        got2 = sh.energy()  # a second evaluation must reproduce the first bit for bit
+        for k in ("rd", "es_real", "es_recip", "es_self", "coulombic", "polar", "total", "dipole_rrms"):
+            a, b = getattr(got, k), getattr(ref, k)
+            scale = max(abs(b), 1e-13 * max(abs(ref.es_real), abs(ref.es_self), 1.0)) if k in ("coulombic", "total") else abs(b)
+            if not abs(a - b) <= 1e-11 * scale + 1e-13 * max(abs(ref.es_real), abs(ref.es_self)) * (k in ("coulombic", "total")):
+                print(f"[rank {rank}] {name} {k}: sharded {a!r} vs single {b!r}", flush=True)
+                ok = False
+            if getattr(got2, k) != a:
+                print(f"[rank {rank}] {name} {k}: not reproducible {getattr(got2, k)!r} vs {a!r}", flush=True)
+                ok = False
+        if got.polar_iterations != ref.polar_iterations or got.iter_success != ref.iter_success:
+            print(f"[rank {rank}] {name}: iterations {got.polar_iterations} vs {ref.polar_iterations}", flush=True)
+            ok = False
+        if ref_arr is not None:
+            arr = sh.atom_arrays()
+            for k in ("mu", "ef_static", "ef_induced", "ef_induced_change", "dipole_rrms"):
+                scale = max(np.abs(ref_arr[k]).max(), 1e-300)
+                if k == "ef_induced_change":
+                    scale = max(scale, np.abs(ref_arr["ef_induced"]).max())
+                err = np.abs(arr[k] - ref_arr[k]).max() / scale
+                if not err <= 1e-11:
+                    print(f"[rank {rank}] {name} {k}: max err {err:.3e}", flush=True)
+                    ok = False
+        eng.close()
+        if rank == 0:
+            print(f"case {name}: E={got.total!r} iterations={got.polar_iterations}", flush=True)
+    t = torch.tensor([0 if ok else 1], device="cuda")
+    dist.all_reduce(t)
+    dist.destroy_process_group()
+    if int(t.item()) != 0:
+        sys.exit(1)
+    if rank == 0:
+        print("SHARDED_OK", flush=True)
+
+
+if __name__ == "__main__":
+    main()
