@@ -1,0 +1,474 @@
+/*
+ * energy_shim.c -- the drop-in boundary: MPMC's own entry points
+ *
+ *     double energy(system_t *)                 reference src/energy/energy.c:67-226
+ *     double energy_no_observables(system_t *)  reference src/energy/energy.c:232-318
+ *     double polar(system_t *)                  reference src/energy/polar.c:31-135
+ *     void   pairs(system_t *) and the pair-list maintenance calls   src/energy/pairs.c
+ *     thole_resize_matrices / thole_amatrix     src/polarization/thole_matrix.c
+ *
+ * implemented over the C ABI of libmpmc_b200 (include/mpmc_b200.h).  The file is compiled against
+ * the reference's OWN headers (-I<reference>/src/include, same cmake_config.h) and linked with
+ * the reference's unmodified host sources (main, io, mc, mersenne, histogram, ...) in place of
+ * src/energy/{energy,pairs,polar}.c and src/polarization/*.c; see mpmc_b200/shim/Makefile and
+ * INTEGRATION.md.  The MC driver, the parser, the RNG and the writers are the reference's.
+ *
+ * What the shim does per call: walk the molecule/atom lists in list order (the order
+ * rebuild_arrays() defines, src/energy/pairs.c:12-38), pack the fields the hot path reads into
+ * flat arrays, send only what changed since the previous call to the device, evaluate, and write
+ * the results back into system_t / atom_t exactly where the reference leaves them.
+ * The O(N^2) pair_t lists are never allocated: every atom->pairs stays NULL.
+ *
+ * No CPU fallback: options the CUDA engine does not implement end in error() + die(-1).
+ */
+#include <mc.h>
+
+#include "mpmc_b200.h"
+
+static mpmc_b200_ctx *g_ctx = NULL;
+
+/* host image of what was last sent to the device */
+static int g_n = -1;
+static int g_cap = 0;
+static double *g_pos, *g_q, *g_alpha, *g_eps, *g_sig, *g_mmass;
+static int *g_mol, *g_frozen;
+static double *n_pos, *n_q, *n_alpha, *n_eps, *n_sig, *n_mmass; /* freshly packed */
+static int *n_mol, *n_frozen;
+static double *w_mu, *w_es, *w_ei, *w_eic, *w_rrms, *w_rank; /* write-back staging */
+static mpmc_b200_params g_params;
+static int g_have_params = 0;
+
+static void shim_die(const char *what) {
+    char buf[MAXLINE];
+    snprintf(buf, MAXLINE, "B200: %s: %s\n", what, mpmc_b200_last_error());
+    error(buf);
+    die(-1);
+}
+
+static void shim_unsupported(const char *what) {
+    char buf[MAXLINE];
+    snprintf(buf, MAXLINE,
+             "B200: %s is not implemented by the B200 energy engine (and there is no CPU fallback in this build)\n", what);
+    error(buf);
+    die(-1);
+}
+
+static void shim_shutdown(void) {
+    if (g_ctx) mpmc_b200_destroy(g_ctx);
+    g_ctx = NULL;
+}
+
+static void shim_init(void) {
+    int dev = 0;
+    const char *env;
+    if (g_ctx) return;
+    env = getenv("MPMC_B200_DEVICE"); /* one MC chain per GPU: the launcher sets this per process */
+    if (env) dev = atoi(env);
+    if (mpmc_b200_create(&g_ctx, dev)) shim_die("cannot create the CUDA context");
+    atexit(shim_shutdown);
+}
+
+static void *xrealloc(void *p, size_t bytes) {
+    void *q = realloc(p, bytes ? bytes : 1);
+    memnullcheck(q, bytes, __LINE__ - 1, __FILE__);
+    return q;
+}
+
+static void shim_reserve(int n) {
+    int cap;
+    if (n <= g_cap) return;
+    cap = n + n / 4 + 64;
+#define GROW(ptr, type, mult) ptr = (type *)xrealloc(ptr, sizeof(type) * (size_t)(mult) * cap)
+    GROW(g_pos, double, 3);
+    GROW(g_q, double, 1);
+    GROW(g_alpha, double, 1);
+    GROW(g_eps, double, 1);
+    GROW(g_sig, double, 1);
+    GROW(g_mmass, double, 1);
+    GROW(g_mol, int, 1);
+    GROW(g_frozen, int, 1);
+    GROW(n_pos, double, 3);
+    GROW(n_q, double, 1);
+    GROW(n_alpha, double, 1);
+    GROW(n_eps, double, 1);
+    GROW(n_sig, double, 1);
+    GROW(n_mmass, double, 1);
+    GROW(n_mol, int, 1);
+    GROW(n_frozen, int, 1);
+    GROW(w_mu, double, 3);
+    GROW(w_es, double, 3);
+    GROW(w_ei, double, 3);
+    GROW(w_eic, double, 3);
+    GROW(w_rrms, double, 1);
+    GROW(w_rank, double, 1);
+#undef GROW
+    g_cap = cap;
+}
+
+/* system_t / pbc_t scalars the hot path reads -> mpmc_b200_params */
+static void shim_fill_params(const system_t *s, mpmc_b200_params *P) {
+    int p, q;
+    memset(P, 0, sizeof(*P));
+    for (p = 0; p < 3; p++)
+        for (q = 0; q < 3; q++) {
+            P->basis[p][q] = s->pbc->basis[p][q];
+            P->reciprocal_basis[p][q] = s->pbc->reciprocal_basis[p][q];
+        }
+    P->cutoff = s->pbc->cutoff;
+    P->volume = s->pbc->volume;
+    P->ewald_alpha = s->ewald_alpha;
+    P->ewald_kmax = s->ewald_kmax;
+    P->feynman_hibbs = s->feynman_hibbs;
+    P->feynman_hibbs_order = s->feynman_hibbs_order;
+    P->temperature = s->temperature;
+    P->rd_lrc = s->rd_lrc;
+    P->mixing = s->waldmanhagler ? MPMC_MIX_WALDMAN_HAGLER
+                                 : s->halgren_mixing ? MPMC_MIX_HALGREN : s->c6_mixing ? MPMC_MIX_C6 : MPMC_MIX_LORENTZ_BERTHELOT;
+    P->rd_only = s->rd_only;
+    P->cavity_autoreject_absolute = s->cavity_autoreject_absolute;
+    P->cavity_autoreject_scale = s->cavity_autoreject_scale;
+    P->polarization = s->polarization;
+    P->polar_iterative = s->polar_iterative;
+    P->damp_type = s->damp_type == DAMPING_OFF ? MPMC_DAMP_OFF : s->damp_type == DAMPING_LINEAR ? MPMC_DAMP_LINEAR : MPMC_DAMP_EXPONENTIAL;
+    P->polar_damp = s->polar_damp;
+    P->polar_max_iter = s->polar_max_iter;
+    P->polar_precision = s->polar_precision;
+    P->polar_gamma = s->polar_gamma;
+    P->polar_gs = s->polar_gs;
+    P->polar_gs_ranked = s->polar_gs_ranked;
+    P->polar_sor = s->polar_sor;
+    P->polar_esor = s->polar_esor;
+    P->polar_palmo = s->polar_palmo;
+    P->polar_rrms = s->polar_rrms;
+    P->polar_zodid = s->polar_zodid;
+    P->polar_ewald = s->polar_ewald;
+    P->polar_ewald_full = s->polar_ewald_full;
+    P->polar_wolf = s->polar_wolf;
+    P->polar_wolf_full = s->polar_wolf_full;
+    P->polar_wolf_alpha_lookup = s->polar_wolf_alpha_lookup;
+    P->polar_wolf_alpha = s->polar_wolf_alpha;
+    P->polar_wolf_alpha_lookup_cutoff = s->polar_wolf_alpha_lookup_cutoff;
+    P->polar_ewald_alpha = s->polar_ewald_alpha;
+}
+
+/* the rd_energy / electrostatics switches of energy() (energy.c:132-176) the engine does not cover */
+static void shim_check_supported(const system_t *s) {
+    if (s->rd_anharmonic) shim_unsupported("rd_anharmonic");
+    if (s->sg) shim_unsupported("sg (Silvera-Goldman)");
+    if (s->dreiding) shim_unsupported("dreiding");
+    if (s->lj_buffered_14_7) shim_unsupported("lj_buffered_14_7");
+    if (s->disp_expansion) shim_unsupported("disp_expansion");
+    if (s->cdvdw_exp_repulsion || s->cdvdw_sig_repulsion) shim_unsupported("cdvdw repulsion");
+    if (s->gwp) shim_unsupported("gwp");
+    if (s->axilrod_teller) shim_unsupported("axilrod_teller");
+    if (s->spectre) shim_unsupported("spectre");
+    if (s->polarvdw) shim_unsupported("polarvdw");
+    if (s->wolf) shim_unsupported("wolf (coulombic_wolf)");
+    if (s->rd_crystal) shim_unsupported("rd_crystal");
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * O(N) duties of the reference's pair bookkeeping (src/energy/pairs.c, src/energy/energy.c:16-46)
+ * ---------------------------------------------------------------------------------------------- */
+int countNatoms(system_t *system) {
+    molecule_t *m;
+    atom_t *a;
+    int N = 0;
+    for (m = system->molecules; m; m = m->next)
+        for (a = m->atoms; a; a = a->next) N++;
+    return N;
+}
+
+void countN(system_t *system) {
+    molecule_t *m;
+    system->observables->N = 0;
+    system->observables->spin_ratio = 0;
+    for (m = system->molecules; m; m = m->next) {
+        if (!(m->frozen || m->adiabatic || m->target)) {
+            system->observables->N += 1.0;
+            if (m->nuclear_spin == NUCLEAR_SPIN_PARA) system->observables->spin_ratio += 1.0;
+        }
+        if (system->ensemble == ENSEMBLE_NVE) system->N = system->observables->N;
+    }
+}
+
+/* atom_array[] / molecule_array[] in list order: other reference code indexes them */
+void rebuild_arrays(system_t *system) {
+    molecule_t *m;
+    atom_t *a;
+    int n = system->natoms;
+    free(system->atom_array);
+    free(system->molecule_array);
+    system->molecule_array = malloc((n ? n : 1) * sizeof(molecule_t *));
+    memnullcheck(system->molecule_array, n * sizeof(molecule_t *), __LINE__ - 1, __FILE__);
+    system->atom_array = malloc((n ? n : 1) * sizeof(atom_t *));
+    memnullcheck(system->atom_array, n * sizeof(atom_t *), __LINE__ - 1, __FILE__);
+    n = 0;
+    for (m = system->molecules; m; m = m->next)
+        for (a = m->atoms; a; a = a->next) {
+            system->molecule_array[n] = m;
+            system->atom_array[n] = a;
+            n++;
+        }
+    system->natoms = n;
+}
+
+/* molecular centre of mass; also refreshes molecule->mass, which the Feynman-Hibbs reduced mass
+ * reads (src/energy/pairs.c:364-385, src/energy/lj.c:22-23) */
+void update_com(molecule_t *molecules) {
+    int i;
+    molecule_t *m;
+    atom_t *a;
+    for (m = molecules; m; m = m->next) {
+        for (i = 0; i < 3; i++) m->com[i] = 0;
+        if (!(m->spectre || m->target)) {
+            for (a = m->atoms, m->mass = 0; a; a = a->next) {
+                m->mass += a->mass;
+                for (i = 0; i < 3; i++) m->com[i] += a->mass * a->pos[i];
+            }
+            for (i = 0; i < 3; i++) m->com[i] /= m->mass;
+        }
+    }
+}
+
+/* pairs(): the reference fills N(N-1)/2 pair_t here (src/energy/pairs.c:293-361).  The device
+ * kernels recompute exclusions, mixing and minimum images in registers, so only the O(N) duties
+ * remain: pointer arrays, centres of mass, wrapped coordinates.  (The GS rank metric is computed
+ * on the device and written back by the evaluation.) */
+void pairs(system_t *system) {
+    system->natoms = countNatoms(system);
+    rebuild_arrays(system);
+    update_com(system->molecules);
+    wrapall(system->molecules, system->pbc);
+}
+
+/* pair-list maintenance entry points called by the MC driver (src/io/input.c:1783-1792,
+ * src/mc/mc_moves.c:664-775): nothing to maintain, every atom->pairs stays NULL */
+void setup_pairs(system_t *system) { (void)system; }
+void flag_all_pairs(system_t *system) { (void)system; }
+void update_pairs_insert(system_t *system) { (void)system; }
+void update_pairs_remove(system_t *system) { (void)system; }
+void unupdate_pairs_insert(system_t *system) { (void)system; }
+void unupdate_pairs_remove(system_t *system) { (void)system; }
+
+/* minimum_image() keeps its reference semantics for the few callers outside the hot path
+ * (src/energy/axilrod_teller.cpp:132-146 passes a scratch pair_t): src/energy/pairs.c:230-290 */
+void minimum_image(system_t *system, atom_t *atom_i, atom_t *atom_j, pair_t *pair_ptr) {
+    int p, q;
+    double img[3], d[3], di[3], r2 = 0, ri2 = 0;
+    pair_ptr->recalculate_energy = 1;
+    for (p = 0; p < 3; p++) {
+        d[p] = atom_i->pos[p] - atom_j->pos[p];
+        pair_ptr->d_prev[p] = d[p];
+    }
+    for (p = 0; p < 3; p++) {
+        for (q = 0, img[p] = 0; q < 3; q++) img[p] += system->pbc->reciprocal_basis[q][p] * d[q];
+        img[p] = rint(img[p]);
+    }
+    for (p = 0; p < 3; p++) {
+        for (q = 0, di[p] = 0; q < 3; q++) di[p] += system->pbc->basis[q][p] * img[q];
+        di[p] = d[p] - di[p];
+        r2 += d[p] * d[p];
+        ri2 += di[p] * di[p];
+    }
+    pair_ptr->r = sqrt(r2);
+    if (isnan(sqrt(ri2)) != 0) {
+        pair_ptr->rimg = pair_ptr->r;
+        for (p = 0; p < 3; p++) pair_ptr->dimg[p] = d[p];
+    } else {
+        pair_ptr->rimg = sqrt(ri2);
+        for (p = 0; p < 3; p++) pair_ptr->dimg[p] = di[p];
+    }
+}
+
+/* The dense 3N x 3N matrices are never built (src/polarization/thole_matrix.c:149-191): leaving
+ * both NULL makes free_matrices() a no-op (src/main/cleanup.c:138-139). */
+void thole_resize_matrices(system_t *system) {
+    system->A_matrix = NULL;
+    system->B_matrix = NULL;
+    system->checkpoint->thole_N_atom = system->natoms;
+}
+void thole_amatrix(system_t *system) {
+    (void)system;
+    shim_unsupported("thole_amatrix (dense A matrix; used only by disp_expansion / vdw)");
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * host lists -> device image
+ * ---------------------------------------------------------------------------------------------- */
+static void shim_sync_device(system_t *system) {
+    molecule_t *m;
+    atom_t *a;
+    mpmc_b200_params P;
+    int n = 0, molidx = 0, i, same, first, last;
+
+    shim_init();
+    shim_check_supported(system);
+
+    shim_fill_params(system, &P);
+    if (!g_have_params || memcmp(&P, &g_params, sizeof(P)) != 0) {
+        if (mpmc_b200_set_params(g_ctx, &P)) shim_die("set_params");
+        g_params = P;
+        g_have_params = 1;
+    }
+
+    shim_reserve(system->natoms);
+    for (m = system->molecules; m; m = m->next, molidx++)
+        for (a = m->atoms; a; a = a->next, n++) {
+            n_pos[3 * n] = a->pos[0];
+            n_pos[3 * n + 1] = a->pos[1];
+            n_pos[3 * n + 2] = a->pos[2];
+            n_q[n] = a->charge;
+            n_alpha[n] = a->polarizability;
+            n_eps[n] = a->epsilon;
+            n_sig[n] = a->sigma;
+            n_mmass[n] = m->mass;
+            n_mol[n] = molidx;
+            n_frozen[n] = a->frozen;
+        }
+
+    /* a translation / rotation changes positions only; an insertion, a removal or a restored
+     * molecule changes the atom count or the per-atom parameters and needs the full image */
+    same = (n == g_n) && !memcmp(n_q, g_q, sizeof(double) * n) && !memcmp(n_alpha, g_alpha, sizeof(double) * n) &&
+           !memcmp(n_eps, g_eps, sizeof(double) * n) && !memcmp(n_sig, g_sig, sizeof(double) * n) &&
+           !memcmp(n_mmass, g_mmass, sizeof(double) * n) && !memcmp(n_mol, g_mol, sizeof(int) * n) &&
+           !memcmp(n_frozen, g_frozen, sizeof(int) * n);
+    if (!same) {
+        if (mpmc_b200_set_atoms(g_ctx, n, n_pos, n_q, n_alpha, n_eps, n_sig, n_mmass, n_mol, n_frozen)) shim_die("set_atoms");
+        memcpy(g_q, n_q, sizeof(double) * n);
+        memcpy(g_alpha, n_alpha, sizeof(double) * n);
+        memcpy(g_eps, n_eps, sizeof(double) * n);
+        memcpy(g_sig, n_sig, sizeof(double) * n);
+        memcpy(g_mmass, n_mmass, sizeof(double) * n);
+        memcpy(g_mol, n_mol, sizeof(int) * n);
+        memcpy(g_frozen, n_frozen, sizeof(int) * n);
+        memcpy(g_pos, n_pos, sizeof(double) * 3 * n);
+        g_n = n;
+        return;
+    }
+    first = -1;
+    last = -1;
+    for (i = 0; i < n; i++)
+        if (n_pos[3 * i] != g_pos[3 * i] || n_pos[3 * i + 1] != g_pos[3 * i + 1] || n_pos[3 * i + 2] != g_pos[3 * i + 2]) {
+            if (first < 0) first = i;
+            last = i;
+        }
+    if (first >= 0) {
+        if (mpmc_b200_set_positions(g_ctx, first, last - first + 1, n_pos + 3 * first)) shim_die("set_positions");
+        memcpy(g_pos + 3 * first, n_pos + 3 * first, sizeof(double) * 3 * (last - first + 1));
+    }
+}
+
+/* what polar() leaves in atom_t (read by write_dipole / write_field, src/io/output.c:1029-1088) */
+static void shim_write_back_atoms(system_t *system) {
+    molecule_t *m;
+    atom_t *a;
+    int n = 0, p;
+    if (mpmc_b200_get_atom_arrays(g_ctx, w_mu, w_es, w_ei, w_eic, w_rrms, system->polar_gs_ranked ? w_rank : NULL))
+        shim_die("get_atom_arrays");
+    for (m = system->molecules; m; m = m->next)
+        for (a = m->atoms; a; a = a->next, n++) {
+            for (p = 0; p < 3; p++) {
+                a->mu[p] = w_mu[3 * n + p];
+                a->ef_static[p] = w_es[3 * n + p];
+                a->ef_induced[p] = w_ei[3 * n + p];
+                a->ef_induced_change[p] = w_eic[3 * n + p];
+            }
+            a->dipole_rrms = w_rrms[n];
+            if (system->polar_gs_ranked) a->rank_metric = w_rank[n];
+        }
+}
+
+static void shim_polar_epilogue(system_t *system, const mpmc_b200_energies *e) {
+    char linebuf[MAXLINE];
+    shim_write_back_atoms(system);
+    if (!system->polar_iterative) return;
+    system->nodestats->polarization_iterations = (double)e->polar_iterations;
+    system->observables->dipole_rrms = e->dipole_rrms;
+    if (e->iter_success) system->iter_success = 1; /* thole_iterative.c:207; the MC driver resets it (mc.c:347) */
+    if (system->iter_success) {                    /* polar.c:66-89 */
+        switch (system->ensemble) {
+            case ENSEMBLE_UVT:
+            case ENSEMBLE_NVT:
+            case ENSEMBLE_NVE:
+            case ENSEMBLE_NPT:
+                sprintf(linebuf, "POLAR: polarization iterative solver convergence failure on mc step %d.\n", system->step);
+                break;
+            case ENSEMBLE_REPLAY:
+                sprintf(linebuf, "POLAR: polarization iterative solver convergence failure on configuration %d.\n", system->step);
+                break;
+            default:
+                sprintf(linebuf, "POLAR: polarization iterative solver failed to reach convergence.\n");
+        }
+        error(linebuf);
+    }
+}
+
+/* coulombic_self() also stores the per-atom point self energy (src/energy/coulombic.c:103-108) */
+static void shim_es_self_points(system_t *system) {
+    molecule_t *m;
+    atom_t *a;
+    for (m = system->molecules; m; m = m->next)
+        for (a = m->atoms; a; a = a->next)
+            if (!a->frozen) a->es_self_point_energy = system->ewald_alpha * a->charge * a->charge / sqrt(M_PI);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * entry points
+ * ---------------------------------------------------------------------------------------------- */
+double polar(system_t *system) {
+    mpmc_b200_energies e;
+    if (system->polarization && !system->polar_iterative && !system->polar_zodid && !system->polar_ewald_full)
+        shim_unsupported("matrix-inversion polarization (polar_iterative off)");
+    shim_sync_device(system);
+    if (mpmc_b200_polar(g_ctx, &e)) shim_die("polar");
+    shim_polar_epilogue(system, &e);
+    return e.polar;
+}
+
+static double shim_energy(system_t *system, int with_observables) {
+    mpmc_b200_energies e;
+    double potential_energy = 0, rd_energy = 0, coulombic_energy = 0, polar_energy = 0;
+    const int es_on = !(system->sg || system->rd_only);
+
+    system->natoms = countNatoms(system);
+    pairs(system);
+    if (es_on && system->polarization && !system->polar_iterative && !system->polar_zodid && !system->polar_ewald_full)
+        shim_unsupported("matrix-inversion polarization (polar_iterative off)");
+    shim_sync_device(system);
+    if (mpmc_b200_energy(g_ctx, &e)) shim_die("energy");
+
+    if (e.autorejected) { /* cavity_autoreject_absolute found a bad contact: energy.c:99-102,187-191 */
+        potential_energy = MAXVALUE;
+        if (with_observables) system->count_autorejects++;
+    } else {
+        if (es_on && system->polarization) {
+            polar_energy = e.polar;
+            if (with_observables) system->observables->polarization_energy = polar_energy;
+            shim_polar_epilogue(system, &e);
+        }
+        rd_energy = e.rd;
+        if (with_observables) system->observables->rd_energy = rd_energy;
+        if (es_on) {
+            coulombic_energy = e.coulombic;
+            if (with_observables) system->observables->coulombic_energy = coulombic_energy;
+            shim_es_self_points(system);
+        }
+    }
+    potential_energy += rd_energy + coulombic_energy + polar_energy; /* + vdw + three-body: unsupported => 0 */
+    if (!with_observables) return potential_energy;
+
+    system->observables->energy = potential_energy;
+    countN(system);
+    system->observables->spin_ratio /= system->observables->N;
+    if (system->ensemble == ENSEMBLE_NVE) {
+        system->observables->kinetic_energy = system->total_energy - potential_energy;
+        system->observables->temperature = (2.0 / 3.0) * system->observables->kinetic_energy / system->observables->N;
+    }
+    system->observables->NU = system->observables->N * system->observables->energy;
+    system->last_volume = system->pbc->volume;
+    return potential_energy;
+}
+
+double energy(system_t *system) { return shim_energy(system, 1); }
+double energy_no_observables(system_t *system) { return shim_energy(system, 0); }

@@ -139,12 +139,16 @@ int main(int argc, char **argv) {
     printf("energy N %.17g\n", s->observables->N);
     printf("energy polar_iterations %.17g\n", s->nodestats->polarization_iterations);
     printf("energy iter_success %d\n", s->iter_success);
-    /* the three Ewald pieces separately (pure functions of the pair lists) */
+    /* the three Ewald pieces separately (pure functions of the pair lists).  Not available when
+     * this driver is linked against the B200 drop-in (mpmc_b200/shim, -DSHIM_DRIVER): there are
+     * no pair lists there. */
+#ifndef SHIM_DRIVER
     if (!s->rd_only && !s->wolf) {
         printf("energy es_recip %.17g\n", coulombic_reciprocal(s));
         printf("energy es_self %.17g\n", coulombic_self(s));
         printf("energy es_real %.17g\n", coulombic_real(s));
     }
+#endif
 
     n = 0;
     for (m = s->molecules; m; m = m->next)
