@@ -183,25 +183,33 @@ int mpmc_b200_energy_finish(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
  *        -> all-gather ef_static rows (buffer 3, rows from mpmc_b200_shard_field_rows)
  *   stage INIT                                    mu0 = gamma alpha E_s for all rows (replicated)
  *   per iteration it = 1, 2, ...:
- *     stage PASS(it)                              contraction + new_mu + residual for own rows
- *        -> precision mode: all-reduce(max) of scalar slot 12 (buffer 2), then read it
- *     stage PALMO                                 only on the last iteration, when polar_palmo is set
- *     stage COMMIT(it)                            mu rows = new_mu | SOR | ESOR
- *        -> all-gather mu rows (buffer 0, rows from mpmc_b200_shard_rows)
+ *     stage PASS(it)                              symmetric dipole-tensor contraction over this shard's
+ *                                                 tile pairs: its contribution to E_ind of ALL rows
+ *        -> all-reduce(sum) of buffer 4 (the one real exchange of the path, 3 n_pol doubles)
+ *     stage UPDATE(it)                            new_mu + residual (slot 12 of buffer 2) for all rows,
+ *                                                 identical on every rank
+ *     on the last iteration, when polar_palmo is set:
+ *       stage PALMO -> all-reduce(sum) of buffer 4 -> stage PALMO_FINISH
+ *     stage COMMIT(it)                            mu = new_mu | SOR | ESOR, all rows (no dipole all-gather)
  *     (stage FAIL instead, when it reaches 128 in precision mode: mu = alpha E_s, iter_success = 1)
  *   stage ENERGY(iterations)                      U_pol partial over own rows
  *   mpmc_b200_energy_finish()                     partial energies; the caller sums them over ranks
  * This is thole_iterative() (src/polarization/thole_iterative.c:168-259) cut at the points where
- * the dipole vector has to be exchanged. */
+ * partial induced fields have to be combined.  With MPMC_B200_K4=rows in the environment the
+ * row-by-row contraction is used instead: PASS updates own rows and the caller all-gathers the dipole
+ * rows of buffer 0 after COMMIT (UPDATE / PALMO_FINISH are then no-ops). */
 enum { MPMC_STAGE_FIELD = 0, MPMC_STAGE_INIT = 1, MPMC_STAGE_PASS = 2, MPMC_STAGE_PALMO = 3, MPMC_STAGE_COMMIT = 4,
-       MPMC_STAGE_ENERGY = 5, MPMC_STAGE_FAIL = 6 };
+       MPMC_STAGE_ENERGY = 5, MPMC_STAGE_FAIL = 6, MPMC_STAGE_UPDATE = 7, MPMC_STAGE_PALMO_FINISH = 8 };
 int mpmc_b200_polar_stage(mpmc_b200_ctx *ctx, int stage, int iteration);
+/* 1 when the symmetric contraction (all-reduce of buffer 4) is active, 0 for the row form (all-gather of buffer 0) */
+int mpmc_b200_uses_symmetric_contraction(mpmc_b200_ctx *ctx);
 /* atom rows [begin,end) (padded, tile aligned) whose static field this shard computes */
 int mpmc_b200_shard_field_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_atoms_padded);
 /* Raw device pointer + element count of an internal buffer, for collectives
  * issued by the caller on the same stream.  which: 0 = packed dipoles mu
  * [3][n_pol_padded] (SoA), 1 = packed new dipoles, 2 = the 32 device scalars (slot 12 = max squared
- * dipole change of the last pass, as a double), 3 = static field [3][n_atoms_padded]. */
+ * dipole change of the last pass, as a double), 3 = static field [3][n_atoms_padded], 4 = induced field
+ * partial sums [3][n_pol_padded] of the symmetric contraction. */
 int mpmc_b200_device_buffer(mpmc_b200_ctx *ctx, int which, void **dev_ptr, long long *n_doubles);
 /* rows [begin,end) of the packed polarizable index space owned by this shard */
 int mpmc_b200_shard_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_pol, int *n_pol_padded);

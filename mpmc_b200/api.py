@@ -27,7 +27,8 @@ DAMP_OFF, DAMP_LINEAR, DAMP_EXPONENTIAL = 0, 1, 2
 MIX_LB, MIX_WH, MIX_HALGREN, MIX_C6 = 0, 1, 2, 3
 
 # enum of mpmc_b200_polar_stage (include/mpmc_b200.h)
-STAGE_FIELD, STAGE_INIT, STAGE_PASS, STAGE_PALMO, STAGE_COMMIT, STAGE_ENERGY, STAGE_FAIL = range(7)
+(STAGE_FIELD, STAGE_INIT, STAGE_PASS, STAGE_PALMO, STAGE_COMMIT, STAGE_ENERGY, STAGE_FAIL, STAGE_UPDATE,
+ STAGE_PALMO_FINISH) = range(9)
 
 E2REDUCED = 408.7816  # reference src/include/defines.h:45
 DEBYE2SKA = 85.10597636  # defines.h:51
@@ -303,6 +304,7 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_energy_finish.argtypes = [vp, C.POINTER(Energies)]
     lib.mpmc_b200_polar_stage.argtypes = [vp, C.c_int, C.c_int]
     lib.mpmc_b200_device_buffer.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(C.c_longlong)]
+    lib.mpmc_b200_uses_symmetric_contraction.argtypes = [vp]
     lib.mpmc_b200_shard_rows.argtypes = [vp, ip, ip, ip, ip]
     lib.mpmc_b200_shard_field_rows.argtypes = [vp, ip, ip, ip]
     lib.mpmc_b200_get_atom_arrays.argtypes = [vp, dp, dp, dp, dp, dp, dp]
@@ -323,7 +325,7 @@ ABI_SYMBOLS = [
     "mpmc_b200_abi_version", "mpmc_b200_last_error", "mpmc_b200_create", "mpmc_b200_destroy", "mpmc_b200_set_stream",
     "mpmc_b200_set_params", "mpmc_b200_set_atoms", "mpmc_b200_set_positions", "mpmc_b200_set_shard",
     "mpmc_b200_energy", "mpmc_b200_polar", "mpmc_b200_energy_enqueue", "mpmc_b200_energy_finish",
-    "mpmc_b200_polar_stage", "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
+    "mpmc_b200_polar_stage", "mpmc_b200_uses_symmetric_contraction", "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
     "mpmc_b200_get_atom_arrays",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak",
 ]
@@ -399,6 +401,9 @@ class Engine:
 
     def polar_stage(self, stage: int, iteration: int = 0):
         self._check(self.lib.mpmc_b200_polar_stage(self._ctx, stage, iteration))
+
+    def uses_symmetric_contraction(self) -> bool:
+        return bool(self.lib.mpmc_b200_uses_symmetric_contraction(self._ctx))
 
     def device_buffer(self, which: int):
         ptr, n = C.c_void_p(), C.c_longlong()

@@ -148,6 +148,10 @@ struct mpmc_b200_ctx {
     int wolf_table_max = 0;
     double wolf_table_alpha = -1.0, wolf_table_cut = -1.0;
     int field_jsplits = 1, dipole_jsplits = 1;
+    // symmetric K4 (dipole_sym_kernel.cu): cluster boxes, I-side / J-side partial rows, reduced field
+    bool use_sym = true;
+    DevBuf<double> cbox, sym_partI, sym_partJ, esum;
+    int sym_ysplits = 1;
     int fb = 0, fe = 0, pb = 0, pe = 0;  // this shard's static-field rows (atom space) and dipole rows (packed space)
 
     DevBuf<double> scalars;
@@ -550,6 +554,15 @@ static int repack(Ctx* c) {
         c->rank_packed.ensure(pp) || c->rmin_part.ensure(ptiles + 8) ||
         c->field_cnt.ensure((size_t)c->field_jsplits * (np / TILE) + 8))
         FAIL(11, "cudaMalloc failed");
+    {
+        // symmetric K4: CTAs = I tiles x offset slices; a few waves of 4 CTAs per SM
+        const int own_tiles = std::max(1, ptiles / std::max(c->world, 1));
+        const int K1 = ptiles / 2 + 1;
+        c->sym_ysplits = std::max(1, std::min(K1, (16 * sms + own_tiles - 1) / own_tiles));
+        if (c->cbox.ensure((size_t)6 * (pp / 32)) || c->sym_partI.ensure((size_t)c->sym_ysplits * 3 * pp) ||
+            c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
+            FAIL(11, "cudaMalloc failed");
+    }
     CU(cudaMemsetAsync(c->ef_static.p, 0, sizeof(double) * 3 * np, st));
     for (DevBuf<double>* b : {&c->es, &c->mu, &c->mu_old, &c->mu_new, &c->eind, &c->eic})
         CU(cudaMemsetAsync(b->p, 0, sizeof(double) * 3 * pp, st));
@@ -774,6 +787,10 @@ static int polar_init(Ctx* c) {
     const double gscale = (!P.polar_sor && !P.polar_esor) ? P.polar_gamma : 1.0;
     launch_dipole_init(c->pol.dev(), c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st);
     c->launches++;
+    if (c->use_sym && c->pol.n > 0) {
+        launch_cluster_boxes(c->pol.dev(), c->cbox.p, st);
+        c->launches++;
+    }
     const bool want_rrms = P.polar_rrms || P.polar_precision > 0;
     if (!want_rrms) CU(cudaMemsetAsync(c->rrms.p, 0, sizeof(double) * pp, st));
     CU(cudaMemsetAsync(c->eind.p, 0, sizeof(double) * 3 * pp, st));
@@ -785,9 +802,44 @@ static int polar_init(Ctx* c) {
 
 // one Jacobi-family pass over this shard's rows: contract_dipoles + calc_dipole_rrms + the
 // are_we_done_yet residual (thole_iterative.c:27-117); mu itself is not touched
+// symmetric contraction of this shard's I tiles -> c->esum (contribution to E_ind of ALL rows)
+static int polar_contract_sym(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    int tb, te;
+    shard_range(c->pol.n_pad / TILE, c->rank, c->world, tb, te);
+    kev_mark(c);
+    launch_dipole_contract_sym(make_cell(P), is_ortho(P), c->pol.dev(), dipole_opts(P), c->mu.p, c->cbox.p, tb, te,
+                               c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p, c->esum.p, c->stream);
+    kev_mark(c);
+    c->launches += 2;
+    c->cnt.contractions += 1;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// new_mu, residual, rrms from the reduced field (all rows: after the all-reduce every rank holds the complete E_ind)
+static int polar_update_sym(Ctx* c, int it) {
+    const mpmc_b200_params& P = c->P;
+    unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
+    const bool precision_mode = P.polar_precision != 0.0;
+    if (precision_mode) CU(cudaMemsetAsync(errbits, 0, sizeof(unsigned long long), c->stream));
+    launch_dipole_update(c->pol.dev(), update_opts(P, it), c->esum.p, 1, c->es.p, c->mu.p, c->mu_old.p, c->mu_new.p,
+                         c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr, 0, c->pol.n_pad, c->stream);
+    c->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// one Jacobi-family pass over this shard's rows: contract_dipoles + calc_dipole_rrms + the
+// are_we_done_yet residual (thole_iterative.c:27-117); mu itself is not touched
 static int polar_jacobi_pass(Ctx* c, int it) {
     const mpmc_b200_params& P = c->P;
     cudaStream_t st = c->stream;
+    if (c->use_sym) {
+        if (polar_contract_sym(c)) return 10;
+        if (c->world > 1) return 0;  // the caller all-reduces esum, then runs MPMC_STAGE_UPDATE
+        return polar_update_sym(c, it);
+    }
     const SubsetDev pol = c->pol.dev();
     unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
     const bool precision_mode = P.polar_precision != 0.0;
@@ -822,9 +874,21 @@ static int palmo_nonpolar_rows(Ctx* c, const SubsetDev& src, const double* mu) {
 }
 
 // palmo_contraction (thole_iterative.c:119-141) with the CURRENT mu, this shard's rows
+static int polar_palmo_finish_sym(Ctx* c) {
+    launch_palmo_finish(c->pol.dev(), c->esum.p, 1, c->eind.p, c->eic.p, 0, c->pol.n_pad, c->stream);
+    c->launches++;
+    CU(cudaGetLastError());
+    return palmo_nonpolar_rows(c, c->pol.dev(), c->mu.p);
+}
+
 static int polar_palmo_pass(Ctx* c) {
     const mpmc_b200_params& P = c->P;
     const SubsetDev pol = c->pol.dev();
+    if (c->use_sym) {
+        if (polar_contract_sym(c)) return 10;
+        if (c->world > 1) return 0;  // all-reduce of esum, then MPMC_STAGE_PALMO_FINISH
+        return polar_palmo_finish_sym(c);
+    }
     launch_dipole_contract(make_cell(P), is_ortho(P), pol, dipole_opts(P), c->mu.p, c->pb, c->pe, c->dipole_jsplits,
                            c->epart.p, c->stream);
     launch_palmo_finish(pol, c->epart.p, c->dipole_jsplits, c->eind.p, c->eic.p, c->pb, c->pe, c->stream);
@@ -836,7 +900,9 @@ static int polar_palmo_pass(Ctx* c) {
 
 // mu = new_mu | SOR | ESOR mix (thole_iterative.c:242-252), this shard's rows
 static int polar_commit(Ctx* c, int it) {
-    launch_dipole_commit(c->pol.dev(), update_opts(c->P, it), c->mu_old.p, c->mu_new.p, c->mu.p, c->pb, c->pe, c->stream);
+    const bool all = c->use_sym;  // symmetric K4: every rank updates every row (no dipole all-gather)
+    launch_dipole_commit(c->pol.dev(), update_opts(c->P, it), c->mu_old.p, c->mu_new.p, c->mu.p, all ? 0 : c->pb,
+                         all ? c->pol.n_pad : c->pe, c->stream);
     c->launches++;
     CU(cudaGetLastError());
     return 0;
@@ -1175,6 +1241,10 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
     c->device = device;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     c->own_stream = true;
+    {   // A/B switch for profiling: MPMC_B200_K4=rows selects the row-by-row contraction of dipole_kernel.cu
+        const char* v = getenv("MPMC_B200_K4");
+        c->use_sym = !(v && strcmp(v, "rows") == 0);
+    }
     for (int p = 0; p < PH_COUNT; p++) {
         CU(cudaEventCreate(&c->ev[p][0]));
         CU(cudaEventCreate(&c->ev[p][1]));
@@ -1198,7 +1268,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
                               &c->kweight_field, &c->kvec, &c->sf_partial, &c->sf, &c->ef_static, &c->epart, &c->es, &c->mu,
                               &c->mu_old, &c->mu_new, &c->eind, &c->eic, &c->rrms, &c->rank_packed, &c->rmin_part,
                               &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms,
-                              &c->wolf_table, &c->scalars})
+                              &c->wolf_table, &c->scalars, &c->cbox, &c->sym_partI, &c->sym_partJ, &c->esum})
         b->release();
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();
     c->tiles.release();
@@ -1367,9 +1437,15 @@ int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
         case MPMC_STAGE_PASS:
             if (P.polar_zodid || c->pol.n <= 0) return 0;
             return polar_jacobi_pass(c, iteration) ? 10 : 0;
+        case MPMC_STAGE_UPDATE:
+            if (P.polar_zodid || c->pol.n <= 0 || !c->use_sym || c->world == 1) return 0;  // done inside PASS
+            return polar_update_sym(c, iteration) ? 10 : 0;
         case MPMC_STAGE_PALMO:
             if (P.polar_zodid || c->pol.n <= 0) return 0;
             return polar_palmo_pass(c) ? 10 : 0;
+        case MPMC_STAGE_PALMO_FINISH:
+            if (P.polar_zodid || c->pol.n <= 0 || !c->use_sym || c->world == 1) return 0;  // done inside PALMO
+            return polar_palmo_finish_sym(c) ? 10 : 0;
         case MPMC_STAGE_COMMIT:
             if (P.polar_zodid || c->pol.n <= 0) return 0;
             return polar_commit(c, iteration) ? 10 : 0;
@@ -1391,6 +1467,8 @@ int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
     }
 }
 
+int mpmc_b200_uses_symmetric_contraction(mpmc_b200_ctx* c) { return (c && c->use_sym) ? 1 : 0; }
+
 int mpmc_b200_shard_field_rows(mpmc_b200_ctx* c, int* begin, int* end, int* n_atoms_padded) {
     if (!c) FAIL(1, "null ctx");
     if (!c->have_atoms) FAIL(2, "no atoms");
@@ -1410,6 +1488,7 @@ int mpmc_b200_device_buffer(mpmc_b200_ctx* c, int which, void** dev_ptr, long lo
         case 1: *dev_ptr = c->mu_new.p; *n_doubles = 3LL * c->pol.n_pad; break;
         case 2: *dev_ptr = c->scalars.p; *n_doubles = 32; break;
         case 3: *dev_ptr = c->ef_static.p; *n_doubles = 3LL * c->n_pad; break;
+        case 4: *dev_ptr = c->esum.p; *n_doubles = 3LL * c->pol.n_pad; break;
         default: FAIL(1, "unknown buffer");
     }
     return 0;
@@ -1434,18 +1513,27 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
     CU(cudaSetDevice(c->device));
     const int n = c->n, np = c->n_pad, pp = c->pol.n_pad;
     std::vector<double> buf((size_t)3 * std::max(np, pp));
-    auto scatter3 = [&](const DevBuf<double>& d, double* out) -> int {
+    // sharded runs: mu is complete on every rank; the other arrays are reported for this rank's rows only
+    // (zero elsewhere) so that the caller's sum over ranks reassembles them
+    int kb = 0, ke = c->pol.n;
+    if (c->world > 1) {
+        int tb, te;
+        shard_range(pp / TILE, c->rank, c->world, tb, te);
+        kb = tb * TILE;
+        ke = std::min(te * TILE, c->pol.n);
+    }
+    auto scatter3 = [&](const DevBuf<double>& d, double* out, bool own_only = true) -> int {
         if (!out) return 0;
         CU(cudaMemcpyAsync(buf.data(), d.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
         std::fill(out, out + 3 * (size_t)n, 0.0);
-        for (int k = 0; k < c->pol.n; k++) {
+        for (int k = own_only ? kb : 0; k < (own_only ? ke : c->pol.n); k++) {
             const int g = c->pol.idx[k];
             for (int d3 = 0; d3 < 3; d3++) out[3 * g + d3] = buf[(size_t)d3 * pp + k];
         }
         return 0;
     };
-    if (scatter3(c->mu, mu) || scatter3(c->eind, ef_induced) || scatter3(c->eic, ef_induced_change)) return 10;
+    if (scatter3(c->mu, mu, false) || scatter3(c->eind, ef_induced) || scatter3(c->eic, ef_induced_change)) return 10;
     if (ef_induced_change && c->eic_np_valid && c->nonpol.n > 0) {
         const int qp = c->nonpol.n_pad;
         std::vector<double> nb((size_t)3 * qp);
@@ -1465,7 +1553,7 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
         CU(cudaMemcpyAsync(buf.data(), d.p, sizeof(double) * pp, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
         std::fill(out, out + n, 0.0);
-        for (int k = 0; k < c->pol.n; k++) out[c->pol.idx[k]] = buf[k];
+        for (int k = kb; k < ke; k++) out[c->pol.idx[k]] = buf[k];
         return 0;
     };
     if (scatter1(c->rrms, dipole_rrms) || scatter1(c->rank_packed, rank_metric)) return 10;

@@ -88,6 +88,16 @@ void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, con
 // palmo: field of the dipoles at the atoms of `rows` (the non-polarizable atoms), out[3][rows.n_pad]
 void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, const SubsetDev& pol, const DipoleOpts& o,
                             const double* mu, int row_begin, int row_end, double* out, cudaStream_t s);
+// Symmetric form of the contraction (dipole_sym_kernel.cu): T_ij computed once per unordered pair and
+// applied in both directions.  I tiles [tile_begin, tile_end) x offsets 0..T/2 (split in `ysplits` slices);
+// partial rows: epartI [ysplits][3][n_pad], epartJ [dipole_sym_partial_rows(n_pad)][3][n_pad];
+// esum [3][n_pad] receives this launch's contribution to E_ind for ALL rows (summed over ranks by the
+// caller in sharded runs).  cbox [6][n_pad/32] from launch_cluster_boxes().
+int dipole_sym_partial_rows(int n_pad);
+void launch_cluster_boxes(const SubsetDev& pol, double* cbox, cudaStream_t s);
+void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
+                                const double* cbox, int tile_begin, int tile_end, int ysplits, double* epartI,
+                                double* epartJ, double* esum, cudaStream_t s);
 struct UpdateOpts {
     int sor, esor, save_old, do_rrms;
     double gamma;

@@ -6,9 +6,14 @@ What is split (BASELINE north_star):
     -> partial scalars, summed over ranks at the end (one all-reduce of 12 doubles);
   * static-field rows (thole_field, reference src/polarization/thole_field.c:14-36)
     -> one all-gather of the field rows;
-  * dipole rows of every solver pass (contract_dipoles, src/polarization/thole_iterative.c:27-59)
-    -> an all-gather of the new dipole rows after EVERY pass (the one real exchange of the
-       path), plus an all-reduce(max) of the residual in polar_precision mode.
+  * the tile pairs of every solver pass (contract_dipoles, src/polarization/thole_iterative.c:27-59):
+    the dipole tensor is symmetric, so each rank evaluates T_ij once for its share of the unordered
+    tile pairs and applies it in both directions -> its contribution to the induced field of ALL rows
+    -> an all-reduce(sum) of the induced field (3 n_pol doubles) after EVERY pass: the one real
+       exchange of the path.  Every rank then updates every dipole (a few microseconds), so no
+       dipole all-gather and no residual all-reduce are needed.
+    (With the row-by-row contraction, MPMC_B200_K4=rows, rows are owned instead: an all-gather of
+    the new dipole rows after every pass plus an all-reduce(max) of the residual.)
 Gauss-Seidel modes are sequential in atom order and stay on one GPU.
 
 The collectives are issued by ``Exchange`` on the same CUDA stream as the engine's kernels, so no
@@ -154,6 +159,7 @@ class ShardedEngine:
             self.ex.all_gather_rows(self._view(3), 3, np_atoms)
             eng.polar_stage(api.STAGE_INIT)
             mu = self._view(0)
+            sym = bool(eng.uses_symmetric_contraction())
             if not p.polar_zodid and n_pol > 0:
                 allowed = p.polar_precision * p.polar_precision * DEBYE2SKA * DEBYE2SKA  # thole_iterative.c:106
                 keep = True
@@ -164,16 +170,24 @@ class ShardedEngine:
                         failed = True
                         break
                     eng.polar_stage(api.STAGE_PASS, iterations)
+                    if sym:
+                        self.ex.all_reduce(self._view(4), "sum")
+                        eng.polar_stage(api.STAGE_UPDATE, iterations)
                     if p.polar_precision == 0.0:
                         keep = iterations != p.polar_max_iter
                     else:
                         err = self._view(2)[12:13]
-                        self.ex.all_reduce(err, "max")
+                        if not sym:
+                            self.ex.all_reduce(err, "max")
                         keep = float(err.item()) > allowed
                     if p.polar_palmo and not keep:
                         eng.polar_stage(api.STAGE_PALMO)
+                        if sym:
+                            self.ex.all_reduce(self._view(4), "sum")
+                            eng.polar_stage(api.STAGE_PALMO_FINISH)
                     eng.polar_stage(api.STAGE_COMMIT, iterations)
-                    self.ex.all_gather_rows(mu, 3, pp)
+                    if not sym:
+                        self.ex.all_gather_rows(mu, 3, pp)
             eng.polar_stage(api.STAGE_ENERGY, iterations)
         part = eng.energy_finish()
         cnt = eng.counters()
@@ -198,8 +212,8 @@ class ShardedEngine:
         if self.world > 1:
             import torch
 
-            # mu and ef_static are complete on every rank after their all-gathers; the rest is
-            # valid on the owning rank's rows and zero elsewhere -> sum over ranks
+            # mu and ef_static are complete on every rank; the rest is reported for the owning
+            # rank's rows and zero elsewhere -> sum over ranks
             for k in ("ef_induced", "ef_induced_change", "dipole_rrms"):
                 t = torch.from_numpy(arr[k]).to(self.device)
                 self.ex.all_reduce(t, "sum")

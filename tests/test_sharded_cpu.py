@@ -43,9 +43,13 @@ class HostEngine:
 
     torch_device = "cpu"
 
-    def __init__(self, n_pol, seed=3):
+    def __init__(self, n_pol, seed=3, sym=True):
         self.n_pol, self.rank, self.world = n_pol, 0, 1
         self.seed = seed
+        self.sym = sym
+
+    def uses_symmetric_contraction(self):
+        return self.sym
 
     def set_shard(self, rank, world):
         self.rank, self.world = rank, world
@@ -61,7 +65,7 @@ class HostEngine:
         self.alpha = rng.uniform(0.5, 1.0, size=n)
         self.es_full = rng.normal(size=(3, n))
         self.bufs = {0: torch.zeros(3 * pp, dtype=torch.float64), 2: torch.zeros(32, dtype=torch.float64),
-                     3: torch.zeros(3 * self.npad, dtype=torch.float64)}
+                     3: torch.zeros(3 * self.npad, dtype=torch.float64), 4: torch.zeros(3 * pp, dtype=torch.float64)}
         self.mu_new = np.zeros((3, pp))
         self.mu_old = np.zeros((3, pp))
         self.eind = np.zeros((3, pp))
@@ -109,6 +113,31 @@ class HostEngine:
             mu[:] = 0.0
             mu[:, :self.n_pol] = self.alpha * self.es * self.p.polar_gamma
             self.eic[:] = 0.0
+        elif self.sym and stage in (api.STAGE_PASS, api.STAGE_PALMO):
+            # this rank's share of the pair sum (its column block of T) for ALL rows -> buffer 4
+            n = self.n_pol
+            x = mu[:, :n].T.reshape(-1)
+            cols = np.arange(3 * b, 3 * e)
+            part = -(self.T[:, cols] @ x[cols]).reshape(n, 3).T
+            es4 = self.bufs[4].numpy().reshape(3, self.pp)
+            es4[:] = 0.0
+            es4[:, :n] = part
+        elif self.sym and stage == api.STAGE_UPDATE:
+            n = self.n_pol
+            es4 = self.bufs[4].numpy().reshape(3, self.pp)
+            self.mu_old[:, :n] = mu[:, :n]
+            self.eind[:, :n] = es4[:, :n]
+            self.mu_new[:, :n] = self.alpha * (self.es + self.eind[:, :n])
+            d = self.mu_new[:, :n] - self.mu_old[:, :n]
+            self.bufs[2][12] = float((d * d).max())
+        elif self.sym and stage == api.STAGE_PALMO_FINISH:
+            n = self.n_pol
+            es4 = self.bufs[4].numpy().reshape(3, self.pp)
+            self.eic[:, :n] = -self.eind[:, :n] + es4[:, :n]
+        elif self.sym and stage == api.STAGE_COMMIT:
+            mu[:, :self.n_pol] = self.mu_new[:, :self.n_pol]
+        elif stage in (api.STAGE_UPDATE, api.STAGE_PALMO_FINISH):
+            pass
         elif stage == api.STAGE_PASS:
             self.mu_old[:, b:e] = mu[:, b:e]
             self.eind[:, b:e] = self._contract(b, e)
@@ -139,8 +168,11 @@ class HostEngine:
 
     def atom_arrays(self):
         mu = self.bufs[0].numpy().reshape(3, self.pp)[:, :self.n_pol].T.copy()
-        return {"mu": mu, "ef_static": self.es.T.copy(), "ef_induced": self.eind[:, :self.n_pol].T.copy(),
-                "ef_induced_change": self.eic[:, :self.n_pol].T.copy(), "dipole_rrms": np.zeros(self.n_pol)}
+        own = np.zeros((3, self.pp))
+        b, e = self._rows()
+        own[:, b:e] = 1.0  # like the engine: summed arrays are reported for own rows only
+        return {"mu": mu, "ef_static": self.es.T.copy(), "ef_induced": (self.eind * own)[:, :self.n_pol].T.copy(),
+                "ef_induced_change": (self.eic * own)[:, :self.n_pol].T.copy(), "dipole_rrms": np.zeros(self.n_pol)}
 
 
 def _system(**kw):
@@ -152,15 +184,15 @@ def _system(**kw):
     return api.System(p, np.zeros((1, 3)), z, z, z, z, z, np.zeros(1, dtype=np.int32), np.zeros(1, dtype=np.int32))
 
 
-def _solve(rank, world, n_pol, kw):
-    eng = HostEngine(n_pol)
+def _solve(rank, world, n_pol, kw, sym=True):
+    eng = HostEngine(n_pol, sym=sym)
     sh = ShardedEngine(eng, rank, world)
     sh.set_system(_system(**kw))
     e = sh._energy_sharded()
     return e, sh.atom_arrays(), eng.log
 
 
-def _worker(rank, world, port, n_pol, kw, ret):
+def _worker(rank, world, port, n_pol, kw, ret, sym=True):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -175,7 +207,7 @@ def _worker(rank, world, port, n_pol, kw, ret):
         Exchange(rank, world).all_gather_rows(buf, 3, npad)
         assert torch.equal(buf, full)
         # 2. the staged solver
-        e, arr, log = _solve(rank, world, n_pol, kw)
+        e, arr, log = _solve(rank, world, n_pol, kw, sym)
         ret[rank] = (e.polar, e.polar_iterations, e.iter_success, arr["mu"], arr["ef_induced"], arr["ef_induced_change"], log)
     finally:
         dist.destroy_process_group()
@@ -184,12 +216,15 @@ def _worker(rank, world, port, n_pol, kw, ret):
 @pytest.mark.parametrize("kw", [dict(polar_max_iter=6), dict(polar_max_iter=4, polar_palmo=1),
                                 dict(polar_max_iter=0, polar_precision=1e-9),
                                 dict(polar_max_iter=0, polar_precision=1e-9, polar_palmo=1)])
-def test_two_rank_solver_equals_one_rank(kw):
+@pytest.mark.parametrize("sym", [True, False])
+def test_two_rank_solver_equals_one_rank(kw, sym):
+    """sym=True: symmetric contraction, all-reduce of the induced field; sym=False: row form,
+    all-gather of the dipole rows (MPMC_B200_K4=rows)."""
     n_pol, world = 300, 2
-    ref_e, ref_arr, ref_log = _solve(0, 1, n_pol, kw)
+    ref_e, ref_arr, ref_log = _solve(0, 1, n_pol, kw, sym)
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(world, _free_port(), n_pol, kw, ret), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), n_pol, kw, ret, sym), nprocs=world, join=True)
     assert ref_e.polar_iterations > 1
     for r in range(world):
         upol, it, fail, mu, eind, eic, log = ret[r]
@@ -200,4 +235,4 @@ def test_two_rank_solver_equals_one_rank(kw):
         np.testing.assert_allclose(eind, ref_arr["ef_induced"], rtol=0, atol=1e-13)
         np.testing.assert_allclose(eic, ref_arr["ef_induced_change"], rtol=0, atol=1e-13)
     if kw.get("polar_palmo"):
-        assert ref_log.count(api.STAGE_PALMO) == 1 and ref_log[-3] == api.STAGE_PALMO
+        assert ref_log.count(api.STAGE_PALMO) == 1 and ref_log[-4 if sym else -3] == api.STAGE_PALMO
