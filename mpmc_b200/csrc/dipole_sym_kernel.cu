@@ -36,6 +36,8 @@ struct SymConsts {
     double wd1, wd2, ircut3;  // wolf-full (thole_matrix.c:123-130)
     double far2;              // r^2 beyond which damp1 == damp2 == 1.0 exactly; <= 0: never
     double Lx, Ly, Lz, iLx, iLy, iLz;  // orthorhombic box (cluster classification only)
+    double ec[12];                     // 1/k!, k = 0..11 (exp_neg_fast)
+    int fastexp;                       // l * (largest possible r) < 700: exp_neg_fast is valid
 };
 
 template <bool ORTHO>
@@ -128,9 +130,9 @@ __device__ __forceinline__ double cluster_gap2(const SymConsts& k, const double*
 }
 
 struct SymArgs {
-    int n, np, T;
-    int tile_begin;  // first I tile of this launch (gridDim.x tiles follow)
-    int K;           // T/2: offsets 0..K
+    int n, np, S;    // polarizable atoms, padded, super tiles (np / 256)
+    int tile_begin;  // first I super tile of this launch (gridDim.x follow)
+    int K;           // S/2: offsets 0..K
     int kper;        // offsets per gridDim.y slice
     const double *x, *y, *z, *aux;
     const int* mol;
@@ -140,48 +142,119 @@ struct SymArgs {
     double* epartJ;      // [K][3][np]
 };
 
-// one (i-cluster in registers) x (j-cluster of 32 in shared memory) block, both directions
-template <bool ORTHO, int DAMP, bool WF, bool FAR, bool CHECK>
-__device__ __forceinline__ void cluster_pair(const Cell& c, const SymConsts& k, int lane, int i, int jbase_global, int n,
-                                             const double* __restrict__ sx, const double* __restrict__ sy,
-                                             const double* __restrict__ sz, const double* __restrict__ smx,
-                                             const double* __restrict__ smy, const double* __restrict__ smz,
-                                             const double* __restrict__ saux, const int* __restrict__ smol, double xi,
-                                             double yi, double zi, double mxi, double myi, double mzi, double auxi, int moli,
-                                             double& exi, double& eyi, double& ezi, double& ajx, double& ajy, double& ajz) {
+constexpr int STILE = 256;  // atoms per super tile: 2 per thread
+constexpr int JREC = 6;     // doubles per staged j record: x y z mx my mz
+
+// 1/sqrt(a): MUFU.RSQ64H seed (2^-22.9) + one third-order step, no range checks (a is a squared distance
+// between distinct atoms).  5 fp64 instructions like the library's fast path, without its slow-path test.
+__device__ __forceinline__ double rsqrt_fast(double a) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+    const double e = fma(a, -(y * y), 1.0);
+    const double p = fma(e, 0.375, 0.5);
+    return fma(p, y * e, y);
+}
+
+// e^{-x} for 0 <= x < 700: Cody-Waite reduction by ln2 with the magic-number rint, degree-11 Taylor
+// polynomial on |r| <= ln2/2 (truncation error 6.4e-15 relative), exponent inserted with one integer add.
+// The coefficients arrive through the constant bank (kernel parameter), so every DFMA takes its constant
+// as an operand instead of materialising it with two moves.
+__device__ __forceinline__ double exp_neg_fast(const SymConsts& k, double x) {
+    const double magic = 6755399441055744.0;
+    const double t = fma(x, -1.4426950408889634, magic);
+    const double nd = t - magic;
+    double r = fma(nd, -6.93147180369123816490e-01, -x);
+    r = fma(nd, -1.90821492927058770002e-10, r);
+    double p = k.ec[11];
+    p = fma(p, r, k.ec[10]);
+    p = fma(p, r, k.ec[9]);
+    p = fma(p, r, k.ec[8]);
+    p = fma(p, r, k.ec[7]);
+    p = fma(p, r, k.ec[6]);
+    p = fma(p, r, k.ec[5]);
+    p = fma(p, r, k.ec[4]);
+    p = fma(p, r, k.ec[3]);
+    p = fma(p, r, k.ec[2]);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const int n = __double2loint(t);
+    return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+
+// c1 = damp1/r^3, c2 = 3 damp2/r^5 from r^2 (exponential damping, fast math helpers)
+template <bool WF, bool FAR, bool FASTEXP>
+__device__ __forceinline__ void coeffs_exp(const SymConsts& k, double r2, double& c1, double& c2) {
+    const double ir = rsqrt_fast(r2);
+    const double ir2 = ir * ir;
+    const double ir3 = ir * ir2;
+    if (FAR) {
+        c1 = ir3;
+        c2 = (3.0 * ir3) * ir2;
+    } else {
+        const double r = r2 * ir;
+        const double lr = k.l * r;
+        const double e = FASTEXP ? exp_neg_fast(k, lr) : exp(-lr);
+        const double damp1 = 1.0 - e * (k.l2h * r2 + lr + 1.0);
+        const double damp2 = damp1 - e * (k.l3s * r2 * r);
+        c1 = damp1 * ir3;
+        c2 = 3.0 * damp2 * ir3 * ir2;
+    }
+    if (WF) {
+        c1 -= k.wd1;
+        c2 -= k.wd2 * ir2;
+    }
+}
+
+// One j-cluster of 32 (records staged twice in a row, so lane+s never wraps) against the two i atoms a
+// lane keeps in registers; T once per unordered pair, applied in both directions.
+template <bool ORTHO, int DAMP, bool WF, bool FAR, bool CHECK, bool FASTEXP>
+__device__ __forceinline__ void cluster_pair2(const Cell& c, const SymConsts& k, int lane, int ia, int jbase_global, int n,
+                                              const double* __restrict__ rec, const double* __restrict__ saux,
+                                              const int* __restrict__ smol, const double (&pi)[2][6],
+                                              const double (&auxi)[2], const int (&moli)[2], double (&ei)[2][3],
+                                              double& ajx, double& ajy, double& ajz) {
     ajx = ajy = ajz = 0.0;
-#pragma unroll 2
+    const double* base = rec + lane * JREC;
+#pragma unroll 8
     for (int s = 0; s < 32; s++) {
-        const int jl = (lane + s) & 31;
-        double dx = xi - sx[jl], dy = yi - sy[jl], dz = zi - sz[jl];
-        const double mxj = smx[jl], myj = smy[jl], mzj = smz[jl];
-        min_image_xu<ORTHO>(c, dx, dy, dz);
-        const double r2 = dx * dx + dy * dy + dz * dz;
-        double c1, c2;
+        const double2 pxy = *reinterpret_cast<const double2*>(base + s * JREC);
+        const double2 pzm = *reinterpret_cast<const double2*>(base + s * JREC + 2);
+        const double2 pmm = *reinterpret_cast<const double2*>(base + s * JREC + 4);
+        const double xj = pxy.x, yj = pxy.y, zj = pzm.x, mxj = pzm.y, myj = pmm.x, mzj = pmm.y;
         double auxj = 0.0;
-        bool same = false;
-        if (DAMP != MPMC_DAMP_EXPONENTIAL) auxj = saux[jl];
-        if (DAMP == MPMC_DAMP_OFF) same = (moli == smol[jl]);
-        tensor_coeffs<DAMP, WF, FAR>(k, r2, auxi, auxj, same, c1, c2);
-        if (CHECK) {
-            const bool valid = (i < n) && (jbase_global + jl < n);
-            c1 = valid ? c1 : 0.0;
-            c2 = valid ? c2 : 0.0;
+        int molj = 0;
+        if (DAMP != MPMC_DAMP_EXPONENTIAL) auxj = saux[lane + s];
+        if (DAMP == MPMC_DAMP_OFF) molj = smol[lane + s];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            double dx = pi[u][0] - xj, dy = pi[u][1] - yj, dz = pi[u][2] - zj;
+            min_image_xu<ORTHO>(c, dx, dy, dz);
+            const double r2 = dx * dx + dy * dy + dz * dz;
+            double c1, c2;
+            if (DAMP == MPMC_DAMP_EXPONENTIAL)
+                coeffs_exp<WF, FAR, FASTEXP>(k, r2, c1, c2);
+            else
+                tensor_coeffs<DAMP, WF, false>(k, r2, auxi[u], auxj, moli[u] == molj, c1, c2);
+            if (CHECK) {
+                const bool valid = (ia + 32 * u < n) && (jbase_global + ((lane + s) & 31) < n);
+                c1 = valid ? c1 : 0.0;
+                c2 = valid ? c2 : 0.0;
+            }
+            const double dmj = (dx * mxj + dy * myj + dz * mzj) * c2;
+            const double dmi = (dx * pi[u][3] + dy * pi[u][4] + dz * pi[u][5]) * c2;
+            ei[u][0] = fma(dmj, dx, ei[u][0]);
+            ei[u][1] = fma(dmj, dy, ei[u][1]);
+            ei[u][2] = fma(dmj, dz, ei[u][2]);
+            ei[u][0] = fma(-c1, mxj, ei[u][0]);
+            ei[u][1] = fma(-c1, myj, ei[u][1]);
+            ei[u][2] = fma(-c1, mzj, ei[u][2]);
+            ajx = fma(dmi, dx, ajx);
+            ajy = fma(dmi, dy, ajy);
+            ajz = fma(dmi, dz, ajz);
+            ajx = fma(-c1, pi[u][3], ajx);
+            ajy = fma(-c1, pi[u][4], ajy);
+            ajz = fma(-c1, pi[u][5], ajz);
         }
-        const double dmj = (dx * mxj + dy * myj + dz * mzj) * c2;
-        const double dmi = (dx * mxi + dy * myi + dz * mzi) * c2;
-        exi = fma(dmj, dx, exi);
-        eyi = fma(dmj, dy, eyi);
-        ezi = fma(dmj, dz, ezi);
-        exi = fma(-c1, mxj, exi);
-        eyi = fma(-c1, myj, eyi);
-        ezi = fma(-c1, mzj, ezi);
-        ajx = fma(dmi, dx, ajx);
-        ajy = fma(dmi, dy, ajy);
-        ajz = fma(dmi, dz, ajz);
-        ajx = fma(-c1, mxi, ajx);
-        ajy = fma(-c1, myi, ajy);
-        ajz = fma(-c1, mzi, ajz);
         // the accumulator follows its j: lane l needs the one lane l+1 holds now
         const int src = (lane + 1) & 31;
         ajx = __shfl_sync(0xffffffffu, ajx, src);
@@ -190,108 +263,140 @@ __device__ __forceinline__ void cluster_pair(const Cell& c, const SymConsts& k, 
     }
 }
 
-template <bool ORTHO, int DAMP, bool WF>
-__global__ void __launch_bounds__(TILE) dipole_sym_kernel(Cell c, SymConsts k, SymArgs a) {
-    __shared__ double sx[TILE], sy[TILE], sz[TILE], smx[TILE], smy[TILE], smz[TILE], saux[TILE];
-    __shared__ int smol[TILE];
+template <bool ORTHO, int DAMP, bool WF, bool FASTEXP>
+__global__ void __launch_bounds__(TILE, 4) dipole_sym_kernel(Cell c, SymConsts k, SymArgs a) {
+    // j records of one half super tile: 4 clusters x (32 records stored twice) x 6 doubles
+    __shared__ __align__(16) double srec[4][64][JREC];
+    __shared__ double saux[4][64];
+    __shared__ int smol[4][64];
     __shared__ double sej[4][3][TILE];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int I = a.tile_begin + blockIdx.x;
-    const int np = a.np, T = a.T, nclus = np >> 5;
-    const int i = I * TILE + tid;
-    const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
-    const double mxi = a.mu[i], myi = a.mu[np + i], mzi = a.mu[2 * np + i];
-    const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[i];
-    const int moli = (DAMP == MPMC_DAMP_OFF) ? a.mol[i] : 0;
-    const int ci = I * 4 + w;
-    double exi = 0.0, eyi = 0.0, ezi = 0.0;
+    const int np = a.np, S = a.S, nclus = np >> 5;
+    // thread t keeps atoms ia and ia + 32: warp w owns the i-clusters 2w and 2w+1 of the super tile
+    const int ia = I * STILE + w * 64 + lane;
+    double pi[2][6], auxi[2] = {0.0, 0.0}, ei[2][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
+    int moli[2] = {0, 0};
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+        const int i = ia + 32 * u;
+        pi[u][0] = a.x[i];
+        pi[u][1] = a.y[i];
+        pi[u][2] = a.z[i];
+        pi[u][3] = a.mu[i];
+        pi[u][4] = a.mu[np + i];
+        pi[u][5] = a.mu[2 * np + i];
+        if (DAMP != MPMC_DAMP_EXPONENTIAL) auxi[u] = a.aux[i];
+        if (DAMP == MPMC_DAMP_OFF) moli[u] = a.mol[i];
+    }
+    const int ci = (I * STILE + w * 64) >> 5;  // first of this warp's two i-clusters
 
     const int k0 = blockIdx.y * a.kper, k1 = min(k0 + a.kper, a.K + 1);
     for (int kk = k0; kk < k1; kk++) {
-        if (kk > 0 && 2 * kk == T && I >= kk) continue;  // even T: the half-way offset belongs to I < T/2
+        if (kk > 0 && 2 * kk == S && I >= kk) continue;  // even S: the half-way offset belongs to I < S/2
         int J = I + kk;
-        if (J >= T) J -= T;
-        __syncthreads();
-        {
-            const int j = J * TILE + tid;
-            sx[tid] = a.x[j];
-            sy[tid] = a.y[j];
-            sz[tid] = a.z[j];
-            smx[tid] = a.mu[j];
-            smy[tid] = a.mu[np + j];
-            smz[tid] = a.mu[2 * np + j];
-            if (DAMP != MPMC_DAMP_EXPONENTIAL) saux[tid] = a.aux[j];
-            if (DAMP == MPMC_DAMP_OFF) smol[tid] = a.mol[j];
-        }
-        __syncthreads();
-        if (kk == 0) {
-            // diagonal tile: every ordered pair inside the tile, I side only
-            const int jn = min(TILE, a.n - J * TILE);
-            if (i < a.n) {
-                for (int jj = 0; jj < jn; jj++) {
-                    if (jj == tid) continue;
-                    double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
-                    min_image_xu<ORTHO>(c, dx, dy, dz);
-                    const double r2 = dx * dx + dy * dy + dz * dz;
-                    double c1, c2;
-                    tensor_coeffs<DAMP, WF, false>(k, r2, auxi, saux[jj], moli == smol[jj], c1, c2);
-                    const double dmj = (dx * smx[jj] + dy * smy[jj] + dz * smz[jj]) * c2;
-                    exi = fma(dmj, dx, exi);
-                    eyi = fma(dmj, dy, eyi);
-                    ezi = fma(dmj, dz, ezi);
-                    exi = fma(-c1, smx[jj], exi);
-                    eyi = fma(-c1, smy[jj], eyi);
-                    ezi = fma(-c1, smz[jj], ezi);
-                }
-            }
-            continue;
-        }
-        const bool check = ((I + 1) * TILE > a.n) || ((J + 1) * TILE > a.n);  // tiles that hold padding
-        // classification of the 4 (i-cluster, j-cluster) blocks of this warp: lanes 0..3 test one each
-        unsigned farmask = 0;
-        if (ORTHO && DAMP == MPMC_DAMP_EXPONENTIAL && k.far2 > 0.0) {
-            bool f = false;
-            if (lane < 4) f = cluster_gap2(k, a.cbox, a.cbox, nclus, ci, J * 4 + lane) >= k.far2;
-            farmask = __ballot_sync(0xffffffffu, f) & 0xfu;
-        }
+        if (J >= S) J -= S;
 #pragma unroll 1
-        for (int b = 0; b < 4; b++) {
-            const int jc = (w + b) & 3;
-            const int o = jc * 32;
-            double ajx, ajy, ajz;
-            const bool far = (farmask >> jc) & 1u;
-#define CP(FAR, CHECK)                                                                                                \
-    cluster_pair<ORTHO, DAMP, WF, FAR, CHECK>(c, k, lane, i, J * TILE + o, a.n, sx + o, sy + o, sz + o, smx + o, smy + o, \
-                                              smz + o, saux + o, smol + o, xi, yi, zi, mxi, myi, mzi, auxi, moli, exi,  \
-                                              eyi, ezi, ajx, ajy, ajz)
-            if (check) {
-                CP(false, true);
-            } else if (far) {
-                CP(true, false);
-            } else {
-                CP(false, false);
-            }
-#undef CP
-            sej[w][0][o + lane] = ajx;
-            sej[w][1][o + lane] = ajy;
-            sej[w][2][o + lane] = ajz;
-        }
-        __syncthreads();
-        {
-            double* ej = a.epartJ + (size_t)(kk - 1) * 3 * np + (size_t)J * TILE + tid;
+        for (int half = 0; half < 2; half++) {
+            const int jb = J * STILE + half * TILE;  // first atom of this half
+            __syncthreads();
+            {
+                const int j = jb + tid;
+                const int cl = tid >> 5, l = tid & 31;
+                const double xj = a.x[j], yj = a.y[j], zj = a.z[j];
+                const double mx = a.mu[j], my = a.mu[np + j], mz = a.mu[2 * np + j];
 #pragma unroll
-            for (int cc = 0; cc < 3; cc++) ej[(size_t)cc * np] = ((sej[0][cc][tid] + sej[1][cc][tid]) + sej[2][cc][tid]) + sej[3][cc][tid];
+                for (int d = 0; d < 2; d++) {
+                    double* r = &srec[cl][l + 32 * d][0];
+                    r[0] = xj;
+                    r[1] = yj;
+                    r[2] = zj;
+                    r[3] = mx;
+                    r[4] = my;
+                    r[5] = mz;
+                }
+                if (DAMP != MPMC_DAMP_EXPONENTIAL) saux[cl][l] = saux[cl][l + 32] = a.aux[j];
+                if (DAMP == MPMC_DAMP_OFF) smol[cl][l] = smol[cl][l + 32] = a.mol[j];
+            }
+            __syncthreads();
+            if (kk == 0) {
+                // diagonal super tile: every ordered pair inside it, I side only
+                const int jn = min(TILE, a.n - jb);
+#pragma unroll
+                for (int u = 0; u < 2; u++) {
+                    const int i = ia + 32 * u;
+                    if (i >= a.n) continue;
+                    for (int jj = 0; jj < jn; jj++) {
+                        if (jb + jj == i) continue;
+                        const double* r = &srec[jj >> 5][jj & 31][0];
+                        double dx = pi[u][0] - r[0], dy = pi[u][1] - r[1], dz = pi[u][2] - r[2];
+                        min_image_xu<ORTHO>(c, dx, dy, dz);
+                        const double r2 = dx * dx + dy * dy + dz * dz;
+                        double c1, c2;
+                        tensor_coeffs<DAMP, WF, false>(k, r2, auxi[u], saux[jj >> 5][jj & 31], moli[u] == smol[jj >> 5][jj & 31],
+                                                       c1, c2);
+                        const double dmj = (dx * r[3] + dy * r[4] + dz * r[5]) * c2;
+                        ei[u][0] = fma(dmj, dx, ei[u][0]);
+                        ei[u][1] = fma(dmj, dy, ei[u][1]);
+                        ei[u][2] = fma(dmj, dz, ei[u][2]);
+                        ei[u][0] = fma(-c1, r[3], ei[u][0]);
+                        ei[u][1] = fma(-c1, r[4], ei[u][1]);
+                        ei[u][2] = fma(-c1, r[5], ei[u][2]);
+                    }
+                }
+                continue;
+            }
+            const bool check = ((I + 1) * STILE > a.n) || (jb + TILE > a.n);  // tiles that hold padding
+            // (2 i-clusters) x (4 j-clusters): lanes 0..7 test one combination each
+            unsigned farmask = 0;
+            if (ORTHO && DAMP == MPMC_DAMP_EXPONENTIAL && k.far2 > 0.0) {
+                bool f = false;
+                if (lane < 8) f = cluster_gap2(k, a.cbox, a.cbox, nclus, ci + (lane >> 2), (jb >> 5) + (lane & 3)) >= k.far2;
+                farmask = __ballot_sync(0xffffffffu, f);
+                farmask = farmask & (farmask >> 4) & 0xfu;  // both i-clusters far from j-cluster b
+            }
+#pragma unroll 1
+            for (int b = 0; b < 4; b++) {
+                const int jc = (w + b) & 3;
+                double ajx, ajy, ajz;
+                const bool far = (farmask >> jc) & 1u;
+#define CP(FAR, CHECK)                                                                                                     \
+    cluster_pair2<ORTHO, DAMP, WF, FAR, CHECK, FASTEXP>(c, k, lane, ia, jb + jc * 32, a.n, &srec[jc][0][0], &saux[jc][0], \
+                                                        &smol[jc][0], pi, auxi, moli, ei, ajx, ajy, ajz)
+                if (check) {
+                    CP(false, true);
+                } else if (far) {
+                    CP(true, false);
+                } else {
+                    CP(false, false);
+                }
+#undef CP
+                sej[w][0][jc * 32 + lane] = ajx;
+                sej[w][1][jc * 32 + lane] = ajy;
+                sej[w][2][jc * 32 + lane] = ajz;
+            }
+            __syncthreads();
+            {
+                double* ej = a.epartJ + (size_t)(kk - 1) * 3 * np + (size_t)jb + tid;
+#pragma unroll
+                for (int cc = 0; cc < 3; cc++)
+                    ej[(size_t)cc * np] = ((sej[0][cc][tid] + sej[1][cc][tid]) + sej[2][cc][tid]) + sej[3][cc][tid];
+            }
         }
     }
     double* e = a.epartI + (size_t)blockIdx.y * 3 * np;
-    e[i] = exi;
-    e[np + i] = eyi;
-    e[2 * np + i] = ezi;
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+        const int i = ia + 32 * u;
+        e[i] = ei[u][0];
+        e[np + i] = ei[u][1];
+        e[2 * np + i] = ei[u][2];
+    }
 }
 
 // E_ind[c][i] = sum_y epartI[y][c][i] (if tile(i) was an I tile of this launch) + sum_k epartJ[k-1][c][i] over the
 // offsets k whose I = tile(i) - k was processed.  Fixed order: y ascending, then k ascending in 8 interleaved lanes
-// combined in lane order.  One CTA = 32 consecutive atoms x 3 components x 8 k-lanes.
+// combined in lane order.  One CTA = 32 consecutive atoms x 3 components x 8 k-lanes.  T = super tiles.
 __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, int K, int tile_begin, int tile_end, int ysplits,
                                                                 const double* __restrict__ epartI,
                                                                 const double* __restrict__ epartJ,
@@ -299,7 +404,7 @@ __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, i
     __shared__ double part[8][3][32];
     const int li = threadIdx.x & 31, lk = threadIdx.x >> 5;
     const int i = blockIdx.x * 32 + li;
-    const int J = i / TILE;
+    const int J = i / STILE;
     double s0 = 0.0, s1 = 0.0, s2 = 0.0;
     if (lk == 0 && J >= tile_begin && J < tile_end) {
         for (int y = 0; y < ysplits; y++) {
@@ -383,6 +488,17 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
         const double rf = 48.0 / l * (1.0 + 1e-12);
         k.far2 = rf * rf;
     }
+    {
+        double f = 1.0;
+        for (int q = 0; q < 12; q++) {
+            k.ec[q] = 1.0 / f;
+            f *= (double)(q + 1);
+        }
+        // largest minimum-image separation is below half the sum of the lattice vector lengths
+        double rmax = 0.0;
+        for (int q = 0; q < 3; q++) rmax += 0.5 * sqrt(c.B[q][0] * c.B[q][0] + c.B[q][1] * c.B[q][1] + c.B[q][2] * c.B[q][2]);
+        k.fastexp = (l >= 0.0 && l * rmax < 700.0) ? 1 : 0;
+    }
     k.Lx = c.B[0][0];
     k.Ly = c.B[1][1];
     k.Lz = c.B[2][2];
@@ -400,24 +516,26 @@ void launch_cluster_boxes(const SubsetDev& pol, double* cbox, cudaStream_t s) {
     cluster_box_kernel<<<(nclus * 32 + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pol.x, pol.y, pol.z, cbox);
 }
 
+int dipole_sym_tile() { return STILE; }
+
 int dipole_sym_partial_rows(int n_pad) {
-    const int K = (n_pad / TILE) / 2;
+    const int K = (n_pad / STILE) / 2;
     return K > 1 ? K : 1;
 }
 
 void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
                                 const double* cbox, int tile_begin, int tile_end, int ysplits, double* epartI,
                                 double* epartJ, double* esum, cudaStream_t s) {
-    const int np = pol.n_pad, T = np / TILE, K = T / 2;
+    const int np = pol.n_pad, S = np / STILE, K = S / 2;
     const int ntile = tile_end - tile_begin;
-    if (T <= 0) return;
+    if (S <= 0) return;
     const SymConsts k = make_sym_consts(c, ortho, o);
     if (ysplits < 1) ysplits = 1;
     if (ysplits > K + 1) ysplits = K + 1;
     SymArgs a;
     a.n = pol.n;
     a.np = np;
-    a.T = T;
+    a.S = S;
     a.tile_begin = tile_begin;
     a.K = K;
     a.kper = (K + 1 + ysplits - 1) / ysplits;
@@ -433,16 +551,21 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
     a.epartJ = epartJ;
     if (ntile > 0) {
         dim3 grid(ntile, ysplits);
-#define LAUNCH(ORTHO, DAMP, WF) dipole_sym_kernel<ORTHO, DAMP, WF><<<grid, TILE, 0, s>>>(c, k, a)
-#define DISPATCH(ORTHO)                                              \
-    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
-        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true); \
-        else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false);            \
-    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                    \
-        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false);                      \
-    } else {                                                         \
-        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true);         \
-        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false);                    \
+#define LAUNCH(ORTHO, DAMP, WF, FE) dipole_sym_kernel<ORTHO, DAMP, WF, FE><<<grid, TILE, 0, s>>>(c, k, a)
+#define DISPATCH(ORTHO)                                                         \
+    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                                 \
+        if (k.fastexp) {                                                        \
+            if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true, true);  \
+            else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false, true);             \
+        } else {                                                                \
+            if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true, false); \
+            else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false, false);            \
+        }                                                                       \
+    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                               \
+        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false, false);                          \
+    } else {                                                                    \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true, false);             \
+        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false, false);                        \
     }
         if (ortho) {
             DISPATCH(true)
@@ -452,7 +575,7 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
 #undef DISPATCH
 #undef LAUNCH
     }
-    dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, T, K, tile_begin, tile_end, ysplits, epartI, epartJ, esum);
+    dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, S, K, tile_begin, tile_end, ysplits, epartI, epartJ, esum);
 }
 
 }  // namespace mpmc

@@ -501,7 +501,7 @@ static int repack(Ctx* c) {
         }
         if (c->halpha[i] != 0.0) pol.push_back(i);
     }
-    const int polpad = TILE * std::max(c->world, 1);
+    const int polpad = dipole_sym_tile() * std::max(c->world, 1);  // super tiles of the symmetric K4, equal shards
     if (pack_subset(c, c->charged, charged, TILE, false) || pack_subset(c, c->recip, recip, TILE, false) ||
         pack_subset(c, c->pol, pol, polpad, true) || pack_subset(c, c->nonpol, nonpol, polpad, true))
         return 11;
@@ -556,8 +556,9 @@ static int repack(Ctx* c) {
         FAIL(11, "cudaMalloc failed");
     {
         // symmetric K4: CTAs = I tiles x offset slices; a few waves of 4 CTAs per SM
-        const int own_tiles = std::max(1, ptiles / std::max(c->world, 1));
-        const int K1 = ptiles / 2 + 1;
+        const int stiles = pp / dipole_sym_tile();
+        const int own_tiles = std::max(1, stiles / std::max(c->world, 1));
+        const int K1 = stiles / 2 + 1;
         c->sym_ysplits = std::max(1, std::min(K1, (16 * sms + own_tiles - 1) / own_tiles));
         if (c->cbox.ensure((size_t)6 * (pp / 32)) || c->sym_partI.ensure((size_t)c->sym_ysplits * 3 * pp) ||
             c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
@@ -806,7 +807,7 @@ static int polar_init(Ctx* c) {
 static int polar_contract_sym(Ctx* c) {
     const mpmc_b200_params& P = c->P;
     int tb, te;
-    shard_range(c->pol.n_pad / TILE, c->rank, c->world, tb, te);
+    shard_range(c->pol.n_pad / dipole_sym_tile(), c->rank, c->world, tb, te);
     kev_mark(c);
     launch_dipole_contract_sym(make_cell(P), is_ortho(P), c->pol.dev(), dipole_opts(P), c->mu.p, c->cbox.p, tb, te,
                                c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p, c->esum.p, c->stream);
