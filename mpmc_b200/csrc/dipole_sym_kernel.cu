@@ -437,8 +437,12 @@ __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, i
     }
 }
 
-// centre and half extent of every 32-atom cluster (valid atoms only)
-__global__ void __launch_bounds__(256) cluster_box_kernel(int n, int np, const double* __restrict__ x,
+// centre and half extent of every 32-atom cluster (valid atoms only).  Orthorhombic boxes: positions are
+// taken as minimum-image displacements from the cluster's first atom, so a cluster whose atoms sit in
+// different periodic images (MPMC keeps unwrapped coordinates) still gets a tight box; the gap test in
+// cluster_gap2 is invariant under lattice translations of either cluster.
+__global__ void __launch_bounds__(256) cluster_box_kernel(int n, int np, double Lx, double Ly, double Lz, double iLx,
+                                                          double iLy, double iLz, int ortho, const double* __restrict__ x,
                                                           const double* __restrict__ y, const double* __restrict__ z,
                                                           double* __restrict__ cbox) {
     const int lane = threadIdx.x & 31;
@@ -447,20 +451,24 @@ __global__ void __launch_bounds__(256) cluster_box_kernel(int n, int np, const d
     if (cl >= nclus) return;
     const int i = cl * 32 + lane;
     const bool live = i < n;
-    const double px[3] = {live ? x[i] : 0.0, live ? y[i] : 0.0, live ? z[i] : 0.0};
+    double px[3] = {live ? x[i] : 0.0, live ? y[i] : 0.0, live ? z[i] : 0.0};
     const unsigned any = __ballot_sync(0xffffffffu, live);
+    const double L[3] = {Lx, Ly, Lz}, iL[3] = {iLx, iLy, iLz};
 #pragma unroll
     for (int d = 0; d < 3; d++) {
-        double lo = live ? px[d] : 1.0e300, hi = live ? px[d] : -1.0e300;
+        const double p0 = __shfl_sync(0xffffffffu, px[d], 0);  // lane 0 is live whenever any lane is
+        double v = px[d] - p0;
+        if (ortho) v = fma(-L[d], rint(v * iL[d]), v);
+        double lo = live ? v : 1.0e300, hi = live ? v : -1.0e300;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
             hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
         }
         if (lane == 0) {
-            cbox[d * nclus + cl] = any ? 0.5 * (lo + hi) : 0.0;
-            // round the half extent up by one ulp-scale so the bound stays conservative
-            cbox[(3 + d) * nclus + cl] = any ? 0.5 * (hi - lo) * (1.0 + 1e-14) + 1e-300 : 1.0e30;
+            cbox[d * nclus + cl] = any ? p0 + 0.5 * (lo + hi) : 0.0;
+            // half extent padded so that rounding in centre / extent can never make the bound optimistic
+            cbox[(3 + d) * nclus + cl] = any ? 0.5 * (hi - lo) * (1.0 + 1e-12) + 1e-9 : 1.0e30;
         }
     }
 }
@@ -510,10 +518,11 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
 
 }  // namespace
 
-void launch_cluster_boxes(const SubsetDev& pol, double* cbox, cudaStream_t s) {
+void launch_cluster_boxes(const Cell& c, bool ortho, const SubsetDev& pol, double* cbox, cudaStream_t s) {
     const int nclus = pol.n_pad / 32;
     if (nclus <= 0) return;
-    cluster_box_kernel<<<(nclus * 32 + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pol.x, pol.y, pol.z, cbox);
+    cluster_box_kernel<<<(nclus * 32 + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, c.B[0][0], c.B[1][1], c.B[2][2], c.R[0][0],
+                                                                c.R[1][1], c.R[2][2], ortho ? 1 : 0, pol.x, pol.y, pol.z, cbox);
 }
 
 int dipole_sym_tile() { return STILE; }

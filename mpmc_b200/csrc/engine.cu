@@ -150,6 +150,8 @@ struct mpmc_b200_ctx {
     int field_jsplits = 1, dipole_jsplits = 1;
     // symmetric K4 (dipole_sym_kernel.cu): cluster boxes, I-side / J-side partial rows, reduced field
     bool use_sym = true;
+    bool pol_sorted = false, resort_pending = false;
+    std::vector<double> hx_sort, hy_sort, hz_sort;  // positions at the time of the last spatial sort
     DevBuf<double> cbox, sym_partI, sym_partJ, esum;
     int sym_ysplits = 1;
     int fb = 0, fe = 0, pb = 0, pe = 0;  // this shard's static-field rows (atom space) and dipole rows (packed space)
@@ -440,6 +442,66 @@ static int build_kvectors(Ctx* c) {
     return 0;
 }
 
+// Spatial order of a set of atoms for the symmetric K4: recursive bisection along the longest axis of
+// the (wrapped) bounding box, split points on multiples of 32, so that every 32-atom cluster the kernel
+// classifies by its bounding box is a compact brick.  Any order gives the same sums up to rounding (the
+// reference's contract_dipoles adds j in list order, thole_iterative.c:38-46); the order is a pure function
+// of the positions, so results stay reproducible run to run.
+static void spatial_order(const Ctx* c, std::vector<int>& idx) {
+    const int n = (int)idx.size();
+    if (n <= 32) return;
+    const mpmc_b200_params& P = c->P;
+    // wrapped fractional coordinates scaled by the lattice vector lengths
+    std::vector<double> w(3 * (size_t)n);
+    double len[3];
+    for (int q = 0; q < 3; q++) len[q] = sqrt(P.basis[q][0] * P.basis[q][0] + P.basis[q][1] * P.basis[q][1] + P.basis[q][2] * P.basis[q][2]);
+    for (int k = 0; k < n; k++) {
+        const int g = idx[k];
+        const double r[3] = {c->hx[g], c->hy[g], c->hz[g]};
+        for (int p = 0; p < 3; p++) {
+            double f = P.reciprocal_basis[0][p] * r[0] + P.reciprocal_basis[1][p] * r[1] + P.reciprocal_basis[2][p] * r[2];
+            f -= floor(f);
+            w[3 * (size_t)k + p] = f * len[p];
+        }
+    }
+    std::vector<int> ord(n);
+    std::iota(ord.begin(), ord.end(), 0);
+    struct Range { int b, e; };
+    std::vector<Range> stack;
+    stack.push_back({0, n});
+    while (!stack.empty()) {
+        const Range r = stack.back();
+        stack.pop_back();
+        const int sz = r.e - r.b;
+        if (sz <= 32) {
+            std::sort(ord.begin() + r.b, ord.begin() + r.e);  // fixed order inside a cluster: by atom index
+            continue;
+        }
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (int k = r.b; k < r.e; k++)
+            for (int p = 0; p < 3; p++) {
+                const double v = w[3 * (size_t)ord[k] + p];
+                lo[p] = std::min(lo[p], v);
+                hi[p] = std::max(hi[p], v);
+            }
+        int ax = 0;
+        if (hi[1] - lo[1] > hi[ax] - lo[ax]) ax = 1;
+        if (hi[2] - lo[2] > hi[ax] - lo[ax]) ax = 2;
+        const int clusters = (sz + 31) / 32;
+        const int left = (clusters / 2) * 32;
+        const int mid = r.b + left;
+        std::nth_element(ord.begin() + r.b, ord.begin() + mid, ord.begin() + r.e, [&](int u, int v) {
+            const double a = w[3 * (size_t)u + ax], b = w[3 * (size_t)v + ax];
+            return a < b || (a == b && u < v);
+        });
+        stack.push_back({mid, r.e});
+        stack.push_back({r.b, mid});
+    }
+    std::vector<int> out(n);
+    for (int k = 0; k < n; k++) out[k] = idx[ord[k]];
+    idx.swap(out);
+}
+
 static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_multiple, bool with_aux) {
     const mpmc_b200_params& P = c->P;
     s.idx = idx;
@@ -500,6 +562,16 @@ static int repack(Ctx* c) {
             if (!c->hfrozen[i]) recip.push_back(i);  // coulombic.c:74-75
         }
         if (c->halpha[i] != 0.0) pol.push_back(i);
+    }
+    // Jacobi family: the polarizable list is kept in spatial order (symmetric K4); Gauss-Seidel processes
+    // atoms in list / rank order and keeps the list order
+    c->pol_sorted = false;
+    if (c->use_sym && !(c->P.polar_gs || c->P.polar_gs_ranked) && c->have_params) {
+        spatial_order(c, pol);
+        c->pol_sorted = true;
+        c->hx_sort = c->hx;
+        c->hy_sort = c->hy;
+        c->hz_sort = c->hz;
     }
     const int polpad = dipole_sym_tile() * std::max(c->world, 1);  // super tiles of the symmetric K4, equal shards
     if (pack_subset(c, c->charged, charged, TILE, false) || pack_subset(c, c->recip, recip, TILE, false) ||
@@ -598,6 +670,16 @@ static void kev_mark(Ctx* c) {
 }
 
 static int refresh_subsets(Ctx* c) {
+    if (c->resort_pending && c->pol_sorted) {
+        std::vector<int> pol = c->pol.idx;
+        std::sort(pol.begin(), pol.end());
+        spatial_order(c, pol);
+        if (pack_subset(c, c->pol, pol, dipole_sym_tile() * std::max(c->world, 1), true)) return 11;
+        c->hx_sort = c->hx;
+        c->hy_sort = c->hy;
+        c->hz_sort = c->hz;
+    }
+    c->resort_pending = false;
     if (!c->subsets_stale) return 0;
     for (Subset* s : {&c->charged, &c->recip, &c->pol, &c->nonpol}) {
         if (s->n <= 0) continue;
@@ -789,7 +871,7 @@ static int polar_init(Ctx* c) {
     launch_dipole_init(c->pol.dev(), c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st);
     c->launches++;
     if (c->use_sym && c->pol.n > 0) {
-        launch_cluster_boxes(c->pol.dev(), c->cbox.p, st);
+        launch_cluster_boxes(make_cell(P), is_ortho(P), c->pol.dev(), c->cbox.p, st);
         c->launches++;
     }
     const bool want_rrms = P.polar_rrms || P.polar_precision > 0;
@@ -1301,7 +1383,8 @@ int mpmc_b200_set_stream(mpmc_b200_ctx* c, void* cuda_stream) {
 
 int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
     if (!c || !p) FAIL(1, "null argument");
-    const bool repack_needed = c->have_atoms && (p->damp_type != c->P.damp_type);
+    const bool repack_needed = c->have_atoms && (p->damp_type != c->P.damp_type || p->polar_gs != c->P.polar_gs ||
+                                                  p->polar_gs_ranked != c->P.polar_gs_ranked);
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;
@@ -1364,6 +1447,18 @@ int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double
         sx[k] = c->hx[first + k] = pos[3 * k];
         sy[k] = c->hy[first + k] = pos[3 * k + 1];
         sz[k] = c->hz[first + k] = pos[3 * k + 2];
+    }
+    if (c->pol_sorted && !c->resort_pending) {
+        // clusters stay compact as long as no atom has drifted far from where it was sorted
+        const double lim2 = 1.5 * 1.5;
+        for (int k = 0; k < count; k++) {
+            const int g = first + k;
+            const double dx = c->hx[g] - c->hx_sort[g], dy = c->hy[g] - c->hy_sort[g], dz = c->hz[g] - c->hz_sort[g];
+            if (dx * dx + dy * dy + dz * dz > lim2) {
+                c->resort_pending = true;
+                break;
+            }
+        }
     }
     CU(cudaMemcpyAsync(c->x.p + first, sx, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(c->y.p + first, sy, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));

@@ -95,7 +95,7 @@ void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, co
 // caller in sharded runs).  cbox [6][n_pad/32] from launch_cluster_boxes().
 int dipole_sym_tile();  // atoms per super tile (256): n_pad of the polarizable subset must be a multiple
 int dipole_sym_partial_rows(int n_pad);
-void launch_cluster_boxes(const SubsetDev& pol, double* cbox, cudaStream_t s);
+void launch_cluster_boxes(const Cell& c, bool ortho, const SubsetDev& pol, double* cbox, cudaStream_t s);
 void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
                                 const double* cbox, int tile_begin, int tile_end, int ysplits, double* epartI,
                                 double* epartJ, double* esum, cudaStream_t s);
