@@ -21,7 +21,7 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmpmc_b200.so")
+LIB_PATH = os.environ.get("MPMC_B200_LIB") or os.path.join(_HERE, "lib", "libmpmc_b200.so")  # env: profiling builds
 
 DAMP_OFF, DAMP_LINEAR, DAMP_EXPONENTIAL = 0, 1, 2
 MIX_LB, MIX_WH, MIX_HALGREN, MIX_C6 = 0, 1, 2, 3

@@ -25,6 +25,9 @@
 //     (e^{-lr}(...) < 2^-54 for l r >= 48): then exp() and the damping polynomial are skipped -- the
 //     result is bit-identical to evaluating them.
 //   * minimum image: rint() runs on the conversion pipe (FRND.F64), not on the fp64 FMA pipe.
+#include <cstdlib>
+#include <cstring>
+
 #include "kernels.h"
 
 namespace mpmc {
@@ -142,6 +145,13 @@ struct SymArgs {
     double* epartJ;      // [K][3][np]
 };
 
+#ifndef SYM_UNROLL
+#define SYM_UNROLL 4  // 8 overflows the instruction cache (ncu: stall_no_instruction), 2 and 4 time alike
+#endif
+#ifndef SYM_MINB
+#define SYM_MINB 4
+#endif
+constexpr int kSymUnroll = SYM_UNROLL;
 constexpr int STILE = 256;  // atoms per super tile: 2 per thread
 constexpr int JREC = 6;     // doubles per staged j record: x y z mx my mz
 
@@ -215,7 +225,7 @@ __device__ __forceinline__ void cluster_pair2(const Cell& c, const SymConsts& k,
                                               double& ajx, double& ajy, double& ajz) {
     ajx = ajy = ajz = 0.0;
     const double* base = rec + lane * JREC;
-#pragma unroll 8
+#pragma unroll kSymUnroll
     for (int s = 0; s < 32; s++) {
         const double2 pxy = *reinterpret_cast<const double2*>(base + s * JREC);
         const double2 pzm = *reinterpret_cast<const double2*>(base + s * JREC + 2);
@@ -264,7 +274,7 @@ __device__ __forceinline__ void cluster_pair2(const Cell& c, const SymConsts& k,
 }
 
 template <bool ORTHO, int DAMP, bool WF, bool FASTEXP>
-__global__ void __launch_bounds__(TILE, 4) dipole_sym_kernel(Cell c, SymConsts k, SymArgs a) {
+__global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymConsts k, SymArgs a) {
     // j records of one half super tile: 4 clusters x (32 records stored twice) x 6 doubles
     __shared__ __align__(16) double srec[4][64][JREC];
     __shared__ double saux[4][64];
@@ -506,6 +516,10 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
         double rmax = 0.0;
         for (int q = 0; q < 3; q++) rmax += 0.5 * sqrt(c.B[q][0] * c.B[q][0] + c.B[q][1] * c.B[q][1] + c.B[q][2] * c.B[q][2]);
         k.fastexp = (l >= 0.0 && l * rmax < 700.0) ? 1 : 0;
+    }
+    if (const char* v = getenv("MPMC_B200_SYM_FAR")) {  // timing experiments only ("all" gives wrong fields)
+        if (!strcmp(v, "off")) k.far2 = 0.0;
+        if (!strcmp(v, "all") && k.far2 > 0.0) k.far2 = 1e-300;
     }
     k.Lx = c.B[0][0];
     k.Ly = c.B[1][1];

@@ -631,7 +631,9 @@ static int repack(Ctx* c) {
         const int stiles = pp / dipole_sym_tile();
         const int own_tiles = std::max(1, stiles / std::max(c->world, 1));
         const int K1 = stiles / 2 + 1;
-        c->sym_ysplits = std::max(1, std::min(K1, (16 * sms + own_tiles - 1) / own_tiles));
+        int per_sm = 48;  // measured on M4: 16 -> 48 CTAs per SM removes most of the last-wave tail
+        if (const char* v = getenv("MPMC_B200_SYM_CTAS_PER_SM")) per_sm = std::max(1, atoi(v));
+        c->sym_ysplits = std::max(1, std::min(K1, (per_sm * sms + own_tiles - 1) / own_tiles));
         if (c->cbox.ensure((size_t)6 * (pp / 32)) || c->sym_partI.ensure((size_t)c->sym_ysplits * 3 * pp) ||
             c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
             FAIL(11, "cudaMalloc failed");
