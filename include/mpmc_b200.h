@@ -179,8 +179,8 @@ int mpmc_b200_energy_finish(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
  * context's stream and returns; between stages the CALLER runs the collectives (on the same
  * stream) over the buffers returned by mpmc_b200_device_buffer():
  *   mpmc_b200_energy_enqueue()                    pair tiles + k-sum partials of this shard
- *   stage FIELD                                   static field for this shard's atom rows
- *        -> all-gather ef_static rows (buffer 3, rows from mpmc_b200_shard_field_rows)
+ *   stage FIELD                                   static field at the atoms of this shard's spatial clusters
+ *        -> all-reduce(sum) of ef_static (buffer 3; rows other ranks own are zero)
  *   stage INIT                                    mu0 = gamma alpha E_s for all rows (replicated)
  *   per iteration it = 1, 2, ...:
  *     stage PASS(it)                              symmetric dipole-tensor contraction over this shard's
@@ -203,6 +203,9 @@ enum { MPMC_STAGE_FIELD = 0, MPMC_STAGE_INIT = 1, MPMC_STAGE_PASS = 2, MPMC_STAG
 int mpmc_b200_polar_stage(mpmc_b200_ctx *ctx, int stage, int iteration);
 /* 1 when the symmetric contraction (all-reduce of buffer 4) is active, 0 for the row form (all-gather of buffer 0) */
 int mpmc_b200_uses_symmetric_contraction(mpmc_b200_ctx *ctx);
+/* 1 when the static field is computed per spatial cluster (every rank writes scattered rows of buffer 3: combine
+ * with an all-reduce(sum)), 0 for the row-tile form (contiguous row blocks: all-gather) */
+int mpmc_b200_uses_cluster_field(mpmc_b200_ctx *ctx);
 /* atom rows [begin,end) (padded, tile aligned) whose static field this shard computes */
 int mpmc_b200_shard_field_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_atoms_padded);
 /* Raw device pointer + element count of an internal buffer, for collectives

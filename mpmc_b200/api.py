@@ -305,6 +305,7 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_polar_stage.argtypes = [vp, C.c_int, C.c_int]
     lib.mpmc_b200_device_buffer.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(C.c_longlong)]
     lib.mpmc_b200_uses_symmetric_contraction.argtypes = [vp]
+    lib.mpmc_b200_uses_cluster_field.argtypes = [vp]
     lib.mpmc_b200_shard_rows.argtypes = [vp, ip, ip, ip, ip]
     lib.mpmc_b200_shard_field_rows.argtypes = [vp, ip, ip, ip]
     lib.mpmc_b200_get_atom_arrays.argtypes = [vp, dp, dp, dp, dp, dp, dp]
@@ -325,7 +326,8 @@ ABI_SYMBOLS = [
     "mpmc_b200_abi_version", "mpmc_b200_last_error", "mpmc_b200_create", "mpmc_b200_destroy", "mpmc_b200_set_stream",
     "mpmc_b200_set_params", "mpmc_b200_set_atoms", "mpmc_b200_set_positions", "mpmc_b200_set_shard",
     "mpmc_b200_energy", "mpmc_b200_polar", "mpmc_b200_energy_enqueue", "mpmc_b200_energy_finish",
-    "mpmc_b200_polar_stage", "mpmc_b200_uses_symmetric_contraction", "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
+    "mpmc_b200_polar_stage", "mpmc_b200_uses_symmetric_contraction", "mpmc_b200_uses_cluster_field",
+    "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
     "mpmc_b200_get_atom_arrays",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak",
 ]
@@ -404,6 +406,9 @@ class Engine:
 
     def uses_symmetric_contraction(self) -> bool:
         return bool(self.lib.mpmc_b200_uses_symmetric_contraction(self._ctx))
+
+    def uses_cluster_field(self) -> bool:
+        return bool(self.lib.mpmc_b200_uses_cluster_field(self._ctx))
 
     def device_buffer(self, which: int):
         ptr, n = C.c_void_p(), C.c_longlong()

@@ -90,4 +90,46 @@ __device__ __forceinline__ double block_reduce(double v, double* scratch) {
     return v;
 }
 
+// Orthorhombic box lengths for the cluster-level distance bounds.
+struct BoxLen {
+    double Lx, Ly, Lz, iLx, iLy, iLz;
+};
+__host__ __device__ inline BoxLen box_len(const Cell& c) {
+    BoxLen b;
+    b.Lx = c.B[0][0];
+    b.Ly = c.B[1][1];
+    b.Lz = c.B[2][2];
+    b.iLx = c.R[0][0];
+    b.iLy = c.R[1][1];
+    b.iLz = c.R[2][2];
+    return b;
+}
+
+// Lower bound of the minimum-image distance^2 between any atom of cluster ca (boxes `a`) and any atom of
+// cluster cb (boxes `b`), orthorhombic box: per axis |minimg(centre_a - centre_b)| - (half_a + half_b), clamped
+// at 0.  Box arrays are [6][nclus]: centre xyz, half extent xyz (cluster_box_kernel).
+__device__ __forceinline__ double cluster_gap2(const BoxLen& k, const double* __restrict__ a, int na, int ca,
+                                               const double* __restrict__ b, int nb, int cb) {
+    double g2 = 0.0;
+    {
+        double d = a[0 * na + ca] - b[0 * nb + cb];
+        d = fabs(fma(-k.Lx, rint(d * k.iLx), d)) - (a[3 * na + ca] + b[3 * nb + cb]);
+        d = fmax(d, 0.0);
+        g2 = fma(d, d, g2);
+    }
+    {
+        double d = a[1 * na + ca] - b[1 * nb + cb];
+        d = fabs(fma(-k.Ly, rint(d * k.iLy), d)) - (a[4 * na + ca] + b[4 * nb + cb]);
+        d = fmax(d, 0.0);
+        g2 = fma(d, d, g2);
+    }
+    {
+        double d = a[2 * na + ca] - b[2 * nb + cb];
+        d = fabs(fma(-k.Lz, rint(d * k.iLz), d)) - (a[5 * na + ca] + b[5 * nb + cb]);
+        d = fmax(d, 0.0);
+        g2 = fma(d, d, g2);
+    }
+    return g2;
+}
+
 }  // namespace mpmc

@@ -38,7 +38,7 @@ struct SymConsts {
     double l, l2h, l3s;       // l, l^2/2, l^3/6
     double wd1, wd2, ircut3;  // wolf-full (thole_matrix.c:123-130)
     double far2;              // r^2 beyond which damp1 == damp2 == 1.0 exactly; <= 0: never
-    double Lx, Ly, Lz, iLx, iLy, iLz;  // orthorhombic box (cluster classification only)
+    BoxLen box;               // orthorhombic box (cluster classification only)
     double ec[12];                     // 1/k!, k = 0..11 (exp_neg_fast)
     int fastexp;                       // l * (largest possible r) < 700: exp_neg_fast is valid
 };
@@ -104,32 +104,6 @@ __device__ __forceinline__ void tensor_coeffs(const SymConsts& k, double r2, dou
             c2 -= k.wd2 * ir2;
         }
     }
-}
-
-// lower bound of the minimum-image distance^2 between two clusters (orthorhombic box):
-// per axis |minimg(ci - cj)| - (hi + hj), clamped at 0
-__device__ __forceinline__ double cluster_gap2(const SymConsts& k, const double* __restrict__ a, const double* __restrict__ b,
-                                               int nclus, int ca, int cb) {
-    double g2 = 0.0;
-    {
-        double d = a[0 * nclus + ca] - b[0 * nclus + cb];
-        d = fabs(fma(-k.Lx, rint(d * k.iLx), d)) - (a[3 * nclus + ca] + b[3 * nclus + cb]);
-        d = fmax(d, 0.0);
-        g2 = fma(d, d, g2);
-    }
-    {
-        double d = a[1 * nclus + ca] - b[1 * nclus + cb];
-        d = fabs(fma(-k.Ly, rint(d * k.iLy), d)) - (a[4 * nclus + ca] + b[4 * nclus + cb]);
-        d = fmax(d, 0.0);
-        g2 = fma(d, d, g2);
-    }
-    {
-        double d = a[2 * nclus + ca] - b[2 * nclus + cb];
-        d = fabs(fma(-k.Lz, rint(d * k.iLz), d)) - (a[5 * nclus + ca] + b[5 * nclus + cb]);
-        d = fmax(d, 0.0);
-        g2 = fma(d, d, g2);
-    }
-    return g2;
 }
 
 struct SymArgs {
@@ -361,7 +335,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
             unsigned farmask = 0;
             if (ORTHO && DAMP == MPMC_DAMP_EXPONENTIAL && k.far2 > 0.0) {
                 bool f = false;
-                if (lane < 8) f = cluster_gap2(k, a.cbox, a.cbox, nclus, ci + (lane >> 2), (jb >> 5) + (lane & 3)) >= k.far2;
+                if (lane < 8) f = cluster_gap2(k.box, a.cbox, nclus, ci + (lane >> 2), a.cbox, nclus, (jb >> 5) + (lane & 3)) >= k.far2;
                 farmask = __ballot_sync(0xffffffffu, f);
                 farmask = farmask & (farmask >> 4) & 0xfu;  // both i-clusters far from j-cluster b
             }
@@ -521,12 +495,7 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
         if (!strcmp(v, "off")) k.far2 = 0.0;
         if (!strcmp(v, "all") && k.far2 > 0.0) k.far2 = 1e-300;
     }
-    k.Lx = c.B[0][0];
-    k.Ly = c.B[1][1];
-    k.Lz = c.B[2][2];
-    k.iLx = c.R[0][0];
-    k.iLy = c.R[1][1];
-    k.iLz = c.R[2][2];
+    k.box = box_len(c);
     return k;
 }
 

@@ -69,6 +69,7 @@ struct Subset {
     std::vector<int> idx;  // atom indices, ascending
     int n = 0, n_pad = 0;
     DevBuf<double> x, y, z, q, alpha, aux;
+    DevBuf<double> eps, sig, mm, cbox;  // only the sorted image of all atoms (cutoff kernels)
     DevBuf<int> mol, flags, didx;
     SubsetDev dev() const {
         SubsetDev d;
@@ -83,11 +84,16 @@ struct Subset {
         d.mol = mol.p;
         d.flags = flags.p;
         d.idx = didx.p;
+        d.eps = eps.p;
+        d.sig = sig.p;
+        d.molmass = mm.p;
+        d.cbox = cbox.p;
         return d;
     }
     void release() {
         x.release(), y.release(), z.release(), q.release(), alpha.release(), aux.release();
         mol.release(), flags.release(), didx.release();
+        eps.release(), sig.release(), mm.release(), cbox.release();
     }
 };
 
@@ -151,6 +157,14 @@ struct mpmc_b200_ctx {
     // symmetric K4 (dipole_sym_kernel.cu): cluster boxes, I-side / J-side partial rows, reduced field
     bool use_sym = true;
     bool pol_sorted = false, resort_pending = false;
+    // cluster form of the cutoff kernels K1 / K3: all atoms in spatial order
+    bool use_clusters = true;
+    Subset sorted;
+    DevBuf<int> follow;        // list order: later atoms of the same, not entirely frozen, molecule
+    DevBuf<double> intra_part;
+    int pair_kslices = 1;
+    bool boxes_fresh = false;  // sorted.cbox matches the current positions
+    double pairs_tested_analytic = 0.0;
     std::vector<double> hx_sort, hy_sort, hz_sort;  // positions at the time of the last spatial sort
     DevBuf<double> cbox, sym_partI, sym_partJ, esum;
     int sym_ysplits = 1;
@@ -502,7 +516,7 @@ static void spatial_order(const Ctx* c, std::vector<int>& idx) {
     idx.swap(out);
 }
 
-static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_multiple, bool with_aux) {
+static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_multiple, bool with_aux, bool with_lj = false) {
     const mpmc_b200_params& P = c->P;
     s.idx = idx;
     s.n = (int)idx.size();
@@ -529,6 +543,16 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
     if (upload(s.x, x, st) || upload(s.y, y, st) || upload(s.z, z, st) || upload(s.q, q, st) || upload(s.alpha, al, st) ||
         upload(s.aux, aux, st) || upload(s.mol, mol, st) || upload(s.flags, fl, st) || upload(s.didx, di, st))
         return 11;
+    if (with_lj) {
+        std::vector<double> e(s.n_pad, 0.0), sg(s.n_pad, 0.0), mm(s.n_pad, 0.0);
+        for (int k = 0; k < s.n; k++) {
+            e[k] = c->heps[idx[k]];
+            sg[k] = c->hsig[idx[k]];
+            mm[k] = c->hmm[idx[k]];
+        }
+        if (upload(s.eps, e, st) || upload(s.sig, sg, st) || upload(s.mm, mm, st)) return 11;
+        if (s.cbox.ensure((size_t)6 * (s.n_pad / 32))) return 11;
+    }
     return 0;
 }
 
@@ -581,29 +605,70 @@ static int repack(Ctx* c) {
     c->hperm.assign(c->pol.n_pad, 0);
     std::iota(c->hperm.begin(), c->hperm.end(), 0);
 
-    // tile pairs of the upper triangle, skipping tile pairs in which every atom is frozen
-    const int nt = np / TILE;
-    std::vector<char> all_frozen(nt, 1);
-    for (int t = 0; t < nt; t++)
-        for (int k = t * TILE; k < std::min(n, (t + 1) * TILE); k++)
-            if (!c->hfrozen[k]) all_frozen[t] = 0;
-    std::vector<int2> tiles;
-    tiles.reserve((size_t)nt * (nt + 1) / 2);
-    // interleave short (near-diagonal-first) ordering is irrelevant: every tile pair costs the same
-    for (int I = 0; I < nt; I++)
-        for (int J = I; J < nt; J++) {
-            if (all_frozen[I] && all_frozen[J]) continue;
-            tiles.push_back(make_int2(I, J));
-        }
-    c->ntiles = (int)tiles.size();
-    if (tiles.empty()) tiles.push_back(make_int2(0, 0));
-    if (upload(c->tiles, tiles, st)) return 11;
-    c->pair_stride = round_up(std::max(c->ntiles, 1), 32);
-    if (c->pair_part.ensure((size_t)PAIR_NPART * c->pair_stride)) FAIL(11, "cudaMalloc failed");
-
-    // reciprocal chunks: about two CTAs per SM
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    if (c->use_clusters) {
+        // spatially sorted image of ALL atoms for the cutoff kernels (K1, K3)
+        std::vector<int> all(n);
+        std::iota(all.begin(), all.end(), 0);
+        spatial_order(c, all);
+        if (pack_subset(c, c->sorted, all, 32, false, true)) return 11;
+        if (!c->pol_sorted) {  // the drift check of set_positions needs the sort-time positions in either case
+            c->hx_sort = c->hx;
+            c->hy_sort = c->hy;
+            c->hz_sort = c->hz;
+        }
+        // intramolecular erf term: list order, molecules are contiguous (pairs.c:28-34)
+        std::vector<int> follow(np, 0);
+        double same_mol_pairs = 0.0;  // pairs of one molecule that are not frozen-frozen
+        for (int b = 0; b < n;) {
+            int e = b, nfz = 0;
+            while (e < n && c->hmol[e] == c->hmol[b]) nfz += c->hfrozen[e++];
+            const int m = e - b;
+            if (nfz < m)
+                for (int i = b; i < e; i++) follow[i] = e - 1 - i;
+            same_mol_pairs += 0.5 * m * (m - 1.0) - 0.5 * nfz * (nfz - 1.0);
+            b = e;
+        }
+        double nfrozen = 0.0;
+        for (int i = 0; i < n; i++) nfrozen += c->hfrozen[i];
+        // pairs the reference evaluates geometry for in lj()/coulombic_real(): not frozen-frozen, not same molecule
+        c->pairs_tested_analytic = 0.5 * n * (n - 1.0) - 0.5 * nfrozen * (nfrozen - 1.0) - same_mol_pairs;
+        if (upload(c->follow, follow, st)) return 11;
+        if (c->intra_part.ensure((size_t)(np + 255) / 256 + 8)) FAIL(11, "cudaMalloc failed");
+        const int nclus = c->sorted.n_pad / 32;
+        const int own = std::max(1, nclus / std::max(c->world, 1) + 1);
+        const int ctas_x = (own + 3) / 4;
+        const int batches = (nclus / 2 + 1 + 31) / 32;
+        c->pair_kslices = std::max(1, std::min(batches, (8 * sms + ctas_x - 1) / ctas_x));
+        const int cols = pair_cluster_columns(c->sorted.n_pad, 0, own, c->pair_kslices);
+        c->ntiles = 0;
+        c->pair_stride = round_up(std::max(cols, 1), 32);
+        if (c->pair_part.ensure((size_t)PAIR_NPART * c->pair_stride)) FAIL(11, "cudaMalloc failed");
+    } else {
+    // tile pairs of the upper triangle, skipping tile pairs in which every atom is frozen
+        const int nt = np / TILE;
+        std::vector<char> all_frozen(nt, 1);
+        for (int t = 0; t < nt; t++)
+            for (int k = t * TILE; k < std::min(n, (t + 1) * TILE); k++)
+                if (!c->hfrozen[k]) all_frozen[t] = 0;
+        std::vector<int2> tiles;
+        tiles.reserve((size_t)nt * (nt + 1) / 2);
+        // interleave short (near-diagonal-first) ordering is irrelevant: every tile pair costs the same
+        for (int I = 0; I < nt; I++)
+            for (int J = I; J < nt; J++) {
+                if (all_frozen[I] && all_frozen[J]) continue;
+                tiles.push_back(make_int2(I, J));
+            }
+        c->ntiles = (int)tiles.size();
+        if (tiles.empty()) tiles.push_back(make_int2(0, 0));
+        if (upload(c->tiles, tiles, st)) return 11;
+        c->pair_stride = round_up(std::max(c->ntiles, 1), 32);
+        if (c->pair_part.ensure((size_t)PAIR_NPART * c->pair_stride)) FAIL(11, "cudaMalloc failed");
+
+    }
+
+    // reciprocal chunks: about two CTAs per SM
     const int target = 2 * sms;
     c->recip_apc = std::max(64, round_up((std::max(c->charged.n, 1) + target - 1) / target, 64));
     // (chunking is computed per use from the subset actually summed)
@@ -624,7 +689,7 @@ static int repack(Ctx* c) {
         c->mu.ensure((size_t)3 * pp) || c->mu_old.ensure((size_t)3 * pp) || c->mu_new.ensure((size_t)3 * pp) ||
         c->eind.ensure((size_t)3 * pp) || c->eic.ensure((size_t)3 * pp) || c->rrms.ensure(pp) ||
         c->rank_packed.ensure(pp) || c->rmin_part.ensure(ptiles + 8) ||
-        c->field_cnt.ensure((size_t)c->field_jsplits * (np / TILE) + 8))
+        c->field_cnt.ensure((size_t)std::max(c->field_jsplits * (np / TILE), np / 32) + 40))
         FAIL(11, "cudaMalloc failed");
     {
         // symmetric K4: CTAs = I tiles x offset slices; a few waves of 4 CTAs per SM
@@ -672,6 +737,17 @@ static void kev_mark(Ctx* c) {
 }
 
 static int refresh_subsets(Ctx* c) {
+    if (c->resort_pending && c->use_clusters) {
+        std::vector<int> all(c->n);
+        std::iota(all.begin(), all.end(), 0);
+        spatial_order(c, all);
+        if (pack_subset(c, c->sorted, all, 32, false, true)) return 11;
+        if (!c->pol_sorted) {
+            c->hx_sort = c->hx;
+            c->hy_sort = c->hy;
+            c->hz_sort = c->hz;
+        }
+    }
     if (c->resort_pending && c->pol_sorted) {
         std::vector<int> pol = c->pol.idx;
         std::sort(pol.begin(), pol.end());
@@ -683,7 +759,7 @@ static int refresh_subsets(Ctx* c) {
     }
     c->resort_pending = false;
     if (!c->subsets_stale) return 0;
-    for (Subset* s : {&c->charged, &c->recip, &c->pol, &c->nonpol}) {
+    for (Subset* s : {&c->charged, &c->recip, &c->pol, &c->nonpol, &c->sorted}) {
         if (s->n <= 0) continue;
         gather_positions_kernel<<<(s->n + 255) / 256, 256, 0, c->stream>>>(c->x.p, c->y.p, c->z.p, s->didx.p, s->n, s->x.p,
                                                                           s->y.p, s->z.p);
@@ -832,6 +908,21 @@ static int polar_field(Ctx* c) {
             fo.mode = FIELD_WOLF;
     } else
         fo.mode = FIELD_NOPBC;
+    if (c->use_clusters) {
+        if (c->charged.n > 0) {
+            const SubsetDev sd = c->sorted.dev();  // cluster boxes were computed by the pair phase of this evaluation
+            if (!c->boxes_fresh) {
+                launch_cluster_boxes(cell, ortho, sd, sd.cbox, st);
+                c->launches++;
+            }
+            int cb, ce;
+            shard_range(c->sorted.n_pad / 32, c->rank, c->world, cb, ce);
+            launch_static_field_clusters(cell, ortho, sd, fo, cb, ce, P.cutoff + 1e-6, accumulate, c->ef_static.p, np,
+                                         c->field_cnt.p, st);
+            sum_reduce_kernel<<<1, 1024, 0, st>>>(c->field_cnt.p, std::max(ce - cb, 0), c->scalars.p + S_FIELDCNT);
+            c->launches += 2;
+        }
+    } else
     if (c->charged.n > 0 && fe > fb) {
         const int gx = (fe - fb + TILE - 1) / TILE;
         launch_static_field(cell, ortho, a, c->charged.dev(), fo, fb, fe, c->field_jsplits, c->epart.p, c->field_cnt.p, st);
@@ -1194,6 +1285,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
         if (build_kvectors(c)) return 10;
     if (c->analytic_dirty) compute_analytic(c);
     refresh_subsets(c);
+    c->boxes_fresh = false;
     c->launches = 0;
     for (int p = 0; p < PH_COUNT; p++) c->ev_used[p] = false;
     c->kev_used = 0;
@@ -1214,14 +1306,38 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
         po.fh_order = P.feynman_hibbs ? (P.feynman_hibbs_order == 2 ? 2 : 4) : 0;
         po.mixing = P.mixing;
         po.rd_only = P.rd_only;
+        if (c->use_clusters) {
+            // cluster boxes of the sorted image (this evaluation's positions), then K1 over this shard's i-clusters
+            const SubsetDev sd = c->sorted.dev();
+            launch_cluster_boxes(cell, ortho, sd, sd.cbox, st);
+            c->boxes_fresh = true;
+            int cb, ce;
+            shard_range(c->sorted.n_pad / 32, c->rank, c->world, cb, ce);
+            const double cull = std::max(P.cutoff, P.cavity_autoreject_absolute ? P.cavity_autoreject_scale : 0.0) + 1e-6;
+            launch_pair_energy_clusters(cell, ortho, sd, po, cb, ce, c->pair_kslices, cull, c->pair_part.p, c->pair_stride, st);
+            const int cols = pair_cluster_columns(c->sorted.n_pad, cb, ce, c->pair_kslices);
+            launch_pair_reduce(c->pair_part.p, std::max(cols, 0), c->pair_stride, c->scalars.p + S_PAIR, st);
+            // intramolecular erf term (coulombic.c:176-183), list-order rows of this shard; overwrites slot 2
+            int rb, re;
+            shard_range(c->n_pad / TILE, c->rank, c->world, rb, re);
+            rb *= TILE;
+            re = std::min(re * TILE, c->n);
+            if (!P.rd_only) {
+                launch_intra_erf(atoms_dev(c), c->follow.p, P.ewald_alpha, rb, std::max(re, rb), c->intra_part.p,
+                                 c->scalars.p + S_PAIR + 2, st);
+                c->launches += 2;
+            }
+            c->launches += 3;
+        } else {
         int tb, te;
-        shard_range(c->ntiles, c->rank, c->world, tb, te);
-        if (te > tb) {
-            launch_pair_energy(cell, ortho, atoms_dev(c), po, c->tiles.p + tb, te - tb, c->pair_part.p, c->pair_stride, st);
+            shard_range(c->ntiles, c->rank, c->world, tb, te);
+            if (te > tb) {
+                launch_pair_energy(cell, ortho, atoms_dev(c), po, c->tiles.p + tb, te - tb, c->pair_part.p, c->pair_stride, st);
+                c->launches++;
+            }
+            launch_pair_reduce(c->pair_part.p, std::max(te - tb, 0), c->pair_stride, c->scalars.p + S_PAIR, st);
             c->launches++;
         }
-        launch_pair_reduce(c->pair_part.p, std::max(te - tb, 0), c->pair_stride, c->scalars.p + S_PAIR, st);
-        c->launches++;
         phase_end(c, PH_PAIR);
         CU(cudaGetLastError());
 
@@ -1275,7 +1391,7 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     memset(out, 0, sizeof(*out));
     const bool lead = (c->rank == 0);  // host-side analytic terms are added once (rank 0) in sharded runs
     out->min_intermolecular_r = h[S_PAIR + 3];
-    c->cnt.pairs_tested = h[S_PAIR + 4];
+    c->cnt.pairs_tested = c->use_clusters ? (c->rank == 0 ? c->pairs_tested_analytic : 0.0) : h[S_PAIR + 4];
     c->cnt.pairs_lj = h[S_PAIR + 5];
     c->cnt.pairs_es = h[S_PAIR + 6];
     c->cnt.kernel_launches = c->launches;
@@ -1329,6 +1445,9 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
     {   // A/B switch for profiling: MPMC_B200_K4=rows selects the row-by-row contraction of dipole_kernel.cu
         const char* v = getenv("MPMC_B200_K4");
         c->use_sym = !(v && strcmp(v, "rows") == 0);
+        // MPMC_B200_CUTOFF=tiles selects the all-pairs tile form of K1 / K3 (no cluster culling)
+        v = getenv("MPMC_B200_CUTOFF");
+        c->use_clusters = !(v && strcmp(v, "tiles") == 0);
     }
     for (int p = 0; p < PH_COUNT; p++) {
         CU(cudaEventCreate(&c->ev[p][0]));
@@ -1363,6 +1482,9 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     c->nonpol.release();
     c->eic_np.release();
     c->gs.release();
+    c->sorted.release();
+    c->follow.release();
+    c->intra_part.release();
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -1450,7 +1572,7 @@ int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double
         sy[k] = c->hy[first + k] = pos[3 * k + 1];
         sz[k] = c->hz[first + k] = pos[3 * k + 2];
     }
-    if (c->pol_sorted && !c->resort_pending) {
+    if ((c->pol_sorted || c->use_clusters) && !c->resort_pending && c->hx_sort.size() == c->hx.size()) {
         // clusters stay compact as long as no atom has drifted far from where it was sorted
         const double lim2 = 1.5 * 1.5;
         for (int k = 0; k < count; k++) {
@@ -1466,6 +1588,7 @@ int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double
     CU(cudaMemcpyAsync(c->y.p + first, sy, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(c->z.p + first, sz, sizeof(double) * count, cudaMemcpyHostToDevice, c->stream));
     c->subsets_stale = true;
+    c->boxes_fresh = false;
     return 0;
 }
 
@@ -1566,6 +1689,7 @@ int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
 }
 
 int mpmc_b200_uses_symmetric_contraction(mpmc_b200_ctx* c) { return (c && c->use_sym) ? 1 : 0; }
+int mpmc_b200_uses_cluster_field(mpmc_b200_ctx* c) { return (c && c->use_clusters) ? 1 : 0; }
 
 int mpmc_b200_shard_field_rows(mpmc_b200_ctx* c, int* begin, int* end, int* n_atoms_padded) {
     if (!c) FAIL(1, "null ctx");

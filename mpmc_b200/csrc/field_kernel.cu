@@ -17,6 +17,55 @@ namespace mpmc {
 constexpr double kOneOverSqrtPiField = 0.56418958354;  // thole_field.c:10 (truncated constant, kept)
 constexpr double kOneOverSqrtPiEwald = 0.5641895835477562869480794515607725858440506293289988;  // polar_ewald.c:6
 
+// field of source j (charge qj) at atom i: one term of thole_field_nopbc / _wolf / real_term
+template <bool ORTHO, int MODE>
+__device__ __forceinline__ void field_term(const Cell& c, const FieldOpts& o, double xi, double yi, double zi, double qi,
+                                           int moli, int fli, double xj, double yj, double zj, double qj, int molj, int fj,
+                                           double& ex, double& ey, double& ez, int& cnt) {
+    do {
+            if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) break;  // thole_field.c:49, polar_ewald.c:49
+            const bool same = (moli == molj);
+            if (MODE != FIELD_EWALD_REAL && same) break;  // thole_field.c:50
+            double dx = xi - xj, dy = yi - yj, dz = zi - zj;
+            if (MODE == FIELD_EWALD_REAL && same && dx == 0.0 && dy == 0.0 && dz == 0.0) break;  // the atom itself
+            min_image<ORTHO>(c, dx, dy, dz);
+            const double r2 = dx * dx + dy * dy + dz * dz;
+            const double r = sqrt(r2);
+            double f;  // E_i += q_j * f * d
+            if (MODE == FIELD_EWALD_REAL) {
+                if ((r > c.cutoff) || (r == 0.0)) break;  // polar_ewald.c:51
+                const bool excluded = same || (qi == 0.0);   // pair es_excluded (pairs.c:61-77); q_j != 0 by construction
+                const double g = 2.0 * o.a * kOneOverSqrtPiEwald * exp(-o.a * o.a * r2) * r;
+                f = excluded ? (g - erf(o.a * r)) / (r * r2) : (g + erfc(o.a * r)) / (r2 * r);
+            } else {
+                if (!((r - kSMALL_dR < c.cutoff) && (r != 0.0))) break;  // thole_field.c:55
+                if (MODE == FIELD_NOPBC) {
+                    f = 1.0 / (r * r * r);
+                } else {
+                    const double rr = 1.0 / r;
+                    if (MODE == FIELD_WOLF_A0) {
+                        const double rR = 1.0 / c.cutoff;
+                        f = (rr * rr - rR * rR) * rr;
+                    } else {
+                        double bigmess;
+                        if (MODE == FIELD_WOLF_LOOKUP) {  // polar_wolf_lookup.c:28-32 (truncating index)
+                            const int kx = (int)(r * 1000);
+                            bigmess = (kx >= o.table_max) ? 0.0 : o.table[kx];
+                        } else {
+                            bigmess = erfc(o.a * r) * rr * rr + 2.0 * o.a * kOneOverSqrtPiField * exp(-o.a * o.a * r * r) * rr;
+                        }
+                        f = (bigmess - o.cutoffterm) * rr;
+                    }
+                }
+            }
+            const double qf = qj * f;
+            ex += qf * dx;
+            ey += qf * dy;
+            ez += qf * dz;
+            cnt++;
+    } while (0);
+}
+
 template <bool ORTHO, int MODE>
 __global__ void __launch_bounds__(TILE) static_field_kernel(Cell c, AtomsDev a, SubsetDev ch, FieldOpts o, int row_begin,
                                                             int row_end, int tiles_per_split,
@@ -48,47 +97,8 @@ __global__ void __launch_bounds__(TILE) static_field_kernel(Cell c, AtomsDev a, 
         }
         __syncthreads();
         for (int jj = 0; jj < TILE; jj++) {
-            const int fj = sfl[jj];
-            if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) continue;  // thole_field.c:49, polar_ewald.c:49
-            const bool same = (moli == smol[jj]);
-            if (MODE != FIELD_EWALD_REAL && same) continue;  // thole_field.c:50
-            double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
-            if (MODE == FIELD_EWALD_REAL && same && dx == 0.0 && dy == 0.0 && dz == 0.0) continue;  // the atom itself
-            min_image<ORTHO>(c, dx, dy, dz);
-            const double r2 = dx * dx + dy * dy + dz * dz;
-            const double r = sqrt(r2);
-            double f;  // E_i += q_j * f * d
-            if (MODE == FIELD_EWALD_REAL) {
-                if ((r > c.cutoff) || (r == 0.0)) continue;  // polar_ewald.c:51
-                const bool excluded = same || (qi == 0.0);   // pair es_excluded (pairs.c:61-77); q_j != 0 by construction
-                const double g = 2.0 * o.a * kOneOverSqrtPiEwald * exp(-o.a * o.a * r2) * r;
-                f = excluded ? (g - erf(o.a * r)) / (r * r2) : (g + erfc(o.a * r)) / (r2 * r);
-            } else {
-                if (!((r - kSMALL_dR < c.cutoff) && (r != 0.0))) continue;  // thole_field.c:55
-                if (MODE == FIELD_NOPBC) {
-                    f = 1.0 / (r * r * r);
-                } else {
-                    const double rr = 1.0 / r;
-                    if (MODE == FIELD_WOLF_A0) {
-                        const double rR = 1.0 / c.cutoff;
-                        f = (rr * rr - rR * rR) * rr;
-                    } else {
-                        double bigmess;
-                        if (MODE == FIELD_WOLF_LOOKUP) {  // polar_wolf_lookup.c:28-32 (truncating index)
-                            const int kx = (int)(r * 1000);
-                            bigmess = (kx >= o.table_max) ? 0.0 : o.table[kx];
-                        } else {
-                            bigmess = erfc(o.a * r) * rr * rr + 2.0 * o.a * kOneOverSqrtPiField * exp(-o.a * o.a * r * r) * rr;
-                        }
-                        f = (bigmess - o.cutoffterm) * rr;
-                    }
-                }
-            }
-            const double qf = sq[jj] * f;
-            ex += qf * dx;
-            ey += qf * dy;
-            ez += qf * dz;
-            cnt++;
+            field_term<ORTHO, MODE>(c, o, xi, yi, zi, qi, moli, fli, sx[jj], sy[jj], sz[jj], sq[jj], smol[jj], sfl[jj], ex, ey, ez,
+                                    cnt);
         }
     }
     if (live) {
@@ -100,6 +110,80 @@ __global__ void __launch_bounds__(TILE) static_field_kernel(Cell c, AtomsDev a, 
     if (count_part) {
         double v = block_reduce<0>((double)cnt, red);
         if (tid == 0) count_part[blockIdx.y * gridDim.x + blockIdx.x] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Cluster form of K3 (the default): spatially sorted image of all atoms, one WARP per 32-atom i-cluster
+// (row-owned: lane l accumulates the field at atom ci*32+l over ALL sources, no atomics, no partial rows).
+// The j-clusters are scanned in batches of 32 (lane l tests cluster kb+l with cluster_gap2); clusters
+// proven to lie beyond the cutoff are skipped: thole_field.c:55 / polar_ewald.c:51 add nothing for them.
+// ------------------------------------------------------------------------------------------------
+struct __align__(16) FieldRec {
+    double x, y, z, q;
+    int mol, fl;
+};
+
+template <bool ORTHO, int MODE>
+__global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a, FieldOpts o, BoxLen box, int clus_begin,
+                                                             int clus_end, double cull2, int accumulate,
+                                                             double* __restrict__ ef, int ef_stride,
+                                                             double* __restrict__ count_part) {
+    __shared__ FieldRec rec[4][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int ci = clus_begin + blockIdx.x * 4 + w;
+    if (ci >= clus_end) return;  // whole warp; no block-level barrier below
+    const int nclus = a.n_pad >> 5;
+    const int i = ci * 32 + lane;
+    const double xi = a.x[i], yi = a.y[i], zi = a.z[i], qi = a.q[i];
+    const int moli = a.mol[i], fli = a.flags[i];
+    double ex = 0.0, ey = 0.0, ez = 0.0;
+    int cnt = 0;
+    for (int kb = 0; kb < nclus; kb += 32) {
+        const int cj = kb + lane;
+        bool pass = cj < nclus;
+        if (pass && cull2 > 0.0) pass = cluster_gap2(box, a.cbox, nclus, ci, a.cbox, nclus, cj) <= cull2;
+        unsigned mask = __ballot_sync(0xffffffffu, pass);
+        while (mask) {
+            const int b = __ffs(mask) - 1;
+            mask &= mask - 1;
+            __syncwarp();
+            {
+                const int j = (kb + b) * 32 + lane;
+                FieldRec r;
+                r.x = a.x[j];
+                r.y = a.y[j];
+                r.z = a.z[j];
+                r.q = a.q[j];
+                r.mol = a.mol[j];
+                r.fl = a.flags[j];
+                rec[w][lane] = r;
+            }
+            __syncwarp();
+            const bool self_cluster = (kb + b == ci);
+            for (int s = 0; s < 32; s++) {
+                const FieldRec& r = rec[w][s];
+                if (r.q == 0.0) continue;                  // a source without charge adds exact zeros
+                if (self_cluster && s == lane) continue;   // the atom itself
+                field_term<ORTHO, MODE>(c, o, xi, yi, zi, qi, moli, fli, r.x, r.y, r.z, r.q, r.mol, r.fl, ex, ey, ez, cnt);
+            }
+        }
+    }
+    if (fli & F_VALID) {
+        const int g = a.idx[i];
+        if (accumulate) {
+            ef[0 * ef_stride + g] += ex;
+            ef[1 * ef_stride + g] += ey;
+            ef[2 * ef_stride + g] += ez;
+        } else {
+            ef[0 * ef_stride + g] = ex;
+            ef[1 * ef_stride + g] = ey;
+            ef[2 * ef_stride + g] = ez;
+        }
+    }
+    if (count_part) {
+        const double v = warp_sum((double)cnt);
+        if (lane == 0) count_part[ci - clus_begin] = v;
     }
 }
 
@@ -123,6 +207,34 @@ void launch_static_field(const Cell& c, bool ortho, const AtomsDev& a, const Sub
     dim3 grid((rows + TILE - 1) / TILE, jsplits);
 #define LAUNCH(ORTHO, MODE)                                                                                         \
     static_field_kernel<ORTHO, MODE><<<grid, TILE, 0, s>>>(c, a, charged, o, row_begin, row_end, tps, epart, count_part)
+#define DISPATCH(ORTHO)                                     \
+    switch (o.mode) {                                       \
+        case FIELD_NOPBC: LAUNCH(ORTHO, FIELD_NOPBC); break; \
+        case FIELD_WOLF_A0: LAUNCH(ORTHO, FIELD_WOLF_A0); break; \
+        case FIELD_WOLF: LAUNCH(ORTHO, FIELD_WOLF); break;  \
+        case FIELD_WOLF_LOOKUP: LAUNCH(ORTHO, FIELD_WOLF_LOOKUP); break; \
+        default: LAUNCH(ORTHO, FIELD_EWALD_REAL);           \
+    }
+    if (ortho) {
+        DISPATCH(true)
+    } else {
+        DISPATCH(false)
+    }
+#undef DISPATCH
+#undef LAUNCH
+}
+
+void launch_static_field_clusters(const Cell& c, bool ortho, const SubsetDev& a, const FieldOpts& o, int clus_begin,
+                                  int clus_end, double cull, bool accumulate, double* ef, int ef_stride, double* count_part,
+                                  cudaStream_t s) {
+    const int nown = clus_end - clus_begin;
+    if (nown <= 0) return;
+    const double cull2 = (ortho && cull > 0.0) ? cull * cull : 0.0;
+    const BoxLen box = box_len(c);
+    const int grid = (nown + 3) / 4;
+#define LAUNCH(ORTHO, MODE)                                                                                              \
+    field_cluster_kernel<ORTHO, MODE><<<grid, TILE, 0, s>>>(c, a, o, box, clus_begin, clus_end, cull2, accumulate ? 1 : 0, ef, \
+                                                            ef_stride, count_part)
 #define DISPATCH(ORTHO)                                     \
     switch (o.mode) {                                       \
         case FIELD_NOPBC: LAUNCH(ORTHO, FIELD_NOPBC); break; \

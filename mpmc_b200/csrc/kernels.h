@@ -22,6 +22,9 @@ struct SubsetDev {
     double *x, *y, *z, *q, *alpha;
     double *aux;  // dipole kernels: alpha^(1/6) for linear damping, the charge for damping off
     int *mol, *flags, *idx;  // idx = index in AtomsDev
+    // only in the spatially sorted image of ALL atoms used by the cutoff kernels (else null):
+    double *eps, *sig, *molmass;
+    double* cbox;  // [6][n_pad/32] cluster boxes of this evaluation
 };
 
 // ---- K1: fused LJ(+FH) + Ewald real(+FH) + intramolecular erf + min distance ------------------
@@ -37,6 +40,16 @@ struct PairOpts {
 constexpr int PAIR_NPART = 8;  // rd, es, intra, min_r, n_tested, n_lj, n_es, (unused)
 void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const int2* tiles, int ntiles,
                         double* partial /*[PAIR_NPART][ntiles_stride]*/, int stride, cudaStream_t s);
+// Cluster form of K1 on the spatially sorted image: one warp per 32-atom i-cluster, candidate j-clusters
+// (ci + k) mod nclus, k = 0..nclus/2 (every unordered cluster pair once), culled by the bounding-box gap against
+// `cull` (>= cutoff; <= 0: no culling).  partial [PAIR_NPART][stride], one column per (slice, own cluster).
+void launch_pair_energy_clusters(const Cell& c, bool ortho, const SubsetDev& sorted, const PairOpts& o, int clus_begin,
+                                 int clus_end, int kslices, double cull, double* partial, int stride, cudaStream_t s);
+int pair_cluster_columns(int n_pad_sorted, int clus_begin, int clus_end, int kslices);  // columns of `partial` used
+// intramolecular erf term of coulombic_real() (src/energy/coulombic.c:176-183) over list-order atoms;
+// follow[i] = number of later atoms of the same (not entirely frozen) molecule; part[blocks] -> sum_out
+void launch_intra_erf(const AtomsDev& a, const int* follow, double ewald_alpha, int row_begin, int row_end, double* part,
+                      double* sum_out, cudaStream_t s);
 void launch_pair_reduce(const double* partial, int ntiles, int stride, double* out /*[PAIR_NPART]*/, cudaStream_t s);
 
 // ---- K2: reciprocal-space structure factor -----------------------------------------------------
@@ -71,6 +84,11 @@ void launch_static_field(const Cell& c, bool ortho, const AtomsDev& a, const Sub
                          int row_begin, int row_end, int jsplits, double* epart /*[jsplits][3][n_pad]*/,
                          double* count_part, cudaStream_t s);
 // ef[c][i] (+)= sum_js epart[js][c][i]
+// Cluster form of K3 on the spatially sorted image: one warp per i-cluster, all j-clusters culled by the gap;
+// writes ef[c][idx[i]] (list order), accumulating when `accumulate`; count_part[cluster] = contributions.
+void launch_static_field_clusters(const Cell& c, bool ortho, const SubsetDev& sorted, const FieldOpts& o, int clus_begin,
+                                  int clus_end, double cull, bool accumulate, double* ef, int ef_stride, double* count_part,
+                                  cudaStream_t s);
 void launch_field_reduce(const double* epart, int jsplits, int n_pad, int row_begin, int row_end, bool accumulate,
                          double* ef, cudaStream_t s);
 

@@ -68,6 +68,91 @@ __device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double 
     }
 }
 
+struct PairAcc {
+    double rd, es, intra, minr;
+    int n_tested, n_lj, n_es;
+};
+
+// all terms of one pair (i in registers, j given): pair_exclusions + minimum_image + lj + coulombic_real
+template <bool ORTHO, int FH>
+__device__ __forceinline__ void pair_terms(const Cell& c, const PairConsts& k, int mixing, int rd_only, double xi, double yi,
+                                           double zi, double qi, double ei, double si, double mi, int moli, int fli,
+                                           bool lj_i, double xj, double yj, double zj, double qj, double ej, double sj,
+                                           double mj, int molj, int fj, PairAcc& A) {
+    do {
+        // skip padding and frozen-frozen pairs (pairs.c:81, lj.c:193, coulombic.c:165)
+        if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) break;
+        double dx = xi - xj, dy = yi - yj, dz = zi - zj;
+        const double qq = qi * qj;
+        if (moli == molj) {
+            // same molecule: rd and es excluded (pairs.c:61-64); charge-to-screen term with the
+            // UN-imaged separation (coulombic.c:179-180)
+            if (!rd_only && qq != 0.0) {
+                double r = sqrt(dx * dx + dy * dy + dz * dz);
+                A.intra += qq * erf(k.alpha * r) / r;
+            }
+            break;
+        }
+        min_image<ORTHO>(c, dx, dy, dz);
+        const double r2 = dx * dx + dy * dy + dz * dz;
+        const double r = sqrt(r2);
+        A.n_tested++;
+        A.minr = fmin(A.minr, r);
+
+                const bool do_lj = (r - kSMALL_dR < k.cutoff) && lj_i && (ej != 0.0) && (sj != 0.0);
+        const bool do_es = !rd_only && !(r > k.cutoff) && (qq != 0.0);
+        if (!(do_lj || do_es)) break;
+        const double ir = 1.0 / r;
+        double mured = 0.0;
+        if (FH) mured = kAMU2KG * mi * mj / (mi + mj);
+
+        if (do_lj) {
+            double eps, sigma;
+            bool att;
+            mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
+            const double sor = fabs(sigma) * ir;
+            double s6 = sor * sor * sor;
+            s6 *= s6;
+            const double term6 = s6, term12 = att ? 0.0 : s6 * s6;
+            double u = 4.0 * eps * (term12 - term6);
+            if (FH) {  // lj.c:29-50
+                const double ir2 = ir * ir, ir3 = ir2 * ir, ir4 = ir3 * ir;
+                const double dE = -24.0 * eps * (2.0 * term12 - term6) * ir;
+                const double d2E = 24.0 * eps * (26.0 * term12 - 7.0 * term6) * ir2;
+                u += (k.fh2_pref / mured) * (d2E + 2.0 * dE * ir);
+                if (FH >= 4) {
+                    const double d3E = -1344.0 * eps * (6.0 * term12 - term6) * ir3;
+                    const double d4E = 12096.0 * eps * (10.0 * term12 - term6) * ir4;
+                    u += (k.fh4_pref / (mured * mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
+                }
+            }
+            A.rd += u;
+            A.n_lj++;
+        }
+        if (do_es) {
+            const double erfc_term = erfc(k.alpha * r);
+            double u = qq * erfc_term * ir;
+            if (FH) {  // coulombic.c:132-141
+                const double gaussian_term = exp(-k.a2 * r2);
+                const double ir2 = ir * ir, ir3 = ir * ir2, ir4 = ir2 * ir2;
+                const double g = gaussian_term * k.inv_sqrt_pi;
+                const double du = -2.0 * k.alpha * g * ir - erfc_term * ir2;
+                const double d2u = 4.0 * g * (k.a3 + ir2) + 2.0 * erfc_term * ir3;
+                u += (k.fh2_pref / mured) * (d2u + 2.0 * du * ir);
+                if (FH >= 4) {
+                    const double d3u = g * (-8.0 * (k.a3 * k.a2) * r - 8.0 * k.a3 * ir - 12.0 * k.alpha * ir3) -
+                                       6.0 * erfc_term * ir4;
+                    const double d4u = g * (8.0 * k.a3 * k.a2 + 16.0 * k.a3 * k.a4 * r2 + 32.0 * k.a3 * ir2 + 48.0 * ir4) +
+                                       24.0 * erfc_term * (ir4 * ir);
+                    u += (k.fh4_pref_es / (mured * mured)) * (15.0 * du * ir3 + 4.0 * d3u * ir + d4u);
+                }
+            }
+            A.es += u;
+            A.n_es++;
+        }
+    } while (0);
+}
+
 template <bool ORTHO, int FH>
 __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, PairConsts k, int mixing, int rd_only,
                                                            const int2* __restrict__ tiles, double* __restrict__ partial,
@@ -95,85 +180,16 @@ __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, P
     const int moli = a.mol[i], fli = a.flags[i];
     __syncthreads();
 
-    double rd = 0.0, es = 0.0, intra = 0.0, minr = kMAXVALUE;
-    int n_tested = 0, n_lj = 0, n_es = 0;
+    PairAcc A = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
     const bool lj_i = (ei != 0.0) && (si != 0.0);
     const int j0 = (t.x == t.y) ? tid + 1 : 0;
 
     for (int jj = j0; jj < TILE; jj++) {
-        const int fj = sfl[jj];
-        // skip padding and frozen-frozen pairs (pairs.c:81, lj.c:193, coulombic.c:165)
-        if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) continue;
-        double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
-        const double qq = qi * sq[jj];
-        if (moli == smol[jj]) {
-            // same molecule: rd and es excluded (pairs.c:61-64); charge-to-screen term with the
-            // UN-imaged separation (coulombic.c:179-180)
-            if (!rd_only && qq != 0.0) {
-                double r = sqrt(dx * dx + dy * dy + dz * dz);
-                intra += qq * erf(k.alpha * r) / r;
-            }
-            continue;
-        }
-        min_image<ORTHO>(c, dx, dy, dz);
-        const double r2 = dx * dx + dy * dy + dz * dz;
-        const double r = sqrt(r2);
-        n_tested++;
-        minr = fmin(minr, r);
-
-        const double ej = se[jj], sj = ss[jj];
-        const bool do_lj = (r - kSMALL_dR < k.cutoff) && lj_i && (ej != 0.0) && (sj != 0.0);
-        const bool do_es = !rd_only && !(r > k.cutoff) && (qq != 0.0);
-        if (!(do_lj || do_es)) continue;
-        const double ir = 1.0 / r;
-        double mured = 0.0;
-        if (FH) mured = kAMU2KG * mi * sm[jj] / (mi + sm[jj]);
-
-        if (do_lj) {
-            double eps, sigma;
-            bool att;
-            mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
-            const double sor = fabs(sigma) * ir;
-            double s6 = sor * sor * sor;
-            s6 *= s6;
-            const double term6 = s6, term12 = att ? 0.0 : s6 * s6;
-            double u = 4.0 * eps * (term12 - term6);
-            if (FH) {  // lj.c:29-50
-                const double ir2 = ir * ir, ir3 = ir2 * ir, ir4 = ir3 * ir;
-                const double dE = -24.0 * eps * (2.0 * term12 - term6) * ir;
-                const double d2E = 24.0 * eps * (26.0 * term12 - 7.0 * term6) * ir2;
-                u += (k.fh2_pref / mured) * (d2E + 2.0 * dE * ir);
-                if (FH >= 4) {
-                    const double d3E = -1344.0 * eps * (6.0 * term12 - term6) * ir3;
-                    const double d4E = 12096.0 * eps * (10.0 * term12 - term6) * ir4;
-                    u += (k.fh4_pref / (mured * mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
-                }
-            }
-            rd += u;
-            n_lj++;
-        }
-        if (do_es) {
-            const double erfc_term = erfc(k.alpha * r);
-            double u = qq * erfc_term * ir;
-            if (FH) {  // coulombic.c:132-141
-                const double gaussian_term = exp(-k.a2 * r2);
-                const double ir2 = ir * ir, ir3 = ir * ir2, ir4 = ir2 * ir2;
-                const double g = gaussian_term * k.inv_sqrt_pi;
-                const double du = -2.0 * k.alpha * g * ir - erfc_term * ir2;
-                const double d2u = 4.0 * g * (k.a3 + ir2) + 2.0 * erfc_term * ir3;
-                u += (k.fh2_pref / mured) * (d2u + 2.0 * du * ir);
-                if (FH >= 4) {
-                    const double d3u = g * (-8.0 * (k.a3 * k.a2) * r - 8.0 * k.a3 * ir - 12.0 * k.alpha * ir3) -
-                                       6.0 * erfc_term * ir4;
-                    const double d4u = g * (8.0 * k.a3 * k.a2 + 16.0 * k.a3 * k.a4 * r2 + 32.0 * k.a3 * ir2 + 48.0 * ir4) +
-                                       24.0 * erfc_term * (ir4 * ir);
-                    u += (k.fh4_pref_es / (mured * mured)) * (15.0 * du * ir3 + 4.0 * d3u * ir + d4u);
-                }
-            }
-            es += u;
-            n_es++;
-        }
+        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, ei, si, mi, moli, fli, lj_i, sx[jj], sy[jj], sz[jj], sq[jj],
+                              se[jj], ss[jj], sm[jj], smol[jj], sfl[jj], A);
     }
+    const double rd = A.rd, es = A.es, intra = A.intra, minr = A.minr;
+    const int n_tested = A.n_tested, n_lj = A.n_lj, n_es = A.n_es;
 
     // fixed-order block reduction, one partial row per tile pair
     double v;
@@ -193,6 +209,122 @@ __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, P
     if (tid == 0) partial[6 * stride + blockIdx.x] = v;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Cluster form of K1 (the default): atoms in spatial order, one WARP per 32-atom i-cluster.  Lane l keeps
+// atom ci*32+l in registers.  Candidate j-clusters are (ci + k) mod nclus, k = 0..nclus/2, so every unordered
+// cluster pair is met exactly once and every warp has the same number of candidates; a batch of 32 candidates
+// is tested against the cutoff in one step (lane l tests candidate l: bounding-box gap, cluster_gap2) and only
+// the survivors are staged (per-warp shared memory, 64-byte records) and walked.  With an 8 A cutoff in a
+// 128 x 128 x 43 A box this visits ~3 % of the pairs the reference tests -- the rest are proven to be
+// outside the cutoff, where lj() and coulombic_real() add nothing (lj.c:191, coulombic.c:167).
+// No CTA-level synchronisation; one partial column per (slice, cluster), reduced in fixed order.
+// ------------------------------------------------------------------------------------------------
+struct __align__(16) PairRec {
+    double x, y, z, q, eps, sig, mm;
+    int mol, fl;
+};
+
+template <bool ORTHO, int FH>
+__global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a, PairConsts k, BoxLen box, int mixing,
+                                                            int rd_only, int clus_begin, int clus_end, int kper, double cull2,
+                                                            double* __restrict__ partial, int stride) {
+    __shared__ PairRec rec[4][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int ci = clus_begin + blockIdx.x * 4 + w;
+    if (ci >= clus_end) return;  // whole warp; no block-level barrier is used below
+    const int nclus = a.n_pad >> 5;
+    const int i = ci * 32 + lane;
+    const double xi = a.x[i], yi = a.y[i], zi = a.z[i], qi = a.q[i], ei = a.eps[i], si = a.sig[i], mi = a.molmass[i];
+    const int moli = a.mol[i], fli = a.flags[i];
+    const bool lj_i = (ei != 0.0) && (si != 0.0);
+    PairAcc A = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
+
+    const int K = nclus / 2;
+    const int k0 = blockIdx.y * kper, k1 = min(k0 + kper, K + 1);
+    for (int kb = k0; kb < k1; kb += 32) {
+        const int kk = kb + lane;
+        bool pass = kk < k1 && !(kk > 0 && 2 * kk == nclus && ci >= kk);  // even nclus: half-way offset for ci < nclus/2 only
+        int cj = ci + kk;
+        if (cj >= nclus) cj -= nclus;
+        if (pass && cull2 > 0.0) pass = cluster_gap2(box, a.cbox, nclus, ci, a.cbox, nclus, cj) <= cull2;
+        unsigned mask = __ballot_sync(0xffffffffu, pass);
+        while (mask) {
+            const int b = __ffs(mask) - 1;
+            mask &= mask - 1;
+            const int kk2 = kb + b;
+            int cj2 = ci + kk2;
+            if (cj2 >= nclus) cj2 -= nclus;
+            __syncwarp();
+            {
+                const int j = cj2 * 32 + lane;
+                PairRec r;
+                r.x = a.x[j];
+                r.y = a.y[j];
+                r.z = a.z[j];
+                r.q = a.q[j];
+                r.eps = a.eps[j];
+                r.sig = a.sig[j];
+                r.mm = a.molmass[j];
+                r.mol = a.mol[j];
+                r.fl = a.flags[j];
+                rec[w][lane] = r;
+            }
+            __syncwarp();
+            const int s0 = (kk2 == 0) ? lane + 1 : 0;  // inside one cluster: j > i
+            for (int s = s0; s < 32; s++) {
+                const PairRec& r = rec[w][s];
+                pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, ei, si, mi, moli, fli, lj_i, r.x, r.y, r.z, r.q,
+                                      r.eps, r.sig, r.mm, r.mol, r.fl, A);
+            }
+        }
+    }
+    // same-molecule pairs are handled by intra_erf_kernel (list order): drop what pair_terms collected for them
+    const double rd = warp_sum(A.rd), es = warp_sum(A.es), minr = warp_min(A.minr);
+    const double nlj = warp_sum((double)A.n_lj), nes = warp_sum((double)A.n_es);
+    if (lane == 0) {
+        const int col = blockIdx.y * (clus_end - clus_begin) + (ci - clus_begin);
+        partial[0 * stride + col] = rd;
+        partial[1 * stride + col] = es;
+        partial[2 * stride + col] = 0.0;
+        partial[3 * stride + col] = minr;
+        partial[4 * stride + col] = 0.0;
+        partial[5 * stride + col] = nlj;
+        partial[6 * stride + col] = nes;
+    }
+}
+
+__global__ void __launch_bounds__(256) intra_erf_kernel(AtomsDev a, const int* __restrict__ follow, double alpha,
+                                                        int row_begin, int row_end, double* __restrict__ part) {
+    __shared__ double red[32];
+    const int i = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    double acc = 0.0;
+    if (i < row_end) {
+        const int nf = follow[i];
+        if (nf > 0) {
+            const double xi = a.x[i], yi = a.y[i], zi = a.z[i], qi = a.q[i];
+            const int fi = a.flags[i];
+            for (int j = i + 1; j <= i + nf; j++) {
+                if ((fi & a.flags[j]) & F_FROZEN) continue;  // coulombic.c:165
+                const double qq = qi * a.q[j];
+                if (qq == 0.0) continue;
+                const double dx = xi - a.x[j], dy = yi - a.y[j], dz = zi - a.z[j];
+                const double r = sqrt(dx * dx + dy * dy + dz * dz);  // UN-imaged (coulombic.c:180)
+                acc += qq * erf(alpha * r) / r;
+            }
+        }
+    }
+    acc = block_reduce<0>(acc, red);
+    if (threadIdx.x == 0) part[blockIdx.x] = acc;
+}
+
+__global__ void __launch_bounds__(1024) intra_sum_kernel(const double* __restrict__ in, int n, double* __restrict__ out) {
+    __shared__ double red[32];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) acc += in[i];
+    acc = block_reduce<0>(acc, red);
+    if (threadIdx.x == 0) out[0] = acc;
+}
+
 // One CTA sums the per-tile partials in a fixed order (deterministic run to run).
 __global__ void __launch_bounds__(1024) pair_reduce_kernel(const double* __restrict__ partial, int ntiles, int stride,
                                                            double* __restrict__ out) {
@@ -208,9 +340,60 @@ __global__ void __launch_bounds__(1024) pair_reduce_kernel(const double* __restr
     }
 }
 
-void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const int2* tiles, int ntiles,
-                        double* partial, int stride, cudaStream_t s) {
-    if (ntiles <= 0) return;
+static PairConsts make_pair_consts(const Cell& c, const PairOpts& o);
+
+void launch_pair_energy_clusters(const Cell& c, bool ortho, const SubsetDev& a, const PairOpts& o, int clus_begin,
+                                 int clus_end, int kslices, double cull, double* partial, int stride, cudaStream_t s) {
+    const int nown = clus_end - clus_begin;
+    if (nown <= 0) return;
+    const PairConsts k = make_pair_consts(c, o);
+    const int nclus = a.n_pad / 32, K = nclus / 2;
+    if (kslices < 1) kslices = 1;
+    int kper = (K + 1 + kslices - 1) / kslices;
+    kper = ((kper + 31) / 32) * 32;  // whole candidate batches per slice
+    kslices = (K + 1 + kper - 1) / kper;
+    const double cull2 = (ortho && cull > 0.0) ? cull * cull : 0.0;  // the gap bound is orthorhombic only
+    const BoxLen box = box_len(c);
+    dim3 grid((nown + 3) / 4, kslices);
+#define LAUNCH(ORTHO, FH)                                                                                                 \
+    pair_cluster_kernel<ORTHO, FH><<<grid, TILE, 0, s>>>(c, a, k, box, o.mixing, o.rd_only, clus_begin, clus_end, kper, cull2, \
+                                                         partial, stride)
+    if (ortho) {
+        if (o.fh_order == 0)
+            LAUNCH(true, 0);
+        else if (o.fh_order == 2)
+            LAUNCH(true, 2);
+        else
+            LAUNCH(true, 4);
+    } else {
+        if (o.fh_order == 0)
+            LAUNCH(false, 0);
+        else if (o.fh_order == 2)
+            LAUNCH(false, 2);
+        else
+            LAUNCH(false, 4);
+    }
+#undef LAUNCH
+}
+
+int pair_cluster_columns(int n_pad_sorted, int clus_begin, int clus_end, int kslices) {
+    const int nclus = n_pad_sorted / 32, K = nclus / 2;
+    if (kslices < 1) kslices = 1;
+    int kper = (K + 1 + kslices - 1) / kslices;
+    kper = ((kper + 31) / 32) * 32;
+    kslices = (K + 1 + kper - 1) / kper;
+    return kslices * (clus_end - clus_begin);
+}
+
+void launch_intra_erf(const AtomsDev& a, const int* follow, double ewald_alpha, int row_begin, int row_end, double* part,
+                      double* sum_out, cudaStream_t s) {
+    const int rows = row_end - row_begin;
+    const int nb = (rows + 255) / 256;
+    if (rows > 0) intra_erf_kernel<<<nb, 256, 0, s>>>(a, follow, ewald_alpha, row_begin, row_end, part);
+    intra_sum_kernel<<<1, 1024, 0, s>>>(part, rows > 0 ? nb : 0, sum_out);
+}
+
+static PairConsts make_pair_consts(const Cell& c, const PairOpts& o) {
     PairConsts k;
     k.cutoff = c.cutoff;
     k.alpha = o.ewald_alpha;
@@ -221,6 +404,13 @@ void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const Pair
     k.fh2_pref = kM2A2 * (kHBAR2 / (24.0 * kKB * o.temperature));
     k.fh4_pref = kM2A4 * (kHBAR4 / (1152.0 * kKB2 * o.temperature * o.temperature));
     k.fh4_pref_es = kM2A4 * (kHBAR4 / (1152.0 * (kKB * kKB * o.temperature * o.temperature)));
+    return k;
+}
+
+void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const int2* tiles, int ntiles,
+                        double* partial, int stride, cudaStream_t s) {
+    if (ntiles <= 0) return;
+    const PairConsts k = make_pair_consts(c, o);
 #define LAUNCH(ORTHO, FH) \
     pair_energy_kernel<ORTHO, FH><<<ntiles, TILE, 0, s>>>(c, a, k, o.mixing, o.rd_only, tiles, partial, stride)
     if (ortho) {

@@ -4,8 +4,8 @@
 What is split (BASELINE north_star):
   * pair tiles of the LJ + Ewald-real kernel and the atom chunks of the structure factor
     -> partial scalars, summed over ranks at the end (one all-reduce of 12 doubles);
-  * static-field rows (thole_field, reference src/polarization/thole_field.c:14-36)
-    -> one all-gather of the field rows;
+  * static-field rows (thole_field, reference src/polarization/thole_field.c:14-36), by spatial cluster
+    -> one all-reduce(sum) of the field (each row is written by exactly one rank, zero elsewhere);
   * the tile pairs of every solver pass (contract_dipoles, src/polarization/thole_iterative.c:27-59):
     the dipole tensor is symmetric, so each rank evaluates T_ij once for its share of the unordered
     tile pairs and applies it in both directions -> its contribution to the induced field of ALL rows
@@ -156,7 +156,10 @@ class ShardedEngine:
             _, _, n_pol, pp = eng.shard_rows()
             _, _, np_atoms = eng.shard_field_rows()
             eng.polar_stage(api.STAGE_FIELD)
-            self.ex.all_gather_rows(self._view(3), 3, np_atoms)
+            if getattr(eng, "uses_cluster_field", lambda: False)():
+                self.ex.all_reduce(self._view(3), "sum")  # rows of other ranks' clusters are zero here
+            else:
+                self.ex.all_gather_rows(self._view(3), 3, np_atoms)
             eng.polar_stage(api.STAGE_INIT)
             mu = self._view(0)
             sym = bool(eng.uses_symmetric_contraction())
