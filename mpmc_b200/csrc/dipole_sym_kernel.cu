@@ -149,18 +149,21 @@ __device__ __forceinline__ double exp_neg_fast(const SymConsts& k, double x) {
     const double nd = t - magic;
     double r = fma(nd, -6.93147180369123816490e-01, -x);
     r = fma(nd, -1.90821492927058770002e-10, r);
-    double p = k.ec[11];
-    p = fma(p, r, k.ec[10]);
-    p = fma(p, r, k.ec[9]);
-    p = fma(p, r, k.ec[8]);
-    p = fma(p, r, k.ec[7]);
-    p = fma(p, r, k.ec[6]);
-    p = fma(p, r, k.ec[5]);
-    p = fma(p, r, k.ec[4]);
-    p = fma(p, r, k.ec[3]);
-    p = fma(p, r, k.ec[2]);
-    p = fma(p, r, 1.0);
-    p = fma(p, r, 1.0);
+    // even / odd split: two independent Horner chains in r^2 (depth 7 instead of 11; with two pairs in flight
+    // that is four chains, enough to keep the half-rate fp64 pipe fed from one warp)
+    const double r2 = r * r;
+    double pe = k.ec[10], po = k.ec[11];
+    pe = fma(pe, r2, k.ec[8]);
+    po = fma(po, r2, k.ec[9]);
+    pe = fma(pe, r2, k.ec[6]);
+    po = fma(po, r2, k.ec[7]);
+    pe = fma(pe, r2, k.ec[4]);
+    po = fma(po, r2, k.ec[5]);
+    pe = fma(pe, r2, k.ec[2]);
+    po = fma(po, r2, k.ec[3]);
+    pe = fma(pe, r2, 1.0);
+    po = fma(po, r2, 1.0);
+    const double p = fma(po, r, pe);
     const int n = __double2loint(t);
     return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
 }
@@ -341,7 +344,8 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
             }
 #pragma unroll 1
             for (int b = 0; b < 4; b++) {
-                const int jc = (w + b) & 3;
+                const int jc = b;  // all four warps on the same j-cluster: their i-clusters are neighbours, so the
+                                   // far / damped classes coincide and nobody waits long at the barrier
                 double ajx, ajy, ajz;
                 const bool far = (farmask >> jc) & 1u;
 #define CP(FAR, CHECK)                                                                                                     \
