@@ -69,6 +69,15 @@ def synthetic_cases():
         "mixed_wolf_full": _variant(m, polar_wolf_full=1, polar_wolf_alpha=0.13),
         "mixed_polar_ewald": _variant(m, polar_ewald=1),
         "mixed_tri_polar_ewald": _variant(t, polar_ewald=1),
+        # full-Ewald polarization (ewald_full(): polar_ewald.c:375-418)
+        "mixed_ewald_full": _variant(m, polar_ewald_full=1),
+        "mixed_tri_ewald_full": _variant(t, polar_ewald_full=1, polar_max_iter=6),
+        "mixed_ewald_full_precision_palmo_rrms": _variant(m, polar_ewald_full=1, polar_precision=1e-5, polar_max_iter=0,
+                                                          polar_palmo=1, polar_rrms=1),
+        "mixed_ewald_full_sor": _variant(m, polar_ewald_full=1, polar_sor=1, polar_gamma=0.8, polar_max_iter=7),
+        "mixed_ewald_full_esor_cutoff7": _variant(m, polar_ewald_full=1, polar_esor=1, polar_gamma=1.2, cutoff=7.0,
+                                                  ewald_alpha=0.45, polar_ewald_alpha=0.45, polar_palmo=1),
+        "h2_fluid_500_ewald_full": _variant(systems.h2_fluid(500), polar_ewald_full=1),
         "mixed_damp_off": _variant(m, damp_type=DAMP_OFF, polar_max_iter=3),
         "mixed_damp_linear": _variant(m, damp_type=DAMP_LINEAR, polar_damp=2.1304),
         "mixed_wh": _variant(m, mixing=MIX_WH),

@@ -731,12 +731,185 @@ static int o_thole_iterative(const osys_t *s, const double *ef_static, const dou
     return iteration_counter;
 }
 
+
+/* ------------------------------------------------------------------ */
+/* full-Ewald polarization                                             */
+/* ------------------------------------------------------------------ */
+/* damp_factor(): src/polarization/polar_ewald.c:28-36 */
+static double o_damp_factor(double t, int i) {
+    double poo = 1.0 + t + 0.5 * t * t;
+    if (i == 3) poo += t * t * t / 6.0;
+    return poo * exp(-t);
+}
+
+/* One row of induced_real_term(): src/polarization/polar_ewald.c:176-230.  Both atoms polarizable,
+ * rimg <= cutoff; frozen-frozen and intramolecular pairs are NOT excluded.  The reference visits
+ * pair (lo,hi) once and updates both rows; row i receives its updates in ascending partner order,
+ * component c in the order q = 0,1,2 (see the p,q loop at :206-226). */
+static void o_ewald_induced_real_row(const osys_t *s, int i, const int *pol, int npol, const double *mu, double *acc) {
+    const mpmc_b200_params *P = s->p;
+    double a = P->polar_ewald_alpha, l = P->polar_damp;
+    int jj, p, q;
+    for (jj = 0; jj < npol; jj++) {
+        int j = pol[jj];
+        ogeom_t g;
+        if (j == i) continue;
+        o_geom(s, i < j ? i : j, i < j ? j : i, &g);
+        if (g.rimg > P->cutoff) continue;
+        double r = g.rimg, ir = 1.0 / r, ir3 = ir * ir * ir, ir5 = ir * ir * ir3;
+        double erfcar = erfc(a * r), expa2r2 = exp(-a * a * r * r);
+        double s2 = erfcar + 2.0 * a * r * O_OneOverSqrtPi_ewald * expa2r2 +
+                    4.0 * a * a * a * r * r * r / 3.0 * O_OneOverSqrtPi_ewald * expa2r2 - o_damp_factor(l * r, 3);
+        double s1d = erfcar + 2.0 * a * r * O_OneOverSqrtPi_ewald * expa2r2 - o_damp_factor(l * r, 2);
+        for (p = 0; p < 3; p++)
+            for (q = 0; q < 3; q++) {
+                double s1 = (p == q) ? s1d : 0;
+                double T = 3.0 * g.dimg[p] * g.dimg[q] * s2 * ir5 - s1 * ir3;
+                acc[p] += T * mu[3 * j + q];
+            }
+    }
+}
+
+/* induced_recip_term(): src/polarization/polar_ewald.c:232-294, all atoms.  The loop at :265-266
+ * overwrites kweight for p = 0,1,2, so only k[2] survives and the same scalar is added to all three
+ * field components (:282-286) -- reproduced as is. */
+static void o_ewald_induced_recip(const osys_t *s, const double *mu, double *ef) {
+    const mpmc_b200_params *P = s->p;
+    int kmax = P->ewald_kmax, l[3], p, q, i, n = s->n;
+    double a = P->polar_ewald_alpha;
+    for (l[0] = 0; l[0] <= kmax; l[0]++)
+        for (l[1] = (!l[0] ? 0 : -kmax); l[1] <= kmax; l[1]++)
+            for (l[2] = ((!l[0] && !l[1]) ? 1 : -kmax); l[2] <= kmax; l[2]++) {
+                double k[3], k2, kweight = 0, Pcos = 0, Psin = 0;
+                if (l[0] * l[0] + l[1] * l[1] + l[2] * l[2] > kmax * kmax) continue;
+                for (p = 0; p < 3; p++) {
+                    k[p] = 0;
+                    for (q = 0; q < 3; q++) k[p] += 2.0 * M_PI * P->reciprocal_basis[p][q] * l[q];
+                }
+                k2 = k[0] * k[0] + k[1] * k[1] + k[2] * k[2];
+                for (p = 0; p < 3; p++) kweight = 8.0 * M_PI / P->volume * exp(-k2 / (4.0 * a * a)) / k2 * k[p];
+                for (i = 0; i < n; i++) {
+                    const double *r = s->pos + 3 * i, *m = mu + 3 * i;
+                    double d1 = k[0] * m[0] + k[1] * m[1] + k[2] * m[2];
+                    double d2 = k[0] * r[0] + k[1] * r[1] + k[2] * r[2];
+                    Pcos += d1 * cos(d2);
+                    Psin += d1 * sin(d2);
+                }
+#pragma omp parallel for schedule(static) private(p)
+                for (i = 0; i < n; i++) {
+                    const double *r = s->pos + 3 * i;
+                    for (p = 0; p < 3; p++) {
+                        double d1 = k[0] * r[0] + k[1] * r[1] + k[2] * r[2];
+                        ef[3 * i + p] += kweight * (-sin(d1) * Psin - cos(d1) * Pcos);
+                    }
+                }
+            }
+}
+
+/* clear_ef_induced + induced_real_term + induced_recip_term + induced_corr_term
+ * (polar_ewald.c:151-163,176-317) for the current mu */
+#define O_SqrtPi_ewald 1.77245385091 /* polar_ewald.c:7, the truncated constant is the reference's */
+static void o_ewald_induced_field(const osys_t *s, const int *pol, int npol, const double *mu, double *ef) {
+    const mpmc_b200_params *P = s->p;
+    int n = s->n, i, p;
+    double a = P->polar_ewald_alpha, totalmu[3] = {0, 0, 0};
+    memset(ef, 0, sizeof(double) * 3 * n);
+#pragma omp parallel for schedule(dynamic, 8)
+    for (i = 0; i < n; i++)
+        if (s->alpha[i] != 0) o_ewald_induced_real_row(s, i, pol, npol, mu, ef + 3 * i);
+    o_ewald_induced_recip(s, mu, ef);
+    for (i = 0; i < n; i++)
+        for (p = 0; p < 3; p++) totalmu[p] += mu[3 * i + p];
+    for (i = 0; i < n; i++)
+        for (p = 0; p < 3; p++)
+            ef[3 * i + p] += -4.0 * M_PI / (3.0 * P->volume) * totalmu[p] + 4.0 * a * a * a / (3.0 * O_SqrtPi_ewald) * mu[3 * i + p];
+}
+
+/* ewald_full(): src/polarization/polar_ewald.c:375-418 with init_dipoles_ewald :135-148,
+ * new_dipoles :319-345, ewald_palmo_contraction :347-371; calc_dipole_rrms / are_we_done_yet are the
+ * ones of thole_iterative.c:61-117.  The iteration counter is 0-based here (are_we_done_yet sees
+ * 0,1,2,...: polar_max_iter = m gives m+1 passes) and the rrms is taken BEFORE new_dipoles, i.e.
+ * from the previous pass' new_mu / old_mu -- both as in the reference.  Returns the number of
+ * passes (the reference does not report it: nodestats->polarization_iterations is left alone). */
+static int o_ewald_full(const osys_t *s, const double *ef_static, double *mu, double *ef_induced, double *eic,
+                        double *old_mu, double *new_mu, double *rrms, int *iter_success, double *contractions) {
+    const mpmc_b200_params *P = s->p;
+    int n = s->n, i, p, npol = 0, count = 0, keep = 1;
+    int *pol = (int *)malloc(sizeof(int) * (n > 0 ? n : 1));
+    for (i = 0; i < n; i++)
+        if (s->alpha[i] != 0.0) pol[npol++] = i;
+    for (i = 0; i < n; i++)
+        for (p = 0; p < 3; p++) {
+            old_mu[3 * i + p] = 0;
+            new_mu[3 * i + p] = mu[3 * i + p] = s->alpha[i] * ef_static[3 * i + p];
+        }
+    while (keep) {
+        if (count >= O_MAX_ITERATION_COUNT && P->polar_precision) {
+            *iter_success = 1;
+            break;
+        }
+        o_ewald_induced_field(s, pol, npol, mu, ef_induced);
+        *contractions += 1;
+        if (P->polar_rrms || P->polar_precision > 0)
+            for (i = 0; i < n; i++) {
+                double acc = 0;
+                for (p = 0; p < 3; p++) {
+                    double carry = new_mu[3 * i + p] - old_mu[3 * i + p];
+                    acc += carry * carry;
+                }
+                acc /= new_mu[3 * i] * new_mu[3 * i] + new_mu[3 * i + 1] * new_mu[3 * i + 1] + new_mu[3 * i + 2] * new_mu[3 * i + 2];
+                acc = sqrt(acc);
+                if (!isfinite(acc)) acc = 0;
+                rrms[i] = acc;
+            }
+        for (i = 0; i < n; i++)
+            for (p = 0; p < 3; p++) {
+                int k = 3 * i + p;
+                old_mu[k] = mu[k];
+                new_mu[k] = s->alpha[i] * (ef_static[k] + ef_induced[k]);
+                if (P->polar_sor)
+                    new_mu[k] = mu[k] = P->polar_gamma * new_mu[k] + (1.0 - P->polar_gamma) * old_mu[k];
+                else if (P->polar_esor)
+                    new_mu[k] = mu[k] = (1.0 - exp(-P->polar_gamma * (count + 1))) * new_mu[k] +
+                                        exp(-P->polar_gamma * (count + 1)) * old_mu[k];
+                else
+                    mu[k] = new_mu[k];
+            }
+        keep = 0;
+        if (P->polar_precision == 0.0) {
+            if (count != P->polar_max_iter) keep = 1;
+        } else {
+            double allowed = P->polar_precision * P->polar_precision * O_DEBYE2SKA * O_DEBYE2SKA;
+            for (i = 0; i < n && !keep; i++)
+                for (p = 0; p < 3; p++) {
+                    double err = new_mu[3 * i + p] - old_mu[3 * i + p];
+                    if (err * err > allowed) {
+                        keep = 1;
+                        break;
+                    }
+                }
+        }
+        if (P->polar_palmo && !keep) {
+            o_ewald_induced_field(s, pol, npol, mu, ef_induced);
+            *contractions += 1;
+            for (i = 0; i < n; i++) {
+                if (s->alpha[i] == 0) continue;
+                for (p = 0; p < 3; p++)
+                    eic[3 * i + p] = ef_induced[3 * i + p] - (new_mu[3 * i + p] / s->alpha[i] - ef_static[3 * i + p]);
+            }
+        }
+        count++;
+    }
+    free(pol);
+    return count;
+}
+
 /* ------------------------------------------------------------------ */
 /* entry points                                                        */
 /* ------------------------------------------------------------------ */
 static int o_check(const mpmc_b200_params *P) {
-    if (P->polarization && !P->polar_iterative && !P->polar_zodid) return 3; /* LU inversion path: out of scope */
-    if (P->polarization && P->polar_ewald_full) return 4;                     /* ewald_full: next */
+    if (P->polarization && !P->polar_iterative && !P->polar_zodid && !P->polar_ewald_full)
+        return 3; /* LU inversion path: out of scope */
     return 0;
 }
 
@@ -768,14 +941,25 @@ int mpmc_oracle_polar(const mpmc_b200_params *P, int n, const double *pos, const
     for (i = 0; i < n; i++)
         if (polarizability[i] != 0.0) pol[npol++] = i;
     if (P->polar_iterative && P->polar_gs_ranked) o_rank_metric(&s, pol, npol, b_rk);
-    o_static_field(&s, b_es, &pairs_field);
     out->iter_success = 0;
-    out->polar_iterations = o_thole_iterative(&s, b_es, b_rk, b_mu, b_ei, b_eic, old_mu, new_mu, b_rr,
-                                              &out->iter_success, &contractions);
-    for (i = 0; i < n; i++) { /* get_dipole_rrms(): polar.c:13-28 */
-        if (isfinite(b_rr[i])) rr += b_rr[i];
+    if (P->polar_ewald_full) { /* polar.c:54-57: ewald_full() does its own Ewald static field (zero_out, recip, real) */
+        mpmc_b200_params P2 = *P;
+        osys_t s2 = s;
+        P2.polar_ewald = 1;
+        s2.p = &P2;
+        o_static_field(&s2, b_es, &pairs_field);
+        o_ewald_full(&s, b_es, b_mu, b_ei, b_eic, old_mu, new_mu, b_rr, &out->iter_success, &contractions);
+        out->polar_iterations = 0; /* not reported by the reference on this branch */
+        out->dipole_rrms = 0;
+    } else {
+        o_static_field(&s, b_es, &pairs_field);
+        out->polar_iterations = o_thole_iterative(&s, b_es, b_rk, b_mu, b_ei, b_eic, old_mu, new_mu, b_rr,
+                                                  &out->iter_success, &contractions);
+        for (i = 0; i < n; i++) { /* get_dipole_rrms(): polar.c:13-28 */
+            if (isfinite(b_rr[i])) rr += b_rr[i];
+        }
+        out->dipole_rrms = n ? rr / n : 0;
     }
-    out->dipole_rrms = n ? rr / n : 0;
     for (i = 0; i < n; i++) { /* polar.c:108-116 */
         potential += b_mu[3 * i] * b_es[3 * i] + b_mu[3 * i + 1] * b_es[3 * i + 1] + b_mu[3 * i + 2] * b_es[3 * i + 2];
         if (P->polar_palmo)
