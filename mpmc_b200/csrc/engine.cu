@@ -106,7 +106,8 @@ enum Slot {
     S_POLAR = 9,   // 3: sum mu.Es, sum mu.eic, sum rrms
     S_ERR = 12,    // max err^2 bits (as unsigned long long)
     S_FIELDCNT = 13,
-    S_COUNT = 16
+    S_TOTMU = 16,  // 3: sum of the dipoles (full-Ewald polarization)
+    S_COUNT = 20
 };
 
 }  // namespace
@@ -131,6 +132,8 @@ struct mpmc_b200_ctx {
     Subset nonpol;                   // alpha == 0 atoms: rows of the palmo field that are only written back
     DevBuf<double> eic_np;           // [3][nonpol.n_pad]
     bool eic_np_valid = false;
+    DevBuf<double> eind_np;          // [3][nonpol.n_pad]: ef_induced of the alpha == 0 atoms (full-Ewald polarization only)
+    bool eind_np_valid = false;
     DevBuf<int2> tiles;
     int ntiles = 0;
     DevBuf<double> pair_part;
@@ -590,7 +593,7 @@ static int repack(Ctx* c) {
     // Jacobi family: the polarizable list is kept in spatial order (symmetric K4); Gauss-Seidel processes
     // atoms in list / rank order and keeps the list order
     c->pol_sorted = false;
-    if (c->use_sym && !(c->P.polar_gs || c->P.polar_gs_ranked) && c->have_params) {
+    if (c->use_sym && (!(c->P.polar_gs || c->P.polar_gs_ranked) || c->P.polar_ewald_full) && c->have_params) {
         spatial_order(c, pol);
         c->pol_sorted = true;
         c->hx_sort = c->hx;
@@ -601,7 +604,8 @@ static int repack(Ctx* c) {
     if (pack_subset(c, c->charged, charged, TILE, false) || pack_subset(c, c->recip, recip, TILE, false) ||
         pack_subset(c, c->pol, pol, polpad, true) || pack_subset(c, c->nonpol, nonpol, polpad, true))
         return 11;
-    if (c->eic_np.ensure((size_t)3 * c->nonpol.n_pad)) FAIL(11, "cudaMalloc failed");
+    if (c->eic_np.ensure((size_t)3 * c->nonpol.n_pad) || c->eind_np.ensure((size_t)3 * c->nonpol.n_pad))
+        FAIL(11, "cudaMalloc failed");
     c->hperm.assign(c->pol.n_pad, 0);
     std::iota(c->hperm.begin(), c->hperm.end(), 0);
 
@@ -788,10 +792,9 @@ static AtomsDev atoms_dev(Ctx* c) {
 
 static int check_supported(const mpmc_b200_params& P) {
     if (P.polarization && !P.rd_only) {
-        if (P.polar_ewald_full) FAIL(3, "polar_ewald_full is not implemented in the B200 engine yet (SURVEY 8f f1)");
-        if (!P.polar_iterative && !P.polar_zodid)
+        if (!P.polar_iterative && !P.polar_zodid && !P.polar_ewald_full)
             FAIL(3, "matrix-inversion polarization (polar_iterative off) is out of scope: O(N^3) dense LU");
-        if (!P.polar_zodid && P.polar_precision == 0.0 && P.polar_max_iter <= 0)
+        if (!P.polar_zodid && !P.polar_ewald_full && P.polar_precision == 0.0 && P.polar_max_iter <= 0)
             FAIL(3, "polar_max_iter must be > 0 when polar_precision is 0");
         if (P.damp_type < 0 || P.damp_type > 2) FAIL(3, "unknown damp_type");
     }
@@ -837,6 +840,7 @@ static void polar_prepare(Ctx* c) {
     c->pending_iterations = 0;
     c->pending_iter_success = 0;
     c->eic_np_valid = false;
+    c->eind_np_valid = false;
     c->cnt.contractions = 0;
     c->cnt.n_polarizable = c->pol.n;
     c->cnt.pairs_dipole = (double)c->pol.n * std::max(c->pol.n - 1, 0);
@@ -867,7 +871,7 @@ static int polar_field(Ctx* c) {
     fo.cutoffterm = 0.0;
     fo.a = 0.0;
     bool accumulate = false;
-    if (P.polar_ewald) {
+    if (P.polar_ewald || P.polar_ewald_full) {  // ewald_full() computes its own Ewald static field (polar_ewald.c:379-382)
         fo.mode = FIELD_EWALD_REAL;
         fo.a = P.polar_ewald_alpha;
         // recip_term(): S(k) over ALL atoms (polar_ewald.c:104-108); zero-charge atoms add exact zeros
@@ -960,10 +964,10 @@ static int polar_init(Ctx* c) {
     const mpmc_b200_params& P = c->P;
     cudaStream_t st = c->stream;
     const int np = c->n_pad, pp = c->pol.n_pad;
-    const double gscale = (!P.polar_sor && !P.polar_esor) ? P.polar_gamma : 1.0;
+    const double gscale = (!P.polar_sor && !P.polar_esor && !P.polar_ewald_full) ? P.polar_gamma : 1.0;  // polar_ewald.c:144
     launch_dipole_init(c->pol.dev(), c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st);
     c->launches++;
-    if (c->use_sym && c->pol.n > 0) {
+    if ((c->use_sym || P.polar_ewald_full) && c->pol.n > 0) {
         launch_cluster_boxes(make_cell(P), is_ortho(P), c->pol.dev(), c->cbox.p, st);
         c->launches++;
     }
@@ -1093,6 +1097,98 @@ static int polar_energy_partial(Ctx* c) {
     return 0;
 }
 
+
+// ---- ewald_full(): src/polarization/polar_ewald.c:375-418 on ONE device.  c->es / c->mu hold E_s and
+// mu0 = alpha E_s (polar_init).  The pass counter is 0-based and are_we_done_yet sees it as is, the rrms is
+// taken before new_dipoles -- both as in the reference.
+static int ewald_full_field(Ctx* c, const EwaldFullOpts& eo, const KVecDev& kv, int apc) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    const Cell cell = make_cell(P);
+    const SubsetDev pol = c->pol.dev();
+    kev_mark(c);
+    const int js = launch_induced_real_clusters(cell, is_ortho(P), pol, eo, c->cbox.p, c->mu.p, c->dipole_jsplits, c->epart.p, st);
+    kev_mark(c);
+    const int chunks = launch_dipole_sf(cell, pol, kv, c->kvec.p, c->mu.p, apc, c->sf_partial.p, st);
+    launch_recip_finish(kv, c->sf_partial.p, chunks, 0.0, c->sf.p, nullptr, 0, 0, st);
+    launch_total_mu(pol, c->mu.p, c->scalars.p + S_TOTMU, st);
+    launch_induced_finish(cell, pol, kv, c->kvec.p, c->sf.p, eo, c->epart.p, js, c->scalars.p + S_TOTMU, c->mu.p, c->eind.p, st);
+    c->launches += 5;
+    c->cnt.contractions += 1;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+static int enqueue_ewald_full(Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    const int pp = c->pol.n_pad;
+    if (c->world > 1) FAIL(3, "polar_ewald_full is single-GPU in this round (replicas only)");
+    if (c->pol.n <= 0) return 0;
+    const SubsetDev pol = c->pol.dev();
+    unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
+    EwaldFullOpts eo;
+    eo.a = P.polar_ewald_alpha;
+    eo.damp = P.polar_damp;
+    KVecDev kv;
+    kv.nk = c->nk;
+    kv.kmax = P.ewald_kmax;
+    kv.l = c->kl.p;
+    kv.weight = c->kweight_field.p;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    const int apc = std::max(64, round_up((c->pol.n + 2 * sms - 1) / (2 * sms), 64));
+    const int chunks = (c->pol.n + apc - 1) / apc;
+    if (c->sf_partial.ensure((size_t)std::max(chunks, 1) * 2 * std::max(c->nk, 1)) ||
+        c->epart.ensure((size_t)c->dipole_jsplits * 3 * pp))
+        FAIL(11, "cudaMalloc failed");
+    // init_dipoles_ewald (:135-148): old_mu = 0, new_mu = mu = alpha E_s
+    CU(cudaMemsetAsync(c->mu_old.p, 0, sizeof(double) * 3 * pp, st));
+    CU(cudaMemcpyAsync(c->mu_new.p, c->mu.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToDevice, st));
+    const bool precision_mode = P.polar_precision != 0.0;
+    const double allowed = P.polar_precision * P.polar_precision * kDEBYE2SKA * kDEBYE2SKA;
+    UpdateOpts uo = update_opts(P, 0);
+    int count = 0;
+    bool keep = true;
+    while (keep) {
+        if (count >= kMAX_ITERATION_COUNT && precision_mode) {  // :391-394: dipoles are left as they are
+            c->pending_iter_success = 1;
+            break;
+        }
+        if (ewald_full_field(c, eo, kv, apc)) return 10;
+        uo.iteration = count;
+        if (precision_mode) CU(cudaMemsetAsync(errbits, 0, sizeof(unsigned long long), st));
+        launch_ewald_update(pol, uo, c->es.p, c->eind.p, c->mu.p, c->mu_old.p, c->mu_new.p, c->rrms.p,
+                            precision_mode ? errbits : nullptr, st);
+        c->launches++;
+        if (!precision_mode)
+            keep = (count != P.polar_max_iter);
+        else {
+            CU(cudaMemcpyAsync(c->h_scalars + S_ERR, c->scalars.p + S_ERR, sizeof(double), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            double worst;
+            memcpy(&worst, c->h_scalars + S_ERR, sizeof(double));
+            keep = worst > allowed;
+        }
+        if (P.polar_palmo && !keep) {  // ewald_palmo_contraction (:347-371)
+            if (ewald_full_field(c, eo, kv, apc)) return 10;
+            launch_ewald_palmo_finish(pol, c->es.p, c->eind.p, c->mu_new.p, c->eic.p, st);
+            c->launches++;
+        }
+        count++;
+    }
+    c->pending_iterations = count;
+    // ef_induced of the alpha == 0 atoms (write-back only): reciprocal + surface terms of the last field pass
+    if (c->nonpol.n > 0 && count > 0) {
+        launch_induced_finish(make_cell(P), c->nonpol.dev(), kv, c->kvec.p, c->sf.p, eo, nullptr, 0, c->scalars.p + S_TOTMU,
+                              nullptr, c->eind_np.p, st);
+        c->launches++;
+        c->eind_np_valid = true;
+    }
+    CU(cudaGetLastError());
+    return 0;
+}
+
 // ---- polar(): static field + solver + energy on ONE device.  Enqueue only (precision mode syncs
 // per iteration).  thole_iterative(): thole_iterative.c:168-259.
 static int enqueue_polar(Ctx* c) {
@@ -1110,11 +1206,13 @@ static int enqueue_polar(Ctx* c) {
     const bool want_rrms = P.polar_rrms || P.polar_precision > 0;
     const DipoleOpts dop = dipole_opts(P);
     UpdateOpts uo = update_opts(P, 0);
-    const bool gs = P.polar_gs || P.polar_gs_ranked;
+    const bool gs = (P.polar_gs || P.polar_gs_ranked) && !P.polar_ewald_full;
     const double allowed = P.polar_precision * P.polar_precision * kDEBYE2SKA * kDEBYE2SKA;
     const int js = c->dipole_jsplits;
 
-    if (!P.polar_zodid && c->pol.n > 0) {
+    if (P.polar_ewald_full) {  // polar.c:54-57 takes this branch before looking at polar_iterative / zodid
+        if (enqueue_ewald_full(c)) return 10;
+    } else if (!P.polar_zodid && c->pol.n > 0) {
         if (gs && c->world > 1) FAIL(3, "Gauss-Seidel polarization is single-GPU only (sequential dependency)");
         // ---- Gauss-Seidel working set (processing order = hperm) ----
         SubsetDev g = pol;
@@ -1417,6 +1515,10 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
         out->dipole_rrms = c->n ? h[S_POLAR + 2] / c->n : 0.0;
         out->polar_iterations = c->pending_iterations;
         out->iter_success = c->pending_iter_success;
+        if (P.polar_ewald_full) {  // polar.c:54-57: this branch reports neither the pass count nor the rrms
+            out->polar_iterations = 0;
+            out->dipole_rrms = 0.0;
+        }
     }
     out->total = out->rd + out->coulombic + out->polar;  // energy.c:194
     return 0;
@@ -1763,6 +1865,14 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
         CU(cudaStreamSynchronize(c->stream));
         for (int k = 0; k < c->nonpol.n; k++)
             for (int d3 = 0; d3 < 3; d3++) ef_induced_change[3 * c->nonpol.idx[k] + d3] = nb[(size_t)d3 * qp + k];
+    }
+    if (ef_induced && c->eind_np_valid && c->nonpol.n > 0) {
+        const int qp = c->nonpol.n_pad;
+        std::vector<double> nb((size_t)3 * qp);
+        CU(cudaMemcpyAsync(nb.data(), c->eind_np.p, sizeof(double) * 3 * qp, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        for (int k = 0; k < c->nonpol.n; k++)
+            for (int d3 = 0; d3 < 3; d3++) ef_induced[3 * c->nonpol.idx[k] + d3] = nb[(size_t)d3 * qp + k];
     }
     if (ef_static) {
         CU(cudaMemcpyAsync(buf.data(), c->ef_static.p, sizeof(double) * 3 * np, cudaMemcpyDeviceToHost, c->stream));

@@ -1,0 +1,365 @@
+// ewald_full_kernel.cu -- K7: full-Ewald polarization.
+//
+// Reference loops replaced (relative to the reference tree, src/polarization/polar_ewald.c):
+//   induced_real_term()   :176-230   cutoff pairs of polarizable atoms, erfc-screened damped tensor
+//   induced_recip_term()  :232-294   k-sum of the dipole structure factor, all atoms
+//   induced_corr_term()   :296-317   surface term -4 pi/(3V) sum(mu) and self term 4 a^3/(3 sqrt(pi)) mu_i
+//   init_dipoles_ewald / new_dipoles / ewald_palmo_contraction  :135-148, :319-371
+//   calc_dipole_rrms / are_we_done_yet (thole_iterative.c:61-117) as ewald_full() :375-418 calls them
+//
+// Layout: the polarizable subset in spatial order (the same packed image the symmetric K4 uses), solver
+// vectors [3][n_pad].  Nothing is accumulated with atomics: the real term is row-owned (one warp per
+// 32-atom i-cluster, j-clusters culled by their bounding boxes against the cutoff, j range split into
+// `jsplits` slices written to separate partial rows), the dipole structure factor is summed per chunk
+// and then in chunk order, the per-atom k-sum runs in k order.
+//
+// Two reference quirks are reproduced because parity is against the reference as it is:
+//   * polar_ewald.c:265-266 overwrites `kweight` in a loop over p, so only k_z survives and the same
+//     scalar is added to all three components of the reciprocal induced field (:282-286);
+//   * SqrtPi is the truncated 1.77245385091 (:7).
+#include "kernels.h"
+
+namespace mpmc {
+
+namespace {
+
+constexpr double kOneOverSqrtPi = 0.5641895835477562869480794515607725858440506293289988;
+constexpr double kSqrtPiRef = 1.77245385091;
+
+struct JRec {
+    double x, y, z, mx, my, mz;
+    int valid, pad;
+};
+
+// E_i += T_ij mu_j with T = 3 d d^T s2 / r^5 - s1 / r^3 (polar_ewald.c:196-226)
+template <bool ORTHO>
+__device__ __forceinline__ void induced_real_pair(const Cell& c, const EwaldFullOpts& k, double xi, double yi, double zi,
+                                                  const JRec& r, double& ex, double& ey, double& ez) {
+    double dx = xi - r.x, dy = yi - r.y, dz = zi - r.z;
+    min_image<ORTHO>(c, dx, dy, dz);
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    const double rr = sqrt(r2);
+    if (rr > c.cutoff) return;  // :188 (r == cutoff is kept)
+    const double ir = 1.0 / rr, ir3 = ir * ir * ir, ir5 = ir * ir * ir3;
+    const double a = k.a;
+    const double erfcar = erfc(a * rr), ex2 = exp(-a * a * r2);
+    const double t = k.damp * rr, et = exp(-t);
+    const double df2 = (1.0 + t + 0.5 * t * t) * et;            // damp_factor(t, 2)
+    const double df3 = (1.0 + t + 0.5 * t * t + t * t * t / 6.0) * et;  // damp_factor(t, 3)
+    const double g = 2.0 * a * rr * kOneOverSqrtPi * ex2;
+    const double s1 = erfcar + g - df2;
+    const double s2 = erfcar + g + 4.0 * a * a * a * rr * r2 / 3.0 * kOneOverSqrtPi * ex2 - df3;
+    const double dmu = dx * r.mx + dy * r.my + dz * r.mz;
+    const double w2 = 3.0 * s2 * ir5 * dmu, w1 = s1 * ir3;
+    ex += w2 * dx - w1 * r.mx;
+    ey += w2 * dy - w1 * r.my;
+    ez += w2 * dz - w1 * r.mz;
+}
+
+template <bool ORTHO>
+__global__ void __launch_bounds__(TILE) induced_real_cluster_kernel(Cell c, SubsetDev a, EwaldFullOpts k, BoxLen box,
+                                                                    const double* __restrict__ cbox, double cull2,
+                                                                    const double* __restrict__ mu, int batches_per_slice,
+                                                                    double* __restrict__ part) {
+    __shared__ JRec rec[4][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int nclus = a.n_pad >> 5, np = a.n_pad;
+    const int ci = blockIdx.x * 4 + w;
+    if (ci >= nclus) return;  // whole warp; no block-level barrier below
+    const int i = ci * 32 + lane;
+    const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
+    double ex = 0.0, ey = 0.0, ez = 0.0;
+    const int b0 = blockIdx.y * batches_per_slice * 32;
+    const int b1 = min(nclus, b0 + batches_per_slice * 32);
+    for (int kb = b0; kb < b1; kb += 32) {
+        const int cj = kb + lane;
+        bool pass = cj < b1;
+        if (pass && cull2 > 0.0) pass = cluster_gap2(box, cbox, nclus, ci, cbox, nclus, cj) <= cull2;
+        unsigned mask = __ballot_sync(0xffffffffu, pass);
+        while (mask) {
+            const int b = __ffs(mask) - 1;
+            mask &= mask - 1;
+            __syncwarp();
+            {
+                const int j = (kb + b) * 32 + lane;
+                JRec r;
+                r.x = a.x[j];
+                r.y = a.y[j];
+                r.z = a.z[j];
+                r.mx = mu[j];
+                r.my = mu[np + j];
+                r.mz = mu[2 * np + j];
+                r.valid = j < a.n;
+                r.pad = 0;
+                rec[w][lane] = r;
+            }
+            __syncwarp();
+            const bool self_cluster = (kb + b == ci);
+            for (int s = 0; s < 32; s++) {
+                const JRec& r = rec[w][s];
+                if (!r.valid) continue;
+                if (self_cluster && s == lane) continue;
+                induced_real_pair<ORTHO>(c, k, xi, yi, zi, r, ex, ey, ez);
+            }
+        }
+    }
+    double* out = part + (size_t)blockIdx.y * 3 * np;
+    out[i] = ex;
+    out[np + i] = ey;
+    out[2 * np + i] = ez;
+}
+
+// Dipole structure factor: P(k) = sum_j (k . mu_j) e^{i k.r_j}  (polar_ewald.c:268-276); same phase
+// tables as recip_sf_kernel, the weight depends on k.
+constexpr int DS_ATOMS = 64;
+constexpr int DS_THREADS = 256;
+
+__global__ void __launch_bounds__(DS_THREADS) dipole_sf_kernel(Cell c, SubsetDev at, KVecDev kv,
+                                                              const double* __restrict__ kvec,
+                                                              const double* __restrict__ mu, int atoms_per_chunk,
+                                                              double* __restrict__ sf_partial) {
+    extern __shared__ double smem[];
+    const int nl = kv.kmax + 1, np = at.n_pad;
+    double* tcos = smem;
+    double* tsin = tcos + 3 * nl * DS_ATOMS;
+    double* tm = tsin + 3 * nl * DS_ATOMS;  // [3][DS_ATOMS]
+    const int a0 = blockIdx.x * atoms_per_chunk;
+    const int a1 = min(a0 + atoms_per_chunk, at.n);
+    double sre[8], sim[8];
+#pragma unroll
+    for (int m = 0; m < 8; m++) sre[m] = sim[m] = 0.0;
+    for (int base = a0; base < a1; base += DS_ATOMS) {
+        const int cnt = min(DS_ATOMS, a1 - base);
+        __syncthreads();
+        for (int w = threadIdx.x; w < 3 * nl * DS_ATOMS; w += DS_THREADS) {
+            const int aa = w % DS_ATOMS, l = (w / DS_ATOMS) % nl, ax = w / (DS_ATOMS * nl);
+            double cs = 1.0, sn = 0.0;
+            if (aa < cnt) {
+                const int g = base + aa;
+                const double sfrac = c.R[0][ax] * at.x[g] + c.R[1][ax] * at.y[g] + c.R[2][ax] * at.z[g];
+                sincospi(2.0 * (double)l * sfrac, &sn, &cs);
+            }
+            tcos[w] = cs;
+            tsin[w] = sn;
+        }
+        for (int w = threadIdx.x; w < 3 * DS_ATOMS; w += DS_THREADS) {
+            const int aa = w % DS_ATOMS, d = w / DS_ATOMS;
+            tm[w] = (aa < cnt) ? mu[d * np + base + aa] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int m = 0; m < 8; m++) {
+            const int ik = threadIdx.x + m * DS_THREADS;
+            if (ik >= kv.nk) break;
+            const int l0 = kv.l[ik], l1 = kv.l[kv.nk + ik], l2 = kv.l[2 * kv.nk + ik];
+            const double kx = kvec[ik], ky = kvec[kv.nk + ik], kz = kvec[2 * kv.nk + ik];
+            const int o0 = (0 * nl + l0) * DS_ATOMS, o1 = (1 * nl + abs(l1)) * DS_ATOMS, o2 = (2 * nl + abs(l2)) * DS_ATOMS;
+            const double sg1 = l1 < 0 ? -1.0 : 1.0, sg2 = l2 < 0 ? -1.0 : 1.0;
+            double re = 0.0, im = 0.0;
+            for (int aa = 0; aa < DS_ATOMS; aa++) {
+                const double c0 = tcos[o0 + aa], s0 = tsin[o0 + aa];
+                const double c1 = tcos[o1 + aa], s1 = sg1 * tsin[o1 + aa];
+                const double c2 = tcos[o2 + aa], s2 = sg2 * tsin[o2 + aa];
+                const double c01 = c0 * c1 - s0 * s1, s01 = s0 * c1 + c0 * s1;
+                const double cc = c01 * c2 - s01 * s2, ss = s01 * c2 + c01 * s2;
+                const double km = kx * tm[aa] + ky * tm[DS_ATOMS + aa] + kz * tm[2 * DS_ATOMS + aa];
+                re += km * cc;
+                im += km * ss;
+            }
+            sre[m] += re;
+            sim[m] += im;
+        }
+    }
+    double* out = sf_partial + (size_t)blockIdx.x * 2 * kv.nk;
+#pragma unroll
+    for (int m = 0; m < 8; m++) {
+        const int ik = threadIdx.x + m * DS_THREADS;
+        if (ik >= kv.nk) break;
+        out[ik] = sre[m];
+        out[kv.nk + ik] = sim[m];
+    }
+}
+
+// sum of the dipoles (polar_ewald.c:303-307), one CTA, fixed order
+__global__ void __launch_bounds__(1024) total_mu_kernel(int n, int np, const double* __restrict__ mu, double* __restrict__ out) {
+    __shared__ double red[32];
+    for (int d = 0; d < 3; d++) {
+        double acc = 0.0;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) acc += mu[d * np + i];
+        acc = block_reduce<0>(acc, red);
+        if (threadIdx.x == 0) out[d] = acc;
+        __syncthreads();
+    }
+}
+
+// ef_induced of the rows of `rows`: real-space partial rows (if any) + the reciprocal term
+//   g_i = sum_k w_k ( -sin(k.r_i) Im P(k) - cos(k.r_i) Re P(k) ),  w_k = scale exp(-k^2/4a^2)/k^2 k_z
+// added to all three components (:278-287) + surface and self terms (:310-314).
+__global__ void __launch_bounds__(TILE) induced_finish_kernel(Cell c, SubsetDev rows, KVecDev kv, const double* __restrict__ kvec,
+                                                              const double* __restrict__ sf, double scale,
+                                                              const double* __restrict__ part, int jsplits, int part_np,
+                                                              const double* __restrict__ total_mu, double surf, double selfc,
+                                                              const double* __restrict__ mu, double* __restrict__ out) {
+    extern __shared__ double smem[];
+    const int nl = kv.kmax + 1, np = rows.n_pad;
+    double* tcos = smem;  // [axis][l][thread]
+    double* tsin = tcos + 3 * nl * TILE;
+    const int i = blockIdx.x * TILE + threadIdx.x;
+    const bool live = i < rows.n;
+    const double x = live ? rows.x[i] : 0.0, y = live ? rows.y[i] : 0.0, z = live ? rows.z[i] : 0.0;
+    for (int ax = 0; ax < 3; ax++) {
+        const double sfrac = c.R[0][ax] * x + c.R[1][ax] * y + c.R[2][ax] * z;
+        for (int l = 0; l < nl; l++) {
+            double sn, cs;
+            sincospi(2.0 * (double)l * sfrac, &sn, &cs);
+            tcos[(ax * nl + l) * TILE + threadIdx.x] = cs;
+            tsin[(ax * nl + l) * TILE + threadIdx.x] = sn;
+        }
+    }
+    double g = 0.0;
+    for (int ik = 0; ik < kv.nk; ik++) {
+        const int l0 = kv.l[ik], l1 = kv.l[kv.nk + ik], l2 = kv.l[2 * kv.nk + ik];
+        const int o0 = (0 * nl + l0) * TILE + threadIdx.x, o1 = (1 * nl + abs(l1)) * TILE + threadIdx.x,
+                  o2 = (2 * nl + abs(l2)) * TILE + threadIdx.x;
+        const double c0 = tcos[o0], s0 = tsin[o0];
+        const double c1 = tcos[o1], s1 = (l1 < 0 ? -1.0 : 1.0) * tsin[o1];
+        const double c2 = tcos[o2], s2 = (l2 < 0 ? -1.0 : 1.0) * tsin[o2];
+        const double c01 = c0 * c1 - s0 * s1, s01 = s0 * c1 + c0 * s1;
+        const double cc = c01 * c2 - s01 * s2, ss = s01 * c2 + c01 * s2;
+        const double wk = scale * kv.weight[ik] * kvec[2 * kv.nk + ik];
+        g += wk * (-ss * sf[kv.nk + ik] - cc * sf[ik]);
+    }
+    if (i >= np) return;
+    for (int d = 0; d < 3; d++) {
+        double e = 0.0;
+        if (live) {
+            for (int js = 0; js < jsplits; js++) e += part[((size_t)js * 3 + d) * part_np + i];
+            e += g;
+            e += surf * total_mu[d] + (mu ? selfc * mu[d * np + i] : 0.0);
+        }
+        out[d * np + i] = e;
+    }
+}
+
+// calc_dipole_rrms (previous pass' new_mu / old_mu, as ewald_full() orders it) + new_dipoles (:319-345)
+// + the are_we_done_yet residual
+__global__ void ewald_update_kernel(int n, int np, const double* __restrict__ alpha, UpdateOpts o,
+                                    const double* __restrict__ es, const double* __restrict__ eind,
+                                    double* __restrict__ mu, double* __restrict__ mu_old, double* __restrict__ mu_new,
+                                    double* __restrict__ rrms, unsigned long long* __restrict__ max_err2_bits) {
+    __shared__ double red[32];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double worst = 0.0;
+    if (i < np) {
+        const double al = i < n ? alpha[i] : 0.0;
+        if (o.do_rrms) {
+            double num = 0.0, den = 0.0;
+            for (int d = 0; d < 3; d++) {
+                const double nw = mu_new[d * np + i], df = nw - mu_old[d * np + i];
+                num += df * df;
+                den += nw * nw;
+            }
+            double v = sqrt(num / den);
+            if (!isfinite(v)) v = 0.0;
+            rrms[i] = v;
+        }
+        const double wold = o.esor ? exp(-o.gamma * (double)(o.iteration + 1)) : 0.0;
+        for (int d = 0; d < 3; d++) {
+            const double old = mu[d * np + i];
+            double nw = al * (es[d * np + i] + eind[d * np + i]);
+            if (o.sor)
+                nw = o.gamma * nw + (1.0 - o.gamma) * old;
+            else if (o.esor)
+                nw = (1.0 - wold) * nw + wold * old;
+            mu_old[d * np + i] = old;
+            mu_new[d * np + i] = nw;
+            mu[d * np + i] = nw;
+            const double df = nw - old;
+            worst = fmax(worst, df * df);
+        }
+    }
+    worst = block_reduce<2>(worst, red);
+    if (threadIdx.x == 0 && max_err2_bits) atomicMax(max_err2_bits, (unsigned long long)__double_as_longlong(worst));
+}
+
+// ewald_palmo_contraction (:347-371): eic = ef_induced - (new_mu / alpha - ef_static), alpha != 0
+__global__ void ewald_palmo_finish_kernel(int n, int np, const double* __restrict__ alpha, const double* __restrict__ es,
+                                          const double* __restrict__ eind, const double* __restrict__ mu_new,
+                                          double* __restrict__ eic) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double al = alpha[i];
+    if (al == 0.0) return;
+    for (int d = 0; d < 3; d++) eic[d * np + i] = eind[d * np + i] - (mu_new[d * np + i] / al - es[d * np + i]);
+}
+
+}  // namespace
+
+int launch_induced_real_clusters(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
+                                 const double* mu, int jsplits, double* part, cudaStream_t s) {
+    const int nclus = pol.n_pad / 32;
+    if (nclus <= 0) return 0;
+    const double cull = c.cutoff + 1e-6;
+    const double cull2 = ortho ? cull * cull : 0.0;
+    const int batches = (nclus + 31) / 32;
+    if (jsplits < 1) jsplits = 1;
+    if (jsplits > batches) jsplits = batches;
+    const int bps = (batches + jsplits - 1) / jsplits;
+    jsplits = (batches + bps - 1) / bps;
+    dim3 grid((nclus + 3) / 4, jsplits);
+    if (ortho)
+        induced_real_cluster_kernel<true><<<grid, TILE, 0, s>>>(c, pol, o, box_len(c), cbox, cull2, mu, bps, part);
+    else
+        induced_real_cluster_kernel<false><<<grid, TILE, 0, s>>>(c, pol, o, box_len(c), cbox, cull2, mu, bps, part);
+    return jsplits;
+}
+
+int launch_dipole_sf(const Cell& c, const SubsetDev& pol, const KVecDev& kv, const double* kvec, const double* mu,
+                     int atoms_per_chunk, double* sf_partial, cudaStream_t s) {
+    const int nchunks = (pol.n + atoms_per_chunk - 1) / atoms_per_chunk;
+    if (nchunks <= 0) return 0;
+    const size_t smem = sizeof(double) * (6 * (kv.kmax + 1) * DS_ATOMS + 3 * DS_ATOMS);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(dipole_sf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    dipole_sf_kernel<<<nchunks, DS_THREADS, smem, s>>>(c, pol, kv, kvec, mu, atoms_per_chunk, sf_partial);
+    return nchunks;
+}
+
+void launch_total_mu(const SubsetDev& pol, const double* mu, double* out3, cudaStream_t s) {
+    total_mu_kernel<<<1, 1024, 0, s>>>(pol.n, pol.n_pad, mu, out3);
+}
+
+void launch_induced_finish(const Cell& c, const SubsetDev& rows, const KVecDev& kv, const double* kvec, const double* sf,
+                           const EwaldFullOpts& o, const double* part, int jsplits, const double* total_mu, const double* mu,
+                           double* out, cudaStream_t s) {
+    if (rows.n_pad <= 0) return;
+    const size_t smem = sizeof(double) * 6 * (kv.kmax + 1) * TILE;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(induced_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    const double scale = 8.0 * M_PI / c.volume;                            // :266
+    const double surf = -4.0 * M_PI / (3.0 * c.volume);                    // :314
+    const double selfc = 4.0 * o.a * o.a * o.a / (3.0 * kSqrtPiRef);       // :314
+    induced_finish_kernel<<<rows.n_pad / TILE, TILE, smem, s>>>(c, rows, kv, kvec, sf, scale, part, part ? jsplits : 0,
+                                                               rows.n_pad, total_mu, surf, selfc, mu, out);
+}
+
+void launch_ewald_update(const SubsetDev& pol, const UpdateOpts& o, const double* es, const double* eind, double* mu,
+                         double* mu_old, double* mu_new, double* rrms, unsigned long long* max_err2_bits, cudaStream_t s) {
+    if (pol.n_pad <= 0) return;
+    ewald_update_kernel<<<(pol.n_pad + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pol.alpha, o, es, eind, mu, mu_old, mu_new,
+                                                              rrms, max_err2_bits);
+}
+
+void launch_ewald_palmo_finish(const SubsetDev& pol, const double* es, const double* eind, const double* mu_new, double* eic,
+                               cudaStream_t s) {
+    if (pol.n <= 0) return;
+    ewald_palmo_finish_kernel<<<(pol.n + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pol.alpha, es, eind, mu_new, eic);
+}
+
+}  // namespace mpmc

@@ -147,6 +147,30 @@ void launch_gs_sweep(const Cell& c, bool ortho, const SubsetDev& pol, const Dipo
 void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank /*[pol n_pad]*/,
                         cudaStream_t s);
 
+// ---- K7: full-Ewald polarization (ewald_full_kernel.cu) -----------------------------------------
+// replaces induced_real_term / induced_recip_term / induced_corr_term / new_dipoles /
+// ewald_palmo_contraction (src/polarization/polar_ewald.c:176-371)
+struct EwaldFullOpts {
+    double a;     // polar_ewald_alpha
+    double damp;  // polar_damp
+};
+// row-owned real-space term over the spatially ordered polarizable subset; returns the number of j slices
+// written to part [slices][3][n_pad]
+int launch_induced_real_clusters(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
+                                 const double* mu, int jsplits, double* part, cudaStream_t s);
+// P(k) = sum_j (k.mu_j) e^{ik.r_j}: per-chunk partials [chunks][2][nk] (sum with launch_recip_finish); returns chunks
+int launch_dipole_sf(const Cell& c, const SubsetDev& pol, const KVecDev& kv, const double* kvec, const double* mu,
+                     int atoms_per_chunk, double* sf_partial, cudaStream_t s);
+void launch_total_mu(const SubsetDev& pol, const double* mu, double* out3, cudaStream_t s);
+// out[3][rows.n_pad] = sum_js part + reciprocal term + surface term (+ self term when mu != null)
+void launch_induced_finish(const Cell& c, const SubsetDev& rows, const KVecDev& kv, const double* kvec, const double* sf,
+                           const EwaldFullOpts& o, const double* part, int jsplits, const double* total_mu, const double* mu,
+                           double* out, cudaStream_t s);
+void launch_ewald_update(const SubsetDev& pol, const UpdateOpts& o, const double* es, const double* eind, double* mu,
+                         double* mu_old, double* mu_new, double* rrms, unsigned long long* max_err2_bits, cudaStream_t s);
+void launch_ewald_palmo_finish(const SubsetDev& pol, const double* es, const double* eind, const double* mu_new, double* eic,
+                               cudaStream_t s);
+
 // fp64 FMA throughput probe
 double measure_fp64_peak_tflops(cudaStream_t s);
 

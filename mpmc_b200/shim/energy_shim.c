@@ -382,6 +382,10 @@ static void shim_write_back_atoms(system_t *system) {
 static void shim_polar_epilogue(system_t *system, const mpmc_b200_energies *e) {
     char linebuf[MAXLINE];
     shim_write_back_atoms(system);
+    if (system->polar_ewald_full) { /* polar.c:54-57: ewald_full() reports a failed solve only (polar_ewald.c:391-394) */
+        if (e->iter_success) system->iter_success = 1;
+        return;
+    }
     if (!system->polar_iterative) return;
     system->nodestats->polarization_iterations = (double)e->polar_iterations;
     system->observables->dipole_rrms = e->dipole_rrms;

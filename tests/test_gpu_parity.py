@@ -41,6 +41,25 @@ def test_cuda_matches_oracle_midsize(engine, builder, kw):
         gu.assert_atom_arrays(engine.atom_arrays(), oarr, s, rtol=1e-10, label=s.name)
 
 
+@pytest.mark.parametrize("builder,kw,par", [
+    (systems.h2_fluid, dict(n_atoms=3000), dict(polar_max_iter=5)),
+    (systems.mof_h2, dict(cells=(3, 3, 1)), dict(polar_precision=1e-5, polar_max_iter=0, polar_palmo=1, polar_rrms=1)),
+])
+def test_ewald_full_matches_oracle_midsize(engine, builder, kw, par):
+    """Full-Ewald polarization (ewald_full(), polar_ewald.c:375-418) at sizes with many clusters and j slices."""
+    from oracle import oracle
+
+    s = builder(**kw)
+    s.params.polar_ewald_full = 1
+    for k, v in par.items():
+        setattr(s.params, k, v)
+    engine.set_system(s)
+    got = engine.energy()
+    exp, _, oarr = oracle.energy(s, nthreads=0)
+    gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=s.name)
+    gu.assert_atom_arrays(engine.atom_arrays(), oarr, s, rtol=1e-10, label=s.name)
+
+
 def test_polar_entry_point(engine):
     s, exp = gu.load("mixed_default")
     engine.set_system(s)

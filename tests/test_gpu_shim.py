@@ -27,7 +27,8 @@ PROGRAM = os.path.join(BUILD, "mpmc_b200")
 SINGLE_POINT = ["ref_small", "ref_socmof", "ref_socmof_production", "mixed_default", "mixed_tri_default", "mixed_gs_ranked",
                 "mixed_palmo", "mixed_precision", "mixed_polar_ewald", "mixed_wolf_full", "mixed_wh", "mixed_sor",
                 "mixed_autoreject_fires", "mixed_nopolar_kmax5", "mixed_rd_only", "co2_fluid_375", "h2_fluid_500",
-                "ref_test_lenard_jones", "ref_test_coulombic"]
+                "ref_test_lenard_jones", "ref_test_coulombic", "mixed_ewald_full", "mixed_ewald_full_precision_palmo_rrms",
+                "mixed_tri_ewald_full"]
 
 
 def _need(path):
