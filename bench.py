@@ -306,16 +306,23 @@ def own_arm(args):
     h2d = n * 3 * 8
     d2h = 32 * 8 + (4 * 3 + 2) * 8 * n if s.params.polarization else 32 * 8
     movable = np.flatnonzero(s.frozen == 0)
+    arr = sh.atom_arrays() if s.params.polarization else None  # the caller's write-back buffers, reused every step
     barrier()
+    t_set = t_eval = t_wb = 0.0
     t0 = time.perf_counter()
     for k in range(args.steps):
         # one MC translation of one molecule (5 sites), applied on the host copy the caller owns
         first = int(movable[0]) + 5 * int(rng.integers(0, max(1, movable.size // 5)))
         hnp[first:first + 5] += rng.uniform(-0.05, 0.05, size=3)
+        ta = time.perf_counter()
         sh.set_positions(0, hnp)           # host -> device, all positions (the drop-in does not diff)
+        tb = time.perf_counter()
         e = sh.energy()                    # device -> host: energies
+        tc = time.perf_counter()
         if s.params.polarization:
-            arr = sh.atom_arrays()         # device -> host: mu, ef_static, ef_induced, ... as polar() writes back
+            arr = sh.atom_arrays(arr)      # device -> host: mu, ef_static, ef_induced, ... as polar() writes back
+        td = time.perf_counter()
+        t_set, t_eval, t_wb = t_set + (tb - ta), t_eval + (tc - tb), t_wb + (td - tc)
         launches += sh.kernel_launches()
     barrier()
     sec = time.perf_counter() - t0
@@ -361,7 +368,9 @@ def own_arm(args):
                    "mc_steps_per_s": 1e3 / ms_per_step, "l2": "flushed between timed iterations (256 MiB fill)",
                    "parallelism": f"rows{world}", "energy_K": e.total},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "mc_steps_per_s": args.steps / float(t.item())},
+                "mc_steps_per_s": args.steps / float(t.item()),
+                "host_ms_per_step": {"set_positions": 1e3 * t_set / args.steps, "energy": 1e3 * t_eval / args.steps,
+                                     "write_back": 1e3 * t_wb / args.steps}},
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
     }
     print(json.dumps(line))

@@ -221,6 +221,10 @@ int mpmc_b200_shard_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_pol, i
  * mu, ef_static, ef_induced, ef_induced_change : [3*n] ; dipole_rrms, rank_metric : [n] */
 int mpmc_b200_get_atom_arrays(mpmc_b200_ctx *ctx, double *mu, double *ef_static, double *ef_induced,
                               double *ef_induced_change, double *dipole_rrms, double *rank_metric);
+/* Sharded runs: 1 when every rank's get_atom_arrays() is complete (symmetric contraction: the all-reduced
+ * field lets every rank update every row; only the write-back-only palmo rows of non-polarizable atoms stay
+ * per rank), 0 when the row-owned arrays hold this rank's rows only and must be summed over ranks. */
+int mpmc_b200_atom_arrays_complete(mpmc_b200_ctx *ctx);
 
 int mpmc_b200_get_counters(mpmc_b200_ctx *ctx, mpmc_b200_counters *out);
 

@@ -309,6 +309,7 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_shard_rows.argtypes = [vp, ip, ip, ip, ip]
     lib.mpmc_b200_shard_field_rows.argtypes = [vp, ip, ip, ip]
     lib.mpmc_b200_get_atom_arrays.argtypes = [vp, dp, dp, dp, dp, dp, dp]
+    lib.mpmc_b200_atom_arrays_complete.argtypes = [vp]
     lib.mpmc_b200_get_counters.argtypes = [vp, C.POINTER(Counters)]
     lib.mpmc_b200_phase_ms.argtypes = [vp, C.c_char_p, dp]
     lib.mpmc_b200_measure_fp64_peak.argtypes = [vp, dp]
@@ -328,7 +329,7 @@ ABI_SYMBOLS = [
     "mpmc_b200_energy", "mpmc_b200_polar", "mpmc_b200_energy_enqueue", "mpmc_b200_energy_finish",
     "mpmc_b200_polar_stage", "mpmc_b200_uses_symmetric_contraction", "mpmc_b200_uses_cluster_field",
     "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
-    "mpmc_b200_get_atom_arrays",
+    "mpmc_b200_get_atom_arrays", "mpmc_b200_atom_arrays_complete",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak",
 ]
 
@@ -407,6 +408,9 @@ class Engine:
     def uses_symmetric_contraction(self) -> bool:
         return bool(self.lib.mpmc_b200_uses_symmetric_contraction(self._ctx))
 
+    def atom_arrays_complete(self) -> bool:
+        return bool(self.lib.mpmc_b200_atom_arrays_complete(self._ctx))
+
     def uses_cluster_field(self) -> bool:
         return bool(self.lib.mpmc_b200_uses_cluster_field(self._ctx))
 
@@ -425,11 +429,14 @@ class Engine:
         self._check(self.lib.mpmc_b200_shard_field_rows(self._ctx, C.byref(b), C.byref(e), C.byref(npad)))
         return b.value, e.value, npad.value
 
-    def atom_arrays(self) -> dict:
+    def atom_arrays(self, out: Optional[dict] = None) -> dict:
+        """Per-atom results in reference list order.  `out` (a dict returned by an earlier call for the
+        same atom count) is refilled in place, like the write-back buffers a C caller keeps."""
         n = self.n
-        out = {k: np.zeros((n, 3)) for k in ("mu", "ef_static", "ef_induced", "ef_induced_change")}
-        out["dipole_rrms"] = np.zeros(n)
-        out["rank_metric"] = np.zeros(n)
+        if out is None or out["dipole_rrms"].shape[0] != n:
+            out = {k: np.empty((n, 3)) for k in ("mu", "ef_static", "ef_induced", "ef_induced_change")}
+            out["dipole_rrms"] = np.empty(n)
+            out["rank_metric"] = np.empty(n)
         self._check(self.lib.mpmc_b200_get_atom_arrays(self._ctx, _dp(out["mu"]), _dp(out["ef_static"]),
                                                        _dp(out["ef_induced"]), _dp(out["ef_induced_change"]),
                                                        _dp(out["dipole_rrms"]), _dp(out["rank_metric"])))

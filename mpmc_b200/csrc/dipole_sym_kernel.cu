@@ -111,6 +111,8 @@ struct SymArgs {
     int tile_begin;  // first I super tile of this launch (gridDim.x follow)
     int K;           // S/2: offsets 0..K
     int kper;        // offsets per gridDim.y slice
+    int hsplit;      // 1: a CTA walks both halves of the J super tile; 2: gridDim.z = 2, one half each (finer grain
+                     // for the short launches of a sharded run, where the last wave would otherwise cost ~10 %)
     const double *x, *y, *z, *aux;
     const int* mol;
     const double* mu;    // [3][np]
@@ -283,8 +285,9 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
         if (kk > 0 && 2 * kk == S && I >= kk) continue;  // even S: the half-way offset belongs to I < S/2
         int J = I + kk;
         if (J >= S) J -= S;
+        const int h0 = a.hsplit == 2 ? (int)blockIdx.z : 0, h1 = a.hsplit == 2 ? (int)blockIdx.z + 1 : 2;
 #pragma unroll 1
-        for (int half = 0; half < 2; half++) {
+        for (int half = h0; half < h1; half++) {
             const int jb = J * STILE + half * TILE;  // first atom of this half
             __syncthreads();
             {
@@ -372,7 +375,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
             }
         }
     }
-    double* e = a.epartI + (size_t)blockIdx.y * 3 * np;
+    double* e = a.epartI + (size_t)(blockIdx.y * a.hsplit + blockIdx.z) * 3 * np;
 #pragma unroll
     for (int u = 0; u < 2; u++) {
         const int i = ia + 32 * u;
@@ -545,8 +548,16 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
     a.cbox = cbox;
     a.epartI = epartI;
     a.epartJ = epartJ;
+    int sms = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    a.hsplit = ((long long)ntile * ysplits < 8LL * SYM_MINB * sms) ? 2 : 1;  // fewer than 8 waves: split the J halves
+    if (const char* v = getenv("MPMC_B200_SYM_HSPLIT")) a.hsplit = atoi(v) == 2 ? 2 : 1;
     if (ntile > 0) {
-        dim3 grid(ntile, ysplits);
+        dim3 grid(ntile, ysplits, a.hsplit);
 #define LAUNCH(ORTHO, DAMP, WF, FE) dipole_sym_kernel<ORTHO, DAMP, WF, FE><<<grid, TILE, 0, s>>>(c, k, a)
 #define DISPATCH(ORTHO)                                                         \
     if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                                 \
@@ -571,7 +582,7 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
 #undef DISPATCH
 #undef LAUNCH
     }
-    dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, S, K, tile_begin, tile_end, ysplits, epartI, epartJ, esum);
+    dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, S, K, tile_begin, tile_end, ysplits * a.hsplit, epartI, epartJ, esum);
 }
 
 }  // namespace mpmc

@@ -177,12 +177,18 @@ struct mpmc_b200_ctx {
     double* h_scalars = nullptr;  // pinned
     double* h_stage = nullptr;    // pinned staging for positions
     size_t h_stage_cap = 0;
+    DevBuf<double> wb;            // write-back image (writeback_kernel), 14 n doubles
+    double* h_wb = nullptr;       // pinned
+    size_t h_wb_cap = 0;
 
     // host-side analytic terms
     double lrc_pair = 0, lrc_self = 0, es_self = 0;
     bool analytic_dirty = true;
     bool subsets_stale = false;
 
+    cudaStream_t side = nullptr;  // K1 / K2 overlap with the polarization solve
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool side_active = false;
     cudaEvent_t ev[PH_COUNT][2];
     bool ev_used[PH_COUNT] = {false, false, false, false, false};
     float phase_ms[PH_COUNT] = {0, 0, 0, 0, 0};
@@ -274,6 +280,50 @@ __global__ void reset_dipoles_kernel(int n, int np, const double* __restrict__ a
     for (int c = 0; c < 3; c++) {
         mu[c * np + i] = alpha[i] * es[c * np + i];
         eic[c * np + i] = 0.0;
+    }
+}
+
+// What polar() leaves in atom_t, assembled on the device in the caller's layout (list order, [n][3]):
+// out = mu | ef_static | ef_induced | ef_induced_change | dipole_rrms | rank_metric  (14 n doubles, zero filled
+// beforehand).  Packed rows [own_b, own_e) carry the row-owned arrays; mu (and everything when own_b..own_e is
+// the whole range) is complete.  One D2H copy of the result replaces six staged ones + host scatter loops.
+__global__ void writeback_kernel(int n, int np, const double* __restrict__ ef_static, int n_pol, int pp,
+                                 const int* __restrict__ pol_idx, const double* __restrict__ mu,
+                                 const double* __restrict__ eind, const double* __restrict__ eic,
+                                 const double* __restrict__ rrms, const double* __restrict__ rank_metric, int own_b,
+                                 int own_e, int n_np, int qp, const int* __restrict__ np_idx,
+                                 const double* __restrict__ eind_np, const double* __restrict__ eic_np,
+                                 double* __restrict__ out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    double* o_mu = out;
+    double* o_es = out + 3 * (size_t)n;
+    double* o_ei = out + 6 * (size_t)n;
+    double* o_eic = out + 9 * (size_t)n;
+    double* o_rr = out + 12 * (size_t)n;
+    double* o_rk = out + 13 * (size_t)n;
+    if (t < n)
+        for (int d = 0; d < 3; d++) o_es[3 * (size_t)t + d] = ef_static[(size_t)d * np + t];
+    if (t < n_pol) {
+        const size_t g = pol_idx[t];
+        const bool own = t >= own_b && t < own_e;
+        for (int d = 0; d < 3; d++) {
+            o_mu[3 * g + d] = mu[(size_t)d * pp + t];
+            if (own) {
+                o_ei[3 * g + d] = eind[(size_t)d * pp + t];
+                o_eic[3 * g + d] = eic[(size_t)d * pp + t];
+            }
+        }
+        if (own) {
+            o_rr[g] = rrms[t];
+            o_rk[g] = rank_metric[t];
+        }
+    }
+    if (t < n_np && (eind_np || eic_np)) {
+        const size_t g = np_idx[t];
+        for (int d = 0; d < 3; d++) {
+            if (eind_np) o_ei[3 * g + d] = eind_np[(size_t)d * qp + t];
+            if (eic_np) o_eic[3 * g + d] = eic_np[(size_t)d * qp + t];
+        }
     }
 }
 
@@ -703,7 +753,7 @@ static int repack(Ctx* c) {
         int per_sm = 48;  // measured on M4: 16 -> 48 CTAs per SM removes most of the last-wave tail
         if (const char* v = getenv("MPMC_B200_SYM_CTAS_PER_SM")) per_sm = std::max(1, atoi(v));
         c->sym_ysplits = std::max(1, std::min(K1, (per_sm * sms + own_tiles - 1) / own_tiles));
-        if (c->cbox.ensure((size_t)6 * (pp / 32)) || c->sym_partI.ensure((size_t)c->sym_ysplits * 3 * pp) ||
+        if (c->cbox.ensure((size_t)6 * (pp / 32)) || c->sym_partI.ensure((size_t)2 * c->sym_ysplits * 3 * pp) ||
             c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
             FAIL(11, "cudaMalloc failed");
     }
@@ -723,11 +773,19 @@ static void shard_range(int total_units, int rank, int world, int& b, int& e) {
     e = (int)((long long)total_units * (rank + 1) / world);
 }
 
-static void phase_begin(Ctx* c, Phase p) {
-    cudaEventRecord(c->ev[p][0], c->stream);
+static void phase_begin(Ctx* c, Phase p, cudaStream_t st = nullptr) {
+    cudaEventRecord(c->ev[p][0], st ? st : c->stream);
     c->ev_used[p] = true;
 }
-static void phase_end(Ctx* c, Phase p) { cudaEventRecord(c->ev[p][1], c->stream); }
+static void phase_end(Ctx* c, Phase p, cudaStream_t st = nullptr) { cudaEventRecord(c->ev[p][1], st ? st : c->stream); }
+
+// The pair (K1) and reciprocal (K2) energies do not feed the polarization solve: they run on a side stream
+// forked from the engine's stream and are joined before the evaluation's results are read.
+static void join_side(Ctx* c) {
+    if (!c->side_active) return;
+    cudaStreamWaitEvent(c->stream, c->ev_join, 0);
+    c->side_active = false;
+}
 
 // bracket one K4 launch with its own event pair (at most 160 per evaluation are timed)
 static void kev_mark(Ctx* c) {
@@ -804,7 +862,8 @@ static int check_supported(const mpmc_b200_params& P) {
 
 // ---- reciprocal sum over a subset; leaves S(k) in c->sf and (optionally) the energy in a scalar slot
 static int run_structure_factor(Ctx* c, const Subset& sub, const DevBuf<double>& weight, double scale, double* energy_slot,
-                                bool sharded) {
+                                bool sharded, cudaStream_t st = nullptr) {
+    if (!st) st = c->stream;
     KVecDev kv;
     kv.nk = c->nk;
     kv.kmax = c->P.ewald_kmax;
@@ -823,11 +882,10 @@ static int run_structure_factor(Ctx* c, const Subset& sub, const DevBuf<double>&
     if (sharded) shard_range(c->nk, c->rank, c->world, kb, ke);
     if (c->sf_partial.ensure((size_t)std::max(mine, 1) * 2 * std::max(c->nk, 1))) FAIL(11, "cudaMalloc failed");
     if (c->nk > 0 && sub.n > 0 && mine > 0) {
-        launch_recip_sf(make_cell(c->P), sub.dev(), kv, cb, ce, apc, c->sf_partial.p, c->stream);
+        launch_recip_sf(make_cell(c->P), sub.dev(), kv, cb, ce, apc, c->sf_partial.p, st);
         c->launches++;
     }
-    launch_recip_finish(kv, c->sf_partial.p, (c->nk > 0 && sub.n > 0) ? mine : 0, scale, c->sf.p, energy_slot, kb, ke,
-                        c->stream);
+    launch_recip_finish(kv, c->sf_partial.p, (c->nk > 0 && sub.n > 0) ? mine : 0, scale, c->sf.p, energy_slot, kb, ke, st);
     c->launches++;
     CU(cudaGetLastError());
     return 0;
@@ -1397,7 +1455,26 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
     const bool ortho = is_ortho(P);
 
     if (with_pair_part) {
-        phase_begin(c, PH_PAIR);
+        // fork: with polarization on (and nothing that needs the pair result on the host first), K1 + K2 run on
+        // the side stream while the static field and the dipole solve proceed on the engine's stream
+        static const bool overlap_env = [] { const char* v = getenv("MPMC_B200_OVERLAP"); return !(v && v[0] == '0'); }();
+        const bool will_polar = P.polarization && !P.rd_only && (with_polar_part || c->world > 1);
+        const bool overlap = overlap_env && will_polar && !P.cavity_autoreject_absolute && !P.polar_ewald &&
+                             !P.polar_ewald_full && c->use_clusters && c->side != nullptr;
+        cudaStream_t ps = st;
+        if (c->use_clusters) {
+            // cluster boxes of the sorted image (this evaluation's positions): read by K1 and by K3
+            const SubsetDev sd = c->sorted.dev();
+            launch_cluster_boxes(cell, ortho, sd, sd.cbox, st);
+            c->boxes_fresh = true;
+            c->launches++;
+        }
+        if (overlap) {
+            CU(cudaEventRecord(c->ev_fork, st));
+            CU(cudaStreamWaitEvent(c->side, c->ev_fork, 0));
+            ps = c->side;
+        }
+        phase_begin(c, PH_PAIR, ps);
         PairOpts po;
         po.ewald_alpha = P.ewald_alpha;
         po.temperature = P.temperature;
@@ -1405,16 +1482,14 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
         po.mixing = P.mixing;
         po.rd_only = P.rd_only;
         if (c->use_clusters) {
-            // cluster boxes of the sorted image (this evaluation's positions), then K1 over this shard's i-clusters
+            // K1 over this shard's i-clusters
             const SubsetDev sd = c->sorted.dev();
-            launch_cluster_boxes(cell, ortho, sd, sd.cbox, st);
-            c->boxes_fresh = true;
             int cb, ce;
             shard_range(c->sorted.n_pad / 32, c->rank, c->world, cb, ce);
             const double cull = std::max(P.cutoff, P.cavity_autoreject_absolute ? P.cavity_autoreject_scale : 0.0) + 1e-6;
-            launch_pair_energy_clusters(cell, ortho, sd, po, cb, ce, c->pair_kslices, cull, c->pair_part.p, c->pair_stride, st);
+            launch_pair_energy_clusters(cell, ortho, sd, po, cb, ce, c->pair_kslices, cull, c->pair_part.p, c->pair_stride, ps);
             const int cols = pair_cluster_columns(c->sorted.n_pad, cb, ce, c->pair_kslices);
-            launch_pair_reduce(c->pair_part.p, std::max(cols, 0), c->pair_stride, c->scalars.p + S_PAIR, st);
+            launch_pair_reduce(c->pair_part.p, std::max(cols, 0), c->pair_stride, c->scalars.p + S_PAIR, ps);
             // intramolecular erf term (coulombic.c:176-183), list-order rows of this shard; overwrites slot 2
             int rb, re;
             shard_range(c->n_pad / TILE, c->rank, c->world, rb, re);
@@ -1422,21 +1497,21 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
             re = std::min(re * TILE, c->n);
             if (!P.rd_only) {
                 launch_intra_erf(atoms_dev(c), c->follow.p, P.ewald_alpha, rb, std::max(re, rb), c->intra_part.p,
-                                 c->scalars.p + S_PAIR + 2, st);
+                                 c->scalars.p + S_PAIR + 2, ps);
                 c->launches += 2;
             }
-            c->launches += 3;
+            c->launches += 2;
         } else {
-        int tb, te;
+            int tb, te;
             shard_range(c->ntiles, c->rank, c->world, tb, te);
             if (te > tb) {
-                launch_pair_energy(cell, ortho, atoms_dev(c), po, c->tiles.p + tb, te - tb, c->pair_part.p, c->pair_stride, st);
+                launch_pair_energy(cell, ortho, atoms_dev(c), po, c->tiles.p + tb, te - tb, c->pair_part.p, c->pair_stride, ps);
                 c->launches++;
             }
-            launch_pair_reduce(c->pair_part.p, std::max(te - tb, 0), c->pair_stride, c->scalars.p + S_PAIR, st);
+            launch_pair_reduce(c->pair_part.p, std::max(te - tb, 0), c->pair_stride, c->scalars.p + S_PAIR, ps);
             c->launches++;
         }
-        phase_end(c, PH_PAIR);
+        phase_end(c, PH_PAIR, ps);
         CU(cudaGetLastError());
 
         if (P.cavity_autoreject_absolute) {  // energy.c:99-102: a bad contact skips every other term
@@ -1450,11 +1525,15 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
             }
         }
         if (!P.rd_only) {
-            phase_begin(c, PH_RECIP);
+            phase_begin(c, PH_RECIP, ps);
             c->cnt.kvectors = c->nk;
             c->cnt.recip_atoms = c->recip.n;
-            if (run_structure_factor(c, c->recip, c->kweight, 4.0 * M_PI / P.volume, c->scalars.p + S_RECIP, true)) return 10;
-            phase_end(c, PH_RECIP);
+            if (run_structure_factor(c, c->recip, c->kweight, 4.0 * M_PI / P.volume, c->scalars.p + S_RECIP, true, ps)) return 10;
+            phase_end(c, PH_RECIP, ps);
+        }
+        if (overlap) {
+            CU(cudaEventRecord(c->ev_join, c->side));
+            c->side_active = true;
         }
     }
     c->last_had_polar = false;
@@ -1462,6 +1541,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
         if (enqueue_polar(c)) return 10;
         c->last_had_polar = true;
     }
+    if (with_polar_part || !(P.polarization && !P.rd_only)) join_side(c);  // sharded runs join in STAGE_ENERGY
     phase_end(c, PH_TOTAL);
     c->pending = true;
     return 0;
@@ -1471,6 +1551,7 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     if (!c->pending) FAIL(2, "no evaluation pending");
     const mpmc_b200_params& P = c->P;
     cudaStream_t st = c->stream;
+    join_side(c);
     CU(cudaMemcpyAsync(c->h_scalars, c->scalars.p, sizeof(double) * 32, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     c->pending = false;
@@ -1555,6 +1636,9 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         CU(cudaEventCreate(&c->ev[p][0]));
         CU(cudaEventCreate(&c->ev[p][1]));
     }
+    CU(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     if (c->scalars.ensure(64)) FAIL(11, "cudaMalloc failed");
     CU(cudaMallocHost(&c->h_scalars, sizeof(double) * 64));
     *out = c;
@@ -1565,6 +1649,12 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->side) {
+        cudaStreamSynchronize(c->side);
+        cudaStreamDestroy(c->side);
+    }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     for (int p = 0; p < PH_COUNT; p++) {
         cudaEventDestroy(c->ev[p][0]);
         cudaEventDestroy(c->ev[p][1]);
@@ -1583,12 +1673,15 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     c->pol.release();
     c->nonpol.release();
     c->eic_np.release();
+    c->eind_np.release();
+    c->wb.release();
     c->gs.release();
     c->sorted.release();
     c->follow.release();
     c->intra_part.release();
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->h_wb) cudaFreeHost(c->h_wb);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -1596,6 +1689,8 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
 int mpmc_b200_set_stream(mpmc_b200_ctx* c, void* cuda_stream) {
     if (!c) FAIL(1, "null ctx");
     CU(cudaStreamSynchronize(c->stream));
+    if (c->side) CU(cudaStreamSynchronize(c->side));
+    c->side_active = false;
     if (c->own_stream) cudaStreamDestroy(c->stream);
     if (cuda_stream) {
         c->stream = (cudaStream_t)cuda_stream;
@@ -1610,7 +1705,8 @@ int mpmc_b200_set_stream(mpmc_b200_ctx* c, void* cuda_stream) {
 int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
     if (!c || !p) FAIL(1, "null argument");
     const bool repack_needed = c->have_atoms && (p->damp_type != c->P.damp_type || p->polar_gs != c->P.polar_gs ||
-                                                  p->polar_gs_ranked != c->P.polar_gs_ranked);
+                                                  p->polar_gs_ranked != c->P.polar_gs_ranked ||
+                                                  p->polar_ewald_full != c->P.polar_ewald_full);
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;
@@ -1783,6 +1879,7 @@ int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
             phase_end(c, PH_DIPOLE);
             c->pending_iterations = iteration;
             if (polar_energy_partial(c)) return 10;
+            join_side(c);
             phase_end(c, PH_TOTAL);
             c->pending = true;
             return 0;
@@ -1836,60 +1933,50 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
     if (!c->have_atoms) FAIL(2, "no atoms");
     CU(cudaSetDevice(c->device));
     const int n = c->n, np = c->n_pad, pp = c->pol.n_pad;
-    std::vector<double> buf((size_t)3 * std::max(np, pp));
-    // sharded runs: mu is complete on every rank; the other arrays are reported for this rank's rows only
-    // (zero elsewhere) so that the caller's sum over ranks reassembles them
+    if (n <= 0) return 0;
+    // Sharded runs: mu and ef_static are complete on every rank.  With the symmetric contraction every rank
+    // also holds the complete E_ind / rrms (all-reduced field, every rank updates every row); in the row form
+    // the row-owned arrays are reported for this rank's rows only (zero elsewhere) and the caller sums over ranks.
     int kb = 0, ke = c->pol.n;
-    if (c->world > 1) {
+    if (c->world > 1 && !mpmc_b200_atom_arrays_complete(c)) {
         int tb, te;
         shard_range(pp / TILE, c->rank, c->world, tb, te);
         kb = tb * TILE;
         ke = std::min(te * TILE, c->pol.n);
     }
-    auto scatter3 = [&](const DevBuf<double>& d, double* out, bool own_only = true) -> int {
-        if (!out) return 0;
-        CU(cudaMemcpyAsync(buf.data(), d.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        std::fill(out, out + 3 * (size_t)n, 0.0);
-        for (int k = own_only ? kb : 0; k < (own_only ? ke : c->pol.n); k++) {
-            const int g = c->pol.idx[k];
-            for (int d3 = 0; d3 < 3; d3++) out[3 * g + d3] = buf[(size_t)d3 * pp + k];
-        }
-        return 0;
-    };
-    if (scatter3(c->mu, mu, false) || scatter3(c->eind, ef_induced) || scatter3(c->eic, ef_induced_change)) return 10;
-    if (ef_induced_change && c->eic_np_valid && c->nonpol.n > 0) {
-        const int qp = c->nonpol.n_pad;
-        std::vector<double> nb((size_t)3 * qp);
-        CU(cudaMemcpyAsync(nb.data(), c->eic_np.p, sizeof(double) * 3 * qp, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        for (int k = 0; k < c->nonpol.n; k++)
-            for (int d3 = 0; d3 < 3; d3++) ef_induced_change[3 * c->nonpol.idx[k] + d3] = nb[(size_t)d3 * qp + k];
+    const size_t total = (size_t)14 * n;
+    if (c->wb.ensure(total)) FAIL(11, "cudaMalloc failed");
+    if (c->h_wb_cap < total) {
+        if (c->h_wb) cudaFreeHost(c->h_wb);
+        c->h_wb = nullptr;
+        c->h_wb_cap = total + total / 4;
+        CU(cudaMallocHost(&c->h_wb, sizeof(double) * c->h_wb_cap));
     }
-    if (ef_induced && c->eind_np_valid && c->nonpol.n > 0) {
-        const int qp = c->nonpol.n_pad;
-        std::vector<double> nb((size_t)3 * qp);
-        CU(cudaMemcpyAsync(nb.data(), c->eind_np.p, sizeof(double) * 3 * qp, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        for (int k = 0; k < c->nonpol.n; k++)
-            for (int d3 = 0; d3 < 3; d3++) ef_induced[3 * c->nonpol.idx[k] + d3] = nb[(size_t)d3 * qp + k];
-    }
-    if (ef_static) {
-        CU(cudaMemcpyAsync(buf.data(), c->ef_static.p, sizeof(double) * 3 * np, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        for (int i = 0; i < n; i++)
-            for (int d3 = 0; d3 < 3; d3++) ef_static[3 * i + d3] = buf[(size_t)d3 * np + i];
-    }
-    auto scatter1 = [&](const DevBuf<double>& d, double* out) -> int {
-        if (!out) return 0;
-        CU(cudaMemcpyAsync(buf.data(), d.p, sizeof(double) * pp, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        std::fill(out, out + n, 0.0);
-        for (int k = kb; k < ke; k++) out[c->pol.idx[k]] = buf[k];
-        return 0;
-    };
-    if (scatter1(c->rrms, dipole_rrms) || scatter1(c->rank_packed, rank_metric)) return 10;
+    cudaStream_t st = c->stream;
+    CU(cudaMemsetAsync(c->wb.p, 0, sizeof(double) * total, st));
+    const int m = std::max(n, std::max(c->pol.n, c->nonpol.n));
+    writeback_kernel<<<(m + 255) / 256, 256, 0, st>>>(
+        n, np, c->ef_static.p, c->pol.n, pp, c->pol.didx.p, c->mu.p, c->eind.p, c->eic.p, c->rrms.p, c->rank_packed.p, kb, ke,
+        c->nonpol.n, c->nonpol.n_pad, c->nonpol.didx.p, c->eind_np_valid ? c->eind_np.p : nullptr,
+        c->eic_np_valid ? c->eic_np.p : nullptr, c->wb.p);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(c->h_wb, c->wb.p, sizeof(double) * total, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const double* h = c->h_wb;
+    if (mu) memcpy(mu, h, sizeof(double) * 3 * n);
+    if (ef_static) memcpy(ef_static, h + 3 * (size_t)n, sizeof(double) * 3 * n);
+    if (ef_induced) memcpy(ef_induced, h + 6 * (size_t)n, sizeof(double) * 3 * n);
+    if (ef_induced_change) memcpy(ef_induced_change, h + 9 * (size_t)n, sizeof(double) * 3 * n);
+    if (dipole_rrms) memcpy(dipole_rrms, h + 12 * (size_t)n, sizeof(double) * n);
+    if (rank_metric) memcpy(rank_metric, h + 13 * (size_t)n, sizeof(double) * n);
     return 0;
+}
+
+int mpmc_b200_atom_arrays_complete(mpmc_b200_ctx* c) {
+    if (!c) return 0;
+    if (c->world <= 1) return 1;
+    const bool gs = c->P.polar_gs || c->P.polar_gs_ranked;
+    return (c->use_sym && !gs) ? 1 : 0;
 }
 
 int mpmc_b200_get_counters(mpmc_b200_ctx* c, mpmc_b200_counters* out) {

@@ -129,17 +129,20 @@ __global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a
                                                              int clus_end, double cull2, int accumulate,
                                                              double* __restrict__ ef, int ef_stride,
                                                              double* __restrict__ count_part) {
+    // One CTA per i-cluster: its four warps scan interleaved batches of j-clusters (a warp's serial scan is the
+    // critical path of this latency-bound kernel) and their partial fields are added in warp order.
     __shared__ FieldRec rec[4][32];
+    __shared__ double sred[4][4][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int ci = clus_begin + blockIdx.x * 4 + w;
-    if (ci >= clus_end) return;  // whole warp; no block-level barrier below
+    const int ci = clus_begin + blockIdx.x;
+    if (ci >= clus_end) return;  // whole CTA
     const int nclus = a.n_pad >> 5;
     const int i = ci * 32 + lane;
     const double xi = a.x[i], yi = a.y[i], zi = a.z[i], qi = a.q[i];
     const int moli = a.mol[i], fli = a.flags[i];
     double ex = 0.0, ey = 0.0, ez = 0.0;
     int cnt = 0;
-    for (int kb = 0; kb < nclus; kb += 32) {
+    for (int kb = w * 32; kb < nclus; kb += 128) {
         const int cj = kb + lane;
         bool pass = cj < nclus;
         if (pass && cull2 > 0.0) pass = cluster_gap2(box, a.cbox, nclus, ci, a.cbox, nclus, cj) <= cull2;
@@ -169,6 +172,16 @@ __global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a
             }
         }
     }
+    sred[w][0][lane] = ex;
+    sred[w][1][lane] = ey;
+    sred[w][2][lane] = ez;
+    sred[w][3][lane] = (double)cnt;
+    __syncthreads();
+    if (w != 0) return;
+    ex = ((sred[0][0][lane] + sred[1][0][lane]) + sred[2][0][lane]) + sred[3][0][lane];
+    ey = ((sred[0][1][lane] + sred[1][1][lane]) + sred[2][1][lane]) + sred[3][1][lane];
+    ez = ((sred[0][2][lane] + sred[1][2][lane]) + sred[2][2][lane]) + sred[3][2][lane];
+    const double cntd = ((sred[0][3][lane] + sred[1][3][lane]) + sred[2][3][lane]) + sred[3][3][lane];
     if (fli & F_VALID) {
         const int g = a.idx[i];
         if (accumulate) {
@@ -182,7 +195,7 @@ __global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a
         }
     }
     if (count_part) {
-        const double v = warp_sum((double)cnt);
+        const double v = warp_sum(cntd);
         if (lane == 0) count_part[ci - clus_begin] = v;
     }
 }
@@ -231,7 +244,7 @@ void launch_static_field_clusters(const Cell& c, bool ortho, const SubsetDev& a,
     if (nown <= 0) return;
     const double cull2 = (ortho && cull > 0.0) ? cull * cull : 0.0;
     const BoxLen box = box_len(c);
-    const int grid = (nown + 3) / 4;
+    const int grid = nown;
 #define LAUNCH(ORTHO, MODE)                                                                                              \
     field_cluster_kernel<ORTHO, MODE><<<grid, TILE, 0, s>>>(c, a, o, box, clus_begin, clus_end, cull2, accumulate ? 1 : 0, ef, \
                                                             ef_stride, count_part)

@@ -108,7 +108,7 @@ void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, co
                             const double* mu, int row_begin, int row_end, double* out, cudaStream_t s);
 // Symmetric form of the contraction (dipole_sym_kernel.cu): T_ij computed once per unordered pair and
 // applied in both directions.  I super tiles (256 atoms) [tile_begin, tile_end) x offsets 0..S/2 (split in `ysplits` slices);
-// partial rows: epartI [ysplits][3][n_pad], epartJ [dipole_sym_partial_rows(n_pad)][3][n_pad];
+// partial rows: epartI [2 * ysplits][3][n_pad], epartJ [dipole_sym_partial_rows(n_pad)][3][n_pad];
 // esum [3][n_pad] receives this launch's contribution to E_ind for ALL rows (summed over ranks by the
 // caller in sharded runs).  cbox [6][n_pad/32] from launch_cluster_boxes().
 int dipole_sym_tile();  // atoms per super tile (256): n_pad of the polarizable subset must be a multiple

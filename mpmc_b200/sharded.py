@@ -210,13 +210,25 @@ class ShardedEngine:
         self._last_cnt = cnt
         return out
 
-    def atom_arrays(self) -> dict:
-        arr = self.eng.atom_arrays()
+    def atom_arrays(self, out: Optional[dict] = None) -> dict:
+        arr = self.eng.atom_arrays(out) if out is not None else self.eng.atom_arrays()
         if self.world > 1:
             import torch
 
-            # mu and ef_static are complete on every rank; the rest is reported for the owning
-            # rank's rows and zero elsewhere -> sum over ranks
+            complete = getattr(self.eng, "atom_arrays_complete", lambda: False)()
+            if complete:
+                # symmetric contraction: every rank holds every row; only the palmo rows of the
+                # non-polarizable atoms (write-back only) are computed per rank
+                if self.system.params.polar_palmo:
+                    eic = arr["ef_induced_change"]
+                    if self.rank != 0:
+                        eic[np.asarray(self.system.polarizability) != 0.0] = 0.0
+                    t = torch.from_numpy(eic).to(self.device)
+                    self.ex.all_reduce(t, "sum")
+                    arr["ef_induced_change"] = t.cpu().numpy()
+                return arr
+            # row form: mu and ef_static are complete on every rank; the rest is reported for the
+            # owning rank's rows and zero elsewhere -> sum over ranks
             for k in ("ef_induced", "ef_induced_change", "dipole_rrms"):
                 t = torch.from_numpy(arr[k]).to(self.device)
                 self.ex.all_reduce(t, "sum")
