@@ -206,6 +206,18 @@ int mpmc_b200_uses_symmetric_contraction(mpmc_b200_ctx *ctx);
 /* 1 when the static field is computed per spatial cluster (every rank writes scattered rows of buffer 3: combine
  * with an all-reduce(sum)), 0 for the row-tile form (contiguous row blocks: all-gather) */
 int mpmc_b200_uses_cluster_field(mpmc_b200_ctx *ctx);
+/* Peer-memory exchange of the symmetric contraction's partial sums (optional; one process per GPU on ONE node,
+ * NVLink / NVSwitch peer access).  After set_shard + set_atoms every rank calls peer_export (allocates the
+ * exchange buffer, returns its 64-byte CUDA IPC handle), the caller all-gathers the handles (rank order) and
+ * every rank calls peer_connect.  While peer_active() is 1 the staged protocol needs NO collective between
+ * MPMC_STAGE_PASS and MPMC_STAGE_UPDATE (nor PALMO / PALMO_FINISH): the reduce kernel publishes this rank's
+ * partial field with a flag in every peer's memory and the update kernel waits for all flags, adds the partial
+ * fields in rank order and updates (and, without palmo, commits) the dipoles -- one kernel instead of
+ * all-reduce + update + commit.  peer_active() drops to 0 when the padded polarizable count changes (uVT):
+ * export / connect again or keep using the all-reduce of buffer 4. */
+int mpmc_b200_peer_export(mpmc_b200_ctx *ctx, unsigned char *handle64);
+int mpmc_b200_peer_connect(mpmc_b200_ctx *ctx, int world, const unsigned char *handles /* [world][64] */);
+int mpmc_b200_peer_active(mpmc_b200_ctx *ctx);
 /* atom rows [begin,end) (padded, tile aligned) whose static field this shard computes */
 int mpmc_b200_shard_field_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_atoms_padded);
 /* Raw device pointer + element count of an internal buffer, for collectives

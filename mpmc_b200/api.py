@@ -310,6 +310,9 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_shard_field_rows.argtypes = [vp, ip, ip, ip]
     lib.mpmc_b200_get_atom_arrays.argtypes = [vp, dp, dp, dp, dp, dp, dp]
     lib.mpmc_b200_atom_arrays_complete.argtypes = [vp]
+    lib.mpmc_b200_peer_export.argtypes = [vp, C.c_char_p]
+    lib.mpmc_b200_peer_connect.argtypes = [vp, C.c_int, C.c_char_p]
+    lib.mpmc_b200_peer_active.argtypes = [vp]
     lib.mpmc_b200_get_counters.argtypes = [vp, C.POINTER(Counters)]
     lib.mpmc_b200_phase_ms.argtypes = [vp, C.c_char_p, dp]
     lib.mpmc_b200_measure_fp64_peak.argtypes = [vp, dp]
@@ -330,6 +333,7 @@ ABI_SYMBOLS = [
     "mpmc_b200_polar_stage", "mpmc_b200_uses_symmetric_contraction", "mpmc_b200_uses_cluster_field",
     "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
     "mpmc_b200_get_atom_arrays", "mpmc_b200_atom_arrays_complete",
+    "mpmc_b200_peer_export", "mpmc_b200_peer_connect", "mpmc_b200_peer_active",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak",
 ]
 
@@ -410,6 +414,18 @@ class Engine:
 
     def atom_arrays_complete(self) -> bool:
         return bool(self.lib.mpmc_b200_atom_arrays_complete(self._ctx))
+
+    def peer_export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._check(self.lib.mpmc_b200_peer_export(self._ctx, buf))
+        return buf.raw
+
+    def peer_connect(self, handles) -> None:
+        blob = b"".join(handles)
+        self._check(self.lib.mpmc_b200_peer_connect(self._ctx, len(handles), blob))
+
+    def peer_active(self) -> bool:
+        return bool(self.lib.mpmc_b200_peer_active(self._ctx))
 
     def uses_cluster_field(self) -> bool:
         return bool(self.lib.mpmc_b200_uses_cluster_field(self._ctx))

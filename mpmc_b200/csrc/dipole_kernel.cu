@@ -315,6 +315,84 @@ __global__ void dipole_commit_kernel(int n, int np, UpdateOpts o, const double* 
     }
 }
 
+// ---- peer-memory forms (see PeerWait in kernels.h) ----------------------------------------------
+__device__ __forceinline__ void peer_wait(const PeerWait& pw) {
+    if (threadIdx.x == 0) {
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (int r = 0; r < pw.world; r++) {
+            for (;;) {
+                unsigned long long v;
+                asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(pw.my_flags + r) : "memory");
+                if (v >= pw.seq) break;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 5000000000ull) {  // 5 s: a peer died; fail the evaluation instead of hanging the GPU
+                    *pw.timeout_flag = 1.0;
+                    break;
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) dipole_update_peer_kernel(int n, int np, const double* __restrict__ alpha, UpdateOpts o,
+                                                                 PeerWait pw, const double* __restrict__ es,
+                                                                 double* __restrict__ mu, double* __restrict__ mu_old,
+                                                                 double* __restrict__ mu_new, double* __restrict__ eind,
+                                                                 double* __restrict__ rrms,
+                                                                 unsigned long long* __restrict__ max_err2_bits, int commit) {
+    __shared__ double red[32];
+    peer_wait(pw);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double worst = 0.0;
+    if (i < n) {
+        const double al = alpha[i];
+        double num = 0.0, den = 0.0;
+        const double wold = (commit && o.esor) ? exp(-o.gamma * o.iteration) : 0.0;
+        for (int cdim = 0; cdim < 3; cdim++) {
+            double e = 0.0;
+            for (int r = 0; r < pw.world; r++) e += __ldcv(pw.src[r] + (size_t)cdim * np + i);  // rank order, L1 bypassed
+            eind[cdim * np + i] = e;
+            const double old = mu[cdim * np + i];
+            if (o.save_old) mu_old[cdim * np + i] = old;
+            const double nw = al * (es[cdim * np + i] + e);  // thole_iterative.c:49
+            mu_new[cdim * np + i] = nw;
+            const double d = nw - old;
+            worst = fmax(worst, d * d);
+            num += d * d;
+            den += nw * nw;
+            if (commit) {  // thole_iterative.c:242-252
+                double v = nw;
+                if (o.sor)
+                    v = o.gamma * nw + (1.0 - o.gamma) * old;
+                else if (o.esor)
+                    v = (1.0 - wold) * nw + wold * old;
+                mu[cdim * np + i] = v;
+            }
+        }
+        if (o.do_rrms) {
+            double v = sqrt(num / den);
+            if (!isfinite(v)) v = 0.0;
+            rrms[i] = v;
+        }
+    }
+    worst = block_reduce<2>(worst, red);
+    if (threadIdx.x == 0 && max_err2_bits) atomicMax(max_err2_bits, (unsigned long long)__double_as_longlong(worst));
+}
+
+__global__ void __launch_bounds__(256) palmo_finish_peer_kernel(int n, int np, PeerWait pw, const double* __restrict__ eind,
+                                                                double* __restrict__ eic) {
+    peer_wait(pw);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int cdim = 0; cdim < 3; cdim++) {
+        double e = 0.0;
+        for (int r = 0; r < pw.world; r++) e += __ldcv(pw.src[r] + (size_t)cdim * np + i);
+        eic[cdim * np + i] = -eind[cdim * np + i] + e;  // thole_iterative.c:129-130
+    }
+}
+
 __global__ void palmo_finish_kernel(int n, int np, const double* __restrict__ epart, int jsplits,
                                     const double* __restrict__ eind, double* __restrict__ eic, int row_begin, int row_end) {
     const int i = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
@@ -372,6 +450,19 @@ void launch_dipole_commit(const SubsetDev& pol, const UpdateOpts& o, const doubl
     const int rows = row_end - row_begin;
     if (rows <= 0) return;
     dipole_commit_kernel<<<(rows + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, o, mu_old, mu_new, mu, row_begin, row_end);
+}
+
+void launch_dipole_update_peer(const SubsetDev& pol, const UpdateOpts& o, const PeerWait& pw, const double* es, double* mu,
+                               double* mu_old, double* mu_new, double* eind, double* rrms,
+                               unsigned long long* max_err2_bits, int commit, cudaStream_t s) {
+    if (pol.n_pad <= 0) return;
+    dipole_update_peer_kernel<<<(pol.n_pad + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pol.alpha, o, pw, es, mu, mu_old, mu_new,
+                                                                    eind, rrms, max_err2_bits, commit);
+}
+
+void launch_palmo_finish_peer(const SubsetDev& pol, const PeerWait& pw, const double* eind, double* eic, cudaStream_t s) {
+    if (pol.n_pad <= 0) return;
+    palmo_finish_peer_kernel<<<(pol.n_pad + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pw, eind, eic);
 }
 
 void launch_palmo_finish(const SubsetDev& pol, const double* epart, int jsplits, const double* eind, double* eic,

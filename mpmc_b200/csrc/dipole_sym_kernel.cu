@@ -109,6 +109,7 @@ __device__ __forceinline__ void tensor_coeffs(const SymConsts& k, double r2, dou
 struct SymArgs {
     int n, np, S;    // polarizable atoms, padded, super tiles (np / 256)
     int tile_begin;  // first I super tile of this launch (gridDim.x follow)
+    int L0, L1;      // work items (I, offset slice y), L = I * gridDim.y + y, owned by this launch: [L0, L1)
     int K;           // S/2: offsets 0..K
     int kper;        // offsets per gridDim.y slice
     int hsplit;      // 1: a CTA walks both halves of the J super tile; 2: gridDim.z = 2, one half each (finer grain
@@ -261,6 +262,10 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
     __shared__ double sej[4][3][TILE];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int I = a.tile_begin + blockIdx.x;
+    {
+        const int L = I * (int)gridDim.y + (int)blockIdx.y;
+        if (L < a.L0 || L >= a.L1) return;  // another rank's item (whole CTA, before any barrier)
+    }
     const int np = a.np, S = a.S, nclus = np >> 5;
     // thread t keeps atoms ia and ia + 32: warp w owns the i-clusters 2w and 2w+1 of the super tile
     const int ia = I * STILE + w * 64 + lane;
@@ -388,7 +393,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
 // E_ind[c][i] = sum_y epartI[y][c][i] (if tile(i) was an I tile of this launch) + sum_k epartJ[k-1][c][i] over the
 // offsets k whose I = tile(i) - k was processed.  Fixed order: y ascending, then k ascending in 8 interleaved lanes
 // combined in lane order.  One CTA = 32 consecutive atoms x 3 components x 8 k-lanes.  T = super tiles.
-__global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, int K, int tile_begin, int tile_end, int ysplits,
+__global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, int K, int L0, int L1, int Y, int kper, int hsplit,
                                                                 const double* __restrict__ epartI,
                                                                 const double* __restrict__ epartJ,
                                                                 double* __restrict__ esum) {
@@ -397,8 +402,10 @@ __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, i
     const int i = blockIdx.x * 32 + li;
     const int J = i / STILE;
     double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-    if (lk == 0 && J >= tile_begin && J < tile_end) {
-        for (int y = 0; y < ysplits; y++) {
+    if (lk == 0) {
+        for (int y = 0; y < Y * hsplit; y++) {
+            const int L = J * Y + y / hsplit;
+            if (L < L0 || L >= L1) continue;  // item (J, y) belongs to another rank
             const double* e = epartI + (size_t)y * 3 * np;
             s0 += e[i];
             s1 += e[np + i];
@@ -408,7 +415,8 @@ __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, i
     for (int kk = 1 + lk; kk <= K; kk += 8) {
         int I = J - kk;
         if (I < 0) I += T;
-        if (I < tile_begin || I >= tile_end) continue;
+        const int L = I * Y + kk / kper;
+        if (L < L0 || L >= L1) continue;
         if (2 * kk == T && I >= kk) continue;
         const double* e = epartJ + (size_t)(kk - 1) * 3 * np;
         s0 += e[i];
@@ -426,6 +434,18 @@ __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, i
         for (int q = 1; q < 8; q++) s += part[q][cc][li];
         esum[(size_t)cc * np + i] = s;
     }
+}
+
+// Raises this rank's flag in every peer's memory.  Launched right after dipole_sym_reduce_kernel on the same stream:
+// the kernel boundary makes the partial field complete in this GPU's memory, the system-scope fence + release
+// store order it before the flag for readers on other GPUs.  (A fence in every CTA of the reduce kernel instead of
+// this 3 us launch cost 24 us per contraction at 8 GPUs.)
+__global__ void peer_signal_kernel(PeerSignal sig) {
+    const int r = threadIdx.x;
+    if (r >= sig.world) return;
+    __threadfence_system();
+    unsigned long long* f = sig.flags[r] + sig.me;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(sig.seq) : "memory");
 }
 
 // centre and half extent of every 32-atom cluster (valid atoms only).  Orthorhombic boxes: positions are
@@ -523,10 +543,9 @@ int dipole_sym_partial_rows(int n_pad) {
 }
 
 void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
-                                const double* cbox, int tile_begin, int tile_end, int ysplits, double* epartI,
-                                double* epartJ, double* esum, cudaStream_t s) {
+                                const double* cbox, int rank, int world, int ysplits, double* epartI,
+                                double* epartJ, double* esum, cudaStream_t s, const PeerSignal* sig) {
     const int np = pol.n_pad, S = np / STILE, K = S / 2;
-    const int ntile = tile_end - tile_begin;
     if (S <= 0) return;
     const SymConsts k = make_sym_consts(c, ortho, o);
     if (ysplits < 1) ysplits = 1;
@@ -535,7 +554,6 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
     a.n = pol.n;
     a.np = np;
     a.S = S;
-    a.tile_begin = tile_begin;
     a.K = K;
     a.kper = (K + 1 + ysplits - 1) / ysplits;
     ysplits = (K + 1 + a.kper - 1) / a.kper;
@@ -554,8 +572,18 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
-    a.hsplit = ((long long)ntile * ysplits < 8LL * SYM_MINB * sms) ? 2 : 1;  // fewer than 8 waves: split the J halves
+    // Splitting the J halves over gridDim.z doubles the CTAs of the short launches of a sharded run; measured on
+    // 4 and 8 GPUs (profiles/r01_multi_gpu.md) it LOSES 8 %, so it stays an experiment switch.
+    a.hsplit = 1;
+    (void)sms;
     if (const char* v = getenv("MPMC_B200_SYM_HSPLIT")) a.hsplit = atoi(v) == 2 ? 2 : 1;
+    // Sharding unit: the work item (I tile, offset slice y) -- every item has the same number of pairs, and a
+    // contiguous range of the flattened index balances the ranks to one item (whole I tiles leave 22 vs 23 at 8 GPUs).
+    const long long items = (long long)S * ysplits;
+    a.L0 = (int)(items * rank / world);
+    a.L1 = (int)(items * (rank + 1) / world);
+    a.tile_begin = a.L0 / ysplits;
+    const int ntile = a.L1 > a.L0 ? (a.L1 - 1) / ysplits - a.tile_begin + 1 : 0;
     if (ntile > 0) {
         dim3 grid(ntile, ysplits, a.hsplit);
 #define LAUNCH(ORTHO, DAMP, WF, FE) dipole_sym_kernel<ORTHO, DAMP, WF, FE><<<grid, TILE, 0, s>>>(c, k, a)
@@ -582,7 +610,8 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
 #undef DISPATCH
 #undef LAUNCH
     }
-    dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, S, K, tile_begin, tile_end, ysplits * a.hsplit, epartI, epartJ, esum);
+    dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, S, K, a.L0, a.L1, ysplits, a.kper, a.hsplit, epartI, epartJ, esum);
+    if (sig && sig->world > 1) peer_signal_kernel<<<1, 32, 0, s>>>(*sig);
 }
 
 }  // namespace mpmc

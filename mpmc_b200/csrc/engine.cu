@@ -107,7 +107,8 @@ enum Slot {
     S_ERR = 12,    // max err^2 bits (as unsigned long long)
     S_FIELDCNT = 13,
     S_TOTMU = 16,  // 3: sum of the dipoles (full-Ewald polarization)
-    S_COUNT = 20
+    S_PEER_TIMEOUT = 20,  // set to 1.0 by a peer-wait kernel whose peer never signalled
+    S_COUNT = 21
 };
 
 }  // namespace
@@ -186,6 +187,12 @@ struct mpmc_b200_ctx {
     bool analytic_dirty = true;
     bool subsets_stale = false;
 
+    // peer-memory exchange of the induced-field partial sums (sharded runs; see PeerSignal / PeerWait)
+    unsigned char* peer_local = nullptr;  // one IPC-exported allocation: [2][3][peer_cap] doubles | 16 flags | counter
+    size_t peer_cap = 0;                  // rows per component the allocation was sized for
+    void* peer_base[PEER_MAX] = {nullptr};  // every rank's allocation as seen from this process
+    bool peer_ready = false;
+    unsigned long long peer_seq = 0;
     cudaStream_t side = nullptr;  // K1 / K2 overlap with the polarization solve
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool side_active = false;
@@ -1038,18 +1045,61 @@ static int polar_init(Ctx* c) {
     return 0;
 }
 
+// ---- peer-memory exchange: layout of one rank's exported allocation
+static size_t peer_bytes(size_t cap) { return sizeof(double) * 2 * 3 * cap + sizeof(unsigned long long) * 16 + 64; }
+static double* peer_buf(void* base, size_t cap, int parity) { return reinterpret_cast<double*>(base) + (size_t)parity * 3 * cap; }
+static unsigned long long* peer_flags(void* base, size_t cap) {
+    return reinterpret_cast<unsigned long long*>(reinterpret_cast<double*>(base) + 2 * 3 * cap);
+}
+static bool peer_active(const Ctx* c) {
+    return c->peer_ready && c->world > 1 && c->use_sym && (size_t)c->pol.n_pad == c->peer_cap;
+}
+static void peer_teardown(Ctx* c) {
+    for (int r = 0; r < PEER_MAX; r++) {
+        if (c->peer_base[r] && r != c->rank) cudaIpcCloseMemHandle(c->peer_base[r]);
+        c->peer_base[r] = nullptr;
+    }
+    if (c->peer_local) cudaFree(c->peer_local);
+    c->peer_local = nullptr;
+    c->peer_cap = 0;
+    c->peer_ready = false;
+}
+
+static PeerWait peer_wait_args(Ctx* c) {
+    PeerWait pw;
+    memset(&pw, 0, sizeof(pw));
+    pw.world = c->world;
+    pw.seq = c->peer_seq;
+    pw.my_flags = peer_flags(c->peer_base[c->rank], c->peer_cap);
+    for (int r = 0; r < c->world; r++) pw.src[r] = peer_buf(c->peer_base[r], c->peer_cap, (int)(c->peer_seq & 1ull));
+    pw.timeout_flag = c->scalars.p + S_PEER_TIMEOUT;
+    return pw;
+}
+
 // one Jacobi-family pass over this shard's rows: contract_dipoles + calc_dipole_rrms + the
 // are_we_done_yet residual (thole_iterative.c:27-117); mu itself is not touched
 // symmetric contraction of this shard's I tiles -> c->esum (contribution to E_ind of ALL rows)
 static int polar_contract_sym(Ctx* c) {
     const mpmc_b200_params& P = c->P;
-    int tb, te;
-    shard_range(c->pol.n_pad / dipole_sym_tile(), c->rank, c->world, tb, te);
     kev_mark(c);
-    launch_dipole_contract_sym(make_cell(P), is_ortho(P), c->pol.dev(), dipole_opts(P), c->mu.p, c->cbox.p, tb, te,
+    if (peer_active(c)) {
+        // this rank's contribution goes to its exported buffer (double buffered by the parity of the sequence
+        // number: a peer may still be reading the previous one); peer_signal_kernel then raises the flags
+        c->peer_seq++;
+        PeerSignal sg;
+        memset(&sg, 0, sizeof(sg));
+        sg.world = c->world;
+        sg.me = c->rank;
+        sg.seq = c->peer_seq;
+        for (int r = 0; r < c->world; r++) sg.flags[r] = peer_flags(c->peer_base[r], c->peer_cap);
+        launch_dipole_contract_sym(make_cell(P), is_ortho(P), c->pol.dev(), dipole_opts(P), c->mu.p, c->cbox.p, c->rank, c->world,
+                                   c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p,
+                                   peer_buf(c->peer_base[c->rank], c->peer_cap, (int)(c->peer_seq & 1ull)), c->stream, &sg);
+    } else
+    launch_dipole_contract_sym(make_cell(P), is_ortho(P), c->pol.dev(), dipole_opts(P), c->mu.p, c->cbox.p, c->rank, c->world,
                                c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p, c->esum.p, c->stream);
     kev_mark(c);
-    c->launches += 2;
+    c->launches += peer_active(c) ? 3 : 2;
     c->cnt.contractions += 1;
     CU(cudaGetLastError());
     return 0;
@@ -1061,6 +1111,11 @@ static int polar_update_sym(Ctx* c, int it) {
     unsigned long long* errbits = reinterpret_cast<unsigned long long*>(c->scalars.p + S_ERR);
     const bool precision_mode = P.polar_precision != 0.0;
     if (precision_mode) CU(cudaMemsetAsync(errbits, 0, sizeof(unsigned long long), c->stream));
+    if (peer_active(c))  // all-reduce + update (+ commit unless palmo still needs the old dipoles) in one kernel
+        launch_dipole_update_peer(c->pol.dev(), update_opts(P, it), peer_wait_args(c), c->es.p, c->mu.p, c->mu_old.p,
+                                  c->mu_new.p, c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr,
+                                  P.polar_palmo ? 0 : 1, c->stream);
+    else
     launch_dipole_update(c->pol.dev(), update_opts(P, it), c->esum.p, 1, c->es.p, c->mu.p, c->mu_old.p, c->mu_new.p,
                          c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr, 0, c->pol.n_pad, c->stream);
     c->launches++;
@@ -1113,6 +1168,9 @@ static int palmo_nonpolar_rows(Ctx* c, const SubsetDev& src, const double* mu) {
 
 // palmo_contraction (thole_iterative.c:119-141) with the CURRENT mu, this shard's rows
 static int polar_palmo_finish_sym(Ctx* c) {
+    if (peer_active(c))
+        launch_palmo_finish_peer(c->pol.dev(), peer_wait_args(c), c->eind.p, c->eic.p, c->stream);
+    else
     launch_palmo_finish(c->pol.dev(), c->esum.p, 1, c->eind.p, c->eic.p, 0, c->pol.n_pad, c->stream);
     c->launches++;
     CU(cudaGetLastError());
@@ -1138,6 +1196,7 @@ static int polar_palmo_pass(Ctx* c) {
 
 // mu = new_mu | SOR | ESOR mix (thole_iterative.c:242-252), this shard's rows
 static int polar_commit(Ctx* c, int it) {
+    if (peer_active(c) && !c->P.polar_palmo) return 0;  // committed by dipole_update_peer_kernel
     const bool all = c->use_sym;  // symmetric K4: every rank updates every row (no dipole all-gather)
     launch_dipole_commit(c->pol.dev(), update_opts(c->P, it), c->mu_old.p, c->mu_new.p, c->mu.p, all ? 0 : c->pb,
                          all ? c->pol.n_pad : c->pe, c->stream);
@@ -1567,6 +1626,7 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
         c->contract_ms_sum += ms;
     }
     const double* h = c->h_scalars;
+    if (h[S_PEER_TIMEOUT] != 0.0) FAIL(12, "peer exchange timed out: a rank never published its induced-field partial sums");
     memset(out, 0, sizeof(*out));
     const bool lead = (c->rank == 0);  // host-side analytic terms are added once (rank 0) in sharded runs
     out->min_intermolecular_r = h[S_PAIR + 3];
@@ -1682,6 +1742,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->h_wb) cudaFreeHost(c->h_wb);
+    peer_teardown(c);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -1794,6 +1855,7 @@ int mpmc_b200_set_shard(mpmc_b200_ctx* c, int rank, int world) {
     if (!c) FAIL(1, "null ctx");
     if (world < 1 || rank < 0 || rank >= world) FAIL(1, "bad shard");
     const bool changed = (world != c->world);
+    if (changed || rank != c->rank) peer_teardown(c);  // the exchange buffers belong to the old shard layout
     c->rank = rank;
     c->world = world;
     if (changed && c->have_atoms) {
@@ -1888,6 +1950,52 @@ int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
 }
 
 int mpmc_b200_uses_symmetric_contraction(mpmc_b200_ctx* c) { return (c && c->use_sym) ? 1 : 0; }
+
+// ---- peer-memory exchange set-up (CUDA IPC; one process per GPU on one node)
+int mpmc_b200_peer_export(mpmc_b200_ctx* c, unsigned char* handle64) {
+    if (!c || !handle64) FAIL(1, "null argument");
+    if (!c->have_atoms) FAIL(2, "mpmc_b200_set_atoms has not been called");
+    if (sizeof(cudaIpcMemHandle_t) > 64) FAIL(3, "unexpected cudaIpcMemHandle_t size");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    peer_teardown(c);
+    c->peer_cap = (size_t)c->pol.n_pad;
+    const size_t bytes = peer_bytes(c->peer_cap);
+    CU(cudaMalloc(&c->peer_local, bytes));
+    CU(cudaMemset(c->peer_local, 0, bytes));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, c->peer_local));
+    memset(handle64, 0, 64);
+    memcpy(handle64, &h, sizeof(h));
+    return 0;
+}
+
+int mpmc_b200_peer_connect(mpmc_b200_ctx* c, int world, const unsigned char* handles) {
+    if (!c || !handles) FAIL(1, "null argument");
+    if (world != c->world || world > PEER_MAX) FAIL(1, "peer_connect: world does not match set_shard (or exceeds 8)");
+    if (!c->peer_local) FAIL(2, "mpmc_b200_peer_export has not been called");
+    CU(cudaSetDevice(c->device));
+    for (int r = 0; r < world; r++) {
+        if (r == c->rank) {
+            c->peer_base[r] = c->peer_local;
+            continue;
+        }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + 64 * (size_t)r, sizeof(h));
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            cudaGetLastError();
+            peer_teardown(c);
+            FAIL(13, "cudaIpcOpenMemHandle failed (no peer access between the ranks' GPUs?)");
+        }
+        c->peer_base[r] = p;
+    }
+    c->peer_seq = 0;
+    c->peer_ready = true;
+    return 0;
+}
+
+int mpmc_b200_peer_active(mpmc_b200_ctx* c) { return (c && peer_active(c)) ? 1 : 0; }
 int mpmc_b200_uses_cluster_field(mpmc_b200_ctx* c) { return (c && c->use_clusters) ? 1 : 0; }
 
 int mpmc_b200_shard_field_rows(mpmc_b200_ctx* c, int* begin, int* end, int* n_atoms_padded) {

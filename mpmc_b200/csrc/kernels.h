@@ -107,16 +107,35 @@ void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, con
 void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, const SubsetDev& pol, const DipoleOpts& o,
                             const double* mu, int row_begin, int row_end, double* out, cudaStream_t s);
 // Symmetric form of the contraction (dipole_sym_kernel.cu): T_ij computed once per unordered pair and
-// applied in both directions.  I super tiles (256 atoms) [tile_begin, tile_end) x offsets 0..S/2 (split in `ysplits` slices);
+// applied in both directions.  Work items = (I super tile of 256 atoms) x (slice of the offsets 0..S/2, `ysplits` slices); rank r of
+// `world` takes the r-th contiguous share of the flattened items;
 // partial rows: epartI [2 * ysplits][3][n_pad], epartJ [dipole_sym_partial_rows(n_pad)][3][n_pad];
 // esum [3][n_pad] receives this launch's contribution to E_ind for ALL rows (summed over ranks by the
 // caller in sharded runs).  cbox [6][n_pad/32] from launch_cluster_boxes().
+// Peer-memory exchange of the induced-field partial sums (multi-GPU, one process per GPU): every rank's reduce
+// kernel leaves its contribution to E_ind of ALL rows in a buffer the other ranks can read over NVLink
+// (CUDA IPC), then raises a flag in every peer's memory; the update kernel of each rank waits for all flags and
+// adds the `world` contributions in rank order -- the all-reduce, the field sum and the dipole update are one
+// kernel, and every rank gets bit-identical sums.
+constexpr int PEER_MAX = 8;
+struct PeerSignal {             // producer side (peer_signal_kernel, launched after dipole_sym_reduce_kernel)
+    int world, me;
+    unsigned long long seq;     // flag value to publish
+    unsigned long long* flags[PEER_MAX];  // flags[r] = rank r's flag array (peer pointer); slot `me` is written
+};
+struct PeerWait {               // consumer side (dipole_update_peer_kernel, palmo_finish_peer_kernel)
+    int world;
+    unsigned long long seq;
+    const unsigned long long* my_flags;  // local flag array, slot r written by rank r
+    const double* src[PEER_MAX];         // src[r] = rank r's partial field [3][n_pad] (peer pointer)
+    double* timeout_flag;                // set to 1.0 if a peer never signalled (host turns it into an error)
+};
 int dipole_sym_tile();  // atoms per super tile (256): n_pad of the polarizable subset must be a multiple
 int dipole_sym_partial_rows(int n_pad);
 void launch_cluster_boxes(const Cell& c, bool ortho, const SubsetDev& pol, double* cbox, cudaStream_t s);
 void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
-                                const double* cbox, int tile_begin, int tile_end, int ysplits, double* epartI,
-                                double* epartJ, double* esum, cudaStream_t s);
+                                const double* cbox, int rank, int world, int ysplits, double* epartI,
+                                double* epartJ, double* esum, cudaStream_t s, const PeerSignal* sig = nullptr);
 struct UpdateOpts {
     int sor, esor, save_old, do_rrms;
     double gamma;
@@ -126,6 +145,12 @@ struct UpdateOpts {
 void launch_dipole_update(const SubsetDev& pol, const UpdateOpts& o, const double* epart, int jsplits, const double* es,
                           const double* mu, double* mu_old, double* mu_new, double* eind, double* rrms,
                           unsigned long long* max_err2_bits, int row_begin, int row_end, cudaStream_t s);
+// Peer form: waits for every rank's flag, E_ind = sum_r src[r] (rank order), then the same update; with
+// `commit` the dipoles are committed in the same kernel (Jacobi without palmo).
+void launch_dipole_update_peer(const SubsetDev& pol, const UpdateOpts& o, const PeerWait& pw, const double* es, double* mu,
+                               double* mu_old, double* mu_new, double* eind, double* rrms,
+                               unsigned long long* max_err2_bits, int commit, cudaStream_t s);
+void launch_palmo_finish_peer(const SubsetDev& pol, const PeerWait& pw, const double* eind, double* eic, cudaStream_t s);
 // mu = new_mu | SOR | ESOR mix (src/polarization/thole_iterative.c:242-252)
 void launch_dipole_commit(const SubsetDev& pol, const UpdateOpts& o, const double* mu_old, const double* mu_new,
                           double* mu, int row_begin, int row_end, cudaStream_t s);

@@ -121,6 +121,26 @@ class ShardedEngine:
             self.eng.set_shard(self.rank, self.world)
         self.eng.set_system(s)
         self._views = {}
+        self._connect_peers()
+
+    def _connect_peers(self):
+        """Exchange the CUDA IPC handles of the ranks' exchange buffers (mpmc_b200_peer_export /
+        peer_connect): afterwards the per-iteration all-reduce of the induced field is done by the
+        engine's own update kernel over NVLink peer memory.  MPMC_B200_PEER=0 keeps the NCCL all-reduce."""
+        import os
+
+        eng = self.eng
+        if self.world == 1 or not hasattr(eng, "peer_export") or os.environ.get("MPMC_B200_PEER", "1") == "0":
+            return
+        p = self.system.params
+        if not (p.polarization and not p.rd_only and eng.uses_symmetric_contraction()) or self.world > 8:
+            return
+        import torch.distributed as dist
+
+        handles = [None] * self.world
+        dist.all_gather_object(handles, eng.peer_export(), group=self.ex.group)
+        eng.peer_connect(handles)
+        dist.barrier(group=self.ex.group)
 
     def set_positions(self, first: int, pos: np.ndarray):
         self.eng.set_positions(first, pos)
@@ -163,6 +183,7 @@ class ShardedEngine:
             eng.polar_stage(api.STAGE_INIT)
             mu = self._view(0)
             sym = bool(eng.uses_symmetric_contraction())
+            peer = sym and bool(getattr(eng, "peer_active", lambda: False)())  # exchange inside the update kernel
             if not p.polar_zodid and n_pol > 0:
                 allowed = p.polar_precision * p.polar_precision * DEBYE2SKA * DEBYE2SKA  # thole_iterative.c:106
                 keep = True
@@ -174,7 +195,8 @@ class ShardedEngine:
                         break
                     eng.polar_stage(api.STAGE_PASS, iterations)
                     if sym:
-                        self.ex.all_reduce(self._view(4), "sum")
+                        if not peer:
+                            self.ex.all_reduce(self._view(4), "sum")
                         eng.polar_stage(api.STAGE_UPDATE, iterations)
                     if p.polar_precision == 0.0:
                         keep = iterations != p.polar_max_iter
@@ -186,7 +208,8 @@ class ShardedEngine:
                     if p.polar_palmo and not keep:
                         eng.polar_stage(api.STAGE_PALMO)
                         if sym:
-                            self.ex.all_reduce(self._view(4), "sum")
+                            if not peer:
+                                self.ex.all_reduce(self._view(4), "sum")
                             eng.polar_stage(api.STAGE_PALMO_FINISH)
                     eng.polar_stage(api.STAGE_COMMIT, iterations)
                     if not sym:
@@ -245,5 +268,8 @@ class ShardedEngine:
     def counters_own(self) -> OwnCounters:
         c = self._last_cnt
         b, e, n_pol, _ = self.eng.shard_rows() if c.n_polarizable > 0 else (0, 0, 0, 0)
+        if self.world > 1 and self.eng.uses_symmetric_contraction():
+            # symmetric K4: the (I tile, offset slice) work items are dealt out evenly, 1/world of the pairs each
+            return OwnCounters(pairs_dipole_own=float(n_pol) * max(n_pol - 1, 0) / self.world)
         rows = max(0, min(e, n_pol) - b)
         return OwnCounters(pairs_dipole_own=float(rows) * max(n_pol - 1, 0))

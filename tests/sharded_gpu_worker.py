@@ -44,6 +44,8 @@ def main():
         eng = Engine(local, stream=stream.cuda_stream)
         sh = ShardedEngine(eng, rank, world, stream=stream)
         sh.set_system(s)
+        if rank == 0 and name == "mof_jacobi10":
+            print(f"PEER_ACTIVE={int(eng.peer_active())}", flush=True)
         got = sh.energy()
         got2 = sh.energy()  # a second evaluation must reproduce the first bit for bit
         for k in ("rd", "es_real", "es_recip", "es_self", "coulombic", "polar", "total", "dipole_rrms"):

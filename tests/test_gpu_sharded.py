@@ -11,7 +11,10 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def test_sharded_equals_single_gpu():
+@pytest.mark.parametrize("peer", ["1", "0"])
+def test_sharded_equals_single_gpu(peer):
+    """peer=1: induced-field exchange inside the update kernel over CUDA-IPC peer memory (default);
+    peer=0: NCCL all-reduce between the contraction and the update."""
     import torch
 
     n = torch.cuda.device_count()
@@ -24,5 +27,7 @@ def test_sharded_equals_single_gpu():
     s.close()
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                         "--master-addr", "127.0.0.1", "--master-port", str(port),
-                        os.path.join(ROOT, "tests", "sharded_gpu_worker.py")], capture_output=True, text=True, timeout=900)
+                        os.path.join(ROOT, "tests", "sharded_gpu_worker.py")], capture_output=True, text=True, timeout=900,
+                       env=dict(os.environ, MPMC_B200_PEER=peer))
+    assert f"PEER_ACTIVE={peer}" in r.stdout, r.stdout[-4000:] + r.stderr[-4000:]
     assert r.returncode == 0 and "SHARDED_OK" in r.stdout, r.stdout[-4000:] + r.stderr[-4000:]
