@@ -47,6 +47,10 @@ def build_workload(name: str):
     """Synthetic systems of BASELINE.json's configs."""
     from mpmc_b200 import systems
 
+    if name.endswith("_ewald_full"):  # SURVEY 8f f1: the same system solved with full-Ewald polarization
+        s = build_workload(name[:-len("_ewald_full")])
+        s.params.polar_ewald_full = 1
+        return s
     if name == "mof_h2_63k":  # config 4: MOF supercell + H2, ~63k atoms, full polarizable energy, Jacobi x10
         return systems.mof_h2()
     if name == "mof_h2_42k":
@@ -347,6 +351,17 @@ def own_arm(args):
                 "flops_per_launch": k4_flops, "ms_per_launch": c_ms,
                 "whole_eval_tflops": algorithmic_flops(cnt, fh) / (ms_per_step * 1e-3) / 1e12,
                 "phase_ms": {k: float(np.mean(v)) for k, v in phases.items()}}
+    # fp64-pipe view of the same launch: K4 EXECUTES 41 (far cluster pair, no damping) .. 69 (damped) fp64
+    # instructions per unordered pair (SASS count), far fewer than the 2 x 126 algorithmic flops the
+    # reference's formula implies, which is why `frac` exceeds 1.  One fp64 instruction = 1 lane-op of the
+    # 148 SM x 64 lanes/clk pipe whose DFMA rate (2 flop) is `peak`.
+    if c_ms > 0 and peak_tf > 0:
+        unordered = 0.5 * own.pairs_dipole_own
+        lane_ops_per_s = peak_tf * 1e12 / 2.0
+        roofline["pipe_frac_bounds"] = [41.0 * unordered / (c_ms * 1e-3) / lane_ops_per_s,
+                                        69.0 * unordered / (c_ms * 1e-3) / lane_ops_per_s]
+        roofline["pipe_frac_note"] = ("executed fp64 instr per unordered pair between 41 (all cluster pairs far) and 69 "
+                                      "(all damped); ncu sm__pipe_fp64 utilisation of the same kernel: profiles/")
     prof = os.path.join(ROOT, "profiles", "k4_traffic.json")
     if os.path.exists(prof):
         try:

@@ -61,17 +61,21 @@ __global__ void __launch_bounds__(TILE) induced_real_cluster_kernel(Cell c, Subs
                                                                     const double* __restrict__ cbox, double cull2,
                                                                     const double* __restrict__ mu, int batches_per_slice,
                                                                     double* __restrict__ part) {
+    // One CTA per i-cluster: the four warps scan interleaved batches of 32 j-clusters (a warp's serial scan is the
+    // critical path; ncu of the one-warp-per-cluster form: 13.7 % achieved occupancy, 3.58 ms at 46k atoms) and
+    // their partial fields are added in warp order.
     __shared__ JRec rec[4][32];
+    __shared__ double sred[4][3][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int nclus = a.n_pad >> 5, np = a.n_pad;
-    const int ci = blockIdx.x * 4 + w;
-    if (ci >= nclus) return;  // whole warp; no block-level barrier below
+    const int ci = blockIdx.x;
+    if (ci >= nclus) return;  // whole CTA
     const int i = ci * 32 + lane;
     const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
     double ex = 0.0, ey = 0.0, ez = 0.0;
     const int b0 = blockIdx.y * batches_per_slice * 32;
     const int b1 = min(nclus, b0 + batches_per_slice * 32);
-    for (int kb = b0; kb < b1; kb += 32) {
+    for (int kb = b0 + w * 32; kb < b1; kb += 128) {
         const int cj = kb + lane;
         bool pass = cj < b1;
         if (pass && cull2 > 0.0) pass = cluster_gap2(box, cbox, nclus, ci, cbox, nclus, cj) <= cull2;
@@ -103,10 +107,15 @@ __global__ void __launch_bounds__(TILE) induced_real_cluster_kernel(Cell c, Subs
             }
         }
     }
+    sred[w][0][lane] = ex;
+    sred[w][1][lane] = ey;
+    sred[w][2][lane] = ez;
+    __syncthreads();
+    if (w != 0) return;
     double* out = part + (size_t)blockIdx.y * 3 * np;
-    out[i] = ex;
-    out[np + i] = ey;
-    out[2 * np + i] = ez;
+    out[i] = ((sred[0][0][lane] + sred[1][0][lane]) + sred[2][0][lane]) + sred[3][0][lane];
+    out[np + i] = ((sred[0][1][lane] + sred[1][1][lane]) + sred[2][1][lane]) + sred[3][1][lane];
+    out[2 * np + i] = ((sred[0][2][lane] + sred[1][2][lane]) + sred[2][2][lane]) + sred[3][2][lane];
 }
 
 // Dipole structure factor: P(k) = sum_j (k . mu_j) e^{i k.r_j}  (polar_ewald.c:268-276); same phase
@@ -306,7 +315,7 @@ int launch_induced_real_clusters(const Cell& c, bool ortho, const SubsetDev& pol
     if (jsplits > batches) jsplits = batches;
     const int bps = (batches + jsplits - 1) / jsplits;
     jsplits = (batches + bps - 1) / bps;
-    dim3 grid((nclus + 3) / 4, jsplits);
+    dim3 grid(nclus, jsplits);
     if (ortho)
         induced_real_cluster_kernel<true><<<grid, TILE, 0, s>>>(c, pol, o, box_len(c), cbox, cull2, mu, bps, part);
     else
