@@ -1787,6 +1787,7 @@ int mpmc_b200_set_atoms(mpmc_b200_ctx* c, int n, const double* pos, const double
     if (!c->have_params) FAIL(2, "call mpmc_b200_set_params before mpmc_b200_set_atoms");
     if (n < 0 || (n > 0 && (!pos || !charge || !polarizability || !epsilon || !sigma || !mol_mass || !mol_id || !frozen)))
         FAIL(1, "bad atom arrays");
+    if (n > CULL_MAX_BATCHES * 32 * 32 - 4096) FAIL(3, "more than ~2M atoms: raise CULL_MAX_BATCHES (common.cuh)");
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     c->n = n;

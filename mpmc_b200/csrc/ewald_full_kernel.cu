@@ -73,19 +73,21 @@ __global__ void __launch_bounds__(TILE) induced_real_cluster_kernel(Cell c, Subs
     const int i = ci * 32 + lane;
     const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
     double ex = 0.0, ey = 0.0, ez = 0.0;
-    const int b0 = blockIdx.y * batches_per_slice * 32;
-    const int b1 = min(nclus, b0 + batches_per_slice * 32);
-    for (int kb = b0 + w * 32; kb < b1; kb += 128) {
-        const int cj = kb + lane;
-        bool pass = cj < b1;
-        if (pass && cull2 > 0.0) pass = cluster_gap2(box, cbox, nclus, ci, cbox, nclus, cj) <= cull2;
-        unsigned mask = __ballot_sync(0xffffffffu, pass);
+    __shared__ unsigned smask[CULL_MAX_BATCHES];
+    const int nb_all = (nclus + 31) >> 5;
+    const int b0 = blockIdx.y * batches_per_slice, b1 = min(nb_all, b0 + batches_per_slice);
+    cull_masks(box, cbox, nclus, ci, cull2, b0, b1, smask);
+    int pos = 0;
+    for (int b = b0; b < b1; b++) {
+        unsigned mask = smask[b - b0];
         while (mask) {
-            const int b = __ffs(mask) - 1;
+            const int bit = __ffs(mask) - 1;
             mask &= mask - 1;
+            if (((pos++) & 3) != w) continue;  // warp-uniform
+            const int cj = b * 32 + bit;
             __syncwarp();
             {
-                const int j = (kb + b) * 32 + lane;
+                const int j = cj * 32 + lane;
                 JRec r;
                 r.x = a.x[j];
                 r.y = a.y[j];
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(TILE) induced_real_cluster_kernel(Cell c, Subs
                 rec[w][lane] = r;
             }
             __syncwarp();
-            const bool self_cluster = (kb + b == ci);
+            const bool self_cluster = (cj == ci);
             for (int s = 0; s < 32; s++) {
                 const JRec& r = rec[w][s];
                 if (!r.valid) continue;

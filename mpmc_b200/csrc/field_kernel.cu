@@ -142,17 +142,20 @@ __global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a
     const int moli = a.mol[i], fli = a.flags[i];
     double ex = 0.0, ey = 0.0, ez = 0.0;
     int cnt = 0;
-    for (int kb = w * 32; kb < nclus; kb += 128) {
-        const int cj = kb + lane;
-        bool pass = cj < nclus;
-        if (pass && cull2 > 0.0) pass = cluster_gap2(box, a.cbox, nclus, ci, a.cbox, nclus, cj) <= cull2;
-        unsigned mask = __ballot_sync(0xffffffffu, pass);
+    __shared__ unsigned smask[CULL_MAX_BATCHES];
+    const int nb = min((nclus + 31) >> 5, CULL_MAX_BATCHES);
+    cull_masks(box, a.cbox, nclus, ci, cull2, 0, nb, smask);
+    int pos = 0;
+    for (int b = 0; b < nb; b++) {
+        unsigned mask = smask[b];
         while (mask) {
-            const int b = __ffs(mask) - 1;
+            const int bit = __ffs(mask) - 1;
             mask &= mask - 1;
+            if (((pos++) & 3) != w) continue;  // warp-uniform: every fourth passing cluster is this warp's
+            const int cj = b * 32 + bit;
             __syncwarp();
             {
-                const int j = (kb + b) * 32 + lane;
+                const int j = cj * 32 + lane;
                 FieldRec r;
                 r.x = a.x[j];
                 r.y = a.y[j];
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a
                 rec[w][lane] = r;
             }
             __syncwarp();
-            const bool self_cluster = (kb + b == ci);
+            const bool self_cluster = (cj == ci);
             for (int s = 0; s < 32; s++) {
                 const FieldRec& r = rec[w][s];
                 if (r.q == 0.0) continue;                  // a source without charge adds exact zeros
