@@ -74,6 +74,30 @@ static void *xrealloc(void *p, size_t bytes) {
     return q;
 }
 
+/* MPMC_B200_SHIM_TIMING=1: where a drop-in energy() call spends its host time (printed at exit) */
+#include <time.h>
+static double t_acc[5];
+static long t_calls = 0, t_fast = 0;
+static int t_on = -1;
+static double shim_now(void) {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+static void shim_timing_report(void) {
+    if (t_on == 1 && t_calls > 0)
+        fprintf(stderr,
+                "MPMC_B200_SHIM_TIMING: %ld energy() calls (%ld on the cached-sequence pass); ms per call: host lists %.3f, "
+                "upload %.3f, device energy %.3f, write-back + epilogue %.3f, whole call %.3f\n",
+                t_calls, t_fast, t_acc[0] / t_calls, t_acc[1] / t_calls, t_acc[2] / t_calls, t_acc[3] / t_calls, t_acc[4] / t_calls);
+}
+
+static void shim_timing_init(void) {
+    if (t_on >= 0) return;
+    t_on = getenv("MPMC_B200_SHIM_TIMING") ? 1 : 0;
+    if (t_on) atexit(shim_timing_report);
+}
+
 static void shim_reserve(int n) {
     int cap;
     if (n <= g_cap) return;
@@ -296,22 +320,11 @@ void thole_amatrix(system_t *system) {
 /* ------------------------------------------------------------------------------------------------
  * host lists -> device image
  * ---------------------------------------------------------------------------------------------- */
-static void shim_sync_device(system_t *system) {
+/* flat image of the lists -> n_* arrays (list walk; the fast path of shim_fast_pass() fills the same arrays) */
+static int shim_pack(system_t *system) {
     molecule_t *m;
     atom_t *a;
-    mpmc_b200_params P;
-    int n = 0, molidx = 0, i, same, first, last;
-
-    shim_init();
-    shim_check_supported(system);
-
-    shim_fill_params(system, &P);
-    if (!g_have_params || memcmp(&P, &g_params, sizeof(P)) != 0) {
-        if (mpmc_b200_set_params(g_ctx, &P)) shim_die("set_params");
-        g_params = P;
-        g_have_params = 1;
-    }
-
+    int n = 0, molidx = 0;
     shim_reserve(system->natoms);
     for (m = system->molecules; m; m = m->next, molidx++)
         for (a = m->atoms; a; a = a->next, n++) {
@@ -326,6 +339,23 @@ static void shim_sync_device(system_t *system) {
             n_mol[n] = molidx;
             n_frozen[n] = a->frozen;
         }
+    return n;
+}
+
+/* parameters + the packed image (n atoms in n_*) -> device, sending only what changed */
+static void shim_upload(system_t *system, int n) {
+    mpmc_b200_params P;
+    int i, same, first, last;
+
+    shim_init();
+    shim_check_supported(system);
+
+    shim_fill_params(system, &P);
+    if (!g_have_params || memcmp(&P, &g_params, sizeof(P)) != 0) {
+        if (mpmc_b200_set_params(g_ctx, &P)) shim_die("set_params");
+        g_params = P;
+        g_have_params = 1;
+    }
 
     /* a translation / rotation changes positions only; an insertion, a removal or a restored
      * molecule changes the atom count or the per-atom parameters and needs the full image */
@@ -359,6 +389,101 @@ static void shim_sync_device(system_t *system) {
     }
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Fast path of the O(N) host duties.  The reference's lists are chains of individually allocated 912-byte
+ * atoms: every walk is a chain of dependent cache misses (~5 ms per walk at 64k atoms), and energy() used to
+ * make eight of them (count x2, rebuild_arrays, update_com, wrapall, pack, self points, write-back).  The
+ * pointer sequence is cached after a full walk; later calls check that the lists still are that sequence
+ * (molecule k -> k+1, first atom, atom i -> i+1: independent loads, which the core overlaps) and do count,
+ * COM (pairs.c:364-385), wrapping (output.c:142-183), self points (coulombic.c:103-108) and packing in that one
+ * pass.  Any relinking (uVT insert / remove / restore, replay) fails the check and takes the full walks.
+ * ---------------------------------------------------------------------------------------------- */
+static molecule_t **c_mol = NULL;   /* molecules in list order */
+static atom_t **c_atom = NULL;      /* atoms in list order */
+static int *c_first = NULL;         /* index of a molecule's first atom */
+static int c_nmol = 0, c_natom = 0, c_molcap = 0, c_atomcap = 0, c_valid = 0;
+
+static void shim_cache_topology(system_t *system) {
+    molecule_t *m;
+    atom_t *a;
+    int nm = 0, na = 0;
+    for (m = system->molecules; m; m = m->next) nm++;
+    na = system->natoms;
+    if (nm + 1 > c_molcap) {
+        c_molcap = nm + nm / 4 + 64;
+        c_mol = (molecule_t **)xrealloc(c_mol, sizeof(molecule_t *) * c_molcap);
+        c_first = (int *)xrealloc(c_first, sizeof(int) * c_molcap);
+    }
+    if (na > c_atomcap) {
+        c_atomcap = na + na / 4 + 64;
+        c_atom = (atom_t **)xrealloc(c_atom, sizeof(atom_t *) * c_atomcap);
+    }
+    nm = 0;
+    na = 0;
+    for (m = system->molecules; m; m = m->next) {
+        c_mol[nm] = m;
+        c_first[nm++] = na;
+        for (a = m->atoms; a; a = a->next) c_atom[na++] = a;
+    }
+    c_first[nm] = na;
+    c_nmol = nm;
+    c_natom = na;
+    c_valid = (na == system->natoms);
+}
+
+/* returns the atom count when the cached sequence still is the list (everything done), -1 otherwise */
+static int shim_fast_pass(system_t *system, int es_on) {
+    const pbc_t *pbc = system->pbc;
+    const double self_c = system->ewald_alpha / sqrt(M_PI);
+    int k, i, p, q;
+    if (!c_valid || c_nmol <= 0 || system->molecules != c_mol[0] || !system->atom_array || !system->molecule_array) return -1;
+    shim_reserve(c_natom);
+    for (k = 0; k < c_nmol; k++) {
+        molecule_t *m = c_mol[k];
+        const int b = c_first[k], e = c_first[k + 1];
+        double com[3] = {0, 0, 0}, mass = 0, dimg[3] = {0, 0, 0}, d[3];
+        if (m->next != (k + 1 < c_nmol ? c_mol[k + 1] : NULL) || m->atoms != (e > b ? c_atom[b] : NULL)) return -1;
+        for (i = b; i < e; i++) {
+            const atom_t *a = c_atom[i];
+            if (a->next != (i + 1 < e ? c_atom[i + 1] : NULL)) return -1;
+            mass += a->mass;
+            for (p = 0; p < 3; p++) com[p] += a->mass * a->pos[p];
+        }
+        for (p = 0; p < 3; p++) m->com[p] = 0; /* update_com(): pairs.c:364-385 */
+        if (!(m->spectre || m->target)) {
+            m->mass = mass;
+            for (p = 0; p < 3; p++) m->com[p] = com[p] / mass;
+        }
+        if (!m->frozen) { /* wrapall(): output.c:142-183 */
+            for (p = 0; p < 3; p++) {
+                for (q = 0, d[p] = 0; q < 3; q++) d[p] += pbc->reciprocal_basis[q][p] * m->com[q];
+                d[p] = rint(d[p]);
+            }
+            for (p = 0; p < 3; p++) {
+                for (q = 0, dimg[p] = 0; q < 3; q++) dimg[p] += pbc->basis[q][p] * d[q];
+                m->wrapped_com[p] = dimg[p];
+            }
+        }
+        for (i = b; i < e; i++) {
+            atom_t *a = c_atom[i];
+            for (p = 0; p < 3; p++) {
+                a->wrapped_pos[p] = m->frozen ? a->pos[p] : a->pos[p] - dimg[p];
+                n_pos[3 * i + p] = a->pos[p];
+            }
+            n_q[i] = a->charge;
+            n_alpha[i] = a->polarizability;
+            n_eps[i] = a->epsilon;
+            n_sig[i] = a->sigma;
+            n_mmass[i] = m->mass;
+            n_mol[i] = k;
+            n_frozen[i] = a->frozen;
+            if (es_on && !a->frozen) a->es_self_point_energy = self_c * a->charge * a->charge; /* coulombic.c:103-108 */
+        }
+    }
+    system->natoms = c_natom;
+    return c_natom;
+}
+
 /* what polar() leaves in atom_t (read by write_dipole / write_field, src/io/output.c:1029-1088) */
 static void shim_write_back_atoms(system_t *system) {
     molecule_t *m;
@@ -366,6 +491,20 @@ static void shim_write_back_atoms(system_t *system) {
     int n = 0, p;
     if (mpmc_b200_get_atom_arrays(g_ctx, w_mu, w_es, w_ei, w_eic, w_rrms, system->polar_gs_ranked ? w_rank : NULL))
         shim_die("get_atom_arrays");
+    if (c_valid && c_natom == system->natoms) { /* the sequence was checked (or rebuilt) by shim_prepare() of this call */
+        for (n = 0; n < c_natom; n++) {
+            a = c_atom[n];
+            for (p = 0; p < 3; p++) {
+                a->mu[p] = w_mu[3 * n + p];
+                a->ef_static[p] = w_es[3 * n + p];
+                a->ef_induced[p] = w_ei[3 * n + p];
+                a->ef_induced_change[p] = w_eic[3 * n + p];
+            }
+            a->dipole_rrms = w_rrms[n];
+            if (system->polar_gs_ranked) a->rank_metric = w_rank[n];
+        }
+        return;
+    }
     for (m = system->molecules; m; m = m->next)
         for (a = m->atoms; a; a = a->next, n++) {
             for (p = 0; p < 3; p++) {
@@ -381,7 +520,11 @@ static void shim_write_back_atoms(system_t *system) {
 
 static void shim_polar_epilogue(system_t *system, const mpmc_b200_energies *e) {
     char linebuf[MAXLINE];
-    shim_write_back_atoms(system);
+    {
+        const double t0 = (t_on == 1) ? shim_now() : 0.0;
+        shim_write_back_atoms(system);
+        if (t_on == 1) t_acc[3] += shim_now() - t0;
+    }
     if (system->polar_ewald_full) { /* polar.c:54-57: ewald_full() reports a failed solve only (polar_ewald.c:391-394) */
         if (e->iter_success) system->iter_success = 1;
         return;
@@ -417,6 +560,33 @@ static void shim_es_self_points(system_t *system) {
             if (!a->frozen) a->es_self_point_energy = system->ewald_alpha * a->charge * a->charge / sqrt(M_PI);
 }
 
+/* host lists -> O(N) duties + packed image + device: the one-pass fast path when the lists are the cached
+ * sequence, else the reference-shaped walks (which also refresh the cache) */
+static void shim_prepare(system_t *system, int es_on) {
+    static int fast = -1;
+    double t0 = 0, t1;
+    int n;
+    if (fast < 0) fast = getenv("MPMC_B200_SHIM_SLOW") ? 0 : 1; /* MPMC_B200_SHIM_SLOW=1: always the reference-shaped walks */
+    shim_timing_init();
+    if (t_on) t0 = shim_now();
+    n = fast ? shim_fast_pass(system, es_on) : -1;
+    if (n >= 0) t_fast++;
+    if (n < 0) {
+        system->natoms = countNatoms(system);
+        pairs(system);
+        n = shim_pack(system);
+        shim_cache_topology(system);
+        if (es_on) shim_es_self_points(system);
+    }
+    if (t_on) {
+        t1 = shim_now();
+        t_acc[0] += t1 - t0;
+        t0 = t1;
+    }
+    shim_upload(system, n);
+    if (t_on) t_acc[1] += shim_now() - t0;
+}
+
 /* ------------------------------------------------------------------------------------------------
  * entry points
  * ---------------------------------------------------------------------------------------------- */
@@ -424,7 +594,7 @@ double polar(system_t *system) {
     mpmc_b200_energies e;
     if (system->polarization && !system->polar_iterative && !system->polar_zodid && !system->polar_ewald_full)
         shim_unsupported("matrix-inversion polarization (polar_iterative off)");
-    shim_sync_device(system);
+    shim_prepare(system, 0);
     if (mpmc_b200_polar(g_ctx, &e)) shim_die("polar");
     shim_polar_epilogue(system, &e);
     return e.polar;
@@ -435,12 +605,21 @@ static double shim_energy(system_t *system, int with_observables) {
     double potential_energy = 0, rd_energy = 0, coulombic_energy = 0, polar_energy = 0;
     const int es_on = !(system->sg || system->rd_only);
 
-    system->natoms = countNatoms(system);
-    pairs(system);
     if (es_on && system->polarization && !system->polar_iterative && !system->polar_zodid && !system->polar_ewald_full)
         shim_unsupported("matrix-inversion polarization (polar_iterative off)");
-    shim_sync_device(system);
-    if (mpmc_b200_energy(g_ctx, &e)) shim_die("energy");
+    shim_timing_init();
+    {
+        const double tw = (t_on == 1) ? shim_now() : 0.0;
+        double te;
+        shim_prepare(system, es_on);
+        te = (t_on == 1) ? shim_now() : 0.0;
+        if (mpmc_b200_energy(g_ctx, &e)) shim_die("energy");
+        if (t_on == 1) {
+            t_acc[2] += shim_now() - te;
+            t_calls++;
+            t_acc[4] -= tw; /* closed at the end of this function */
+        }
+    }
 
     if (e.autorejected) { /* cavity_autoreject_absolute found a bad contact: energy.c:99-102,187-191 */
         potential_energy = MAXVALUE;
@@ -456,10 +635,10 @@ static double shim_energy(system_t *system, int with_observables) {
         if (es_on) {
             coulombic_energy = e.coulombic;
             if (with_observables) system->observables->coulombic_energy = coulombic_energy;
-            shim_es_self_points(system);
         }
     }
     potential_energy += rd_energy + coulombic_energy + polar_energy; /* + vdw + three-body: unsupported => 0 */
+    if (t_on == 1) t_acc[4] += shim_now();
     if (!with_observables) return potential_energy;
 
     system->observables->energy = potential_energy;

@@ -63,13 +63,19 @@ def test_dropin_energy_matches_reference_fixture(name, tmp_path):
         gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label=name)
 
 
+@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks"])
 @pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt"])
-def test_dropin_fixed_seed_trajectory(name, tmp_path):
+def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
+    """host_path: the shim's one-pass O(N) duties over the cached pointer sequence (default; every relinking of the
+    lists -- uVT insert / remove, rejected moves -- must be detected) or the reference-shaped list walks."""
     _need(PROGRAM)
     d = json.load(open(os.path.join(gu.GOLD, name + ".json")))
     (tmp_path / d["pqr_name"]).write_text(d["pqr"])
     (tmp_path / "input").write_text(d["input"])
-    r = subprocess.run([PROGRAM, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1200)
+    env = dict(os.environ)
+    if host_path == "list_walks":
+        env["MPMC_B200_SHIM_SLOW"] = "1"
+    r = subprocess.run([PROGRAM, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1200, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     rows = [l for l in (tmp_path / "small.energy.dat").read_text().splitlines() if not l.startswith("#")]
     ref = d["energy_rows"]
