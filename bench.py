@@ -47,12 +47,19 @@ def build_workload(name: str):
     """Synthetic systems of BASELINE.json's configs."""
     from mpmc_b200 import systems
 
+    if name.endswith("_gs_production"):  # the solver options of MPMC's production inputs (Gauss-Seidel, single GPU)
+        s = build_workload(name[:-len("_gs_production")])
+        p = s.params
+        p.polar_gs_ranked, p.polar_max_iter, p.polar_palmo, p.polar_wolf, p.polar_wolf_alpha = 1, 4, 1, 1, 0.13
+        return s
     if name.endswith("_ewald_full"):  # SURVEY 8f f1: the same system solved with full-Ewald polarization
         s = build_workload(name[:-len("_ewald_full")])
         s.params.polar_ewald_full = 1
         return s
     if name == "mof_h2_63k":  # config 4: MOF supercell + H2, ~63k atoms, full polarizable energy, Jacobi x10
         return systems.mof_h2()
+    if name == "mof_h2_21k":  # config 3 shape: 128.388 x 42.796 x 42.796 A, Jacobi x4 (3_PCN61/iter.inp)
+        return systems.mof_h2(cells=(9, 3, 3), polar_max_iter=4)
     if name == "mof_h2_42k":
         return systems.mof_h2(cells=(9, 6, 3))
     if name == "mof_h2_7k":

@@ -18,6 +18,8 @@ namespace mpmc {
 struct DipoleConsts {
     double l, l2h, l3s;       // l, l^2/2, l^3/6
     double wd1, wd2, ircut3;  // wolf-full: wdamp1/rcut^3, 3*wdamp2/rcut^3 (0 when off)
+    double ec[12];            // 1/k! for exp_neg_fast
+    int fastexp;              // l * (largest possible r) < 700: exp_neg_fast is valid
 };
 
 // contribution of source (sx,sy,sz,mu) to the field at (xi,yi,zi); aux_i/aux_j: alpha^(1/6) (linear)
@@ -28,14 +30,14 @@ __device__ __forceinline__ void tensor_apply(const Cell& c, const DipoleConsts& 
                                              double& ex, double& ey, double& ez) {
     min_image<ORTHO>(c, dx, dy, dz);
     const double r2 = dx * dx + dy * dy + dz * dz;
-    const double ir = rsqrt(r2);
+    const double ir = rsqrt_fast(r2);
     const double r = r2 * ir;
     const double ir2 = ir * ir;
     const double ir3 = ir * ir2;
     double damp1, damp2;
     if (DAMP == MPMC_DAMP_EXPONENTIAL) {
         const double lr = k.l * r;
-        const double e = exp(-lr);
+        const double e = k.fastexp ? exp_neg_fast(k, lr) : exp(-lr);
         damp1 = 1.0 - e * (k.l2h * r2 + lr + 1.0);
         damp2 = damp1 - e * (k.l3s * r2 * r);
     } else if (DAMP == MPMC_DAMP_LINEAR) {
@@ -138,6 +140,10 @@ static DipoleConsts make_consts(const Cell& c, const DipoleOpts& o) {
         k.wd1 = w1 / rcut3;
         k.wd2 = 3.0 * w2 / rcut3;
     }
+    fill_exp_coeffs(k.ec);
+    double rmax = 0.0;  // largest minimum-image separation is below half the sum of the lattice vector lengths
+    for (int q = 0; q < 3; q++) rmax += 0.5 * sqrt(c.B[q][0] * c.B[q][0] + c.B[q][1] * c.B[q][1] + c.B[q][2] * c.B[q][2]);
+    k.fastexp = (l >= 0.0 && l * rmax < 700.0) ? 1 : 0;
     return k;
 }
 
@@ -579,6 +585,171 @@ void launch_gs_sweep(const Cell& c, bool ortho, const SubsetDev& pol, const Dipo
 #undef DISPATCH
 #undef LAUNCH
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Gauss-Seidel in delta form.  With mu_new = mu_old + delta the field atom i sees in a sweep is
+//     E_i = - sum_{j != i} T_ij mu_old_j  -  sum_{j < i} T_ij delta_j
+// The first sum is one Jacobi contraction with the old dipoles: the symmetric K4 kernel does it for all rows
+// at once (T_ij once per unordered pair).  The second is strictly lower triangular and is resolved block by
+// block, right-looking: gs_delta_block_kernel finishes the 128 atoms of block b in order (E already holds the
+// pushes of all earlier blocks) and leaves delta_b; gs_push_kernel subtracts T_ib delta_b from every later row
+// (row-owned, no atomics).  Per sweep: N^2/2 (symmetric) + N^2/2 (pushes) pair evaluations in ~2 N/128 short
+// launches, instead of N^2 in the panel form above whose 148-CTA panels leave the GPU mostly idle.
+// Same algebra as contract_dipoles() with polar_gs (thole_iterative.c:38-53); only the association of the
+// sums differs (1e-16 relative per term).
+// ------------------------------------------------------------------------------------------------
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(TILE) gs_delta_block_kernel(Cell c, SubsetDev p, DipoleConsts k, const double* __restrict__ aux,
+                                                              const double* __restrict__ alpha, const double* __restrict__ esum,
+                                                              const double* __restrict__ es, double* __restrict__ mu,
+                                                              double* __restrict__ mu_new, double* __restrict__ eind,
+                                                              double* __restrict__ delta, int block) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], saux[TILE];
+    __shared__ int smol[TILE];
+    __shared__ double sdx, sdy, sdz;
+    const int tid = threadIdx.x, np = p.n_pad;
+    const int i = block * TILE + tid;
+    const bool live = i < p.n;
+    const double xi = p.x[i], yi = p.y[i], zi = p.z[i];
+    const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[i];
+    const int moli = p.mol[i];
+    sx[tid] = xi;
+    sy[tid] = yi;
+    sz[tid] = zi;
+    saux[tid] = auxi;
+    smol[tid] = moli;
+    double ex = esum[i], ey = esum[np + i], ez = esum[2 * np + i];
+    const double ox = mu[i], oy = mu[np + i], oz = mu[2 * np + i];
+    const double al = live ? alpha[i] : 0.0;
+    const double esx = es[i], esy = es[np + i], esz = es[2 * np + i];
+    const int jn = min(TILE, p.n - block * TILE);
+    if (!live) {
+        delta[i] = 0.0;
+        delta[np + i] = 0.0;
+        delta[2 * np + i] = 0.0;
+    }
+    __syncthreads();
+    for (int kk = 0; kk < jn; kk++) {
+        if (tid == kk) {
+            const double nx = al * (esx + ex), ny = al * (esy + ey), nz = al * (esz + ez);  // thole_iterative.c:49-53
+            sdx = nx - ox;
+            sdy = ny - oy;
+            sdz = nz - oz;
+            mu_new[i] = nx;
+            mu_new[np + i] = ny;
+            mu_new[2 * np + i] = nz;
+            mu[i] = nx;
+            mu[np + i] = ny;
+            mu[2 * np + i] = nz;
+            eind[i] = ex;
+            eind[np + i] = ey;
+            eind[2 * np + i] = ez;
+            delta[i] = sdx;
+            delta[np + i] = sdy;
+            delta[2 * np + i] = sdz;
+        }
+        __syncthreads();
+        if (live && tid > kk)
+            tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[kk], yi - sy[kk], zi - sz[kk], sdx, sdy, sdz, auxi, saux[kk],
+                                          moli == smol[kk], ex, ey, ez);
+        __syncthreads();
+    }
+}
+
+// esum_i -= sum_{k in block} T_ik delta_k for the rows i >= row_begin.  CTA = 64 rows x 4 column groups of 32:
+// the four partial sums of a row are added in group order (fixed association).
+constexpr int PUSH_ROWS = 64;
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(4 * PUSH_ROWS) gs_push_kernel(Cell c, SubsetDev p, DipoleConsts k, const double* __restrict__ aux,
+                                                               const double* __restrict__ delta, int block, int row_begin,
+                                                               double* __restrict__ esum) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], sdx[TILE], sdy[TILE], sdz[TILE], saux[TILE];
+    __shared__ int smol[TILE];
+    __shared__ double red[3][3][PUSH_ROWS];
+    const int tid = threadIdx.x, np = p.n_pad;
+    if (tid < TILE) {
+        const int j = block * TILE + tid;
+        sx[tid] = p.x[j];
+        sy[tid] = p.y[j];
+        sz[tid] = p.z[j];
+        sdx[tid] = delta[j];
+        sdy[tid] = delta[np + j];
+        sdz[tid] = delta[2 * np + j];
+        saux[tid] = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[j];
+        smol[tid] = p.mol[j];
+    }
+    __syncthreads();
+    const int r = tid % PUSH_ROWS, g = tid / PUSH_ROWS;
+    const int i = row_begin + blockIdx.x * PUSH_ROWS + r;
+    const bool live = i < p.n;
+    double ex = 0.0, ey = 0.0, ez = 0.0;
+    if (live) {
+        const double xi = p.x[i], yi = p.y[i], zi = p.z[i];
+        const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[i];
+        const int moli = p.mol[i];
+        const int jn = min(TILE, p.n - block * TILE);
+        const int j0 = g * 32, j1 = min(j0 + 32, jn);
+#pragma unroll 2
+        for (int jj = j0; jj < j1; jj++)
+            tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[jj], yi - sy[jj], zi - sz[jj], sdx[jj], sdy[jj], sdz[jj], auxi, saux[jj],
+                                          moli == smol[jj], ex, ey, ez);
+    }
+    if (g > 0) {
+        red[g - 1][0][r] = ex;
+        red[g - 1][1][r] = ey;
+        red[g - 1][2][r] = ez;
+    }
+    __syncthreads();
+    if (g == 0 && live) {
+        ex = ((ex + red[0][0][r]) + red[1][0][r]) + red[2][0][r];
+        ey = ((ey + red[0][1][r]) + red[1][1][r]) + red[2][1][r];
+        ez = ((ez + red[0][2][r]) + red[1][2][r]) + red[2][2][r];
+        esum[i] += ex;  // tensor_apply accumulates -T m
+        esum[np + i] += ey;
+        esum[2 * np + i] += ez;
+    }
+}
+
+void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* cbox, int ysplits,
+                           double* epartI, double* epartJ, double* esum, const double* es, double* mu, double* mu_new,
+                           double* eind, double* delta, cudaStream_t s) {
+    const DipoleConsts k = make_consts(c, o);
+    const int ntiles = pol.n_pad / TILE;
+    const double* aux = pol.aux;
+    const double* alpha = pol.alpha;
+    // Jacobi part with the dipoles as they are at the start of the sweep
+    launch_dipole_contract_sym(c, ortho, pol, o, mu, cbox, 0, 1, ysplits, epartI, epartJ, esum, s);
+    const int nlive_tiles = (pol.n + TILE - 1) / TILE;
+    for (int b = 0; b < nlive_tiles; b++) {
+        const int row_begin = (b + 1) * TILE;
+        const int rows = pol.n - row_begin;
+        const int pgrid = rows > 0 ? (rows + PUSH_ROWS - 1) / PUSH_ROWS : 0;
+#define LAUNCH(ORTHO, DAMP, WF)                                                                                                \
+    {                                                                                                                          \
+        gs_delta_block_kernel<ORTHO, DAMP, WF><<<1, TILE, 0, s>>>(c, pol, k, aux, alpha, esum, es, mu, mu_new, eind, delta, b); \
+        if (pgrid > 0)                                                                                                         \
+            gs_push_kernel<ORTHO, DAMP, WF><<<pgrid, 4 * PUSH_ROWS, 0, s>>>(c, pol, k, aux, delta, b, row_begin, esum);       \
+    }
+#define DISPATCH(ORTHO)                                              \
+    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true)  \
+        else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false)             \
+    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                    \
+        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false)                       \
+    } else {                                                         \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true)          \
+        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false)                     \
+    }
+        if (ortho) {
+            DISPATCH(true)
+        } else {
+            DISPATCH(false)
+        }
+#undef DISPATCH
+#undef LAUNCH
+    }
+    (void)ntiles;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -132,45 +132,6 @@ constexpr int kSymUnroll = SYM_UNROLL;
 constexpr int STILE = 256;  // atoms per super tile: 2 per thread
 constexpr int JREC = 6;     // doubles per staged j record: x y z mx my mz
 
-// 1/sqrt(a): MUFU.RSQ64H seed (2^-22.9) + one third-order step, no range checks (a is a squared distance
-// between distinct atoms).  5 fp64 instructions like the library's fast path, without its slow-path test.
-__device__ __forceinline__ double rsqrt_fast(double a) {
-    double y;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
-    const double e = fma(a, -(y * y), 1.0);
-    const double p = fma(e, 0.375, 0.5);
-    return fma(p, y * e, y);
-}
-
-// e^{-x} for 0 <= x < 700: Cody-Waite reduction by ln2 with the magic-number rint, degree-11 Taylor
-// polynomial on |r| <= ln2/2 (truncation error 6.4e-15 relative), exponent inserted with one integer add.
-// The coefficients arrive through the constant bank (kernel parameter), so every DFMA takes its constant
-// as an operand instead of materialising it with two moves.
-__device__ __forceinline__ double exp_neg_fast(const SymConsts& k, double x) {
-    const double magic = 6755399441055744.0;
-    const double t = fma(x, -1.4426950408889634, magic);
-    const double nd = t - magic;
-    double r = fma(nd, -6.93147180369123816490e-01, -x);
-    r = fma(nd, -1.90821492927058770002e-10, r);
-    // even / odd split: two independent Horner chains in r^2 (depth 7 instead of 11; with two pairs in flight
-    // that is four chains, enough to keep the half-rate fp64 pipe fed from one warp)
-    const double r2 = r * r;
-    double pe = k.ec[10], po = k.ec[11];
-    pe = fma(pe, r2, k.ec[8]);
-    po = fma(po, r2, k.ec[9]);
-    pe = fma(pe, r2, k.ec[6]);
-    po = fma(po, r2, k.ec[7]);
-    pe = fma(pe, r2, k.ec[4]);
-    po = fma(po, r2, k.ec[5]);
-    pe = fma(pe, r2, k.ec[2]);
-    po = fma(po, r2, k.ec[3]);
-    pe = fma(pe, r2, 1.0);
-    po = fma(po, r2, 1.0);
-    const double p = fma(po, r, pe);
-    const int n = __double2loint(t);
-    return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
-}
-
 // c1 = damp1/r^3, c2 = 3 damp2/r^5 from r^2 (exponential damping, fast math helpers)
 template <bool WF, bool FAR, bool FASTEXP>
 __device__ __forceinline__ void coeffs_exp(const SymConsts& k, double r2, double& c1, double& c2) {

@@ -151,7 +151,8 @@ struct mpmc_b200_ctx {
     DevBuf<double> ef_static;  // [3][n_pad]
     DevBuf<double> epart;      // max(field, dipole) partials
     DevBuf<double> es, mu, mu_old, mu_new, eind, eic, rrms, rank_packed, rmin_part, field_cnt;
-    DevBuf<double> g_es, g_mu, g_mu_old, g_mu_new, g_eind, g_eic, g_rrms;  // GS space
+    DevBuf<double> g_es, g_mu, g_mu_old, g_mu_new, g_eind, g_eic, g_rrms, g_delta;  // GS space
+    bool gs_delta = true;  // delta form of the sweep (symmetric Jacobi part + block pushes); MPMC_B200_GS=panels: panel form
     DevBuf<int> perm;
     std::vector<int> hperm;
     DevBuf<double> wolf_table;
@@ -1351,7 +1352,8 @@ static int enqueue_polar(Ctx* c) {
                 c->gs.alpha.ensure(pp) || c->gs.aux.ensure(pp) || c->gs.mol.ensure(pp) || c->gs.flags.ensure(pp) ||
                 c->gs.didx.ensure(pp) || c->perm.ensure(pp) || c->g_es.ensure(3 * (size_t)pp) ||
                 c->g_mu.ensure(3 * (size_t)pp) || c->g_mu_old.ensure(3 * (size_t)pp) || c->g_mu_new.ensure(3 * (size_t)pp) ||
-                c->g_eind.ensure(3 * (size_t)pp) || c->g_eic.ensure(3 * (size_t)pp) || c->g_rrms.ensure(pp))
+                c->g_eind.ensure(3 * (size_t)pp) || c->g_eic.ensure(3 * (size_t)pp) || c->g_rrms.ensure(pp) ||
+                c->g_delta.ensure(3 * (size_t)pp))
                 FAIL(11, "cudaMalloc failed");
         }
         auto to_gs_space = [&](bool first) -> int {
@@ -1381,6 +1383,10 @@ static int enqueue_polar(Ctx* c) {
             g.alpha = c->gs.alpha.p;
             g.aux = c->gs.aux.p;
             g.mol = c->gs.mol.p;
+            if (c->gs_delta) {  // cluster boxes of the atoms in processing order, for the symmetric Jacobi part of a sweep
+                launch_cluster_boxes(cell, ortho, g, c->cbox.p, st);
+                c->launches++;
+            }
             CU(cudaGetLastError());
             return 0;
         };
@@ -1426,8 +1432,16 @@ static int enqueue_polar(Ctx* c) {
             if (precision_mode) CU(cudaMemsetAsync(errbits, 0, sizeof(unsigned long long), st));
             if (gs) {
                 if (uo.save_old) CU(cudaMemcpyAsync(c->g_mu_old.p, c->g_mu.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToDevice, st));
-                launch_gs_sweep(cell, ortho, g, dop, nullptr, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->epart.p, st);
-                c->launches += 2 * (pp / TILE);
+                if (c->gs_delta) {
+                    kev_mark(c);
+                    launch_gs_sweep_delta(cell, ortho, g, dop, c->cbox.p, c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p,
+                                          c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->g_delta.p, st);
+                    kev_mark(c);
+                    c->launches += 2 + 2 * ((c->pol.n + TILE - 1) / TILE);
+                } else {
+                    launch_gs_sweep(cell, ortho, g, dop, nullptr, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->epart.p, st);
+                    c->launches += 2 * (pp / TILE);
+                }
                 if (want_rrms || precision_mode) {
                     gs_check_kernel<<<(c->pol.n + 255) / 256, 256, 0, st>>>(c->pol.n, pp, c->g_mu_new.p, c->g_mu_old.p,
                                                                           uo.do_rrms, c->g_rrms.p, errbits);
@@ -1450,7 +1464,14 @@ static int enqueue_polar(Ctx* c) {
             }
 
             if (P.polar_palmo && !keep) {  // palmo_contraction (:119-141) with the CURRENT mu
-                if (gs) {
+                if (gs && c->gs_delta) {
+                    launch_dipole_contract_sym(cell, ortho, g, dop, c->g_mu.p, c->cbox.p, 0, 1, c->sym_ysplits, c->sym_partI.p,
+                                               c->sym_partJ.p, c->esum.p, st);
+                    launch_palmo_finish(g, c->esum.p, 1, c->g_eind.p, c->g_eic.p, 0, pp, st);
+                    c->launches += 3;
+                    c->cnt.contractions += 1;
+                    if (palmo_nonpolar_rows(c, g, c->g_mu.p)) return 10;
+                } else if (gs) {
                     launch_dipole_contract(cell, ortho, g, dop, c->g_mu.p, 0, pp, js, c->epart.p, st);
                     launch_palmo_finish(g, c->epart.p, js, c->g_eind.p, c->g_eic.p, 0, pp, st);
                     c->launches += 2;
@@ -1691,6 +1712,8 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         // MPMC_B200_CUTOFF=tiles selects the all-pairs tile form of K1 / K3 (no cluster culling)
         v = getenv("MPMC_B200_CUTOFF");
         c->use_clusters = !(v && strcmp(v, "tiles") == 0);
+        v = getenv("MPMC_B200_GS");
+        c->gs_delta = c->use_sym && !(v && strcmp(v, "panels") == 0);
     }
     for (int p = 0; p < PH_COUNT; p++) {
         CU(cudaEventCreate(&c->ev[p][0]));
@@ -1723,7 +1746,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     for (DevBuf<double>* b : {&c->x, &c->y, &c->z, &c->q, &c->eps, &c->sig, &c->molmass, &c->alpha, &c->pair_part, &c->kweight,
                               &c->kweight_field, &c->kvec, &c->sf_partial, &c->sf, &c->ef_static, &c->epart, &c->es, &c->mu,
                               &c->mu_old, &c->mu_new, &c->eind, &c->eic, &c->rrms, &c->rank_packed, &c->rmin_part,
-                              &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms,
+                              &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms, &c->g_delta,
                               &c->wolf_table, &c->scalars, &c->cbox, &c->sym_partI, &c->sym_partJ, &c->esum})
         b->release();
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();

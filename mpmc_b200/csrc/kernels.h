@@ -168,6 +168,11 @@ void launch_polar_energy(const SubsetDev& pol, const double* mu, const double* e
 // Gauss-Seidel sweep (polar_gs / polar_gs_ranked): blocked forward substitution in `order`.
 void launch_gs_sweep(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const int* order,
                      const double* es, double* mu, double* mu_new, double* eind, double* scratch, cudaStream_t s);
+// Delta form of the sweep (dipole_kernel.cu): one symmetric Jacobi contraction with the old dipoles + right-looking
+// block pushes of delta = mu_new - mu_old.  cbox = cluster boxes of `pol` in ITS order; delta [3][n_pad] scratch.
+void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* cbox, int ysplits,
+                           double* epartI, double* epartJ, double* esum, const double* es, double* mu, double* mu_new,
+                           double* eind, double* delta, cudaStream_t s);
 // rank metric of pairs() (src/energy/pairs.c:337-360)
 void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank /*[pol n_pad]*/,
                         cudaStream_t s);
