@@ -24,12 +24,10 @@ struct DipoleConsts {
 
 // contribution of source (sx,sy,sz,mu) to the field at (xi,yi,zi); aux_i/aux_j: alpha^(1/6) (linear)
 // or charge (damping off); same_mol only matters for damping off.
-template <bool ORTHO, int DAMP, bool WF>
-__device__ __forceinline__ void tensor_apply(const Cell& c, const DipoleConsts& k, double dx, double dy, double dz,
-                                             double mx, double my, double mz, double aux_i, double aux_j, bool same_mol,
-                                             double& ex, double& ey, double& ez) {
-    min_image<ORTHO>(c, dx, dy, dz);
-    const double r2 = dx * dx + dy * dy + dz * dz;
+// c1 = damp1 / r^3 (delta_pq coefficient), c2 = 3 damp2 / r^5 (d_p d_q coefficient) of T_ij from r^2
+template <int DAMP, bool WF>
+__device__ __forceinline__ void tensor_coeff(const DipoleConsts& k, double r2, double aux_i, double aux_j, bool same_mol,
+                                             double& c1, double& c2) {
     const double ir = rsqrt_fast(r2);
     const double r = r2 * ir;
     const double ir2 = ir * ir;
@@ -54,8 +52,8 @@ __device__ __forceinline__ void tensor_apply(const Cell& c, const DipoleConsts& 
         const bool excl = same_mol || aux_i == 0.0 || aux_j == 0.0;
         damp1 = damp2 = excl ? 0.0 : 1.0;
     }
-    double c1 = damp1 * ir3;               // delta_pq coefficient
-    double c2 = 3.0 * damp2 * ir3 * ir2;   // d_p d_q coefficient
+    c1 = damp1 * ir3;
+    c2 = 3.0 * damp2 * ir3 * ir2;
     if (WF) {                              // thole_matrix.c:123-130
         if (DAMP == MPMC_DAMP_OFF) {
             c1 -= damp1 * k.ircut3;
@@ -65,6 +63,16 @@ __device__ __forceinline__ void tensor_apply(const Cell& c, const DipoleConsts& 
             c2 -= k.wd2 * ir2;
         }
     }
+}
+
+template <bool ORTHO, int DAMP, bool WF>
+__device__ __forceinline__ void tensor_apply(const Cell& c, const DipoleConsts& k, double dx, double dy, double dz,
+                                             double mx, double my, double mz, double aux_i, double aux_j, bool same_mol,
+                                             double& ex, double& ey, double& ez) {
+    min_image<ORTHO>(c, dx, dy, dz);
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    double c1, c2;
+    tensor_coeff<DAMP, WF>(k, r2, aux_i, aux_j, same_mol, c1, c2);
     const double dm = (dx * mx + dy * my + dz * mz) * c2;
     ex += dm * dx - c1 * mx;
     ey += dm * dy - c1 * my;
@@ -657,6 +665,106 @@ __global__ void __launch_bounds__(TILE) gs_delta_block_kernel(Cell c, SubsetDev 
     }
 }
 
+// (c1, c2) of every in-block pair (i > k) of every 128-atom block, pair (i, k) at i (i-1)/2 + k: they depend on the
+// positions only, so one launch serves all sweeps of an evaluation; the sequential block kernel then reads them from
+// shared memory instead of evaluating rsqrt / exp inside its 128-step dependency chain.
+constexpr int GS_PAIRS = TILE * (TILE - 1) / 2;
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(TILE) gs_block_coeff_kernel(Cell c, SubsetDev p, DipoleConsts k, const double* __restrict__ aux,
+                                                              double2* __restrict__ coef) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], saux[TILE];
+    __shared__ int smol[TILE];
+    const int tid = threadIdx.x, b = blockIdx.x;
+    const int j = b * TILE + tid;
+    sx[tid] = p.x[j];
+    sy[tid] = p.y[j];
+    sz[tid] = p.z[j];
+    saux[tid] = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[j];
+    smol[tid] = p.mol[j];
+    __syncthreads();
+    const int jn = min(TILE, p.n - b * TILE);
+    double2* out = coef + (size_t)b * GS_PAIRS;
+    for (int idx = tid; idx < GS_PAIRS; idx += TILE) {
+        int i = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)idx)) * 0.5f);
+        while (i * (i - 1) / 2 > idx) i--;
+        while ((i + 1) * i / 2 <= idx) i++;
+        const int kk = idx - i * (i - 1) / 2;
+        double2 v = make_double2(0.0, 0.0);
+        if (i < jn) {
+            double dx = sx[i] - sx[kk], dy = sy[i] - sy[kk], dz = sz[i] - sz[kk];
+            min_image<ORTHO>(c, dx, dy, dz);
+            tensor_coeff<DAMP, WF>(k, dx * dx + dy * dy + dz * dz, saux[i], saux[kk], smol[i] == smol[kk], v.x, v.y);
+        }
+        out[idx] = v;
+    }
+}
+
+template <bool ORTHO>
+__global__ void __launch_bounds__(TILE) gs_delta_block_table_kernel(Cell c, SubsetDev p, const double* __restrict__ alpha,
+                                                                    const double2* __restrict__ coef,
+                                                                    const double* __restrict__ esum, const double* __restrict__ es,
+                                                                    double* __restrict__ mu, double* __restrict__ mu_new,
+                                                                    double* __restrict__ eind, double* __restrict__ delta, int block) {
+    extern __shared__ double2 sc[];  // [GS_PAIRS]
+    __shared__ double sx[TILE], sy[TILE], sz[TILE];
+    __shared__ double sdx, sdy, sdz;
+    const int tid = threadIdx.x, np = p.n_pad;
+    const int i = block * TILE + tid;
+    const bool live = i < p.n;
+    {
+        const double2* src = coef + (size_t)block * GS_PAIRS;
+        for (int idx = tid; idx < GS_PAIRS; idx += TILE) sc[idx] = src[idx];
+    }
+    const double xi = p.x[i], yi = p.y[i], zi = p.z[i];
+    sx[tid] = xi;
+    sy[tid] = yi;
+    sz[tid] = zi;
+    double ex = esum[i], ey = esum[np + i], ez = esum[2 * np + i];
+    const double ox = mu[i], oy = mu[np + i], oz = mu[2 * np + i];
+    const double al = live ? alpha[i] : 0.0;
+    const double esx = es[i], esy = es[np + i], esz = es[2 * np + i];
+    const int jn = min(TILE, p.n - block * TILE);
+    if (!live) {
+        delta[i] = 0.0;
+        delta[np + i] = 0.0;
+        delta[2 * np + i] = 0.0;
+    }
+    const double2* row = sc + tid * (tid - 1) / 2;
+    __syncthreads();
+    for (int kk = 0; kk < jn; kk++) {
+        if (tid == kk) {
+            const double nx = al * (esx + ex), ny = al * (esy + ey), nz = al * (esz + ez);  // thole_iterative.c:49-53
+            sdx = nx - ox;
+            sdy = ny - oy;
+            sdz = nz - oz;
+            mu_new[i] = nx;
+            mu_new[np + i] = ny;
+            mu_new[2 * np + i] = nz;
+            mu[i] = nx;
+            mu[np + i] = ny;
+            mu[2 * np + i] = nz;
+            eind[i] = ex;
+            eind[np + i] = ey;
+            eind[2 * np + i] = ez;
+            delta[i] = sdx;
+            delta[np + i] = sdy;
+            delta[2 * np + i] = sdz;
+        }
+        __syncthreads();
+        if (live && tid > kk) {
+            const double2 cf = row[kk];
+            double dx = xi - sx[kk], dy = yi - sy[kk], dz = zi - sz[kk];
+            min_image<ORTHO>(c, dx, dy, dz);
+            const double mx = sdx, my = sdy, mz = sdz;
+            const double dm = (dx * mx + dy * my + dz * mz) * cf.y;
+            ex += dm * dx - cf.x * mx;
+            ey += dm * dy - cf.x * my;
+            ez += dm * dz - cf.x * mz;
+        }
+        __syncthreads();
+    }
+}
+
 // esum_i -= sum_{k in block} T_ik delta_k for the rows i >= row_begin.  CTA = 64 rows x 4 column groups of 32:
 // the four partial sums of a row are added in group order (fixed association).
 constexpr int PUSH_ROWS = 64;
@@ -711,9 +819,44 @@ __global__ void __launch_bounds__(4 * PUSH_ROWS) gs_push_kernel(Cell c, SubsetDe
     }
 }
 
+size_t gs_block_coeff_doubles(int n_pad) { return (size_t)(n_pad / TILE) * GS_PAIRS * 2; }
+
+void launch_gs_block_coeffs(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* coef, cudaStream_t s) {
+    const DipoleConsts k = make_consts(c, o);
+    const int nb = (pol.n + TILE - 1) / TILE;
+    if (nb <= 0) return;
+    const double* aux = pol.aux;
+    double2* out = reinterpret_cast<double2*>(coef);
+#define LAUNCH(ORTHO, DAMP, WF) gs_block_coeff_kernel<ORTHO, DAMP, WF><<<nb, TILE, 0, s>>>(c, pol, k, aux, out);
+#define DISPATCH(ORTHO)                                              \
+    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true)  \
+        else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false)             \
+    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                    \
+        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false)                       \
+    } else {                                                         \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true)          \
+        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false)                     \
+    }
+    if (ortho) {
+        DISPATCH(true)
+    } else {
+        DISPATCH(false)
+    }
+#undef DISPATCH
+#undef LAUNCH
+}
+
 void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* cbox, int ysplits,
                            double* epartI, double* epartJ, double* esum, const double* es, double* mu, double* mu_new,
-                           double* eind, double* delta, cudaStream_t s) {
+                           double* eind, double* delta, const double* coef, cudaStream_t s) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(gs_delta_block_table_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GS_PAIRS * sizeof(double2)));
+        cudaFuncSetAttribute(gs_delta_block_table_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GS_PAIRS * sizeof(double2)));
+        attr_set = true;
+    }
+    const double2* cf = reinterpret_cast<const double2*>(coef);
     const DipoleConsts k = make_consts(c, o);
     const int ntiles = pol.n_pad / TILE;
     const double* aux = pol.aux;
@@ -727,7 +870,11 @@ void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, cons
         const int pgrid = rows > 0 ? (rows + PUSH_ROWS - 1) / PUSH_ROWS : 0;
 #define LAUNCH(ORTHO, DAMP, WF)                                                                                                \
     {                                                                                                                          \
-        gs_delta_block_kernel<ORTHO, DAMP, WF><<<1, TILE, 0, s>>>(c, pol, k, aux, alpha, esum, es, mu, mu_new, eind, delta, b); \
+        if (cf)                                                                                                                \
+            gs_delta_block_table_kernel<ORTHO><<<1, TILE, GS_PAIRS * sizeof(double2), s>>>(c, pol, alpha, cf, esum, es, mu,     \
+                                                                                         mu_new, eind, delta, b);             \
+        else                                                                                                                   \
+            gs_delta_block_kernel<ORTHO, DAMP, WF><<<1, TILE, 0, s>>>(c, pol, k, aux, alpha, esum, es, mu, mu_new, eind, delta, b); \
         if (pgrid > 0)                                                                                                         \
             gs_push_kernel<ORTHO, DAMP, WF><<<pgrid, 4 * PUSH_ROWS, 0, s>>>(c, pol, k, aux, delta, b, row_begin, esum);       \
     }

@@ -151,7 +151,7 @@ struct mpmc_b200_ctx {
     DevBuf<double> ef_static;  // [3][n_pad]
     DevBuf<double> epart;      // max(field, dipole) partials
     DevBuf<double> es, mu, mu_old, mu_new, eind, eic, rrms, rank_packed, rmin_part, field_cnt;
-    DevBuf<double> g_es, g_mu, g_mu_old, g_mu_new, g_eind, g_eic, g_rrms, g_delta;  // GS space
+    DevBuf<double> g_es, g_mu, g_mu_old, g_mu_new, g_eind, g_eic, g_rrms, g_delta, g_coef;  // GS space
     bool gs_delta = true;  // delta form of the sweep (symmetric Jacobi part + block pushes); MPMC_B200_GS=panels: panel form
     DevBuf<int> perm;
     std::vector<int> hperm;
@@ -1353,7 +1353,7 @@ static int enqueue_polar(Ctx* c) {
                 c->gs.didx.ensure(pp) || c->perm.ensure(pp) || c->g_es.ensure(3 * (size_t)pp) ||
                 c->g_mu.ensure(3 * (size_t)pp) || c->g_mu_old.ensure(3 * (size_t)pp) || c->g_mu_new.ensure(3 * (size_t)pp) ||
                 c->g_eind.ensure(3 * (size_t)pp) || c->g_eic.ensure(3 * (size_t)pp) || c->g_rrms.ensure(pp) ||
-                c->g_delta.ensure(3 * (size_t)pp))
+                c->g_delta.ensure(3 * (size_t)pp) || (c->gs_delta && c->g_coef.ensure(gs_block_coeff_doubles(pp))))
                 FAIL(11, "cudaMalloc failed");
         }
         auto to_gs_space = [&](bool first) -> int {
@@ -1385,7 +1385,8 @@ static int enqueue_polar(Ctx* c) {
             g.mol = c->gs.mol.p;
             if (c->gs_delta) {  // cluster boxes of the atoms in processing order, for the symmetric Jacobi part of a sweep
                 launch_cluster_boxes(cell, ortho, g, c->cbox.p, st);
-                c->launches++;
+                launch_gs_block_coeffs(cell, ortho, g, dop, c->g_coef.p, st);  // in-block tensor coefficients of this order
+                c->launches += 2;
             }
             CU(cudaGetLastError());
             return 0;
@@ -1435,7 +1436,7 @@ static int enqueue_polar(Ctx* c) {
                 if (c->gs_delta) {
                     kev_mark(c);
                     launch_gs_sweep_delta(cell, ortho, g, dop, c->cbox.p, c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p,
-                                          c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->g_delta.p, st);
+                                          c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->g_delta.p, c->g_coef.p, st);
                     kev_mark(c);
                     c->launches += 2 + 2 * ((c->pol.n + TILE - 1) / TILE);
                 } else {
@@ -1746,7 +1747,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     for (DevBuf<double>* b : {&c->x, &c->y, &c->z, &c->q, &c->eps, &c->sig, &c->molmass, &c->alpha, &c->pair_part, &c->kweight,
                               &c->kweight_field, &c->kvec, &c->sf_partial, &c->sf, &c->ef_static, &c->epart, &c->es, &c->mu,
                               &c->mu_old, &c->mu_new, &c->eind, &c->eic, &c->rrms, &c->rank_packed, &c->rmin_part,
-                              &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms, &c->g_delta,
+                              &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms, &c->g_delta, &c->g_coef,
                               &c->wolf_table, &c->scalars, &c->cbox, &c->sym_partI, &c->sym_partJ, &c->esum})
         b->release();
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();

@@ -170,9 +170,13 @@ void launch_gs_sweep(const Cell& c, bool ortho, const SubsetDev& pol, const Dipo
                      const double* es, double* mu, double* mu_new, double* eind, double* scratch, cudaStream_t s);
 // Delta form of the sweep (dipole_kernel.cu): one symmetric Jacobi contraction with the old dipoles + right-looking
 // block pushes of delta = mu_new - mu_old.  cbox = cluster boxes of `pol` in ITS order; delta [3][n_pad] scratch.
+// coef (optional, gs_block_coeff_doubles(n_pad) doubles from launch_gs_block_coeffs for the SAME order): tensor
+// coefficients of the in-block pairs, read by the sequential block kernel instead of being recomputed.
+size_t gs_block_coeff_doubles(int n_pad);
+void launch_gs_block_coeffs(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* coef, cudaStream_t s);
 void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* cbox, int ysplits,
                            double* epartI, double* epartJ, double* esum, const double* es, double* mu, double* mu_new,
-                           double* eind, double* delta, cudaStream_t s);
+                           double* eind, double* delta, const double* coef, cudaStream_t s);
 // rank metric of pairs() (src/energy/pairs.c:337-360)
 void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank /*[pol n_pad]*/,
                         cudaStream_t s);
