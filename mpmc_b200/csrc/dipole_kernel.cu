@@ -765,6 +765,109 @@ __global__ void __launch_bounds__(TILE) gs_delta_block_table_kernel(Cell c, Subs
     }
 }
 
+// Warp-synchronous form of the sequential block kernel.  The 128 atoms of a block are four sub-blocks of 32, one per
+// warp.  -T_ik of every pair inside a sub-block is tabulated (full symmetric 3x3, 93 KB of shared memory) before the
+// chain starts, so one step of the chain is: candidate delta of lane k (3 dependent fp64 ops) -> three 64-bit shuffles
+// -> nine FMAs in chains of three; no block barrier, no rsqrt/exp.  Between sub-blocks (three block barriers) the
+// later warps apply the 32 finished deltas to their rows with the ordinary pair evaluation (independent pairs, pipelined).
+constexpr int GS_SUB = 32, GS_SUBPAIRS = GS_SUB * (GS_SUB - 1) / 2;  // 496
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(TILE) gs_delta_block_warp_kernel(Cell c, SubsetDev p, DipoleConsts k, const double* __restrict__ aux,
+                                                                   const double* __restrict__ alpha, const double* __restrict__ esum,
+                                                                   const double* __restrict__ es, double* __restrict__ mu,
+                                                                   double* __restrict__ mu_new, double* __restrict__ eind,
+                                                                   double* __restrict__ delta, int block) {
+    extern __shared__ double tens[];  // [4][GS_SUBPAIRS][6]: -T = c2 d d^T - c1 I  (xx xy xz yy yz zz)
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], saux[TILE], sdl[3][TILE];
+    __shared__ int smol[TILE];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, np = p.n_pad;
+    const int i = block * TILE + tid;
+    const int jn = min(TILE, p.n - block * TILE);
+    const bool live = tid < jn;
+    const double xi = p.x[i], yi = p.y[i], zi = p.z[i];
+    const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[i];
+    const int moli = p.mol[i];
+    sx[tid] = xi;
+    sy[tid] = yi;
+    sz[tid] = zi;
+    saux[tid] = auxi;
+    smol[tid] = moli;
+    double ex = esum[i], ey = esum[np + i], ez = esum[2 * np + i];
+    const double ox = mu[i], oy = mu[np + i], oz = mu[2 * np + i];
+    const double al = live ? alpha[i] : 0.0;
+    const double esx = es[i], esy = es[np + i], esz = es[2 * np + i];
+    __syncthreads();
+    for (int idx = tid; idx < 4 * GS_SUBPAIRS; idx += TILE) {
+        const int s = idx / GS_SUBPAIRS, q = idx - s * GS_SUBPAIRS;
+        int a = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
+        while (a * (a - 1) / 2 > q) a--;
+        while ((a + 1) * a / 2 <= q) a++;
+        const int b = q - a * (a - 1) / 2;  // pair (a, b), b < a, inside sub-block s
+        const int ia = s * GS_SUB + a, ib = s * GS_SUB + b;
+        double m[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (ia < jn) {  // ib < ia: both atoms exist
+            double dx = sx[ia] - sx[ib], dy = sy[ia] - sy[ib], dz = sz[ia] - sz[ib];
+            min_image<ORTHO>(c, dx, dy, dz);
+            double c1, c2;
+            tensor_coeff<DAMP, WF>(k, dx * dx + dy * dy + dz * dz, saux[ia], saux[ib], smol[ia] == smol[ib], c1, c2);
+            m[0] = c2 * dx * dx - c1;
+            m[1] = c2 * dx * dy;
+            m[2] = c2 * dx * dz;
+            m[3] = c2 * dy * dy - c1;
+            m[4] = c2 * dy * dz;
+            m[5] = c2 * dz * dz - c1;
+        }
+        double* t = tens + (size_t)idx * 6;
+#pragma unroll
+        for (int e = 0; e < 6; e++) t[e] = m[e];
+    }
+    __syncthreads();
+    for (int s = 0; s < 4; s++) {
+        if (w == s) {
+            const double* trow = tens + ((size_t)s * GS_SUBPAIRS + (size_t)lane * (lane - 1) / 2) * 6;
+            for (int kk = 0; kk < GS_SUB; kk++) {
+                // every lane forms its candidate; lane kk's is final (its field is complete): thole_iterative.c:49-53
+                const double cx = al * (esx + ex) - ox, cy = al * (esy + ey) - oy, cz = al * (esz + ez) - oz;
+                const double bx = __shfl_sync(0xffffffffu, cx, kk), by = __shfl_sync(0xffffffffu, cy, kk),
+                             bz = __shfl_sync(0xffffffffu, cz, kk);
+                if (lane > kk) {
+                    const double* t = trow + kk * 6;
+                    ex += t[0] * bx + t[1] * by + t[2] * bz;
+                    ey += t[1] * bx + t[3] * by + t[4] * bz;
+                    ez += t[2] * bx + t[4] * by + t[5] * bz;
+                }
+            }
+            const double nx = al * (esx + ex), ny = al * (esy + ey), nz = al * (esz + ez);
+            sdl[0][tid] = nx - ox;
+            sdl[1][tid] = ny - oy;
+            sdl[2][tid] = nz - oz;
+            if (live) {
+                mu_new[i] = nx;
+                mu_new[np + i] = ny;
+                mu_new[2 * np + i] = nz;
+                mu[i] = nx;
+                mu[np + i] = ny;
+                mu[2 * np + i] = nz;
+                eind[i] = ex;
+                eind[np + i] = ey;
+                eind[2 * np + i] = ez;
+            }
+            delta[i] = live ? nx - ox : 0.0;
+            delta[np + i] = live ? ny - oy : 0.0;
+            delta[2 * np + i] = live ? nz - oz : 0.0;
+        }
+        if (s == 3) break;
+        __syncthreads();
+        if (w > s && live) {
+            const int j1 = min((s + 1) * GS_SUB, jn);
+#pragma unroll 2
+            for (int j = s * GS_SUB; j < j1; j++)
+                tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[j], yi - sy[j], zi - sz[j], sdl[0][j], sdl[1][j], sdl[2][j], auxi,
+                                              saux[j], moli == smol[j], ex, ey, ez);
+        }
+    }
+}
+
 // esum_i -= sum_{k in block} T_ik delta_k for the rows i >= row_begin.  CTA = 64 rows x 4 column groups of 32:
 // the four partial sums of a row are added in group order (fixed association).
 constexpr int PUSH_ROWS = 64;
@@ -857,6 +960,14 @@ void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, cons
         attr_set = true;
     }
     const double2* cf = reinterpret_cast<const double2*>(coef);
+    static int warp_form = -1;  // MPMC_B200_GS_BLOCK=table|plain selects the earlier block kernels (A/B)
+    if (warp_form < 0) {
+        const char* v = getenv("MPMC_B200_GS_BLOCK");
+        warp_form = (v && (!strcmp(v, "table") || !strcmp(v, "plain"))) ? 0 : 1;
+        if (v && !strcmp(v, "plain")) warp_form = 2;
+    }
+    if (warp_form == 2) cf = nullptr;
+    const size_t wsmem = sizeof(double) * 4 * GS_SUBPAIRS * 6;
     const DipoleConsts k = make_consts(c, o);
     const int ntiles = pol.n_pad / TILE;
     const double* aux = pol.aux;
@@ -870,7 +981,16 @@ void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, cons
         const int pgrid = rows > 0 ? (rows + PUSH_ROWS - 1) / PUSH_ROWS : 0;
 #define LAUNCH(ORTHO, DAMP, WF)                                                                                                \
     {                                                                                                                          \
-        if (cf)                                                                                                                \
+        if (warp_form == 1) {                                                                                                  \
+            static bool wattr = false;                                                                                         \
+            if (!wattr) {                                                                                                      \
+                cudaFuncSetAttribute(gs_delta_block_warp_kernel<ORTHO, DAMP, WF>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                     (int)wsmem);                                                                              \
+                wattr = true;                                                                                                  \
+            }                                                                                                                  \
+            gs_delta_block_warp_kernel<ORTHO, DAMP, WF><<<1, TILE, wsmem, s>>>(c, pol, k, aux, alpha, esum, es, mu, mu_new,    \
+                                                                             eind, delta, b);                                 \
+        } else if (cf)                                                                                                         \
             gs_delta_block_table_kernel<ORTHO><<<1, TILE, GS_PAIRS * sizeof(double2), s>>>(c, pol, alpha, cf, esum, es, mu,     \
                                                                                          mu_new, eind, delta, b);             \
         else                                                                                                                   \
