@@ -701,7 +701,11 @@ static int repack(Ctx* c) {
         const int nclus = c->sorted.n_pad / 32;
         const int own = std::max(1, nclus / std::max(c->world, 1) + 1);
         const int ctas_x = (own + 3) / 4;
-        const int batches = (nclus / 2 + 1 + 31) / 32;
+        // Without polarization K1 is the critical path: slice down to one candidate offset per warp (small systems are
+        // bound by a warp's serial walk).  With polarization K1 runs beside the solve on the side stream and only has to
+        // finish before it does: whole batches of 32 offsets per slice, so that it takes few issue slots from K3 / K4.
+        const bool k1_critical = !(c->P.polarization && !c->P.rd_only);
+        const int batches = k1_critical ? nclus / 2 + 1 : (nclus / 2 + 1 + 31) / 32;
         c->pair_kslices = std::max(1, std::min(batches, (8 * sms + ctas_x - 1) / ctas_x));
         const int cols = pair_cluster_columns(c->sorted.n_pad, 0, own, c->pair_kslices);
         c->ntiles = 0;
@@ -1052,6 +1056,15 @@ static double* peer_buf(void* base, size_t cap, int parity) { return reinterpret
 static unsigned long long* peer_flags(void* base, size_t cap) {
     return reinterpret_cast<unsigned long long*>(reinterpret_cast<double*>(base) + 2 * 3 * cap);
 }
+// Which Jacobi contraction runs.  The symmetric kernel's work item is a 256 x 256 tile pair (~130 us of one CTA):
+// below ~8k polarizable atoms its grid does not fill the GPU and an evaluation costs one item per iteration however
+// small the system, while the row form with the j range fully split ((n/128)^2 CTAs of 128 x 128 pairs) finishes in
+// 10-60 us despite doing every pair twice.  Sharded runs always use the symmetric form (its exchange protocol).
+static bool sym_now(const Ctx* c) {
+    const char* v = getenv("MPMC_B200_SYM_MIN");  // read per call: the tests switch it inside one process
+    const int min_pad = v ? atoi(v) : 8192;
+    return c->use_sym && (c->world > 1 || c->pol.n_pad >= min_pad);
+}
 static bool peer_active(const Ctx* c) {
     return c->peer_ready && c->world > 1 && c->use_sym && (size_t)c->pol.n_pad == c->peer_cap;
 }
@@ -1129,7 +1142,7 @@ static int polar_update_sym(Ctx* c, int it) {
 static int polar_jacobi_pass(Ctx* c, int it) {
     const mpmc_b200_params& P = c->P;
     cudaStream_t st = c->stream;
-    if (c->use_sym) {
+    if (sym_now(c)) {
         if (polar_contract_sym(c)) return 10;
         if (c->world > 1) return 0;  // the caller all-reduces esum, then runs MPMC_STAGE_UPDATE
         return polar_update_sym(c, it);
@@ -1181,7 +1194,7 @@ static int polar_palmo_finish_sym(Ctx* c) {
 static int polar_palmo_pass(Ctx* c) {
     const mpmc_b200_params& P = c->P;
     const SubsetDev pol = c->pol.dev();
-    if (c->use_sym) {
+    if (sym_now(c)) {
         if (polar_contract_sym(c)) return 10;
         if (c->world > 1) return 0;  // all-reduce of esum, then MPMC_STAGE_PALMO_FINISH
         return polar_palmo_finish_sym(c);
@@ -1198,7 +1211,7 @@ static int polar_palmo_pass(Ctx* c) {
 // mu = new_mu | SOR | ESOR mix (thole_iterative.c:242-252), this shard's rows
 static int polar_commit(Ctx* c, int it) {
     if (peer_active(c) && !c->P.polar_palmo) return 0;  // committed by dipole_update_peer_kernel
-    const bool all = c->use_sym;  // symmetric K4: every rank updates every row (no dipole all-gather)
+    const bool all = sym_now(c);  // symmetric K4: every rank updates every row (no dipole all-gather)
     launch_dipole_commit(c->pol.dev(), update_opts(c->P, it), c->mu_old.p, c->mu_new.p, c->mu.p, all ? 0 : c->pb,
                          all ? c->pol.n_pad : c->pe, c->stream);
     c->launches++;
@@ -1720,7 +1733,11 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         CU(cudaEventCreate(&c->ev[p][0]));
         CU(cudaEventCreate(&c->ev[p][1]));
     }
-    CU(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    {   // lowest priority: the static field + dipole solve on the engine's stream are the critical path, K1 / K2 fill in
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        CU(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, lo));
+    }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     if (c->scalars.ensure(64)) FAIL(11, "cudaMalloc failed");

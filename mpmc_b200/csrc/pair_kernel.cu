@@ -350,7 +350,8 @@ void launch_pair_energy_clusters(const Cell& c, bool ortho, const SubsetDev& a, 
     const int nclus = a.n_pad / 32, K = nclus / 2;
     if (kslices < 1) kslices = 1;
     int kper = (K + 1 + kslices - 1) / kslices;
-    kper = ((kper + 31) / 32) * 32;  // whole candidate batches per slice
+    if (kper > 32) kper = ((kper + 31) / 32) * 32;  // whole candidate batches per slice; small systems: finer slices
+                                                    // (a warp's serial walk over its cluster pairs is the latency)
     kslices = (K + 1 + kper - 1) / kper;
     const double cull2 = (ortho && cull > 0.0) ? cull * cull : 0.0;  // the gap bound is orthorhombic only
     const BoxLen box = box_len(c);
@@ -380,7 +381,7 @@ int pair_cluster_columns(int n_pad_sorted, int clus_begin, int clus_end, int ksl
     const int nclus = n_pad_sorted / 32, K = nclus / 2;
     if (kslices < 1) kslices = 1;
     int kper = (K + 1 + kslices - 1) / kslices;
-    kper = ((kper + 31) / 32) * 32;
+    if (kper > 32) kper = ((kper + 31) / 32) * 32;
     kslices = (K + 1 + kper - 1) / kper;
     return kslices * (clus_end - clus_begin);
 }

@@ -24,6 +24,23 @@ def test_cuda_matches_reference_fixture(engine, name):
     assert engine.counters().kernel_launches > 0
 
 
+SYM_SMALL = ["mixed_default", "mixed_tri_default", "mixed_palmo", "mixed_sor", "mixed_esor", "mixed_precision", "mixed_rrms",
+             "mixed_wolf_full", "mixed_damp_off", "mixed_damp_linear", "h2_fluid_500", "h2_fluid_500_precision_palmo_rrms",
+             "ref_socmof"]
+
+
+@pytest.mark.parametrize("name", SYM_SMALL)
+def test_symmetric_contraction_on_small_fixtures(engine, name, monkeypatch):
+    """Below 8,192 padded polarizable atoms a single GPU uses the row form of K4 (latency); MPMC_B200_SYM_MIN=0 forces
+    the symmetric kernel so that its damping / wolf / triclinic / padding variants stay pinned to the reference fixtures."""
+    monkeypatch.setenv("MPMC_B200_SYM_MIN", "0")
+    s, exp = gu.load(name)
+    engine.set_system(s)
+    got = engine.energy()
+    gu.assert_energies(got.to_dict(), exp, rtol=1e-10, label=name)
+    gu.assert_atom_arrays(engine.atom_arrays(), exp, s, rtol=1e-10, label=name)
+
+
 @pytest.mark.parametrize("builder,kw", [
     (systems.h2_fluid, dict(n_atoms=4000)),
     (systems.co2_fluid, dict(n_mol=1500)),
