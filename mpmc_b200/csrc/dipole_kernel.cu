@@ -279,13 +279,15 @@ __global__ void dipole_update_kernel(int n, int np, const double* __restrict__ a
                                      const double* __restrict__ epart, int jsplits, const double* __restrict__ es,
                                      const double* __restrict__ mu, double* __restrict__ mu_old,
                                      double* __restrict__ mu_new, double* __restrict__ eind, double* __restrict__ rrms,
-                                     unsigned long long* __restrict__ max_err2_bits, int row_begin, int row_end) {
+                                     unsigned long long* __restrict__ max_err2_bits, int row_begin, int row_end,
+                                     double* mu_commit) {
     __shared__ double red[32];
     const int i = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
     double worst = 0.0;
     if (i < row_end && i < n) {
         const double al = alpha[i];
         double num = 0.0, den = 0.0;
+        const double wold = (mu_commit && o.esor) ? exp(-o.gamma * o.iteration) : 0.0;
         for (int cdim = 0; cdim < 3; cdim++) {
             double e = 0.0;
             for (int js = 0; js < jsplits; js++) e += epart[((size_t)js * 3 + cdim) * np + i];
@@ -298,6 +300,14 @@ __global__ void dipole_update_kernel(int n, int np, const double* __restrict__ a
             worst = fmax(worst, d * d);  // are_we_done_yet, thole_iterative.c:108-111
             num += d * d;
             den += nw * nw;
+            if (mu_commit) {  // commit fused (no palmo pass needs the old dipoles): thole_iterative.c:242-252
+                double v = nw;
+                if (o.sor)
+                    v = o.gamma * nw + (1.0 - o.gamma) * old;
+                else if (o.esor)
+                    v = (1.0 - wold) * nw + wold * old;
+                mu_commit[cdim * np + i] = v;
+            }
         }
         if (o.do_rrms) {  // calc_dipole_rrms, thole_iterative.c:69-77
             double v = sqrt(num / den);
@@ -452,11 +462,11 @@ void launch_dipole_init(const SubsetDev& pol, const double* ef_static, int atoms
 
 void launch_dipole_update(const SubsetDev& pol, const UpdateOpts& o, const double* epart, int jsplits, const double* es,
                           const double* mu, double* mu_old, double* mu_new, double* eind, double* rrms,
-                          unsigned long long* max_err2_bits, int row_begin, int row_end, cudaStream_t s) {
+                          unsigned long long* max_err2_bits, int row_begin, int row_end, cudaStream_t s, double* mu_commit) {
     const int rows = row_end - row_begin;
     if (rows <= 0) return;
     dipole_update_kernel<<<(rows + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pol.alpha, o, epart, jsplits, es, mu, mu_old,
-                                                          mu_new, eind, rrms, max_err2_bits, row_begin, row_end);
+                                                          mu_new, eind, rrms, max_err2_bits, row_begin, row_end, mu_commit);
 }
 
 void launch_dipole_commit(const SubsetDev& pol, const UpdateOpts& o, const double* mu_old, const double* mu_new, double* mu,

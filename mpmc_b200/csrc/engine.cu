@@ -1131,7 +1131,8 @@ static int polar_update_sym(Ctx* c, int it) {
                                   P.polar_palmo ? 0 : 1, c->stream);
     else
     launch_dipole_update(c->pol.dev(), update_opts(P, it), c->esum.p, 1, c->es.p, c->mu.p, c->mu_old.p, c->mu_new.p,
-                         c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr, 0, c->pol.n_pad, c->stream);
+                         c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr, 0, c->pol.n_pad, c->stream,
+                         P.polar_palmo ? nullptr : c->mu.p);
     c->launches++;
     CU(cudaGetLastError());
     return 0;
@@ -1156,7 +1157,8 @@ static int polar_jacobi_pass(Ctx* c, int it) {
                            c->epart.p, st);
     kev_mark(c);
     launch_dipole_update(pol, update_opts(P, it), c->epart.p, c->dipole_jsplits, c->es.p, c->mu.p, c->mu_old.p,
-                         c->mu_new.p, c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr, c->pb, c->pe, st);
+                         c->mu_new.p, c->eind.p, c->rrms.p, precision_mode ? errbits : nullptr, c->pb, c->pe, st,
+                         P.polar_palmo ? nullptr : c->mu.p);
     c->launches += 2;
     c->cnt.contractions += 1;
     CU(cudaGetLastError());
@@ -1210,7 +1212,7 @@ static int polar_palmo_pass(Ctx* c) {
 
 // mu = new_mu | SOR | ESOR mix (thole_iterative.c:242-252), this shard's rows
 static int polar_commit(Ctx* c, int it) {
-    if (peer_active(c) && !c->P.polar_palmo) return 0;  // committed by dipole_update_peer_kernel
+    if (!c->P.polar_palmo) return 0;  // committed by the update kernel itself (only a palmo pass needs the old dipoles)
     const bool all = sym_now(c);  // symmetric K4: every rank updates every row (no dipole all-gather)
     launch_dipole_commit(c->pol.dev(), update_opts(c->P, it), c->mu_old.p, c->mu_new.p, c->mu.p, all ? 0 : c->pb,
                          all ? c->pol.n_pad : c->pe, c->stream);

@@ -141,10 +141,11 @@ struct UpdateOpts {
     double gamma;
     int iteration;
 };
-// E_ind = sum_js epart; new_mu = alpha (E_s + E_ind); max (new-old)^2; rrms.  Does not touch mu.
+// E_ind = sum_js epart; new_mu = alpha (E_s + E_ind); max (new-old)^2; rrms.  Touches mu only when mu_commit is given.
 void launch_dipole_update(const SubsetDev& pol, const UpdateOpts& o, const double* epart, int jsplits, const double* es,
                           const double* mu, double* mu_old, double* mu_new, double* eind, double* rrms,
-                          unsigned long long* max_err2_bits, int row_begin, int row_end, cudaStream_t s);
+                          unsigned long long* max_err2_bits, int row_begin, int row_end, cudaStream_t s,
+                          double* mu_commit = nullptr /* == mu: commit the rows in the same kernel */);
 // Peer form: waits for every rank's flag, E_ind = sum_r src[r] (rank order), then the same update; with
 // `commit` the dipoles are committed in the same kernel (Jacobi without palmo).
 void launch_dipole_update_peer(const SubsetDev& pol, const UpdateOpts& o, const PeerWait& pw, const double* es, double* mu,
