@@ -14,6 +14,8 @@ from __future__ import annotations
 
 import json
 import os
+
+import numpy as np
 import subprocess
 import sys
 import tempfile
@@ -62,8 +64,16 @@ def main():
     quick = "--quick" in sys.argv
     uvt = "pressure 70.0\nh2_fugacity on\ninsert_probability 0.666\nmove_factor 0.001\nrot_factor 0.01\n"
     nvt = "move_factor 0.01\nrot_factor 0.01\n"
+    from tests import golden_util as gu
+
+    socmof, _ = gu.load("ref_socmof")  # the reference's shipped In-soc-MOF + 156 H2 system (1,236 atoms) as a flat fixture
+    first = np.r_[True, socmof.mol_id[1:] != socmof.mol_id[:-1]]
+    socmof.meta["atom_mass"] = np.where(first, socmof.mol_mass, 0.0)  # molecule masses on the first atom (as test_gpu_shim does)
     cases = [
         # name, system, ensemble, extra, (short, long) steps for the drop-in, (short, long) for the reference or None
+        ("socMOF+BSSP 1,236 atoms NVT, FH4, Jacobi x10 -- the system of the reference's only published timing "
+         "(0.478-0.492 s/step on a Xeon E5-2670 core, 0.136 s/step with its fp32 CUDA kernel; BASELINE.md 1)", socmof, "nvt", nvt,
+         (100, 4100), (2, 12)),
         ("h2_fluid_1000 NVT, Jacobi x10, FH4 (config 5, small N)", systems.h2_fluid(1000), "nvt", nvt, (100, 6100), (2, 42)),
         ("co2_fluid_12k NVT, LJ+Ewald, no polarization (config 2)", systems.co2_fluid(4096), "nvt", nvt, (50, 1550), (1, 3)),
         ("mof_h2_21k uVT, Jacobi x4, FH4, cutoff 8 A (config 3 shape: 128.4 x 42.8 x 42.8 A)",
@@ -71,6 +81,8 @@ def main():
         ("mof_h2_63k NVT, Jacobi x10 (config 4 system as a trajectory)", systems.mof_h2(), "nvt", nvt, (5, 125), None),
     ]
     if quick:
+        cases = cases[:1]
+    if "--only-socmof" in sys.argv:
         cases = cases[:1]
     for name, s, ens, extra, (a, b), ref in cases:
         v, err = steps_per_s(DROPIN, s, ens, a, b, extra, 900)
