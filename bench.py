@@ -369,8 +369,24 @@ def own_arm(args):
                                         69.0 * unordered / (c_ms * 1e-3) / lane_ops_per_s]
         roofline["pipe_frac_note"] = ("executed fp64 instr per unordered pair between 41 (all cluster pairs far) and 69 "
                                       "(all damped); ncu sm__pipe_fp64 utilisation of the same kernel: profiles/")
+    list_pairs = float(getattr(cnt, "pairs_induced_list", 0.0))
+    if s.params.polar_ewald_full and list_pairs > 0 and c_ms > 0:
+        # full-Ewald polarization: the per-pass kernel between the phase marks is the pair-list apply (K7), HBM-bound:
+        # 48-byte entries streamed once + 3 x 8 bytes of field written per polarizable atom (the mu_j gathers hit L2)
+        nbytes = 48.0 * list_pairs + 24.0 * cnt.n_polarizable
+        hbm = None
+        try:
+            hbm = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+            src = "MEASURED_PEAKS.json hbm_gbs (driver-measured copy bandwidth)"
+        except Exception:
+            hbm, src = 7700.0, "fallback: nominal HBM3e bandwidth of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+        ach = nbytes / (c_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": "induced_list_apply_kernel (K7, per solver pass)", "achieved": ach, "peak": hbm,
+                    "unit": "GB/s", "frac": ach / hbm, "traffic": None, "peak_source": src, "bytes_per_launch": nbytes,
+                    "list_pairs": list_pairs, "ms_per_launch": c_ms,
+                    "phase_ms": {k: float(np.mean(v)) for k, v in phases.items()}}
     prof = os.path.join(ROOT, "profiles", "k4_traffic.json")
-    if os.path.exists(prof):
+    if os.path.exists(prof) and roofline["bound"] == "fp64":
         try:
             roofline["traffic"] = json.load(open(prof)).get(args.workload)
         except Exception:

@@ -124,6 +124,7 @@ typedef struct mpmc_b200_counters {
     int n_atoms, n_polarizable;
     int kernel_launches;      /* kernels of THIS library launched by the last evaluation */
     int reserved;
+    double pairs_induced_list; /* polar_ewald_full: ordered in-cutoff polarizable pairs held in the pair list (0: on the fly) */
 } mpmc_b200_counters;
 
 typedef struct mpmc_b200_ctx mpmc_b200_ctx;

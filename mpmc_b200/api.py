@@ -143,6 +143,7 @@ class Counters(C.Structure):
         ("n_polarizable", C.c_int),
         ("kernel_launches", C.c_int),
         ("reserved", C.c_int),
+        ("pairs_induced_list", C.c_double),
     ]
 
     def to_dict(self) -> dict:

@@ -134,6 +134,12 @@ struct mpmc_b200_ctx {
     DevBuf<double> eic_np;           // [3][nonpol.n_pad]
     bool eic_np_valid = false;
     DevBuf<double> eind_np;          // [3][nonpol.n_pad]: ef_induced of the alpha == 0 atoms (full-Ewald polarization only)
+    // full-Ewald polarization: pair list of the real-space term, rebuilt by every energy() (ewald_full_kernel.cu PairEntry)
+    DevBuf<unsigned int> k7_cnt;
+    DevBuf<unsigned long long> k7_offs;
+    DevBuf<char> k7_list;
+    bool k7_list_on = false;
+    double k7_list_cap_gb = 16.0;    // MPMC_B200_K7_LIST_GB; 0 = always the on-the-fly kernel
     bool eind_np_valid = false;
     DevBuf<int2> tiles;
     int ntiles = 0;
@@ -897,8 +903,7 @@ static int run_structure_factor(Ctx* c, const Subset& sub, const DevBuf<double>&
         launch_recip_sf(make_cell(c->P), sub.dev(), kv, cb, ce, apc, c->sf_partial.p, st);
         c->launches++;
     }
-    launch_recip_finish(kv, c->sf_partial.p, (c->nk > 0 && sub.n > 0) ? mine : 0, scale, c->sf.p, energy_slot, kb, ke, st);
-    c->launches++;
+    c->launches += launch_recip_finish(kv, c->sf_partial.p, (c->nk > 0 && sub.n > 0) ? mine : 0, scale, c->sf.p, energy_slot, kb, ke, st);
     CU(cudaGetLastError());
     return 0;
 }
@@ -1240,13 +1245,17 @@ static int ewald_full_field(Ctx* c, const EwaldFullOpts& eo, const KVecDev& kv, 
     const Cell cell = make_cell(P);
     const SubsetDev pol = c->pol.dev();
     kev_mark(c);
-    const int js = launch_induced_real_clusters(cell, is_ortho(P), pol, eo, c->cbox.p, c->mu.p, c->dipole_jsplits, c->epart.p, st);
+    int js = 1;
+    if (c->k7_list_on)
+        launch_induced_list_apply(pol, c->k7_offs.p, c->k7_list.p, c->mu.p, c->epart.p, st);
+    else
+        js = launch_induced_real_clusters(cell, is_ortho(P), pol, eo, c->cbox.p, c->mu.p, c->dipole_jsplits, c->epart.p, st);
     kev_mark(c);
     const int chunks = launch_dipole_sf(cell, pol, kv, c->kvec.p, c->mu.p, apc, c->sf_partial.p, st);
-    launch_recip_finish(kv, c->sf_partial.p, chunks, 0.0, c->sf.p, nullptr, 0, 0, st);
-    launch_total_mu(pol, c->mu.p, c->scalars.p + S_TOTMU, st);
+    launch_recip_finish(kv, c->sf_partial.p, chunks, 0.0, c->sf.p, nullptr, 0, 0, st, pol.n, pol.n_pad, c->mu.p,
+                        c->scalars.p + S_TOTMU);  // + sum(mu) for the surface term
     launch_induced_finish(cell, pol, kv, c->kvec.p, c->sf.p, eo, c->epart.p, js, c->scalars.p + S_TOTMU, c->mu.p, c->eind.p, st);
-    c->launches += 5;
+    c->launches += 4;
     c->cnt.contractions += 1;
     CU(cudaGetLastError());
     return 0;
@@ -1275,6 +1284,31 @@ static int enqueue_ewald_full(Ctx* c) {
     if (c->sf_partial.ensure((size_t)std::max(chunks, 1) * 2 * std::max(c->nk, 1)) ||
         c->epart.ensure((size_t)c->dipole_jsplits * 3 * pp))
         FAIL(11, "cudaMalloc failed");
+    // Pair list of the real-space term: count, size, fill (one host sync per energy(); the solver passes then stream it).
+    // Above the memory cap (a fluid with cutoff = L/2 and 10^5 atoms) the tensor is re-evaluated on the fly every pass.
+    c->k7_list_on = false;
+    if (c->k7_list_cap_gb > 0.0 && (pp >> 5) <= 32 * CULL_MAX_BATCHES) {
+        const Cell cell = make_cell(P);
+        if (c->k7_cnt.ensure((size_t)4 * pp) || c->k7_offs.ensure((size_t)4 * pp + 1)) FAIL(11, "cudaMalloc failed");
+        launch_induced_list_count(cell, is_ortho(P), pol, eo, c->cbox.p, c->k7_cnt.p, c->k7_offs.p, st);
+        CU(cudaMemcpyAsync(c->h_scalars + 40, c->k7_offs.p + (size_t)4 * pp, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        unsigned long long total;
+        memcpy(&total, c->h_scalars + 40, sizeof(total));
+        const double bytes = (double)total * (double)induced_list_entry_bytes();
+        c->launches += 2;
+        c->cnt.pairs_induced_list = 0.0;
+        if (bytes <= c->k7_list_cap_gb * 1073741824.0) {
+            if (c->k7_list.ensure((size_t)std::max<unsigned long long>(total, 1) * induced_list_entry_bytes())) {
+                cudaGetLastError();  // not enough memory for the list: on-the-fly kernel
+            } else {
+                launch_induced_list_fill(cell, is_ortho(P), pol, eo, c->cbox.p, c->k7_offs.p, c->k7_list.p, st);
+                c->launches++;
+                c->k7_list_on = true;
+                c->cnt.pairs_induced_list = (double)total;
+            }
+        }
+    }
     // init_dipoles_ewald (:135-148): old_mu = 0, new_mu = mu = alpha E_s
     CU(cudaMemsetAsync(c->mu_old.p, 0, sizeof(double) * 3 * pp, st));
     CU(cudaMemcpyAsync(c->mu_new.p, c->mu.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToDevice, st));
@@ -1728,6 +1762,8 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         // MPMC_B200_CUTOFF=tiles selects the all-pairs tile form of K1 / K3 (no cluster culling)
         v = getenv("MPMC_B200_CUTOFF");
         c->use_clusters = !(v && strcmp(v, "tiles") == 0);
+        v = getenv("MPMC_B200_K7_LIST_GB");
+        if (v) c->k7_list_cap_gb = atof(v);
         v = getenv("MPMC_B200_GS");
         c->gs_delta = c->use_sym && !(v && strcmp(v, "panels") == 0);
     }
@@ -1770,6 +1806,9 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
                               &c->wolf_table, &c->scalars, &c->cbox, &c->sym_partI, &c->sym_partJ, &c->esum})
         b->release();
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();
+    c->k7_cnt.release();
+    c->k7_offs.release();
+    c->k7_list.release();
     c->tiles.release();
     c->charged.release();
     c->recip.release();

@@ -304,6 +304,197 @@ __global__ void ewald_palmo_finish_kernel(int n, int np, const double* __restric
     for (int d = 0; d < 3; d++) eic[d * np + i] = eind[d * np + i] - (mu_new[d * np + i] / al - es[d * np + i]);
 }
 
+
+// ---- pair list of the real-space term ---------------------------------------------------------------------------------
+// The tensor of an in-cutoff pair depends on the positions only, so erfc / exp / rsqrt are evaluated ONCE per energy():
+// a CSR list (row = atom i, four consecutive segments = the four warps of its cluster's CTA) holds, per in-cutoff pair,
+// the minimum-image vector, the two coefficients w1 = s1 / r^3, w2 = 3 s2 / r^5 and the partner index (48 bytes).  Every
+// solver pass then streams the list (HBM / L2 bound, ~25 fp64 instructions per pair) instead of re-evaluating ~400.
+// Traversal, and therefore the order of every sum, is the deterministic pass-mask walk of induced_real_cluster_kernel.
+struct PairEntry {
+    double dx, dy, dz, w1, w2;
+    long long j;
+};
+
+// `sqrt(r2) > cutoff` (polar_ewald.c:188) without the square root except in a 1e-12-wide shell around the cutoff
+struct CutTest {
+    double cut, lo, hi;
+};
+__device__ __forceinline__ bool inside_cutoff(const CutTest& t, double r2) {
+    if (r2 < t.lo) return true;
+    if (r2 > t.hi) return false;
+    return !(sqrt(r2) > t.cut);
+}
+
+struct QueuedPair {
+    double dx, dy, dz;
+    unsigned long long dest;
+    int j, pad;
+};
+
+// erfc / exp evaluated for ONE pair per lane (dense: the queue below holds in-cutoff pairs only)
+__device__ __forceinline__ void list_emit(const EwaldFullOpts& k, const QueuedPair& q, PairEntry* __restrict__ list) {
+    const double r2 = q.dx * q.dx + q.dy * q.dy + q.dz * q.dz;
+    const double rr = sqrt(r2);
+    const double ir = 1.0 / rr, ir3 = ir * ir * ir, ir5 = ir * ir * ir3;
+    const double aa = k.a;
+    const double erfcar = erfc(aa * rr), ex2 = exp(-aa * aa * r2);
+    const double t = k.damp * rr, et = exp(-t);
+    const double df2 = (1.0 + t + 0.5 * t * t) * et;
+    const double df3 = (1.0 + t + 0.5 * t * t + t * t * t / 6.0) * et;
+    const double g = 2.0 * aa * rr * kOneOverSqrtPi * ex2;
+    const double s1 = erfcar + g - df2;
+    const double s2 = erfcar + g + 4.0 * aa * aa * aa * rr * r2 / 3.0 * kOneOverSqrtPi * ex2 - df3;
+    PairEntry e;
+    e.dx = q.dx;
+    e.dy = q.dy;
+    e.dz = q.dz;
+    e.w1 = s1 * ir3;
+    e.w2 = 3.0 * s2 * ir5;
+    e.j = q.j;
+    list[q.dest] = e;
+}
+
+// FILL = false: counts per (atom, warp slot).  FILL = true: the same walk; the lanes of a warp own the 32 atoms of the
+// i-cluster and meet an in-cutoff partner in ~1 of 6 tests, so the in-cutoff pairs are first compacted (ballot + prefix)
+// into a 64-entry ring per warp and the erfc / exp body runs on 32 queued pairs at a time, one per lane.
+template <bool ORTHO, bool FILL>
+__global__ void __launch_bounds__(TILE) induced_list_kernel(Cell c, SubsetDev a, EwaldFullOpts k, BoxLen box,
+                                                            const double* __restrict__ cbox, double cull2,
+                                                            const unsigned long long* __restrict__ offs,
+                                                            unsigned int* __restrict__ cnt, PairEntry* __restrict__ list) {
+    __shared__ double jx[4][32], jy[4][32], jz[4][32];
+    __shared__ unsigned smask[CULL_MAX_BATCHES];
+    __shared__ QueuedPair ring[FILL ? 4 : 1][FILL ? 64 : 1];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int nclus = a.n_pad >> 5;
+    const int ci = blockIdx.x;
+    if (ci >= nclus) return;
+    const int i = ci * 32 + lane;
+    const bool live = i < a.n;
+    const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
+    const int nb = min((nclus + 31) >> 5, CULL_MAX_BATCHES);
+    cull_masks(box, cbox, nclus, ci, cull2, 0, nb, smask);
+    CutTest ct;
+    ct.cut = c.cutoff;
+    ct.lo = c.cutoff * c.cutoff * (1.0 - 1e-12);
+    ct.hi = c.cutoff * c.cutoff * (1.0 + 1e-12);
+    unsigned int n = 0;
+    unsigned long long at = FILL ? offs[(size_t)i * 4 + w] : 0ull;
+    int head = 0, qn = 0;  // warp-uniform
+    const unsigned lt = (1u << lane) - 1u;
+    int pos = 0;
+    for (int b = 0; b < nb; b++) {
+        unsigned mask = smask[b];
+        while (mask) {
+            const int bit = __ffs(mask) - 1;
+            mask &= mask - 1;
+            if (((pos++) & 3) != w) continue;
+            const int cj = b * 32 + bit;
+            __syncwarp();
+            jx[w][lane] = a.x[cj * 32 + lane];
+            jy[w][lane] = a.y[cj * 32 + lane];
+            jz[w][lane] = a.z[cj * 32 + lane];
+            __syncwarp();
+            const int jn = min(32, a.n - cj * 32);
+            for (int s = 0; s < jn; s++) {
+                double dx = xi - jx[w][s], dy = yi - jy[w][s], dz = zi - jz[w][s];
+                min_image<ORTHO>(c, dx, dy, dz);
+                const double r2 = dx * dx + dy * dy + dz * dz;
+                const bool in = live && !(cj == ci && s == lane) && inside_cutoff(ct, r2);
+                if (!FILL) {
+                    n += in ? 1u : 0u;
+                } else {
+                    const unsigned m = __ballot_sync(0xffffffffu, in);
+                    if (m == 0u) continue;
+                    if (in) {
+                        QueuedPair& q = ring[w][(head + qn + __popc(m & lt)) & 63];
+                        q.dx = dx;
+                        q.dy = dy;
+                        q.dz = dz;
+                        q.dest = at++;
+                        q.j = cj * 32 + s;
+                    }
+                    qn += __popc(m);
+                    if (qn >= 32) {
+                        __syncwarp();
+                        list_emit(k, ring[w][(head + lane) & 63], list);
+                        __syncwarp();
+                        head = (head + 32) & 63;
+                        qn -= 32;
+                    }
+                }
+            }
+        }
+    }
+    if (FILL) {
+        __syncwarp();
+        if (lane < qn) list_emit(k, ring[w][(head + lane) & 63], list);
+    } else
+        cnt[(size_t)i * 4 + w] = n;
+}
+
+// exclusive scan of m counters (one CTA; m = 4 n_pad ~ 2e5): offs[q] = sum_{p<q} cnt[p], offs[m] = total
+__global__ void __launch_bounds__(1024) list_scan_kernel(const unsigned int* __restrict__ cnt, int m,
+                                                         unsigned long long* __restrict__ offs) {
+    __shared__ unsigned long long part[1024];
+    const int t = threadIdx.x;
+    const int chunk = (m + 1023) / 1024;
+    const int b = t * chunk, e = min(b + chunk, m);
+    unsigned long long sum = 0;
+    for (int q = b; q < e; q++) sum += cnt[q];
+    part[t] = sum;
+    __syncthreads();
+    if (t == 0) {
+        unsigned long long run = 0;
+        for (int q = 0; q < 1024; q++) {
+            const unsigned long long v = part[q];
+            part[q] = run;
+            run += v;
+        }
+        offs[m] = run;
+    }
+    __syncthreads();
+    unsigned long long run = part[t];
+    for (int q = b; q < e; q++) {
+        offs[q] = run;
+        run += cnt[q];
+    }
+}
+
+// one warp per atom: E_i = sum over its list entries of w2 (d . mu_j) d - w1 mu_j; lanes stride the entries, fixed-order
+// butterfly reduction
+__global__ void __launch_bounds__(256) induced_list_apply_kernel(int n, int np, const unsigned long long* __restrict__ offs,
+                                                                 const PairEntry* __restrict__ list,
+                                                                 const double* __restrict__ mu, double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (i >= np) return;
+    double ex = 0.0, ey = 0.0, ez = 0.0;
+    if (i < n) {
+        const unsigned long long b = offs[(size_t)i * 4], e = offs[(size_t)i * 4 + 4];
+        for (unsigned long long q = b + lane; q < e; q += 32) {
+            const PairEntry p = list[q];
+            const double mx = mu[p.j], my = mu[np + p.j], mz = mu[2 * (size_t)np + p.j];
+            const double dm = (p.dx * mx + p.dy * my + p.dz * mz) * p.w2;
+            ex += dm * p.dx - p.w1 * mx;
+            ey += dm * p.dy - p.w1 * my;
+            ez += dm * p.dz - p.w1 * mz;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ex += __shfl_xor_sync(0xffffffffu, ex, o);
+        ey += __shfl_xor_sync(0xffffffffu, ey, o);
+        ez += __shfl_xor_sync(0xffffffffu, ez, o);
+    }
+    if (lane == 0) {
+        out[i] = ex;
+        out[np + i] = ey;
+        out[2 * (size_t)np + i] = ez;
+    }
+}
+
 }  // namespace
 
 int launch_induced_real_clusters(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
@@ -371,6 +562,45 @@ void launch_ewald_palmo_finish(const SubsetDev& pol, const double* es, const dou
                                cudaStream_t s) {
     if (pol.n <= 0) return;
     ewald_palmo_finish_kernel<<<(pol.n + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pol.alpha, es, eind, mu_new, eic);
+}
+
+
+// ---- pair-list form of the real-space term (see PairEntry)
+size_t induced_list_entry_bytes() { return sizeof(PairEntry); }
+
+// counts per (atom, warp slot) and their exclusive scan: cnt [4 n_pad] uints, offs [4 n_pad + 1] u64 (offs[4 n_pad] = total)
+void launch_induced_list_count(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
+                               unsigned int* cnt, unsigned long long* offs, cudaStream_t s) {
+    const int nclus = pol.n_pad / 32;
+    if (nclus <= 0) return;
+    const double cull = c.cutoff + 1e-6;
+    const double cull2 = ortho ? cull * cull : 0.0;
+    if (ortho)
+        induced_list_kernel<true, false><<<nclus, TILE, 0, s>>>(c, pol, o, box_len(c), cbox, cull2, offs, cnt, nullptr);
+    else
+        induced_list_kernel<false, false><<<nclus, TILE, 0, s>>>(c, pol, o, box_len(c), cbox, cull2, offs, cnt, nullptr);
+    list_scan_kernel<<<1, 1024, 0, s>>>(cnt, 4 * pol.n_pad, offs);
+}
+
+void launch_induced_list_fill(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
+                              const unsigned long long* offs, void* list, cudaStream_t s) {
+    const int nclus = pol.n_pad / 32;
+    if (nclus <= 0) return;
+    const double cull = c.cutoff + 1e-6;
+    const double cull2 = ortho ? cull * cull : 0.0;
+    PairEntry* l = reinterpret_cast<PairEntry*>(list);
+    if (ortho)
+        induced_list_kernel<true, true><<<nclus, TILE, 0, s>>>(c, pol, o, box_len(c), cbox, cull2, offs, nullptr, l);
+    else
+        induced_list_kernel<false, true><<<nclus, TILE, 0, s>>>(c, pol, o, box_len(c), cbox, cull2, offs, nullptr, l);
+}
+
+void launch_induced_list_apply(const SubsetDev& pol, const unsigned long long* offs, const void* list, const double* mu,
+                               double* part, cudaStream_t s) {
+    if (pol.n_pad <= 0) return;
+    const long long threads = (long long)pol.n_pad * 32;
+    induced_list_apply_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(pol.n, pol.n_pad, offs,
+                                                                              reinterpret_cast<const PairEntry*>(list), mu, part);
 }
 
 }  // namespace mpmc

@@ -61,9 +61,12 @@ struct KVecDev {
 };
 void launch_recip_sf(const Cell& c, const SubsetDev& atoms, const KVecDev& kv, int chunk_begin, int chunk_end,
                      int atoms_per_chunk, double* sf_partial /*[nchunks][2][nk]*/, cudaStream_t s);
-// energy_out = scale * sum_{k in [k_begin,k_end)} w_k |S(k)|^2 : the k-vector range is this shard's share
-void launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale,
-                         double* sf /*[2][nk]*/, double* energy_out, int k_begin, int k_end, cudaStream_t s);
+// sf = sum over chunks (always written); energy_out (optional) = scale * sum_{k in [k_begin,k_end)} w_k |S(k)|^2 : the
+// k-vector range is this shard's share.  mu (optional, [3][mu_np]): mu_total[3] = sum of the first mu_n dipoles, in the same
+// launch.  Returns the number of kernels launched.
+int launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale,
+                        double* sf /*[2][nk]*/, double* energy_out, int k_begin, int k_end, cudaStream_t s, int mu_n = 0,
+                        int mu_np = 0, const double* mu = nullptr, double* mu_total = nullptr);
 // recip_term() of the Ewald static field (src/polarization/polar_ewald.c:78-132)
 void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, const double* kvec /*[3][nk]*/,
                         const double* sf, double scale, int row_begin, int row_end, double* ef /*[3][n_pad]*/,
@@ -193,6 +196,15 @@ struct EwaldFullOpts {
 // written to part [slices][3][n_pad]
 int launch_induced_real_clusters(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
                                  const double* mu, int jsplits, double* part, cudaStream_t s);
+// Pair-list form of the same term: erfc / exp / rsqrt once per energy(), every pass streams 48-byte entries.
+// count -> (host reads offs[4 n_pad] = total, sizes `list`) -> fill -> apply per pass (part [3][n_pad], one slice).
+size_t induced_list_entry_bytes();
+void launch_induced_list_count(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
+                               unsigned int* cnt, unsigned long long* offs, cudaStream_t s);
+void launch_induced_list_fill(const Cell& c, bool ortho, const SubsetDev& pol, const EwaldFullOpts& o, const double* cbox,
+                              const unsigned long long* offs, void* list, cudaStream_t s);
+void launch_induced_list_apply(const SubsetDev& pol, const unsigned long long* offs, const void* list, const double* mu,
+                               double* part, cudaStream_t s);
 // P(k) = sum_j (k.mu_j) e^{ik.r_j}: per-chunk partials [chunks][2][nk] (sum with launch_recip_finish); returns chunks
 int launch_dipole_sf(const Cell& c, const SubsetDev& pol, const KVecDev& kv, const double* kvec, const double* mu,
                      int atoms_per_chunk, double* sf_partial, cudaStream_t s);

@@ -86,27 +86,59 @@ __global__ void __launch_bounds__(RC_THREADS) recip_sf_kernel(Cell c, SubsetDev 
     }
 }
 
-// S(k) = sum over chunks (chunk order); E = scale * sum_k w_k |S(k)|^2, k in list order per thread
-// then fixed-order block reduction.
-__global__ void __launch_bounds__(1024) recip_finish_kernel(KVecDev kv, const double* __restrict__ sf_partial, int nchunks,
-                                                            double scale, double* __restrict__ sf,
+// S(k) = sum over chunks.  One CTA per 32 k-vectors: thread (kx, cy) adds the chunks cy, cy + 32, ... of its k-vector
+// (independent loads: the serial one-thread-per-k form waited nchunks x one memory latency, 136 us at 300 chunks),
+// then the 32 partials of a k-vector are added in cy order.  The CTA behind the last k block, if `mu` is given, sums the
+// three components of the dipoles (full-Ewald polarization: the surface term needs sum(mu) in the same pass).
+__global__ void __launch_bounds__(1024) chunk_sum_kernel(int nk, const double* __restrict__ sf_partial, int nchunks,
+                                                         double* __restrict__ sf, int kblocks, int mu_n, int mu_np,
+                                                         const double* __restrict__ mu, double* __restrict__ mu_total) {
+    __shared__ double red[2][32][33];
+    const int kx = threadIdx.x & 31, cy = threadIdx.x >> 5;
+    if ((int)blockIdx.x >= kblocks) {
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+        for (int i = threadIdx.x; i < mu_n; i += 1024) {
+            a0 += mu[i];
+            a1 += mu[mu_np + i];
+            a2 += mu[2 * (size_t)mu_np + i];
+        }
+        double* scratch = &red[0][0][0];
+        a0 = block_reduce<0>(a0, scratch);
+        if (threadIdx.x == 0) mu_total[0] = a0;
+        a1 = block_reduce<0>(a1, scratch);
+        if (threadIdx.x == 0) mu_total[1] = a1;
+        a2 = block_reduce<0>(a2, scratch);
+        if (threadIdx.x == 0) mu_total[2] = a2;
+        return;
+    }
+    const int ik = blockIdx.x * 32 + kx;
+    double re = 0.0, im = 0.0;
+    if (ik < nk)
+        for (int ch = cy; ch < nchunks; ch += 32) {
+            re += sf_partial[(size_t)ch * 2 * nk + ik];
+            im += sf_partial[(size_t)ch * 2 * nk + nk + ik];
+        }
+    red[0][cy][kx] = re;
+    red[1][cy][kx] = im;
+    __syncthreads();
+    if (cy < 2 && ik < nk) {  // warp 0: real parts, warp 1: imaginary parts
+        double v = 0.0;
+        for (int q = 0; q < 32; q++) v += red[cy][q][kx];
+        sf[cy * nk + ik] = v;
+    }
+}
+
+// E = scale * sum_k w_k |S(k)|^2 over this shard's k-vectors: k in list order per thread, fixed-order block reduction
+__global__ void __launch_bounds__(1024) recip_energy_kernel(KVecDev kv, const double* __restrict__ sf, double scale,
                                                             double* __restrict__ energy_out, int k_begin, int k_end) {
     __shared__ double red[32];
     double acc = 0.0;
-    for (int ik = threadIdx.x; ik < kv.nk; ik += blockDim.x) {
-        double re = 0.0, im = 0.0;
-        for (int ch = 0; ch < nchunks; ch++) {
-            re += sf_partial[(size_t)ch * 2 * kv.nk + ik];
-            im += sf_partial[(size_t)ch * 2 * kv.nk + kv.nk + ik];
-        }
-        if (sf) {
-            sf[ik] = re;
-            sf[kv.nk + ik] = im;
-        }
-        if (ik >= k_begin && ik < k_end) acc += kv.weight[ik] * (re * re + im * im);  // this shard's k-vectors
+    for (int ik = k_begin + threadIdx.x; ik < k_end; ik += blockDim.x) {
+        const double re = sf[ik], im = sf[kv.nk + ik];
+        acc += kv.weight[ik] * (re * re + im * im);
     }
     double v = block_reduce<0>(acc, red);
-    if (threadIdx.x == 0 && energy_out) *energy_out = v * scale;
+    if (threadIdx.x == 0) *energy_out = v * scale;
 }
 
 // Ewald static field, reciprocal part: for every atom i (frozen and uncharged included)
@@ -166,9 +198,20 @@ void launch_recip_sf(const Cell& c, const SubsetDev& atoms, const KVecDev& kv, i
     recip_sf_kernel<<<n, RC_THREADS, smem, s>>>(c, atoms, kv, chunk_begin, atoms_per_chunk, sf_partial);
 }
 
-void launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale, double* sf,
-                         double* energy_out, int k_begin, int k_end, cudaStream_t s) {
-    recip_finish_kernel<<<1, 1024, 0, s>>>(kv, sf_partial, nchunks, scale, sf, energy_out, k_begin, k_end);
+int launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale, double* sf,
+                        double* energy_out, int k_begin, int k_end, cudaStream_t s, int mu_n, int mu_np, const double* mu,
+                        double* mu_total) {
+    const int kblocks = (kv.nk + 31) / 32;
+    int launches = 0;
+    if (kblocks + (mu ? 1 : 0) > 0) {
+        chunk_sum_kernel<<<kblocks + (mu ? 1 : 0), 1024, 0, s>>>(kv.nk, sf_partial, nchunks, sf, kblocks, mu_n, mu_np, mu, mu_total);
+        launches++;
+    }
+    if (energy_out) {
+        recip_energy_kernel<<<1, 1024, 0, s>>>(kv, sf, scale, energy_out, k_begin, k_end);
+        launches++;
+    }
+    return launches;
 }
 
 void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, const double* kvec, const double* sf,
