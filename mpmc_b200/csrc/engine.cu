@@ -139,6 +139,7 @@ struct mpmc_b200_ctx {
     DevBuf<unsigned long long> k7_offs;
     DevBuf<char> k7_list;
     bool k7_list_on = false;
+    bool k7_grouped_sf = true;       // MPMC_B200_K7_SF=plain: one thread per k-vector
     double k7_list_cap_gb = 16.0;    // MPMC_B200_K7_LIST_GB; 0 = always the on-the-fly kernel
     bool eind_np_valid = false;
     DevBuf<int2> tiles;
@@ -148,6 +149,8 @@ struct mpmc_b200_ctx {
 
     // reciprocal space
     DevBuf<int> kl;
+    DevBuf<int4> kgroups;  // (l0, l1) runs of the k list, see build_kvectors
+    int nkgroups = 0, kgroup_max = 0;
     DevBuf<double> kweight, kweight_field, kvec, sf_partial, sf;
     int nk = 0;
     bool kdirty = true;
@@ -513,6 +516,22 @@ static int build_kvectors(Ctx* c) {
             l[p * nk + ik] = ll[p];
             kv[p * nk + ik] = k[p];
         }
+    }
+    // (l0, l1) groups of the list (runs of consecutive l2), largest first: dipole_sf_grouped_kernel
+    {
+        std::vector<int4> groups;
+        int maxc = 0;
+        for (int ik = 0; ik < nk;) {
+            int e = ik + 1;
+            while (e < nk && l0[e] == l0[ik] && l1[e] == l1[ik] && l2[e] == l2[e - 1] + 1) e++;
+            groups.push_back(make_int4(ik, l0[ik], l1[ik], (l2[ik] + 64) | ((e - ik) << 8)));
+            maxc = std::max(maxc, e - ik);
+            ik = e;
+        }
+        std::stable_sort(groups.begin(), groups.end(), [](const int4& a, const int4& b) { return (a.w >> 8) > (b.w >> 8); });
+        c->nkgroups = (int)groups.size();
+        c->kgroup_max = maxc;
+        if (!groups.empty() && upload(c->kgroups, groups, c->stream)) return 11;
     }
     c->nk = nk;
     if (upload(c->kl, l, c->stream) || upload(c->kweight, w, c->stream) || upload(c->kweight_field, wf, c->stream) ||
@@ -1251,7 +1270,11 @@ static int ewald_full_field(Ctx* c, const EwaldFullOpts& eo, const KVecDev& kv, 
     else
         js = launch_induced_real_clusters(cell, is_ortho(P), pol, eo, c->cbox.p, c->mu.p, c->dipole_jsplits, c->epart.p, st);
     kev_mark(c);
-    const int chunks = launch_dipole_sf(cell, pol, kv, c->kvec.p, c->mu.p, apc, c->sf_partial.p, st);
+    KGroupsDev kg;
+    kg.ngroups = c->nkgroups;
+    kg.max_count = c->kgroup_max;
+    kg.groups = c->kgroups.p;
+    const int chunks = launch_dipole_sf(cell, pol, kv, c->kvec.p, c->mu.p, apc, c->sf_partial.p, st, c->k7_grouped_sf ? &kg : nullptr);
     launch_recip_finish(kv, c->sf_partial.p, chunks, 0.0, c->sf.p, nullptr, 0, 0, st, pol.n, pol.n_pad, c->mu.p,
                         c->scalars.p + S_TOTMU);  // + sum(mu) for the surface term
     launch_induced_finish(cell, pol, kv, c->kvec.p, c->sf.p, eo, c->epart.p, js, c->scalars.p + S_TOTMU, c->mu.p, c->eind.p, st);
@@ -1279,7 +1302,11 @@ static int enqueue_ewald_full(Ctx* c) {
     kv.weight = c->kweight_field.p;
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
-    const int apc = std::max(64, round_up((c->pol.n + 2 * sms - 1) / (2 * sms), 64));
+    // chunks of the dipole structure factor: the grouped kernel holds one 384..512-thread CTA per SM (register-bound), so
+    // one chunk per SM; the per-k kernel two
+    const bool grouped = c->k7_grouped_sf && c->nkgroups > 0 && c->kgroup_max <= 15 && ((c->nkgroups + 31) / 32) * 32 * 4 <= 512;
+    const int per = grouped ? sms : 2 * sms;
+    const int apc = std::max(64, round_up((c->pol.n + per - 1) / per, 64));
     const int chunks = (c->pol.n + apc - 1) / apc;
     if (c->sf_partial.ensure((size_t)std::max(chunks, 1) * 2 * std::max(c->nk, 1)) ||
         c->epart.ensure((size_t)c->dipole_jsplits * 3 * pp))
@@ -1762,6 +1789,8 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         // MPMC_B200_CUTOFF=tiles selects the all-pairs tile form of K1 / K3 (no cluster culling)
         v = getenv("MPMC_B200_CUTOFF");
         c->use_clusters = !(v && strcmp(v, "tiles") == 0);
+        v = getenv("MPMC_B200_K7_SF");
+        c->k7_grouped_sf = !(v && strcmp(v, "plain") == 0);
         v = getenv("MPMC_B200_K7_LIST_GB");
         if (v) c->k7_list_cap_gb = atof(v);
         v = getenv("MPMC_B200_GS");
@@ -1806,6 +1835,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
                               &c->wolf_table, &c->scalars, &c->cbox, &c->sym_partI, &c->sym_partJ, &c->esum})
         b->release();
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();
+    c->kgroups.release();
     c->k7_cnt.release();
     c->k7_offs.release();
     c->k7_list.release();

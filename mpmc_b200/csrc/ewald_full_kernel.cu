@@ -26,6 +26,10 @@ namespace {
 constexpr double kOneOverSqrtPi = 0.5641895835477562869480794515607725858440506293289988;
 constexpr double kSqrtPiRef = 1.77245385091;
 
+__device__ __forceinline__ double flip_sign_if(double v, bool neg) {
+    return __hiloint2double(__double2hiint(v) ^ (neg ? 0x80000000 : 0), __double2loint(v));
+}
+
 struct JRec {
     double x, y, z, mx, my, mz;
     int valid, pad;
@@ -191,6 +195,116 @@ __global__ void __launch_bounds__(DS_THREADS) dipole_sf_kernel(Cell c, SubsetDev
     }
 }
 
+// Grouped form of the same sum (kmax <= 7): one thread per (l0, l1) GROUP of the lexicographic k list -- its k-vectors
+// differ only in l2 (a contiguous run l2 = d0 .. d0 + count - 1, count <= 15) -- so the phase product of the first two
+// axes and l0 M0 + l1 M1 (k . mu = sum_q l_q M_q with M_q = 2 pi sum_p R[p][q] mu_p) are formed once per (group, atom):
+// 7 executed fp64 instructions per (k, atom) + 6 per (group, atom) against 17 in dipole_sf_kernel.  Groups arrive
+// sorted by count (engine.cu:build_kvectors) so the lanes of a warp run the same number of l2 steps; SG_SUB threads
+// share a group (atoms aa = sub, sub + SG_SUB, ... of every 64-atom batch) and are added in sub order at the end.
+// Phase tables: [atom][axis][l] (conflict-free for lanes with different l), e^{i l theta} by recurrence from l = 1.
+constexpr int SG_MAXD = 15;
+constexpr int SG_ATOMS = 64;
+constexpr int SG_SUB = 4;
+
+__global__ void __launch_bounds__(512) dipole_sf_grouped_kernel(Cell c, SubsetDev at, int nk, int nl, int ngroups, int gthreads,
+                                                                const int4* __restrict__ groups,
+                                                                const double* __restrict__ mu, int atoms_per_chunk,
+                                                                double* __restrict__ sf_partial) {
+    extern __shared__ double smem[];
+    const int ST = 3 * nl, np = at.n_pad;
+    double* tcos = smem;                    // [SG_ATOMS][3 nl]
+    double* tsin = tcos + SG_ATOMS * ST;
+    double* tm = tsin + SG_ATOMS * ST;      // [SG_ATOMS][3]: M_q
+    const int gi = threadIdx.x % gthreads, sub = threadIdx.x / gthreads;
+    const bool has = gi < ngroups;
+    const int4 g = has ? groups[gi] : make_int4(0, 0, 0, 0);
+    const int l0 = g.y, l1 = g.z, d0 = (g.w & 0xff) - 64, count = has ? (g.w >> 8) : 0;
+    const int wmax = __reduce_max_sync(0xffffffffu, count);
+    const int al1 = abs(l1);
+    const double l0d = (double)l0, l1d = (double)l1;
+    double re[SG_MAXD], im[SG_MAXD];
+#pragma unroll
+    for (int q = 0; q < SG_MAXD; q++) re[q] = im[q] = 0.0;
+    const int a0 = blockIdx.x * atoms_per_chunk;
+    const int a1 = min(a0 + atoms_per_chunk, at.n);
+    for (int base = a0; base < a1; base += SG_ATOMS) {
+        const int cnt = min(SG_ATOMS, a1 - base);
+        __syncthreads();
+        for (int w = threadIdx.x; w < 3 * SG_ATOMS; w += blockDim.x) {
+            const int aa = w % SG_ATOMS, ax = w / SG_ATOMS;
+            double c1 = 1.0, s1 = 0.0, m = 0.0;
+            if (aa < cnt) {
+                const int gidx = base + aa;
+                const double sfrac = c.R[0][ax] * at.x[gidx] + c.R[1][ax] * at.y[gidx] + c.R[2][ax] * at.z[gidx];
+                sincospi(2.0 * sfrac, &s1, &c1);
+                m = 2.0 * M_PI * (c.R[0][ax] * mu[gidx] + c.R[1][ax] * mu[np + gidx] + c.R[2][ax] * mu[2 * (size_t)np + gidx]);
+            }
+            double cl = 1.0, sl = 0.0;
+            double* tc = tcos + aa * ST + ax * nl;
+            double* ts = tsin + aa * ST + ax * nl;
+            for (int l = 0; l < nl; l++) {
+                tc[l] = cl;
+                ts[l] = sl;
+                const double cn = cl * c1 - sl * s1;
+                sl = sl * c1 + cl * s1;
+                cl = cn;
+            }
+            tm[aa * 3 + ax] = m;
+        }
+        __syncthreads();
+        if (wmax > 0)
+            for (int aa = sub; aa < cnt; aa += SG_SUB) {
+                const double* tc = tcos + aa * ST;
+                const double* ts = tsin + aa * ST;
+                const double c0 = tc[l0], s0 = ts[l0];
+                const double c1 = tc[nl + al1], s1 = flip_sign_if(ts[nl + al1], l1 < 0);
+                const double c01 = c0 * c1 - s0 * s1, s01 = s0 * c1 + c0 * s1;
+                const double m2 = tm[aa * 3 + 2];
+                const double km01 = l0d * tm[aa * 3] + l1d * tm[aa * 3 + 1];
+#pragma unroll
+                for (int q = 0; q < SG_MAXD; q++) {
+                    if (q < wmax) {  // warp-uniform
+                        const int d = d0 + q, ad = min(abs(d), nl - 1);
+                        const double c2 = tc[2 * nl + ad], s2 = flip_sign_if(ts[2 * nl + ad], d < 0);
+                        const double cc = c01 * c2 - s01 * s2, ss = s01 * c2 + c01 * s2;
+                        const double km = km01 + (double)d * m2;
+                        re[q] += km * cc;
+                        im[q] += km * ss;
+                    }
+                }
+            }
+    }
+    // add the SG_SUB partial sums of a group in sub order (staged through the table memory)
+    double* stage = smem;  // [2 SG_MAXD][gthreads]
+    for (int r = 1; r < SG_SUB; r++) {
+        __syncthreads();
+        if (sub == r) {
+#pragma unroll
+            for (int q = 0; q < SG_MAXD; q++) {
+                stage[(2 * q) * gthreads + gi] = re[q];
+                stage[(2 * q + 1) * gthreads + gi] = im[q];
+            }
+        }
+        __syncthreads();
+        if (sub == 0) {
+#pragma unroll
+            for (int q = 0; q < SG_MAXD; q++) {
+                re[q] += stage[(2 * q) * gthreads + gi];
+                im[q] += stage[(2 * q + 1) * gthreads + gi];
+            }
+        }
+    }
+    if (sub == 0 && has) {
+        double* out = sf_partial + (size_t)blockIdx.x * 2 * nk;
+#pragma unroll
+        for (int q = 0; q < SG_MAXD; q++)
+            if (q < count) {
+                out[g.x + q] = re[q];
+                out[nk + g.x + q] = im[q];
+            }
+    }
+}
+
 // sum of the dipoles (polar_ewald.c:303-307), one CTA, fixed order
 __global__ void __launch_bounds__(1024) total_mu_kernel(int n, int np, const double* __restrict__ mu, double* __restrict__ out) {
     __shared__ double red[32];
@@ -206,39 +320,66 @@ __global__ void __launch_bounds__(1024) total_mu_kernel(int n, int np, const dou
 // ef_induced of the rows of `rows`: real-space partial rows (if any) + the reciprocal term
 //   g_i = sum_k w_k ( -sin(k.r_i) Im P(k) - cos(k.r_i) Re P(k) ),  w_k = scale exp(-k^2/4a^2)/k^2 k_z
 // added to all three components (:278-287) + surface and self terms (:310-314).
-__global__ void __launch_bounds__(TILE) induced_finish_kernel(Cell c, SubsetDev rows, KVecDev kv, const double* __restrict__ kvec,
-                                                              const double* __restrict__ sf, double scale,
-                                                              const double* __restrict__ part, int jsplits, int part_np,
-                                                              const double* __restrict__ total_mu, double surf, double selfc,
-                                                              const double* __restrict__ mu, double* __restrict__ out) {
+//
+// One thread per atom, 64-thread CTAs (726 CTAs at 46k atoms: the 128-thread form left 148 SMs with 2 or 3 CTAs each).
+// The k list is lexicographic in (l0, l1, l2) (engine.cu:build_kvectors), so the phase product of the first two axes is
+// kept while l2 runs; w_k Re P / w_k Im P are formed once per CTA; sin(-x) is a sign-bit flip.  Executed fp64
+// instructions per (k, atom): 6 + 4 per (l0, l1) group (~1 amortised), against 17 in the first form.
+constexpr int FIN_TILE = 64;
+
+__global__ void __launch_bounds__(FIN_TILE) induced_finish_kernel(Cell c, SubsetDev rows, KVecDev kv, const double* __restrict__ kvec,
+                                                                  const double* __restrict__ sf, double scale,
+                                                                  const double* __restrict__ part, int jsplits, int part_np,
+                                                                  const double* __restrict__ total_mu, double surf, double selfc,
+                                                                  const double* __restrict__ mu, double* __restrict__ out) {
     extern __shared__ double smem[];
-    const int nl = kv.kmax + 1, np = rows.n_pad;
+    const int nl = kv.kmax + 1, np = rows.n_pad, nk = kv.nk;
     double* tcos = smem;  // [axis][l][thread]
-    double* tsin = tcos + 3 * nl * TILE;
-    const int i = blockIdx.x * TILE + threadIdx.x;
+    double* tsin = tcos + 3 * nl * FIN_TILE;
+    double* kA = tsin + 3 * nl * FIN_TILE;  // w_k Re P(k)
+    double* kB = kA + nk;                   // w_k Im P(k)
+    int* lpack = reinterpret_cast<int*>(kB + nk);
+    const int i = blockIdx.x * FIN_TILE + threadIdx.x;
     const bool live = i < rows.n;
     const double x = live ? rows.x[i] : 0.0, y = live ? rows.y[i] : 0.0, z = live ? rows.z[i] : 0.0;
-    for (int ax = 0; ax < 3; ax++) {
+    for (int ik = threadIdx.x; ik < nk; ik += FIN_TILE) {
+        const double wk = scale * kv.weight[ik] * kvec[2 * nk + ik];
+        kA[ik] = wk * sf[ik];
+        kB[ik] = wk * sf[nk + ik];
+        lpack[ik] = kv.l[ik] | ((kv.l[nk + ik] + 64) << 8) | ((kv.l[2 * nk + ik] + 64) << 16);
+    }
+    for (int ax = 0; ax < 3; ax++) {  // e^{i l theta}, l = 0 .. kmax, by recurrence from one sincospi
         const double sfrac = c.R[0][ax] * x + c.R[1][ax] * y + c.R[2][ax] * z;
+        double s1, c1, cl = 1.0, sl = 0.0;
+        sincospi(2.0 * sfrac, &s1, &c1);
         for (int l = 0; l < nl; l++) {
-            double sn, cs;
-            sincospi(2.0 * (double)l * sfrac, &sn, &cs);
-            tcos[(ax * nl + l) * TILE + threadIdx.x] = cs;
-            tsin[(ax * nl + l) * TILE + threadIdx.x] = sn;
+            tcos[(ax * nl + l) * FIN_TILE + threadIdx.x] = cl;
+            tsin[(ax * nl + l) * FIN_TILE + threadIdx.x] = sl;
+            const double cn = cl * c1 - sl * s1;
+            sl = sl * c1 + cl * s1;
+            cl = cn;
         }
     }
+    __syncthreads();
     double g = 0.0;
-    for (int ik = 0; ik < kv.nk; ik++) {
-        const int l0 = kv.l[ik], l1 = kv.l[kv.nk + ik], l2 = kv.l[2 * kv.nk + ik];
-        const int o0 = (0 * nl + l0) * TILE + threadIdx.x, o1 = (1 * nl + abs(l1)) * TILE + threadIdx.x,
-                  o2 = (2 * nl + abs(l2)) * TILE + threadIdx.x;
-        const double c0 = tcos[o0], s0 = tsin[o0];
-        const double c1 = tcos[o1], s1 = (l1 < 0 ? -1.0 : 1.0) * tsin[o1];
-        const double c2 = tcos[o2], s2 = (l2 < 0 ? -1.0 : 1.0) * tsin[o2];
-        const double c01 = c0 * c1 - s0 * s1, s01 = s0 * c1 + c0 * s1;
+    int p01 = -1;
+    double c01 = 1.0, s01 = 0.0;
+    for (int ik = 0; ik < nk; ik++) {
+        const int lp = lpack[ik];
+        if ((lp & 0xffff) != p01) {  // CTA-uniform
+            p01 = lp & 0xffff;
+            const int l0 = lp & 0xff, l1 = ((lp >> 8) & 0xff) - 64;
+            const int o0 = (0 * nl + l0) * FIN_TILE + threadIdx.x, o1 = (1 * nl + abs(l1)) * FIN_TILE + threadIdx.x;
+            const double c0 = tcos[o0], s0 = tsin[o0];
+            const double c1 = tcos[o1], s1 = flip_sign_if(tsin[o1], l1 < 0);
+            c01 = c0 * c1 - s0 * s1;
+            s01 = s0 * c1 + c0 * s1;
+        }
+        const int l2 = ((lp >> 16) & 0xff) - 64;
+        const int o2 = (2 * nl + abs(l2)) * FIN_TILE + threadIdx.x;
+        const double c2 = tcos[o2], s2 = flip_sign_if(tsin[o2], l2 < 0);
         const double cc = c01 * c2 - s01 * s2, ss = s01 * c2 + c01 * s2;
-        const double wk = scale * kv.weight[ik] * kvec[2 * kv.nk + ik];
-        g += wk * (-ss * sf[kv.nk + ik] - cc * sf[ik]);
+        g -= ss * kB[ik] + cc * kA[ik];
     }
     if (i >= np) return;
     for (int d = 0; d < 3; d++) {
@@ -517,9 +658,26 @@ int launch_induced_real_clusters(const Cell& c, bool ortho, const SubsetDev& pol
 }
 
 int launch_dipole_sf(const Cell& c, const SubsetDev& pol, const KVecDev& kv, const double* kvec, const double* mu,
-                     int atoms_per_chunk, double* sf_partial, cudaStream_t s) {
+                     int atoms_per_chunk, double* sf_partial, cudaStream_t s, const KGroupsDev* kg) {
     const int nchunks = (pol.n + atoms_per_chunk - 1) / atoms_per_chunk;
     if (nchunks <= 0) return 0;
+    if (kg && kg->ngroups > 0 && kg->max_count <= SG_MAXD) {
+        const int nl = kv.kmax + 1;
+        const int gthreads = (kg->ngroups + 31) / 32 * 32;
+        if (gthreads * SG_SUB <= 512) {
+            const size_t tables = sizeof(double) * (2 * SG_ATOMS * 3 * nl + 3 * SG_ATOMS);
+            const size_t stage = sizeof(double) * 2 * SG_MAXD * gthreads;
+            const size_t smem = tables > stage ? tables : stage;
+            static bool attr_set_g = false;
+            if (!attr_set_g) {
+                cudaFuncSetAttribute(dipole_sf_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+                attr_set_g = true;
+            }
+            dipole_sf_grouped_kernel<<<nchunks, gthreads * SG_SUB, smem, s>>>(c, pol, kv.nk, nl, kg->ngroups, gthreads, kg->groups, mu,
+                                                                             atoms_per_chunk, sf_partial);
+            return nchunks;
+        }
+    }
     const size_t smem = sizeof(double) * (6 * (kv.kmax + 1) * DS_ATOMS + 3 * DS_ATOMS);
     static bool attr_set = false;
     if (!attr_set) {
@@ -538,7 +696,7 @@ void launch_induced_finish(const Cell& c, const SubsetDev& rows, const KVecDev& 
                            const EwaldFullOpts& o, const double* part, int jsplits, const double* total_mu, const double* mu,
                            double* out, cudaStream_t s) {
     if (rows.n_pad <= 0) return;
-    const size_t smem = sizeof(double) * 6 * (kv.kmax + 1) * TILE;
+    const size_t smem = sizeof(double) * (6 * (kv.kmax + 1) * FIN_TILE + 2 * (size_t)kv.nk) + sizeof(int) * kv.nk;
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(induced_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -547,7 +705,7 @@ void launch_induced_finish(const Cell& c, const SubsetDev& rows, const KVecDev& 
     const double scale = 8.0 * M_PI / c.volume;                            // :266
     const double surf = -4.0 * M_PI / (3.0 * c.volume);                    // :314
     const double selfc = 4.0 * o.a * o.a * o.a / (3.0 * kSqrtPiRef);       // :314
-    induced_finish_kernel<<<rows.n_pad / TILE, TILE, smem, s>>>(c, rows, kv, kvec, sf, scale, part, part ? jsplits : 0,
+    induced_finish_kernel<<<(rows.n_pad + FIN_TILE - 1) / FIN_TILE, FIN_TILE, smem, s>>>(c, rows, kv, kvec, sf, scale, part, part ? jsplits : 0,
                                                                rows.n_pad, total_mu, surf, selfc, mu, out);
 }
 

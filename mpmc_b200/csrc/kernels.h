@@ -206,8 +206,14 @@ void launch_induced_list_fill(const Cell& c, bool ortho, const SubsetDev& pol, c
 void launch_induced_list_apply(const SubsetDev& pol, const unsigned long long* offs, const void* list, const double* mu,
                                double* part, cudaStream_t s);
 // P(k) = sum_j (k.mu_j) e^{ik.r_j}: per-chunk partials [chunks][2][nk] (sum with launch_recip_finish); returns chunks
+// kg (optional): the (l0, l1) groups of the lexicographic k list, sorted by count (descending):
+// {first k index, l0, l1, (first l2 + 64) | count << 8}; with it and max_count <= 15 the grouped kernel runs.
+struct KGroupsDev {
+    int ngroups, max_count;
+    const int4* groups;
+};
 int launch_dipole_sf(const Cell& c, const SubsetDev& pol, const KVecDev& kv, const double* kvec, const double* mu,
-                     int atoms_per_chunk, double* sf_partial, cudaStream_t s);
+                     int atoms_per_chunk, double* sf_partial, cudaStream_t s, const KGroupsDev* kg = nullptr);
 void launch_total_mu(const SubsetDev& pol, const double* mu, double* out3, cudaStream_t s);
 // out[3][rows.n_pad] = sum_js part + reciprocal term + surface term (+ self term when mu != null)
 void launch_induced_finish(const Cell& c, const SubsetDev& rows, const KVecDev& kv, const double* kvec, const double* sf,
