@@ -46,7 +46,7 @@
 extern "C" {
 #endif
 
-#define MPMC_B200_ABI_VERSION 1
+#define MPMC_B200_ABI_VERSION 2
 
 /* damp_type: src/include/defines.h DAMPING_* enum */
 enum { MPMC_DAMP_OFF = 0, MPMC_DAMP_LINEAR = 1, MPMC_DAMP_EXPONENTIAL = 2 };
@@ -90,6 +90,11 @@ typedef struct mpmc_b200_params {
     double polar_wolf_alpha;
     double polar_wolf_alpha_lookup_cutoff;
     double polar_ewald_alpha;
+    /* Wolf-summed electrostatics (system_t.wolf, structs.h; coulombic.c:27-28,269-308): coulombic()
+     * = coulombic_wolf() alone -- shifted pair sum, no reciprocal / self / intramolecular term.
+     * Appended last so the layout of the earlier members is unchanged. */
+    int es_wolf;
+    int reserved0;
 } mpmc_b200_params;
 
 /* What energy() puts into observables_t (structs.h:152-162) plus its parts. */

@@ -74,6 +74,8 @@ class Params(C.Structure):
         ("polar_wolf_alpha", C.c_double),
         ("polar_wolf_alpha_lookup_cutoff", C.c_double),
         ("polar_ewald_alpha", C.c_double),
+        ("es_wolf", C.c_int),
+        ("reserved0", C.c_int),
     ]
 
     def to_dict(self) -> dict:
@@ -321,7 +323,7 @@ def load_library(path: str = LIB_PATH):
         f = getattr(lib, name)
         if name not in ("mpmc_b200_last_error", "mpmc_b200_destroy"):
             f.restype = C.c_int
-    if lib.mpmc_b200_abi_version() != 1:
+    if lib.mpmc_b200_abi_version() != 2:
         raise RuntimeError("libmpmc_b200.so ABI version mismatch")
     _lib = lib
     return lib

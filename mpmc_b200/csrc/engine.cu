@@ -894,6 +894,8 @@ static int check_supported(const mpmc_b200_params& P) {
         if (P.damp_type < 0 || P.damp_type > 2) FAIL(3, "unknown damp_type");
     }
     if (P.feynman_hibbs && !(P.temperature > 0.0)) FAIL(3, "feynman_hibbs needs temperature > 0");
+    // coulombic_wolf(): src/energy/coulombic.c:293-297 -- the reference dies on this combination
+    if (P.es_wolf && !P.rd_only && P.feynman_hibbs) FAIL(3, "COULOMBIC: FH + es_wolf is not implemented");
     return 0;
 }
 
@@ -1638,6 +1640,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
         po.fh_order = P.feynman_hibbs ? (P.feynman_hibbs_order == 2 ? 2 : 4) : 0;
         po.mixing = P.mixing;
         po.rd_only = P.rd_only;
+        po.es_wolf = P.es_wolf;
         if (c->use_clusters) {
             // K1 over this shard's i-clusters
             const SubsetDev sd = c->sorted.dev();
@@ -1652,7 +1655,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
             shard_range(c->n_pad / TILE, c->rank, c->world, rb, re);
             rb *= TILE;
             re = std::min(re * TILE, c->n);
-            if (!P.rd_only) {
+            if (!P.rd_only && !P.es_wolf) {  // coulombic_wolf() has no intramolecular term
                 launch_intra_erf(atoms_dev(c), c->follow.p, P.ewald_alpha, rb, std::max(re, rb), c->intra_part.p,
                                  c->scalars.p + S_PAIR + 2, ps);
                 c->launches += 2;
@@ -1681,7 +1684,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
                 return 0;
             }
         }
-        if (!P.rd_only) {
+        if (!P.rd_only && !P.es_wolf) {  // coulombic.c:27-28: wolf replaces real + reciprocal + self
             phase_begin(c, PH_RECIP, ps);
             c->cnt.kvectors = c->nk;
             c->cnt.recip_atoms = c->recip.n;
@@ -1743,8 +1746,8 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     out->rd = (out->rd_pair + (lead ? c->lrc_pair : 0.0)) + (lead ? c->lrc_self : 0.0);
     if (!P.rd_only) {
         out->es_real = h[S_PAIR + 1] - h[S_PAIR + 2];
-        out->es_recip = h[S_RECIP];
-        out->es_self = lead ? c->es_self : 0.0;
+        out->es_recip = P.es_wolf ? 0.0 : h[S_RECIP];
+        out->es_self = (lead && !P.es_wolf) ? c->es_self : 0.0;
         out->coulombic = out->es_real + out->es_recip + out->es_self;
     }
     if (c->last_had_polar) {

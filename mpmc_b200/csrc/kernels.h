@@ -36,6 +36,7 @@ struct PairOpts {
     int fh_order;  // 0 = off, 2, 4
     int mixing;
     int rd_only;
+    int es_wolf = 0;  // coulombic_wolf() instead of coulombic_real() (needs fh_order == 0)
 };
 constexpr int PAIR_NPART = 8;  // rd, es, intra, min_r, n_tested, n_lj, n_es, (unused)
 void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const int2* tiles, int ntiles,

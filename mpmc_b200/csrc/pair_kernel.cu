@@ -11,6 +11,7 @@
 //   pair_exclusions()  src/energy/pairs.c:56-227     minimum_image()  src/energy/pairs.c:230-290
 //   lj()               src/energy/lj.c:181-260       lj_fh_corr()     src/energy/lj.c:11-54
 //   coulombic_real()   src/energy/coulombic.c:159-191  coulombic_real_FH()  src/energy/coulombic.c:115-146
+//   coulombic_wolf()   src/energy/coulombic.c:269-308 (option `wolf`; replaces real + reciprocal + self)
 //   cavity_absolute_check()  src/energy/energy.c:49-64
 #include "kernels.h"
 
@@ -21,6 +22,9 @@ struct PairConsts {
     double fh2_pref, fh4_pref;  // M2A2*HBAR2/(24 KB T) and M2A4*HBAR4/(1152 KB2 T^2), before 1/mu_red powers
     double fh4_pref_es;         // coulombic.c:141 spells KB*KB instead of the KB2 constant (differs at 4.7e-10)
     double inv_sqrt_pi;
+    // coulombic_wolf(): erf(alpha R)/R and 1/R^2 (coulombic.c:275-276,290); only read by the FH == 0 kernels
+    double wolf_shift, wolf_ir2;
+    int wolf;
 };
 
 __device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double ej, double sj, double& eps,
@@ -87,7 +91,7 @@ __device__ __forceinline__ void pair_terms(const Cell& c, const PairConsts& k, i
         if (moli == molj) {
             // same molecule: rd and es excluded (pairs.c:61-64); charge-to-screen term with the
             // UN-imaged separation (coulombic.c:179-180)
-            if (!rd_only && qq != 0.0) {
+            if (!rd_only && qq != 0.0 && !(FH == 0 && k.wolf)) {
                 double r = sqrt(dx * dx + dy * dy + dz * dz);
                 A.intra += qq * erf(k.alpha * r) / r;
             }
@@ -100,7 +104,8 @@ __device__ __forceinline__ void pair_terms(const Cell& c, const PairConsts& k, i
         A.minr = fmin(A.minr, r);
 
                 const bool do_lj = (r - kSMALL_dR < k.cutoff) && lj_i && (ej != 0.0) && (sj != 0.0);
-        const bool do_es = !rd_only && !(r > k.cutoff) && (qq != 0.0);
+        // coulombic.c:167 skips r > cutoff; coulombic_wolf() keeps r < R only (coulombic.c:288)
+        const bool do_es = !rd_only && ((FH == 0 && k.wolf) ? (r < k.cutoff) : !(r > k.cutoff)) && (qq != 0.0);
         if (!(do_lj || do_es)) break;
         const double ir = 1.0 / r;
         double mured = 0.0;
@@ -129,7 +134,12 @@ __device__ __forceinline__ void pair_terms(const Cell& c, const PairConsts& k, i
             A.rd += u;
             A.n_lj++;
         }
-        if (do_es) {
+        if (FH == 0 && k.wolf) {
+            if (do_es) {  // coulombic.c:289-290
+                A.es += qq * (ir - k.wolf_shift - k.wolf_ir2 * (k.cutoff - r));
+                A.n_es++;
+            }
+        } else if (do_es) {
             const double erfc_term = erfc(k.alpha * r);
             double u = qq * erfc_term * ir;
             if (FH) {  // coulombic.c:132-141
@@ -405,6 +415,9 @@ static PairConsts make_pair_consts(const Cell& c, const PairOpts& o) {
     k.fh2_pref = kM2A2 * (kHBAR2 / (24.0 * kKB * o.temperature));
     k.fh4_pref = kM2A4 * (kHBAR4 / (1152.0 * kKB2 * o.temperature * o.temperature));
     k.fh4_pref_es = kM2A4 * (kHBAR4 / (1152.0 * (kKB * kKB * o.temperature * o.temperature)));
+    k.wolf = o.es_wolf && o.fh_order == 0;
+    k.wolf_shift = erf(k.alpha * k.cutoff) / k.cutoff;
+    k.wolf_ir2 = (1.0 / k.cutoff) * (1.0 / k.cutoff);
     return k;
 }
 

@@ -274,6 +274,8 @@ def write_input(s: System, path: str, pqr_name: str, ensemble: str = "total_ener
     a(f"rd_lrc {'on' if p.rd_lrc else 'off'}")
     if p.rd_only:
         a("rd_only on")
+    if p.es_wolf:
+        a("wolf on")
     if p.feynman_hibbs:
         a("feynman_hibbs on")
         a(f"feynman_hibbs_order {p.feynman_hibbs_order}")

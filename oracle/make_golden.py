@@ -87,6 +87,10 @@ def synthetic_cases():
         "mixed_nofh_nolrc": _variant(m, feynman_hibbs=0, rd_lrc=0),
         "mixed_nopolar_kmax5": _variant(m, polarization=0, ewald_kmax=5),
         "mixed_rd_only": _variant(m, rd_only=1, polarization=0),
+        # Wolf-summed electrostatics (coulombic_wolf(): coulombic.c:269-308); FH must be off (:293-297)
+        "mixed_es_wolf": _variant(m, es_wolf=1, feynman_hibbs=0),
+        "mixed_tri_es_wolf_nopolar": _variant(t, es_wolf=1, feynman_hibbs=0, polarization=0),
+        "co2_fluid_375_es_wolf": _variant(systems.co2_fluid(125), es_wolf=1, feynman_hibbs=0),
         "mixed_autoreject_fires": _variant(m, cavity_autoreject_absolute=1, cavity_autoreject_scale=3.2),
         "mixed_autoreject_quiet": _variant(m, cavity_autoreject_absolute=1, cavity_autoreject_scale=0.5),
         "mixed_cutoff7": _variant(m, cutoff=7.0, ewald_alpha=0.45, polar_ewald_alpha=0.45),

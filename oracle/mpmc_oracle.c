@@ -248,6 +248,15 @@ static void o_pair_row(const osys_t *s, int i, orow_t *acc) {
             acc->rd_pair += rd;
             acc->lrc_pair += lrc;
         }
+        /* ---- coulombic_wolf(): coulombic.c:269-308 (option `wolf`) ---- */
+        if (!P->rd_only && P->es_wolf) {
+            double R = cutoff, iR = 1.0 / R, erfaRoverR = erf(alpha * R) / R;
+            double r = g.rimg, ir = 1.0 / r;
+            if (!e.frozen && !e.es_excluded && (r < R)) {
+                acc->es_real += s->q[i] * s->q[j] * (ir - erfaRoverR - iR * iR * (R - r));
+                acc->n_es += 1;
+            }
+        } else
         /* ---- coulombic_real() ---- */
         if (!P->rd_only && !e.frozen) {
             double r = g.rimg, es = 0, intra = 0;
@@ -910,6 +919,7 @@ static int o_ewald_full(const osys_t *s, const double *ef_static, double *mu, do
 static int o_check(const mpmc_b200_params *P) {
     if (P->polarization && !P->polar_iterative && !P->polar_zodid && !P->polar_ewald_full)
         return 3; /* LU inversion path: out of scope */
+    if (P->es_wolf && !P->rd_only && P->feynman_hibbs) return 3; /* coulombic.c:293-297: the reference dies */
     return 0;
 }
 
@@ -1066,8 +1076,10 @@ int mpmc_oracle_energy(const mpmc_b200_params *P, int n, const double *pos, cons
     if (!P->rd_only) { /* coulombic(): coulombic.c:22-39 */
         double nk = 0, nq = 0;
         out->es_real = tot.es_real;
-        out->es_recip = o_recip(&s, &nk, &nq);
-        out->es_self = o_self(&s);
+        if (!P->es_wolf) { /* coulombic.c:27-28: wolf replaces real + reciprocal + self */
+            out->es_recip = o_recip(&s, &nk, &nq);
+            out->es_self = o_self(&s);
+        }
         out->coulombic = out->es_real + out->es_recip + out->es_self;
         if (cnt) {
             cnt->kvectors = nk;

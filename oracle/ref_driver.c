@@ -147,6 +147,10 @@ int main(int argc, char **argv) {
         printf("energy es_recip %.17g\n", coulombic_reciprocal(s));
         printf("energy es_self %.17g\n", coulombic_self(s));
         printf("energy es_real %.17g\n", coulombic_real(s));
+    } else if (!s->rd_only && s->wolf) { /* coulombic(): coulombic.c:27-28 */
+        printf("energy es_recip 0\n");
+        printf("energy es_self 0\n");
+        printf("energy es_real %.17g\n", coulombic_wolf(s));
     }
 #endif
 

@@ -29,6 +29,48 @@ SYM_SMALL = ["mixed_default", "mixed_tri_default", "mixed_palmo", "mixed_sor", "
              "ref_socmof"]
 
 
+@pytest.mark.parametrize("builder,kw,cutoffs", [
+    (systems.co2_fluid, dict(n_mol=1500), ("clusters", "tiles")),
+    (systems.mof_h2, dict(cells=(3, 3, 1)), ("clusters",)),
+])
+def test_es_wolf_matches_oracle_midsize(engine, builder, kw, cutoffs, monkeypatch):
+    """Option `wolf` (coulombic_wolf(), coulombic.c:269-308) at a size where K1 runs many cluster pairs per warp; both
+    forms of K1 (cluster form and the all-pairs tile form behind MPMC_B200_CUTOFF=tiles)."""
+    from oracle import oracle
+
+    s = builder(**kw)
+    s.params.es_wolf = 1
+    s.params.feynman_hibbs = 0
+    exp, _, oarr = oracle.energy(s, nthreads=0)
+    assert exp.es_recip == 0.0 and exp.es_self == 0.0 and exp.es_real != 0.0
+    from mpmc_b200 import Engine
+
+    for form in cutoffs:
+        monkeypatch.setenv("MPMC_B200_CUTOFF", form)  # read when the context is created
+        eng = engine if form == "clusters" else Engine(0)
+        try:
+            eng.set_system(s)
+            got = eng.energy()
+            gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=f"{s.name} es_wolf {form}")
+            assert got.es_recip == 0.0 and got.es_self == 0.0
+            if s.params.polarization:
+                gu.assert_atom_arrays(eng.atom_arrays(), oarr, s, rtol=1e-10, label=s.name)
+        finally:
+            if eng is not engine:
+                eng.close()
+
+
+def test_es_wolf_with_feynman_hibbs_is_refused(engine):
+    """coulombic.c:293-297: the reference dies on FH + wolf; the engine refuses the parameters (no silent fallback)."""
+    s = systems.h2_fluid(500)
+    s.params.es_wolf = 1
+    assert s.params.feynman_hibbs
+    with pytest.raises(RuntimeError, match="es_wolf"):
+        engine.set_system(s)
+    engine.set_system(systems.h2_fluid(500))  # the context stays usable
+    assert engine.energy().total != 0.0
+
+
 @pytest.mark.parametrize("name", SYM_SMALL)
 def test_symmetric_contraction_on_small_fixtures(engine, name, monkeypatch):
     """Below 8,192 padded polarizable atoms a single GPU uses the row form of K4 (latency); MPMC_B200_SYM_MIN=0 forces
