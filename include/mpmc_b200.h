@@ -94,6 +94,12 @@ typedef struct mpmc_b200_params {
      * = coulombic_wolf() alone -- shifted pair sum, no reciprocal / self / intramolecular term.
      * Appended last so the layout of the earlier members is unchanged. */
     int es_wolf;
+    /* rd_crystal (structs.h; lj.c:109-162,175-216,264-267): LJ summed over the periodic images
+     * (-(order-1)..order-1)^3 of every pair (same-molecule pairs included, without their home image) inside the
+     * wider cutoff 2*cutoff*(order-0.5), plus each atom's interaction with its own images.  The image terms of
+     * the pairs and of the atoms themselves are reported inside energies.rd_pair. */
+    int rd_crystal;
+    int rd_crystal_order;
     int reserved0;
 } mpmc_b200_params;
 

@@ -75,6 +75,8 @@ class Params(C.Structure):
         ("polar_wolf_alpha_lookup_cutoff", C.c_double),
         ("polar_ewald_alpha", C.c_double),
         ("es_wolf", C.c_int),
+        ("rd_crystal", C.c_int),
+        ("rd_crystal_order", C.c_int),
         ("reserved0", C.c_int),
     ]
 

@@ -108,7 +108,8 @@ enum Slot {
     S_FIELDCNT = 13,
     S_TOTMU = 16,  // 3: sum of the dipoles (full-Ewald polarization)
     S_PEER_TIMEOUT = 20,  // set to 1.0 by a peer-wait kernel whose peer never signalled
-    S_COUNT = 21
+    S_CRYSTAL = 22,       // 2: rd_crystal image sums of the pairs, pairs counted
+    S_COUNT = 24
 };
 
 }  // namespace
@@ -146,6 +147,13 @@ struct mpmc_b200_ctx {
     int ntiles = 0;
     DevBuf<double> pair_part;
     int pair_stride = 0;
+    // rd_crystal (lj.c:175-216): all tile pairs of the list-ordered atoms, image vectors, partial sums
+    DevBuf<int2> crystal_tiles;
+    int crystal_ntiles = 0, crystal_stride = 0, crystal_nimg = 0;
+    DevBuf<double> crystal_part, crystal_img;
+    std::vector<double> h_crystal_img;
+    bool crystal_img_dirty = true;
+    double crystal_self = 0;  // rd_crystal_self() summed over the atoms (host, compute_analytic)
 
     // reciprocal space
     DevBuf<int> kl;
@@ -411,6 +419,11 @@ static void host_mix(int mixing, double ei, double si, double ej, double sj, dou
     }
 }
 
+// lj(): src/energy/lj.c:175-178 -- with rd_crystal the LJ cutoff (pair test, image sums, LRC) is wider
+static double rd_cutoff(const mpmc_b200_params& P) {
+    return P.rd_crystal ? 2.0 * P.cutoff * ((double)P.rd_crystal_order - 0.5) : P.cutoff;
+}
+
 static double lrc_value(double eps, double sigma, double cutoff, double volume) {
     // lj_lrc_corr / lj_lrc_self (src/energy/lj.c:69-80, 92-103)
     double sig_cut = fabs(sigma) / cutoff;
@@ -462,15 +475,52 @@ static void compute_analytic(Ctx* c) {
                     npairs = 0.5 * types[a].total * (types[a].total - 1) - 0.5 * types[a].frozen * (types[a].frozen - 1);
                 else
                     npairs = types[a].total * types[b].total - types[a].frozen * types[b].frozen;
-                if (npairs > 0) pair_sum += npairs * lrc_value(eps, sigma, P.cutoff, P.volume);
+                if (npairs > 0) pair_sum += npairs * lrc_value(eps, sigma, rd_cutoff(P), P.volume);
             }
             if (types[a].sig != 0 && types[a].eps != 0) {
                 double mobile = types[a].total - types[a].frozen;
-                if (mobile > 0) self_sum += mobile * lrc_value(types[a].eps, types[a].sig, P.cutoff, P.volume);
+                if (mobile > 0) self_sum += mobile * lrc_value(types[a].eps, types[a].sig, rd_cutoff(P), P.volume);
             }
         }
         c->lrc_pair = pair_sum;
         c->lrc_self = self_sum;
+    }
+    c->crystal_self = 0.0;
+    c->h_crystal_img.clear();
+    if (P.rd_crystal) {
+        // image vectors a[p] = sum_q basis[q][p] * l[q] in the loop order of lj.c:199-211
+        const int m = P.rd_crystal_order - 1;
+        const double cut = rd_cutoff(P);
+        for (int l0 = -m; l0 <= m; l0++)
+            for (int l1 = -m; l1 <= m; l1++)
+                for (int l2 = -m; l2 <= m; l2++) {
+                    const int l[3] = {l0, l1, l2};
+                    for (int p = 0; p < 3; p++) {
+                        double a = 0;
+                        for (int q = 0; q < 3; q++) a += P.basis[q][p] * l[q];
+                        c->h_crystal_img.push_back(a);
+                    }
+                }
+        c->crystal_nimg = (int)c->h_crystal_img.size() / 3;
+        c->crystal_img_dirty = true;
+        // rd_crystal_self() (lj.c:109-162; spectre / polarvdw / cdvdw off): every atom -- frozen ones included -- with
+        // its own images, half weight; added per atom in list order as lj.c:264-267 does
+        const int home = (c->crystal_nimg - 1) / 2;
+        for (int i = 0; i < c->n; i++) {
+            const double sig = c->hsig[i], eps = c->heps[i];
+            if (sig == 0 && eps == 0) continue;
+            double s6 = 0, s12 = 0;
+            for (int k = 0; k < c->crystal_nimg; k++) {
+                if (k == home) continue;
+                const double* a = &c->h_crystal_img[3 * k];
+                const double r = sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+                if (r > cut) continue;
+                const double sor = fabs(sig) / r;
+                s6 += 0.5 * pow(sor, 6);
+                s12 += 0.5 * pow(sor, 12);
+            }
+            c->crystal_self += 4.0 * eps * ((sig < 0.0 ? 0.0 : s12) - s6);
+        }
     }
     if (!P.rd_only) {  // coulombic_self (src/energy/coulombic.c:97-112), same accumulation order
         double self_potential = 0.0;
@@ -759,6 +809,24 @@ static int repack(Ctx* c) {
 
     }
 
+    c->crystal_ntiles = 0;
+    if (c->P.rd_crystal) {  // all tile pairs of the upper triangle except those in which every atom is frozen
+        const int nt = np / TILE;
+        std::vector<char> all_frozen(nt, 1);
+        for (int t = 0; t < nt; t++)
+            for (int k = t * TILE; k < std::min(n, (t + 1) * TILE); k++)
+                if (!c->hfrozen[k]) all_frozen[t] = 0;
+        std::vector<int2> ct;
+        for (int I = 0; I < nt; I++)
+            for (int J = I; J < nt; J++)
+                if (!(all_frozen[I] && all_frozen[J])) ct.push_back(make_int2(I, J));
+        c->crystal_ntiles = (int)ct.size();
+        if (ct.empty()) ct.push_back(make_int2(0, 0));
+        if (upload(c->crystal_tiles, ct, st)) return 11;
+        c->crystal_stride = round_up(std::max(c->crystal_ntiles, 1), 32);
+        if (c->crystal_part.ensure((size_t)2 * c->crystal_stride)) FAIL(11, "cudaMalloc failed");
+    }
+
     // reciprocal chunks: about two CTAs per SM
     const int target = 2 * sms;
     c->recip_apc = std::max(64, round_up((std::max(c->charged.n, 1) + target - 1) / target, 64));
@@ -896,6 +964,11 @@ static int check_supported(const mpmc_b200_params& P) {
     if (P.feynman_hibbs && !(P.temperature > 0.0)) FAIL(3, "feynman_hibbs needs temperature > 0");
     // coulombic_wolf(): src/energy/coulombic.c:293-297 -- the reference dies on this combination
     if (P.es_wolf && !P.rd_only && P.feynman_hibbs) FAIL(3, "COULOMBIC: FH + es_wolf is not implemented");
+    if (P.rd_crystal) {  // check_input.c:1258-1262
+        if (P.rd_crystal_order <= 0) FAIL(3, "rd crystal order must be positive");
+        const int side = 2 * P.rd_crystal_order - 1;
+        if (side * side * side > crystal_max_images()) FAIL(3, "rd_crystal_order > 4 is not supported");
+    }
     return 0;
 }
 
@@ -1641,6 +1714,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
         po.mixing = P.mixing;
         po.rd_only = P.rd_only;
         po.es_wolf = P.es_wolf;
+        po.no_lj = P.rd_crystal ? 1 : 0;
         if (c->use_clusters) {
             // K1 over this shard's i-clusters
             const SubsetDev sd = c->sorted.dev();
@@ -1670,6 +1744,18 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
             }
             launch_pair_reduce(c->pair_part.p, std::max(te - tb, 0), c->pair_stride, c->scalars.p + S_PAIR, ps);
             c->launches++;
+        }
+        if (P.rd_crystal) {  // LJ image sums over this shard's tile pairs (lj.c:196-216)
+            if (c->crystal_img_dirty) {
+                if (upload(c->crystal_img, c->h_crystal_img, ps)) return 11;
+                c->crystal_img_dirty = false;
+            }
+            int tb, te;
+            shard_range(c->crystal_ntiles, c->rank, c->world, tb, te);
+            launch_crystal_lj(cell, ortho, atoms_dev(c), po, rd_cutoff(P), c->crystal_img.p, c->crystal_nimg,
+                              c->crystal_tiles.p + tb, te - tb, c->crystal_part.p, c->crystal_stride,
+                              c->scalars.p + S_CRYSTAL, ps);
+            c->launches += (te > tb) ? 2 : 1;
         }
         phase_end(c, PH_PAIR, ps);
         CU(cudaGetLastError());
@@ -1732,7 +1818,7 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     const bool lead = (c->rank == 0);  // host-side analytic terms are added once (rank 0) in sharded runs
     out->min_intermolecular_r = h[S_PAIR + 3];
     c->cnt.pairs_tested = c->use_clusters ? (c->rank == 0 ? c->pairs_tested_analytic : 0.0) : h[S_PAIR + 4];
-    c->cnt.pairs_lj = h[S_PAIR + 5];
+    c->cnt.pairs_lj = h[S_PAIR + 5] + (P.rd_crystal ? h[S_CRYSTAL + 1] : 0.0);
     c->cnt.pairs_es = h[S_PAIR + 6];
     c->cnt.kernel_launches = c->launches;
     c->cnt.pairs_field = 0.5 * h[S_FIELDCNT];
@@ -1742,6 +1828,7 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
         return 0;
     }
     out->rd_pair = h[S_PAIR + 0];
+    if (P.rd_crystal) out->rd_pair += h[S_CRYSTAL] + (lead ? c->crystal_self : 0.0);  // lj.c:196-216, 264-267
     out->rd_lrc = lead ? (c->lrc_pair + c->lrc_self) : 0.0;
     out->rd = (out->rd_pair + (lead ? c->lrc_pair : 0.0)) + (lead ? c->lrc_self : 0.0);
     if (!P.rd_only) {
@@ -1882,7 +1969,8 @@ int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
     if (!c || !p) FAIL(1, "null argument");
     const bool repack_needed = c->have_atoms && (p->damp_type != c->P.damp_type || p->polar_gs != c->P.polar_gs ||
                                                   p->polar_gs_ranked != c->P.polar_gs_ranked ||
-                                                  p->polar_ewald_full != c->P.polar_ewald_full);
+                                                  p->polar_ewald_full != c->P.polar_ewald_full ||
+                                                  (p->rd_crystal != 0) != (c->P.rd_crystal != 0));
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;

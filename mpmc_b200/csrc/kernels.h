@@ -37,7 +37,13 @@ struct PairOpts {
     int mixing;
     int rd_only;
     int es_wolf = 0;  // coulombic_wolf() instead of coulombic_real() (needs fh_order == 0)
+    int no_lj = 0;    // K1 without the LJ term (rd_crystal: launch_crystal_lj computes it)
 };
+// rd_crystal (lj.c:175-216): LJ image sums over all tile pairs of the list-ordered atoms.  img [nimg][3] = B^T l in the
+// reference's loop order; partial [2][stride] (energy, pair count); out[0..1] = their fixed-order sums.
+int crystal_max_images();
+void launch_crystal_lj(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, double rd_cutoff, const double* img,
+                       int nimg, const int2* tiles, int ntiles, double* partial, int stride, double* out, cudaStream_t s);
 constexpr int PAIR_NPART = 8;  // rd, es, intra, min_r, n_tested, n_lj, n_es, (unused)
 void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const int2* tiles, int ntiles,
                         double* partial /*[PAIR_NPART][ntiles_stride]*/, int stride, cudaStream_t s);

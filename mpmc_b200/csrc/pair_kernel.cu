@@ -12,6 +12,7 @@
 //   lj()               src/energy/lj.c:181-260       lj_fh_corr()     src/energy/lj.c:11-54
 //   coulombic_real()   src/energy/coulombic.c:159-191  coulombic_real_FH()  src/energy/coulombic.c:115-146
 //   coulombic_wolf()   src/energy/coulombic.c:269-308 (option `wolf`; replaces real + reciprocal + self)
+//   lj() with rd_crystal   src/energy/lj.c:175-216 (image sums; crystal_lj_kernel below)
 //   cavity_absolute_check()  src/energy/energy.c:49-64
 #include "kernels.h"
 
@@ -25,6 +26,7 @@ struct PairConsts {
     // coulombic_wolf(): erf(alpha R)/R and 1/R^2 (coulombic.c:275-276,290); only read by the FH == 0 kernels
     double wolf_shift, wolf_ir2;
     int wolf;
+    int no_lj;  // rd_crystal: the LJ term comes from crystal_lj_kernel, K1 keeps electrostatics + minimum distance
 };
 
 __device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double ej, double sj, double& eps,
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, P
     __syncthreads();
 
     PairAcc A = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
-    const bool lj_i = (ei != 0.0) && (si != 0.0);
+    const bool lj_i = (ei != 0.0) && (si != 0.0) && !k.no_lj;
     const int j0 = (t.x == t.y) ? tid + 1 : 0;
 
     for (int jj = j0; jj < TILE; jj++) {
@@ -246,7 +248,7 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
     const int i = ci * 32 + lane;
     const double xi = a.x[i], yi = a.y[i], zi = a.z[i], qi = a.q[i], ei = a.eps[i], si = a.sig[i], mi = a.molmass[i];
     const int moli = a.mol[i], fli = a.flags[i];
-    const bool lj_i = (ei != 0.0) && (si != 0.0);
+    const bool lj_i = (ei != 0.0) && (si != 0.0) && !k.no_lj;
     PairAcc A = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
 
     const int K = nclus / 2;
@@ -416,6 +418,7 @@ static PairConsts make_pair_consts(const Cell& c, const PairOpts& o) {
     k.fh4_pref = kM2A4 * (kHBAR4 / (1152.0 * kKB2 * o.temperature * o.temperature));
     k.fh4_pref_es = kM2A4 * (kHBAR4 / (1152.0 * (kKB * kKB * o.temperature * o.temperature)));
     k.wolf = o.es_wolf && o.fh_order == 0;
+    k.no_lj = o.no_lj;
     k.wolf_shift = erf(k.alpha * k.cutoff) / k.cutoff;
     k.wolf_ir2 = (1.0 / k.cutoff) * (1.0 / k.cutoff);
     return k;
@@ -443,6 +446,146 @@ void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const Pair
             LAUNCH(false, 4);
     }
 #undef LAUNCH
+}
+
+// ------------------------------------------------------------------------------------------------
+// rd_crystal (lj.c:175-216): the LJ term of EVERY pair that is not frozen-frozen -- same-molecule pairs included --
+// summed over the periodic images l in (-(order-1)..order-1)^3 of the UN-imaged separation, inside the wider cutoff
+// 2*cutoff*(order-0.5); same-molecule pairs skip their home image (lj.c:203).  All-pairs tiles of the list-ordered
+// atoms (no cutoff culling applies: the wider cutoff exceeds the minimum-image range), the image vectors
+// B^T l staged in shared memory in the reference's loop order, i atom in registers, j tile in shared memory.
+// The Feynman-Hibbs correction uses the summed terms with the minimum-image distance, as lj_fh_corr() does
+// (lj.c:247-248).  Fixed-order block sums, one partial per tile pair.
+constexpr int CRYSTAL_MAX_IMG = 343;  // rd_crystal_order <= 4
+
+template <bool ORTHO, int FH>
+__global__ void __launch_bounds__(TILE) crystal_lj_kernel(Cell c, AtomsDev a, PairConsts k, int mixing, double rd_cutoff,
+                                                          const double* __restrict__ img, int nimg,
+                                                          const int2* __restrict__ tiles, double* __restrict__ partial,
+                                                          int stride) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], se[TILE], ss[TILE], sm[TILE];
+    __shared__ int smol[TILE], sfl[TILE];
+    __shared__ double ix[CRYSTAL_MAX_IMG], iy[CRYSTAL_MAX_IMG], iz[CRYSTAL_MAX_IMG];
+    __shared__ double red[32];
+
+    const int2 t = tiles[blockIdx.x];
+    const int tid = threadIdx.x;
+    const int i = t.x * TILE + tid;
+    {
+        const int j = t.y * TILE + tid;
+        sx[tid] = a.x[j];
+        sy[tid] = a.y[j];
+        sz[tid] = a.z[j];
+        se[tid] = a.eps[j];
+        ss[tid] = a.sig[j];
+        sm[tid] = a.molmass[j];
+        smol[tid] = a.mol[j];
+        sfl[tid] = a.flags[j];
+    }
+    for (int m = tid; m < nimg; m += TILE) {
+        ix[m] = img[3 * m + 0];
+        iy[m] = img[3 * m + 1];
+        iz[m] = img[3 * m + 2];
+    }
+    const double xi = a.x[i], yi = a.y[i], zi = a.z[i], ei = a.eps[i], si = a.sig[i], mi = a.molmass[i];
+    const int moli = a.mol[i], fli = a.flags[i];
+    __syncthreads();
+
+    const int home = (nimg - 1) / 2;  // l = (0,0,0) sits in the middle of the symmetric loop nest
+    const bool lj_i = (ei != 0.0) && (si != 0.0);
+    const int j0 = (t.x == t.y) ? tid + 1 : 0;
+    double rd = 0.0;
+    int n_lj = 0;
+    for (int jj = j0; jj < TILE; jj++) {
+        const int fj = sfl[jj];
+        if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) continue;  // padding; frozen pairs (lj.c:193)
+        const double ej = se[jj], sj = ss[jj];
+        // a pair with a zero eps or sigma on either atom mixes to eps = 0 or sigma = 0 under every rule
+        // (pairs.c:84-211) and adds exactly 0 (also through lj_fh_corr): skipped
+        if (!(lj_i && ej != 0.0 && sj != 0.0)) continue;
+        const double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
+        double mx = dx, my = dy, mz = dz;
+        min_image<ORTHO>(c, mx, my, mz);
+        const double rimg = sqrt(mx * mx + my * my + mz * mz);
+        if (!(rimg - kSMALL_dR < rd_cutoff)) continue;  // lj.c:191
+        double eps, sigma;
+        bool att;
+        mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
+        const double asig = fabs(sigma);
+        const bool same = (moli == smol[jj]);
+        double s6 = 0.0, s12 = 0.0;
+        for (int m = 0; m < nimg; m++) {
+            if (same && m == home) continue;  // lj.c:203
+            const double ax = ix[m] + dx, ay = iy[m] + dy, az = iz[m] + dz;
+            const double r = sqrt(ax * ax + ay * ay + az * az);
+            if (r > rd_cutoff) continue;  // lj.c:213
+            const double sor = asig / r;
+            double t6 = sor * sor * sor;
+            t6 *= t6;
+            s6 += t6;
+            s12 += t6 * t6;
+        }
+        const double term6 = s6, term12 = att ? 0.0 : s12;
+        double u = 4.0 * eps * (term12 - term6);
+        if (FH) {  // lj.c:29-50 with pair->rimg
+            const double ir = 1.0 / rimg, ir2 = ir * ir, ir3 = ir2 * ir, ir4 = ir3 * ir;
+            const double mured = kAMU2KG * mi * sm[jj] / (mi + sm[jj]);
+            const double dE = -24.0 * eps * (2.0 * term12 - term6) * ir;
+            const double d2E = 24.0 * eps * (26.0 * term12 - 7.0 * term6) * ir2;
+            u += (k.fh2_pref / mured) * (d2E + 2.0 * dE * ir);
+            if (FH >= 4) {
+                const double d3E = -1344.0 * eps * (6.0 * term12 - term6) * ir3;
+                const double d4E = 12096.0 * eps * (10.0 * term12 - term6) * ir4;
+                u += (k.fh4_pref / (mured * mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
+            }
+        }
+        rd += u;
+        n_lj++;
+    }
+    double v = block_reduce<0>(rd, red);
+    if (tid == 0) partial[0 * stride + blockIdx.x] = v;
+    v = block_reduce<0>((double)n_lj, red);
+    if (tid == 0) partial[1 * stride + blockIdx.x] = v;
+}
+
+// One CTA sums the two partial rows of crystal_lj_kernel in a fixed order: out[0] = energy, out[1] = pair count.
+__global__ void __launch_bounds__(1024) crystal_reduce_kernel(const double* __restrict__ partial, int ntiles, int stride,
+                                                              double* __restrict__ out) {
+    __shared__ double red[32];
+    for (int q = 0; q < 2; q++) {
+        double acc = 0.0;
+        for (int t = threadIdx.x; t < ntiles; t += blockDim.x) acc += partial[q * stride + t];
+        const double v = block_reduce<0>(acc, red);
+        if (threadIdx.x == 0) out[q] = v;
+    }
+}
+
+int crystal_max_images() { return CRYSTAL_MAX_IMG; }
+
+void launch_crystal_lj(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, double rd_cutoff, const double* img,
+                       int nimg, const int2* tiles, int ntiles, double* partial, int stride, double* out, cudaStream_t s) {
+    const PairConsts k = make_pair_consts(c, o);
+    if (ntiles > 0) {
+#define LAUNCH(ORTHO, FH) \
+    crystal_lj_kernel<ORTHO, FH><<<ntiles, TILE, 0, s>>>(c, a, k, o.mixing, rd_cutoff, img, nimg, tiles, partial, stride)
+        if (ortho) {
+            if (o.fh_order == 0)
+                LAUNCH(true, 0);
+            else if (o.fh_order == 2)
+                LAUNCH(true, 2);
+            else
+                LAUNCH(true, 4);
+        } else {
+            if (o.fh_order == 0)
+                LAUNCH(false, 0);
+            else if (o.fh_order == 2)
+                LAUNCH(false, 2);
+            else
+                LAUNCH(false, 4);
+        }
+#undef LAUNCH
+    }
+    crystal_reduce_kernel<<<1, 1024, 0, s>>>(partial, ntiles > 0 ? ntiles : 0, stride, out);
 }
 
 void launch_pair_reduce(const double* partial, int ntiles, int stride, double* out, cudaStream_t s) {

@@ -150,6 +150,8 @@ static void shim_fill_params(const system_t *s, mpmc_b200_params *P) {
                                  : s->halgren_mixing ? MPMC_MIX_HALGREN : s->c6_mixing ? MPMC_MIX_C6 : MPMC_MIX_LORENTZ_BERTHELOT;
     P->rd_only = s->rd_only;
     P->es_wolf = s->wolf; /* coulombic(): coulombic.c:27-28 */
+    P->rd_crystal = s->rd_crystal; /* lj(): lj.c:175-216,264-267 */
+    P->rd_crystal_order = s->rd_crystal_order;
     P->cavity_autoreject_absolute = s->cavity_autoreject_absolute;
     P->cavity_autoreject_scale = s->cavity_autoreject_scale;
     P->polarization = s->polarization;
@@ -188,7 +190,6 @@ static void shim_check_supported(const system_t *s) {
     if (s->axilrod_teller) shim_unsupported("axilrod_teller");
     if (s->spectre) shim_unsupported("spectre");
     if (s->polarvdw) shim_unsupported("polarvdw");
-    if (s->rd_crystal) shim_unsupported("rd_crystal");
 }
 
 /* ------------------------------------------------------------------------------------------------

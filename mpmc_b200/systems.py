@@ -276,6 +276,9 @@ def write_input(s: System, path: str, pqr_name: str, ensemble: str = "total_ener
         a("rd_only on")
     if p.es_wolf:
         a("wolf on")
+    if p.rd_crystal:
+        a("rd_crystal on")
+        a(f"rd_crystal_order {p.rd_crystal_order}")
     if p.feynman_hibbs:
         a("feynman_hibbs on")
         a(f"feynman_hibbs_order {p.feynman_hibbs_order}")

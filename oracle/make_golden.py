@@ -91,6 +91,12 @@ def synthetic_cases():
         "mixed_es_wolf": _variant(m, es_wolf=1, feynman_hibbs=0),
         "mixed_tri_es_wolf_nopolar": _variant(t, es_wolf=1, feynman_hibbs=0, polarization=0),
         "co2_fluid_375_es_wolf": _variant(systems.co2_fluid(125), es_wolf=1, feynman_hibbs=0),
+        # LJ image sums (rd_crystal: lj.c:109-162,175-216,264-267)
+        "mixed_rd_crystal2": _variant(m, rd_crystal=1, rd_crystal_order=2),
+        "mixed_tri_rd_crystal2_fh2": _variant(t, rd_crystal=1, rd_crystal_order=2, feynman_hibbs_order=2),
+        "mixed_rd_crystal3_nofh_nopolar": _variant(m, rd_crystal=1, rd_crystal_order=3, feynman_hibbs=0, polarization=0),
+        "mixed_rd_crystal1_wh": _variant(m, rd_crystal=1, rd_crystal_order=1, mixing=MIX_WH, polarization=0),
+        "co2_fluid_375_rd_crystal2": _variant(systems.co2_fluid(125), rd_crystal=1, rd_crystal_order=2),
         "mixed_autoreject_fires": _variant(m, cavity_autoreject_absolute=1, cavity_autoreject_scale=3.2),
         "mixed_autoreject_quiet": _variant(m, cavity_autoreject_absolute=1, cavity_autoreject_scale=0.5),
         "mixed_cutoff7": _variant(m, cutoff=7.0, ewald_alpha=0.45, polar_ewald_alpha=0.45),

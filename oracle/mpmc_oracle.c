@@ -210,6 +210,59 @@ static double o_es_fh(const osys_t *s, int i, int j, double r, double gaussian_t
     return fh2 + fh4;
 }
 
+/* lj(): src/energy/lj.c:175-178 -- with rd_crystal the LJ cutoff (pair test, image sums, LRC) is wider */
+static double o_rd_cutoff(const mpmc_b200_params *P) {
+    if (P->rd_crystal) return 2.0 * P->cutoff * ((double)P->rd_crystal_order - 0.5);
+    return P->cutoff;
+}
+
+/* the image sums of lj() with rd_crystal on: src/energy/lj.c:196-216.  d = pos_i - pos_j, NOT imaged. */
+static void o_crystal_sums(const osys_t *s, int i, int j, const opair_t *e, double cutoff, double *s6, double *s12) {
+    const mpmc_b200_params *P = s->p;
+    int l[3], p, q, m = P->rd_crystal_order - 1;
+    double a[3], r, sor;
+    *s6 = 0;
+    *s12 = 0;
+    for (l[0] = -m; l[0] <= m; l[0]++)
+        for (l[1] = -m; l[1] <= m; l[1]++)
+            for (l[2] = -m; l[2] <= m; l[2]++) {
+                if (!l[0] && !l[1] && !l[2] && e->rd_excluded) continue; /* no home image for excluded pairs */
+                for (p = 0; p < 3; p++) {
+                    a[p] = 0;
+                    for (q = 0; q < 3; q++) a[p] += P->basis[q][p] * l[q];
+                    a[p] += s->pos[3 * i + p] - s->pos[3 * j + p];
+                }
+                r = sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+                if (r > cutoff) continue;
+                sor = fabs(e->sigma) / r;
+                *s6 += pow(sor, 6);
+                *s12 += pow(sor, 12);
+            }
+}
+
+/* rd_crystal_self(): src/energy/lj.c:109-162 (spectre / polarvdw / cdvdw off): an atom with its own images */
+static double o_crystal_self(const osys_t *s, int i, double cutoff) {
+    const mpmc_b200_params *P = s->p;
+    int l[3], p, q, m = P->rd_crystal_order - 1;
+    double a[3], r, sor, s6 = 0, s12 = 0;
+    if (s->sig[i] == 0 && s->eps[i] == 0) return 0;
+    for (l[0] = -m; l[0] <= m; l[0]++)
+        for (l[1] = -m; l[1] <= m; l[1]++)
+            for (l[2] = -m; l[2] <= m; l[2]++) {
+                if (!l[0] && !l[1] && !l[2]) continue;
+                for (p = 0; p < 3; p++) {
+                    a[p] = 0;
+                    for (q = 0; q < 3; q++) a[p] += P->basis[q][p] * l[q];
+                }
+                r = sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+                if (r > cutoff) continue;
+                sor = fabs(s->sig[i]) / r;
+                s6 += 0.5 * pow(sor, 6);
+                s12 += 0.5 * pow(sor, 12);
+            }
+    return 4.0 * s->eps[i] * ((s->sig[i] < 0.0 ? 0.0 : s12) - s6);
+}
+
 typedef struct {
     double rd_pair, lrc_pair, es_real, min_r;
     double n_tested, n_lj, n_es;
@@ -221,7 +274,7 @@ typedef struct {
  * When seq != NULL the terms are added to seq[] in reference order instead. */
 static void o_pair_row(const osys_t *s, int i, orow_t *acc) {
     const mpmc_b200_params *P = s->p;
-    double cutoff = P->cutoff, alpha = P->ewald_alpha;
+    double cutoff = P->cutoff, alpha = P->ewald_alpha, rd_cutoff = o_rd_cutoff(P);
     int j;
     for (j = i + 1; j < s->n; j++) {
         opair_t e;
@@ -234,12 +287,13 @@ static void o_pair_row(const osys_t *s, int i, orow_t *acc) {
         /* ---- lj() ---- */
         {
             double rd = 0, lrc = 0;
-            if (P->rd_lrc) lrc = o_lrc_pair(s, &e, cutoff);
-            if ((g.rimg - O_SMALL_dR < cutoff) && !e.rd_excluded && !e.frozen) {
+            if (P->rd_lrc) lrc = o_lrc_pair(s, &e, rd_cutoff);
+            if ((g.rimg - O_SMALL_dR < rd_cutoff) && (!e.rd_excluded || P->rd_crystal) && !e.frozen) { /* lj.c:191-193 */
                 double sor = fabs(e.sigma) / g.rimg;
                 double s6 = sor * sor * sor;
                 s6 *= s6;
                 double s12 = s6 * s6;
+                if (P->rd_crystal) o_crystal_sums(s, i, j, &e, rd_cutoff, &s6, &s12);
                 double term6 = s6, term12 = e.attractive_only ? 0 : s12;
                 rd += 4.0 * e.epsilon * (term12 - term6);
                 if (P->feynman_hibbs) rd += o_lj_fh(s, i, j, g.rimg, e.epsilon, term12, term6);
@@ -920,6 +974,7 @@ static int o_check(const mpmc_b200_params *P) {
     if (P->polarization && !P->polar_iterative && !P->polar_zodid && !P->polar_ewald_full)
         return 3; /* LU inversion path: out of scope */
     if (P->es_wolf && !P->rd_only && P->feynman_hibbs) return 3; /* coulombic.c:293-297: the reference dies */
+    if (P->rd_crystal && P->rd_crystal_order <= 0) return 3;      /* check_input.c:1258-1262 */
     return 0;
 }
 
@@ -1067,8 +1122,12 @@ int mpmc_oracle_energy(const mpmc_b200_params *P, int n, const double *pos, cons
 
     { /* lj(): lj.c:256,270-273 */
         double lrc_self = 0;
+        double crystal_self = 0; /* lj.c:264-267: every atom, frozen ones included; kept in rd_pair */
+        if (P->rd_crystal)
+            for (i = 0; i < n; i++) crystal_self += o_crystal_self(&s, i, o_rd_cutoff(P));
+        tot.rd_pair += crystal_self;
         if (P->rd_lrc)
-            for (i = 0; i < n; i++) lrc_self += o_lrc_self(&s, i, P->cutoff);
+            for (i = 0; i < n; i++) lrc_self += o_lrc_self(&s, i, o_rd_cutoff(P));
         out->rd_pair = tot.rd_pair;
         out->rd_lrc = tot.lrc_pair + lrc_self;
         out->rd = (tot.rd_pair + tot.lrc_pair) + lrc_self;

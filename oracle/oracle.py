@@ -114,6 +114,8 @@ def parse_snapshot(text: str, name: str = ""):
     d["basis"] = np.array(par["basis"]).reshape(3, 3)
     d["reciprocal_basis"] = np.array(par["reciprocal_basis"]).reshape(3, 3)
     d["es_wolf"] = int(par.get("wolf", 0))
+    d["rd_crystal"] = int(par.get("rd_crystal", 0))
+    d["rd_crystal_order"] = int(par.get("rd_crystal_order", 0))
     d["mixing"] = MIX_WH if par["waldmanhagler"] else MIX_HALGREN if par["halgren_mixing"] else MIX_C6 if par[
         "c6_mixing"] else MIX_LB
     p = Params.from_dict(d)

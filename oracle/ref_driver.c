@@ -128,6 +128,8 @@ int main(int argc, char **argv) {
     PD(polar_wolf_alpha_lookup_cutoff);
     PD(polar_ewald_alpha);
     PI(wolf);
+    PI(rd_crystal);
+    PI(rd_crystal_order);
     PI(ensemble);
 
     printf("energy returned %.17g\n", e);

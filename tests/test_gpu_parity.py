@@ -60,6 +60,44 @@ def test_es_wolf_matches_oracle_midsize(engine, builder, kw, cutoffs, monkeypatc
                 eng.close()
 
 
+@pytest.mark.parametrize("builder,kw,order", [
+    (systems.co2_fluid, dict(n_mol=1500), 2),
+    (systems.h2_fluid, dict(n_atoms=2000), 3),
+])
+def test_rd_crystal_matches_oracle_midsize(engine, builder, kw, order):
+    """rd_crystal (lj.c:175-216,264-267): LJ image sums over many tile pairs (diagonal and off-diagonal tiles, ragged
+    last tile), same-molecule pairs without their home image, the atoms' own images, the wider LRC cutoff."""
+    from oracle import oracle
+
+    s = builder(**kw)
+    s.params.rd_crystal = 1
+    s.params.rd_crystal_order = order
+    exp, _, oarr = oracle.energy(s, nthreads=0)
+    engine.set_system(s)
+    got = engine.energy()
+    gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=f"{s.name} rd_crystal {order}")
+    assert abs(got.rd_pair - exp.rd_pair) <= 1e-10 * abs(exp.rd_pair)
+    if s.params.polarization:
+        gu.assert_atom_arrays(engine.atom_arrays(), oarr, s, rtol=1e-10, label=s.name)
+    # switching the option off again on the same context gives the plain LJ sum back
+    s.params.rd_crystal = 0
+    plain, _, _ = oracle.energy(s, nthreads=0)
+    engine.set_system(s)
+    got = engine.energy()
+    gu.assert_energies(got.to_dict(), plain.to_dict(), rtol=1e-10, label=f"{s.name} rd_crystal off again")
+    assert abs(exp.rd_pair - plain.rd_pair) > 1e-5 * abs(plain.rd_pair)
+
+
+def test_rd_crystal_order_limits(engine):
+    s = systems.h2_fluid(500)
+    s.params.rd_crystal = 1
+    for bad in (0, 5):
+        s.params.rd_crystal_order = bad
+        with pytest.raises(RuntimeError, match="rd.crystal"):
+            engine.set_system(s)
+    engine.set_system(systems.h2_fluid(500))
+
+
 def test_es_wolf_with_feynman_hibbs_is_refused(engine):
     """coulombic.c:293-297: the reference dies on FH + wolf; the engine refuses the parameters (no silent fallback)."""
     s = systems.h2_fluid(500)
