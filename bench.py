@@ -43,19 +43,45 @@ UNIT = "Gpair/s"
 FLOP_GEOM, FLOP_PAIR_FH4, FLOP_PAIR, FLOP_FIELD, FLOP_DIPOLE, FLOP_RECIP = 51.0, 369.0, 153.0, 81.0, 126.0, 49.0
 
 
+OPTION_SUFFIXES = ("_gs_production", "_ewald_full", "_es_wolf", "_rd_crystal1", "_rd_crystal2", "_rd_crystal3",
+                   "_rd_crystal4")
+
+
+def split_workload(name: str):
+    """(base workload, option suffixes left to right): mof_h2_63k_ewald_full -> ("mof_h2_63k", ["_ewald_full"])."""
+    found = []
+    while True:
+        for k in OPTION_SUFFIXES:
+            if name.endswith(k):
+                found.insert(0, k)
+                name = name[:-len(k)]
+                break
+        else:
+            return name, found
+
+
+def apply_options(s, suffixes):
+    """The option suffixes of a workload name applied to a system (the full-size one or the CPU arm's sample)."""
+    p = s.params
+    for k in suffixes:
+        if k == "_gs_production":  # the solver options of MPMC's production inputs (Gauss-Seidel, single GPU)
+            p.polar_gs_ranked, p.polar_max_iter, p.polar_palmo, p.polar_wolf, p.polar_wolf_alpha = 1, 4, 1, 1, 0.13
+        elif k == "_ewald_full":  # SURVEY 8f f1: the same system solved with full-Ewald polarization
+            p.polar_ewald_full = 1
+        elif k == "_es_wolf":  # SURVEY 8f f4: coulombic_wolf() instead of the Ewald sum (the reference needs FH off)
+            p.es_wolf, p.feynman_hibbs = 1, 0
+        elif k.startswith("_rd_crystal"):  # SURVEY 8f f4: LJ summed over the (2*order-1)^3 periodic images
+            p.rd_crystal, p.rd_crystal_order = 1, int(k[-1])
+    return s
+
+
 def build_workload(name: str):
-    """Synthetic systems of BASELINE.json's configs."""
+    """Synthetic systems of BASELINE.json's configs, optionally with option suffixes."""
     from mpmc_b200 import systems
 
-    if name.endswith("_gs_production"):  # the solver options of MPMC's production inputs (Gauss-Seidel, single GPU)
-        s = build_workload(name[:-len("_gs_production")])
-        p = s.params
-        p.polar_gs_ranked, p.polar_max_iter, p.polar_palmo, p.polar_wolf, p.polar_wolf_alpha = 1, 4, 1, 1, 0.13
-        return s
-    if name.endswith("_ewald_full"):  # SURVEY 8f f1: the same system solved with full-Ewald polarization
-        s = build_workload(name[:-len("_ewald_full")])
-        s.params.polar_ewald_full = 1
-        return s
+    base, suffixes = split_workload(name)
+    if suffixes:
+        return apply_options(build_workload(base), suffixes)
     if name == "mof_h2_63k":  # config 4: MOF supercell + H2, ~63k atoms, full polarizable energy, Jacobi x10
         return systems.mof_h2()
     if name == "mof_h2_21k":  # config 3 shape: 128.388 x 42.796 x 42.796 A, Jacobi x4 (3_PCN61/iter.inp)
@@ -140,6 +166,19 @@ def _cpu_sample_system(workload: str, budget_s: float, calls: int):
     """A bounded sample of the workload: the same generator and options on a smaller supercell, so
     that `calls` evaluations of the O(N^2) CPU path fit in `budget_s` (2.1e-7 N^2 s per reference
     call on one core of this class of host, from the 1,236-atom sample: 0.32 s)."""
+    from mpmc_b200 import systems
+
+    workload, suffixes = split_workload(workload)
+    for k in suffixes:  # the image sums multiply the reference's LJ loop
+        if k.startswith("_rd_crystal"):
+            budget_s /= 1.0 + 0.3 * (2 * int(k[-1]) - 1) ** 3
+    s, what = _cpu_sample_base(workload, budget_s, calls)
+    if suffixes:
+        what += " with the options of " + "".join(suffixes)
+    return apply_options(s, suffixes), what
+
+
+def _cpu_sample_base(workload: str, budget_s: float, calls: int):
     from mpmc_b200 import systems
 
     if workload.startswith("mof_h2"):

@@ -34,6 +34,15 @@ def main():
     s.params.polar_sor, s.params.polar_gamma = 1, 0.8
     cases.append(("mixed_tri_sor", s))
     cases.append(("co2_nopolar", systems.co2_fluid(500)))
+    s = systems.co2_fluid(500)  # coulombic_wolf(): no reciprocal / self term on any rank
+    s.params.es_wolf, s.params.feynman_hibbs = 1, 0
+    cases.append(("co2_es_wolf", s))
+    s = systems.mixed_small()  # rd_crystal: tile pairs of the image sums split by rank, self-image term on rank 0 only
+    s.params.rd_crystal, s.params.rd_crystal_order = 1, 2
+    cases.append(("mixed_rd_crystal2", s))
+    s = systems.co2_fluid(500)
+    s.params.rd_crystal, s.params.rd_crystal_order = 1, 3
+    cases.append(("co2_rd_crystal3", s))
     ok = True
     for name, s in cases:
         one = Engine(local, stream=stream.cuda_stream)
