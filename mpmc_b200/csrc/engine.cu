@@ -1971,11 +1971,11 @@ int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
                                                   p->polar_gs_ranked != c->P.polar_gs_ranked ||
                                                   p->polar_ewald_full != c->P.polar_ewald_full ||
                                                   (p->rd_crystal != 0) != (c->P.rd_crystal != 0));
+    if (check_supported(*p)) return 3;  // refused parameters leave the context as it was
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;
     c->analytic_dirty = true;
-    if (check_supported(c->P)) return 3;
     if (repack_needed) {
         CU(cudaSetDevice(c->device));
         if (repack(c)) return 10;

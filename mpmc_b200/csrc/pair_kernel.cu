@@ -492,6 +492,7 @@ __global__ void __launch_bounds__(TILE) crystal_lj_kernel(Cell c, AtomsDev a, Pa
     __syncthreads();
 
     const int home = (nimg - 1) / 2;  // l = (0,0,0) sits in the middle of the symmetric loop nest
+    const double cut2_lo = rd_cutoff * rd_cutoff * (1.0 - 1e-12), cut2_hi = rd_cutoff * rd_cutoff * (1.0 + 1e-12);
     const bool lj_i = (ei != 0.0) && (si != 0.0);
     const int j0 = (t.x == t.y) ? tid + 1 : 0;
     double rd = 0.0;
@@ -511,19 +512,21 @@ __global__ void __launch_bounds__(TILE) crystal_lj_kernel(Cell c, AtomsDev a, Pa
         double eps, sigma;
         bool att;
         mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
-        const double asig = fabs(sigma);
+        const double sig2 = sigma * sigma;
         const bool same = (moli == smol[jj]);
         double s6 = 0.0, s12 = 0.0;
         for (int m = 0; m < nimg; m++) {
             if (same && m == home) continue;  // lj.c:203
             const double ax = ix[m] + dx, ay = iy[m] + dy, az = iz[m] + dz;
-            const double r = sqrt(ax * ax + ay * ay + az * az);
-            if (r > rd_cutoff) continue;  // lj.c:213
-            const double sor = asig / r;
-            double t6 = sor * sor * sor;
-            t6 *= t6;
+            const double r2 = ax * ax + ay * ay + az * az;
+            // lj.c:213 `r > cutoff` without the square root except in a 1e-12-wide shell around the cutoff
+            if (r2 > cut2_hi) continue;
+            if (r2 >= cut2_lo && sqrt(r2) > rd_cutoff) continue;
+            const double y = rsqrt_fast(r2);  // (|sigma| / r)^6 = (sigma^2 / r^2)^3: no sqrt, no division
+            const double t2 = sig2 * (y * y);
+            const double t6 = t2 * t2 * t2;
             s6 += t6;
-            s12 += t6 * t6;
+            s12 = fma(t6, t6, s12);
         }
         const double term6 = s6, term12 = att ? 0.0 : s12;
         double u = 4.0 * eps * (term12 - term6);
