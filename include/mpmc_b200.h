@@ -179,6 +179,15 @@ int mpmc_b200_set_shard(mpmc_b200_ctx *ctx, int rank, int world);
 
 /* energy(): all kernels + device->host copy of the scalars; synchronous. */
 int mpmc_b200_energy(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
+/* Opt-in incremental evaluation (the reference recomputes everything every step, TODO:2; its own pair_t cache,
+ * src/energy/pairs.c:243-250, is the same idea): with on != 0 -- or MPMC_B200_INCREMENTAL=1 in the environment when the
+ * context is created -- mpmc_b200_energy() after mpmc_b200_set_positions() of at most 128 atoms re-evaluates only the
+ * pairs that contain a moved atom and the moved atoms' terms of S(k), and adds the change to the last result.  Applies
+ * to non-polarizable runs (or rd_only) without cavity_autoreject_absolute and rd_crystal on one GPU; everything else,
+ * every set_params / set_atoms, and every 256th call (MPMC_B200_INCREMENTAL_REFRESH) is a full evaluation.  Results
+ * agree with the full evaluation to rounding, not bit for bit, hence opt-in.  mpmc_b200_counters.reserved is 1 when
+ * the last evaluation was incremental; energies.min_intermolecular_r is then not maintained (0). */
+int mpmc_b200_set_incremental(mpmc_b200_ctx *ctx, int on);
 /* polar() alone: static field + solver + U_pol; synchronous. */
 int mpmc_b200_polar(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
 

@@ -303,6 +303,7 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_set_atoms.argtypes = [vp, C.c_int, dp, dp, dp, dp, dp, dp, ip, ip]
     lib.mpmc_b200_set_positions.argtypes = [vp, C.c_int, C.c_int, dp]
     lib.mpmc_b200_set_shard.argtypes = [vp, C.c_int, C.c_int]
+    lib.mpmc_b200_set_incremental.argtypes = [vp, C.c_int]
     lib.mpmc_b200_energy.argtypes = [vp, C.POINTER(Energies)]
     lib.mpmc_b200_polar.argtypes = [vp, C.POINTER(Energies)]
     lib.mpmc_b200_energy_enqueue.argtypes = [vp]
@@ -339,7 +340,7 @@ ABI_SYMBOLS = [
     "mpmc_b200_device_buffer", "mpmc_b200_shard_rows", "mpmc_b200_shard_field_rows",
     "mpmc_b200_get_atom_arrays", "mpmc_b200_atom_arrays_complete",
     "mpmc_b200_peer_export", "mpmc_b200_peer_connect", "mpmc_b200_peer_active",
-    "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak",
+    "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak", "mpmc_b200_set_incremental",
 ]
 
 
@@ -388,6 +389,13 @@ class Engine:
     def set_positions(self, first: int, pos: np.ndarray):
         pos = np.ascontiguousarray(pos, dtype=np.float64).reshape(-1, 3)
         self._check(self.lib.mpmc_b200_set_positions(self._ctx, int(first), int(pos.shape[0]), _dp(pos)))
+
+    def set_incremental(self, on: bool):
+        """Opt-in incremental energy() after small moves (include/mpmc_b200.h: mpmc_b200_set_incremental)."""
+        self._check(self.lib.mpmc_b200_set_incremental(self._ctx, 1 if on else 0))
+
+    def last_eval_incremental(self) -> bool:
+        return bool(self.counters().reserved)
 
     def set_shard(self, rank: int, world: int):
         self._check(self.lib.mpmc_b200_set_shard(self._ctx, rank, world))

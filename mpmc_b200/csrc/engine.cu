@@ -200,6 +200,17 @@ struct mpmc_b200_ctx {
     double* h_wb = nullptr;       // pinned
     size_t h_wb_cap = 0;
 
+    // incremental evaluation after small moves (opt-in: MPMC_B200_INCREMENTAL=1 / mpmc_b200_set_incremental)
+    bool inc_enabled = false;
+    bool inc_valid = false;          // inc_base / sf describe the positions the device held at the last evaluation
+    int inc_since_full = 0;          // incremental evaluations since the last full one (rounding drift bound)
+    mpmc_b200_energies inc_base;     // energies of the last evaluation
+    mpmc_b200_counters inc_cnt;      // its counters
+    std::vector<MovedRec> inc_moved; // atoms that moved since then, with their positions then and now
+    std::vector<int> inc_slot;       // per atom: index in inc_moved + 1, 0 = not moved
+    DevBuf<MovedRec> inc_moved_dev;
+    DevBuf<double> inc_part, inc_out;
+
     // host-side analytic terms
     double lrc_pair = 0, lrc_self = 0, es_self = 0;
     bool analytic_dirty = true;
@@ -694,6 +705,9 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
 
 static int repack(Ctx* c) {
     const int n = c->n;
+    c->inc_valid = false;
+    c->inc_moved.clear();
+    c->inc_slot.assign(n, 0);
     cudaStream_t st = c->stream;
     c->n_pad = std::max(round_up(n, TILE * std::max(c->world, 1)), TILE);
     const int np = c->n_pad;
@@ -1669,6 +1683,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
     const mpmc_b200_params& P = c->P;
     cudaStream_t st = c->stream;
     CU(cudaSetDevice(c->device));
+    c->inc_valid = false;  // S(k) and the sums are rewritten: mpmc_b200_energy() re-arms the incremental path afterwards
     if (c->kdirty)
         if (build_kvectors(c)) return 10;
     if (c->analytic_dirty) compute_analytic(c);
@@ -1879,6 +1894,8 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         // MPMC_B200_CUTOFF=tiles selects the all-pairs tile form of K1 / K3 (no cluster culling)
         v = getenv("MPMC_B200_CUTOFF");
         c->use_clusters = !(v && strcmp(v, "tiles") == 0);
+        v = getenv("MPMC_B200_INCREMENTAL");
+        c->inc_enabled = v && v[0] == '1';
         v = getenv("MPMC_B200_K7_SF");
         c->k7_grouped_sf = !(v && strcmp(v, "plain") == 0);
         v = getenv("MPMC_B200_K7_LIST_GB");
@@ -1972,6 +1989,7 @@ int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
                                                   p->polar_ewald_full != c->P.polar_ewald_full ||
                                                   (p->rd_crystal != 0) != (c->P.rd_crystal != 0));
     if (check_supported(*p)) return 3;  // refused parameters leave the context as it was
+    c->inc_valid = false;
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;
@@ -2030,6 +2048,30 @@ int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double
         CU(cudaStreamSynchronize(c->stream));  // staging buffer reuse
     }
     double *sx = c->h_stage, *sy = sx + count, *sz = sy + count;
+    if (c->inc_valid) {  // remember which atoms really move, and where they were at the last evaluation
+        for (int k = 0; k < count && c->inc_valid; k++) {
+            const int g = first + k;
+            if (pos[3 * k] == c->hx[g] && pos[3 * k + 1] == c->hy[g] && pos[3 * k + 2] == c->hz[g]) continue;
+            if (!c->inc_slot[g]) {
+                if ((int)c->inc_moved.size() >= INC_MAX_MOVED) {
+                    c->inc_valid = false;  // too many: the next evaluation is a full one
+                    break;
+                }
+                MovedRec r;
+                r.xo = c->hx[g], r.yo = c->hy[g], r.zo = c->hz[g];
+                r.q = c->hq[g], r.eps = c->heps[g], r.sig = c->hsig[g], r.mm = c->hmm[g];
+                r.mol = c->hmol[g], r.fl = F_VALID | (c->hfrozen[g] ? F_FROZEN : 0), r.idx = g, r.pad = 0;
+                c->inc_moved.push_back(r);
+                c->inc_slot[g] = (int)c->inc_moved.size();
+            }
+            MovedRec& r = c->inc_moved[c->inc_slot[g] - 1];
+            r.xn = pos[3 * k], r.yn = pos[3 * k + 1], r.zn = pos[3 * k + 2];
+        }
+        if (!c->inc_valid) {
+            for (const MovedRec& r : c->inc_moved) c->inc_slot[r.idx] = 0;
+            c->inc_moved.clear();
+        }
+    }
     for (int k = 0; k < count; k++) {
         sx[k] = c->hx[first + k] = pos[3 * k];
         sy[k] = c->hy[first + k] = pos[3 * k + 1];
@@ -2070,12 +2112,114 @@ int mpmc_b200_set_shard(mpmc_b200_ctx* c, int rank, int world) {
     return 0;
 }
 
+// ---- incremental evaluation -----------------------------------------------------------------------------
+// Applies to what changes with a few moved atoms and nothing else: the K1 pair sums and S(k).  Polarization (every dipole
+// changes), the cavity minimum distance (not decomposable) and the rd_crystal image sums keep the full evaluation.
+static bool inc_supported(const Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    return c->inc_enabled && c->world == 1 && !(P.polarization && !P.rd_only) && !P.cavity_autoreject_absolute &&
+           !P.rd_crystal;
+}
+
+static void inc_clear_moved(Ctx* c) {
+    for (const MovedRec& r : c->inc_moved) c->inc_slot[r.idx] = 0;
+    c->inc_moved.clear();
+}
+
+static int incremental_energy(Ctx* c, mpmc_b200_energies* out) {
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    CU(cudaSetDevice(c->device));
+    // an atom that moved and came back (a rejected move restored bit for bit) has nothing to add
+    std::vector<MovedRec> mv;
+    for (const MovedRec& r : c->inc_moved)
+        if (!(r.xn == r.xo && r.yn == r.yo && r.zn == r.zo)) mv.push_back(r);
+    c->launches = 0;
+    *out = c->inc_base;
+    c->cnt = c->inc_cnt;
+    if (!mv.empty()) {
+        const int nb = c->n_pad / TILE;
+        const int stride = round_up(nb, 32);
+        if (c->inc_moved_dev.ensure(INC_MAX_MOVED) || c->inc_part.ensure((size_t)INC_NPART * stride) || c->inc_out.ensure(8))
+            FAIL(11, "cudaMalloc failed");
+        CU(cudaMemcpyAsync(c->inc_moved_dev.p, mv.data(), sizeof(MovedRec) * mv.size(), cudaMemcpyHostToDevice, st));
+        PairOpts po;
+        po.ewald_alpha = P.ewald_alpha;
+        po.temperature = P.temperature;
+        po.fh_order = P.feynman_hibbs ? (P.feynman_hibbs_order == 2 ? 2 : 4) : 0;
+        po.mixing = P.mixing;
+        po.rd_only = P.rd_only;
+        po.es_wolf = P.es_wolf;
+        const Cell cell = make_cell(P);
+        launch_pair_delta(cell, is_ortho(P), atoms_dev(c), po, c->inc_moved_dev.p, (int)mv.size(), c->inc_part.p, stride,
+                          c->inc_out.p, st);
+        c->launches += 2;
+        const bool recip = !P.rd_only && !P.es_wolf;
+        if (recip) {
+            KVecDev kv;
+            kv.nk = c->nk;
+            kv.kmax = P.ewald_kmax;
+            kv.l = c->kl.p;
+            kv.weight = c->kweight.p;
+            launch_recip_delta(kv, c->kvec.p, c->inc_moved_dev.p, (int)mv.size(), c->sf.p, 4.0 * M_PI / P.volume,
+                               c->inc_out.p + INC_NPART, st);
+            c->launches += 2;
+        }
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(c->h_scalars, c->inc_out.p, sizeof(double) * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        const double* h = c->h_scalars;
+        out->rd_pair += h[0];
+        out->rd = (out->rd_pair + c->lrc_pair) + c->lrc_self;
+        if (!P.rd_only) {
+            out->es_real += h[1] - h[2];
+            if (recip) out->es_recip = h[INC_NPART];
+            out->coulombic = out->es_real + out->es_recip + out->es_self;
+        }
+        out->total = out->rd + out->coulombic + out->polar;
+        c->cnt.pairs_lj += h[3];
+        c->cnt.pairs_es += h[4];
+    }
+    out->min_intermolecular_r = 0.0;  // not maintained by the incremental path (cavity_autoreject disables it)
+    c->cnt.kernel_launches = c->launches;
+    c->cnt.reserved = 1;  // the last evaluation was incremental
+    c->inc_base = *out;
+    c->inc_cnt = c->cnt;
+    inc_clear_moved(c);
+    c->inc_since_full++;
+    return 0;
+}
+
 int mpmc_b200_energy(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
     if (!c || !out) FAIL(1, "null argument");
     if (c->world > 1) FAIL(2, "sharded contexts are driven with mpmc_b200_energy_enqueue / mpmc_b200_polar_stage");
+    static const int refresh = [] { const char* v = getenv("MPMC_B200_INCREMENTAL_REFRESH"); return v ? atoi(v) : 256; }();
+    if (c->inc_valid && inc_supported(c) && !c->kdirty && !c->analytic_dirty && c->inc_since_full < refresh) {
+        const int rc = incremental_energy(c, out);
+        if (rc) c->inc_valid = false;
+        return rc;
+    }
+    c->inc_valid = false;
+    inc_clear_moved(c);
     int rc = enqueue_energy(c, true, true);
     if (rc) return rc;
-    return finish_energy(c, out);
+    rc = finish_energy(c, out);
+    if (!rc && inc_supported(c) && !out->autorejected) {  // this evaluation is the base of the next incremental ones
+        c->inc_base = *out;
+        c->inc_cnt = c->cnt;
+        c->inc_since_full = 0;
+        if ((int)c->inc_slot.size() != c->n) c->inc_slot.assign(c->n, 0);
+        c->inc_valid = true;
+    }
+    return rc;
+}
+
+int mpmc_b200_set_incremental(mpmc_b200_ctx* c, int on) {
+    if (!c) FAIL(1, "null ctx");
+    c->inc_enabled = on != 0;
+    c->inc_valid = false;
+    inc_clear_moved(c);
+    return 0;
 }
 
 int mpmc_b200_polar(mpmc_b200_ctx* c, mpmc_b200_energies* out) {

@@ -44,6 +44,19 @@ struct PairOpts {
 int crystal_max_images();
 void launch_crystal_lj(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, double rd_cutoff, const double* img,
                        int nimg, const int2* tiles, int ntiles, double* partial, int stride, double* out, cudaStream_t s);
+// ---- incremental evaluation after a small move (opt-in) ---------------------------------------------
+// The atoms whose positions changed since the last evaluation, with their positions then (o) and now (n).
+struct MovedRec {
+    double xn, yn, zn, xo, yo, zo, q, eps, sig, mm;
+    int mol, fl, idx, pad;
+};
+constexpr int INC_MAX_MOVED = 128;
+constexpr int INC_NPART = 5;  // d(rd), d(es), d(intra), d(n_lj), d(n_es)
+// Change of the K1 sums: for every pair with at least one moved atom, the pair terms at the new positions minus the
+// pair terms at the old ones (each such pair once).  One thread per atom j of the list-ordered arrays (which hold the
+// NEW positions), the moved atoms in shared memory.  partial [INC_NPART][stride], one column per CTA; out[INC_NPART].
+void launch_pair_delta(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const MovedRec* moved, int nmoved,
+                       double* partial, int stride, double* out, cudaStream_t s);
 constexpr int PAIR_NPART = 8;  // rd, es, intra, min_r, n_tested, n_lj, n_es, (unused)
 void launch_pair_energy(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const int2* tiles, int ntiles,
                         double* partial /*[PAIR_NPART][ntiles_stride]*/, int stride, cudaStream_t s);
@@ -74,6 +87,10 @@ void launch_recip_sf(const Cell& c, const SubsetDev& atoms, const KVecDev& kv, i
 int launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks, double scale,
                         double* sf /*[2][nk]*/, double* energy_out, int k_begin, int k_end, cudaStream_t s, int mu_n = 0,
                         int mu_np = 0, const double* mu = nullptr, double* mu_total = nullptr);
+// S(k) += sum over the moved, charged, mobile atoms of q (e^{ik.r_new} - e^{ik.r_old}); then energy_out as
+// launch_recip_finish computes it.  Two launches.
+void launch_recip_delta(const KVecDev& kv, const double* kvec /*[3][nk]*/, const MovedRec* moved, int nmoved, double* sf,
+                        double scale, double* energy_out, cudaStream_t s);
 // recip_term() of the Ewald static field (src/polarization/polar_ewald.c:78-132)
 void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, const double* kvec /*[3][nk]*/,
                         const double* sf, double scale, int row_begin, int row_end, double* ef /*[3][n_pad]*/,

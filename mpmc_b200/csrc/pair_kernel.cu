@@ -591,6 +591,93 @@ void launch_crystal_lj(const Cell& c, bool ortho, const AtomsDev& a, const PairO
     crystal_reduce_kernel<<<1, 1024, 0, s>>>(partial, ntiles > 0 ? ntiles : 0, stride, out);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Incremental evaluation (opt-in): after a move of a few atoms only the pairs that contain a moved atom
+// change.  Thread j (list order; the arrays hold the NEW positions) walks the moved atoms m: pair terms with m at its
+// new position minus pair terms with m at its old one -- pair_terms() itself, so exclusions, mixing, FH, the
+// intramolecular erf term and the Wolf form are those of K1.  A pair of two moved atoms is taken once (at the smaller
+// moved index) with both atoms old / both new.  Differences are formed per pair before any summation.
+template <bool ORTHO, int FH>
+__global__ void __launch_bounds__(TILE) pair_delta_kernel(Cell c, AtomsDev a, PairConsts k, int mixing, int rd_only,
+                                                          const MovedRec* __restrict__ moved, int nmoved,
+                                                          double* __restrict__ partial, int stride) {
+    __shared__ MovedRec smv[INC_MAX_MOVED];
+    __shared__ double red[32];
+    const int tid = threadIdx.x;
+    for (int m = tid; m < nmoved; m += TILE) smv[m] = moved[m];
+    __syncthreads();
+    const int j = blockIdx.x * TILE + tid;
+    const double xj = a.x[j], yj = a.y[j], zj = a.z[j], qj = a.q[j], ej = a.eps[j], sj = a.sig[j], mj = a.molmass[j];
+    const int molj = a.mol[j], fj = a.flags[j];
+    int mine = -1;  // index of j in the moved list
+    for (int m = 0; m < nmoved; m++)
+        if (smv[m].idx == j) mine = m;
+    const double xjo = mine >= 0 ? smv[mine].xo : xj, yjo = mine >= 0 ? smv[mine].yo : yj, zjo = mine >= 0 ? smv[mine].zo : zj;
+    double d_rd = 0.0, d_es = 0.0, d_intra = 0.0;
+    int d_nlj = 0, d_nes = 0;
+    for (int m = 0; m < nmoved; m++) {
+        if (mine >= 0 && mine <= m) continue;  // j itself, or a moved pair already taken at the smaller index
+        const MovedRec& r = smv[m];
+        const bool lj_i = (r.eps != 0.0) && (r.sig != 0.0) && !k.no_lj;
+        PairAcc An = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0}, Ao = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
+        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, r.xn, r.yn, r.zn, r.q, r.eps, r.sig, r.mm, r.mol, r.fl, lj_i, xj, yj, zj, qj,
+                              ej, sj, mj, molj, fj, An);
+        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, r.xo, r.yo, r.zo, r.q, r.eps, r.sig, r.mm, r.mol, r.fl, lj_i, xjo, yjo, zjo,
+                              qj, ej, sj, mj, molj, fj, Ao);
+        d_rd += An.rd - Ao.rd;
+        d_es += An.es - Ao.es;
+        d_intra += An.intra - Ao.intra;
+        d_nlj += An.n_lj - Ao.n_lj;
+        d_nes += An.n_es - Ao.n_es;
+    }
+    double v = block_reduce<0>(d_rd, red);
+    if (tid == 0) partial[0 * stride + blockIdx.x] = v;
+    v = block_reduce<0>(d_es, red);
+    if (tid == 0) partial[1 * stride + blockIdx.x] = v;
+    v = block_reduce<0>(d_intra, red);
+    if (tid == 0) partial[2 * stride + blockIdx.x] = v;
+    v = block_reduce<0>((double)d_nlj, red);
+    if (tid == 0) partial[3 * stride + blockIdx.x] = v;
+    v = block_reduce<0>((double)d_nes, red);
+    if (tid == 0) partial[4 * stride + blockIdx.x] = v;
+}
+
+__global__ void __launch_bounds__(1024) delta_reduce_kernel(const double* __restrict__ partial, int ncols, int stride,
+                                                            double* __restrict__ out) {
+    __shared__ double red[32];
+    for (int q = 0; q < INC_NPART; q++) {
+        double acc = 0.0;
+        for (int t = threadIdx.x; t < ncols; t += blockDim.x) acc += partial[q * stride + t];
+        const double v = block_reduce<0>(acc, red);
+        if (threadIdx.x == 0) out[q] = v;
+    }
+}
+
+void launch_pair_delta(const Cell& c, bool ortho, const AtomsDev& a, const PairOpts& o, const MovedRec* moved, int nmoved,
+                       double* partial, int stride, double* out, cudaStream_t s) {
+    const PairConsts k = make_pair_consts(c, o);
+    const int nb = a.n_pad / TILE;
+#define LAUNCH(ORTHO, FH) \
+    pair_delta_kernel<ORTHO, FH><<<nb, TILE, 0, s>>>(c, a, k, o.mixing, o.rd_only, moved, nmoved, partial, stride)
+    if (ortho) {
+        if (o.fh_order == 0)
+            LAUNCH(true, 0);
+        else if (o.fh_order == 2)
+            LAUNCH(true, 2);
+        else
+            LAUNCH(true, 4);
+    } else {
+        if (o.fh_order == 0)
+            LAUNCH(false, 0);
+        else if (o.fh_order == 2)
+            LAUNCH(false, 2);
+        else
+            LAUNCH(false, 4);
+    }
+#undef LAUNCH
+    delta_reduce_kernel<<<1, 1024, 0, s>>>(partial, nb, stride, out);
+}
+
 void launch_pair_reduce(const double* partial, int ntiles, int stride, double* out, cudaStream_t s) {
     pair_reduce_kernel<<<1, 1024, 0, s>>>(partial, ntiles, stride, out);
 }

@@ -214,6 +214,36 @@ int launch_recip_finish(const KVecDev& kv, const double* sf_partial, int nchunks
     return launches;
 }
 
+// Incremental structure factor: one thread per k-vector adds the change of the moved atoms' terms.
+__global__ void __launch_bounds__(128) recip_delta_kernel(int nk, const double* __restrict__ kvec,
+                                                          const MovedRec* __restrict__ moved, int nmoved,
+                                                          double* __restrict__ sf) {
+    __shared__ MovedRec smv[INC_MAX_MOVED];
+    for (int m = threadIdx.x; m < nmoved; m += blockDim.x) smv[m] = moved[m];
+    __syncthreads();
+    const int ik = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ik >= nk) return;
+    const double kx = kvec[ik], ky = kvec[nk + ik], kz = kvec[2 * nk + ik];
+    double re = 0.0, im = 0.0;
+    for (int m = 0; m < nmoved; m++) {
+        const MovedRec& r = smv[m];
+        if (r.q == 0.0 || (r.fl & F_FROZEN)) continue;  // coulombic.c:74: charged, mobile atoms only
+        double sn, cn, so, co;
+        sincos(kx * r.xn + ky * r.yn + kz * r.zn, &sn, &cn);
+        sincos(kx * r.xo + ky * r.yo + kz * r.zo, &so, &co);
+        re += r.q * (cn - co);
+        im += r.q * (sn - so);
+    }
+    sf[ik] += re;
+    sf[nk + ik] += im;
+}
+
+void launch_recip_delta(const KVecDev& kv, const double* kvec, const MovedRec* moved, int nmoved, double* sf, double scale,
+                        double* energy_out, cudaStream_t s) {
+    if (kv.nk > 0 && nmoved > 0) recip_delta_kernel<<<(kv.nk + 127) / 128, 128, 0, s>>>(kv.nk, kvec, moved, nmoved, sf);
+    recip_energy_kernel<<<1, 1024, 0, s>>>(kv, sf, scale, energy_out, 0, kv.nk);
+}
+
 void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, const double* kvec, const double* sf,
                         double scale, int row_begin, int row_end, double* ef, cudaStream_t s) {
     const int rows = row_end - row_begin;

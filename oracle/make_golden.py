@@ -188,6 +188,32 @@ def gen_traj(name):
     print(f"{name}: {len(en)} energy rows")
 
 
+# fixed-seed trajectories of synthetic systems: name: (builder, ensemble, extra keywords)
+TRAJ_SYNTH = {
+    # LJ + Ewald, no polarization (BASELINE config 2 in small): the case the incremental path applies to
+    "traj_co2_nvt": (lambda: systems.co2_fluid(125), "nvt", "preset_seeds 4242\nnumsteps 300\nmove_factor 0.05\nrot_factor 0.05"),
+}
+
+
+def gen_traj_synth(name):
+    build, ensemble, extra = TRAJ_SYNTH[name]
+    s = build()
+    first = np.r_[True, s.mol_id[1:] != s.mol_id[:-1]]
+    s.meta["atom_mass"] = np.where(first, s.mol_mass, 0.0)  # update_com() then recovers molecule_t.mass
+    with tempfile.TemporaryDirectory() as td:
+        inp = systems.write_reference_case(s, td, ensemble=ensemble, extra=extra)
+        r = subprocess.run([oracle.REF_BINARY, "input"], cwd=td, capture_output=True, text=True, timeout=3600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        en = [l for l in open(os.path.join(td, "energy.dat")).read().splitlines() if not l.startswith("#")]
+        final = open(os.path.join(td, "final.pqr")).read()
+        inp_text = open(inp).read()
+        pqr = open(os.path.join(td, "system.pqr")).read()
+    with open(os.path.join(GOLD, name + ".json"), "w") as f:
+        json.dump({"input": inp_text, "pqr_name": "system.pqr", "pqr": pqr, "energy_rows": en, "final_pqr": final,
+                   "energy_file": "energy.dat", "final_file": "final.pqr"}, f, indent=0)
+    print(f"{name}: {len(en)} energy rows")
+
+
 def main():
     oracle.build()
     want = set(sys.argv[1:])
@@ -212,6 +238,10 @@ def main():
         if want and name not in want:
             continue
         gen_traj(name)
+    for name in TRAJ_SYNTH:
+        if want and name not in want:
+            continue
+        gen_traj_synth(name)
 
 
 if __name__ == "__main__":

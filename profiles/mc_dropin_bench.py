@@ -84,6 +84,8 @@ def main():
         cases = cases[:1]
     if "--only-socmof" in sys.argv:
         cases = cases[:1]
+    if "--only-co2" in sys.argv:  # config 2 alone (with --incremental: the opt-in incremental path beside the default)
+        cases = cases[2:3]
     for name, s, ens, extra, (a, b), ref in cases:
         v, err = steps_per_s(DROPIN, s, ens, a, b, extra, 900)
         line = {"case": name, "n_atoms": int(s.n), "ensemble": ens, "dropin_mc_steps_per_s": v, "dropin_error": err or None,
@@ -91,7 +93,11 @@ def main():
         if "--ab" in sys.argv:  # the reference-shaped list walks instead of the cached-sequence pass
             v2, err2 = steps_per_s(DROPIN, s, ens, a, b, extra, 900, {"MPMC_B200_SHIM_SLOW": "1"})
             line["dropin_mc_steps_per_s_reference_shaped_walks"] = v2
-        if ref is not None and os.path.exists(REFERENCE):
+        if "--incremental" in sys.argv:  # only the moved molecule's pairs and S(k) terms per step
+            v3, err3 = steps_per_s(DROPIN, s, ens, a, b, extra, 900, {"MPMC_B200_INCREMENTAL": "1"})
+            line["dropin_mc_steps_per_s_incremental"] = v3
+            line["incremental_error"] = err3 or None
+        if ref is not None and os.path.exists(REFERENCE) and "--no-reference" not in sys.argv:
             rv, rerr = steps_per_s(REFERENCE, s, ens, ref[0], ref[1], extra, 600)
             line.update({"reference_mc_steps_per_s_1core": rv, "reference_error": rerr or None, "reference_steps": list(ref)})
             if v and rv:

@@ -64,8 +64,8 @@ def test_dropin_energy_matches_reference_fixture(name, tmp_path):
         gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label=name)
 
 
-@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks"])
-@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt"])
+@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "incremental"])
+@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt"])
 def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     """host_path: the shim's one-pass O(N) duties over the cached pointer sequence (default; every relinking of the
     lists -- uVT insert / remove, rejected moves -- must be detected) or the reference-shaped list walks."""
@@ -76,9 +76,11 @@ def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     env = dict(os.environ)
     if host_path == "list_walks":
         env["MPMC_B200_SHIM_SLOW"] = "1"
+    if host_path == "incremental":  # applies to traj_co2_nvt; the polarizable cases must not change
+        env["MPMC_B200_INCREMENTAL"] = "1"
     r = subprocess.run([PROGRAM, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1200, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    rows = [l for l in (tmp_path / "small.energy.dat").read_text().splitlines() if not l.startswith("#")]
+    rows = [l for l in (tmp_path / d.get("energy_file", "small.energy.dat")).read_text().splitlines() if not l.startswith("#")]
     ref = d["energy_rows"]
     assert len(rows) == len(ref)
     for k, (a, b) in enumerate(zip(rows, ref)):
@@ -86,5 +88,5 @@ def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
         # columns: step E ES RD POL VDW KE T N spin V T_core, printed with 6 decimals
         assert fa[0] == fb[0] and fa[8] == fb[8], f"{name} row {k}: step / N differ: {a} | {b}"
         assert np.all(np.abs(fa - fb) <= 2e-6 + 1e-9 * np.abs(fb)), f"{name} row {k}:\n{a}\n{b}"
-    final = (tmp_path / "small.final.pdb").read_text()
+    final = (tmp_path / d.get("final_file", "small.final.pdb")).read_text()
     assert final == d["final_pqr"], "final configuration differs from the reference's"
