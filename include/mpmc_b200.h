@@ -188,6 +188,13 @@ int mpmc_b200_energy(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
  * agree with the full evaluation to rounding, not bit for bit, hence opt-in.  mpmc_b200_counters.reserved is 1 when
  * the last evaluation was incremental; energies.min_intermolecular_r is then not maintained (0). */
 int mpmc_b200_set_incremental(mpmc_b200_ctx *ctx, int on);
+/* Opt-in warm start of the dipole solve (the other half of the same idea): with on != 0 -- or MPMC_B200_WARM_START=1 in
+ * the environment -- the tolerance-mode iteration (polar_precision != 0; thole_iterative.c:168-259) starts from the
+ * converged dipoles of the previous evaluation instead of init_dipoles()'s gamma alpha E_s (thole_iterative.c:13-25).
+ * It converges to the same tolerance in fewer passes; dipoles and U_pol then agree with the cold start to the solver
+ * tolerance, not bit for bit, and nodestats->polarization_iterations is smaller -- hence opt-in.  Fixed-iteration
+ * runs (polar_max_iter), polar_zodid, polar_ewald_full and sharded contexts are never warm-started. */
+int mpmc_b200_set_warm_start(mpmc_b200_ctx *ctx, int on);
 /* polar() alone: static field + solver + U_pol; synchronous. */
 int mpmc_b200_polar(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
 

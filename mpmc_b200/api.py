@@ -304,6 +304,7 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_set_positions.argtypes = [vp, C.c_int, C.c_int, dp]
     lib.mpmc_b200_set_shard.argtypes = [vp, C.c_int, C.c_int]
     lib.mpmc_b200_set_incremental.argtypes = [vp, C.c_int]
+    lib.mpmc_b200_set_warm_start.argtypes = [vp, C.c_int]
     lib.mpmc_b200_energy.argtypes = [vp, C.POINTER(Energies)]
     lib.mpmc_b200_polar.argtypes = [vp, C.POINTER(Energies)]
     lib.mpmc_b200_energy_enqueue.argtypes = [vp]
@@ -341,6 +342,7 @@ ABI_SYMBOLS = [
     "mpmc_b200_get_atom_arrays", "mpmc_b200_atom_arrays_complete",
     "mpmc_b200_peer_export", "mpmc_b200_peer_connect", "mpmc_b200_peer_active",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak", "mpmc_b200_set_incremental",
+    "mpmc_b200_set_warm_start",
 ]
 
 
@@ -393,6 +395,10 @@ class Engine:
     def set_incremental(self, on: bool):
         """Opt-in incremental energy() after small moves (include/mpmc_b200.h: mpmc_b200_set_incremental)."""
         self._check(self.lib.mpmc_b200_set_incremental(self._ctx, 1 if on else 0))
+
+    def set_warm_start(self, on: bool):
+        """Opt-in warm start of the tolerance-mode dipole solve (include/mpmc_b200.h: mpmc_b200_set_warm_start)."""
+        self._check(self.lib.mpmc_b200_set_warm_start(self._ctx, 1 if on else 0))
 
     def last_eval_incremental(self) -> bool:
         return bool(self.counters().reserved)

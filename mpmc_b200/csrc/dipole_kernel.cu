@@ -261,7 +261,8 @@ void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, con
 // K5
 // ------------------------------------------------------------------------------------------------
 __global__ void dipole_init_kernel(SubsetDev p, const double* __restrict__ ef_static, int atoms_n_pad, double gscale,
-                                   double* __restrict__ es, double* __restrict__ mu, int row_begin, int row_end) {
+                                   double* __restrict__ es, double* __restrict__ mu, int row_begin, int row_end,
+                                   const double* __restrict__ mu_start) {
     const int i = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= row_end) return;
     const int np = p.n_pad;
@@ -271,8 +272,17 @@ __global__ void dipole_init_kernel(SubsetDev p, const double* __restrict__ ef_st
     for (int cdim = 0; cdim < 3; cdim++) {
         const double e = live ? ef_static[cdim * atoms_n_pad + g] : 0.0;
         es[cdim * np + i] = e;
-        mu[cdim * np + i] = (al * e) * gscale;  // thole_iterative.c:19-21
+        // thole_iterative.c:19-21; opt-in warm start: the converged dipoles of the previous evaluation (atom space)
+        mu[cdim * np + i] = (mu_start && live) ? mu_start[cdim * atoms_n_pad + g] : (al * e) * gscale;
     }
+}
+
+// converged dipoles -> atom space, kept as the starting point of the next solve (opt-in warm start)
+__global__ void dipole_keep_kernel(SubsetDev p, const double* __restrict__ mu, int atoms_n_pad, double* __restrict__ mu_keep) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n) return;
+    const int g = p.idx[i];
+    for (int cdim = 0; cdim < 3; cdim++) mu_keep[cdim * atoms_n_pad + g] = mu[cdim * p.n_pad + i];
 }
 
 __global__ void dipole_update_kernel(int n, int np, const double* __restrict__ alpha, UpdateOpts o,
@@ -454,10 +464,16 @@ __global__ void __launch_bounds__(1024) polar_energy_kernel(int n, int np, const
 }
 
 void launch_dipole_init(const SubsetDev& pol, const double* ef_static, int atoms_n_pad, double gamma_scale, double* es,
-                        double* mu, int row_begin, int row_end, cudaStream_t s) {
+                        double* mu, int row_begin, int row_end, cudaStream_t s, const double* mu_start) {
     const int rows = row_end - row_begin;
     if (rows <= 0) return;
-    dipole_init_kernel<<<(rows + 255) / 256, 256, 0, s>>>(pol, ef_static, atoms_n_pad, gamma_scale, es, mu, row_begin, row_end);
+    dipole_init_kernel<<<(rows + 255) / 256, 256, 0, s>>>(pol, ef_static, atoms_n_pad, gamma_scale, es, mu, row_begin, row_end,
+                                                          mu_start);
+}
+
+void launch_dipole_keep(const SubsetDev& pol, const double* mu, int atoms_n_pad, double* mu_keep, cudaStream_t s) {
+    if (pol.n <= 0) return;
+    dipole_keep_kernel<<<(pol.n + 255) / 256, 256, 0, s>>>(pol, mu, atoms_n_pad, mu_keep);
 }
 
 void launch_dipole_update(const SubsetDev& pol, const UpdateOpts& o, const double* epart, int jsplits, const double* es,

@@ -200,6 +200,11 @@ struct mpmc_b200_ctx {
     double* h_wb = nullptr;       // pinned
     size_t h_wb_cap = 0;
 
+    // warm-started dipole solve (opt-in: MPMC_B200_WARM_START=1 / mpmc_b200_set_warm_start): in tolerance
+    // mode the iteration starts from the previous evaluation's converged dipoles instead of gamma alpha E_s
+    bool warm_enabled = false, warm_valid = false;
+    DevBuf<double> mu_keep;  // [3][n_pad], atom space (survives re-sorting of the polarizable subset)
+
     // incremental evaluation after small moves (opt-in: MPMC_B200_INCREMENTAL=1 / mpmc_b200_set_incremental)
     bool inc_enabled = false;
     bool inc_valid = false;          // inc_base / sf describe the positions the device held at the last evaluation
@@ -708,6 +713,7 @@ static int repack(Ctx* c) {
     c->inc_valid = false;
     c->inc_moved.clear();
     c->inc_slot.assign(n, 0);
+    c->warm_valid = false;
     cudaStream_t st = c->stream;
     c->n_pad = std::max(round_up(n, TILE * std::max(c->world, 1)), TILE);
     const int np = c->n_pad;
@@ -1141,6 +1147,14 @@ static UpdateOpts update_opts(const mpmc_b200_params& P, int iteration) {
     return uo;
 }
 
+// Warm start applies where it buys time and nothing else: the tolerance-mode iteration (polar_precision), one GPU, not
+// the zodid / full-Ewald branches.  Fixed-iteration runs keep init_dipoles (their result depends on the start).
+static bool warm_start_applies(const Ctx* c) {
+    const mpmc_b200_params& P = c->P;
+    return c->warm_enabled && c->world == 1 && P.polar_precision != 0.0 && !P.polar_zodid && !P.polar_ewald_full;
+}
+static bool warm_start_now(const Ctx* c) { return warm_start_applies(c) && c->warm_valid; }
+
 // init_dipoles (thole_iterative.c:13-25) for ALL packed rows (needs the complete static field) and
 // the per-evaluation clears
 static int polar_init(Ctx* c) {
@@ -1148,7 +1162,8 @@ static int polar_init(Ctx* c) {
     cudaStream_t st = c->stream;
     const int np = c->n_pad, pp = c->pol.n_pad;
     const double gscale = (!P.polar_sor && !P.polar_esor && !P.polar_ewald_full) ? P.polar_gamma : 1.0;  // polar_ewald.c:144
-    launch_dipole_init(c->pol.dev(), c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st);
+    launch_dipole_init(c->pol.dev(), c->ef_static.p, np, gscale, c->es.p, c->mu.p, 0, pp, st,
+                       warm_start_now(c) ? c->mu_keep.p : nullptr);
     c->launches++;
     if ((c->use_sym || P.polar_ewald_full) && c->pol.n > 0) {
         launch_cluster_boxes(make_cell(P), is_ortho(P), c->pol.dev(), c->cbox.p, st);
@@ -1671,6 +1686,13 @@ static int enqueue_polar(Ctx* c) {
         if (permuted)
             if (from_gs_space()) return 10;
     }
+    if (warm_start_applies(c) && c->pol.n > 0 && !c->pending_iter_success) {  // keep the converged dipoles (atom space)
+        if (c->mu_keep.ensure((size_t)3 * c->n_pad)) FAIL(11, "cudaMalloc failed");
+        launch_dipole_keep(c->pol.dev(), c->mu.p, c->n_pad, c->mu_keep.p, st);
+        c->launches++;
+        c->warm_valid = true;
+    } else
+        c->warm_valid = false;
     phase_end(c, PH_DIPOLE);
 
     return polar_energy_partial(c);
@@ -1894,6 +1916,8 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         // MPMC_B200_CUTOFF=tiles selects the all-pairs tile form of K1 / K3 (no cluster culling)
         v = getenv("MPMC_B200_CUTOFF");
         c->use_clusters = !(v && strcmp(v, "tiles") == 0);
+        v = getenv("MPMC_B200_WARM_START");
+        c->warm_enabled = v && v[0] == '1';
         v = getenv("MPMC_B200_INCREMENTAL");
         c->inc_enabled = v && v[0] == '1';
         v = getenv("MPMC_B200_K7_SF");
@@ -1990,6 +2014,7 @@ int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
                                                   (p->rd_crystal != 0) != (c->P.rd_crystal != 0));
     if (check_supported(*p)) return 3;  // refused parameters leave the context as it was
     c->inc_valid = false;
+    c->warm_valid = false;
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;
@@ -2212,6 +2237,13 @@ int mpmc_b200_energy(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
         c->inc_valid = true;
     }
     return rc;
+}
+
+int mpmc_b200_set_warm_start(mpmc_b200_ctx* c, int on) {
+    if (!c) FAIL(1, "null ctx");
+    c->warm_enabled = on != 0;
+    c->warm_valid = false;
+    return 0;
 }
 
 int mpmc_b200_set_incremental(mpmc_b200_ctx* c, int on) {

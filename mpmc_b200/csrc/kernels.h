@@ -185,7 +185,9 @@ void launch_dipole_commit(const SubsetDev& pol, const UpdateOpts& o, const doubl
 // mu0 = gamma alpha E_s (init_dipoles, thole_iterative.c:13-25); also gathers E_s into packed order
 void launch_dipole_init(const SubsetDev& pol, const double* ef_static /*[3][atoms n_pad]*/, int atoms_n_pad,
                         double gamma_scale, double* es /*[3][pol n_pad]*/, double* mu, int row_begin, int row_end,
-                        cudaStream_t s);
+                        cudaStream_t s, const double* mu_start /*[3][atoms n_pad], optional warm start*/ = nullptr);
+// mu (packed) -> mu_keep [3][atoms n_pad]: the starting point of the next solve when the warm start is on
+void launch_dipole_keep(const SubsetDev& pol, const double* mu, int atoms_n_pad, double* mu_keep, cudaStream_t s);
 // ef_induced_change = -ef_induced + sum_js epart (palmo)
 void launch_palmo_finish(const SubsetDev& pol, const double* epart, int jsplits, const double* eind, double* eic,
                          int row_begin, int row_end, cudaStream_t s);

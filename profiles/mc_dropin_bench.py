@@ -80,6 +80,10 @@ def main():
          systems.mof_h2(cells=(9, 3, 3), polar_max_iter=4), "uvt", uvt, (20, 820), None),
         ("mof_h2_63k NVT, Jacobi x10 (config 4 system as a trajectory)", systems.mof_h2(), "nvt", nvt, (5, 125), None),
     ]
+    if "--only-tolerance" in sys.argv:  # SURVEY 8d M4 in tolerance mode (the reference's production setting) as a trajectory
+        tol = systems.mof_h2()
+        tol.params.polar_max_iter, tol.params.polar_precision = 0, 1e-5
+        cases = [("mof_h2_63k NVT, Jacobi to polar_precision 1e-5 (config 4, tolerance mode)", tol, "nvt", nvt, (5, 65), None)]
     if quick:
         cases = cases[:1]
     if "--only-socmof" in sys.argv:
@@ -97,6 +101,10 @@ def main():
             v3, err3 = steps_per_s(DROPIN, s, ens, a, b, extra, 900, {"MPMC_B200_INCREMENTAL": "1"})
             line["dropin_mc_steps_per_s_incremental"] = v3
             line["incremental_error"] = err3 or None
+        if "--warm-start" in sys.argv:  # tolerance-mode solve started from the previous step's dipoles
+            v4, err4 = steps_per_s(DROPIN, s, ens, a, b, extra, 900, {"MPMC_B200_WARM_START": "1"})
+            line["dropin_mc_steps_per_s_warm_start"] = v4
+            line["warm_start_error"] = err4 or None
         if ref is not None and os.path.exists(REFERENCE) and "--no-reference" not in sys.argv:
             rv, rerr = steps_per_s(REFERENCE, s, ens, ref[0], ref[1], extra, 600)
             line.update({"reference_mc_steps_per_s_1core": rv, "reference_error": rerr or None, "reference_steps": list(ref)})

@@ -64,7 +64,7 @@ def test_dropin_energy_matches_reference_fixture(name, tmp_path):
         gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label=name)
 
 
-@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "incremental"])
+@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "incremental", "warm_start"])
 @pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt"])
 def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     """host_path: the shim's one-pass O(N) duties over the cached pointer sequence (default; every relinking of the
@@ -78,6 +78,8 @@ def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
         env["MPMC_B200_SHIM_SLOW"] = "1"
     if host_path == "incremental":  # applies to traj_co2_nvt; the polarizable cases must not change
         env["MPMC_B200_INCREMENTAL"] = "1"
+    if host_path == "warm_start":  # opt-in warm start: never applied to these fixed-iteration runs, which must not change
+        env["MPMC_B200_WARM_START"] = "1"
     r = subprocess.run([PROGRAM, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1200, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     rows = [l for l in (tmp_path / d.get("energy_file", "small.energy.dat")).read_text().splitlines() if not l.startswith("#")]
