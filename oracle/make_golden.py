@@ -192,6 +192,9 @@ def gen_traj(name):
 TRAJ_SYNTH = {
     # LJ + Ewald, no polarization (BASELINE config 2 in small): the case the incremental path applies to
     "traj_co2_nvt": (lambda: systems.co2_fluid(125), "nvt", "preset_seeds 4242\nnumsteps 300\nmove_factor 0.05\nrot_factor 0.05"),
+    # the same with insertions / removals (N goes 125 -> 99): every change of the atom set must drop the incremental state
+    "traj_co2_uvt": (lambda: systems.co2_fluid(125), "uvt", "preset_seeds 99\nnumsteps 300\nmove_factor 0.05\nrot_factor 0.05\n"
+                                                            "pressure 200.0\ninsert_probability 0.4"),
 }
 
 
