@@ -134,7 +134,7 @@ typedef struct mpmc_b200_counters {
     double recip_atoms;       /* atoms in the structure factor */
     int n_atoms, n_polarizable;
     int kernel_launches;      /* kernels of THIS library launched by the last evaluation */
-    int reserved;
+    int incremental;          /* 1 = the last evaluation took the incremental path (mpmc_b200_set_incremental) */
     double pairs_induced_list; /* polar_ewald_full: ordered in-cutoff polarizable pairs held in the pair list (0: on the fly) */
 } mpmc_b200_counters;
 
@@ -185,7 +185,7 @@ int mpmc_b200_energy(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
  * pairs that contain a moved atom and the moved atoms' terms of S(k), and adds the change to the last result.  Applies
  * to non-polarizable runs (or rd_only) without cavity_autoreject_absolute and rd_crystal on one GPU; everything else,
  * every set_params / set_atoms, and every 256th call (MPMC_B200_INCREMENTAL_REFRESH) is a full evaluation.  Results
- * agree with the full evaluation to rounding, not bit for bit, hence opt-in.  mpmc_b200_counters.reserved is 1 when
+ * agree with the full evaluation to rounding, not bit for bit, hence opt-in.  mpmc_b200_counters.incremental is 1 when
  * the last evaluation was incremental; energies.min_intermolecular_r is then not maintained (0). */
 int mpmc_b200_set_incremental(mpmc_b200_ctx *ctx, int on);
 /* Opt-in warm start of the dipole solve (the other half of the same idea): with on != 0 -- or MPMC_B200_WARM_START=1 in

@@ -146,7 +146,7 @@ class Counters(C.Structure):
         ("n_atoms", C.c_int),
         ("n_polarizable", C.c_int),
         ("kernel_launches", C.c_int),
-        ("reserved", C.c_int),
+        ("incremental", C.c_int),
         ("pairs_induced_list", C.c_double),
     ]
 
@@ -401,7 +401,7 @@ class Engine:
         self._check(self.lib.mpmc_b200_set_warm_start(self._ctx, 1 if on else 0))
 
     def last_eval_incremental(self) -> bool:
-        return bool(self.counters().reserved)
+        return bool(self.counters().incremental)
 
     def set_shard(self, rank: int, world: int):
         self._check(self.lib.mpmc_b200_set_shard(self._ctx, rank, world))

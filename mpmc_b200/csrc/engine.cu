@@ -2207,7 +2207,7 @@ static int incremental_energy(Ctx* c, mpmc_b200_energies* out) {
     }
     out->min_intermolecular_r = 0.0;  // not maintained by the incremental path (cavity_autoreject disables it)
     c->cnt.kernel_launches = c->launches;
-    c->cnt.reserved = 1;  // the last evaluation was incremental
+    c->cnt.incremental = 1;
     c->inc_base = *out;
     c->inc_cnt = c->cnt;
     inc_clear_moved(c);
