@@ -26,6 +26,9 @@
  *                            + lj()              (src/energy/lj.c:165-276)
  *                            + coulombic()       (src/energy/coulombic.c:22-39)
  *   mpmc_b200_polar          polar() alone       (src/energy/polar.c:31-135)
+ *   mpmc_b200_set_incremental, mpmc_b200_set_warm_start
+ *                            no reference counterpart: opt-in accelerations of the same energy() (the
+ *                            reference's TODO:2; its pair_t cache src/energy/pairs.c:243-250 is the idea)
  *   mpmc_b200_get_atom_arrays  the per-atom fields polar() writes back:
  *                            mu, ef_static, ef_induced, ef_induced_change,
  *                            dipole_rrms (structs.h:47-49), rank_metric
