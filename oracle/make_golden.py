@@ -188,6 +188,81 @@ def gen_traj(name):
     print(f"{name}: {len(en)} energy rows")
 
 
+# BASELINE config 3: the shipped PCN-61 + H2 system (sample_configs_gpu/3_PCN61: 6,048 frozen framework atoms + 3,027
+# five-site H2 = 21,183 atoms, options of iter.inp).  The reference needs ~80 GB for it (pair lists + A matrix), so:
+#   ref_pcn61_h2_500   the framework + the first 500 H2 (8,548 atoms) through the UNMODIFIED reference;
+#   oracle_pcn61_full  the whole file, parsed here (parser checked against the reference's own parse of the part),
+#                      options exactly as the reference parsed iter.inp, expected values from the ORACLE -- the one
+#                      fixture not generated by the reference (its name says so; tests treat it as oracle-pinned).
+PCN61 = "sample_configs_gpu/3_PCN61"
+
+
+def parse_pqr(path):
+    """Columns of read_molecules() (reference src/io/read_pqr.c:212-218): ATOM id type moltype F|M molid x y z mass q alpha
+    eps sig.  Molecules are runs of equal molid, in file order (list order); molecule mass = sum of its atoms' masses."""
+    rows = [l.split() for l in open(path) if l.startswith("ATOM")]
+    n = len(rows)
+    pos = np.array([[float(t[6]), float(t[7]), float(t[8])] for t in rows])
+    mass = np.array([float(t[9]) for t in rows])
+    q = np.array([float(t[10]) for t in rows]) * systems.E2REDUCED
+    alpha = np.array([float(t[11]) for t in rows])
+    eps = np.array([float(t[12]) for t in rows])
+    sig = np.array([float(t[13]) for t in rows])
+    frozen = np.array([1 if t[4] == "F" else 0 for t in rows], dtype=np.int32)
+    molid = np.array([int(t[5]) for t in rows])
+    mol = np.zeros(n, dtype=np.int32)
+    mol[1:] = np.cumsum(molid[1:] != molid[:-1])
+    mol_mass = np.zeros(n)
+    for m in range(int(mol[-1]) + 1):
+        sel = mol == m
+        mm = 0.0
+        for v in mass[sel]:  # the reference adds the atoms' masses in list order
+            mm += v
+        mol_mass[sel] = mm
+    return pos, q, alpha, eps, sig, mol_mass, mol, frozen
+
+
+def gen_pcn61(want):
+    from mpmc_b200.api import System
+
+    names = ("ref_pcn61_h2_500", "oracle_pcn61_full")
+    if want and not (set(names) & want):
+        return
+    src = os.path.join(REF, PCN61)
+    lines = [l for l in open(os.path.join(src, "input.pdb")).read().splitlines() if l.startswith("ATOM")]
+    keep, mols = [], []
+    for l in lines:
+        t = l.split()
+        if t[4] != "F":
+            if t[5] not in mols:
+                if len(mols) >= 500:
+                    continue
+                mols.append(t[5])
+        keep.append(l)
+    with tempfile.TemporaryDirectory() as td:
+        with open(os.path.join(td, "input.pdb"), "w") as f:
+            f.write("\n".join(keep) + "\nEND\n")
+        shutil.copy(os.path.join(src, "iter.inp"), td)
+        part, exp, _ = oracle.run_reference(os.path.join(td, "iter.inp"))
+        mine = parse_pqr(os.path.join(td, "input.pdb"))
+    for a, b in zip(mine, (part.pos, part.charge, part.polarizability, part.epsilon, part.sigma, part.mol_mass, part.mol_id,
+                           part.frozen)):
+        assert np.array_equal(np.asarray(a), np.asarray(b)), "parse_pqr disagrees with the reference's parser"
+    if not want or "ref_pcn61_h2_500" in want:
+        save("ref_pcn61_h2_500", part, exp, {"source": f"{PCN61}/iter.inp", "extra": "framework + the first 500 H2 of input.pdb"})
+        print(f"ref_pcn61_h2_500: n={part.n} total={exp['total']!r} polar={exp['polar']!r}")
+    if not want or "oracle_pcn61_full" in want:
+        pos, q, alpha, eps, sig, mm, mol, frozen = parse_pqr(os.path.join(src, "input.pdb"))
+        full = System(part.params, pos, q, alpha, eps, sig, mm, mol, frozen, "oracle_pcn61_full")
+        e, _, arr = oracle.energy(full, nthreads=0)
+        expf = e.to_dict()
+        expf.update({k: arr[k] for k in ("mu", "ef_static", "ef_induced", "ef_induced_change", "dipole_rrms", "rank_metric")})
+        expf["polar_ewald_full"] = 0
+        save("oracle_pcn61_full", full, expf, {"source": f"{PCN61}/input.pdb + iter.inp", "pinned_by": "oracle (oracle/mpmc_oracle.c); "
+                                              "the reference needs ~80 GB for this system"})
+        print(f"oracle_pcn61_full: n={full.n} total={expf['total']!r} polar={expf['polar']!r} iters={expf['polar_iterations']}")
+
+
 # fixed-seed trajectories of synthetic systems: name: (builder, ensemble, extra keywords)
 TRAJ_SYNTH = {
     # LJ + Ewald, no polarization (BASELINE config 2 in small): the case the incremental path (SURVEY 8f f2) applies to
@@ -237,6 +312,7 @@ def main():
             print(f"{name}: n={sr.n} total={e['total']!r} polar={e['polar']!r} iters={e['polar_iterations']}")
         except Exception as ex:  # noqa: BLE001
             print(f"{name}: FAILED {str(ex)[-600:]}")
+    gen_pcn61(want)
     for name in TRAJ:
         if want and name not in want:
             continue

@@ -14,6 +14,8 @@ CASES = gu.case_names()
 
 @pytest.mark.parametrize("name", CASES)
 def test_cuda_matches_reference_fixture(engine, name):
+    """Every fixture of tests/golden: generated from the unmodified reference, except oracle_pcn61_full (BASELINE config 3
+    at full size, 21,183 atoms: the reference needs ~80 GB), whose expected values come from the oracle."""
     s, exp = gu.load(name)
     engine.set_system(s)
     got = engine.energy()

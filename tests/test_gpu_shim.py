@@ -29,7 +29,7 @@ SINGLE_POINT = ["ref_small", "ref_socmof", "ref_socmof_production", "mixed_defau
                 "mixed_autoreject_fires", "mixed_nopolar_kmax5", "mixed_rd_only", "co2_fluid_375", "h2_fluid_500",
                 "ref_test_lenard_jones", "ref_test_coulombic", "mixed_ewald_full", "mixed_ewald_full_precision_palmo_rrms",
                 "mixed_tri_ewald_full", "mixed_es_wolf", "mixed_tri_es_wolf_nopolar",
-                "mixed_rd_crystal2", "mixed_tri_rd_crystal2_fh2"]
+                "mixed_rd_crystal2", "mixed_tri_rd_crystal2_fh2", "ref_pcn61_h2_500"]
 
 
 def _need(path):

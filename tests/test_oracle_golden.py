@@ -16,7 +16,11 @@ def test_fixtures_present():
         assert must in CASES
 
 
-@pytest.mark.parametrize("name", [c for c in CASES if not c.startswith("ref_socmof")])
+BIG = ("ref_socmof", "ref_pcn61")  # checked once, on all threads
+ORACLE_MADE = [c for c in CASES if c.startswith("oracle_")]  # expected values from the oracle itself: nothing to pin here
+
+
+@pytest.mark.parametrize("name", [c for c in CASES if not c.startswith(BIG) and c not in ORACLE_MADE])
 @pytest.mark.parametrize("nthreads", [1, 4])
 def test_oracle_matches_reference(name, nthreads):
     s, exp = gu.load(name)
@@ -26,12 +30,35 @@ def test_oracle_matches_reference(name, nthreads):
         gu.assert_atom_arrays(arr, exp, s, rtol=1e-12, label=name)
 
 
-@pytest.mark.parametrize("name", ["ref_socmof", "ref_socmof_production"])
+@pytest.mark.parametrize("name", ["ref_socmof", "ref_socmof_production", "ref_pcn61_h2_500"])
 def test_oracle_matches_reference_socmof(name):
     s, exp = gu.load(name)
     e, c, arr = oracle.energy(s, nthreads=0)
-    gu.assert_energies(e.to_dict(), exp, rtol=1e-12, label=name)
+    # ref_pcn61_h2_500 (8,548 atoms): lj() adds 3.6e7 pair terms AND 3.6e7 tiny per-pair LRC terms into ONE running sum
+    # (lj.c:256); that sum's own rounding is ~2e-11 of rd here (measured: every other quantity -- Ewald pieces, U_pol, all
+    # dipoles and fields -- is bit-identical, rd differs by 2.4e-11 relative whatever the thread count).  The oracle keeps
+    # per-row sums, so rd is held to north_star's 1e-10 for this fixture and everything else to 1e-12.
+    big = name.startswith("ref_pcn61")
+    gu.assert_energies(e.to_dict(), exp, rtol=1e-10 if big else 1e-12, label=name)
+    if big:
+        for k in ("es_real", "es_recip", "es_self", "polar"):
+            assert abs(getattr(e, k) - exp[k]) <= 1e-12 * abs(exp[k]), k
     gu.assert_atom_arrays(arr, exp, s, rtol=1e-12, label=name)
+
+
+def test_oracle_made_fixture_is_tied_to_the_reference_parse():
+    """oracle_pcn61_full (BASELINE config 3: the whole shipped PCN-61 + H2 file, 21,183 atoms -- the reference needs ~80 GB for
+    it) carries oracle-generated expected values.  Its INPUTS are tied to the reference: same options as the reference parsed
+    from iter.inp, and its first 8,548 atoms are, bit for bit, the atoms the reference parsed for ref_pcn61_h2_500."""
+    assert ORACLE_MADE == ["oracle_pcn61_full"]
+    full, exp = gu.load("oracle_pcn61_full")
+    part, _ = gu.load("ref_pcn61_h2_500")
+    assert full.n == 21183 and part.n == 8548
+    assert full.params.to_dict() == part.params.to_dict()
+    n = part.n
+    for k in ("pos", "charge", "polarizability", "epsilon", "sigma", "mol_mass", "mol_id", "frozen"):
+        assert np.array_equal(getattr(full, k)[:n], getattr(part, k)), k
+    assert int(exp["polar_iterations"]) == 4 and exp["total"] < 0
 
 
 def test_reference_published_goldens():
