@@ -67,3 +67,27 @@ def assert_atom_arrays(got: dict, exp: dict, s: System, rtol=1e-10, label=""):
     err = np.abs(got["dipole_rrms"] - exp["dipole_rrms"]).max()
     assert err <= 1e-8 * max(1.0, np.abs(exp["dipole_rrms"]).max()), f"{label} dipole_rrms {err:.3e}"
     assert np.array_equal(got["rank_metric"], exp["rank_metric"]), f"{label} rank_metric"
+
+
+def run_and_check_trajectory(program, name, tmp_path, env=None):
+    """Runs an MPMC-compatible program on the input of the fixed-seed trajectory fixture `name` (tests/golden/traj_*.json,
+    generated with the unmodified reference) and compares every energy_output row -- i.e. the accept / reject sequence --
+    and the final configuration with the reference's."""
+    import subprocess
+
+    d = json.load(open(os.path.join(GOLD, name + ".json")))
+    (tmp_path / d["pqr_name"]).write_text(d["pqr"])
+    (tmp_path / "input").write_text(d["input"])
+    r = subprocess.run([program, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1200,
+                       env=dict(os.environ, **(env or {})))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    rows = [l for l in (tmp_path / d.get("energy_file", "small.energy.dat")).read_text().splitlines() if not l.startswith("#")]
+    ref = d["energy_rows"]
+    assert len(rows) == len(ref)
+    for k, (a, b) in enumerate(zip(rows, ref)):
+        fa, fb = np.array(a.split(), dtype=float), np.array(b.split(), dtype=float)
+        # columns: step E ES RD POL VDW KE T N spin V T_core, printed with 6 decimals
+        assert fa[0] == fb[0] and fa[8] == fb[8], f"{name} row {k}: step / N differ: {a} | {b}"
+        assert np.all(np.abs(fa - fb) <= 2e-6 + 1e-9 * np.abs(fb)), f"{name} row {k}:\n{a}\n{b}"
+    final = (tmp_path / d.get("final_file", "small.final.pdb")).read_text()
+    assert final == d["final_pqr"], "final configuration differs from the reference's"

@@ -70,25 +70,11 @@ def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     """host_path: the shim's one-pass O(N) duties over the cached pointer sequence (default; every relinking of the
     lists -- uVT insert / remove, rejected moves -- must be detected) or the reference-shaped list walks."""
     _need(PROGRAM)
-    d = json.load(open(os.path.join(gu.GOLD, name + ".json")))
-    (tmp_path / d["pqr_name"]).write_text(d["pqr"])
-    (tmp_path / "input").write_text(d["input"])
-    env = dict(os.environ)
+    env = {}
     if host_path == "list_walks":
         env["MPMC_B200_SHIM_SLOW"] = "1"
     if host_path == "incremental":  # SURVEY 8f f2 (opt-in): applies to traj_co2_nvt; the polarizable cases must not change
         env["MPMC_B200_INCREMENTAL"] = "1"
     if host_path == "warm_start":  # opt-in warm start: never applied to these fixed-iteration runs, which must not change
         env["MPMC_B200_WARM_START"] = "1"
-    r = subprocess.run([PROGRAM, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1200, env=env)
-    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    rows = [l for l in (tmp_path / d.get("energy_file", "small.energy.dat")).read_text().splitlines() if not l.startswith("#")]
-    ref = d["energy_rows"]
-    assert len(rows) == len(ref)
-    for k, (a, b) in enumerate(zip(rows, ref)):
-        fa, fb = np.array(a.split(), dtype=float), np.array(b.split(), dtype=float)
-        # columns: step E ES RD POL VDW KE T N spin V T_core, printed with 6 decimals
-        assert fa[0] == fb[0] and fa[8] == fb[8], f"{name} row {k}: step / N differ: {a} | {b}"
-        assert np.all(np.abs(fa - fb) <= 2e-6 + 1e-9 * np.abs(fb)), f"{name} row {k}:\n{a}\n{b}"
-    final = (tmp_path / d.get("final_file", "small.final.pdb")).read_text()
-    assert final == d["final_pqr"], "final configuration differs from the reference's"
+    gu.run_and_check_trajectory(PROGRAM, name, tmp_path, env)
