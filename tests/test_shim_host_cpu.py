@@ -31,3 +31,44 @@ def hoststub():
 def test_shim_host_logic_reproduces_reference_trajectory(hoststub, name, host_path, tmp_path):
     env = {"MPMC_B200_SHIM_SLOW": "1"} if host_path == "list_walks" else {}
     gu.run_and_check_trajectory(hoststub, name, tmp_path, env)
+
+
+DRIVER = os.path.join(STUB_DIR, "_build", "shim_driver_hoststub")
+
+
+def _single_point_cases():
+    from tests.test_gpu_shim import SINGLE_POINT  # the same list the GPU drop-in test walks
+
+    return SINGLE_POINT
+
+
+@pytest.mark.parametrize("name", _single_point_cases())
+def test_shim_option_plumbing_single_point(hoststub, name, tmp_path):
+    """energy(system_t*) through the shim for every option family (solver switches, Wolf / Ewald fields, full-Ewald
+    polarization, mixing rules, FH, autoreject, rd_only, Wolf electrostatics, rd_crystal, the PCN-61 framework): what
+    shim_fill_params() hands over and what the epilogue and the write-back leave in system_t / atom_t must equal the
+    fixture generated from the unmodified reference -- here with the oracle behind the C ABI, on the GPU in
+    tests/test_gpu_shim.py::test_dropin_energy_matches_reference_fixture."""
+    import numpy as np
+
+    from mpmc_b200 import systems
+    from oracle import oracle  # snapshot parser
+
+    s, exp = gu.load(name)
+    first = np.r_[True, s.mol_id[1:] != s.mol_id[:-1]]
+    s.meta["atom_mass"] = np.where(first, s.mol_mass, 0.0)
+    inp = systems.write_reference_case(s, str(tmp_path))
+    r = subprocess.run([DRIVER, os.path.basename(inp)], cwd=str(tmp_path), capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "MPMC_SNAPSHOT" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    _, got, _ = oracle.parse_snapshot(r.stdout, name)
+    assert got["returned"] == got["total"] or got["total"] >= 1e40 or exp.get("total", 0) >= 1e40
+    for k in ("rd", "coulombic", "polar", "total"):
+        b = exp[k]
+        tol = 1e-10 * abs(b)
+        if k in ("coulombic", "total"):
+            tol += 1e-13 * max(abs(exp.get("es_real", 0.0)), abs(exp.get("es_self", 0.0))) + 1e-10 * (abs(exp["rd"]) + abs(exp["polar"])) * (k == "total")
+        assert abs(got[k] - b) <= tol, f"{name} {k}: shim + oracle {got[k]!r} vs reference {b!r}"
+    assert int(got["polar_iterations"]) == int(exp["polar_iterations"])
+    assert int(got["iter_success"]) == int(exp["iter_success"])
+    if s.params.polarization and not s.params.rd_only and exp["total"] < 1e40:
+        gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label=name)
