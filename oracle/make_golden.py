@@ -270,16 +270,22 @@ TRAJ_SYNTH = {
     # the same with insertions / removals (N goes 125 -> 99): every change of the atom set must drop the incremental state
     "traj_co2_uvt": (lambda: systems.co2_fluid(125), "uvt", "preset_seeds 99\nnumsteps 300\nmove_factor 0.05\nrot_factor 0.05\n"
                                                             "pressure 200.0\ninsert_probability 0.4"),
+    # volume moves (V goes 8000 -> 9006 A^3): the cutoff, alpha, k-vectors and LRC follow the cell; the input leaves the
+    # cutoff to the reference's pbc() so that it is recomputed with every volume change
+    "traj_co2_npt": (lambda: systems.co2_fluid(125), "npt", "preset_seeds 31337\nnumsteps 200\nmove_factor 0.05\nrot_factor 0.05\n"
+                                                            "pressure 100.0\nvolume_probability 0.2\nvolume_change_factor 0.02",
+                     dict(explicit_cutoff=False)),
 }
 
 
 def gen_traj_synth(name):
-    build, ensemble, extra = TRAJ_SYNTH[name]
+    build, ensemble, extra = TRAJ_SYNTH[name][:3]
+    kw = TRAJ_SYNTH[name][3] if len(TRAJ_SYNTH[name]) > 3 else {}
     s = build()
     first = np.r_[True, s.mol_id[1:] != s.mol_id[:-1]]
     s.meta["atom_mass"] = np.where(first, s.mol_mass, 0.0)  # update_com() then recovers molecule_t.mass
     with tempfile.TemporaryDirectory() as td:
-        inp = systems.write_reference_case(s, td, ensemble=ensemble, extra=extra)
+        inp = systems.write_reference_case(s, td, ensemble=ensemble, extra=extra, **kw)
         r = subprocess.run([oracle.REF_BINARY, "input"], cwd=td, capture_output=True, text=True, timeout=3600)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         en = [l for l in open(os.path.join(td, "energy.dat")).read().splitlines() if not l.startswith("#")]
