@@ -432,17 +432,39 @@ static void shim_cache_topology(system_t *system) {
     c_valid = (na == system->natoms);
 }
 
+/* A rejected displacement links the backup copy where the altered molecule was (restore(): mc_moves.c:789-797): one node of
+ * the sequence is new, its neighbours are not.  If `fresh` sits in slot k like that -- same successor, same atom count --
+ * the cache, molecule_array and atom_array (rebuild_arrays(): pairs.c:12-38) are patched in place; 0 when it does not fit
+ * (an insertion, a removal, anything else: the caller falls back to the full walks). */
+static int shim_repair_slot(system_t *system, int k, molecule_t *fresh) {
+    const int b = c_first[k], e = c_first[k + 1];
+    atom_t *a;
+    int i;
+    if (!fresh || fresh->next != (k + 1 < c_nmol ? c_mol[k + 1] : NULL)) return 0;
+    for (a = fresh->atoms, i = b; a && i < e; a = a->next) i++;
+    if (a || i != e) return 0;
+    c_mol[k] = fresh;
+    system->molecule_array[k] = fresh;
+    for (a = fresh->atoms, i = b; a; a = a->next, i++) {
+        c_atom[i] = a;
+        system->atom_array[i] = a;
+    }
+    return 1;
+}
+
 /* returns the atom count when the cached sequence still is the list (everything done), -1 otherwise */
 static int shim_fast_pass(system_t *system, int es_on) {
     const pbc_t *pbc = system->pbc;
     const double self_c = system->ewald_alpha / sqrt(M_PI);
     int k, i, p, q;
-    if (!c_valid || c_nmol <= 0 || system->molecules != c_mol[0] || !system->atom_array || !system->molecule_array) return -1;
+    if (!c_valid || c_nmol <= 0 || !system->atom_array || !system->molecule_array) return -1;
+    if (system->molecules != c_mol[0] && !shim_repair_slot(system, 0, system->molecules)) return -1;
     shim_reserve(c_natom);
     for (k = 0; k < c_nmol; k++) {
         molecule_t *m = c_mol[k];
         const int b = c_first[k], e = c_first[k + 1];
         double com[3] = {0, 0, 0}, mass = 0, dimg[3] = {0, 0, 0}, d[3];
+        if (k + 1 < c_nmol && m->next != c_mol[k + 1] && !shim_repair_slot(system, k + 1, m->next)) return -1;
         if (m->next != (k + 1 < c_nmol ? c_mol[k + 1] : NULL) || m->atoms != (e > b ? c_atom[b] : NULL)) return -1;
         for (i = b; i < e; i++) {
             const atom_t *a = c_atom[i];

@@ -74,3 +74,23 @@ def test_shim_option_plumbing_single_point(hoststub, name, tmp_path):
     assert int(got["iter_success"]) == int(exp["iter_success"])
     if s.params.polarization and not s.params.rd_only and exp["total"] < 1e40:
         gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label=name)
+
+
+def test_cached_sequence_survives_rejected_moves(hoststub, tmp_path):
+    """A rejected displacement links the backup copy of the molecule where the altered one was (restore(), mc_moves.c:789-797):
+    the one-pass host path patches that slot of its cached pointer sequence (and molecule_array / atom_array) instead of
+    falling back to the full list walks -- every call after the first stays on the fast pass in NVT, and the trajectory is
+    still the reference's (checked above)."""
+    import json
+    import re
+
+    d = json.load(open(os.path.join(gu.GOLD, "traj_co2_nvt.json")))
+    (tmp_path / d["pqr_name"]).write_text(d["pqr"])
+    (tmp_path / "input").write_text(d["input"])
+    r = subprocess.run([hoststub, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=900,
+                       env=dict(os.environ, MPMC_B200_SHIM_TIMING="1"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    m = re.search(r"(\d+) energy\(\) calls \((\d+) on the cached-sequence pass\)", r.stderr)
+    assert m, r.stderr[-2000:]
+    calls, fast = int(m.group(1)), int(m.group(2))
+    assert calls == 301 and fast >= calls - 1, f"{fast} of {calls} calls on the cached-sequence pass"
