@@ -444,10 +444,10 @@ static int shim_repair_slot(system_t *system, int k, molecule_t *fresh) {
     for (a = fresh->atoms, i = b; a && i < e; a = a->next) i++;
     if (a || i != e) return 0;
     c_mol[k] = fresh;
-    system->molecule_array[k] = fresh;
     for (a = fresh->atoms, i = b; a; a = a->next, i++) {
         c_atom[i] = a;
-        system->atom_array[i] = a;
+        system->atom_array[i] = a;         /* both arrays are per ATOM: molecule_array[i] is the molecule of atom i */
+        system->molecule_array[i] = fresh; /* (pairs.c:28-34) */
     }
     return 1;
 }
@@ -594,6 +594,22 @@ static void shim_prepare(system_t *system, int es_on) {
     if (t_on) t0 = shim_now();
     n = fast ? shim_fast_pass(system, es_on) : -1;
     if (n >= 0) t_fast++;
+    if (n >= 0) { /* MPMC_B200_SHIM_CHECK=1 (tests): the one-pass result against a real walk of the lists */
+        static int check = -1;
+        if (check < 0) check = getenv("MPMC_B200_SHIM_CHECK") ? 1 : 0;
+        if (check) {
+            molecule_t *m;
+            atom_t *a;
+            int i = 0, k = 0;
+            for (m = system->molecules; m; m = m->next, k++) {
+                if (k >= c_nmol || c_mol[k] != m || c_first[k] != i) shim_die("SHIM_CHECK: molecule sequence");
+                for (a = m->atoms; a; a = a->next, i++)
+                    if (i >= n || c_atom[i] != a || system->atom_array[i] != a || system->molecule_array[i] != m)
+                        shim_die("SHIM_CHECK: atom sequence / atom_array / molecule_array");
+            }
+            if (i != n || k != c_nmol || system->natoms != n) shim_die("SHIM_CHECK: counts");
+        }
+    }
     if (n < 0) {
         system->natoms = countNatoms(system);
         pairs(system);

@@ -31,7 +31,9 @@ def hoststub():
 def test_shim_host_logic_reproduces_reference_trajectory(hoststub, name, host_path, tmp_path):
     """traj_co2_npt (volume moves: every accepted or reverted change of the cell must reach set_params) is checked here
     only; the GPU run of it is left to the next round."""
-    env = {"MPMC_B200_SHIM_SLOW": "1"} if host_path == "list_walks" else {}
+    # MPMC_B200_SHIM_CHECK=1: after every one-pass call the shim compares its cached sequence, atom_array and molecule_array
+    # with a real walk of the lists and dies on any difference
+    env = {"MPMC_B200_SHIM_SLOW": "1"} if host_path == "list_walks" else {"MPMC_B200_SHIM_CHECK": "1"}
     gu.run_and_check_trajectory(hoststub, name, tmp_path, env)
 
 
