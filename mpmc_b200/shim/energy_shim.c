@@ -432,24 +432,70 @@ static void shim_cache_topology(system_t *system) {
     c_valid = (na == system->natoms);
 }
 
-/* A rejected displacement links the backup copy where the altered molecule was (restore(): mc_moves.c:789-797): one node of
- * the sequence is new, its neighbours are not.  If `fresh` sits in slot k like that -- same successor, same atom count --
- * the cache, molecule_array and atom_array (rebuild_arrays(): pairs.c:12-38) are patched in place; 0 when it does not fit
- * (an insertion, a removal, anything else: the caller falls back to the full walks). */
-static int shim_repair_slot(system_t *system, int k, molecule_t *fresh) {
-    const int b = c_first[k], e = c_first[k + 1];
+/* Keeping the cached sequence across the MC driver's relinking (mc_moves.c:567-741 make_move(), :744-804 restore()).  At slot k
+ * the real list holds `fresh` where the cache expects c_mol[k] (NULL past the end).  Three single-node changes are recognised
+ * and the cache is edited in place; anything else returns 0 and the caller falls back to the full walks:
+ *   removal      fresh is the cached successor of slot k               (uVT remove; a rejected insertion)
+ *   insertion    fresh->next is the node the cache has in slot k       (uVT insert; a rejected removal relinks the backup)
+ *   replacement  fresh->next is the cached successor, same atom count  (a rejected displacement relinks the backup copy)
+ * Several of them in one MC step (restore + new move) are met one after the other as the pass walks the list.  Everything
+ * compared is a node reached from system->molecules through real `next` links, so a match always means "this node sits here".
+ * *resized is set when the atom count changed (atom_array / molecule_array are then rebuilt at the end of the pass). */
+static molecule_t *shim_cached(int k) { return k < c_nmol ? c_mol[k] : NULL; }
+
+static int shim_resync(system_t *system, int k, molecule_t *fresh, int *resized) {
     atom_t *a;
-    int i;
-    if (!fresh || fresh->next != (k + 1 < c_nmol ? c_mol[k + 1] : NULL)) return 0;
-    for (a = fresh->atoms, i = b; a && i < e; a = a->next) i++;
-    if (a || i != e) return 0;
-    c_mol[k] = fresh;
-    for (a = fresh->atoms, i = b; a; a = a->next, i++) {
-        c_atom[i] = a;
-        system->atom_array[i] = a;         /* both arrays are per ATOM: molecule_array[i] is the molecule of atom i */
-        system->molecule_array[i] = fresh; /* (pairs.c:28-34) */
+    int i, cnt;
+    if (k < c_nmol && fresh == shim_cached(k + 1)) { /* removal of slot k */
+        const int b = c_first[k], e = c_first[k + 1];
+        cnt = e - b;
+        memmove(c_atom + b, c_atom + e, sizeof(atom_t *) * (size_t)(c_natom - e));
+        memmove(c_mol + k, c_mol + k + 1, sizeof(molecule_t *) * (size_t)(c_nmol - k - 1));
+        for (i = k + 1; i <= c_nmol; i++) c_first[i - 1] = c_first[i] - cnt;
+        c_nmol--;
+        c_natom -= cnt;
+        *resized = 1;
+        return 1;
     }
-    return 1;
+    if (!fresh) return 0;
+    if (fresh->next == shim_cached(k)) { /* insertion before slot k */
+        const int b = c_first[k];
+        for (a = fresh->atoms, cnt = 0; a; a = a->next) cnt++;
+        if (c_nmol + 2 > c_molcap) {
+            c_molcap = c_nmol + c_nmol / 4 + 64;
+            c_mol = (molecule_t **)xrealloc(c_mol, sizeof(molecule_t *) * c_molcap);
+            c_first = (int *)xrealloc(c_first, sizeof(int) * c_molcap);
+        }
+        if (c_natom + cnt > c_atomcap) {
+            c_atomcap = c_natom + cnt + c_natom / 4 + 64;
+            c_atom = (atom_t **)xrealloc(c_atom, sizeof(atom_t *) * c_atomcap);
+        }
+        memmove(c_atom + b + cnt, c_atom + b, sizeof(atom_t *) * (size_t)(c_natom - b));
+        memmove(c_mol + k + 1, c_mol + k, sizeof(molecule_t *) * (size_t)(c_nmol - k));
+        for (i = c_nmol; i >= k; i--) c_first[i + 1] = c_first[i] + cnt;
+        c_mol[k] = fresh;
+        for (a = fresh->atoms, i = b; a; a = a->next, i++) c_atom[i] = a;
+        c_nmol++;
+        c_natom += cnt;
+        shim_reserve(c_natom);
+        *resized = 1;
+        return 1;
+    }
+    if (k < c_nmol && fresh->next == shim_cached(k + 1)) { /* replacement of slot k by a node with as many atoms */
+        const int b = c_first[k], e = c_first[k + 1];
+        for (a = fresh->atoms, i = b; a && i < e; a = a->next) i++;
+        if (a || i != e) return 0;
+        c_mol[k] = fresh;
+        for (a = fresh->atoms, i = b; a; a = a->next, i++) {
+            c_atom[i] = a;
+            if (!*resized) {                       /* both arrays are per ATOM: molecule_array[i] is the molecule of atom i */
+                system->atom_array[i] = a;         /* (pairs.c:28-34); after a resize they are rebuilt as a whole */
+                system->molecule_array[i] = fresh;
+            }
+        }
+        return 1;
+    }
+    return 0;
 }
 
 /* returns the atom count when the cached sequence still is the list (everything done), -1 otherwise */
@@ -457,15 +503,22 @@ static int shim_fast_pass(system_t *system, int es_on) {
     const pbc_t *pbc = system->pbc;
     const double self_c = system->ewald_alpha / sqrt(M_PI);
     int k, i, p, q;
+    molecule_t *real = system->molecules;
+    int resized = 0;
     if (!c_valid || c_nmol <= 0 || !system->atom_array || !system->molecule_array) return -1;
-    if (system->molecules != c_mol[0] && !shim_repair_slot(system, 0, system->molecules)) return -1;
     shim_reserve(c_natom);
-    for (k = 0; k < c_nmol; k++) {
-        molecule_t *m = c_mol[k];
-        const int b = c_first[k], e = c_first[k + 1];
+    for (k = 0;; k++) {
+        molecule_t *m;
+        int b, e, tries = 0;
         double com[3] = {0, 0, 0}, mass = 0, dimg[3] = {0, 0, 0}, d[3];
-        if (k + 1 < c_nmol && m->next != c_mol[k + 1] && !shim_repair_slot(system, k + 1, m->next)) return -1;
-        if (m->next != (k + 1 < c_nmol ? c_mol[k + 1] : NULL) || m->atoms != (e > b ? c_atom[b] : NULL)) return -1;
+        while (real != shim_cached(k)) /* the MC driver relinked something here: edit the cache or give up */
+            if (++tries > 4 || !shim_resync(system, k, real, &resized)) return -1;
+        if (k >= c_nmol) break; /* real == NULL: the end of both */
+        m = c_mol[k];
+        b = c_first[k];
+        e = c_first[k + 1];
+        real = m->next;
+        if (m->atoms != (e > b ? c_atom[b] : NULL)) return -1;
         for (i = b; i < e; i++) {
             const atom_t *a = c_atom[i];
             if (a->next != (i + 1 < e ? c_atom[i + 1] : NULL)) return -1;
@@ -502,6 +555,18 @@ static int shim_fast_pass(system_t *system, int es_on) {
             n_frozen[i] = a->frozen;
             if (es_on && !a->frozen) a->es_self_point_energy = self_c * a->charge * a->charge; /* coulombic.c:103-108 */
         }
+    }
+    if (resized) { /* rebuild_arrays(): pairs.c:12-38, from the sequence just verified */
+        free(system->atom_array);
+        free(system->molecule_array);
+        system->atom_array = (atom_t **)malloc((c_natom ? c_natom : 1) * sizeof(atom_t *));
+        system->molecule_array = (molecule_t **)malloc((c_natom ? c_natom : 1) * sizeof(molecule_t *));
+        if (!system->atom_array || !system->molecule_array) shim_die("out of memory");
+        for (k = 0; k < c_nmol; k++)
+            for (i = c_first[k]; i < c_first[k + 1]; i++) {
+                system->atom_array[i] = c_atom[i];
+                system->molecule_array[i] = c_mol[k];
+            }
     }
     system->natoms = c_natom;
     return c_natom;
