@@ -7,12 +7,19 @@ reference: src/mc/mc.c:302 calls energy() once per step and energy() recomputes 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
 
 Own arm (default): the CUDA engine behind the C ABI (mpmc_b200/lib/libmpmc_b200.so).
-  value  : Gpair-interactions/s, device-timed (CUDA events), system resident in HBM
-  e2e    : same metric through the reference-facing call with HOST buffers: every step copies all
-           atom positions host->device, evaluates, and reads energies + per-atom mu / fields back
-  roofline: the dominant kernel (K4 dipole-tensor contraction), algorithmic fp64 flops per launch
-           (126 flop per ordered polarizable pair) / mean launch time (CUDA events on the
-           launching stream) against the fp64 FMA peak measured on this GPU in the same run
+  value  : Gpair-interactions/s, device-timed (CUDA events), system resident in HBM; one rank per GPU under torchrun,
+           every exchange of a sharded evaluation done by the engine's kernels over NVLink peer memory
+  e2e    : the same metric through the DROP-IN boundary: energy(system_t*) of the reference's own data model
+           (mpmc_b200/shim: list pass, upload of what moved, evaluation on N GPUs from one process, write-back of
+           mu / fields into every atom_t), timed by the same loop that times the reference in the CPU arm
+  e2e_abi: the same through the C ABI with host buffers (ctypes), every rank copying positions in and arrays out
+  config.parity : this run's energies and per-atom arrays against the pin of the workload (tests/golden/pin_*.npz:
+           the unmodified reference where it fits, else the reference-pinned oracle), at every N
+  config.mc_steps_per_s_dropin : MC steps/s of a short `mpmc_b200 <input>` NVT run (BASELINE's first metric)
+  roofline: the dominant kernel (K4 symmetric dipole-tensor contraction): EXECUTED fp64 flops per launch (ncu SASS
+           counts dadd + dmul + 2 dfma, profiles/k4_executed.json) / mean launch time (CUDA events on the launching
+           stream) against the fp64 FMA peak of 148 SMs at the clock sampled under load; the SURVEY 8d algorithmic
+           figure is reported beside it as `algorithmic_tflops`
   cpu_baseline: the unmodified reference (oracle/_ref) or the oracle port, on the host cores
 Reference arm (--impl reference): the reference's own CPU energy() on the host cores.
 
@@ -279,11 +286,80 @@ def reference_arm(args):
 # ------------------------------------------------------------------------------------------------
 # own arm
 # ------------------------------------------------------------------------------------------------
+SHIM_BUILD = os.path.join(ROOT, "mpmc_b200", "shim", "_build")
+SHIM_DRIVER = os.path.join(SHIM_BUILD, "shim_driver")   # energy(system_t*) timing loop over the drop-in library
+DROPIN = os.path.join(SHIM_BUILD, "mpmc_b200")          # the drop-in program: the reference's MC driver over the CUDA engine
+
+
+def dropin_env(n_gpus: int) -> dict:
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    if n_gpus > 1:
+        env["MPMC_B200_DEVICES"] = ",".join(str(k) for k in range(n_gpus))  # one process, n GPUs: mpmc_b200_create_group
+    return env
+
+
+def dropin_energy_seconds(s, n_gpus: int, steps: int, warmup: int):
+    """Seconds per energy(system_t*) call through the drop-in boundary: shim_driver (oracle/ref_driver.c's timing loop
+    linked against the drop-in library -- the same loop that times the reference in the CPU arm) parses the system,
+    then displaces one molecule and calls energy() `steps` times after `warmup` untimed calls.  Each call walks the
+    reference's molecule / atom lists, uploads what changed, evaluates on `n_gpus` GPUs and writes mu / E_static /
+    E_induced back into every atom_t.  Returns (seconds per call, error text)."""
+    if not os.path.exists(SHIM_DRIVER):
+        return None, f"{SHIM_DRIVER} missing (built where /root/reference is present)"
+    from mpmc_b200 import systems
+
+    with tempfile.TemporaryDirectory(prefix="mpmc_dropin_") as td:
+        inp = systems.write_reference_case(s, td)
+        r = subprocess.run([SHIM_DRIVER, os.path.basename(inp), str(max(steps, 2)), str(max(warmup, 1)), "q"], cwd=td,
+                           capture_output=True, text=True, timeout=1200, env=dropin_env(n_gpus))
+    t = [l for l in r.stdout.splitlines() if l.startswith("timing seconds_per_energy")]
+    if r.returncode != 0 or not t:
+        return None, (r.stdout[-400:] + r.stderr[-400:]).replace("\n", " | ")
+    return float(t[-1].split()[2]), ""
+
+
+def dropin_mc_steps_per_s(s, n_gpus: int, short: int, long_: int):
+    """MC steps/s of `mpmc_b200 <input>` (NVT, fixed seed): (long - short) steps / (wall_long - wall_short), so that
+    parsing, the initial energy() and CUDA start-up cancel."""
+    if not os.path.exists(DROPIN):
+        return None
+    from mpmc_b200 import systems
+
+    def wall(steps):
+        with tempfile.TemporaryDirectory(prefix="mpmc_mc_") as td:
+            ex = f"numsteps {steps}\ncorrtime {steps}\npreset_seeds 12345\nmove_factor 0.01\nrot_factor 0.01\n"
+            systems.write_reference_case(s, td, ensemble="nvt", extra=ex)
+            t0 = time.perf_counter()
+            r = subprocess.run([DROPIN, "input"], cwd=td, capture_output=True, text=True, timeout=1200, env=dropin_env(n_gpus))
+            return (time.perf_counter() - t0) if r.returncode == 0 else None
+
+    a, b = wall(short), wall(long_)
+    if a is None or b is None or b <= a:
+        return None
+    return (long_ - short) / (b - a)
+
+
+def executed_flops(workload: str, n_gpus: int):
+    """fp64 flops ONE launch of the dominant kernel executes on one rank: dadd + dmul + 2 dfma thread-level SASS counts
+    of an ncu capture of this workload (profiles/k4_executed.json, written by profiles/capture_k4_executed.py from the
+    raw CSV committed beside it).  The work items of the symmetric contraction are dealt out evenly, so a rank of an
+    n-GPU run executes 1/n of the single-GPU launch."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "k4_executed.json")))[workload]
+    except Exception:
+        return None
+    rec = dict(rec)
+    rec["flops_per_rank_launch"] = (rec["dadd"] + rec["dmul"] + 2.0 * rec["dfma"]) / max(n_gpus, 1)
+    return rec
+
+
 def own_arm(args):
     import torch
     import torch.distributed as dist
 
-    from mpmc_b200 import Engine
+    from mpmc_b200 import Engine, pins
     from mpmc_b200.sharded import ShardedEngine
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -300,11 +376,13 @@ def own_arm(args):
 
     s = build_workload(args.workload)
     fh = bool(s.params.feynman_hibbs)
+    polar = bool(s.params.polarization and not s.params.rd_only)
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     eng = Engine(local, stream=stream.cuda_stream)
     sh = ShardedEngine(eng, rank, world, stream=stream)
     sh.set_system(s)
+    eng_peer = [bool(world > 1 and eng.peer_active())]
 
     def barrier():
         if world > 1:
@@ -314,10 +392,9 @@ def own_arm(args):
     flush = torch.empty(256 * 1024 * 1024 // 8, dtype=torch.float64, device="cuda")  # > 126 MB L2
 
     # ---- warm-up (untimed) ----
-    e0 = None
     for _ in range(max(args.warmup, 0)):
-        e0 = sh.energy()
-    peak_tf = eng.measure_fp64_peak()  # DFMA-chain probe on this GPU, same run (also warms the clocks)
+        sh.energy()
+    peak_probe = eng.measure_fp64_peak()  # DFMA-chain probe on this GPU, same run (also warms the clocks)
 
     # ---- value: device-timed, system resident in HBM ----
     sampler = ClockSampler(local)
@@ -328,6 +405,7 @@ def own_arm(args):
     launches = 0
     contract_ms = []
     phases = {}
+    e = None
     for k in range(args.steps):
         flush.fill_(float(k))  # L2 flush between timed iterations (untimed)
         ev[k][0].record(stream)
@@ -347,29 +425,42 @@ def own_arm(args):
     cnt = sh.counters_total()
     pairs = pair_interactions(cnt)
     value = pairs / (ms_per_step * 1e-3) / 1e9
+    energy_timed = e.total
 
-    # ---- e2e: HOST buffers through the public call, copies inside the timed region ----
+    # ---- parity of THIS run (the resident, unperturbed system) against the pin of the workload ----
+    parity = None
+    arr = sh.atom_arrays() if polar else None  # the caller's write-back buffers, reused below
+    pin_name = pins.for_workload(args.workload)
+    if pin_name is not None and rank == 0:
+        pin = pins.load(pin_name)
+        changed = pins.check_inputs(pin, s)
+        dev = pins.deviation(pin, e.to_dict(), arr)
+        parity = {"pin": pin_name, "pinned_by": pin["meta"]["pinned_by"], "inputs_match": not changed,
+                  "max_rel_dev": dev["max"], "energies": dev["energies"], "arrays": dev["arrays"],
+                  "checksums": dev["checksums"], "iterations_equal": dev["iterations_equal"], "worst": dev["worst"],
+                  "ok": bool(not changed and dev["iterations_equal"] and dev["max"] <= 1e-10)}
+
+    # ---- the same metric through the C ABI with HOST buffers (every rank uploads the positions the caller changed and
+    # reads energies + per-atom arrays back); kept beside the drop-in figure below as `e2e_abi` ----
     n = s.n
     hpos = torch.from_numpy(s.pos.copy()).pin_memory()
     hnp = hpos.numpy()
     rng = np.random.Generator(np.random.PCG64(7))
-    h2d = n * 3 * 8
-    d2h = 32 * 8 + (4 * 3 + 2) * 8 * n if s.params.polarization else 32 * 8
     movable = np.flatnonzero(s.frozen == 0)
-    arr = sh.atom_arrays() if s.params.polarization else None  # the caller's write-back buffers, reused every step
+    sites = 5 if args.workload.startswith(("mof_h2", "h2_fluid")) else 3
     barrier()
     t_set = t_eval = t_wb = 0.0
     t0 = time.perf_counter()
     for k in range(args.steps):
-        # one MC translation of one molecule (5 sites), applied on the host copy the caller owns
-        first = int(movable[0]) + 5 * int(rng.integers(0, max(1, movable.size // 5)))
-        hnp[first:first + 5] += rng.uniform(-0.05, 0.05, size=3)
+        # one MC translation of one molecule, applied on the host copy the caller owns
+        first = int(movable[0]) + sites * int(rng.integers(0, max(1, movable.size // sites)))
+        hnp[first:first + sites] += rng.uniform(-0.05, 0.05, size=3)
         ta = time.perf_counter()
-        sh.set_positions(0, hnp)           # host -> device, all positions (the drop-in does not diff)
+        sh.set_positions(0, hnp)           # host -> device, all positions
         tb = time.perf_counter()
-        e = sh.energy()                    # device -> host: energies
+        sh.energy()                        # device -> host: energies
         tc = time.perf_counter()
-        if s.params.polarization:
+        if polar:
             arr = sh.atom_arrays(arr)      # device -> host: mu, ef_static, ef_induced, ... as polar() writes back
         td = time.perf_counter()
         t_set, t_eval, t_wb = t_set + (tb - ta), t_eval + (tc - tb), t_wb + (td - tc)
@@ -379,41 +470,70 @@ def own_arm(args):
     t = torch.tensor([sec], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = pairs / (float(t.item()) / args.steps) / 1e9
-
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
-
-    # ---- roofline of the dominant kernel (K4) ----
-    c_ms = float(np.mean([x for x in contract_ms if x > 0])) if any(x > 0 for x in contract_ms) else 0.0
+    abi_sec_per_step = float(t.item()) / args.steps
     own = sh.counters_own()
-    k4_flops = FLOP_DIPOLE * own.pairs_dipole_own  # ordered pairs this rank's launch covers
-    ach = k4_flops / (c_ms * 1e-3) / 1e12 if c_ms > 0 else 0.0
-    roofline = {"bound": "fp64", "kernel": "dipole_contract_kernel (K4)", "achieved": ach, "peak": peak_tf,
-                "unit": "TFLOP/s", "frac": (ach / peak_tf) if peak_tf > 0 else None, "traffic": None,
-                "peak_source": "DFMA-chain probe measured on this GPU in this run (MEASURED_PEAKS.json has no fp64 entry)",
-                "flops_per_launch": k4_flops, "ms_per_launch": c_ms,
-                "whole_eval_tflops": algorithmic_flops(cnt, fh) / (ms_per_step * 1e-3) / 1e12,
+    if world > 1:
+        dist.destroy_process_group()  # no NCCL kernel may sit on the other GPUs while the drop-in process uses them
+    if rank != 0:
+        eng.close()
+        return 0
+    eng.close()
+    del flush
+    torch.cuda.empty_cache()
+
+    # ---- e2e: through the drop-in boundary, energy(system_t*) of the reference's own data model ----
+    dsec, derr = dropin_energy_seconds(s, world, args.steps, args.warmup)
+    h2d = sites * 3 * 8                                     # the shim uploads the atoms that moved
+    d2h = 32 * 8 + ((4 * 3 + 2) * 8 * n if polar else 0)    # scalars + what polar() leaves in every atom_t
+    if dsec is not None:
+        e2e = {"value": pairs / dsec / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "through": "energy(system_t*) of the drop-in library (shim_driver: list pass + upload + evaluation on "
+                          f"{world} GPU(s) + write-back into atom_t), one molecule displaced per call",
+               "ms_per_call": dsec * 1e3, "calls_per_s": 1.0 / dsec}
+    else:  # never silently substitute: say that the drop-in figure is missing and why
+        e2e = {"value": None, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "error": derr}
+    e2e_abi = {"value": pairs / abi_sec_per_step / 1e9, "unit": UNIT, "h2d_bytes_per_step": n * 3 * 8, "d2h_bytes_per_step": d2h,
+               "through": "C ABI with host buffers (ctypes): set_positions(all) + energy + get_atom_arrays on every rank",
+               "calls_per_s": 1.0 / abi_sec_per_step,
+               "host_ms_per_step": {"set_positions": 1e3 * t_set / args.steps, "energy": 1e3 * t_eval / args.steps,
+                                    "write_back": 1e3 * t_wb / args.steps}}
+    mc_dropin = None
+    if not args.no_mc_dropin:
+        est = max(ms_per_step * 1e-3, 2e-3)  # size the long run for ~3 s of stepping
+        short = 5
+        mc_dropin = dropin_mc_steps_per_s(s, world, short, short + int(min(max(3.0 / est, 20), 4000)))
+
+    # ---- roofline of the dominant kernel (K4): EXECUTED fp64 flops / launch time / fp64 peak ----
+    c_ms = float(np.mean([x for x in contract_ms if x > 0])) if any(x > 0 for x in contract_ms) else 0.0
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    peak_nominal = 148 * 64 * 2 * sm_mhz * 1e6 / 1e12  # 64 fp64 FMA lanes / clk / SM at the clock sampled under load
+    k4_alg = FLOP_DIPOLE * own.pairs_dipole_own  # SURVEY 8d convention: 126 flop per ordered pair
+    ex = executed_flops(args.workload, world)
+    roofline = {"bound": "fp64", "kernel": "dipole_sym_kernel (K4)", "unit": "TFLOP/s", "peak": peak_nominal,
+                "peak_source": f"148 SM x 64 fp64 FMA lanes x 2 x {sm_mhz:.0f} MHz (clock sampled during the timed region; "
+                               "MEASURED_PEAKS.json carries no fp64 figure)",
+                "peak_dfma_probe": peak_probe, "ms_per_launch": c_ms,
+                "algorithmic_tflops": (k4_alg / (c_ms * 1e-3) / 1e12) if c_ms > 0 else None,
+                "algorithmic_note": "SURVEY 8d convention (126 flop per ORDERED pair as the reference's formula counts "
+                                    "them); the symmetric kernel does the work once per unordered pair in ~75 executed "
+                                    "flop, so this figure exceeds the hardware peak and is NOT the roofline fraction",
+                "whole_eval_algorithmic_tflops": algorithmic_flops(cnt, fh) / (ms_per_step * 1e-3) / 1e12,
                 "phase_ms": {k: float(np.mean(v)) for k, v in phases.items()}}
-    # fp64-pipe view of the same launch: K4 EXECUTES 41 (far cluster pair, no damping) .. 69 (damped) fp64
-    # instructions per unordered pair (SASS count), far fewer than the 2 x 126 algorithmic flops the
-    # reference's formula implies, which is why `frac` exceeds 1.  One fp64 instruction = 1 lane-op of the
-    # 148 SM x 64 lanes/clk pipe whose DFMA rate (2 flop) is `peak`.
-    if c_ms > 0 and peak_tf > 0:
-        unordered = 0.5 * own.pairs_dipole_own
-        lane_ops_per_s = peak_tf * 1e12 / 2.0
-        roofline["pipe_frac_bounds"] = [41.0 * unordered / (c_ms * 1e-3) / lane_ops_per_s,
-                                        69.0 * unordered / (c_ms * 1e-3) / lane_ops_per_s]
-        roofline["pipe_frac_note"] = ("executed fp64 instr per unordered pair between 41 (all cluster pairs far) and 69 "
-                                      "(all damped); ncu sm__pipe_fp64 utilisation of the same kernel: profiles/")
+    if ex is not None and c_ms > 0:
+        ach = ex["flops_per_rank_launch"] / (c_ms * 1e-3) / 1e12
+        roofline.update({"achieved": ach, "frac": ach / peak_nominal, "flops_per_launch": ex["flops_per_rank_launch"],
+                         "flops_source": f"executed dadd + dmul + 2 dfma of the ncu capture {ex.get('source', 'profiles/')}"
+                                         + (f", 1/{world} of the single-GPU launch per rank" if world > 1 else ""),
+                         "traffic": (ex.get("dram_bytes") / world) if ex.get("dram_bytes") else None,
+                         "sm_pipe_fp64_pct": ex.get("pipe_fp64_pct")})
+    else:
+        roofline.update({"achieved": None, "frac": None, "traffic": None,
+                         "flops_source": "no executed-flop capture for this workload (profiles/capture_k4_executed.py)"})
     list_pairs = float(getattr(cnt, "pairs_induced_list", 0.0))
     if s.params.polar_ewald_full and list_pairs > 0 and c_ms > 0:
         # full-Ewald polarization: the per-pass kernel between the phase marks is the pair-list apply (K7), HBM-bound:
         # 48-byte entries streamed once + 3 x 8 bytes of field written per polarizable atom (the mu_j gathers hit L2)
         nbytes = 48.0 * list_pairs + 24.0 * cnt.n_polarizable
-        hbm = None
         try:
             hbm = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
             src = "MEASURED_PEAKS.json hbm_gbs (driver-measured copy bandwidth)"
@@ -424,12 +544,6 @@ def own_arm(args):
                     "unit": "GB/s", "frac": ach / hbm, "traffic": None, "peak_source": src, "bytes_per_launch": nbytes,
                     "list_pairs": list_pairs, "ms_per_launch": c_ms,
                     "phase_ms": {k: float(np.mean(v)) for k, v in phases.items()}}
-    prof = os.path.join(ROOT, "profiles", "k4_traffic.json")
-    if os.path.exists(prof) and roofline["bound"] == "fp64":
-        try:
-            roofline["traffic"] = json.load(open(prof)).get(args.workload)
-        except Exception:
-            pass
 
     cpu = None
     if not args.no_cpu_baseline:
@@ -442,17 +556,16 @@ def own_arm(args):
         "data": "synthetic",
         "config": {"workload": args.workload, "n_atoms": n, "n_polarizable": int(cnt.n_polarizable),
                    "polar_iterations": int(e.polar_iterations), "pair_interactions_per_step": pairs,
-                   "mc_steps_per_s": 1e3 / ms_per_step, "l2": "flushed between timed iterations (256 MiB fill)",
-                   "parallelism": f"rows{world}", "energy_K": e.total},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "mc_steps_per_s": args.steps / float(t.item()),
-                "host_ms_per_step": {"set_positions": 1e3 * t_set / args.steps, "energy": 1e3 * t_eval / args.steps,
-                                     "write_back": 1e3 * t_wb / args.steps}},
+                   "mc_steps_per_s": 1e3 / ms_per_step, "mc_steps_per_s_dropin": mc_dropin,
+                   "l2": "flushed between timed iterations (256 MiB fill)",
+                   "parallelism": f"rows{world}" if world > 1 else "single", "energy_K": energy_timed, "parity": parity,
+                   "exchange": ("engine kernels over NVLink peer memory (static-field rows, induced field of every pass, "
+                                "final scalars); no NCCL call in energy()") if world > 1 and eng_peer[0] else
+                               ("NCCL collectives between staged kernels" if world > 1 else None)},
+        "e2e": e2e, "e2e_abi": e2e_abi,
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
     }
     print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
     return 0
 
 
@@ -464,6 +577,7 @@ def main():
     ap.add_argument("--workload", default="mof_h2_63k")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-mc-dropin", action="store_true", help="skip the short `mpmc_b200 <input>` MC run")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)

@@ -49,7 +49,7 @@
 extern "C" {
 #endif
 
-#define MPMC_B200_ABI_VERSION 2
+#define MPMC_B200_ABI_VERSION 3
 
 /* damp_type: src/include/defines.h DAMPING_* enum */
 enum { MPMC_DAMP_OFF = 0, MPMC_DAMP_LINEAR = 1, MPMC_DAMP_EXPONENTIAL = 2 };
@@ -149,6 +149,16 @@ const char *mpmc_b200_last_error(void);
 /* device = CUDA ordinal.  Fails (non-zero) when no CUDA device is usable. */
 int mpmc_b200_create(mpmc_b200_ctx **ctx, int device);
 void mpmc_b200_destroy(mpmc_b200_ctx *ctx);
+/* One process driving `ndev` (1..8) GPUs of one NVLink / NVSwitch box: the single-process form of the multi-GPU path
+ * SURVEY 7.2 / 8b plan ("one stream per device, created once at first energy()") and the reference's own open TODO
+ * (src/polarization_gpu/polar_cuda.cu:32).  Rank i of the sharded evaluation lives on devices[i] (NULL: 0..ndev-1).
+ * The returned context leads the group: mpmc_b200_set_params / _set_atoms / _set_positions / _energy / _polar /
+ * _get_atom_arrays / _get_counters / _destroy on it act on the whole group, so the drop-in shim only changes its
+ * create call (MPMC_B200_DEVICES).  Every exchange (static-field rows, induced-field partial sums of
+ * every solver pass, the final scalars) is done by the library's own kernels over peer memory; there is no NCCL call.
+ * Jacobi-family solvers only; Gauss-Seidel, polar_ewald_full and cavity_autoreject_absolute are refused (error 3). */
+int mpmc_b200_create_group(mpmc_b200_ctx **ctx, int ndev, const int *devices);
+int mpmc_b200_group_size(mpmc_b200_ctx *ctx);
 
 /* Optional: run on a caller-owned cudaStream_t (passed as void*). NULL = own stream. */
 int mpmc_b200_set_stream(mpmc_b200_ctx *ctx, void *cuda_stream);
@@ -180,7 +190,10 @@ int mpmc_b200_set_positions(mpmc_b200_ctx *ctx, int first, int count, const doub
  */
 int mpmc_b200_set_shard(mpmc_b200_ctx *ctx, int rank, int world);
 
-/* energy(): all kernels + device->host copy of the scalars; synchronous. */
+/* energy(): all kernels + device->host copy of the scalars; synchronous.  On a sharded context (set_shard with
+ * world > 1 after mpmc_b200_peer_export / _connect, or the leader of a group) the whole staged evaluation described
+ * below runs inside the library with every exchange over peer memory, and `out` / the counters are the totals over
+ * all ranks (identical bits on every rank). */
 int mpmc_b200_energy(mpmc_b200_ctx *ctx, mpmc_b200_energies *out);
 /* Opt-in incremental evaluation (the reference recomputes everything every step, TODO:2; its own pair_t cache,
  * src/energy/pairs.c:243-250, is the same idea): with on != 0 -- or MPMC_B200_INCREMENTAL=1 in the environment when the
@@ -264,6 +277,11 @@ int mpmc_b200_shard_rows(mpmc_b200_ctx *ctx, int *begin, int *end, int *n_pol, i
  * mu, ef_static, ef_induced, ef_induced_change : [3*n] ; dipole_rrms, rank_metric : [n] */
 int mpmc_b200_get_atom_arrays(mpmc_b200_ctx *ctx, double *mu, double *ef_static, double *ef_induced,
                               double *ef_induced_change, double *dipole_rrms, double *rank_metric);
+/* The same results without the copy: pointers into the library's pinned host image ([3*n] / [n] doubles, reference
+ * list order), valid until the next call on this context.  The drop-in shim scatters from here straight into atom_t
+ * (src/include/structs.h:47-50) with its host threads. */
+int mpmc_b200_atom_arrays_view(mpmc_b200_ctx *ctx, const double **mu, const double **ef_static, const double **ef_induced,
+                               const double **ef_induced_change, const double **dipole_rrms, const double **rank_metric);
 /* Sharded runs: 1 when every rank's get_atom_arrays() is complete (symmetric contraction: the all-reduced
  * field lets every rank update every row; only the write-back-only palmo rows of non-polarizable atoms stay
  * per rank), 0 when the row-owned arrays hold this rank's rows only and must be summed over ranks. */

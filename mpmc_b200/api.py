@@ -298,6 +298,8 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_create.argtypes = [C.POINTER(vp), C.c_int]
     lib.mpmc_b200_destroy.argtypes = [vp]
     lib.mpmc_b200_destroy.restype = None
+    lib.mpmc_b200_create_group.argtypes = [C.POINTER(vp), C.c_int, ip]
+    lib.mpmc_b200_group_size.argtypes = [vp]
     lib.mpmc_b200_set_stream.argtypes = [vp, vp]
     lib.mpmc_b200_set_params.argtypes = [vp, C.POINTER(Params)]
     lib.mpmc_b200_set_atoms.argtypes = [vp, C.c_int, dp, dp, dp, dp, dp, dp, ip, ip]
@@ -317,6 +319,7 @@ def load_library(path: str = LIB_PATH):
     lib.mpmc_b200_shard_field_rows.argtypes = [vp, ip, ip, ip]
     lib.mpmc_b200_get_atom_arrays.argtypes = [vp, dp, dp, dp, dp, dp, dp]
     lib.mpmc_b200_atom_arrays_complete.argtypes = [vp]
+    lib.mpmc_b200_atom_arrays_view.argtypes = [vp] + [C.POINTER(dp)] * 6
     lib.mpmc_b200_peer_export.argtypes = [vp, C.c_char_p]
     lib.mpmc_b200_peer_connect.argtypes = [vp, C.c_int, C.c_char_p]
     lib.mpmc_b200_peer_active.argtypes = [vp]
@@ -327,7 +330,7 @@ def load_library(path: str = LIB_PATH):
         f = getattr(lib, name)
         if name not in ("mpmc_b200_last_error", "mpmc_b200_destroy"):
             f.restype = C.c_int
-    if lib.mpmc_b200_abi_version() != 2:
+    if lib.mpmc_b200_abi_version() != 3:
         raise RuntimeError("libmpmc_b200.so ABI version mismatch")
     _lib = lib
     return lib
@@ -342,7 +345,7 @@ ABI_SYMBOLS = [
     "mpmc_b200_get_atom_arrays", "mpmc_b200_atom_arrays_complete",
     "mpmc_b200_peer_export", "mpmc_b200_peer_connect", "mpmc_b200_peer_active",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak", "mpmc_b200_set_incremental",
-    "mpmc_b200_set_warm_start",
+    "mpmc_b200_set_warm_start", "mpmc_b200_create_group", "mpmc_b200_group_size", "mpmc_b200_atom_arrays_view",
 ]
 
 
@@ -353,10 +356,16 @@ class EngineError(RuntimeError):
 class Engine:
     """One CUDA context of the energy engine (one per GPU / per MC chain)."""
 
-    def __init__(self, device: int = 0, stream: Optional[int] = None):
+    def __init__(self, device: int = 0, stream: Optional[int] = None, devices=None):
+        """devices: a list of CUDA ordinals makes this the leader of a group -- one process driving several GPUs of one
+        NVLink box (mpmc_b200_create_group); every call below then addresses the whole group."""
         self.lib = load_library()
         self._ctx = C.c_void_p()
-        self._check(self.lib.mpmc_b200_create(C.byref(self._ctx), int(device)))
+        if devices is not None:
+            d = (C.c_int * len(devices))(*[int(x) for x in devices])
+            self._check(self.lib.mpmc_b200_create_group(C.byref(self._ctx), len(devices), d))
+        else:
+            self._check(self.lib.mpmc_b200_create(C.byref(self._ctx), int(device)))
         self.n = 0
         if stream is not None:
             self._check(self.lib.mpmc_b200_set_stream(self._ctx, C.c_void_p(stream)))
@@ -402,6 +411,9 @@ class Engine:
 
     def last_eval_incremental(self) -> bool:
         return bool(self.counters().incremental)
+
+    def group_size(self) -> int:
+        return int(self.lib.mpmc_b200_group_size(self._ctx))
 
     def set_shard(self, rank: int, world: int):
         self._check(self.lib.mpmc_b200_set_shard(self._ctx, rank, world))

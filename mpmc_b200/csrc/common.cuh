@@ -27,6 +27,17 @@ constexpr double kMAXVALUE = 1.0e40;
 constexpr double kSMALL_dR = 1.0e-12;
 constexpr int kMAX_ITERATION_COUNT = 128;
 
+// cudaFuncSetAttribute() applies to the current device only, and one process may drive several GPUs
+// (mpmc_b200_create_group): true the first time a launcher runs with the current device (`seen` is its static bit set).
+inline bool first_on_device(unsigned long long& seen) {
+    int d = 0;
+    cudaGetDevice(&d);
+    const unsigned long long bit = 1ull << (d & 63);
+    if (seen & bit) return false;
+    seen |= bit;
+    return true;
+}
+
 // Scalars every kernel needs, passed by value (lands in the constant bank).
 struct Cell {
     double B[3][3];  // basis[q][p]

@@ -427,6 +427,31 @@ __global__ void __launch_bounds__(256) palmo_finish_peer_kernel(int n, int np, P
     }
 }
 
+// out[i] = sum_r src[r][i] in rank order: the all-gather of row-owned data (the static field: every row is written by
+// exactly one rank and zero elsewhere, so the sum IS the gather and every rank gets the same bits)
+__global__ void __launch_bounds__(256) peer_sum_kernel(PeerWait pw, size_t n, double* __restrict__ out) {
+    peer_wait(pw);
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double e = 0.0;
+    for (int r = 0; r < pw.world; r++) e += __ldcv(pw.src[r] + i);
+    out[i] = e;
+}
+
+// The device scalars of an evaluation combined over the ranks, in rank order (identical bits on every rank):
+// sums, except slot `min_slot` (smallest intermolecular distance) which takes the minimum.
+__global__ void peer_scalars_kernel(PeerWait pw, int n, int min_slot, double* __restrict__ out) {
+    peer_wait(pw);
+    const int i = threadIdx.x;
+    if (i >= n) return;
+    double e = __ldcv(pw.src[0] + i);
+    for (int r = 1; r < pw.world; r++) {
+        const double v = __ldcv(pw.src[r] + i);
+        e = (i == min_slot) ? fmin(e, v) : e + v;
+    }
+    out[i] = e;
+}
+
 __global__ void palmo_finish_kernel(int n, int np, const double* __restrict__ epart, int jsplits,
                                     const double* __restrict__ eind, double* __restrict__ eic, int row_begin, int row_end) {
     const int i = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
@@ -503,6 +528,15 @@ void launch_dipole_update_peer(const SubsetDev& pol, const UpdateOpts& o, const 
 void launch_palmo_finish_peer(const SubsetDev& pol, const PeerWait& pw, const double* eind, double* eic, cudaStream_t s) {
     if (pol.n_pad <= 0) return;
     palmo_finish_peer_kernel<<<(pol.n_pad + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, pw, eind, eic);
+}
+
+void launch_peer_sum(const PeerWait& pw, size_t n, double* out, cudaStream_t s) {
+    if (n == 0) return;
+    peer_sum_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(pw, n, out);
+}
+
+void launch_peer_scalars(const PeerWait& pw, int n, int min_slot, double* out, cudaStream_t s) {
+    peer_scalars_kernel<<<1, 64, 0, s>>>(pw, n, min_slot, out);
 }
 
 void launch_palmo_finish(const SubsetDev& pol, const double* epart, int jsplits, const double* eind, double* eic,
@@ -979,11 +1013,10 @@ void launch_gs_block_coeffs(const Cell& c, bool ortho, const SubsetDev& pol, con
 void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* cbox, int ysplits,
                            double* epartI, double* epartJ, double* esum, const double* es, double* mu, double* mu_new,
                            double* eind, double* delta, const double* coef, cudaStream_t s) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0;
+    if (first_on_device(attr_set)) {
         cudaFuncSetAttribute(gs_delta_block_table_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GS_PAIRS * sizeof(double2)));
         cudaFuncSetAttribute(gs_delta_block_table_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GS_PAIRS * sizeof(double2)));
-        attr_set = true;
     }
     const double2* cf = reinterpret_cast<const double2*>(coef);
     static int warp_form = -1;  // MPMC_B200_GS_BLOCK=table|plain selects the earlier block kernels (A/B)
@@ -1008,11 +1041,10 @@ void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, cons
 #define LAUNCH(ORTHO, DAMP, WF)                                                                                                \
     {                                                                                                                          \
         if (warp_form == 1) {                                                                                                  \
-            static bool wattr = false;                                                                                         \
-            if (!wattr) {                                                                                                      \
+            static unsigned long long wattr = 0;                                                                                         \
+            if (first_on_device(wattr)) {                                                                                                      \
                 cudaFuncSetAttribute(gs_delta_block_warp_kernel<ORTHO, DAMP, WF>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                      (int)wsmem);                                                                              \
-                wattr = true;                                                                                                  \
             }                                                                                                                  \
             gs_delta_block_warp_kernel<ORTHO, DAMP, WF><<<1, TILE, wsmem, s>>>(c, pol, k, aux, alpha, esum, es, mu, mu_new,    \
                                                                              eind, delta, b);                                 \

@@ -479,9 +479,11 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
         for (int q = 0; q < 3; q++) rmax += 0.5 * sqrt(c.B[q][0] * c.B[q][0] + c.B[q][1] * c.B[q][1] + c.B[q][2] * c.B[q][2]);
         k.fastexp = (l >= 0.0 && l * rmax < 700.0) ? 1 : 0;
     }
-    if (const char* v = getenv("MPMC_B200_SYM_FAR")) {  // timing experiments only ("all" gives wrong fields)
+    if (const char* v = getenv("MPMC_B200_SYM_FAR")) {  // A/B timing: "off" evaluates the damping of every pair (same bits)
         if (!strcmp(v, "off")) k.far2 = 0.0;
+#ifdef MPMC_B200_TIMING_EXPERIMENTS  // never in the product build: treating every cluster pair as far gives WRONG fields
         if (!strcmp(v, "all") && k.far2 > 0.0) k.far2 = 1e-300;
+#endif
     }
     k.box = box_len(c);
     return k;
@@ -494,6 +496,10 @@ void launch_cluster_boxes(const Cell& c, bool ortho, const SubsetDev& pol, doubl
     if (nclus <= 0) return;
     cluster_box_kernel<<<(nclus * 32 + 255) / 256, 256, 0, s>>>(pol.n, pol.n_pad, c.B[0][0], c.B[1][1], c.B[2][2], c.R[0][0],
                                                                 c.R[1][1], c.R[2][2], ortho ? 1 : 0, pol.x, pol.y, pol.z, cbox);
+}
+
+void launch_peer_signal(const PeerSignal& sig, cudaStream_t s) {
+    if (sig.world > 1) peer_signal_kernel<<<1, 32, 0, s>>>(sig);
 }
 
 int dipole_sym_tile() { return STILE; }

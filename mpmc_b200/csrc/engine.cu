@@ -222,11 +222,19 @@ struct mpmc_b200_ctx {
     bool subsets_stale = false;
 
     // peer-memory exchange of the induced-field partial sums (sharded runs; see PeerSignal / PeerWait)
-    unsigned char* peer_local = nullptr;  // one IPC-exported allocation: [2][3][peer_cap] doubles | 16 flags | counter
-    size_t peer_cap = 0;                  // rows per component the allocation was sized for
-    void* peer_base[PEER_MAX] = {nullptr};  // every rank's allocation as seen from this process
-    bool peer_ready = false;
-    unsigned long long peer_seq = 0;
+    // One exported allocation per rank (layout: peer_* helpers below): the induced-field partial sums of the symmetric
+    // contraction (double buffered), this rank's static-field rows, its device scalars (double buffered) and one flag
+    // array per exchange channel.  Peers map it through CUDA IPC (one process per GPU) or directly (one process
+    // driving several GPUs: mpmc_b200_create_group).
+    unsigned char* peer_local = nullptr;
+    size_t peer_cap = 0, peer_cap_atoms = 0;  // padded polarizable / atom rows the allocation was sized for
+    void* peer_base[PEER_MAX] = {nullptr};    // every rank's allocation as seen from this process
+    bool peer_ready = false, peer_ipc = false;
+    unsigned long long peer_seq[3] = {0, 0, 0};  // per channel: induced field, static field, scalars
+    bool field_via_peer = false;    // polar_field() leaves this rank's rows in the exported buffer (sharded_eval)
+    bool scalars_complete = false;  // the device scalars of the pending evaluation are already summed over the ranks
+    std::vector<mpmc_b200_ctx*> group;  // leader only (mpmc_b200_create_group): every rank's context, this one first
+    bool group_member = false;          // owned by a leader: destroyed with it
     cudaStream_t side = nullptr;  // K1 / K2 overlap with the polarization solve
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool side_active = false;
@@ -1022,6 +1030,72 @@ static int run_structure_factor(Ctx* c, const Subset& sub, const DevBuf<double>&
     return 0;
 }
 
+// ---- peer-memory exchange: layout of one rank's exported allocation
+// doubles: ind [2][3][cap] | field [3][cap_atoms] | scal [2][64]; then CH_COUNT x PEER_MAX flags
+enum PeerChannel { CH_IND = 0, CH_FIELD = 1, CH_SCAL = 2, CH_COUNT = 3 };
+static size_t peer_doubles(size_t cap, size_t cap_atoms) { return 2 * 3 * cap + 3 * cap_atoms + 2 * 64; }
+static size_t peer_bytes(size_t cap, size_t cap_atoms) {
+    return sizeof(double) * peer_doubles(cap, cap_atoms) + sizeof(unsigned long long) * CH_COUNT * PEER_MAX + 64;
+}
+static double* peer_buf(void* base, size_t cap, int parity) { return reinterpret_cast<double*>(base) + (size_t)parity * 3 * cap; }
+static double* peer_field(void* base, size_t cap) { return reinterpret_cast<double*>(base) + 2 * 3 * cap; }
+static double* peer_scal(void* base, size_t cap, size_t cap_atoms, int parity) {
+    return reinterpret_cast<double*>(base) + 2 * 3 * cap + 3 * cap_atoms + (size_t)parity * 64;
+}
+static unsigned long long* peer_flags(void* base, size_t cap, size_t cap_atoms, int ch) {
+    return reinterpret_cast<unsigned long long*>(reinterpret_cast<double*>(base) + peer_doubles(cap, cap_atoms)) + ch * PEER_MAX;
+}
+// Which Jacobi contraction runs.  The symmetric kernel's work item is a 256 x 256 tile pair (~130 us of one CTA):
+// below ~8k polarizable atoms its grid does not fill the GPU and an evaluation costs one item per iteration however
+// small the system, while the row form with the j range fully split ((n/128)^2 CTAs of 128 x 128 pairs) finishes in
+// 10-60 us despite doing every pair twice.  Sharded runs always use the symmetric form (its exchange protocol).
+static bool sym_now(const Ctx* c) {
+    const char* v = getenv("MPMC_B200_SYM_MIN");  // read per call: the tests switch it inside one process
+    const int min_pad = v ? atoi(v) : 8192;
+    return c->use_sym && (c->world > 1 || c->pol.n_pad >= min_pad);
+}
+static bool peer_active(const Ctx* c) {
+    return c->peer_ready && c->world > 1 && c->use_sym && (size_t)c->pol.n_pad == c->peer_cap &&
+           (size_t)c->n_pad == c->peer_cap_atoms;
+}
+static void peer_teardown(Ctx* c) {
+    for (int r = 0; r < PEER_MAX; r++) {
+        if (c->peer_base[r] && r != c->rank && c->peer_ipc) cudaIpcCloseMemHandle(c->peer_base[r]);
+        c->peer_base[r] = nullptr;
+    }
+    if (c->peer_local) cudaFree(c->peer_local);
+    c->peer_local = nullptr;
+    c->peer_cap = c->peer_cap_atoms = 0;
+    c->peer_ready = false;
+    c->peer_ipc = false;
+}
+
+// consumer side of channel `ch` at its current sequence number
+static PeerWait peer_wait_args(Ctx* c, int ch = CH_IND) {
+    PeerWait pw;
+    memset(&pw, 0, sizeof(pw));
+    pw.world = c->world;
+    pw.seq = c->peer_seq[ch];
+    pw.my_flags = peer_flags(c->peer_base[c->rank], c->peer_cap, c->peer_cap_atoms, ch);
+    const int parity = (int)(pw.seq & 1ull);
+    for (int r = 0; r < c->world; r++)
+        pw.src[r] = ch == CH_IND ? peer_buf(c->peer_base[r], c->peer_cap, parity)
+                    : ch == CH_FIELD ? peer_field(c->peer_base[r], c->peer_cap)
+                                     : peer_scal(c->peer_base[r], c->peer_cap, c->peer_cap_atoms, parity);
+    pw.timeout_flag = c->scalars.p + S_PEER_TIMEOUT;
+    return pw;
+}
+// producer side: next sequence number of channel `ch`, flag slot `rank` of every peer
+static PeerSignal peer_signal_args(Ctx* c, int ch) {
+    PeerSignal sg;
+    memset(&sg, 0, sizeof(sg));
+    sg.world = c->world;
+    sg.me = c->rank;
+    sg.seq = ++c->peer_seq[ch];
+    for (int r = 0; r < c->world; r++) sg.flags[r] = peer_flags(c->peer_base[r], c->peer_cap, c->peer_cap_atoms, ch);
+    return sg;
+}
+
 // ---- polar(): static field + solver + energy.  Enqueue only (precision mode syncs per iteration).
 // row ranges of this shard (tile aligned) and per-evaluation counters
 static void polar_prepare(Ctx* c) {
@@ -1053,7 +1127,10 @@ static int polar_field(Ctx* c) {
     const int fb = c->fb, fe = c->fe;
     // ---------------- static field: thole_field() (thole_field.c:14-36) ----------------
     phase_begin(c, PH_FIELD);
-    CU(cudaMemsetAsync(c->ef_static.p, 0, sizeof(double) * 3 * np, st));
+    // sharded_eval(): this rank's rows go to its exported buffer (zero elsewhere); peer_sum_kernel of every rank then
+    // adds the `world` buffers in rank order into ef_static -- the all-gather of the row-owned field over NVLink
+    double* const ef_dst = c->field_via_peer ? peer_field(c->peer_base[c->rank], c->peer_cap) : c->ef_static.p;
+    CU(cudaMemsetAsync(ef_dst, 0, sizeof(double) * 3 * np, st));
     FieldOpts fo;
     fo.table = nullptr;
     fo.table_max = 0;
@@ -1070,7 +1147,7 @@ static int polar_field(Ctx* c) {
         kv.kmax = P.ewald_kmax;
         kv.l = c->kl.p;
         kv.weight = c->kweight_field.p;
-        launch_recip_field(cell, a, kv, c->kvec.p, c->sf.p, 8.0 * M_PI / P.volume, fb, fe, c->ef_static.p, st);
+        launch_recip_field(cell, a, kv, c->kvec.p, c->sf.p, 8.0 * M_PI / P.volume, fb, fe, ef_dst, st);
         c->launches++;
         accumulate = true;
     } else if (P.polar_wolf || P.polar_wolf_full) {
@@ -1110,7 +1187,7 @@ static int polar_field(Ctx* c) {
             }
             int cb, ce;
             shard_range(c->sorted.n_pad / 32, c->rank, c->world, cb, ce);
-            launch_static_field_clusters(cell, ortho, sd, fo, cb, ce, P.cutoff + 1e-6, accumulate, c->ef_static.p, np,
+            launch_static_field_clusters(cell, ortho, sd, fo, cb, ce, P.cutoff + 1e-6, accumulate, ef_dst, np,
                                          c->field_cnt.p, st);
             sum_reduce_kernel<<<1, 1024, 0, st>>>(c->field_cnt.p, std::max(ce - cb, 0), c->scalars.p + S_FIELDCNT);
             c->launches += 2;
@@ -1119,10 +1196,15 @@ static int polar_field(Ctx* c) {
     if (c->charged.n > 0 && fe > fb) {
         const int gx = (fe - fb + TILE - 1) / TILE;
         launch_static_field(cell, ortho, a, c->charged.dev(), fo, fb, fe, c->field_jsplits, c->epart.p, c->field_cnt.p, st);
-        launch_field_reduce(c->epart.p, c->field_jsplits, np, fb, fe, accumulate, c->ef_static.p, st);
+        launch_field_reduce(c->epart.p, c->field_jsplits, np, fb, fe, accumulate, ef_dst, st);
         // work counter: per-CTA counts of (row, charged source) contributions -> one scalar
         sum_reduce_kernel<<<1, 1024, 0, st>>>(c->field_cnt.p, gx * c->field_jsplits, c->scalars.p + S_FIELDCNT);
         c->launches += 3;
+    }
+    if (c->field_via_peer) {
+        const PeerSignal sg = peer_signal_args(c, CH_FIELD);
+        launch_peer_signal(sg, st);
+        c->launches++;
     }
     phase_end(c, PH_FIELD);
     CU(cudaGetLastError());
@@ -1178,46 +1260,6 @@ static int polar_init(Ctx* c) {
     return 0;
 }
 
-// ---- peer-memory exchange: layout of one rank's exported allocation
-static size_t peer_bytes(size_t cap) { return sizeof(double) * 2 * 3 * cap + sizeof(unsigned long long) * 16 + 64; }
-static double* peer_buf(void* base, size_t cap, int parity) { return reinterpret_cast<double*>(base) + (size_t)parity * 3 * cap; }
-static unsigned long long* peer_flags(void* base, size_t cap) {
-    return reinterpret_cast<unsigned long long*>(reinterpret_cast<double*>(base) + 2 * 3 * cap);
-}
-// Which Jacobi contraction runs.  The symmetric kernel's work item is a 256 x 256 tile pair (~130 us of one CTA):
-// below ~8k polarizable atoms its grid does not fill the GPU and an evaluation costs one item per iteration however
-// small the system, while the row form with the j range fully split ((n/128)^2 CTAs of 128 x 128 pairs) finishes in
-// 10-60 us despite doing every pair twice.  Sharded runs always use the symmetric form (its exchange protocol).
-static bool sym_now(const Ctx* c) {
-    const char* v = getenv("MPMC_B200_SYM_MIN");  // read per call: the tests switch it inside one process
-    const int min_pad = v ? atoi(v) : 8192;
-    return c->use_sym && (c->world > 1 || c->pol.n_pad >= min_pad);
-}
-static bool peer_active(const Ctx* c) {
-    return c->peer_ready && c->world > 1 && c->use_sym && (size_t)c->pol.n_pad == c->peer_cap;
-}
-static void peer_teardown(Ctx* c) {
-    for (int r = 0; r < PEER_MAX; r++) {
-        if (c->peer_base[r] && r != c->rank) cudaIpcCloseMemHandle(c->peer_base[r]);
-        c->peer_base[r] = nullptr;
-    }
-    if (c->peer_local) cudaFree(c->peer_local);
-    c->peer_local = nullptr;
-    c->peer_cap = 0;
-    c->peer_ready = false;
-}
-
-static PeerWait peer_wait_args(Ctx* c) {
-    PeerWait pw;
-    memset(&pw, 0, sizeof(pw));
-    pw.world = c->world;
-    pw.seq = c->peer_seq;
-    pw.my_flags = peer_flags(c->peer_base[c->rank], c->peer_cap);
-    for (int r = 0; r < c->world; r++) pw.src[r] = peer_buf(c->peer_base[r], c->peer_cap, (int)(c->peer_seq & 1ull));
-    pw.timeout_flag = c->scalars.p + S_PEER_TIMEOUT;
-    return pw;
-}
-
 // one Jacobi-family pass over this shard's rows: contract_dipoles + calc_dipole_rrms + the
 // are_we_done_yet residual (thole_iterative.c:27-117); mu itself is not touched
 // symmetric contraction of this shard's I tiles -> c->esum (contribution to E_ind of ALL rows)
@@ -1227,16 +1269,10 @@ static int polar_contract_sym(Ctx* c) {
     if (peer_active(c)) {
         // this rank's contribution goes to its exported buffer (double buffered by the parity of the sequence
         // number: a peer may still be reading the previous one); peer_signal_kernel then raises the flags
-        c->peer_seq++;
-        PeerSignal sg;
-        memset(&sg, 0, sizeof(sg));
-        sg.world = c->world;
-        sg.me = c->rank;
-        sg.seq = c->peer_seq;
-        for (int r = 0; r < c->world; r++) sg.flags[r] = peer_flags(c->peer_base[r], c->peer_cap);
+        const PeerSignal sg = peer_signal_args(c, CH_IND);
         launch_dipole_contract_sym(make_cell(P), is_ortho(P), c->pol.dev(), dipole_opts(P), c->mu.p, c->cbox.p, c->rank, c->world,
                                    c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p,
-                                   peer_buf(c->peer_base[c->rank], c->peer_cap, (int)(c->peer_seq & 1ull)), c->stream, &sg);
+                                   peer_buf(c->peer_base[c->rank], c->peer_cap, (int)(sg.seq & 1ull)), c->stream, &sg);
     } else
     launch_dipole_contract_sym(make_cell(P), is_ortho(P), c->pol.dev(), dipole_opts(P), c->mu.p, c->cbox.p, c->rank, c->world,
                                c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p, c->esum.p, c->stream);
@@ -1703,8 +1739,11 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
     if (!c->have_atoms) FAIL(2, "mpmc_b200_set_atoms has not been called");
     if (check_supported(c->P)) return 3;
     const mpmc_b200_params& P = c->P;
+    if (c->world > 1 && P.cavity_autoreject_absolute)  // a minimum over ALL pairs decides before anything else is summed
+        FAIL(3, "cavity_autoreject_absolute is evaluated on one GPU only (sharded contexts refuse it)");
     cudaStream_t st = c->stream;
     CU(cudaSetDevice(c->device));
+    c->scalars_complete = false;
     c->inc_valid = false;  // S(k) and the sums are rewritten: mpmc_b200_energy() re-arms the incremental path afterwards
     if (c->kdirty)
         if (build_kvectors(c)) return 10;
@@ -1852,9 +1891,11 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     const double* h = c->h_scalars;
     if (h[S_PEER_TIMEOUT] != 0.0) FAIL(12, "peer exchange timed out: a rank never published its induced-field partial sums");
     memset(out, 0, sizeof(*out));
-    const bool lead = (c->rank == 0);  // host-side analytic terms are added once (rank 0) in sharded runs
+    // host-side analytic terms are added once: by rank 0 when the caller sums the ranks' partial energies (staged
+    // protocol), by every rank when the device scalars were already combined over the ranks (sharded_eval)
+    const bool lead = (c->rank == 0) || c->scalars_complete;
     out->min_intermolecular_r = h[S_PAIR + 3];
-    c->cnt.pairs_tested = c->use_clusters ? (c->rank == 0 ? c->pairs_tested_analytic : 0.0) : h[S_PAIR + 4];
+    c->cnt.pairs_tested = c->use_clusters ? (lead ? c->pairs_tested_analytic : 0.0) : h[S_PAIR + 4];
     c->cnt.pairs_lj = h[S_PAIR + 5] + (P.rd_crystal ? h[S_CRYSTAL + 1] : 0.0);
     c->cnt.pairs_es = h[S_PAIR + 6];
     c->cnt.kernel_launches = c->launches;
@@ -1887,6 +1928,200 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
         }
     }
     out->total = out->rd + out->coulombic + out->polar;  // energy.c:194
+    return 0;
+}
+
+// ================================================================================================
+// Sharded evaluation inside the library: `nl` contexts of THIS process, each one rank of the same
+// world (nl == world: one process drives every GPU of the box, mpmc_b200_create_group; nl == 1: one process per GPU,
+// the ranks' exported buffers mapped through CUDA IPC).  thole_iterative() (thole_iterative.c:168-259) cut where partial
+// results have to be combined, with every exchange done by the engine's own kernels over NVLink peer memory:
+//   static field   K3 leaves this rank's rows in its exported buffer      -> peer_sum_kernel        (all-gather)
+//   every pass     K4 leaves its contribution to E_ind of all rows there  -> dipole_update_peer     (all-reduce + update)
+//   the end        the 32 device scalars                                  -> peer_scalars_kernel    (all-reduce)
+// No NCCL call, no host round trip between stages (tolerance mode reads one scalar per pass, as on one GPU).  Stages are
+// issued rank by rank from one host thread; a kernel that waits for a peer's flag is only ever enqueued after every
+// allocation of the evaluation has been made (cudaMalloc may synchronise devices that map each other's memory).
+// ================================================================================================
+static int sharded_eval(Ctx** cs, int nl, bool with_pair, mpmc_b200_energies* out) {
+    Ctx* c0 = cs[0];
+    const mpmc_b200_params& P = c0->P;
+    for (int i = 0; i < nl; i++) {
+        Ctx* c = cs[i];
+        if (!c->have_params || !c->have_atoms) FAIL(2, "no system");
+        if (!peer_active(c)) FAIL(2, "sharded evaluation needs the peer exchange (mpmc_b200_peer_export / _connect after set_atoms)");
+        if (c->world != c0->world || c->n != c0->n || c->pol.n_pad != c0->pol.n_pad) FAIL(2, "ranks hold different systems");
+    }
+    const bool polar = P.polarization && !P.rd_only;
+    if (polar && (P.polar_gs || P.polar_gs_ranked) && !P.polar_ewald_full)
+        FAIL(3, "Gauss-Seidel polarization is single-GPU only (sequential dependency)");
+    if (polar && P.polar_ewald_full) FAIL(3, "polar_ewald_full is single-GPU in this round (replicas only)");
+    // run `fn` for every local rank with its device current; the first non-zero return code ends the evaluation
+    auto each = [&](auto&& fn) -> int {
+        for (int i = 0; i < nl; i++) {
+            Ctx* c = cs[i];
+            if (cudaSetDevice(c->device) != cudaSuccess) {
+                g_err = "cudaSetDevice failed";
+                return 10;
+            }
+            if (const int rc = fn(c)) return rc;
+        }
+        return 0;
+    };
+#define RUN(...)                                             \
+    do {                                                     \
+        if (const int rc__ = each(__VA_ARGS__)) return rc__; \
+    } while (0)
+    RUN([&](Ctx* c) -> int { return enqueue_energy(c, with_pair, false); });
+    int it = 0;
+    if (polar) {
+        RUN([&](Ctx* c) -> int {
+            polar_prepare(c);
+            c->field_via_peer = true;
+            const int rc = polar_field(c);
+            c->field_via_peer = false;
+            c->last_had_polar = true;
+            return rc ? 10 : 0;
+        });
+        RUN([&](Ctx* c) -> int {
+            phase_begin(c, PH_DIPOLE);
+            launch_peer_sum(peer_wait_args(c, CH_FIELD), (size_t)3 * c->n_pad, c->ef_static.p, c->stream);
+            c->launches++;
+            return polar_init(c) ? 10 : 0;
+        });
+        if (!P.polar_zodid && c0->pol.n > 0) {
+            const bool precision_mode = P.polar_precision != 0.0;
+            const double allowed = P.polar_precision * P.polar_precision * kDEBYE2SKA * kDEBYE2SKA;
+            bool keep = true;
+            while (keep) {
+                it++;
+                if (it >= kMAX_ITERATION_COUNT && precision_mode) {  // divergence bail-out (:199-210), every rank alike
+                    RUN([&](Ctx* c) -> int {
+                        reset_dipoles_kernel<<<(c->pol.n + 255) / 256, 256, 0, c->stream>>>(c->pol.n, c->pol.n_pad, c->pol.alpha.p,
+                                                                                           c->es.p, c->mu.p, c->eic.p);
+                        c->launches++;
+                        c->pending_iter_success = 1;
+                        CU(cudaGetLastError());
+                        return 0;
+                    });
+                    break;
+                }
+                RUN([&](Ctx* c) -> int { return polar_jacobi_pass(c, it) ? 10 : 0; });  // contraction + reduce + signal
+                RUN([&](Ctx* c) -> int { return polar_update_sym(c, it) ? 10 : 0; });   // wait + rank-ordered sum + update
+                if (!precision_mode)
+                    keep = (it != P.polar_max_iter);
+                else {  // every rank computed the same residual from the same sums: no exchange, one scalar per rank
+                    RUN([&](Ctx* c) -> int {
+                        CU(cudaMemcpyAsync(c->h_scalars + S_ERR, c->scalars.p + S_ERR, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+                        return 0;
+                    });
+                    RUN([&](Ctx* c) -> int {
+                        CU(cudaStreamSynchronize(c->stream));
+                        return 0;
+                    });
+                    double worst;
+                    memcpy(&worst, c0->h_scalars + S_ERR, sizeof(double));
+                    for (int i = 1; i < nl; i++)
+                        if (memcmp(cs[i]->h_scalars + S_ERR, c0->h_scalars + S_ERR, sizeof(double)) != 0)
+                            FAIL(12, "ranks disagree on the dipole residual (replicated dipoles drifted apart)");
+                    keep = worst > allowed;
+                }
+                if (P.polar_palmo && !keep) {
+                    RUN([&](Ctx* c) -> int { return polar_palmo_pass(c) ? 10 : 0; });
+                    RUN([&](Ctx* c) -> int { return polar_palmo_finish_sym(c) ? 10 : 0; });
+                }
+                RUN([&](Ctx* c) -> int { return polar_commit(c, it) ? 10 : 0; });
+            }
+        }
+        RUN([&](Ctx* c) -> int {
+            phase_end(c, PH_DIPOLE);
+            c->pending_iterations = it;
+            return polar_energy_partial(c) ? 10 : 0;
+        });
+    }
+    // the 32 device scalars, combined over the ranks by every rank (rank order => identical bits everywhere)
+    RUN([&](Ctx* c) -> int {
+        join_side(c);
+        const PeerSignal sg = peer_signal_args(c, CH_SCAL);
+        CU(cudaMemcpyAsync(peer_scal(c->peer_base[c->rank], c->peer_cap, c->peer_cap_atoms, (int)(sg.seq & 1ull)), c->scalars.p,
+                           sizeof(double) * 32, cudaMemcpyDeviceToDevice, c->stream));
+        launch_peer_signal(sg, c->stream);
+        return 0;
+    });
+    RUN([&](Ctx* c) -> int {
+        launch_peer_scalars(peer_wait_args(c, CH_SCAL), 32, S_PAIR + 3, c->scalars.p, c->stream);
+        c->launches += 2;
+        phase_end(c, PH_TOTAL);
+        c->pending = true;
+        c->scalars_complete = true;
+        CU(cudaGetLastError());
+        return 0;
+    });
+#undef RUN
+    int rc_all = 0;
+    for (int i = 0; i < nl; i++) {
+        Ctx* c = cs[i];
+        CU(cudaSetDevice(c->device));
+        mpmc_b200_energies e;
+        const int rc = finish_energy(c, &e);
+        c->scalars_complete = false;
+        if (rc && !rc_all) rc_all = rc;
+        if (i == 0 && !rc) *out = e;
+    }
+    CU(cudaSetDevice(c0->device));
+    return rc_all;
+}
+
+// every rank's context of a group led by `c` (or `c` alone)
+static int local_ranks(Ctx* c, Ctx** cs) {
+    if (c->group.empty()) {
+        cs[0] = c;
+        return 1;
+    }
+    for (size_t i = 0; i < c->group.size(); i++) cs[i] = c->group[i];
+    return (int)c->group.size();
+}
+
+// One process, several GPUs: every context allocates its exchange buffer, peer access is enabled pairwise and the
+// buffers are wired directly (no IPC).  Called after set_atoms / set_params of the whole group when a size changed.
+static int group_connect(Ctx* lead) {
+    const int w = (int)lead->group.size();
+    bool ok = w > 1;
+    for (Ctx* c : lead->group) ok = ok && peer_active(c);
+    if (ok || w <= 1) return 0;
+    for (Ctx* c : lead->group) {
+        CU(cudaSetDevice(c->device));
+        CU(cudaStreamSynchronize(c->stream));
+        if (c->side) CU(cudaStreamSynchronize(c->side));
+    }
+    for (Ctx* c : lead->group) {
+        CU(cudaSetDevice(c->device));
+        peer_teardown(c);
+        if (!c->use_sym) continue;
+        c->peer_cap = (size_t)c->pol.n_pad;
+        c->peer_cap_atoms = (size_t)c->n_pad;
+        const size_t bytes = peer_bytes(c->peer_cap, c->peer_cap_atoms);
+        CU(cudaMalloc(&c->peer_local, bytes));
+        CU(cudaMemset(c->peer_local, 0, bytes));
+        for (Ctx* o : lead->group) {
+            if (o == c) continue;
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled)
+                cudaGetLastError();
+            else if (e != cudaSuccess) {
+                cudaGetLastError();
+                FAIL(13, "cudaDeviceEnablePeerAccess failed: the GPUs of a group must reach each other over NVLink / PCIe P2P");
+            }
+        }
+    }
+    for (Ctx* c : lead->group) {
+        if (!c->use_sym) continue;
+        for (Ctx* o : lead->group) c->peer_base[o->rank] = o->peer_local;
+        memset(c->peer_seq, 0, sizeof(c->peer_seq));
+        c->peer_ipc = false;
+        c->peer_ready = true;
+    }
+    CU(cudaSetDevice(lead->device));
     return 0;
 }
 
@@ -1944,8 +2179,62 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
     return 0;
 }
 
+// One process driving `ndev` GPUs of one NVLink / NVSwitch box: rank i of the sharded evaluation lives
+// on devices[i]; the returned context is rank 0 and leads the group -- set_params / set_atoms / set_positions / energy /
+// polar / get_atom_arrays on it address the whole group, so a caller (the drop-in shim) needs no other change.
+int mpmc_b200_create_group(mpmc_b200_ctx** out, int ndev, const int* devices) {
+    if (!out) FAIL(1, "null ctx pointer");
+    *out = nullptr;
+    if (ndev < 1 || ndev > PEER_MAX) FAIL(1, "a group has 1..8 devices");
+    if (ndev == 1) return mpmc_b200_create(out, devices ? devices[0] : 0);
+    for (int i = 0; i < ndev; i++)
+        for (int j = 0; j < i; j++)
+            if ((devices ? devices[i] : i) == (devices ? devices[j] : j)) FAIL(1, "a device appears twice in the group");
+    std::vector<mpmc_b200_ctx*> g;
+    for (int i = 0; i < ndev; i++) {
+        mpmc_b200_ctx* m = nullptr;
+        const int rc = mpmc_b200_create(&m, devices ? devices[i] : i);
+        if (rc) {
+            const std::string keep = g_err;
+            for (mpmc_b200_ctx* x : g) mpmc_b200_destroy(x);
+            g_err = keep;
+            return rc;
+        }
+        m->rank = i;
+        m->world = ndev;
+        m->group_member = i > 0;
+        g.push_back(m);
+    }
+    for (int i = 0; i < ndev; i++)
+        for (int j = 0; j < ndev; j++) {
+            int can = 1;
+            if (i != j) cudaDeviceCanAccessPeer(&can, g[i]->device, g[j]->device);
+            if (!can) {
+                for (mpmc_b200_ctx* x : g) {
+                    x->group_member = false;
+                    mpmc_b200_destroy(x);
+                }
+                FAIL(13, "the GPUs of a group must have peer access to each other (NVLink / NVSwitch)");
+            }
+        }
+    g[0]->group = g;
+    cudaSetDevice(g[0]->device);
+    *out = g[0];
+    return 0;
+}
+
+int mpmc_b200_group_size(mpmc_b200_ctx* c) { return !c ? 0 : c->group.empty() ? 1 : (int)c->group.size(); }
+
 void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     if (!c) return;
+    if (!c->group.empty()) {  // a group leader owns the other ranks' contexts
+        std::vector<mpmc_b200_ctx*> members(c->group.begin() + 1, c->group.end());
+        c->group.clear();
+        for (mpmc_b200_ctx* m : members) {
+            m->group_member = false;
+            mpmc_b200_destroy(m);
+        }
+    }
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->side) {
@@ -2008,6 +2297,17 @@ int mpmc_b200_set_stream(mpmc_b200_ctx* c, void* cuda_stream) {
 
 int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
     if (!c || !p) FAIL(1, "null argument");
+    if (c->group.size() > 1) {  // the same options on every rank of the group
+        if (check_supported(*p)) return 3;
+        std::vector<mpmc_b200_ctx*> g;
+        g.swap(c->group);
+        int rc = 0;
+        for (mpmc_b200_ctx* m : g)
+            if (!rc) rc = mpmc_b200_set_params(m, p);
+        c->group.swap(g);
+        if (!rc && c->have_atoms) rc = group_connect(c);
+        return rc;
+    }
     const bool repack_needed = c->have_atoms && (p->damp_type != c->P.damp_type || p->polar_gs != c->P.polar_gs ||
                                                   p->polar_gs_ranked != c->P.polar_gs_ranked ||
                                                   p->polar_ewald_full != c->P.polar_ewald_full ||
@@ -2034,6 +2334,16 @@ int mpmc_b200_set_atoms(mpmc_b200_ctx* c, int n, const double* pos, const double
     if (n < 0 || (n > 0 && (!pos || !charge || !polarizability || !epsilon || !sigma || !mol_mass || !mol_id || !frozen)))
         FAIL(1, "bad atom arrays");
     if (n > CULL_MAX_BATCHES * 32 * 32 - 4096) FAIL(3, "more than ~2M atoms: raise CULL_MAX_BATCHES (common.cuh)");
+    if (c->group.size() > 1) {  // every rank holds the whole system (the work is sharded, not the atoms)
+        std::vector<mpmc_b200_ctx*> g;
+        g.swap(c->group);
+        int rc = 0;
+        for (mpmc_b200_ctx* m : g)
+            if (!rc) rc = mpmc_b200_set_atoms(m, n, pos, charge, polarizability, epsilon, sigma, mol_mass, mol_id, frozen);
+        c->group.swap(g);
+        if (!rc) rc = group_connect(c);
+        return rc;
+    }
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     c->n = n;
@@ -2061,6 +2371,16 @@ int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double
     if (!c->have_atoms) FAIL(2, "mpmc_b200_set_atoms has not been called");
     if (first < 0 || count < 0 || first + count > c->n) FAIL(1, "position range out of bounds");
     if (count == 0) return 0;
+    if (c->group.size() > 1) {
+        std::vector<mpmc_b200_ctx*> g;
+        g.swap(c->group);
+        int rc = 0;
+        for (mpmc_b200_ctx* m : g)
+            if (!rc) rc = mpmc_b200_set_positions(m, first, count, pos);
+        c->group.swap(g);
+        CU(cudaSetDevice(c->device));
+        return rc;
+    }
     CU(cudaSetDevice(c->device));
     if (c->h_stage_cap < (size_t)3 * count) {
         if (c->h_stage) {
@@ -2125,6 +2445,7 @@ int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double
 int mpmc_b200_set_shard(mpmc_b200_ctx* c, int rank, int world) {
     if (!c) FAIL(1, "null ctx");
     if (world < 1 || rank < 0 || rank >= world) FAIL(1, "bad shard");
+    if (!c->group.empty() || c->group_member) FAIL(2, "the ranks of a group are fixed by mpmc_b200_create_group");
     const bool changed = (world != c->world);
     if (changed || rank != c->rank) peer_teardown(c);  // the exchange buffers belong to the old shard layout
     c->rank = rank;
@@ -2217,7 +2538,13 @@ static int incremental_energy(Ctx* c, mpmc_b200_energies* out) {
 
 int mpmc_b200_energy(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
     if (!c || !out) FAIL(1, "null argument");
-    if (c->world > 1) FAIL(2, "sharded contexts are driven with mpmc_b200_energy_enqueue / mpmc_b200_polar_stage");
+    if (c->world > 1) {  // sharded: the whole staged evaluation inside the library, exchanges over peer memory
+        Ctx* cs[PEER_MAX];
+        const int nl = local_ranks(c, cs);
+        if (nl > 1 || peer_active(c)) return sharded_eval(cs, nl, true, out);
+        FAIL(2, "sharded context without the peer exchange: call mpmc_b200_peer_export / _connect, or drive the stages "
+                "with mpmc_b200_energy_enqueue / mpmc_b200_polar_stage and your own collectives");
+    }
     static const int refresh = [] { const char* v = getenv("MPMC_B200_INCREMENTAL_REFRESH"); return v ? atoi(v) : 256; }();
     if (c->inc_valid && inc_supported(c) && !c->kdirty && !c->analytic_dirty && c->inc_since_full < refresh) {
         const int rc = incremental_energy(c, out);
@@ -2256,10 +2583,17 @@ int mpmc_b200_set_incremental(mpmc_b200_ctx* c, int on) {
 
 int mpmc_b200_polar(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
     if (!c || !out) FAIL(1, "null argument");
-    if (c->world > 1) FAIL(2, "sharded contexts are driven with mpmc_b200_polar_stage");
-    int rc = enqueue_energy(c, false, true);
-    if (rc) return rc;
-    rc = finish_energy(c, out);
+    int rc;
+    if (c->world > 1) {
+        Ctx* cs[PEER_MAX];
+        const int nl = local_ranks(c, cs);
+        if (!(nl > 1 || peer_active(c))) FAIL(2, "sharded context without the peer exchange (see mpmc_b200_energy)");
+        rc = sharded_eval(cs, nl, false, out);
+    } else {
+        rc = enqueue_energy(c, false, true);
+        if (rc) return rc;
+        rc = finish_energy(c, out);
+    }
     if (!rc) {
         out->rd = out->rd_pair = out->rd_lrc = out->coulombic = out->es_real = out->es_recip = out->es_self = 0.0;
         out->total = out->polar;
@@ -2339,8 +2673,10 @@ int mpmc_b200_peer_export(mpmc_b200_ctx* c, unsigned char* handle64) {
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     peer_teardown(c);
+    if (!c->group.empty() || c->group_member) FAIL(2, "the ranks of a group are wired by the library itself");
     c->peer_cap = (size_t)c->pol.n_pad;
-    const size_t bytes = peer_bytes(c->peer_cap);
+    c->peer_cap_atoms = (size_t)c->n_pad;
+    const size_t bytes = peer_bytes(c->peer_cap, c->peer_cap_atoms);
     CU(cudaMalloc(&c->peer_local, bytes));
     CU(cudaMemset(c->peer_local, 0, bytes));
     cudaIpcMemHandle_t h;
@@ -2365,12 +2701,14 @@ int mpmc_b200_peer_connect(mpmc_b200_ctx* c, int world, const unsigned char* han
         void* p = nullptr;
         if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
             cudaGetLastError();
+            c->peer_ipc = true;  // close the handles opened so far
             peer_teardown(c);
             FAIL(13, "cudaIpcOpenMemHandle failed (no peer access between the ranks' GPUs?)");
         }
         c->peer_base[r] = p;
     }
-    c->peer_seq = 0;
+    memset(c->peer_seq, 0, sizeof(c->peer_seq));
+    c->peer_ipc = true;
     c->peer_ready = true;
     return 0;
 }
@@ -2415,8 +2753,8 @@ int mpmc_b200_shard_rows(mpmc_b200_ctx* c, int* begin, int* end, int* n_pol, int
     return 0;
 }
 
-int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, double* ef_induced,
-                              double* ef_induced_change, double* dipole_rrms, double* rank_metric) {
+// what polar() leaves in atom_t, assembled on the device in the caller's layout -> the pinned host image c->h_wb
+static int fetch_atom_arrays(mpmc_b200_ctx* c) {
     if (!c) FAIL(1, "null ctx");
     if (!c->have_atoms) FAIL(2, "no atoms");
     CU(cudaSetDevice(c->device));
@@ -2441,6 +2779,21 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
         CU(cudaMallocHost(&c->h_wb, sizeof(double) * c->h_wb_cap));
     }
     cudaStream_t st = c->stream;
+    if (c->group.size() > 1 && c->eic_np_valid && c->nonpol.n > 0) {
+        // palmo rows of the non-polarizable atoms (write-back only) are computed tile range by tile range across the
+        // ranks: fetch the other ranks' ranges over the peer link (their streams were synchronised by finish_energy)
+        const int qp = c->nonpol.n_pad;
+        for (size_t r = 1; r < c->group.size(); r++) {
+            mpmc_b200_ctx* o = c->group[r];
+            int tb, te;
+            shard_range(qp / TILE, o->rank, o->world, tb, te);
+            if (te <= tb) continue;
+            for (int d = 0; d < 3; d++)
+                CU(cudaMemcpyPeerAsync(c->eic_np.p + (size_t)d * qp + (size_t)tb * TILE, c->device,
+                                       o->eic_np.p + (size_t)d * qp + (size_t)tb * TILE, o->device,
+                                       sizeof(double) * (size_t)(te - tb) * TILE, st));
+        }
+    }
     CU(cudaMemsetAsync(c->wb.p, 0, sizeof(double) * total, st));
     const int m = std::max(n, std::max(c->pol.n, c->nonpol.n));
     writeback_kernel<<<(m + 255) / 256, 256, 0, st>>>(
@@ -2450,6 +2803,14 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(c->h_wb, c->wb.p, sizeof(double) * total, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, double* ef_induced,
+                              double* ef_induced_change, double* dipole_rrms, double* rank_metric) {
+    if (const int rc = fetch_atom_arrays(c)) return rc;
+    const int n = c->n;
+    if (n <= 0) return 0;
     const double* h = c->h_wb;
     if (mu) memcpy(mu, h, sizeof(double) * 3 * n);
     if (ef_static) memcpy(ef_static, h + 3 * (size_t)n, sizeof(double) * 3 * n);
@@ -2457,6 +2818,20 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx* c, double* mu, double* ef_static, d
     if (ef_induced_change) memcpy(ef_induced_change, h + 9 * (size_t)n, sizeof(double) * 3 * n);
     if (dipole_rrms) memcpy(dipole_rrms, h + 12 * (size_t)n, sizeof(double) * n);
     if (rank_metric) memcpy(rank_metric, h + 13 * (size_t)n, sizeof(double) * n);
+    return 0;
+}
+
+int mpmc_b200_atom_arrays_view(mpmc_b200_ctx* c, const double** mu, const double** ef_static, const double** ef_induced,
+                               const double** ef_induced_change, const double** dipole_rrms, const double** rank_metric) {
+    if (const int rc = fetch_atom_arrays(c)) return rc;
+    const size_t n = (size_t)c->n;
+    const double* h = c->h_wb;
+    if (mu) *mu = h;
+    if (ef_static) *ef_static = h + 3 * n;
+    if (ef_induced) *ef_induced = h + 6 * n;
+    if (ef_induced_change) *ef_induced_change = h + 9 * n;
+    if (dipole_rrms) *dipole_rrms = h + 12 * n;
+    if (rank_metric) *rank_metric = h + 13 * n;
     return 0;
 }
 

@@ -668,10 +668,9 @@ int launch_dipole_sf(const Cell& c, const SubsetDev& pol, const KVecDev& kv, con
             const size_t tables = sizeof(double) * (2 * SG_ATOMS * 3 * nl + 3 * SG_ATOMS);
             const size_t stage = sizeof(double) * 2 * SG_MAXD * gthreads;
             const size_t smem = tables > stage ? tables : stage;
-            static bool attr_set_g = false;
-            if (!attr_set_g) {
+            static unsigned long long attr_set_g = 0;
+            if (first_on_device(attr_set_g)) {
                 cudaFuncSetAttribute(dipole_sf_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-                attr_set_g = true;
             }
             dipole_sf_grouped_kernel<<<nchunks, gthreads * SG_SUB, smem, s>>>(c, pol, kv.nk, nl, kg->ngroups, gthreads, kg->groups, mu,
                                                                              atoms_per_chunk, sf_partial);
@@ -679,10 +678,9 @@ int launch_dipole_sf(const Cell& c, const SubsetDev& pol, const KVecDev& kv, con
         }
     }
     const size_t smem = sizeof(double) * (6 * (kv.kmax + 1) * DS_ATOMS + 3 * DS_ATOMS);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0;
+    if (first_on_device(attr_set)) {
         cudaFuncSetAttribute(dipole_sf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
     }
     dipole_sf_kernel<<<nchunks, DS_THREADS, smem, s>>>(c, pol, kv, kvec, mu, atoms_per_chunk, sf_partial);
     return nchunks;
@@ -697,10 +695,9 @@ void launch_induced_finish(const Cell& c, const SubsetDev& rows, const KVecDev& 
                            double* out, cudaStream_t s) {
     if (rows.n_pad <= 0) return;
     const size_t smem = sizeof(double) * (6 * (kv.kmax + 1) * FIN_TILE + 2 * (size_t)kv.nk) + sizeof(int) * kv.nk;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0;
+    if (first_on_device(attr_set)) {
         cudaFuncSetAttribute(induced_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
     }
     const double scale = 8.0 * M_PI / c.volume;                            // :266
     const double surf = -4.0 * M_PI / (3.0 * c.volume);                    // :314

@@ -157,6 +157,12 @@ struct PeerWait {               // consumer side (dipole_update_peer_kernel, pal
     const double* src[PEER_MAX];         // src[r] = rank r's partial field [3][n_pad] (peer pointer)
     double* timeout_flag;                // set to 1.0 if a peer never signalled (host turns it into an error)
 };
+// The same flag protocol for the other two exchanges of a sharded evaluation (engine.cu: sharded_eval):
+// out[i] = sum over ranks of src[r][i], i < n (static field rows: one owner per row, zero elsewhere => an all-gather)
+void launch_peer_signal(const PeerSignal& sig, cudaStream_t s);
+void launch_peer_sum(const PeerWait& pw, size_t n, double* out, cudaStream_t s);
+// the evaluation's device scalars: sums over ranks, slot min_slot the minimum; n <= 64
+void launch_peer_scalars(const PeerWait& pw, int n, int min_slot, double* out, cudaStream_t s);
 int dipole_sym_tile();  // atoms per super tile (256): n_pad of the polarizable subset must be a multiple
 int dipole_sym_partial_rows(int n_pad);
 void launch_cluster_boxes(const Cell& c, bool ortho, const SubsetDev& pol, double* cbox, cudaStream_t s);

@@ -190,10 +190,9 @@ void launch_recip_sf(const Cell& c, const SubsetDev& atoms, const KVecDev& kv, i
     const int n = chunk_end - chunk_begin;
     if (n <= 0) return;
     const size_t smem = sizeof(double) * (6 * (kv.kmax + 1) * RC_ATOMS + RC_ATOMS);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0;
+    if (first_on_device(attr_set)) {
         cudaFuncSetAttribute(recip_sf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
     }
     recip_sf_kernel<<<n, RC_THREADS, smem, s>>>(c, atoms, kv, chunk_begin, atoms_per_chunk, sf_partial);
 }
@@ -249,10 +248,9 @@ void launch_recip_field(const Cell& c, const AtomsDev& a, const KVecDev& kv, con
     const int rows = row_end - row_begin;
     if (rows <= 0) return;
     const size_t smem = sizeof(double) * 6 * (kv.kmax + 1) * TILE;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0;
+    if (first_on_device(attr_set)) {
         cudaFuncSetAttribute(recip_field_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
     }
     recip_field_kernel<<<(rows + TILE - 1) / TILE, TILE, smem, s>>>(c, a, kv, kvec, sf, scale, row_begin, row_end, ef);
 }

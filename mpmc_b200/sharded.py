@@ -3,7 +3,7 @@
 
 What is split (BASELINE north_star):
   * pair tiles of the LJ + Ewald-real kernel and the atom chunks of the structure factor
-    -> partial scalars, summed over ranks at the end (one all-reduce of 12 doubles);
+    -> partial scalars, summed over ranks at the end;
   * static-field rows (thole_field, reference src/polarization/thole_field.c:14-36), by spatial cluster
     -> one all-reduce(sum) of the field (each row is written by exactly one rank, zero elsewhere);
   * the tile pairs of every solver pass (contract_dipoles, src/polarization/thole_iterative.c:27-59):
@@ -15,6 +15,12 @@ What is split (BASELINE north_star):
     (With the row-by-row contraction, MPMC_B200_K4=rows, rows are owned instead: an all-gather of
     the new dipole rows after every pass plus an all-reduce(max) of the residual.)
 Gauss-Seidel modes are sequential in atom order and stay on one GPU.
+
+Default since round 2: once the ranks have exchanged the CUDA-IPC handles of their exchange buffers (``_connect_peers``,
+the only use of ``torch.distributed`` on this path) ``energy()`` is ONE call into the library -- the staged loop below
+lives in ``engine.cu:sharded_eval`` and every exchange is a kernel of the engine reading peer memory.  The Python staging
+with NCCL collectives remains as the fallback / A-B switch (``MPMC_B200_PEER=0`` or ``MPMC_B200_STAGED=1``) and is what
+the gloo tests exercise on the CPU.
 
 The collectives are issued by ``Exchange`` on the same CUDA stream as the engine's kernels, so no
 host synchronisation separates a pass from its exchange.  ``Exchange`` only needs ``all_gather``
@@ -132,8 +138,7 @@ class ShardedEngine:
         eng = self.eng
         if self.world == 1 or not hasattr(eng, "peer_export") or os.environ.get("MPMC_B200_PEER", "1") == "0":
             return
-        p = self.system.params
-        if not (p.polarization and not p.rd_only and eng.uses_symmetric_contraction()) or self.world > 8:
+        if not eng.uses_symmetric_contraction() or self.world > 8:
             return
         import torch.distributed as dist
 
@@ -166,9 +171,19 @@ class ShardedEngine:
         return self._energy_sharded()
 
     def _energy_sharded(self) -> Energies:
+        import os
+
         import torch
 
         eng, p = self.eng, self.system.params
+        if bool(getattr(eng, "peer_active", lambda: False)()) and os.environ.get("MPMC_B200_STAGED", "0") != "1":
+            # The whole staged evaluation inside the library (engine.cu: sharded_eval): static-field rows, the induced
+            # field of every pass and the final scalars are exchanged by the engine's own kernels over NVLink peer
+            # memory; energies and counters come back as totals, identical on every rank.  No NCCL call at all.
+            out = eng.energy()
+            self._last_cnt = eng.counters()
+            self._launches = self._last_cnt.kernel_launches
+            return out
         eng.energy_enqueue()
         iterations, failed = 0, False
         polar = bool(p.polarization and not p.rd_only)

@@ -58,14 +58,73 @@ static void shim_shutdown(void) {
     g_ctx = NULL;
 }
 
+/* "0,1,2,3", "0-3" or a mix -> device ordinals; returns how many */
+static int shim_parse_devices(const char *spec, int *dev, int max) {
+    int n = 0;
+    const char *p = spec;
+    while (*p && n < max) {
+        char *end;
+        long a = strtol(p, &end, 10), b;
+        if (end == p) break;
+        b = a;
+        p = end;
+        if (*p == '-') {
+            b = strtol(p + 1, &end, 10);
+            if (end == p + 1) break;
+            p = end;
+        }
+        for (; a <= b && n < max; a++) dev[n++] = (int)a;
+        if (*p == ',') p++;
+    }
+    return n;
+}
+
+/* Which GPU(s) this process evaluates on:
+ *   MPMC_B200_DEVICE=k        one GPU (one MC chain per GPU: the ensemble launcher sets this per process)
+ *   MPMC_B200_DEVICES=0-7     ONE chain sharded over several GPUs of the box (static-field rows, dipole-tensor tile
+ *                             pairs of every solver pass, pair clusters and k-vectors split by rank; exchanges over
+ *                             NVLink peer memory inside the library).  MPMC_B200_GPUS=n is short for 0..n-1. */
 static void shim_init(void) {
-    int dev = 0;
+    int dev[8], ndev = 0;
     const char *env;
     if (g_ctx) return;
-    env = getenv("MPMC_B200_DEVICE"); /* one MC chain per GPU: the launcher sets this per process */
-    if (env) dev = atoi(env);
-    if (mpmc_b200_create(&g_ctx, dev)) shim_die("cannot create the CUDA context");
+    if ((env = getenv("MPMC_B200_DEVICES")) != NULL)
+        ndev = shim_parse_devices(env, dev, 8);
+    else if ((env = getenv("MPMC_B200_GPUS")) != NULL) {
+        int k, n = atoi(env);
+        for (k = 0; k < n && k < 8; k++) dev[ndev++] = k;
+    }
+    if (ndev > 1) {
+        if (mpmc_b200_create_group(&g_ctx, ndev, dev)) shim_die("cannot create the CUDA contexts of the device group");
+    } else {
+        int d = ndev == 1 ? dev[0] : 0;
+        if (ndev == 0 && (env = getenv("MPMC_B200_DEVICE")) != NULL) d = atoi(env);
+        if (mpmc_b200_create(&g_ctx, d)) shim_die("cannot create the CUDA context");
+    }
     atexit(shim_shutdown);
+}
+
+/* Host threads for the O(N) duties around a call (one pass over the lists, the scatter of the results into atom_t): the
+ * reference's data model -- 912-byte atoms allocated one by one -- makes both memory-latency bound, which threads hide.
+ * MPMC_B200_HOST_THREADS (default: up to 8 of the cores this process may run on; 1 = the single-threaded passes). */
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+static int g_threads = 0, g_threads_min = 4096; /* below this many atoms the sequential passes are faster */
+static int shim_threads(void) {
+    if (g_threads <= 0) {
+        const char *env = getenv("MPMC_B200_HOST_THREADS");
+        if (getenv("MPMC_B200_HOST_THREADS_MIN")) g_threads_min = atoi(getenv("MPMC_B200_HOST_THREADS_MIN"));
+        g_threads = 1;
+#ifdef _OPENMP
+        g_threads = env ? atoi(env) : omp_get_num_procs();
+        if (!env && g_threads > 8) g_threads = 8;
+        if (g_threads < 1) g_threads = 1;
+#else
+        (void)env;
+#endif
+    }
+    return g_threads;
 }
 
 static void *xrealloc(void *p, size_t bytes) {
@@ -185,7 +244,12 @@ static void shim_check_supported(const system_t *s) {
     if (s->dreiding) shim_unsupported("dreiding");
     if (s->lj_buffered_14_7) shim_unsupported("lj_buffered_14_7");
     if (s->disp_expansion) shim_unsupported("disp_expansion");
-    if (s->cdvdw_exp_repulsion || s->cdvdw_sig_repulsion) shim_unsupported("cdvdw repulsion");
+    /* all three change the LJ mixing inside pair_exclusions() (pairs.c:100-126) */
+    if (s->cdvdw_exp_repulsion || s->cdvdw_sig_repulsion || s->cdvdw_9th_repulsion) shim_unsupported("cdvdw repulsion");
+    /* surface() / surf_fit() evaluate lj_nopbc() / coulombic_nopbc() over atom->pairs (mc/surface.c:26-60), which this
+     * build never allocates: they would return 0.0 without a word */
+    if (s->ensemble == ENSEMBLE_SURF || s->ensemble == ENSEMBLE_SURF_FIT)
+        shim_unsupported("ensemble surf / surf_fit (potential-energy-surface scans over the pair lists)");
     if (s->gwp) shim_unsupported("gwp");
     if (s->axilrod_teller) shim_unsupported("axilrod_teller");
     if (s->spectre) shim_unsupported("spectre");
@@ -261,6 +325,7 @@ void update_com(molecule_t *molecules) {
  * remain: pointer arrays, centres of mass, wrapped coordinates.  (The GS rank metric is computed
  * on the device and written back by the evaluation.) */
 void pairs(system_t *system) {
+    shim_check_supported(system); /* also reached from surface() (mc/surface.c:26), which never calls energy() */
     system->natoms = countNatoms(system);
     rebuild_arrays(system);
     update_com(system->molecules);
@@ -269,7 +334,7 @@ void pairs(system_t *system) {
 
 /* pair-list maintenance entry points called by the MC driver (src/io/input.c:1783-1792,
  * src/mc/mc_moves.c:664-775): nothing to maintain, every atom->pairs stays NULL */
-void setup_pairs(system_t *system) { (void)system; }
+void setup_pairs(system_t *system) { shim_check_supported(system); }
 void flag_all_pairs(system_t *system) { (void)system; }
 void update_pairs_insert(system_t *system) { (void)system; }
 void update_pairs_remove(system_t *system) { (void)system; }
@@ -403,6 +468,10 @@ static molecule_t **c_mol = NULL;   /* molecules in list order */
 static atom_t **c_atom = NULL;      /* atoms in list order */
 static int *c_first = NULL;         /* index of a molecule's first atom */
 static int c_nmol = 0, c_natom = 0, c_molcap = 0, c_atomcap = 0, c_valid = 0;
+static int *t_slot = NULL;          /* threaded pass: molecule slot of atom i */
+static double *t_mass = NULL;       /* threaded pass: atom masses, contiguous */
+static double *t_shift = NULL;      /* threaded pass: [nmol][3] wrapping shift of a molecule */
+static int t_atomcap = 0, t_molcap = 0;
 
 static void shim_cache_topology(system_t *system) {
     molecule_t *m;
@@ -498,6 +567,107 @@ static int shim_resync(system_t *system, int k, molecule_t *fresh, int *resized)
     return 0;
 }
 
+/* The one pass with host threads.  Taken when the cached sequence IS the list, molecule by molecule (checked first, in
+ * order, stopping at the first relinked node, so nothing that make_move() / restore() freed is ever read); any
+ * relinking falls through to the sequential pass below, which edits the cache.  Three sweeps:
+ *   atoms      verify the atom links, copy what the hot path reads into the flat arrays (912-byte stride -> contiguous)
+ *   molecules  mass, centre of mass (pairs.c:364-385) and wrapping shift (output.c:142-183) from the contiguous copies,
+ *              summed in list order exactly as the reference does
+ *   atoms      wrapped_pos, molecule mass / index per atom, point self energies (coulombic.c:103-108)
+ * Same results as the sequential pass bit for bit (every sum keeps its order); returns the atom count or -1. */
+static int shim_threaded_pass(system_t *system, int es_on) {
+    const pbc_t *pbc = system->pbc;
+    const double self_c = system->ewald_alpha / sqrt(M_PI);
+    const int nthreads = shim_threads();
+    int k, i, bad = 0;
+    molecule_t *real = system->molecules;
+    if (nthreads <= 1 || !c_valid || c_nmol <= 0 || c_natom < g_threads_min || !system->atom_array || !system->molecule_array) return -1;
+    for (k = 0; k < c_nmol; k++) { /* the addresses come from the cache, so the loads overlap; the order keeps it safe */
+        if (real != c_mol[k]) return -1;
+        real = c_mol[k]->next;
+    }
+    if (real) return -1;
+    shim_reserve(c_natom);
+    if (c_natom > t_atomcap) {
+        t_atomcap = c_natom + c_natom / 4 + 64;
+        t_slot = (int *)xrealloc(t_slot, sizeof(int) * t_atomcap);
+        t_mass = (double *)xrealloc(t_mass, sizeof(double) * t_atomcap);
+    }
+    if (c_nmol > t_molcap) {
+        t_molcap = c_nmol + c_nmol / 4 + 64;
+        t_shift = (double *)xrealloc(t_shift, sizeof(double) * 3 * t_molcap);
+    }
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+    for (k = 0; k < c_nmol; k++) {
+        int j;
+        if (c_mol[k]->atoms != (c_first[k + 1] > c_first[k] ? c_atom[c_first[k]] : NULL)) {
+#pragma omp atomic write
+            bad = 1;
+        }
+        for (j = c_first[k]; j < c_first[k + 1]; j++) t_slot[j] = k;
+    }
+    if (bad) return -1;
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+    for (i = 0; i < c_natom; i++) {
+        const atom_t *a = c_atom[i];
+        const int last = (i + 1 == c_first[t_slot[i] + 1]);
+        if (a->next != (last ? NULL : c_atom[i + 1])) {
+#pragma omp atomic write
+            bad = 1;
+        }
+        n_pos[3 * i] = a->pos[0];
+        n_pos[3 * i + 1] = a->pos[1];
+        n_pos[3 * i + 2] = a->pos[2];
+        n_q[i] = a->charge;
+        n_alpha[i] = a->polarizability;
+        n_eps[i] = a->epsilon;
+        n_sig[i] = a->sigma;
+        n_frozen[i] = a->frozen;
+        n_mol[i] = t_slot[i];
+        t_mass[i] = a->mass;
+    }
+    if (bad) return -1;
+#pragma omp parallel for schedule(dynamic, 64) num_threads(nthreads)
+    for (k = 0; k < c_nmol; k++) {
+        molecule_t *m = c_mol[k];
+        const int b = c_first[k], e = c_first[k + 1];
+        double com[3] = {0, 0, 0}, mass = 0, dimg[3] = {0, 0, 0}, d[3];
+        int j, p, q;
+        for (j = b; j < e; j++) {
+            mass += t_mass[j];
+            for (p = 0; p < 3; p++) com[p] += t_mass[j] * n_pos[3 * j + p];
+        }
+        for (p = 0; p < 3; p++) m->com[p] = 0; /* update_com(): pairs.c:364-385 */
+        if (!(m->spectre || m->target)) {
+            m->mass = mass;
+            for (p = 0; p < 3; p++) m->com[p] = com[p] / mass;
+        }
+        if (!m->frozen) { /* wrapall(): output.c:142-183 */
+            for (p = 0; p < 3; p++) {
+                for (q = 0, d[p] = 0; q < 3; q++) d[p] += pbc->reciprocal_basis[q][p] * m->com[q];
+                d[p] = rint(d[p]);
+            }
+            for (p = 0; p < 3; p++) {
+                for (q = 0, dimg[p] = 0; q < 3; q++) dimg[p] += pbc->basis[q][p] * d[q];
+                m->wrapped_com[p] = dimg[p];
+            }
+        }
+        for (p = 0; p < 3; p++) t_shift[3 * k + p] = dimg[p];
+    }
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+    for (i = 0; i < c_natom; i++) {
+        atom_t *a = c_atom[i];
+        const int ks = t_slot[i];
+        const molecule_t *m = c_mol[ks];
+        int p;
+        for (p = 0; p < 3; p++) a->wrapped_pos[p] = m->frozen ? n_pos[3 * i + p] : n_pos[3 * i + p] - t_shift[3 * ks + p];
+        n_mmass[i] = m->mass;
+        if (es_on && !n_frozen[i]) a->es_self_point_energy = self_c * n_q[i] * n_q[i]; /* coulombic.c:103-108 */
+    }
+    system->natoms = c_natom;
+    return c_natom;
+}
+
 /* returns the atom count when the cached sequence still is the list (everything done), -1 otherwise */
 static int shim_fast_pass(system_t *system, int es_on) {
     const pbc_t *pbc = system->pbc;
@@ -577,6 +747,28 @@ static void shim_write_back_atoms(system_t *system) {
     molecule_t *m;
     atom_t *a;
     int n = 0, p;
+    if (c_valid && c_natom == system->natoms && shim_threads() > 1 && c_natom >= g_threads_min) {
+        /* straight from the library's pinned host image into atom_t, with the host threads (the sequence was checked
+         * -- or rebuilt -- by shim_prepare() of this call) */
+        const double *v_mu, *v_es, *v_ei, *v_eic, *v_rrms, *v_rank;
+        const int ranked = system->polar_gs_ranked, nthreads = shim_threads();
+        int i;
+        if (mpmc_b200_atom_arrays_view(g_ctx, &v_mu, &v_es, &v_ei, &v_eic, &v_rrms, &v_rank)) shim_die("atom_arrays_view");
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+        for (i = 0; i < c_natom; i++) {
+            atom_t *t = c_atom[i];
+            int pp;
+            for (pp = 0; pp < 3; pp++) {
+                t->mu[pp] = v_mu[3 * i + pp];
+                t->ef_static[pp] = v_es[3 * i + pp];
+                t->ef_induced[pp] = v_ei[3 * i + pp];
+                t->ef_induced_change[pp] = v_eic[3 * i + pp];
+            }
+            t->dipole_rrms = v_rrms[i];
+            if (ranked) t->rank_metric = v_rank[i];
+        }
+        return;
+    }
     if (mpmc_b200_get_atom_arrays(g_ctx, w_mu, w_es, w_ei, w_eic, w_rrms, system->polar_gs_ranked ? w_rank : NULL))
         shim_die("get_atom_arrays");
     if (c_valid && c_natom == system->natoms) { /* the sequence was checked (or rebuilt) by shim_prepare() of this call */
@@ -657,7 +849,8 @@ static void shim_prepare(system_t *system, int es_on) {
     if (fast < 0) fast = getenv("MPMC_B200_SHIM_SLOW") ? 0 : 1; /* MPMC_B200_SHIM_SLOW=1: always the reference-shaped walks */
     shim_timing_init();
     if (t_on) t0 = shim_now();
-    n = fast ? shim_fast_pass(system, es_on) : -1;
+    n = fast ? shim_threaded_pass(system, es_on) : -1;
+    if (n < 0 && fast) n = shim_fast_pass(system, es_on);
     if (n >= 0) t_fast++;
     if (n >= 0) { /* MPMC_B200_SHIM_CHECK=1 (tests): the one-pass result against a real walk of the lists */
         static int check = -1;

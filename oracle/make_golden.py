@@ -298,6 +298,50 @@ def gen_traj_synth(name):
     print(f"{name}: {len(en)} energy rows")
 
 
+# n2 (north_star: "ensemble averages and uptake of the sample MOF runs must agree"): the shipped PCN-61 + H2 uVT input
+# (sample_configs_gpu/3_PCN61/iter.inp, all of its options) on the largest part of the system the reference can hold --
+# the framework + the first 500 H2 (8,548 atoms, ~13 GB) -- for 100 fixed-seed steps: every energy row AND the
+# `OUTPUT:` averages block the reference prints at each corrtime (N, wt %, excess ratio, <U>, <U_pol>, qst, AR ...).
+def gen_traj_pcn61():
+    src = os.path.join(REF, PCN61)
+    lines = [l for l in open(os.path.join(src, "input.pdb")).read().splitlines() if l.startswith("ATOM")]
+    keep, mols = [], []
+    for l in lines:
+        t = l.split()
+        if t[4] != "F":
+            if t[5] not in mols:
+                if len(mols) >= 500:
+                    continue
+                mols.append(t[5])
+        keep.append(l)
+    inp = open(os.path.join(src, "iter.inp")).read()
+    inp = inp.replace("numsteps\t\t4", "numsteps\t\t100").replace("corrtime\t\t2", "corrtime\t\t10")
+    assert "numsteps\t\t100" in inp and "corrtime\t\t10" in inp
+    inp += "\npreset_seeds 20261105\n"
+    with tempfile.TemporaryDirectory() as td:
+        with open(os.path.join(td, "input.pdb"), "w") as f:
+            f.write("\n".join(keep) + "\nEND\n")
+        with open(os.path.join(td, "input"), "w") as f:
+            f.write(inp)
+        r = subprocess.run([oracle.REF_BINARY, "input"], cwd=td, capture_output=True, text=True, timeout=6 * 3600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        en = [l for l in open(os.path.join(td, "RHT+BSSP.energy.dat")).read().splitlines() if not l.startswith("#")]
+        final = open(os.path.join(td, "RHT+BSSP.final.pdb")).read()
+        dip = open(os.path.join(td, "RHT+BSSP.dipole.dat")).read() if os.path.exists(os.path.join(td, "RHT+BSSP.dipole.dat")) else ""
+    out_lines = [l for l in r.stdout.splitlines() if l.startswith("OUTPUT:") and "sec/step" not in l and "collecting statistics" not in l]
+    import gzip
+    import base64
+
+    pack = lambda t: base64.b64encode(gzip.compress(t.encode(), 9)).decode()
+    with open(os.path.join(GOLD, "traj_pcn61_uvt.json"), "w") as f:
+        json.dump({"input": inp, "pqr_name": "input.pdb", "pqr_gz_b64": pack("\n".join(keep) + "\nEND\n"), "energy_rows": en,
+                   "final_gz_b64": pack(final), "dipole_tail": dip.splitlines()[-3:], "output_lines": out_lines,
+                   "energy_file": "RHT+BSSP.energy.dat", "final_file": "RHT+BSSP.final.pdb",
+                   "source": f"{PCN61}/iter.inp + framework and the first 500 H2 of input.pdb; numsteps 100, corrtime 10, "
+                             "preset_seeds 20261105; unmodified reference (oracle/_ref/mpmc_ref)"}, f, indent=0)
+    print(f"traj_pcn61_uvt: {len(en)} energy rows, {len(out_lines)} OUTPUT lines")
+
+
 def main():
     oracle.build()
     want = set(sys.argv[1:])
@@ -327,6 +371,8 @@ def main():
         if want and name not in want:
             continue
         gen_traj_synth(name)
+    if "traj_pcn61_uvt" in want:  # ~30 minutes of the reference on one core: only on request
+        gen_traj_pcn61()
 
 
 if __name__ == "__main__":

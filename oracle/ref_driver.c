@@ -8,9 +8,11 @@
  * (src/energy/energy.c:67) and prints every input the hot path reads and every
  * output it writes with %.17g, so that golden fixtures carry all 53 bits.
  *
- * usage: ref_driver <mpmc input file> [repeat [warmup]]
+ * usage: ref_driver <mpmc input file> [repeat [warmup [flags]]]
  *   repeat > 1 re-evaluates energy() that many times (after `warmup` untimed calls) and
  *   reports seconds per call (CPU baseline timing of the real reference).
+ *   flags: a string of letters -- q: no per-atom lines in the snapshot (timing runs of large systems);
+ *          n: call energy_no_observables() (src/energy/energy.c:232-318) instead of energy().
  * Output goes to stdout after the marker line "MPMC_SNAPSHOT 1"; the
  * reference's own chatter goes to stdout before it / stderr.
  */
@@ -43,7 +45,7 @@ static void p3x3(const char *name, double m[3][3]) {
 
 int main(int argc, char **argv) {
     system_t *s;
-    int repeat = 1, warmup = 0, i, n, molidx;
+    int repeat = 1, warmup = 0, i, n, molidx, quiet = 0, no_obs = 0;
     double e = 0, t0, t1;
     molecule_t *m;
     atom_t *a;
@@ -54,6 +56,10 @@ int main(int argc, char **argv) {
     }
     if (argc > 2) repeat = atoi(argv[2]);
     if (argc > 3) warmup = atoi(argv[3]);
+    if (argc > 4) {
+        quiet = strchr(argv[4], 'q') != NULL;
+        no_obs = strchr(argv[4], 'n') != NULL;
+    }
     if (repeat < 1) repeat = 1;
     rank = 0;
     size = 1;
@@ -83,7 +89,7 @@ int main(int argc, char **argv) {
                 ;
             for (a = m->atoms; a; a = a->next) a->pos[0] += (i & 1) ? 1e-3 : -1e-3;
         }
-        e = energy(s);
+        e = no_obs ? energy_no_observables(s) : energy(s);
     }
     t1 = now_s();
 
@@ -161,7 +167,7 @@ int main(int argc, char **argv) {
         for (a = m->atoms; a; a = a->next) n++;
     printf("natoms %d\n", n);
     molidx = 0;
-    for (m = s->molecules; m; m = m->next, molidx++) {
+    for (m = s->molecules; m && !quiet; m = m->next, molidx++) {
         for (a = m->atoms; a; a = a->next) {
             printf("atom %d %d", molidx, a->frozen);
             printf(" %.17g %.17g %.17g", a->pos[0], a->pos[1], a->pos[2]);

@@ -1,6 +1,6 @@
 /* tests/hoststub/abi_over_oracle.c -- TEST INFRASTRUCTURE ONLY, never part of the product.
  *
- * The nine C-ABI entry points the drop-in shim calls (include/mpmc_b200.h), answered by the CPU oracle
+ * The C-ABI entry points the drop-in shim calls (include/mpmc_b200.h), answered by the CPU oracle
  * (oracle/mpmc_oracle.c) instead of the CUDA engine.  Linked with the shim's own objects into
  * tests/hoststub/_build/mpmc_hoststub so that the HOST logic of mpmc_b200/shim/energy_shim.c -- the list walks and the
  * cached-sequence pass, change detection, uVT relinking, the observables epilogue, the write-back into atom_t -- is
@@ -36,6 +36,15 @@ int mpmc_b200_create(mpmc_b200_ctx **ctx, int device) {
     *ctx = (mpmc_b200_ctx *)calloc(1, sizeof(mpmc_b200_ctx));
     return *ctx ? 0 : 11;
 }
+
+/* a "group" on the host stand-in is one context: what is under test is the shim's parsing of MPMC_B200_DEVICES */
+static int g_group = 1;
+int mpmc_b200_create_group(mpmc_b200_ctx **ctx, int ndev, const int *devices) {
+    (void)devices;
+    g_group = ndev;
+    return mpmc_b200_create(ctx, 0);
+}
+int mpmc_b200_group_size(mpmc_b200_ctx *c) { return c ? g_group : 0; }
 
 void mpmc_b200_destroy(mpmc_b200_ctx *c) {
     if (!c) return;
@@ -104,5 +113,16 @@ int mpmc_b200_get_atom_arrays(mpmc_b200_ctx *c, double *mu, double *ef_static, d
     if (ef_induced_change) memcpy(ef_induced_change, c->eic, sizeof(double) * 3 * n);
     if (dipole_rrms) memcpy(dipole_rrms, c->rrms, sizeof(double) * n);
     if (rank_metric) memcpy(rank_metric, c->rank, sizeof(double) * n);
+    return 0;
+}
+
+int mpmc_b200_atom_arrays_view(mpmc_b200_ctx *c, const double **mu, const double **ef_static, const double **ef_induced,
+                               const double **ef_induced_change, const double **dipole_rrms, const double **rank_metric) {
+    if (mu) *mu = c->mu;
+    if (ef_static) *ef_static = c->es;
+    if (ef_induced) *ef_induced = c->ei;
+    if (ef_induced_change) *ef_induced_change = c->eic;
+    if (dipole_rrms) *dipole_rrms = c->rrms;
+    if (rank_metric) *rank_metric = c->rank;
     return 0;
 }

@@ -24,6 +24,9 @@ def main():
     cases = []
     s = systems.mof_h2(cells=(3, 3, 2))
     cases.append(("mof_jacobi10", s))
+    # BASELINE config 3 shape at full size (21,519 atoms, ~15k polarizable: the peer exchange at the item granularity of
+    # the real runs); also held to its oracle-made pin below
+    cases.append(("mof_h2_21k", systems.mof_h2(cells=(9, 3, 3), polar_max_iter=4)))
     s = systems.h2_fluid(4000)
     s.params.polar_max_iter, s.params.polar_precision, s.params.polar_palmo, s.params.polar_rrms = 0, 1e-6, 1, 1
     cases.append(("h2_precision_palmo_rrms", s))
@@ -79,6 +82,16 @@ def main():
                 if not err <= 1e-11:
                     print(f"[rank {rank}] {name} {k}: max err {err:.3e}", flush=True)
                     ok = False
+        if name == "mof_h2_21k":
+            from mpmc_b200 import pins
+
+            pin = pins.load("pin_mof_h2_21k")
+            dev = pins.deviation(pin, got.to_dict(), arr)
+            if pins.check_inputs(pin, s) or not dev["iterations_equal"] or not dev["max"] <= 1e-10:
+                print(f"[rank {rank}] {name}: deviates from its pin: {dev}", flush=True)
+                ok = False
+            elif rank == 0:
+                print(f"case {name}: max deviation from the oracle-made pin {dev['max']:.2e}", flush=True)
         eng.close()
         if rank == 0:
             print(f"case {name}: E={got.total!r} iterations={got.polar_iterations}", flush=True)

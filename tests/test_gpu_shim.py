@@ -64,17 +64,67 @@ def test_dropin_energy_matches_reference_fixture(name, tmp_path):
         gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label=name)
 
 
-@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "incremental", "warm_start"])
-@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt", "traj_co2_uvt"])
+@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "incremental", "warm_start", "threaded"])
+@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt", "traj_co2_uvt", "traj_co2_npt"])
 def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     """host_path: the shim's one-pass O(N) duties over the cached pointer sequence (default; every relinking of the
-    lists -- uVT insert / remove, rejected moves -- must be detected) or the reference-shaped list walks."""
+    lists -- uVT insert / remove, rejected moves -- must be detected; MPMC_B200_SHIM_CHECK=1 compares the pass with a real
+    list walk after every call), the reference-shaped list walks, or the pass and the scatter with host threads.
+    traj_co2_npt: volume moves change the cell, the cutoff, alpha and the k-vectors every step (mc_moves.c:168-232)."""
     _need(PROGRAM)
-    env = {}
+    env = {"MPMC_B200_HOST_THREADS": "1"}
+    if host_path == "cached_sequence":
+        env["MPMC_B200_SHIM_CHECK"] = "1"
     if host_path == "list_walks":
         env["MPMC_B200_SHIM_SLOW"] = "1"
     if host_path == "incremental":  # SURVEY 8f f2 (opt-in): applies to traj_co2_nvt; the polarizable cases must not change
         env["MPMC_B200_INCREMENTAL"] = "1"
     if host_path == "warm_start":  # opt-in warm start: never applied to these fixed-iteration runs, which must not change
         env["MPMC_B200_WARM_START"] = "1"
+    if host_path == "threaded":
+        env.update({"MPMC_B200_HOST_THREADS": "4", "MPMC_B200_HOST_THREADS_MIN": "0", "MPMC_B200_SHIM_CHECK": "1"})
     gu.run_and_check_trajectory(PROGRAM, name, tmp_path, env)
+
+
+def test_dropin_energy_no_observables(tmp_path):
+    """energy_no_observables() (energy.c:232-318) through the drop-in: same energy, observables_t left alone."""
+    from oracle import oracle  # snapshot parser only
+
+    _need(DRIVER)
+    s, exp = gu.load("mixed_default")
+    first = np.r_[True, s.mol_id[1:] != s.mol_id[:-1]]
+    s.meta["atom_mass"] = np.where(first, s.mol_mass, 0.0)
+    inp = systems.write_reference_case(s, str(tmp_path))
+    r = subprocess.run([DRIVER, os.path.basename(inp), "1", "0", "n"], cwd=str(tmp_path), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "MPMC_SNAPSHOT" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    _, got, _ = oracle.parse_snapshot(r.stdout, "mixed_default")
+    assert abs(got["returned"] - exp["total"]) <= 1e-10 * (abs(exp["rd"]) + abs(exp["polar"]) + abs(exp["coulombic"]))
+    assert got["total"] == 0.0 and got["rd"] == 0.0 and got["polar"] == 0.0
+    gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label="no_observables")
+
+
+def _gpu_count():
+    import ctypes
+
+    try:
+        cuda = ctypes.CDLL("libcudart.so")
+    except OSError:
+        try:
+            import torch
+
+            return torch.cuda.device_count()
+        except Exception:
+            return 1
+    n = ctypes.c_int(0)
+    return n.value if cuda.cudaGetDeviceCount(ctypes.byref(n)) == 0 else 1
+
+
+@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt"])
+def test_dropin_trajectory_on_a_device_group(name, tmp_path):
+    """MPMC_B200_DEVICES=0,1: one MC chain sharded over two GPUs from ONE process (mpmc_b200_create_group) reproduces the
+    reference's fixed-seed trajectory row for row, insertions / removals included (the group re-wires its exchange
+    buffers whenever the padded sizes change)."""
+    if _gpu_count() < 2:
+        pytest.skip("needs two GPUs")
+    _need(PROGRAM)
+    gu.run_and_check_trajectory(PROGRAM, name, tmp_path, {"MPMC_B200_DEVICES": "0,1", "MPMC_B200_SHIM_CHECK": "1"})

@@ -26,14 +26,19 @@ def hoststub():
     return PROGRAM
 
 
-@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks"])
+@pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "threaded"])
 @pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt", "traj_co2_uvt", "traj_co2_npt"])
 def test_shim_host_logic_reproduces_reference_trajectory(hoststub, name, host_path, tmp_path):
-    """traj_co2_npt (volume moves: every accepted or reverted change of the cell must reach set_params) is checked here
-    only; the GPU run of it is left to the next round."""
+    """traj_co2_npt: volume moves -- every accepted or reverted change of the cell must reach set_params (its GPU run:
+    tests/test_gpu_shim.py).  `threaded`: the one pass and the scatter into atom_t with 4 host threads (the default above
+    4,096 atoms, forced here on the small systems), on a group of two devices as the shim parses MPMC_B200_DEVICES."""
     # MPMC_B200_SHIM_CHECK=1: after every one-pass call the shim compares its cached sequence, atom_array and molecule_array
     # with a real walk of the lists and dies on any difference
     env = {"MPMC_B200_SHIM_SLOW": "1"} if host_path == "list_walks" else {"MPMC_B200_SHIM_CHECK": "1"}
+    if host_path == "threaded":
+        env.update({"MPMC_B200_HOST_THREADS": "4", "MPMC_B200_HOST_THREADS_MIN": "0", "MPMC_B200_DEVICES": "0-1"})
+    else:
+        env["MPMC_B200_HOST_THREADS"] = "1"
     gu.run_and_check_trajectory(hoststub, name, tmp_path, env)
 
 
@@ -98,3 +103,44 @@ def test_cached_sequence_survives_relinking(hoststub, name, calls_expected, fast
     assert m, r.stderr[-2000:]
     calls, fast = int(m.group(1)), int(m.group(2))
     assert calls == calls_expected and fast >= fast_min, f"{name}: {fast} of {calls} calls on the cached-sequence pass"
+
+
+@pytest.mark.parametrize("extra,needle", [
+    ("cdvdw_9th_repulsion on\n", "cdvdw repulsion"),
+    ("ensemble surf\nsurf_min 2.0\nsurf_max 4.0\nsurf_inc 0.5\nsurf_ang 0.7\n", "surf"),
+])
+def test_shim_refuses_options_the_engine_does_not_implement(hoststub, extra, needle, tmp_path):
+    """No silent fallback through the drop-in: cdvdw_9th_repulsion changes the LJ mixing inside pair_exclusions()
+    (pairs.c:115-126) and the surf ensembles evaluate lj_nopbc() / coulombic_nopbc() over pair lists this build never
+    allocates -- both must end in error() + die(), not in a run with wrong energies."""
+    import json
+
+    d = json.load(open(os.path.join(gu.GOLD, "traj_co2_nvt.json")))
+    (tmp_path / d["pqr_name"]).write_text(d["pqr"])
+    text = d["input"]
+    if "ensemble" in extra:
+        text = text.replace("ensemble nvt\n", "")
+    (tmp_path / "input").write_text(text + "\n" + extra)
+    r = subprocess.run([hoststub, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=300)
+    out = r.stdout + r.stderr
+    assert r.returncode != 0, out[-2000:]
+    assert "not implemented by the B200 energy engine" in out and needle in out, out[-2000:]
+
+
+def test_energy_no_observables_through_the_shim(hoststub, tmp_path):
+    """energy_no_observables() (energy.c:232-318): the same energy, system->observables left alone."""
+    import numpy as np
+
+    from mpmc_b200 import systems
+    from oracle import oracle
+
+    s, exp = gu.load("mixed_default")
+    first = np.r_[True, s.mol_id[1:] != s.mol_id[:-1]]
+    s.meta["atom_mass"] = np.where(first, s.mol_mass, 0.0)
+    inp = systems.write_reference_case(s, str(tmp_path))
+    r = subprocess.run([DRIVER, os.path.basename(inp), "1", "0", "n"], cwd=str(tmp_path), capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "MPMC_SNAPSHOT" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    _, got, _ = oracle.parse_snapshot(r.stdout, "mixed_default")
+    assert abs(got["returned"] - exp["total"]) <= 1e-10 * (abs(exp["rd"]) + abs(exp["polar"]) + abs(exp["coulombic"]))
+    assert got["total"] == 0.0 and got["rd"] == 0.0 and got["polar"] == 0.0  # observables_t untouched (zero-allocated)
+    gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label="no_observables")
