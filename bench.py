@@ -359,7 +359,8 @@ def own_arm(args):
     import torch
     import torch.distributed as dist
 
-    from mpmc_b200 import Engine, pins
+    from mpmc_b200 import Engine
+    from tests import pins
     from mpmc_b200.sharded import ShardedEngine
 
     world = int(os.environ.get("WORLD_SIZE", "1"))

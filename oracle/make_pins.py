@@ -35,7 +35,7 @@ sys.path.insert(0, ROOT)
 from mpmc_b200 import systems  # noqa: E402
 from oracle import oracle  # noqa: E402
 
-from mpmc_b200.pins import ARRAYS, GOLD, INPUTS, STRIDE, checksums, input_digests  # noqa: E402
+from tests.pins import ARRAYS, GOLD, INPUTS, STRIDE, checksums, input_digests  # noqa: E402
 
 
 def build(name: str):

@@ -1,4 +1,6 @@
-"""Pins of the benchmarked configurations (tests/golden/pin_<workload>.npz, written by oracle/make_pins.py).
+"""TEST / MEASUREMENT INFRASTRUCTURE (not part of the product package).
+
+Pins of the benchmarked configurations (tests/golden/pin_<workload>.npz, written by oracle/make_pins.py).
 
 A pin is the answer of the reference (where it can load the system) or of the reference-pinned oracle for one of
 bench.py's workloads at its FULL size: energies by component, iteration count, a 1-in-16 subsample of every per-atom
@@ -14,7 +16,7 @@ import os
 
 import numpy as np
 
-GOLD = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 ARRAYS = ("mu", "ef_static", "ef_induced", "ef_induced_change", "dipole_rrms", "rank_metric")
 INPUTS = ("pos", "charge", "polarizability", "epsilon", "sigma", "mol_mass", "mol_id", "frozen")
 ENERGY_KEYS = ("rd", "es_real", "es_recip", "es_self", "coulombic", "polar", "total")

@@ -83,7 +83,7 @@ def main():
                     print(f"[rank {rank}] {name} {k}: max err {err:.3e}", flush=True)
                     ok = False
         if name == "mof_h2_21k":
-            from mpmc_b200 import pins
+            from tests import pins
 
             pin = pins.load("pin_mof_h2_21k")
             dev = pins.deviation(pin, got.to_dict(), arr)

@@ -6,7 +6,8 @@ import numpy as np
 import pytest
 
 import bench
-from mpmc_b200 import Engine, pins, systems
+from mpmc_b200 import Engine, systems
+from tests import pins
 from tests import golden_util as gu
 
 pytestmark = pytest.mark.gpu

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import bench
-from mpmc_b200 import pins
+from tests import pins
 
 pytestmark = pytest.mark.gpu
 

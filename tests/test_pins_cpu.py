@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 
 import bench
-from mpmc_b200 import pins
+from tests import pins
 
 
 @pytest.mark.parametrize("name", pins.names())
