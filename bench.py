@@ -570,6 +570,69 @@ def own_arm(args):
     return 0
 
 
+def ensembles_arm(args):
+    """--workload ensembles_<base>: `--gpus` independent fixed-seed NVT chains of <base>, one per GPU (BASELINE config 5's
+    second half; the reference's own parallel mode, src/mc/mc.c:431-432), each the drop-in program `mpmc_b200 <input>`
+    started by mpmc_b200/ensembles.py with MPMC_B200_DEVICE=k and seeds 1..N.  value = pair interactions per second
+    summed over the chains (weak scaling: every GPU carries a whole chain); steps/s per chain from the wall-time
+    difference of a long and a short run.  Under torchrun rank 0 launches all chains; the other ranks leave."""
+    from mpmc_b200 import Engine, ensembles, systems
+
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    base = args.workload[len("ensembles_"):]
+    s = build_workload(base)
+    eng = Engine(0)
+    eng.set_system(s)
+    for _ in range(max(args.warmup, 1)):
+        e = eng.energy()
+    cnt = eng.counters()
+    pairs = pair_interactions(cnt)
+    ms_one = eng.phase_ms("total")
+    launches_per_step = cnt.kernel_launches
+    eng.close()
+    n = args.gpus
+    est = max(ms_one * 1e-3 * 1.3, 1e-3)
+    short, long_ = 5, 5 + int(min(max(4.0 / est, 20 * args.steps), 20000))
+    sampler = ClockSampler(0)
+    walls = {}
+    with tempfile.TemporaryDirectory(prefix="mpmc_ens_") as td:
+        for steps in (short, long_):
+            case = os.path.join(td, f"case_{steps}")
+            ex = f"numsteps {steps}\ncorrtime {steps}\nmove_factor 0.01\nrot_factor 0.01\n"
+            systems.write_reference_case(s, case, ensemble="nvt", extra=ex)
+            if steps == long_:
+                sampler.start()
+            r = ensembles.launch(os.path.join(case, "input"), n, devices=list(range(n)), seeds=list(range(1, n + 1)),
+                                 workdir=os.path.join(td, f"run_{steps}"), env=dropin_env(1))
+            bad = [c for c in r["chains"] if c["rc"] != 0]
+            if bad:
+                raise SystemExit(f"ensemble chain failed: {bad[0]['error']}")
+            walls[steps] = [c["wall_s"] for c in r["chains"]]
+            averages = r["combined"]
+    clocks = sampler.stop()
+    rates = [(long_ - short) / max(b - a, 1e-9) for a, b in zip(walls[short], walls[long_])]
+    value = sum(rates) * pairs / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n, "steps": long_ - short, "warmup": short,
+        "ms_per_step": 1e3 / min(rates), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": args.workload, "n_atoms": s.n, "chains": n, "seeds": list(range(1, n + 1)),
+                   "pair_interactions_per_step": pairs, "mc_steps_per_s_per_chain": rates, "mc_steps_per_s": sum(rates),
+                   "parallelism": f"ensembles{n} (independent chains, no collective)", "l2": "system larger than L2 or "
+                   "flushed by the MC driver's own host work between steps",
+                   "ensemble_averages": {k: averages[k] for k in ("potential energy", "N", "polarization energy") if k in averages}},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 15 * 8, "d2h_bytes_per_step": 32 * 8 + 14 * 8 * s.n,
+                "through": "mpmc_b200 <input>: the reference's MC driver, every step through energy(system_t*)"},
+        "gpu_launches": int(launches_per_step * sum(long_ for _ in range(n))), "clocks": clocks, "roofline": None, "cpu_baseline": None,
+    }
+    if not args.no_cpu_baseline:
+        r = run_cpu_reference(base, 2, 1, budget_s=25.0)
+        line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -581,7 +644,11 @@ def main():
     ap.add_argument("--no-mc-dropin", action="store_true", help="skip the short `mpmc_b200 <input>` MC run")
     args = ap.parse_args()
     if args.impl == "reference":
+        if args.workload.startswith("ensembles_"):
+            args.workload = args.workload[len("ensembles_"):]  # N concurrent replicas of the reference is what that arm times
         return reference_arm(args)
+    if args.workload.startswith("ensembles_"):
+        return ensembles_arm(args)
     return own_arm(args)
 
 

@@ -982,6 +982,421 @@ __global__ void __launch_bounds__(4 * PUSH_ROWS) gs_push_kernel(Cell c, SubsetDe
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Persistent form of the delta sweep: ONE launch per sweep instead of two per 128-atom block (726 at 63k atoms).
+// CTA 0 (the resolver) walks the blocks in order and never leaves its SM; every other CTA (the pushers, one per SM)
+// owns a fixed set of row blocks and applies each finished delta_b to them as soon as the resolver publishes it:
+//
+//   resolver, block b:  E_b = (Jacobi part) + pushacc_b (pushers: deltas of blocks <= b-2) + its own push of b-1
+//                       -> the 4 x 32-step warp-synchronous chain of gs_delta_block_warp_kernel, with the in-sub-block
+//                          tensors read from a table made once per ordering (gs_block_tensor_kernel)
+//                       -> publish delta_b (flag ready[b]) -> push delta_b into the rows of block b+1 itself: that one
+//                          push is the only one on the critical path, so it never crosses a flag
+//   pusher p, row blocks r = 2+p, 2+p+P, ...:  for b = 0, 1, ...: wait ready[b]; acc_r -= T_rb delta_b for its r >= b+2
+//                       (most urgent first); when b = r-2 the sum is complete: publish it (pushacc, flag pushed[r])
+//
+// Look-ahead: while the resolver works on block b+1 the pushers spread delta_b over rows > b+2; only (b -> b+2) has a
+// deadline, one block period away.  Every sum has a fixed order (b ascending, column quarters in order): bit-reproducible.
+// Flags carry the sweep's epoch, so they are never cleared; every wait has a 2 s time-out that ends the kernel with
+// an error flag instead of hanging the GPU.  Launched cooperatively (co-residency of all CTAs is what the waits need).
+// ------------------------------------------------------------------------------------------------
+constexpr int GSP_THREADS = 512;
+constexpr int GSP_MAXOWN = 8;                 // row blocks a pusher may own (shared-memory accumulators)
+constexpr int GS_TENS = 4 * GS_SUBPAIRS * 6;  // doubles of one block's in-sub-block tensor table
+constexpr int GSP_RES_DOUBLES = GS_TENS + 4 * TILE + 3 * TILE + 9 * TILE + 12 * TILE + TILE / 2;
+constexpr int GSP_PUSH_DOUBLES = 7 * TILE + TILE / 2 + GSP_MAXOWN * 12 * TILE;
+constexpr int GSP_SMEM_DOUBLES = GSP_RES_DOUBLES > GSP_PUSH_DOUBLES ? GSP_RES_DOUBLES : GSP_PUSH_DOUBLES;
+
+struct GsSweepArgs {
+    int n, np, nb;  // polarizable atoms, padded, live 128-atom blocks
+    const double *x, *y, *z, *aux, *alpha;
+    const int* mol;
+    const double *esum, *es, *tens;
+    double *mu, *mu_new, *eind, *delta, *pushacc;
+    unsigned *ready, *pushed;
+    unsigned epoch;
+    double* timeout_flag;
+};
+
+// -T = c2 d d^T - c1 I (xx xy xz yy yz zz) of every pair inside the four 32-atom sub-blocks of every block
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(TILE) gs_block_tensor_kernel(Cell c, SubsetDev p, DipoleConsts k, const double* __restrict__ aux,
+                                                               double* __restrict__ tens) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], saux[TILE];
+    __shared__ int smol[TILE];
+    const int tid = threadIdx.x, b = blockIdx.x;
+    const int j = b * TILE + tid;
+    sx[tid] = p.x[j];
+    sy[tid] = p.y[j];
+    sz[tid] = p.z[j];
+    saux[tid] = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[j];
+    smol[tid] = p.mol[j];
+    __syncthreads();
+    const int jn = min(TILE, p.n - b * TILE);
+    double* out = tens + (size_t)b * GS_TENS;
+    for (int idx = tid; idx < 4 * GS_SUBPAIRS; idx += TILE) {
+        const int s = idx / GS_SUBPAIRS, q = idx - s * GS_SUBPAIRS;
+        int a = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
+        while (a * (a - 1) / 2 > q) a--;
+        while ((a + 1) * a / 2 <= q) a++;
+        const int bb = q - a * (a - 1) / 2;  // pair (a, bb), bb < a, inside sub-block s
+        const int ia = s * GS_SUB + a, ib = s * GS_SUB + bb;
+        double m[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (ia < jn) {
+            double dx = sx[ia] - sx[ib], dy = sy[ia] - sy[ib], dz = sz[ia] - sz[ib];
+            min_image<ORTHO>(c, dx, dy, dz);
+            double c1, c2;
+            tensor_coeff<DAMP, WF>(k, dx * dx + dy * dy + dz * dz, saux[ia], saux[ib], smol[ia] == smol[ib], c1, c2);
+            m[0] = c2 * dx * dx - c1;
+            m[1] = c2 * dx * dy;
+            m[2] = c2 * dx * dz;
+            m[3] = c2 * dy * dy - c1;
+            m[4] = c2 * dy * dz;
+            m[5] = c2 * dz * dz - c1;
+        }
+#pragma unroll
+        for (int e = 0; e < 6; e++) out[(size_t)idx * 6 + e] = m[e];
+    }
+}
+
+// thread 0 of a CTA: wait until *flag == epoch (acquire); false after 2 s
+__device__ __forceinline__ bool gsp_wait(const unsigned* flag, unsigned epoch, double* timeout_flag) {
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        unsigned v;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v == epoch) return true;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 2000000000ull) {
+            *timeout_flag = 1.0;
+            return false;
+        }
+    }
+}
+// thread 0 of a CTA, after a barrier that follows the CTA's global writes: publish them
+__device__ __forceinline__ void gsp_post(unsigned* flag, unsigned epoch) {
+    __threadfence();
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flag), "r"(epoch) : "memory");
+}
+
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cell c, DipoleConsts k, GsSweepArgs a) {
+    extern __shared__ double sm[];
+    __shared__ int s_abort;
+    const int tid = threadIdx.x, row = tid & (TILE - 1), q = tid >> 7, lane = tid & 31;
+    const int np = a.np;
+    if (tid == 0) s_abort = 0;
+    __syncthreads();
+    if (blockIdx.x == 0) {
+        // ------------------------------------------------------------------ resolver
+        double* tens = sm;                      // [GS_TENS]
+        double* sx = tens + GS_TENS;            // [128] each
+        double* sy = sx + TILE;
+        double* sz = sy + TILE;
+        double* saux = sz + TILE;
+        double* sdl = saux + TILE;              // [3][128] finished deltas of this block
+        double* part = sdl + 3 * TILE;          // [3][3][128] partial cross pushes of quarters 1..3
+        double* nxt = part + 9 * TILE;          // [4][3][128] this CTA's push of block b into the rows of block b+1
+        int* smol = reinterpret_cast<int*>(nxt + 12 * TILE);
+        for (int b = 0; b < a.nb; b++) {
+            const int i = b * TILE + row;
+            const int jn = min(TILE, a.n - b * TILE);
+            const bool live = row < jn;
+            if (b >= 2 && tid == 0)
+                if (!gsp_wait(a.pushed + b, a.epoch, a.timeout_flag)) s_abort = 1;
+            __syncthreads();  // also: nxt of the previous block is complete, its other buffers are free
+            if (s_abort) return;
+            {
+                const double* src = a.tens + (size_t)b * GS_TENS;
+                for (int idx = tid; idx < GS_TENS; idx += GSP_THREADS) tens[idx] = src[idx];
+            }
+            const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
+            const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[i];
+            const int moli = a.mol[i];
+            double ex = 0.0, ey = 0.0, ez = 0.0, ox = 0.0, oy = 0.0, oz = 0.0, al = 0.0, esx = 0.0, esy = 0.0, esz = 0.0;
+            if (q == 0) {
+                sx[row] = xi;
+                sy[row] = yi;
+                sz[row] = zi;
+                saux[row] = auxi;
+                smol[row] = moli;
+                ex = a.esum[i];
+                ey = a.esum[np + i];
+                ez = a.esum[2 * np + i];
+                if (b >= 2) {
+                    ex += __ldcg(a.pushacc + i);
+                    ey += __ldcg(a.pushacc + np + i);
+                    ez += __ldcg(a.pushacc + 2 * np + i);
+                }
+                if (b >= 1) {
+                    ex += ((nxt[0 * 3 * TILE + row] + nxt[1 * 3 * TILE + row]) + nxt[2 * 3 * TILE + row]) + nxt[3 * 3 * TILE + row];
+                    ey += ((nxt[0 * 3 * TILE + TILE + row] + nxt[1 * 3 * TILE + TILE + row]) + nxt[2 * 3 * TILE + TILE + row]) +
+                          nxt[3 * 3 * TILE + TILE + row];
+                    ez += ((nxt[0 * 3 * TILE + 2 * TILE + row] + nxt[1 * 3 * TILE + 2 * TILE + row]) +
+                           nxt[2 * 3 * TILE + 2 * TILE + row]) + nxt[3 * 3 * TILE + 2 * TILE + row];
+                }
+                ox = a.mu[i];
+                oy = a.mu[np + i];
+                oz = a.mu[2 * np + i];
+                al = live ? a.alpha[i] : 0.0;
+                esx = a.es[i];
+                esy = a.es[np + i];
+                esz = a.es[2 * np + i];
+            }
+            __syncthreads();
+            for (int s = 0; s < 4; s++) {
+                if (q == 0 && (row >> 5) == s) {  // warp s: the 32-step chain (thole_iterative.c:49-53 for 32 atoms in order)
+                    const double* trow = tens + ((size_t)s * GS_SUBPAIRS + (size_t)lane * (lane - 1) / 2) * 6;
+                    for (int kk = 0; kk < GS_SUB; kk++) {
+                        const double cx = al * (esx + ex) - ox, cy = al * (esy + ey) - oy, cz = al * (esz + ez) - oz;
+                        const double bx = __shfl_sync(0xffffffffu, cx, kk), by = __shfl_sync(0xffffffffu, cy, kk),
+                                     bz = __shfl_sync(0xffffffffu, cz, kk);
+                        if (lane > kk) {
+                            const double* t = trow + kk * 6;
+                            ex += t[0] * bx + t[1] * by + t[2] * bz;
+                            ey += t[1] * bx + t[3] * by + t[4] * bz;
+                            ez += t[2] * bx + t[4] * by + t[5] * bz;
+                        }
+                    }
+                    const double nx = al * (esx + ex), ny = al * (esy + ey), nz = al * (esz + ez);
+                    sdl[row] = live ? nx - ox : 0.0;
+                    sdl[TILE + row] = live ? ny - oy : 0.0;
+                    sdl[2 * TILE + row] = live ? nz - oz : 0.0;
+                    if (live) {
+                        a.mu_new[i] = nx;
+                        a.mu_new[np + i] = ny;
+                        a.mu_new[2 * np + i] = nz;
+                        a.mu[i] = nx;
+                        a.mu[np + i] = ny;
+                        a.mu[2 * np + i] = nz;
+                        a.eind[i] = ex;
+                        a.eind[np + i] = ey;
+                        a.eind[2 * np + i] = ez;
+                    }
+                    a.delta[i] = live ? nx - ox : 0.0;
+                    a.delta[np + i] = live ? ny - oy : 0.0;
+                    a.delta[2 * np + i] = live ? nz - oz : 0.0;
+                }
+                if (s == 3) break;
+                __syncthreads();
+                // the 32 finished deltas of sub-block s -> rows of the later sub-blocks, 8 columns per quarter
+                double px = 0.0, py = 0.0, pz = 0.0;
+                const bool later = (row >> 5) > s && live;
+                if (later) {
+                    const int j0 = s * GS_SUB + q * 8, j1 = min(j0 + 8, jn);
+                    for (int j = j0; j < j1; j++)
+                        tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[j], yi - sy[j], zi - sz[j], sdl[j], sdl[TILE + j],
+                                                      sdl[2 * TILE + j], auxi, saux[j], moli == smol[j], px, py, pz);
+                    if (q > 0) {
+                        part[(q - 1) * 3 * TILE + row] = px;
+                        part[(q - 1) * 3 * TILE + TILE + row] = py;
+                        part[(q - 1) * 3 * TILE + 2 * TILE + row] = pz;
+                    }
+                }
+                __syncthreads();
+                if (q == 0 && later) {
+                    ex += ((px + part[row]) + part[3 * TILE + row]) + part[6 * TILE + row];
+                    ey += ((py + part[TILE + row]) + part[3 * TILE + TILE + row]) + part[6 * TILE + TILE + row];
+                    ez += ((pz + part[2 * TILE + row]) + part[3 * TILE + 2 * TILE + row]) + part[6 * TILE + 2 * TILE + row];
+                }
+            }
+            __syncthreads();  // every delta of the block is in sdl and on its way to global memory
+            if (tid == 0) gsp_post(a.ready + b, a.epoch);
+            if (b + 1 < a.nb) {  // the one push on the critical path: block b -> rows of block b+1, 32 columns per quarter
+                const int i2 = (b + 1) * TILE + row;
+                double px = 0.0, py = 0.0, pz = 0.0;
+                if (i2 < a.n) {
+                    const double x2 = a.x[i2], y2 = a.y[i2], z2 = a.z[i2];
+                    const double aux2 = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[i2];
+                    const int mol2 = a.mol[i2];
+                    const int j0 = q * 32, j1 = min(j0 + 32, jn);
+#pragma unroll 2
+                    for (int j = j0; j < j1; j++)
+                        tensor_apply<ORTHO, DAMP, WF>(c, k, x2 - sx[j], y2 - sy[j], z2 - sz[j], sdl[j], sdl[TILE + j],
+                                                      sdl[2 * TILE + j], aux2, saux[j], mol2 == smol[j], px, py, pz);
+                }
+                nxt[q * 3 * TILE + row] = px;
+                nxt[q * 3 * TILE + TILE + row] = py;
+                nxt[q * 3 * TILE + 2 * TILE + row] = pz;
+            }
+        }
+        return;
+    }
+    // ---------------------------------------------------------------------- pusher
+    const int p = (int)blockIdx.x - 1, P = (int)gridDim.x - 1;
+    int nown = 0;
+    for (int r = 2 + p; r < a.nb; r += P) nown++;
+    if (nown == 0) return;
+    double* bx = sm;  // block b: positions, delta, aux  [128] each
+    double* by = bx + TILE;
+    double* bz = by + TILE;
+    double* bdx = bz + TILE;
+    double* bdy = bdx + TILE;
+    double* bdz = bdy + TILE;
+    double* baux = bdz + TILE;
+    int* bmol = reinterpret_cast<int*>(baux + TILE);
+    double* acc = baux + TILE + TILE / 2;  // [nown][4][3][128]
+    for (int idx = tid; idx < nown * 12 * TILE; idx += GSP_THREADS) acc[idx] = 0.0;
+    const int rmax = 2 + p + (nown - 1) * P;
+    for (int b = 0; b + 2 <= rmax; b++) {
+        if (tid == 0)
+            if (!gsp_wait(a.ready + b, a.epoch, a.timeout_flag)) s_abort = 1;
+        __syncthreads();  // also: everybody is done with the previous block's staging buffers
+        if (s_abort) return;
+        const int jn = min(TILE, a.n - b * TILE);
+        if (tid < TILE) {
+            const int j = b * TILE + tid;
+            bx[tid] = a.x[j];
+            by[tid] = a.y[j];
+            bz[tid] = a.z[j];
+            bdx[tid] = __ldcg(a.delta + j);
+            bdy[tid] = __ldcg(a.delta + np + j);
+            bdz[tid] = __ldcg(a.delta + 2 * np + j);
+            baux[tid] = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[j];
+            bmol[tid] = a.mol[j];
+        }
+        __syncthreads();
+        const int k0 = b > p ? (b - p + P - 1) / P : 0;  // first owned row block r >= b + 2
+        for (int kk = k0; kk < nown; kk++) {
+            const int r = 2 + p + kk * P;
+            const int i = r * TILE + row;
+            double* mine = acc + ((size_t)kk * 4 + q) * 3 * TILE;
+            if (i < a.n) {
+                const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
+                const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[i];
+                const int moli = a.mol[i];
+                double ex = 0.0, ey = 0.0, ez = 0.0;
+                const int j0 = q * 32, j1 = min(j0 + 32, jn);
+#pragma unroll 2
+                for (int j = j0; j < j1; j++)
+                    tensor_apply<ORTHO, DAMP, WF>(c, k, xi - bx[j], yi - by[j], zi - bz[j], bdx[j], bdy[j], bdz[j], auxi, baux[j],
+                                                  moli == bmol[j], ex, ey, ez);
+                mine[row] += ex;
+                mine[TILE + row] += ey;
+                mine[2 * TILE + row] += ez;
+            }
+            if (r == b + 2) {  // the deltas of blocks 0..r-2 are all in: hand the sum to the resolver
+                __syncthreads();
+                if (q == 0) {
+                    const double* a0 = acc + (size_t)kk * 12 * TILE;
+#pragma unroll
+                    for (int d = 0; d < 3; d++)
+                        a.pushacc[(size_t)d * np + i] = ((a0[d * TILE + row] + a0[3 * TILE + d * TILE + row]) +
+                                                         a0[6 * TILE + d * TILE + row]) + a0[9 * TILE + d * TILE + row];
+                }
+                __syncthreads();
+                if (tid == 0) gsp_post(a.pushed + r, a.epoch);
+            }
+        }
+    }
+}
+
+size_t gs_block_tensor_doubles(int n_pad) { return (size_t)(n_pad / TILE) * GS_TENS; }
+
+void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* tens, cudaStream_t s) {
+    const DipoleConsts k = make_consts(c, o);
+    const int nb = (pol.n + TILE - 1) / TILE;
+    if (nb <= 0) return;
+    const double* aux = pol.aux;
+#define LAUNCH(ORTHO, DAMP, WF) gs_block_tensor_kernel<ORTHO, DAMP, WF><<<nb, TILE, 0, s>>>(c, pol, k, aux, tens);
+#define DISPATCH(ORTHO)                                              \
+    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true)  \
+        else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false)             \
+    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                    \
+        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false)                       \
+    } else {                                                         \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true)          \
+        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false)                     \
+    }
+    if (ortho) {
+        DISPATCH(true)
+    } else {
+        DISPATCH(false)
+    }
+#undef DISPATCH
+#undef LAUNCH
+}
+
+// One sweep in one launch.  esum must hold the Jacobi part (launch_dipole_contract_sym with the dipoles as they are at
+// the start of the sweep); flags [2 * n_pad / 128] unsigned, zeroed once when allocated; epoch > 0, increasing from call
+// to call.  Returns false -- nothing launched -- when the kernel cannot run here (more row blocks than the pushers'
+// accumulators hold, no cooperative launch, not one CTA per SM): the caller then takes the per-block launches.
+bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* esum,
+                                const double* es, double* mu, double* mu_new, double* eind, double* delta, const double* tens,
+                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s) {
+    const int nb = (pol.n + TILE - 1) / TILE;
+    if (nb <= 0) return true;
+    int dev = 0, sms = 0, coop = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (!coop || sms < 2) return false;
+    const int P = sms - 1;
+    if (nb - 2 > GSP_MAXOWN * P) return false;
+    const size_t smem = sizeof(double) * GSP_SMEM_DOUBLES;
+    const DipoleConsts k = make_consts(c, o);
+    GsSweepArgs a;
+    a.n = pol.n;
+    a.np = pol.n_pad;
+    a.nb = nb;
+    a.x = pol.x;
+    a.y = pol.y;
+    a.z = pol.z;
+    a.aux = pol.aux;
+    a.alpha = pol.alpha;
+    a.mol = pol.mol;
+    a.esum = esum;
+    a.es = es;
+    a.tens = tens;
+    a.mu = mu;
+    a.mu_new = mu_new;
+    a.eind = eind;
+    a.delta = delta;
+    a.pushacc = pushacc;
+    a.ready = flags;
+    a.pushed = flags + pol.n_pad / TILE;
+    a.epoch = epoch;
+    a.timeout_flag = timeout_flag;
+    Cell cc = c;
+    DipoleConsts kk = k;
+    void* args[] = {&cc, &kk, &a};
+    cudaError_t err = cudaErrorInvalidValue;
+#define LAUNCH(ORTHO, DAMP, WF)                                                                                          \
+    {                                                                                                                    \
+        static unsigned long long seen = 0;                                                                              \
+        const void* fn = (const void*)gs_sweep_persistent_kernel<ORTHO, DAMP, WF>;                                       \
+        if (first_on_device(seen)) cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);      \
+        int per_sm = 0;                                                                                                  \
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, GSP_THREADS, smem);                                   \
+        if (per_sm < 1) return false;                                                                                    \
+        err = cudaLaunchCooperativeKernel(fn, dim3(sms), dim3(GSP_THREADS), args, smem, s);                              \
+    }
+#define DISPATCH(ORTHO)                                              \
+    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true)  \
+        else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false)             \
+    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                    \
+        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false)                       \
+    } else {                                                         \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true)          \
+        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false)                     \
+    }
+    if (ortho) {
+        DISPATCH(true)
+    } else {
+        DISPATCH(false)
+    }
+#undef DISPATCH
+#undef LAUNCH
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return true;
+}
+
 size_t gs_block_coeff_doubles(int n_pad) { return (size_t)(n_pad / TILE) * GS_PAIRS * 2; }
 
 void launch_gs_block_coeffs(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* coef, cudaStream_t s) {

@@ -108,6 +108,7 @@ enum Slot {
     S_FIELDCNT = 13,
     S_TOTMU = 16,  // 3: sum of the dipoles (full-Ewald polarization)
     S_PEER_TIMEOUT = 20,  // set to 1.0 by a peer-wait kernel whose peer never signalled
+    S_GS_TIMEOUT = 21,    // set to 1.0 by the persistent Gauss-Seidel sweep when one of its CTAs waited 2 s for another
     S_CRYSTAL = 22,       // 2: rd_crystal image sums of the pairs, pairs counted
     S_COUNT = 24
 };
@@ -170,6 +171,10 @@ struct mpmc_b200_ctx {
     DevBuf<double> es, mu, mu_old, mu_new, eind, eic, rrms, rank_packed, rmin_part, field_cnt;
     DevBuf<double> g_es, g_mu, g_mu_old, g_mu_new, g_eind, g_eic, g_rrms, g_delta, g_coef;  // GS space
     bool gs_delta = true;  // delta form of the sweep (symmetric Jacobi part + block pushes); MPMC_B200_GS=panels: panel form
+    bool gs_persistent = true;  // one cooperative launch per sweep (resolver + pushers); MPMC_B200_GS=blocks: two launches per block
+    DevBuf<double> g_tens, g_pushacc;
+    DevBuf<unsigned> gs_flags;
+    unsigned gs_epoch = 0;
     DevBuf<int> perm;
     std::vector<int> hperm;
     DevBuf<double> wolf_table;
@@ -1569,8 +1574,18 @@ static int enqueue_polar(Ctx* c) {
                 c->gs.didx.ensure(pp) || c->perm.ensure(pp) || c->g_es.ensure(3 * (size_t)pp) ||
                 c->g_mu.ensure(3 * (size_t)pp) || c->g_mu_old.ensure(3 * (size_t)pp) || c->g_mu_new.ensure(3 * (size_t)pp) ||
                 c->g_eind.ensure(3 * (size_t)pp) || c->g_eic.ensure(3 * (size_t)pp) || c->g_rrms.ensure(pp) ||
-                c->g_delta.ensure(3 * (size_t)pp) || (c->gs_delta && c->g_coef.ensure(gs_block_coeff_doubles(pp))))
+                c->g_delta.ensure(3 * (size_t)pp) ||
+                (c->gs_delta && !c->gs_persistent && c->g_coef.ensure(gs_block_coeff_doubles(pp))) ||
+                (c->gs_delta && c->gs_persistent && (c->g_tens.ensure(gs_block_tensor_doubles(pp)) || c->g_pushacc.ensure(3 * (size_t)pp))))
                 FAIL(11, "cudaMalloc failed");
+            if (c->gs_delta && c->gs_persistent) {  // sweep flags carry an epoch and are never cleared: zero them once per allocation
+                const size_t before = c->gs_flags.cap;
+                if (c->gs_flags.ensure(2 * (size_t)(pp / TILE) + 2)) FAIL(11, "cudaMalloc failed");
+                if (c->gs_flags.cap != before) {
+                    CU(cudaMemsetAsync(c->gs_flags.p, 0, sizeof(unsigned) * c->gs_flags.cap, st));
+                    c->gs_epoch = 0;
+                }
+            }
         }
         auto to_gs_space = [&](bool first) -> int {
             // (re)build the permuted working set from the packed-order arrays
@@ -1601,7 +1616,10 @@ static int enqueue_polar(Ctx* c) {
             g.mol = c->gs.mol.p;
             if (c->gs_delta) {  // cluster boxes of the atoms in processing order, for the symmetric Jacobi part of a sweep
                 launch_cluster_boxes(cell, ortho, g, c->cbox.p, st);
-                launch_gs_block_coeffs(cell, ortho, g, dop, c->g_coef.p, st);  // in-block tensor coefficients of this order
+                if (c->gs_persistent)
+                    launch_gs_block_tensors(cell, ortho, g, dop, c->g_tens.p, st);  // in-sub-block tensors of this order
+                else
+                    launch_gs_block_coeffs(cell, ortho, g, dop, c->g_coef.p, st);  // in-block tensor coefficients of this order
                 c->launches += 2;
             }
             CU(cudaGetLastError());
@@ -1651,10 +1669,24 @@ static int enqueue_polar(Ctx* c) {
                 if (uo.save_old) CU(cudaMemcpyAsync(c->g_mu_old.p, c->g_mu.p, sizeof(double) * 3 * pp, cudaMemcpyDeviceToDevice, st));
                 if (c->gs_delta) {
                     kev_mark(c);
-                    launch_gs_sweep_delta(cell, ortho, g, dop, c->cbox.p, c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p,
-                                          c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->g_delta.p, c->g_coef.p, st);
+                    bool one_launch = false;
+                    if (c->gs_persistent) {
+                        // Jacobi part with the dipoles as they are at the start of the sweep, then the whole
+                        // lower-triangular part in one cooperative launch (resolver + pushers with look-ahead)
+                        launch_dipole_contract_sym(cell, ortho, g, dop, c->g_mu.p, c->cbox.p, 0, 1, c->sym_ysplits, c->sym_partI.p,
+                                                   c->sym_partJ.p, c->esum.p, st);
+                        one_launch = launch_gs_sweep_persistent(cell, ortho, g, dop, c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p,
+                                                                c->g_eind.p, c->g_delta.p, c->g_tens.p, c->g_pushacc.p,
+                                                                c->gs_flags.p, ++c->gs_epoch, c->scalars.p + S_GS_TIMEOUT, st);
+                        c->launches += 3;
+                    }
+                    if (!one_launch) {
+                        launch_gs_sweep_delta(cell, ortho, g, dop, c->cbox.p, c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p,
+                                              c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->g_delta.p,
+                                              c->gs_persistent ? nullptr : c->g_coef.p, st);
+                        c->launches += 2 + 2 * ((c->pol.n + TILE - 1) / TILE);
+                    }
                     kev_mark(c);
-                    c->launches += 2 + 2 * ((c->pol.n + TILE - 1) / TILE);
                 } else {
                     launch_gs_sweep(cell, ortho, g, dop, nullptr, c->g_es.p, c->g_mu.p, c->g_mu_new.p, c->g_eind.p, c->epart.p, st);
                     c->launches += 2 * (pp / TILE);
@@ -1890,6 +1922,7 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     }
     const double* h = c->h_scalars;
     if (h[S_PEER_TIMEOUT] != 0.0) FAIL(12, "peer exchange timed out: a rank never published its induced-field partial sums");
+    if (h[S_GS_TIMEOUT] != 0.0) FAIL(12, "Gauss-Seidel sweep timed out: a CTA of the persistent sweep waited 2 s for another");
     memset(out, 0, sizeof(*out));
     // host-side analytic terms are added once: by rank 0 when the caller sums the ranks' partial energies (staged
     // protocol), by every rank when the device scalars were already combined over the ranks (sharded_eval)
@@ -2161,6 +2194,7 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         if (v) c->k7_list_cap_gb = atof(v);
         v = getenv("MPMC_B200_GS");
         c->gs_delta = c->use_sym && !(v && strcmp(v, "panels") == 0);
+        c->gs_persistent = !(v && strcmp(v, "blocks") == 0);
     }
     for (int p = 0; p < PH_COUNT; p++) {
         CU(cudaEventCreate(&c->ev[p][0]));
@@ -2252,10 +2286,12 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
                               &c->kweight_field, &c->kvec, &c->sf_partial, &c->sf, &c->ef_static, &c->epart, &c->es, &c->mu,
                               &c->mu_old, &c->mu_new, &c->eind, &c->eic, &c->rrms, &c->rank_packed, &c->rmin_part,
                               &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms, &c->g_delta, &c->g_coef,
+                              &c->g_tens, &c->g_pushacc,
                               &c->wolf_table, &c->scalars, &c->cbox, &c->sym_partI, &c->sym_partJ, &c->esum})
         b->release();
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();
     c->kgroups.release();
+    c->gs_flags.release();
     c->k7_cnt.release();
     c->k7_offs.release();
     c->k7_list.release();

@@ -213,6 +213,15 @@ void launch_gs_block_coeffs(const Cell& c, bool ortho, const SubsetDev& pol, con
 void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* cbox, int ysplits,
                            double* epartI, double* epartJ, double* esum, const double* es, double* mu, double* mu_new,
                            double* eind, double* delta, const double* coef, cudaStream_t s);
+// Persistent form of the same sweep (dipole_kernel.cu: gs_sweep_persistent_kernel): one cooperative launch per sweep, a
+// resolver CTA walking the blocks and one pusher CTA per other SM spreading each finished delta with look-ahead.
+// tens: gs_block_tensor_doubles(n_pad) doubles from launch_gs_block_tensors for the SAME order; pushacc [3][n_pad];
+// flags [2 * n_pad / 128] unsigned zeroed at allocation; epoch > 0 and increasing.  false = not launchable here.
+size_t gs_block_tensor_doubles(int n_pad);
+void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* tens, cudaStream_t s);
+bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* esum,
+                                const double* es, double* mu, double* mu_new, double* eind, double* delta, const double* tens,
+                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s);
 // rank metric of pairs() (src/energy/pairs.c:337-360)
 void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank /*[pol n_pad]*/,
                         cudaStream_t s);

@@ -266,6 +266,7 @@ static double o_crystal_self(const osys_t *s, int i, double cutoff) {
 typedef struct {
     double rd_pair, lrc_pair, es_real, min_r;
     double n_tested, n_lj, n_es;
+    double rd_running; /* lj.c:256 as written: ONE running sum of (rd_energy + lrc) over the pairs in list order */
 } orow_t;
 
 /* One row i of the pair loops of lj() (src/energy/lj.c:181-260) and
@@ -301,6 +302,7 @@ static void o_pair_row(const osys_t *s, int i, orow_t *acc) {
             }
             acc->rd_pair += rd;
             acc->lrc_pair += lrc;
+            acc->rd_running += rd + lrc;
         }
         /* ---- coulombic_wolf(): coulombic.c:269-308 (option `wolf`) ---- */
         if (!P->rd_only && P->es_wolf) {
@@ -1131,6 +1133,19 @@ int mpmc_oracle_energy(const mpmc_b200_params *P, int n, const double *pos, cons
         out->rd_pair = tot.rd_pair;
         out->rd_lrc = tot.lrc_pair + lrc_self;
         out->rd = (tot.rd_pair + tot.lrc_pair) + lrc_self;
+        if (nthreads == 1) {
+            /* The reference's own association (lj.c:256,264-273): every pair's (rd_energy + lrc), then every atom's
+             * image self term, then every atom's LRC self term, all added one by one to the SAME running sum.  At
+             * 10^4 atoms that sum carries ~1e-10 of rounding that the separated sums above do not (a constant ~1e-4 K
+             * LRC term added 7.5e7 times to a 1e8 K sum rounds the same way every time); reproducing it bit for bit
+             * is what ties the large reference-made pin (tests/golden/pin_co2_fluid_12k.npz) to this restatement. */
+            double potential = tot.rd_running;
+            if (P->rd_crystal)
+                for (i = 0; i < n; i++) potential += o_crystal_self(&s, i, o_rd_cutoff(P));
+            if (P->rd_lrc)
+                for (i = 0; i < n; i++) potential += o_lrc_self(&s, i, o_rd_cutoff(P));
+            out->rd = potential;
+        }
     }
     if (!P->rd_only) { /* coulombic(): coulombic.c:22-39 */
         double nk = 0, nq = 0;

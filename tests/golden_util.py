@@ -76,9 +76,16 @@ def run_and_check_trajectory(program, name, tmp_path, env=None):
     import subprocess
 
     d = json.load(open(os.path.join(GOLD, name + ".json")))
-    (tmp_path / d["pqr_name"]).write_text(d["pqr"])
+
+    def unpack(key):
+        import base64
+        import gzip
+
+        return gzip.decompress(base64.b64decode(d[key + "_gz_b64"])).decode() if key + "_gz_b64" in d else d[key if key != "final" else "final_pqr"]
+
+    (tmp_path / d["pqr_name"]).write_text(unpack("pqr"))
     (tmp_path / "input").write_text(d["input"])
-    r = subprocess.run([program, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1200,
+    r = subprocess.run([program, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1800,
                        env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     rows = [l for l in (tmp_path / d.get("energy_file", "small.energy.dat")).read_text().splitlines() if not l.startswith("#")]
@@ -90,4 +97,20 @@ def run_and_check_trajectory(program, name, tmp_path, env=None):
         assert fa[0] == fb[0] and fa[8] == fb[8], f"{name} row {k}: step / N differ: {a} | {b}"
         assert np.all(np.abs(fa - fb) <= 2e-6 + 1e-9 * np.abs(fb)), f"{name} row {k}:\n{a}\n{b}"
     final = (tmp_path / d.get("final_file", "small.final.pdb")).read_text()
-    assert final == d["final_pqr"], "final configuration differs from the reference's"
+    assert final == unpack("final"), "final configuration differs from the reference's"
+    if "output_lines" in d:
+        # the MC driver's `OUTPUT:` averages (write_averages(), output.c:1133-1280; update_root_averages(),
+        # average.c:213-349): N, wt %, excess ratio, <U>, <U_es>, <U_rd>, <U_pol>, qst, acceptance ratios ... at every
+        # corrtime, printed with 5 decimals -- every number of every block must agree with the reference's
+        import re
+
+        keep = [l for l in r.stdout.splitlines() if l.startswith("OUTPUT:") and "sec/step" not in l and "collecting statistics" not in l]
+        assert len(keep) == len(d["output_lines"]), (len(keep), len(d["output_lines"]))
+        num = re.compile(r"-?\d+\.\d+(?:[eE][-+]?\d+)?|-?\d+")
+        for a, b in zip(keep, d["output_lines"]):
+            na, nb = num.findall(a), num.findall(b)
+            assert re.sub(num, "#", a) == re.sub(num, "#", b), f"{name}: OUTPUT lines differ in shape:\n{a}\n{b}"
+            for x, y in zip(na, nb):
+                x, y = float(x), float(y)
+                assert abs(x - y) <= 2.1e-5 + 2e-9 * abs(y), f"{name}: averages differ:\n{a}\n{b}"
+    return r

@@ -91,10 +91,22 @@ def deviation(pin: dict, energies: dict, arrays: dict | None) -> dict:
             out["worst"] = what
 
     es_scale = max(abs(exp.get("es_real", 0.0)), abs(exp.get("es_self", 0.0)), abs(exp.get("es_recip", 0.0)))
+    # Reference-made pins of 10^4-atom systems: lj() adds every pair's (rd_energy + lrc) to ONE running sum (lj.c:256),
+    # which at this size carries ~1e-10 of rounding of its own.  make_pins.py proves that (the oracle in the
+    # reference's order reproduces the reference's rd bit for bit) and stores the well-conditioned sum beside it:
+    # rd and total are held to 1e-10 against THAT, and to 1e-10 + the reference's measured noise against the reference.
+    rd_cond = pin["meta"].get("rd_conditioned")
+    if rd_cond is not None and "rd" in energies and exp.get("rd"):
+        out["reference_rd_noise"] = abs(exp["rd"] - rd_cond) / abs(exp["rd"])
+        out["rd_vs_reference"] = abs(energies["rd"] - exp["rd"]) / abs(exp["rd"])
     for k in ENERGY_KEYS:
         if k not in exp or k not in energies:
             continue
         b = exp[k]
+        if rd_cond is not None and k == "rd":
+            b = rd_cond
+        if rd_cond is not None and k == "total":
+            b = (exp["total"] - exp["rd"]) + rd_cond
         scale = abs(b)
         if k == "coulombic":
             scale = max(scale, 1e-3 * es_scale)

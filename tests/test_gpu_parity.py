@@ -180,6 +180,36 @@ def test_gauss_seidel_matches_oracle_midsize(engine, par):
     assert got.polar_iterations == exp.polar_iterations
 
 
+@pytest.mark.parametrize("form", ["blocks", "panels"])
+def test_gauss_seidel_launch_forms_agree(engine, form, monkeypatch):
+    """The persistent sweep (one cooperative launch: resolver + pushers, the default) against the per-block launches
+    (MPMC_B200_GS=blocks) and the panel form (MPMC_B200_GS=panels) of the same Gauss-Seidel sweep, ranked and with palmo,
+    on ~135 blocks with a ragged last one: same iteration count, energies and dipoles to rounding; and the default form
+    reproduces itself bit for bit (fixed-order sums, no atomics)."""
+    from mpmc_b200 import Engine
+
+    s = systems.mof_h2(cells=(9, 3, 3), polar_max_iter=4)
+    s.params.polar_gs_ranked, s.params.polar_palmo = 1, 1
+    engine.set_system(s)
+    a = engine.energy()
+    arr = engine.atom_arrays()
+    a2 = engine.energy()
+    assert a2.polar == a.polar and np.array_equal(engine.atom_arrays()["mu"], arr["mu"])
+    monkeypatch.setenv("MPMC_B200_GS", form)  # read when the context is created
+    other = Engine(0)
+    try:
+        other.set_system(s)
+        b = other.energy()
+        barr = other.atom_arrays()
+    finally:
+        other.close()
+    assert a.polar_iterations == b.polar_iterations
+    assert abs(a.polar - b.polar) <= 1e-11 * abs(b.polar)
+    for k in ("mu", "ef_induced", "ef_induced_change"):
+        scale = np.abs(barr[k]).max()
+        assert np.abs(arr[k] - barr[k]).max() <= 1e-11 * scale, k
+
+
 def test_polar_entry_point(engine):
     s, exp = gu.load("mixed_default")
     engine.set_system(s)

@@ -103,6 +103,19 @@ def test_dropin_energy_no_observables(tmp_path):
     gu.assert_atom_arrays(got, exp, s, rtol=1e-10, label="no_observables")
 
 
+def test_dropin_pcn61_uvt_averages_and_uptake(tmp_path):
+    """north_star: "the ensemble averages and uptake of the sample MOF runs must agree".  The shipped PCN-61 + H2 uVT input
+    (sample_configs_gpu/3_PCN61/iter.inp, every option of it) on the largest part of the system the reference can hold
+    (framework + the first 500 H2: 8,548 atoms), 100 fixed-seed steps with insertions / removals: every energy row, the
+    final configuration AND every number of every `OUTPUT:` averages block (N, wt %, excess adsorption ratio, <U>, <U_es>,
+    <U_rd>, <U_pol> with its iteration count, qst, acceptance ratios) equal the unmodified reference's
+    (tests/golden/traj_pcn61_uvt.json, oracle/make_golden.py traj_pcn61_uvt)."""
+    _need(PROGRAM)
+    if not os.path.exists(os.path.join(gu.GOLD, "traj_pcn61_uvt.json")):
+        pytest.fail("tests/golden/traj_pcn61_uvt.json missing: python oracle/make_golden.py traj_pcn61_uvt")
+    gu.run_and_check_trajectory(PROGRAM, "traj_pcn61_uvt", tmp_path, {"MPMC_B200_SHIM_CHECK": "1"})
+
+
 def _gpu_count():
     import ctypes
 
