@@ -1003,7 +1003,7 @@ __global__ void __launch_bounds__(4 * PUSH_ROWS) gs_push_kernel(Cell c, SubsetDe
 constexpr int GSP_THREADS = 512;
 constexpr int GSP_MAXOWN = 8;                 // row blocks a pusher may own (shared-memory accumulators)
 constexpr int GS_TENS = 4 * GS_SUBPAIRS * 6;  // doubles of one block's in-sub-block tensor table
-constexpr int GSP_RES_DOUBLES = GS_TENS + 4 * TILE + 3 * TILE + 9 * TILE + 12 * TILE + TILE / 2;
+constexpr int GSP_RES_DOUBLES = 2 * GS_TENS + 4 * TILE + 3 * TILE + 9 * TILE + 12 * TILE + TILE / 2;  // table double buffered
 constexpr int GSP_PUSH_DOUBLES = 7 * TILE + TILE / 2 + GSP_MAXOWN * 12 * TILE;
 constexpr int GSP_SMEM_DOUBLES = GSP_RES_DOUBLES > GSP_PUSH_DOUBLES ? GSP_RES_DOUBLES : GSP_PUSH_DOUBLES;
 
@@ -1016,13 +1016,22 @@ struct GsSweepArgs {
     unsigned *ready, *pushed;
     unsigned epoch;
     double* timeout_flag;
+    unsigned long long* trace;  // optional [nb][8] globaltimer stamps of the resolver (MPMC_B200_GS_TRACE): wait, load, chain, post, push
 };
 
-// -T = c2 d d^T - c1 I (xx xy xz yy yz zz) of every pair inside the four 32-atom sub-blocks of every block
+#define GSP_STAMP(slot)                                                                \
+    if (a.trace && tid == 0) {                                                         \
+        unsigned long long t__;                                                        \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));                        \
+        a.trace[(size_t)b * 8 + (slot)] = t__;                                         \
+    }
+
+// M = -alpha_a T_ab = alpha_a (c2 d d^T - c1 I)  (xx xy xz yy yz zz) of every pair (a > b) inside the four 32-atom
+// sub-blocks of every block: what a finished delta_b adds to the CANDIDATE delta of a later atom a of its sub-block
 template <bool ORTHO, int DAMP, bool WF>
 __global__ void __launch_bounds__(TILE) gs_block_tensor_kernel(Cell c, SubsetDev p, DipoleConsts k, const double* __restrict__ aux,
                                                                double* __restrict__ tens) {
-    __shared__ double sx[TILE], sy[TILE], sz[TILE], saux[TILE];
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], saux[TILE], sal[TILE];
     __shared__ int smol[TILE];
     const int tid = threadIdx.x, b = blockIdx.x;
     const int j = b * TILE + tid;
@@ -1031,6 +1040,7 @@ __global__ void __launch_bounds__(TILE) gs_block_tensor_kernel(Cell c, SubsetDev
     sz[tid] = p.z[j];
     saux[tid] = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[j];
     smol[tid] = p.mol[j];
+    sal[tid] = j < p.n ? p.alpha[j] : 0.0;
     __syncthreads();
     const int jn = min(TILE, p.n - b * TILE);
     double* out = tens + (size_t)b * GS_TENS;
@@ -1047,12 +1057,13 @@ __global__ void __launch_bounds__(TILE) gs_block_tensor_kernel(Cell c, SubsetDev
             min_image<ORTHO>(c, dx, dy, dz);
             double c1, c2;
             tensor_coeff<DAMP, WF>(k, dx * dx + dy * dy + dz * dz, saux[ia], saux[ib], smol[ia] == smol[ib], c1, c2);
-            m[0] = c2 * dx * dx - c1;
-            m[1] = c2 * dx * dy;
-            m[2] = c2 * dx * dz;
-            m[3] = c2 * dy * dy - c1;
-            m[4] = c2 * dy * dz;
-            m[5] = c2 * dz * dz - c1;
+            const double al = sal[ia];
+            m[0] = al * (c2 * dx * dx - c1);
+            m[1] = al * (c2 * dx * dy);
+            m[2] = al * (c2 * dx * dz);
+            m[3] = al * (c2 * dy * dy - c1);
+            m[4] = al * (c2 * dy * dz);
+            m[5] = al * (c2 * dz * dz - c1);
         }
 #pragma unroll
         for (int e = 0; e < 6; e++) out[(size_t)idx * 6 + e] = m[e];
@@ -1082,7 +1093,7 @@ __device__ __forceinline__ void gsp_post(unsigned* flag, unsigned epoch) {
 
 template <bool ORTHO, int DAMP, bool WF>
 __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cell c, DipoleConsts k, GsSweepArgs a) {
-    extern __shared__ double sm[];
+    extern __shared__ __align__(16) double sm[];
     __shared__ int s_abort;
     const int tid = threadIdx.x, row = tid & (TILE - 1), q = tid >> 7, lane = tid & 31;
     const int np = a.np;
@@ -1090,8 +1101,8 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
     __syncthreads();
     if (blockIdx.x == 0) {
         // ------------------------------------------------------------------ resolver
-        double* tens = sm;                      // [GS_TENS]
-        double* sx = tens + GS_TENS;            // [128] each
+        double* tens0 = sm;                     // [2][GS_TENS]: this block's table and the next one's (cp.async prefetch)
+        double* sx = tens0 + 2 * GS_TENS;       // [128] each
         double* sy = sx + TILE;
         double* sz = sy + TILE;
         double* saux = sz + TILE;
@@ -1099,18 +1110,27 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
         double* part = sdl + 3 * TILE;          // [3][3][128] partial cross pushes of quarters 1..3
         double* nxt = part + 9 * TILE;          // [4][3][128] this CTA's push of block b into the rows of block b+1
         int* smol = reinterpret_cast<int*>(nxt + 12 * TILE);
+        auto prefetch = [&](int blk) {          // table of block `blk` -> buffer blk & 1, 16 bytes per copy, asynchronous
+            const char* src = reinterpret_cast<const char*>(a.tens + (size_t)blk * GS_TENS);
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(tens0 + (size_t)(blk & 1) * GS_TENS);
+            for (int ch = tid; ch < GS_TENS / 2; ch += GSP_THREADS)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * ch), "l"(src + 16 * (size_t)ch) : "memory");
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        prefetch(0);
         for (int b = 0; b < a.nb; b++) {
             const int i = b * TILE + row;
             const int jn = min(TILE, a.n - b * TILE);
             const bool live = row < jn;
+            const double* tens = tens0 + (size_t)(b & 1) * GS_TENS;
+            GSP_STAMP(0)
             if (b >= 2 && tid == 0)
                 if (!gsp_wait(a.pushed + b, a.epoch, a.timeout_flag)) s_abort = 1;
-            __syncthreads();  // also: nxt of the previous block is complete, its other buffers are free
+            asm volatile("cp.async.wait_group 0;" ::: "memory");  // this thread's share of the table of block b has landed
+            __syncthreads();  // ... and everybody's; nxt of the previous block is complete, its other buffers are free
             if (s_abort) return;
-            {
-                const double* src = a.tens + (size_t)b * GS_TENS;
-                for (int idx = tid; idx < GS_TENS; idx += GSP_THREADS) tens[idx] = src[idx];
-            }
+            GSP_STAMP(1)
+            if (b + 1 < a.nb) prefetch(b + 1);  // lands while this block's chains run
             const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
             const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[i];
             const int moli = a.mol[i];
@@ -1145,24 +1165,30 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
                 esz = a.es[2 * np + i];
             }
             __syncthreads();
+            GSP_STAMP(2)
             for (int s = 0; s < 4; s++) {
-                if (q == 0 && (row >> 5) == s) {  // warp s: the 32-step chain (thole_iterative.c:49-53 for 32 atoms in order)
+                if (q == 0 && (row >> 5) == s) {
+                    // Warp s: the 32-step chain (thole_iterative.c:49-53 for 32 atoms in order), carried on the CANDIDATE
+                    // delta c = alpha (E_s + E) - mu_old of every lane: lane k's is final at step k, and a finished delta_k
+                    // changes a later candidate by M_ak delta_k with M = -alpha_a T_ak tabulated -- per step one
+                    // broadcast and a three-deep FMA chain, nothing else on the dependency path.
                     const double* trow = tens + ((size_t)s * GS_SUBPAIRS + (size_t)lane * (lane - 1) / 2) * 6;
+                    double cx = fma(al, esx + ex, -ox), cy = fma(al, esy + ey, -oy), cz = fma(al, esz + ez, -oz);
+#pragma unroll 4
                     for (int kk = 0; kk < GS_SUB; kk++) {
-                        const double cx = al * (esx + ex) - ox, cy = al * (esy + ey) - oy, cz = al * (esz + ez) - oz;
                         const double bx = __shfl_sync(0xffffffffu, cx, kk), by = __shfl_sync(0xffffffffu, cy, kk),
                                      bz = __shfl_sync(0xffffffffu, cz, kk);
                         if (lane > kk) {
                             const double* t = trow + kk * 6;
-                            ex += t[0] * bx + t[1] * by + t[2] * bz;
-                            ey += t[1] * bx + t[3] * by + t[4] * bz;
-                            ez += t[2] * bx + t[4] * by + t[5] * bz;
+                            cx = fma(t[2], bz, fma(t[1], by, fma(t[0], bx, cx)));
+                            cy = fma(t[4], bz, fma(t[3], by, fma(t[1], bx, cy)));
+                            cz = fma(t[5], bz, fma(t[4], by, fma(t[2], bx, cz)));
                         }
                     }
-                    const double nx = al * (esx + ex), ny = al * (esy + ey), nz = al * (esz + ez);
-                    sdl[row] = live ? nx - ox : 0.0;
-                    sdl[TILE + row] = live ? ny - oy : 0.0;
-                    sdl[2 * TILE + row] = live ? nz - oz : 0.0;
+                    const double nx = ox + cx, ny = oy + cy, nz = oz + cz;  // mu_new = mu_old + delta
+                    sdl[row] = live ? cx : 0.0;
+                    sdl[TILE + row] = live ? cy : 0.0;
+                    sdl[2 * TILE + row] = live ? cz : 0.0;
                     if (live) {
                         a.mu_new[i] = nx;
                         a.mu_new[np + i] = ny;
@@ -1170,13 +1196,14 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
                         a.mu[i] = nx;
                         a.mu[np + i] = ny;
                         a.mu[2 * np + i] = nz;
-                        a.eind[i] = ex;
-                        a.eind[np + i] = ey;
-                        a.eind[2 * np + i] = ez;
+                        // the field this atom saw when it was resolved: mu_new = alpha (E_s + E)
+                        a.eind[i] = nx / al - esx;
+                        a.eind[np + i] = ny / al - esy;
+                        a.eind[2 * np + i] = nz / al - esz;
                     }
-                    a.delta[i] = live ? nx - ox : 0.0;
-                    a.delta[np + i] = live ? ny - oy : 0.0;
-                    a.delta[2 * np + i] = live ? nz - oz : 0.0;
+                    a.delta[i] = live ? cx : 0.0;
+                    a.delta[np + i] = live ? cy : 0.0;
+                    a.delta[2 * np + i] = live ? cz : 0.0;
                 }
                 if (s == 3) break;
                 __syncthreads();
@@ -1202,7 +1229,11 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
                 }
             }
             __syncthreads();  // every delta of the block is in sdl and on its way to global memory
-            if (tid == 0) gsp_post(a.ready + b, a.epoch);
+            GSP_STAMP(3)
+            // publish from the last thread: its fence (~5 us of write-ack latency) then stalls one warp of a
+            // throughput-bound phase instead of the thread every stamp and wait of this CTA goes through
+            if (tid == GSP_THREADS - 1) gsp_post(a.ready + b, a.epoch);
+            GSP_STAMP(4)
             if (b + 1 < a.nb) {  // the one push on the critical path: block b -> rows of block b+1, 32 columns per quarter
                 const int i2 = (b + 1) * TILE + row;
                 double px = 0.0, py = 0.0, pz = 0.0;
@@ -1220,6 +1251,7 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
                 nxt[q * 3 * TILE + TILE + row] = py;
                 nxt[q * 3 * TILE + 2 * TILE + row] = pz;
             }
+            GSP_STAMP(5)
         }
         return;
     }
@@ -1325,7 +1357,8 @@ void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, co
 // accumulators hold, no cooperative launch, not one CTA per SM): the caller then takes the per-block launches.
 bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* esum,
                                 const double* es, double* mu, double* mu_new, double* eind, double* delta, const double* tens,
-                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s) {
+                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s,
+                                unsigned long long* trace) {
     const int nb = (pol.n + TILE - 1) / TILE;
     if (nb <= 0) return true;
     int dev = 0, sms = 0, coop = 0;
@@ -1359,6 +1392,7 @@ bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol,
     a.pushed = flags + pol.n_pad / TILE;
     a.epoch = epoch;
     a.timeout_flag = timeout_flag;
+    a.trace = trace;
     Cell cc = c;
     DipoleConsts kk = k;
     void* args[] = {&cc, &kk, &a};

@@ -27,6 +27,10 @@
 //   * minimum image: rint() runs on the conversion pipe (FRND.F64), not on the fp64 FMA pipe.
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <tuple>
+#include <vector>
 
 #include "kernels.h"
 
@@ -108,8 +112,9 @@ __device__ __forceinline__ void tensor_coeffs(const SymConsts& k, double r2, dou
 
 struct SymArgs {
     int n, np, S;    // polarizable atoms, padded, super tiles (np / 256)
-    int tile_begin;  // first I super tile of this launch (gridDim.x follow)
-    int L0, L1;      // work items (I, offset slice y), L = I * gridDim.y + y, owned by this launch: [L0, L1)
+    int Y;           // offset slices: work items (I super tile, slice y), numbered y-major: c = y * S + I
+    int rank, world; // this launch owns the items c with c % world == rank (round robin: every rank gets the same mix of
+                     // near -- damped, expensive -- and far tile pairs; contiguous shares left the ranks 9 % apart)
     int K;           // S/2: offsets 0..K
     int kper;        // offsets per gridDim.y slice
     int hsplit;      // 1: a CTA walks both halves of the J super tile; 2: gridDim.z = 2, one half each (finer grain
@@ -222,12 +227,10 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
     __shared__ int smol[4][64];
     __shared__ double sej[4][3][TILE];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int I = a.tile_begin + blockIdx.x;
-    {
-        const int L = I * (int)gridDim.y + (int)blockIdx.y;
-        if (L < a.L0 || L >= a.L1) return;  // another rank's item (whole CTA, before any barrier)
-    }
     const int np = a.np, S = a.S, nclus = np >> 5;
+    const int cidx = a.rank + (int)blockIdx.x * a.world;  // this rank's blockIdx.x-th item
+    if (cidx >= S * a.Y) return;                          // (whole CTA, before any barrier)
+    const int I = cidx % S, yslice = cidx / S;
     // thread t keeps atoms ia and ia + 32: warp w owns the i-clusters 2w and 2w+1 of the super tile
     const int ia = I * STILE + w * 64 + lane;
     double pi[2][6], auxi[2] = {0.0, 0.0}, ei[2][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
@@ -246,7 +249,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
     }
     const int ci = (I * STILE + w * 64) >> 5;  // first of this warp's two i-clusters
 
-    const int k0 = blockIdx.y * a.kper, k1 = min(k0 + a.kper, a.K + 1);
+    const int k0 = yslice * a.kper, k1 = min(k0 + a.kper, a.K + 1);
     for (int kk = k0; kk < k1; kk++) {
         if (kk > 0 && 2 * kk == S && I >= kk) continue;  // even S: the half-way offset belongs to I < S/2
         int J = I + kk;
@@ -341,7 +344,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
             }
         }
     }
-    double* e = a.epartI + (size_t)(blockIdx.y * a.hsplit + blockIdx.z) * 3 * np;
+    double* e = a.epartI + (size_t)(yslice * a.hsplit + blockIdx.z) * 3 * np;
 #pragma unroll
     for (int u = 0; u < 2; u++) {
         const int i = ia + 32 * u;
@@ -351,10 +354,14 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
     }
 }
 
-// E_ind[c][i] = sum_y epartI[y][c][i] (if tile(i) was an I tile of this launch) + sum_k epartJ[k-1][c][i] over the
-// offsets k whose I = tile(i) - k was processed.  Fixed order: y ascending, then k ascending in 8 interleaved lanes
-// combined in lane order.  One CTA = 32 consecutive atoms x 3 components x 8 k-lanes.  T = super tiles.
-__global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, int K, int L0, int L1, int Y, int kper, int hsplit,
+// E_ind[c][i] = sum of the partial rows this launch wrote for atom i: the I-side rows epartI[y] of the items (tile(i), y)
+// and the J-side rows epartJ[k-1] of the items (tile(i) - k, slice(k)) it owned.  Which rows those are is a pure
+// function of (super tiles, slices, rank, world): the host lists them once per layout (sym_reduce_list: CSR over the
+// super tiles, entry = row index, bit 30 set for a J-side row, in the fixed order y ascending then k ascending), so the
+// kernel touches nothing it does not own -- its time falls with 1/world like the contraction's (the loop over every
+// (y, k) with an ownership test per step cost 70 us at any world size: 13 % of a contraction at 8 GPUs).
+// One CTA = 32 consecutive atoms x 3 components x 8 lanes over the list; the lanes' sums are combined in lane order.
+__global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, const int* __restrict__ offs, const int* __restrict__ rows,
                                                                 const double* __restrict__ epartI,
                                                                 const double* __restrict__ epartJ,
                                                                 double* __restrict__ esum) {
@@ -363,26 +370,14 @@ __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, int T, i
     const int i = blockIdx.x * 32 + li;
     const int J = i / STILE;
     double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-    if (lk == 0) {
-        for (int y = 0; y < Y * hsplit; y++) {
-            const int L = J * Y + y / hsplit;
-            if (L < L0 || L >= L1) continue;  // item (J, y) belongs to another rank
-            const double* e = epartI + (size_t)y * 3 * np;
-            s0 += e[i];
-            s1 += e[np + i];
-            s2 += e[2 * np + i];
-        }
-    }
-    for (int kk = 1 + lk; kk <= K; kk += 8) {
-        int I = J - kk;
-        if (I < 0) I += T;
-        const int L = I * Y + kk / kper;
-        if (L < L0 || L >= L1) continue;
-        if (2 * kk == T && I >= kk) continue;
-        const double* e = epartJ + (size_t)(kk - 1) * 3 * np;
-        s0 += e[i];
-        s1 += e[np + i];
-        s2 += e[2 * np + i];
+    const int e0 = offs[J], e1 = offs[J + 1];
+#pragma unroll 4
+    for (int e = e0 + lk; e < e1; e += 8) {
+        const int r = rows[e];
+        const double* src = ((r & (1 << 30)) ? epartJ : epartI) + (size_t)(r & ((1 << 30) - 1)) * 3 * np;
+        s0 += src[i];
+        s1 += src[np + i];
+        s2 += src[2 * np + i];
     }
     part[lk][0][li] = s0;
     part[lk][1][li] = s1;
@@ -491,6 +486,61 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
 
 }  // namespace
 
+// The partial rows a launch owns, per super tile (see dipole_sym_reduce_kernel), cached on the device per
+// (device, layout): [S + 1] CSR offsets followed by the entries.  The layout changes only with the padded atom count
+// or the shard, so the steady state is a map lookup.
+struct ReduceListKey {
+    int dev, S, K, Y, kper, hsplit, rank, world;
+    bool operator<(const ReduceListKey& o) const {
+        return std::tie(dev, S, K, Y, kper, hsplit, rank, world) < std::tie(o.dev, o.S, o.K, o.Y, o.kper, o.hsplit, o.rank, o.world);
+    }
+};
+static const int* sym_reduce_list(int S, int K, int Y, int kper, int hsplit, int rank, int world, cudaStream_t st) {
+    static std::map<ReduceListKey, int*> cache;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    ReduceListKey key;
+    cudaGetDevice(&key.dev);
+    key.S = S, key.K = K, key.Y = Y, key.kper = kper, key.hsplit = hsplit, key.rank = rank, key.world = world;
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    if (cache.size() > 64) {  // uVT runs walk through many sizes: drop the old layouts (no launch is in flight on them
+        for (auto& kv : cache) {  // once the stream has been synchronised)
+            cudaSetDevice(kv.first.dev);
+            cudaDeviceSynchronize();
+            cudaFree(kv.second);
+        }
+        cache.clear();
+        cudaSetDevice(key.dev);
+    }
+    std::vector<int> offs(S + 1, 0), rows;
+    for (int J = 0; J < S; J++) {
+        offs[J] = (int)rows.size();
+        for (int y = 0; y < Y * hsplit; y++)  // I side: item (J, y / hsplit) wrote row y
+            if (((y / hsplit) * S + J) % world == rank) rows.push_back(y);
+        for (int kk = 1; kk <= K; kk++) {  // J side: item (J - kk, slice of kk) wrote row kk - 1
+            int I = J - kk;
+            if (I < 0) I += S;
+            if (((kk / kper) * S + I) % world != rank) continue;
+            if (2 * kk == S && I >= kk) continue;  // even S: the half-way offset belongs to I < S/2
+            rows.push_back((kk - 1) | (1 << 30));
+        }
+    }
+    offs[S] = (int)rows.size();
+    std::vector<int> all(offs);
+    all.insert(all.end(), rows.begin(), rows.end());
+    int* dev = nullptr;
+    if (cudaMalloc(&dev, sizeof(int) * all.size()) != cudaSuccess) return nullptr;
+    // pageable source: the copy is staged before the call returns, and stream order puts it ahead of the reduce kernel
+    if (cudaMemcpyAsync(dev, all.data(), sizeof(int) * all.size(), cudaMemcpyHostToDevice, st) != cudaSuccess) {
+        cudaFree(dev);
+        return nullptr;
+    }
+    cudaStreamSynchronize(st);
+    cache[key] = dev;
+    return dev;
+}
+
 void launch_cluster_boxes(const Cell& c, bool ortho, const SubsetDev& pol, double* cbox, cudaStream_t s) {
     const int nclus = pol.n_pad / 32;
     if (nclus <= 0) return;
@@ -539,20 +589,26 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
-    // Splitting the J halves over gridDim.z doubles the CTAs of the short launches of a sharded run; measured on
-    // 4 and 8 GPUs (profiles/r01_multi_gpu.md) it LOSES 8 %, so it stays an experiment switch.
+    // Splitting the J halves of a super tile over gridDim.z halves the work item.  It pays where a rank's items make
+    // fewer than ~8 waves of resident CTAs -- 4 and 8 GPUs at 63k atoms: 0.978 -> 0.951 and 0.528 -> 0.501 ms per
+    // contraction (profiles/r02_multi_gpu.md; in round 1 it lost 8 % because the partial-row reduce then cost twice as
+    // much, which the list-driven reduce no longer does) -- and nowhere else.
     a.hsplit = 1;
-    (void)sms;
+    {
+        const long long items_here = ((long long)S * ysplits + world - 1) / world;
+        if (world > 1 && items_here < 8LL * SYM_MINB * sms) a.hsplit = 2;
+    }
     if (const char* v = getenv("MPMC_B200_SYM_HSPLIT")) a.hsplit = atoi(v) == 2 ? 2 : 1;
-    // Sharding unit: the work item (I tile, offset slice y) -- every item has the same number of pairs, and a
-    // contiguous range of the flattened index balances the ranks to one item (whole I tiles leave 22 vs 23 at 8 GPUs).
-    const long long items = (long long)S * ysplits;
-    a.L0 = (int)(items * rank / world);
-    a.L1 = (int)(items * (rank + 1) / world);
-    a.tile_begin = a.L0 / ysplits;
-    const int ntile = a.L1 > a.L0 ? (a.L1 - 1) / ysplits - a.tile_begin + 1 : 0;
-    if (ntile > 0) {
-        dim3 grid(ntile, ysplits, a.hsplit);
+    // Sharding unit: the work item (I tile, offset slice y) -- every item has the same number of pairs; the items are
+    // dealt out round robin over their y-major order, so the ranks differ by at most one item and hold the same mix of
+    // damped and far tile pairs.  One CTA per owned item, in that order (heavy near-diagonal slices first).
+    const int items = S * ysplits;
+    a.Y = ysplits;
+    a.rank = rank;
+    a.world = world;
+    const int mine = items > rank ? (items - rank + world - 1) / world : 0;
+    if (mine > 0) {
+        dim3 grid(mine, 1, a.hsplit);
 #define LAUNCH(ORTHO, DAMP, WF, FE) dipole_sym_kernel<ORTHO, DAMP, WF, FE><<<grid, TILE, 0, s>>>(c, k, a)
 #define DISPATCH(ORTHO)                                                         \
     if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                                 \
@@ -577,7 +633,8 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
 #undef DISPATCH
 #undef LAUNCH
     }
-    dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, S, K, a.L0, a.L1, ysplits, a.kper, a.hsplit, epartI, epartJ, esum);
+    const int* list = sym_reduce_list(S, K, ysplits, a.kper, a.hsplit, rank, world, s);
+    if (list) dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, list, list + S + 1, epartI, epartJ, esum);
     if (sig && sig->world > 1) peer_signal_kernel<<<1, 32, 0, s>>>(*sig);
 }
 

@@ -175,6 +175,7 @@ struct mpmc_b200_ctx {
     DevBuf<double> g_tens, g_pushacc;
     DevBuf<unsigned> gs_flags;
     unsigned gs_epoch = 0;
+    DevBuf<unsigned long long> gs_trace;  // MPMC_B200_GS_TRACE=1: resolver time stamps of the last sweep, summarised on stderr
     DevBuf<int> perm;
     std::vector<int> hperm;
     DevBuf<double> wolf_table;
@@ -1578,6 +1579,8 @@ static int enqueue_polar(Ctx* c) {
                 (c->gs_delta && !c->gs_persistent && c->g_coef.ensure(gs_block_coeff_doubles(pp))) ||
                 (c->gs_delta && c->gs_persistent && (c->g_tens.ensure(gs_block_tensor_doubles(pp)) || c->g_pushacc.ensure(3 * (size_t)pp))))
                 FAIL(11, "cudaMalloc failed");
+            if (c->gs_delta && c->gs_persistent && getenv("MPMC_B200_GS_TRACE") && c->gs_trace.ensure((size_t)(pp / TILE) * 8 + 8))
+                FAIL(11, "cudaMalloc failed");
             if (c->gs_delta && c->gs_persistent) {  // sweep flags carry an epoch and are never cleared: zero them once per allocation
                 const size_t before = c->gs_flags.cap;
                 if (c->gs_flags.ensure(2 * (size_t)(pp / TILE) + 2)) FAIL(11, "cudaMalloc failed");
@@ -1677,7 +1680,8 @@ static int enqueue_polar(Ctx* c) {
                                                    c->sym_partJ.p, c->esum.p, st);
                         one_launch = launch_gs_sweep_persistent(cell, ortho, g, dop, c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p,
                                                                 c->g_eind.p, c->g_delta.p, c->g_tens.p, c->g_pushacc.p,
-                                                                c->gs_flags.p, ++c->gs_epoch, c->scalars.p + S_GS_TIMEOUT, st);
+                                                                c->gs_flags.p, ++c->gs_epoch, c->scalars.p + S_GS_TIMEOUT, st,
+                                                                c->gs_trace.p);
                         c->launches += 3;
                     }
                     if (!one_launch) {
@@ -1921,6 +1925,20 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
         c->contract_ms_sum += ms;
     }
     const double* h = c->h_scalars;
+    if (c->gs_trace.p && c->last_had_polar && (c->P.polar_gs || c->P.polar_gs_ranked) && c->pol.n > 0) {
+        // profiling aid: where the resolver of the last persistent sweep spent its time, per 128-atom block
+        const int nb = (c->pol.n + TILE - 1) / TILE;
+        std::vector<unsigned long long> t((size_t)nb * 8);
+        if (cudaMemcpy(t.data(), c->gs_trace.p, sizeof(unsigned long long) * t.size(), cudaMemcpyDeviceToHost) == cudaSuccess && nb > 4) {
+            double acc[5] = {0, 0, 0, 0, 0};
+            for (int b = 2; b < nb - 1; b++)
+                for (int k = 0; k < 5; k++) acc[k] += (double)(t[(size_t)b * 8 + k + 1] - t[(size_t)b * 8 + k]);
+            fprintf(stderr, "MPMC_B200_GS_TRACE: %d blocks, sweep %.3f ms; per block (us): wait for pushers %.2f, load %.2f, "
+                            "chains + cross pushes %.2f, publish %.2f, push to next block %.2f\n",
+                    nb, (double)(t[(size_t)(nb - 1) * 8 + 5] - t[0]) * 1e-6, acc[0] / (nb - 3) * 1e-3, acc[1] / (nb - 3) * 1e-3,
+                    acc[2] / (nb - 3) * 1e-3, acc[3] / (nb - 3) * 1e-3, acc[4] / (nb - 3) * 1e-3);
+        }
+    }
     if (h[S_PEER_TIMEOUT] != 0.0) FAIL(12, "peer exchange timed out: a rank never published its induced-field partial sums");
     if (h[S_GS_TIMEOUT] != 0.0) FAIL(12, "Gauss-Seidel sweep timed out: a CTA of the persistent sweep waited 2 s for another");
     memset(out, 0, sizeof(*out));
@@ -2292,6 +2310,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();
     c->kgroups.release();
     c->gs_flags.release();
+    c->gs_trace.release();
     c->k7_cnt.release();
     c->k7_offs.release();
     c->k7_list.release();

@@ -221,7 +221,8 @@ size_t gs_block_tensor_doubles(int n_pad);
 void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* tens, cudaStream_t s);
 bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* esum,
                                 const double* es, double* mu, double* mu_new, double* eind, double* delta, const double* tens,
-                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s);
+                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s,
+                                unsigned long long* trace = nullptr /* [blocks][8] resolver time stamps (profiling) */);
 // rank metric of pairs() (src/energy/pairs.c:337-360)
 void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank /*[pol n_pad]*/,
                         cudaStream_t s);
