@@ -1012,6 +1012,7 @@ struct GsSweepArgs {
     const double *x, *y, *z, *aux, *alpha;
     const int* mol;
     const double *esum, *es, *tens;
+    const double2* ctab;  // [nb][2][128 cols][128 rows] (c1, c2) of the pairs (block b, block b) and (block b+1, block b)
     double *mu, *mu_new, *eind, *delta, *pushacc;
     unsigned *ready, *pushed;
     unsigned epoch;
@@ -1068,6 +1069,52 @@ __global__ void __launch_bounds__(TILE) gs_block_tensor_kernel(Cell c, SubsetDev
 #pragma unroll
         for (int e = 0; e < 6; e++) out[(size_t)idx * 6 + e] = m[e];
     }
+}
+
+// (c1, c2) of every pair the RESOLVER applies: rows of block b against columns of block b (the pushes between the
+// sub-blocks of a block) and rows of block b+1 against columns of block b (the one push on the critical path), laid
+// out [column][row] so that a warp of consecutive rows reads 512 contiguous bytes.  Made once per ordering; the
+// resolver then spends ~22 fp64 instructions per pair (minimum image + apply) instead of ~50 (rsqrt, exp, damping).
+constexpr int GS_CTAB = 2 * TILE * TILE;  // double2 entries per block
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(TILE) gs_pair_coeff_kernel(Cell c, SubsetDev p, DipoleConsts k, const double* __restrict__ aux,
+                                                             double2* __restrict__ ctab) {
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], saux[TILE];
+    __shared__ int smol[TILE];
+    const int tid = threadIdx.x, b = blockIdx.x, t = blockIdx.y;
+    const int j = b * TILE + tid;  // column atom staged by this thread
+    sx[tid] = p.x[j];
+    sy[tid] = p.y[j];
+    sz[tid] = p.z[j];
+    saux[tid] = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : aux[j];
+    smol[tid] = p.mol[j];
+    __syncthreads();
+    const int i = (b + t) * TILE + tid;  // row atom of this thread
+    const bool row_live = i < p.n;       // (i < n_pad always: n_pad is padded past the last live block by construction)
+    const double xi = row_live ? p.x[i] : 0.0, yi = row_live ? p.y[i] : 0.0, zi = row_live ? p.z[i] : 0.0;
+    const double auxi = (row_live && DAMP != MPMC_DAMP_EXPONENTIAL) ? aux[i] : 0.0;
+    const int moli = row_live ? p.mol[i] : -1;
+    const int jn = min(TILE, p.n - b * TILE);
+    double2* out = ctab + ((size_t)b * 2 + t) * TILE * TILE;
+    for (int jj = 0; jj < TILE; jj++) {
+        double2 v = make_double2(0.0, 0.0);
+        if (row_live && jj < jn && (t == 1 || tid > jj)) {
+            double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
+            min_image<ORTHO>(c, dx, dy, dz);
+            tensor_coeff<DAMP, WF>(k, dx * dx + dy * dy + dz * dz, auxi, saux[jj], moli == smol[jj], v.x, v.y);
+        }
+        out[(size_t)jj * TILE + tid] = v;
+    }
+}
+
+template <bool ORTHO>
+__device__ __forceinline__ void tensor_apply_coef(const Cell& c, double dx, double dy, double dz, double mx, double my,
+                                                  double mz, const double2 cf, double& ex, double& ey, double& ez) {
+    min_image<ORTHO>(c, dx, dy, dz);
+    const double dm = (dx * mx + dy * my + dz * mz) * cf.y;
+    ex += dm * dx - cf.x * mx;
+    ey += dm * dy - cf.x * my;
+    ez += dm * dz - cf.x * mz;
 }
 
 // thread 0 of a CTA: wait until *flag == epoch (acquire); false after 2 s
@@ -1174,16 +1221,22 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
                     // broadcast and a three-deep FMA chain, nothing else on the dependency path.
                     const double* trow = tens + ((size_t)s * GS_SUBPAIRS + (size_t)lane * (lane - 1) / 2) * 6;
                     double cx = fma(al, esx + ex, -ox), cy = fma(al, esy + ey, -oy), cz = fma(al, esz + ez, -oz);
-#pragma unroll 4
+                    // No branch inside a step: every lane reads "its" entry kk (for lanes <= kk that is somebody else's
+                    // entry or the first doubles behind the table -- valid shared memory, finite values) and the
+                    // result is kept only where lane > kk.  The loads depend on kk alone, so they run ahead of the chain.
+#pragma unroll 8
                     for (int kk = 0; kk < GS_SUB; kk++) {
+                        const double* t = trow + kk * 6;
+                        const double t0 = t[0], t1 = t[1], t2 = t[2], t3 = t[3], t4 = t[4], t5 = t[5];
                         const double bx = __shfl_sync(0xffffffffu, cx, kk), by = __shfl_sync(0xffffffffu, cy, kk),
                                      bz = __shfl_sync(0xffffffffu, cz, kk);
-                        if (lane > kk) {
-                            const double* t = trow + kk * 6;
-                            cx = fma(t[2], bz, fma(t[1], by, fma(t[0], bx, cx)));
-                            cy = fma(t[4], bz, fma(t[3], by, fma(t[1], bx, cy)));
-                            cz = fma(t[5], bz, fma(t[4], by, fma(t[2], bx, cz)));
-                        }
+                        const double ncx = fma(t2, bz, fma(t1, by, fma(t0, bx, cx)));
+                        const double ncy = fma(t4, bz, fma(t3, by, fma(t1, bx, cy)));
+                        const double ncz = fma(t5, bz, fma(t4, by, fma(t2, bx, cz)));
+                        const bool upd = lane > kk;
+                        cx = upd ? ncx : cx;
+                        cy = upd ? ncy : cy;
+                        cz = upd ? ncz : cz;
                     }
                     const double nx = ox + cx, ny = oy + cy, nz = oz + cz;  // mu_new = mu_old + delta
                     sdl[row] = live ? cx : 0.0;
@@ -1212,9 +1265,11 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
                 const bool later = (row >> 5) > s && live;
                 if (later) {
                     const int j0 = s * GS_SUB + q * 8, j1 = min(j0 + 8, jn);
+                    const double2* cf = a.ctab + (size_t)b * GS_CTAB + row;
+#pragma unroll 4
                     for (int j = j0; j < j1; j++)
-                        tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[j], yi - sy[j], zi - sz[j], sdl[j], sdl[TILE + j],
-                                                      sdl[2 * TILE + j], auxi, saux[j], moli == smol[j], px, py, pz);
+                        tensor_apply_coef<ORTHO>(c, xi - sx[j], yi - sy[j], zi - sz[j], sdl[j], sdl[TILE + j], sdl[2 * TILE + j],
+                                                 __ldg(cf + (size_t)j * TILE), px, py, pz);
                     if (q > 0) {
                         part[(q - 1) * 3 * TILE + row] = px;
                         part[(q - 1) * 3 * TILE + TILE + row] = py;
@@ -1239,13 +1294,12 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
                 double px = 0.0, py = 0.0, pz = 0.0;
                 if (i2 < a.n) {
                     const double x2 = a.x[i2], y2 = a.y[i2], z2 = a.z[i2];
-                    const double aux2 = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[i2];
-                    const int mol2 = a.mol[i2];
                     const int j0 = q * 32, j1 = min(j0 + 32, jn);
-#pragma unroll 2
+                    const double2* cf = a.ctab + (size_t)b * GS_CTAB + (size_t)TILE * TILE + row;
+#pragma unroll 4
                     for (int j = j0; j < j1; j++)
-                        tensor_apply<ORTHO, DAMP, WF>(c, k, x2 - sx[j], y2 - sy[j], z2 - sz[j], sdl[j], sdl[TILE + j],
-                                                      sdl[2 * TILE + j], aux2, saux[j], mol2 == smol[j], px, py, pz);
+                        tensor_apply_coef<ORTHO>(c, x2 - sx[j], y2 - sy[j], z2 - sz[j], sdl[j], sdl[TILE + j], sdl[2 * TILE + j],
+                                                 __ldg(cf + (size_t)j * TILE), px, py, pz);
                 }
                 nxt[q * 3 * TILE + row] = px;
                 nxt[q * 3 * TILE + TILE + row] = py;
@@ -1325,13 +1379,19 @@ __global__ void __launch_bounds__(GSP_THREADS, 1) gs_sweep_persistent_kernel(Cel
 }
 
 size_t gs_block_tensor_doubles(int n_pad) { return (size_t)(n_pad / TILE) * GS_TENS; }
+size_t gs_pair_coeff_doubles(int n_pad) { return (size_t)(n_pad / TILE) * GS_CTAB * 2; }
 
-void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* tens, cudaStream_t s) {
+void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* tens, double* ctab,
+                             cudaStream_t s) {
     const DipoleConsts k = make_consts(c, o);
     const int nb = (pol.n + TILE - 1) / TILE;
     if (nb <= 0) return;
     const double* aux = pol.aux;
-#define LAUNCH(ORTHO, DAMP, WF) gs_block_tensor_kernel<ORTHO, DAMP, WF><<<nb, TILE, 0, s>>>(c, pol, k, aux, tens);
+#define LAUNCH(ORTHO, DAMP, WF)                                                        \
+    {                                                                                  \
+        gs_block_tensor_kernel<ORTHO, DAMP, WF><<<nb, TILE, 0, s>>>(c, pol, k, aux, tens); \
+        gs_pair_coeff_kernel<ORTHO, DAMP, WF><<<dim3(nb, 2), TILE, 0, s>>>(c, pol, k, aux, reinterpret_cast<double2*>(ctab)); \
+    }
 #define DISPATCH(ORTHO)                                              \
     if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
         if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true)  \
@@ -1357,8 +1417,8 @@ void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, co
 // accumulators hold, no cooperative launch, not one CTA per SM): the caller then takes the per-block launches.
 bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* esum,
                                 const double* es, double* mu, double* mu_new, double* eind, double* delta, const double* tens,
-                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s,
-                                unsigned long long* trace) {
+                                const double* ctab, double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag,
+                                cudaStream_t s, unsigned long long* trace) {
     const int nb = (pol.n + TILE - 1) / TILE;
     if (nb <= 0) return true;
     int dev = 0, sms = 0, coop = 0;
@@ -1383,6 +1443,7 @@ bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol,
     a.esum = esum;
     a.es = es;
     a.tens = tens;
+    a.ctab = reinterpret_cast<const double2*>(ctab);
     a.mu = mu;
     a.mu_new = mu_new;
     a.eind = eind;

@@ -11,6 +11,10 @@
 // The O(N^2) pair_t lists and the 3N x 3N A matrix are never built: device memory is O(N).
 #include <algorithm>
 #include <cmath>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -115,6 +119,48 @@ enum Slot {
 
 }  // namespace
 
+// One host thread per extra rank of a device group: the ranks' launches are issued side by side (one thread issuing
+// ~60 launches per evaluation to each of 8 devices in turn put 2.4 ms of launch latency on an 6 ms evaluation).
+struct RankWorker {
+    std::thread th;
+    std::mutex m;
+    std::condition_variable cv;
+    std::function<void()> job;
+    bool has_job = false, done = false, quit = false;
+    void loop() {
+        std::unique_lock<std::mutex> lk(m);
+        for (;;) {
+            cv.wait(lk, [&] { return has_job || quit; });
+            if (quit) return;
+            lk.unlock();
+            job();
+            lk.lock();
+            has_job = false;
+            done = true;
+            cv.notify_all();
+        }
+    }
+    void submit(std::function<void()> f) {
+        std::lock_guard<std::mutex> lk(m);
+        job = std::move(f);
+        has_job = true;
+        done = false;
+        cv.notify_all();
+    }
+    void wait() {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return done; });
+    }
+    void stop() {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            quit = true;
+            cv.notify_all();
+        }
+        if (th.joinable()) th.join();
+    }
+};
+
 struct mpmc_b200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -172,7 +218,7 @@ struct mpmc_b200_ctx {
     DevBuf<double> g_es, g_mu, g_mu_old, g_mu_new, g_eind, g_eic, g_rrms, g_delta, g_coef;  // GS space
     bool gs_delta = true;  // delta form of the sweep (symmetric Jacobi part + block pushes); MPMC_B200_GS=panels: panel form
     bool gs_persistent = true;  // one cooperative launch per sweep (resolver + pushers); MPMC_B200_GS=blocks: two launches per block
-    DevBuf<double> g_tens, g_pushacc;
+    DevBuf<double> g_tens, g_pushacc, g_ctab;
     DevBuf<unsigned> gs_flags;
     unsigned gs_epoch = 0;
     DevBuf<unsigned long long> gs_trace;  // MPMC_B200_GS_TRACE=1: resolver time stamps of the last sweep, summarised on stderr
@@ -241,6 +287,8 @@ struct mpmc_b200_ctx {
     bool scalars_complete = false;  // the device scalars of the pending evaluation are already summed over the ranks
     std::vector<mpmc_b200_ctx*> group;  // leader only (mpmc_b200_create_group): every rank's context, this one first
     bool group_member = false;          // owned by a leader: destroyed with it
+    std::vector<RankWorker*> workers;   // leader only: host threads that issue ranks 1.. (MPMC_B200_GROUP_THREADS=0: none)
+    bool layout_dirty = true;           // buffers may still be (re)allocated by the next evaluation: see sharded_eval
     cudaStream_t side = nullptr;  // K1 / K2 overlap with the polarization solve
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool side_active = false;
@@ -724,6 +772,7 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
 
 static int repack(Ctx* c) {
     const int n = c->n;
+    c->layout_dirty = true;
     c->inc_valid = false;
     c->inc_moved.clear();
     c->inc_slot.assign(n, 0);
@@ -1577,7 +1626,8 @@ static int enqueue_polar(Ctx* c) {
                 c->g_eind.ensure(3 * (size_t)pp) || c->g_eic.ensure(3 * (size_t)pp) || c->g_rrms.ensure(pp) ||
                 c->g_delta.ensure(3 * (size_t)pp) ||
                 (c->gs_delta && !c->gs_persistent && c->g_coef.ensure(gs_block_coeff_doubles(pp))) ||
-                (c->gs_delta && c->gs_persistent && (c->g_tens.ensure(gs_block_tensor_doubles(pp)) || c->g_pushacc.ensure(3 * (size_t)pp))))
+                (c->gs_delta && c->gs_persistent && (c->g_tens.ensure(gs_block_tensor_doubles(pp)) || c->g_pushacc.ensure(3 * (size_t)pp) ||
+                                                      c->g_ctab.ensure(gs_pair_coeff_doubles(pp)))))
                 FAIL(11, "cudaMalloc failed");
             if (c->gs_delta && c->gs_persistent && getenv("MPMC_B200_GS_TRACE") && c->gs_trace.ensure((size_t)(pp / TILE) * 8 + 8))
                 FAIL(11, "cudaMalloc failed");
@@ -1620,7 +1670,7 @@ static int enqueue_polar(Ctx* c) {
             if (c->gs_delta) {  // cluster boxes of the atoms in processing order, for the symmetric Jacobi part of a sweep
                 launch_cluster_boxes(cell, ortho, g, c->cbox.p, st);
                 if (c->gs_persistent)
-                    launch_gs_block_tensors(cell, ortho, g, dop, c->g_tens.p, st);  // in-sub-block tensors of this order
+                    launch_gs_block_tensors(cell, ortho, g, dop, c->g_tens.p, c->g_ctab.p, st);  // tables of this order
                 else
                     launch_gs_block_coeffs(cell, ortho, g, dop, c->g_coef.p, st);  // in-block tensor coefficients of this order
                 c->launches += 2;
@@ -1679,7 +1729,7 @@ static int enqueue_polar(Ctx* c) {
                         launch_dipole_contract_sym(cell, ortho, g, dop, c->g_mu.p, c->cbox.p, 0, 1, c->sym_ysplits, c->sym_partI.p,
                                                    c->sym_partJ.p, c->esum.p, st);
                         one_launch = launch_gs_sweep_persistent(cell, ortho, g, dop, c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p,
-                                                                c->g_eind.p, c->g_delta.p, c->g_tens.p, c->g_pushacc.p,
+                                                                c->g_eind.p, c->g_delta.p, c->g_tens.p, c->g_ctab.p, c->g_pushacc.p,
                                                                 c->gs_flags.p, ++c->gs_epoch, c->scalars.p + S_GS_TIMEOUT, st,
                                                                 c->gs_trace.p);
                         c->launches += 3;
@@ -1994,7 +2044,7 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
 // issued rank by rank from one host thread; a kernel that waits for a peer's flag is only ever enqueued after every
 // allocation of the evaluation has been made (cudaMalloc may synchronise devices that map each other's memory).
 // ================================================================================================
-static int sharded_eval(Ctx** cs, int nl, bool with_pair, mpmc_b200_energies* out) {
+static int sharded_enqueue(Ctx** cs, int nl, bool with_pair) {
     Ctx* c0 = cs[0];
     const mpmc_b200_params& P = c0->P;
     for (int i = 0; i < nl; i++) {
@@ -2109,7 +2159,51 @@ static int sharded_eval(Ctx** cs, int nl, bool with_pair, mpmc_b200_energies* ou
         return 0;
     });
 #undef RUN
+    return 0;
+}
+
+static int sharded_eval(Ctx** cs, int nl, bool with_pair, mpmc_b200_energies* out) {
+    Ctx* c0 = cs[0];
+    // The ranks of a device group are issued by one host thread each -- except for the first evaluation after the
+    // layout or the options changed: that one may still allocate (cudaMalloc can synchronise devices that map each
+    // other's memory, and a rank blocked there while a peer's kernel waits for its flag would dead-lock), so it goes
+    // stage by stage from this thread, where every allocation precedes every waiting kernel.
+    bool parallel = nl > 1 && (int)c0->workers.size() == nl - 1;
+    for (int i = 0; i < nl; i++) parallel = parallel && !cs[i]->layout_dirty;
     int rc_all = 0;
+    if (parallel) {
+        std::vector<int> rcs(nl, 0);
+        std::vector<std::string> msgs(nl);
+        for (int i = 1; i < nl; i++)
+            c0->workers[i - 1]->submit([&, i] {
+                Ctx* one = cs[i];
+                rcs[i] = sharded_enqueue(&one, 1, with_pair);
+                if (rcs[i]) msgs[i] = g_err;  // g_err is per thread
+            });
+        rcs[0] = sharded_enqueue(cs, 1, with_pair);
+        if (rcs[0]) msgs[0] = g_err;
+        for (int i = 1; i < nl; i++) c0->workers[i - 1]->wait();
+        for (int i = 0; i < nl; i++)
+            if (rcs[i] && !rc_all) {
+                rc_all = rcs[i];
+                g_err = msgs[i];
+            }
+    } else
+        rc_all = sharded_enqueue(cs, nl, with_pair);
+    if (rc_all) {  // leave no evaluation half enqueued: wait for what was launched (peer waits time out on their own)
+        const std::string keep = g_err;
+        for (int i = 0; i < nl; i++) {
+            cudaSetDevice(cs[i]->device);
+            cudaStreamSynchronize(cs[i]->stream);
+            if (cs[i]->side) cudaStreamSynchronize(cs[i]->side);
+            cs[i]->side_active = false;
+            cs[i]->pending = false;
+        }
+        cudaGetLastError();
+        cudaSetDevice(c0->device);
+        g_err = keep;
+        return rc_all;
+    }
     for (int i = 0; i < nl; i++) {
         Ctx* c = cs[i];
         CU(cudaSetDevice(c->device));
@@ -2118,6 +2212,7 @@ static int sharded_eval(Ctx** cs, int nl, bool with_pair, mpmc_b200_energies* ou
         c->scalars_complete = false;
         if (rc && !rc_all) rc_all = rc;
         if (i == 0 && !rc) *out = e;
+        if (!rc) c->layout_dirty = false;
     }
     CU(cudaSetDevice(c0->device));
     return rc_all;
@@ -2270,6 +2365,15 @@ int mpmc_b200_create_group(mpmc_b200_ctx** out, int ndev, const int* devices) {
             }
         }
     g[0]->group = g;
+    {
+        const char* v = getenv("MPMC_B200_GROUP_THREADS");  // 0: every rank issued from the caller's thread, stage by stage
+        if (!(v && v[0] == '0'))
+            for (int i = 1; i < ndev; i++) {
+                RankWorker* w = new RankWorker();
+                w->th = std::thread([w] { w->loop(); });
+                g[0]->workers.push_back(w);
+            }
+    }
     cudaSetDevice(g[0]->device);
     *out = g[0];
     return 0;
@@ -2279,6 +2383,11 @@ int mpmc_b200_group_size(mpmc_b200_ctx* c) { return !c ? 0 : c->group.empty() ? 
 
 void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     if (!c) return;
+    for (RankWorker* w : c->workers) {
+        w->stop();
+        delete w;
+    }
+    c->workers.clear();
     if (!c->group.empty()) {  // a group leader owns the other ranks' contexts
         std::vector<mpmc_b200_ctx*> members(c->group.begin() + 1, c->group.end());
         c->group.clear();
@@ -2304,7 +2413,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
                               &c->kweight_field, &c->kvec, &c->sf_partial, &c->sf, &c->ef_static, &c->epart, &c->es, &c->mu,
                               &c->mu_old, &c->mu_new, &c->eind, &c->eic, &c->rrms, &c->rank_packed, &c->rmin_part,
                               &c->field_cnt, &c->g_es, &c->g_mu, &c->g_mu_old, &c->g_mu_new, &c->g_eind, &c->g_eic, &c->g_rrms, &c->g_delta, &c->g_coef,
-                              &c->g_tens, &c->g_pushacc,
+                              &c->g_tens, &c->g_pushacc, &c->g_ctab,
                               &c->wolf_table, &c->scalars, &c->cbox, &c->sym_partI, &c->sym_partJ, &c->esum})
         b->release();
     for (DevBuf<int>* b : {&c->mol, &c->flags, &c->kl, &c->perm}) b->release();
@@ -2370,6 +2479,7 @@ int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
     if (check_supported(*p)) return 3;  // refused parameters leave the context as it was
     c->inc_valid = false;
     c->warm_valid = false;
+    c->layout_dirty = true;
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;

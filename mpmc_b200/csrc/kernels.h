@@ -218,11 +218,13 @@ void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, cons
 // tens: gs_block_tensor_doubles(n_pad) doubles from launch_gs_block_tensors for the SAME order; pushacc [3][n_pad];
 // flags [2 * n_pad / 128] unsigned zeroed at allocation; epoch > 0 and increasing.  false = not launchable here.
 size_t gs_block_tensor_doubles(int n_pad);
-void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* tens, cudaStream_t s);
+size_t gs_pair_coeff_doubles(int n_pad);  // (c1, c2) of the pairs the resolver applies itself: [blocks][2][128][128] double2
+void launch_gs_block_tensors(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, double* tens, double* ctab,
+                             cudaStream_t s);
 bool launch_gs_sweep_persistent(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* esum,
                                 const double* es, double* mu, double* mu_new, double* eind, double* delta, const double* tens,
-                                double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag, cudaStream_t s,
-                                unsigned long long* trace = nullptr /* [blocks][8] resolver time stamps (profiling) */);
+                                const double* ctab, double* pushacc, unsigned* flags, unsigned epoch, double* timeout_flag,
+                                cudaStream_t s, unsigned long long* trace = nullptr /* [blocks][8] resolver time stamps */);
 // rank metric of pairs() (src/energy/pairs.c:337-360)
 void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank /*[pol n_pad]*/,
                         cudaStream_t s);

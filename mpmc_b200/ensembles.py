@@ -60,6 +60,14 @@ def parse_devices(spec: Optional[str], n: int) -> List[int]:
     return dev
 
 
+def host_threads_per_chain(chains: int) -> int:
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        cores = os.cpu_count() or 1
+    return max(1, min(8, (cores - 1) // max(chains, 1)))
+
+
 def seeded_input(text: str, seed: int) -> str:
     """The input with `preset_seeds <seed>` (src/io/input.c:118-122), replacing any seed line it had."""
     lines = [l for l in text.splitlines() if not re.match(r"^\s*(preset_seeds|seed)\b", l)]
@@ -93,6 +101,10 @@ def launch(input_path: str, chains: int, devices: Optional[Sequence[int]] = None
         for v in ("MPMC_B200_DEVICES", "MPMC_B200_GPUS"):
             e.pop(v, None)
         e["MPMC_B200_DEVICE"] = str(devices[k % len(devices)])
+        # the chains share the host: split the cores between their shims' host threads (8 chains x 8 spinning OpenMP
+        # threads on 16 cores cost each chain 3.6x, profiles/r02_multi_gpu.md) and let idle threads sleep
+        e.setdefault("MPMC_B200_HOST_THREADS", str(host_threads_per_chain(chains)))
+        e.setdefault("OMP_WAIT_POLICY", "PASSIVE")
         procs.append((k, d, subprocess.Popen([program, "input"], cwd=d, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
                                              env=e), time.perf_counter()))
     results = []
