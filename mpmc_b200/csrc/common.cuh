@@ -143,6 +143,29 @@ __device__ __forceinline__ double cluster_gap2(const BoxLen& k, const double* __
     return g2;
 }
 
+// Upper bound of the same distance^2 (for the image the centres pick): per axis |minimg(centre_a - centre_b)| +
+// (half_a + half_b).  A cluster pair whose span is inside the cutoff has EVERY atom pair inside it.
+__device__ __forceinline__ double cluster_span2(const BoxLen& k, const double* __restrict__ a, int na, int ca,
+                                                const double* __restrict__ b, int nb, int cb) {
+    double s2 = 0.0;
+    {
+        double d = a[0 * na + ca] - b[0 * nb + cb];
+        d = fabs(fma(-k.Lx, rint(d * k.iLx), d)) + (a[3 * na + ca] + b[3 * nb + cb]);
+        s2 = fma(d, d, s2);
+    }
+    {
+        double d = a[1 * na + ca] - b[1 * nb + cb];
+        d = fabs(fma(-k.Ly, rint(d * k.iLy), d)) + (a[4 * na + ca] + b[4 * nb + cb]);
+        s2 = fma(d, d, s2);
+    }
+    {
+        double d = a[2 * na + ca] - b[2 * nb + cb];
+        d = fabs(fma(-k.Lz, rint(d * k.iLz), d)) + (a[5 * na + ca] + b[5 * nb + cb]);
+        s2 = fma(d, d, s2);
+    }
+    return s2;
+}
+
 // ---- fast fp64 helpers shared by the dipole kernels (K: a by-value kernel parameter struct with `double ec[12]` = 1/k!)
 // 1/sqrt(a): MUFU.RSQ64H seed (2^-22.9) + one third-order step, no range checks (a is a squared distance
 // between distinct atoms).  5 fp64 instructions like the library's fast path, without its slow-path test.

@@ -189,10 +189,12 @@ static void contract_dispatch(const Cell& c, bool ortho, const SubsetDev& pol, c
 // palmo_contraction() (thole_iterative.c:119-141) runs over every atom, so non-polarizable atoms
 // get ef_induced_change = - sum_j T_ij mu_j as well (their rows of A exist, thole_matrix.c:73-143);
 // the values never enter an energy (mu_i = 0) but are written back to atom_t.
+// blockIdx.y = slice of the source tiles (tiles_per_split each): with ~140 row tiles at 63k atoms an unsplit launch left
+// every SM with one 4-warp CTA walking 46k sources (7 ms); the slices' partial rows are added in slice order.
 template <bool ORTHO, int DAMP, bool WF>
 __global__ void __launch_bounds__(TILE) dipole_field_at_kernel(Cell c, SubsetDev rows, SubsetDev p, DipoleConsts k,
                                                                const double* __restrict__ mu, int row_begin,
-                                                               double* __restrict__ out) {
+                                                               int tiles_per_split, double* __restrict__ out) {
     __shared__ double sx[TILE], sy[TILE], sz[TILE], smx[TILE], smy[TILE], smz[TILE], saux[TILE];
     __shared__ int smol[TILE];
     const int tid = threadIdx.x;
@@ -202,7 +204,8 @@ __global__ void __launch_bounds__(TILE) dipole_field_at_kernel(Cell c, SubsetDev
     const int moli = rows.mol[i];
     const int np = p.n_pad;
     double ex = 0.0, ey = 0.0, ez = 0.0;
-    for (int jt = 0; jt < np / TILE; jt++) {
+    const int t0 = blockIdx.y * tiles_per_split, t1 = min(t0 + tiles_per_split, np / TILE);
+    for (int jt = t0; jt < t1; jt++) {
         __syncthreads();
         const int j = jt * TILE + tid;
         sx[tid] = p.x[j];
@@ -215,24 +218,51 @@ __global__ void __launch_bounds__(TILE) dipole_field_at_kernel(Cell c, SubsetDev
         smol[tid] = p.mol[j];
         __syncthreads();
         const int jn = min(TILE, p.n - jt * TILE);
+#pragma unroll 2
         for (int jj = 0; jj < jn; jj++)
             tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[jj], yi - sy[jj], zi - sz[jj], smx[jj], smy[jj], smz[jj], auxi,
                                           saux[jj], moli == smol[jj], ex, ey, ez);
     }
     const bool live = i < rows.n;
-    out[i] = live ? ex : 0.0;
-    out[rows.n_pad + i] = live ? ey : 0.0;
-    out[2 * rows.n_pad + i] = live ? ez : 0.0;
+    double* o = out + (size_t)blockIdx.y * 3 * rows.n_pad;
+    o[i] = live ? ex : 0.0;
+    o[rows.n_pad + i] = live ? ey : 0.0;
+    o[2 * rows.n_pad + i] = live ? ez : 0.0;
+}
+
+// out[c][i] = sum over slices (slice order) of part[slice][c][i], rows [row_begin, row_end)
+__global__ void field_at_reduce_kernel(const double* __restrict__ part, int splits, int np, int row_begin, int row_end,
+                                       double* __restrict__ out) {
+    const int i = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= row_end) return;
+    for (int cdim = 0; cdim < 3; cdim++) {
+        double e = 0.0;
+        for (int js = 0; js < splits; js++) e += part[((size_t)js * 3 + cdim) * np + i];
+        out[(size_t)cdim * np + i] = e;
+    }
+}
+
+int dipole_field_at_splits(int row_tiles, int src_tiles) {
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int js = (4 * sms + row_tiles - 1) / (row_tiles > 0 ? row_tiles : 1);
+    if (js > src_tiles) js = src_tiles;
+    return js < 1 ? 1 : js;
 }
 
 void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, const SubsetDev& pol, const DipoleOpts& o,
-                            const double* mu, int row_begin, int row_end, double* out, cudaStream_t s) {
+                            const double* mu, int row_begin, int row_end, double* out, cudaStream_t s, double* part) {
     const int n = row_end - row_begin;
     if (n <= 0 || pol.n <= 0) return;
     const DipoleConsts k = make_consts(c, o);
-    const int grid = n / TILE;
+    const int src_tiles = pol.n_pad / TILE;
+    const int js = part ? dipole_field_at_splits(n / TILE, src_tiles) : 1;
+    const int tps = (src_tiles + js - 1) / js;
+    const dim3 grid(n / TILE, (src_tiles + tps - 1) / tps);
+    double* dst = part ? part : out;
 #define LAUNCH(ORTHO, DAMP, WF) \
-    dipole_field_at_kernel<ORTHO, DAMP, WF><<<grid, TILE, 0, s>>>(c, rows, pol, k, mu, row_begin, out)
+    dipole_field_at_kernel<ORTHO, DAMP, WF><<<grid, TILE, 0, s>>>(c, rows, pol, k, mu, row_begin, tps, dst)
 #define DISPATCH(ORTHO)                                              \
     if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
         if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true); \
@@ -250,6 +280,7 @@ void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, co
     }
 #undef DISPATCH
 #undef LAUNCH
+    if (part) field_at_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(part, (int)grid.y, rows.n_pad, row_begin, row_end, out);
 }
 
 void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
@@ -1592,62 +1623,98 @@ void launch_gs_sweep_delta(const Cell& c, bool ortho, const SubsetDev& pol, cons
 // polarizable atoms; rank_i = number of polarizable partners whose UN-imaged separation is
 // <= 1.5 rmin (the reference mixes the two on purpose or not; reproduced).
 // ------------------------------------------------------------------------------------------------
+// Rank metric of pairs() (src/energy/pairs.c:337-360): rmin = the smallest minimum-image separation of two polarizable
+// atoms; rank_metric_i = the number of polarizable atoms within 1.5 rmin of atom i by the UN-imaged distance.  Both are
+// all-pairs tests, so the only things that matter are filling the GPU (source tiles split over gridDim.y) and keeping
+// the square root out of the loop.  That is exact: sqrt is monotone and correctly rounded, so min sqrt(r2) = sqrt(min r2),
+// and sqrt(r2) <= lim holds exactly when r2 <= t2 with t2 the largest double whose square root is <= lim
+// (rank_finish_kernel finds it by stepping through the neighbouring doubles).  Counts are whole numbers far below 2^53:
+// adding them with atomicAdd is exact in any order.
+constexpr int RANK_MAX_SPLITS = 8;
 template <bool ORTHO, int PASS>
-__global__ void __launch_bounds__(TILE) rank_kernel(Cell c, SubsetDev p, const double* __restrict__ rmin_in,
+__global__ void __launch_bounds__(TILE) rank_kernel(Cell c, SubsetDev p, const double* __restrict__ lim_in, int tiles_per_split,
                                                     double* __restrict__ out) {
     __shared__ double sx[TILE], sy[TILE], sz[TILE];
     __shared__ double red[32];
     const int tid = threadIdx.x, i = blockIdx.x * TILE + tid;
     const double xi = p.x[i], yi = p.y[i], zi = p.z[i];
-    const double lim = PASS == 1 ? rmin_in[0] * 1.5 : 0.0;
-    double best = kMAXVALUE, count = 0.0;
-    for (int jt = 0; jt < p.n_pad / TILE; jt++) {
+    const double t2 = PASS == 1 ? lim_in[2] : 0.0;
+    double best2 = kMAXVALUE;
+    int count = 0;
+    const int t0 = blockIdx.y * tiles_per_split, t1 = min(t0 + tiles_per_split, p.n_pad / TILE);
+    for (int jt = t0; jt < t1; jt++) {
         __syncthreads();
         sx[tid] = p.x[jt * TILE + tid];
         sy[tid] = p.y[jt * TILE + tid];
         sz[tid] = p.z[jt * TILE + tid];
         __syncthreads();
         const int jn = min(TILE, p.n - jt * TILE);
+        const bool own = jt == (int)blockIdx.x;
+#pragma unroll 4
         for (int jj = 0; jj < jn; jj++) {
-            if (jt * TILE + jj == i) continue;
             double dx = xi - sx[jj], dy = yi - sy[jj], dz = zi - sz[jj];
-            if (PASS == 0) {
-                min_image<ORTHO>(c, dx, dy, dz);
-                best = fmin(best, sqrt(dx * dx + dy * dy + dz * dz));
-            } else {
-                if (sqrt(dx * dx + dy * dy + dz * dz) <= lim) count += 1.0;
-            }
+            if (PASS == 0) min_image<ORTHO>(c, dx, dy, dz);
+            const double r2 = dx * dx + dy * dy + dz * dz;
+            const bool self = own && jj == tid;
+            if (PASS == 0)
+                best2 = self ? best2 : fmin(best2, r2);
+            else
+                count += (!self && r2 <= t2) ? 1 : 0;
         }
     }
     if (PASS == 0) {
-        if (i >= p.n) best = kMAXVALUE;
-        best = block_reduce<1>(best, red);
-        if (tid == 0) out[blockIdx.x] = best;
-    } else {
-        out[i] = (i < p.n) ? count : 0.0;
-    }
+        if (i >= p.n) best2 = kMAXVALUE;
+        best2 = block_reduce<1>(best2, red);
+        if (tid == 0) out[blockIdx.y * gridDim.x + blockIdx.x] = best2;
+    } else if (i < p.n && count > 0)
+        atomicAdd(out + i, (double)count);
 }
 
-__global__ void min_reduce_kernel(const double* __restrict__ in, int n, double* __restrict__ out) {
+// out[0] = rmin, out[1] = lim = 1.5 rmin (pairs.c:352), out[2] = the largest r2 with sqrt(r2) <= lim
+__global__ void rank_finish_kernel(const double* __restrict__ in, int n, double* __restrict__ out) {
     __shared__ double red[32];
     double best = kMAXVALUE;
     for (int i = threadIdx.x; i < n; i += blockDim.x) best = fmin(best, in[i]);
     best = block_reduce<1>(best, red);
-    if (threadIdx.x == 0) out[0] = best;
+    if (threadIdx.x == 0) {
+        const double rmin = sqrt(best);
+        const double lim = rmin * 1.5;
+        double x = lim * lim;
+        for (int it = 0; it < 8 && sqrt(x) > lim; it++) x = __longlong_as_double(__double_as_longlong(x) - 1);
+        for (int it = 0; it < 8; it++) {
+            const double up = __longlong_as_double(__double_as_longlong(x) + 1);
+            if (!(sqrt(up) <= lim)) break;
+            x = up;
+        }
+        out[0] = rmin;
+        out[1] = lim;
+        out[2] = x;
+    }
 }
 
 void launch_rank_metric(const Cell& c, bool ortho, const SubsetDev& pol, double* rmin_part, double* rank, cudaStream_t s) {
     const int nt = pol.n_pad / TILE;
     if (nt <= 0) return;
-    // rmin_part: [nt] block minima followed by one slot for the global minimum
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int js = (8 * sms + nt - 1) / nt;
+    js = js < 1 ? 1 : (js > RANK_MAX_SPLITS ? RANK_MAX_SPLITS : js);
+    if (js > nt) js = nt;
+    const int tps = (nt + js - 1) / js;
+    js = (nt + tps - 1) / tps;
+    const dim3 grid(nt, js);
+    // rmin_part: [js * nt] block minima of r^2, then rmin / lim / t2 (needs RANK_MAX_SPLITS * nt + 8 doubles)
+    double* fin = rmin_part + (size_t)js * nt;
+    cudaMemsetAsync(rank, 0, sizeof(double) * pol.n_pad, s);
     if (ortho) {
-        rank_kernel<true, 0><<<nt, TILE, 0, s>>>(c, pol, nullptr, rmin_part);
-        min_reduce_kernel<<<1, 1024, 0, s>>>(rmin_part, nt, rmin_part + nt);
-        rank_kernel<true, 1><<<nt, TILE, 0, s>>>(c, pol, rmin_part + nt, rank);
+        rank_kernel<true, 0><<<grid, TILE, 0, s>>>(c, pol, nullptr, tps, rmin_part);
+        rank_finish_kernel<<<1, 1024, 0, s>>>(rmin_part, js * nt, fin);
+        rank_kernel<true, 1><<<grid, TILE, 0, s>>>(c, pol, fin, tps, rank);
     } else {
-        rank_kernel<false, 0><<<nt, TILE, 0, s>>>(c, pol, nullptr, rmin_part);
-        min_reduce_kernel<<<1, 1024, 0, s>>>(rmin_part, nt, rmin_part + nt);
-        rank_kernel<false, 1><<<nt, TILE, 0, s>>>(c, pol, rmin_part + nt, rank);
+        rank_kernel<false, 0><<<grid, TILE, 0, s>>>(c, pol, nullptr, tps, rmin_part);
+        rank_finish_kernel<<<1, 1024, 0, s>>>(rmin_part, js * nt, fin);
+        rank_kernel<false, 1><<<grid, TILE, 0, s>>>(c, pol, fin, tps, rank);
     }
 }
 

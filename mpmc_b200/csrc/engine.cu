@@ -179,6 +179,7 @@ struct mpmc_b200_ctx {
     DevBuf<int> mol, flags;
     Subset charged, recip, pol, gs;  // gs: polarizable atoms permuted into Gauss-Seidel order
     Subset nonpol;                   // alpha == 0 atoms: rows of the palmo field that are only written back
+    DevBuf<double> eic_np_part;      // [source slices][3][nonpol.n_pad] partial rows of the same
     DevBuf<double> eic_np;           // [3][nonpol.n_pad]
     bool eic_np_valid = false;
     DevBuf<double> eind_np;          // [3][nonpol.n_pad]: ef_induced of the alpha == 0 atoms (full-Ewald polarization only)
@@ -930,7 +931,7 @@ static int repack(Ctx* c) {
     if (c->ef_static.ensure((size_t)3 * np) || c->epart.ensure(epart_need) || c->es.ensure((size_t)3 * pp) ||
         c->mu.ensure((size_t)3 * pp) || c->mu_old.ensure((size_t)3 * pp) || c->mu_new.ensure((size_t)3 * pp) ||
         c->eind.ensure((size_t)3 * pp) || c->eic.ensure((size_t)3 * pp) || c->rrms.ensure(pp) ||
-        c->rank_packed.ensure(pp) || c->rmin_part.ensure(ptiles + 8) ||
+        c->rank_packed.ensure(pp) || c->rmin_part.ensure((size_t)8 * ptiles + 8) ||
         c->field_cnt.ensure((size_t)std::max(c->field_jsplits * (np / TILE), np / 32) + 40))
         FAIL(11, "cudaMalloc failed");
     {
@@ -1392,9 +1393,11 @@ static int palmo_nonpolar_rows(Ctx* c, const SubsetDev& src, const double* mu) {
     shard_range(c->nonpol.n_pad / TILE, c->rank, c->world, tb, te);
     CU(cudaMemsetAsync(c->eic_np.p, 0, sizeof(double) * 3 * c->nonpol.n_pad, c->stream));
     if (te > tb) {
+        const int js = dipole_field_at_splits(te - tb, src.n_pad / TILE);
+        if (c->eic_np_part.ensure((size_t)js * 3 * c->nonpol.n_pad)) FAIL(11, "cudaMalloc failed");
         launch_dipole_field_at(make_cell(c->P), is_ortho(c->P), c->nonpol.dev(), src, dipole_opts(c->P), mu, tb * TILE,
-                               te * TILE, c->eic_np.p, c->stream);
-        c->launches++;
+                               te * TILE, c->eic_np.p, c->stream, c->eic_np_part.p);
+        c->launches += 2;
     }
     c->eic_np_valid = true;
     CU(cudaGetLastError());
@@ -2429,6 +2432,7 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     c->pol.release();
     c->nonpol.release();
     c->eic_np.release();
+    c->eic_np_part.release();
     c->eind_np.release();
     c->wb.release();
     c->gs.release();

@@ -131,8 +131,11 @@ void launch_dipole_contract(const Cell& c, bool ortho, const SubsetDev& pol, con
                             int row_begin, int row_end, int jsplits, double* epart /*[jsplits][3][n_pad]*/,
                             cudaStream_t s);
 // palmo: field of the dipoles at the atoms of `rows` (the non-polarizable atoms), out[3][rows.n_pad]
+// part (optional): [dipole_field_at_splits(row tiles, source tiles)][3][rows.n_pad] scratch -- the source tiles are then
+// split over gridDim.y and the slices' partial rows added in slice order (few row tiles would leave the GPU empty)
+int dipole_field_at_splits(int row_tiles, int src_tiles);
 void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, const SubsetDev& pol, const DipoleOpts& o,
-                            const double* mu, int row_begin, int row_end, double* out, cudaStream_t s);
+                            const double* mu, int row_begin, int row_end, double* out, cudaStream_t s, double* part = nullptr);
 // Symmetric form of the contraction (dipole_sym_kernel.cu): T_ij computed once per unordered pair and
 // applied in both directions.  Work items = (I super tile of 256 atoms) x (slice of the offsets 0..S/2, `ysplits` slices); rank r of
 // `world` takes the r-th contiguous share of the flattened items;

@@ -14,6 +14,10 @@
 //   coulombic_wolf()   src/energy/coulombic.c:269-308 (option `wolf`; replaces real + reciprocal + self)
 //   lj() with rd_crystal   src/energy/lj.c:175-216 (image sums; crystal_lj_kernel below)
 //   cavity_absolute_check()  src/energy/energy.c:49-64
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
 #include "kernels.h"
 
 namespace mpmc {
@@ -79,90 +83,112 @@ struct PairAcc {
     int n_tested, n_lj, n_es;
 };
 
+// What is known about a pair before any expensive term: the minimum-image separation and which terms apply.
+struct PairScreen {
+    double r2, r, qq;
+    bool do_lj, do_es;
+};
+
+// pair_exclusions + minimum_image + the range tests of lj() and coulombic_real(): false when the pair adds nothing
+// beyond what is accumulated here (the intramolecular erf term, the minimum intermolecular distance, the count)
+template <bool ORTHO, int FH>
+__device__ __forceinline__ bool pair_screen(const Cell& c, const PairConsts& k, int rd_only, double xi, double yi, double zi,
+                                            double qi, int moli, int fli, bool lj_i, double xj, double yj, double zj,
+                                            double qj, double ej, double sj, int molj, int fj, PairAcc& A, PairScreen& g) {
+    // skip padding and frozen-frozen pairs (pairs.c:81, lj.c:193, coulombic.c:165)
+    if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) return false;
+    double dx = xi - xj, dy = yi - yj, dz = zi - zj;
+    g.qq = qi * qj;
+    if (moli == molj) {
+        // same molecule: rd and es excluded (pairs.c:61-64); charge-to-screen term with the
+        // UN-imaged separation (coulombic.c:179-180)
+        if (!rd_only && g.qq != 0.0 && !(FH == 0 && k.wolf)) {
+            double r = sqrt(dx * dx + dy * dy + dz * dz);
+            A.intra += g.qq * erf(k.alpha * r) / r;
+        }
+        return false;
+    }
+    min_image<ORTHO>(c, dx, dy, dz);
+    g.r2 = dx * dx + dy * dy + dz * dz;
+    g.r = sqrt(g.r2);
+    A.n_tested++;
+    A.minr = fmin(A.minr, g.r);
+    g.do_lj = (g.r - kSMALL_dR < k.cutoff) && lj_i && (ej != 0.0) && (sj != 0.0);
+    // coulombic.c:167 skips r > cutoff; coulombic_wolf() keeps r < R only (coulombic.c:288)
+    g.do_es = !rd_only && ((FH == 0 && k.wolf) ? (g.r < k.cutoff) : !(g.r > k.cutoff)) && (g.qq != 0.0);
+    return g.do_lj || g.do_es;
+}
+
+// lj() + lj_fh_corr() and coulombic_real() + coulombic_real_FH() / coulombic_wolf() of a screened pair
+template <int FH>
+__device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, double ei, double si, double mi, double ej,
+                                          double sj, double mj, const PairScreen& g, PairAcc& A) {
+    const double r = g.r, r2 = g.r2, qq = g.qq;
+    const bool do_lj = g.do_lj, do_es = g.do_es;
+    const double ir = 1.0 / r;
+    double mured = 0.0;
+    if (FH) mured = kAMU2KG * mi * mj / (mi + mj);
+
+    if (do_lj) {
+        double eps, sigma;
+        bool att;
+        mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
+        const double sor = fabs(sigma) * ir;
+        double s6 = sor * sor * sor;
+        s6 *= s6;
+        const double term6 = s6, term12 = att ? 0.0 : s6 * s6;
+        double u = 4.0 * eps * (term12 - term6);
+        if (FH) {  // lj.c:29-50
+            const double ir2 = ir * ir, ir3 = ir2 * ir, ir4 = ir3 * ir;
+            const double dE = -24.0 * eps * (2.0 * term12 - term6) * ir;
+            const double d2E = 24.0 * eps * (26.0 * term12 - 7.0 * term6) * ir2;
+            u += (k.fh2_pref / mured) * (d2E + 2.0 * dE * ir);
+            if (FH >= 4) {
+                const double d3E = -1344.0 * eps * (6.0 * term12 - term6) * ir3;
+                const double d4E = 12096.0 * eps * (10.0 * term12 - term6) * ir4;
+                u += (k.fh4_pref / (mured * mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
+            }
+        }
+        A.rd += u;
+        A.n_lj++;
+    }
+    if (FH == 0 && k.wolf) {
+        if (do_es) {  // coulombic.c:289-290
+            A.es += qq * (ir - k.wolf_shift - k.wolf_ir2 * (k.cutoff - r));
+            A.n_es++;
+        }
+    } else if (do_es) {
+        const double erfc_term = erfc(k.alpha * r);
+        double u = qq * erfc_term * ir;
+        if (FH) {  // coulombic.c:132-141
+            const double gaussian_term = exp(-k.a2 * r2);
+            const double ir2 = ir * ir, ir3 = ir * ir2, ir4 = ir2 * ir2;
+            const double gg = gaussian_term * k.inv_sqrt_pi;
+            const double du = -2.0 * k.alpha * gg * ir - erfc_term * ir2;
+            const double d2u = 4.0 * gg * (k.a3 + ir2) + 2.0 * erfc_term * ir3;
+            u += (k.fh2_pref / mured) * (d2u + 2.0 * du * ir);
+            if (FH >= 4) {
+                const double d3u = gg * (-8.0 * (k.a3 * k.a2) * r - 8.0 * k.a3 * ir - 12.0 * k.alpha * ir3) -
+                                   6.0 * erfc_term * ir4;
+                const double d4u = gg * (8.0 * k.a3 * k.a2 + 16.0 * k.a3 * k.a4 * r2 + 32.0 * k.a3 * ir2 + 48.0 * ir4) +
+                                   24.0 * erfc_term * (ir4 * ir);
+                u += (k.fh4_pref_es / (mured * mured)) * (15.0 * du * ir3 + 4.0 * d3u * ir + d4u);
+            }
+        }
+        A.es += u;
+        A.n_es++;
+    }
+}
+
 // all terms of one pair (i in registers, j given): pair_exclusions + minimum_image + lj + coulombic_real
 template <bool ORTHO, int FH>
 __device__ __forceinline__ void pair_terms(const Cell& c, const PairConsts& k, int mixing, int rd_only, double xi, double yi,
                                            double zi, double qi, double ei, double si, double mi, int moli, int fli,
                                            bool lj_i, double xj, double yj, double zj, double qj, double ej, double sj,
                                            double mj, int molj, int fj, PairAcc& A) {
-    do {
-        // skip padding and frozen-frozen pairs (pairs.c:81, lj.c:193, coulombic.c:165)
-        if (!((fli & fj) & F_VALID) || ((fli & fj) & F_FROZEN)) break;
-        double dx = xi - xj, dy = yi - yj, dz = zi - zj;
-        const double qq = qi * qj;
-        if (moli == molj) {
-            // same molecule: rd and es excluded (pairs.c:61-64); charge-to-screen term with the
-            // UN-imaged separation (coulombic.c:179-180)
-            if (!rd_only && qq != 0.0 && !(FH == 0 && k.wolf)) {
-                double r = sqrt(dx * dx + dy * dy + dz * dz);
-                A.intra += qq * erf(k.alpha * r) / r;
-            }
-            break;
-        }
-        min_image<ORTHO>(c, dx, dy, dz);
-        const double r2 = dx * dx + dy * dy + dz * dz;
-        const double r = sqrt(r2);
-        A.n_tested++;
-        A.minr = fmin(A.minr, r);
-
-                const bool do_lj = (r - kSMALL_dR < k.cutoff) && lj_i && (ej != 0.0) && (sj != 0.0);
-        // coulombic.c:167 skips r > cutoff; coulombic_wolf() keeps r < R only (coulombic.c:288)
-        const bool do_es = !rd_only && ((FH == 0 && k.wolf) ? (r < k.cutoff) : !(r > k.cutoff)) && (qq != 0.0);
-        if (!(do_lj || do_es)) break;
-        const double ir = 1.0 / r;
-        double mured = 0.0;
-        if (FH) mured = kAMU2KG * mi * mj / (mi + mj);
-
-        if (do_lj) {
-            double eps, sigma;
-            bool att;
-            mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
-            const double sor = fabs(sigma) * ir;
-            double s6 = sor * sor * sor;
-            s6 *= s6;
-            const double term6 = s6, term12 = att ? 0.0 : s6 * s6;
-            double u = 4.0 * eps * (term12 - term6);
-            if (FH) {  // lj.c:29-50
-                const double ir2 = ir * ir, ir3 = ir2 * ir, ir4 = ir3 * ir;
-                const double dE = -24.0 * eps * (2.0 * term12 - term6) * ir;
-                const double d2E = 24.0 * eps * (26.0 * term12 - 7.0 * term6) * ir2;
-                u += (k.fh2_pref / mured) * (d2E + 2.0 * dE * ir);
-                if (FH >= 4) {
-                    const double d3E = -1344.0 * eps * (6.0 * term12 - term6) * ir3;
-                    const double d4E = 12096.0 * eps * (10.0 * term12 - term6) * ir4;
-                    u += (k.fh4_pref / (mured * mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
-                }
-            }
-            A.rd += u;
-            A.n_lj++;
-        }
-        if (FH == 0 && k.wolf) {
-            if (do_es) {  // coulombic.c:289-290
-                A.es += qq * (ir - k.wolf_shift - k.wolf_ir2 * (k.cutoff - r));
-                A.n_es++;
-            }
-        } else if (do_es) {
-            const double erfc_term = erfc(k.alpha * r);
-            double u = qq * erfc_term * ir;
-            if (FH) {  // coulombic.c:132-141
-                const double gaussian_term = exp(-k.a2 * r2);
-                const double ir2 = ir * ir, ir3 = ir * ir2, ir4 = ir2 * ir2;
-                const double g = gaussian_term * k.inv_sqrt_pi;
-                const double du = -2.0 * k.alpha * g * ir - erfc_term * ir2;
-                const double d2u = 4.0 * g * (k.a3 + ir2) + 2.0 * erfc_term * ir3;
-                u += (k.fh2_pref / mured) * (d2u + 2.0 * du * ir);
-                if (FH >= 4) {
-                    const double d3u = g * (-8.0 * (k.a3 * k.a2) * r - 8.0 * k.a3 * ir - 12.0 * k.alpha * ir3) -
-                                       6.0 * erfc_term * ir4;
-                    const double d4u = g * (8.0 * k.a3 * k.a2 + 16.0 * k.a3 * k.a4 * r2 + 32.0 * k.a3 * ir2 + 48.0 * ir4) +
-                                       24.0 * erfc_term * (ir4 * ir);
-                    u += (k.fh4_pref_es / (mured * mured)) * (15.0 * du * ir3 + 4.0 * d3u * ir + d4u);
-                }
-            }
-            A.es += u;
-            A.n_es++;
-        }
-    } while (0);
+    PairScreen g;
+    if (pair_screen<ORTHO, FH>(c, k, rd_only, xi, yi, zi, qi, moli, fli, lj_i, xj, yj, zj, qj, ej, sj, molj, fj, A, g))
+        pair_body<FH>(k, mixing, ei, si, mi, ej, sj, mj, g, A);
 }
 
 template <bool ORTHO, int FH>
@@ -236,11 +262,20 @@ struct __align__(16) PairRec {
     int mol, fl;
 };
 
-template <bool ORTHO, int FH>
+// COMPACT (the default): a cluster pair is screened first -- every lane tests its atom against the 32 staged ones
+// (geometry, range, exclusions: ~35 instructions) and keeps a bit per pair that has an LJ or erfc term -- then the
+// surviving pairs of the whole cluster pair are dealt out densely, 32 at a time, for the expensive part (erfc, exp,
+// the Feynman-Hibbs polynomials: ~200 instructions).  Walking j for all lanes at once kept 16 of 32 lanes busy (ncu,
+// profiles/r01_k1_cluster_ncu_details.csv): a lane whose pair is outside the cutoff waited for its neighbours' bodies.
+// K1 only produces sums, so it does not matter which lane evaluates which pair; the order stays a pure function of
+// the input (bit-reproducible).
+template <bool ORTHO, int FH, bool COMPACT>
 __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a, PairConsts k, BoxLen box, int mixing,
                                                             int rd_only, int clus_begin, int clus_end, int kper, double cull2,
                                                             double* __restrict__ partial, int stride) {
     __shared__ PairRec rec[4][32];
+    __shared__ PairRec irec[COMPACT ? 4 : 1][32];
+    __shared__ unsigned short plist[COMPACT ? 4 : 1][1024];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int ci = clus_begin + blockIdx.x * 4 + w;
     if (ci >= clus_end) return;  // whole warp; no block-level barrier is used below
@@ -250,6 +285,11 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
     const int moli = a.mol[i], fli = a.flags[i];
     const bool lj_i = (ei != 0.0) && (si != 0.0) && !k.no_lj;
     PairAcc A = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
+    if (COMPACT) {
+        PairRec r;
+        r.x = xi, r.y = yi, r.z = zi, r.q = qi, r.eps = ei, r.sig = si, r.mm = mi, r.mol = moli, r.fl = fli;
+        irec[w][lane] = r;
+    }
 
     const int K = nclus / 2;
     const int k0 = blockIdx.y * kper, k1 = min(k0 + kper, K + 1);
@@ -259,7 +299,12 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
         int cj = ci + kk;
         if (cj >= nclus) cj -= nclus;
         if (pass && cull2 > 0.0) pass = cluster_gap2(box, a.cbox, nclus, ci, a.cbox, nclus, cj) <= cull2;
+        // a cluster pair that lies entirely inside the cutoff has nothing to screen out by range: walk it (the dense
+        // form only pays where a good part of the 1,024 pairs drops out: 8 A cutoff in a MOF, not L/2 in a fluid)
+        const bool inside = COMPACT && pass && cull2 > 0.0 &&
+                            cluster_span2(box, a.cbox, nclus, ci, a.cbox, nclus, cj) <= k.cutoff * k.cutoff;
         unsigned mask = __ballot_sync(0xffffffffu, pass);
+        const unsigned inside_mask = __ballot_sync(0xffffffffu, inside);
         while (mask) {
             const int b = __ffs(mask) - 1;
             mask &= mask - 1;
@@ -283,10 +328,50 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
             }
             __syncwarp();
             const int s0 = (kk2 == 0) ? lane + 1 : 0;  // inside one cluster: j > i
-            for (int s = s0; s < 32; s++) {
-                const PairRec& r = rec[w][s];
-                pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, ei, si, mi, moli, fli, lj_i, r.x, r.y, r.z, r.q,
-                                      r.eps, r.sig, r.mm, r.mol, r.fl, A);
+            if (!COMPACT || ((inside_mask >> b) & 1u)) {
+                for (int s = s0; s < 32; s++) {
+                    const PairRec& r = rec[w][s];
+                    pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, ei, si, mi, moli, fli, lj_i, r.x, r.y, r.z,
+                                          r.q, r.eps, r.sig, r.mm, r.mol, r.fl, A);
+                }
+            } else {
+                // screen: one bit per staged atom whose pair with this lane's atom has a body
+                unsigned bits = 0;
+                for (int s = s0; s < 32; s++) {
+                    const PairRec& r = rec[w][s];
+                    PairScreen g;
+                    if (pair_screen<ORTHO, FH>(c, k, rd_only, xi, yi, zi, qi, moli, fli, lj_i, r.x, r.y, r.z, r.q, r.eps, r.sig,
+                                               r.mol, r.fl, A, g))
+                        bits |= 1u << s;
+                }
+                // exclusive prefix of the lanes' counts -> where this lane's pairs go in the list
+                const int cnt = __popc(bits);
+                int incl = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += v;
+                }
+                const int total = __shfl_sync(0xffffffffu, incl, 31);
+                int pos = incl - cnt;
+                while (bits) {
+                    const int s = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    plist[w][pos++] = (unsigned short)((lane << 5) | s);
+                }
+                __syncwarp();
+                // bodies, densely: lane l takes pairs l, l + 32, ...
+                PairAcc scratch = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};  // the screen's side sums were taken above
+                for (int t = lane; t < total; t += 32) {
+                    const int pr = plist[w][t];
+                    const PairRec& ri = irec[w][pr >> 5];
+                    const PairRec& rj = rec[w][pr & 31];
+                    const bool lj_a = (ri.eps != 0.0) && (ri.sig != 0.0) && !k.no_lj;
+                    PairScreen g;
+                    if (pair_screen<ORTHO, FH>(c, k, rd_only, ri.x, ri.y, ri.z, ri.q, ri.mol, ri.fl, lj_a, rj.x, rj.y, rj.z, rj.q,
+                                               rj.eps, rj.sig, rj.mol, rj.fl, scratch, g))
+                        pair_body<FH>(k, mixing, ri.eps, ri.sig, ri.mm, rj.eps, rj.sig, rj.mm, g, A);
+                }
             }
         }
     }
@@ -368,9 +453,23 @@ void launch_pair_energy_clusters(const Cell& c, bool ortho, const SubsetDev& a, 
     const double cull2 = (ortho && cull > 0.0) ? cull * cull : 0.0;  // the gap bound is orthorhombic only
     const BoxLen box = box_len(c);
     dim3 grid((nown + 3) / 4, kslices);
-#define LAUNCH(ORTHO, FH)                                                                                                 \
-    pair_cluster_kernel<ORTHO, FH><<<grid, TILE, 0, s>>>(c, a, k, box, o.mixing, o.rd_only, clus_begin, clus_end, kper, cull2, \
-                                                         partial, stride)
+    // Screening pays where a good part of a passing cluster pair's 1,024 atom pairs drops out, i.e. where the cutoff is
+    // not much larger than a cluster (8 A in a MOF: K1 0.83 -> 0.67 ms at 63k atoms); with the reference's default
+    // cutoff of half the box most cluster pairs are entirely inside it and the two-phase form costs 3-13 % instead
+    // (profiles/r02_k1_compaction.md).  MPMC_B200_K1=walk|compact forces either form (A/B).
+    static const int forced = [] {
+        const char* v = getenv("MPMC_B200_K1");
+        return !v ? 0 : !strcmp(v, "walk") ? 1 : !strcmp(v, "compact") ? 2 : 0;
+    }();
+    const double cluster_edge = cbrt(32.0 * c.volume / (a.n > 0 ? a.n : 1));
+    const bool compact = forced == 2 || (forced == 0 && cull2 > 0.0 && c.cutoff < 2.5 * cluster_edge);
+#define LAUNCH(ORTHO, FH)                                                                                                  \
+    if (compact)                                                                                                           \
+        pair_cluster_kernel<ORTHO, FH, true><<<grid, TILE, 0, s>>>(c, a, k, box, o.mixing, o.rd_only, clus_begin, clus_end,  \
+                                                                   kper, cull2, partial, stride);                          \
+    else                                                                                                                   \
+        pair_cluster_kernel<ORTHO, FH, false><<<grid, TILE, 0, s>>>(c, a, k, box, o.mixing, o.rd_only, clus_begin, clus_end, \
+                                                                    kper, cull2, partial, stride)
     if (ortho) {
         if (o.fh_order == 0)
             LAUNCH(true, 0);
