@@ -221,12 +221,12 @@ inline void fill_exp_coeffs(double* ec) {
 // batches of 32 j-clusters against cluster ci and leave one pass mask per batch in shared memory; afterwards every
 // warp walks the masks in order and takes every fourth passing cluster (position % 4 == warp), so the work is
 // spread evenly over the warps whatever the spatial order, and the assignment -- hence every partial sum -- is a
-// pure function of the geometry (bit-reproducible).  All 128 threads must call.  b0/b1: batch range.
+// pure function of the geometry (bit-reproducible).  Every thread of the CTA must call.  b0/b1: batch range.
 constexpr int CULL_MAX_BATCHES = 2048;  // 65,536 clusters = 2 M atoms
 __device__ __forceinline__ void cull_masks(const BoxLen& box, const double* __restrict__ cbox, int nclus, int ci, double cull2,
                                            int b0, int b1, unsigned* __restrict__ smask) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int b = b0 + w; b < b1; b += 4) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int b = b0 + w; b < b1; b += nw) {
         const int cj = b * 32 + lane;
         bool pass = cj < nclus;
         if (pass && cull2 > 0.0) pass = cluster_gap2(box, cbox, nclus, ci, cbox, nclus, cj) <= cull2;

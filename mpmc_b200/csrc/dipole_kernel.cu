@@ -11,6 +11,8 @@
 // and the linear / off / wolf-full variants of the same switch.  All pairs, minimum image, no
 // cutoff, no exclusions -- exactly the reference's loop bounds.  Atoms with alpha == 0 carry mu == 0
 // in the reference and are simply not in the list.
+#include <cooperative_groups.h>
+
 #include "kernels.h"
 
 namespace mpmc {
@@ -1011,6 +1013,257 @@ __global__ void __launch_bounds__(4 * PUSH_ROWS) gs_push_kernel(Cell c, SubsetDe
         esum[np + i] += ey;
         esum[2 * np + i] += ez;
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused Jacobi-family solve for small systems: thole_iterative() (thole_iterative.c:168-259) in ONE cooperative launch.
+// Below a few thousand polarizable atoms an iteration is launch- and latency-bound (h2_fluid_1000: 600 polarizable atoms,
+// 53 us per iteration for a contraction + an update launch whose CTAs each walk 128 columns in sequence).  Here the
+// grid keeps running across iterations: per iteration every CTA takes (32 rows x 128 columns) items -- 512 threads =
+// 32 rows x 16 lanes, 8 columns per lane, the lanes' sums added in lane order in shared memory -> one partial row per
+// 128-column range -- grid barrier -- every thread updates its rows from the partial rows (the arithmetic of
+// dipole_update_kernel / dipole_commit_kernel: new_mu, SOR / ESOR mix, rrms, the are_we_done_yet residual) -- grid
+// barrier.  Convergence (polar_precision), the 128-iteration bail-out (:199-210) and the Palmo pass (:119-141) are
+// decided inside the kernel; the host reads the iteration count with the other scalars.  Fixed-order sums, no atomics
+// on any field (the residual's atomicMax on non-negative doubles is order independent).
+// ------------------------------------------------------------------------------------------------
+constexpr int FS_THREADS = 512, FS_ROWS = 32, FS_LANES = 16, FS_COLS = 128;
+
+struct FusedArgs {
+    int n, np, njr;  // polarizable atoms, padded, 128-column ranges
+    const double *x, *y, *z, *aux, *alpha, *es;
+    const int* mol;
+    double *mu, *mu_old, *mu_new, *eind, *eic, *rrms;
+    double* part;             // [njr][3][np]
+    double* mu_palmo;         // [3][np]: the dipoles the Palmo pass saw (its rows for the non-polarizable atoms come later)
+    unsigned long long* err;  // [2] residual words, alternating by iteration parity
+    double* out;              // [2]: iterations done, iter_success (1 = bailed out)
+    int max_iter, precision_mode, palmo;
+    double allowed;
+    UpdateOpts uo;
+};
+
+template <bool ORTHO, int DAMP, bool WF>
+__global__ void __launch_bounds__(FS_THREADS, 1) dipole_fused_solver_kernel(Cell c, DipoleConsts k, FusedArgs a) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ double sx[FS_COLS], sy[FS_COLS], sz[FS_COLS], smx[FS_COLS], smy[FS_COLS], smz[FS_COLS], saux[FS_COLS];
+    __shared__ int smol[FS_COLS];
+    __shared__ double red[FS_LANES][3][FS_ROWS];
+    const int tid = threadIdx.x, r = tid & (FS_ROWS - 1), l = tid >> 5;
+    const int np = a.np, n = a.n;
+    const int nrg = (n + FS_ROWS - 1) / FS_ROWS, items = nrg * a.njr;
+    const int gtid = blockIdx.x * FS_THREADS + tid, gthreads = gridDim.x * FS_THREADS;
+
+    // part[jr][.][i] = - sum_{j in range jr, j != i} T_ij mu_j for every row i
+    auto contract = [&](const double* __restrict__ mu) {
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            const int rg = item % nrg, jr = item / nrg;
+            const int i = rg * FS_ROWS + r;
+            __syncthreads();
+            if (tid < FS_COLS) {
+                const int j = jr * FS_COLS + tid;  // < np: np is a multiple of 128
+                sx[tid] = a.x[j];
+                sy[tid] = a.y[j];
+                sz[tid] = a.z[j];
+                smx[tid] = __ldcg(mu + j);
+                smy[tid] = __ldcg(mu + np + j);
+                smz[tid] = __ldcg(mu + 2 * np + j);
+                saux[tid] = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[j];
+                smol[tid] = a.mol[j];
+            }
+            __syncthreads();
+            double ex = 0.0, ey = 0.0, ez = 0.0;
+            if (i < n) {
+                const double xi = a.x[i], yi = a.y[i], zi = a.z[i];
+                const double auxi = (DAMP == MPMC_DAMP_EXPONENTIAL) ? 0.0 : a.aux[i];
+                const int moli = a.mol[i];
+#pragma unroll 4
+                for (int q = 0; q < FS_COLS / FS_LANES; q++) {
+                    const int jj = l + FS_LANES * q, j = jr * FS_COLS + jj;
+                    if (j < n && j != i)
+                        tensor_apply<ORTHO, DAMP, WF>(c, k, xi - sx[jj], yi - sy[jj], zi - sz[jj], smx[jj], smy[jj], smz[jj], auxi,
+                                                      saux[jj], moli == smol[jj], ex, ey, ez);
+                }
+            }
+            red[l][0][r] = ex;
+            red[l][1][r] = ey;
+            red[l][2][r] = ez;
+            __syncthreads();
+            if (tid < 3 * FS_ROWS) {
+                const int cdim = tid >> 5, rr = tid & 31, ii = rg * FS_ROWS + rr;
+                double s = red[0][cdim][rr];
+#pragma unroll
+                for (int q = 1; q < FS_LANES; q++) s += red[q][cdim][rr];
+                if (ii < np) a.part[((size_t)jr * 3 + cdim) * np + ii] = s;
+            }
+        }
+    };
+
+    int it = 0, fail = 0;
+    bool keep = true;
+    while (keep) {
+        it++;
+        if (it >= kMAX_ITERATION_COUNT && a.precision_mode) {  // thole_iterative.c:199-210: mu = alpha E_s, eic = 0
+            for (int i = gtid; i < n; i += gthreads)
+                for (int cdim = 0; cdim < 3; cdim++) {
+                    a.mu[cdim * np + i] = a.alpha[i] * a.es[cdim * np + i];
+                    a.eic[cdim * np + i] = 0.0;
+                }
+            fail = 1;
+            break;
+        }
+        contract(a.mu);
+        grid.sync();
+        if (gtid == 0) a.err[(it + 1) & 1] = 0ull;  // next iteration's word: last read before this iteration's first barrier
+        // ---- update (dipole_update_kernel): E_ind, new_mu, residual, rrms; commit unless a Palmo pass needs the old dipoles
+        {
+            UpdateOpts o = a.uo;
+            o.iteration = it;
+            const bool commit = !a.palmo;
+            const double wold = (commit && o.esor) ? exp(-o.gamma * o.iteration) : 0.0;
+            double worst = 0.0;
+            for (int i = gtid; i < n; i += gthreads) {
+                const double al = a.alpha[i];
+                double num = 0.0, den = 0.0;
+                for (int cdim = 0; cdim < 3; cdim++) {
+                    double e = 0.0;
+                    for (int js = 0; js < a.njr; js++) e += __ldcg(a.part + ((size_t)js * 3 + cdim) * np + i);
+                    a.eind[cdim * np + i] = e;
+                    const double old = a.mu[cdim * np + i];
+                    if (o.save_old) a.mu_old[cdim * np + i] = old;
+                    const double nw = al * (a.es[cdim * np + i] + e);  // thole_iterative.c:49
+                    a.mu_new[cdim * np + i] = nw;
+                    const double d = nw - old;
+                    worst = fmax(worst, d * d);
+                    num += d * d;
+                    den += nw * nw;
+                    if (commit) {  // thole_iterative.c:242-252
+                        double v = nw;
+                        if (o.sor)
+                            v = o.gamma * nw + (1.0 - o.gamma) * old;
+                        else if (o.esor)
+                            v = (1.0 - wold) * nw + wold * old;
+                        a.mu[cdim * np + i] = v;
+                    }
+                }
+                if (o.do_rrms) {
+                    double v = sqrt(num / den);
+                    if (!isfinite(v)) v = 0.0;
+                    a.rrms[i] = v;
+                }
+            }
+            if (a.precision_mode) {
+                worst = warp_max(worst);
+                if ((tid & 31) == 0 && worst > 0.0) atomicMax(a.err + (it & 1), (unsigned long long)__double_as_longlong(worst));
+            }
+        }
+        grid.sync();
+        if (a.precision_mode) {
+            const unsigned long long bits = *reinterpret_cast<volatile unsigned long long*>(a.err + (it & 1));
+            keep = __longlong_as_double((long long)bits) > a.allowed;
+        } else
+            keep = it != a.max_iter;
+        if (a.palmo) {
+            if (!keep) {  // palmo_contraction (:119-141) with the dipoles as they are before this iteration's commit
+                if (a.mu_palmo)
+                    for (int i = gtid; i < np; i += gthreads)
+                        for (int cdim = 0; cdim < 3; cdim++) a.mu_palmo[cdim * np + i] = a.mu[cdim * np + i];
+                contract(a.mu);
+                grid.sync();
+                for (int i = gtid; i < n; i += gthreads)
+                    for (int cdim = 0; cdim < 3; cdim++) {
+                        double e = -a.eind[cdim * np + i];  // thole_iterative.c:129-130
+                        for (int js = 0; js < a.njr; js++) e += __ldcg(a.part + ((size_t)js * 3 + cdim) * np + i);
+                        a.eic[cdim * np + i] = e;
+                    }
+            }
+            // commit (dipole_commit_kernel): mu = new_mu | SOR | ESOR mix
+            for (int i = gtid; i < n; i += gthreads)
+                for (int cdim = 0; cdim < 3; cdim++) {
+                    const double nw = a.mu_new[cdim * np + i];
+                    double v = nw;
+                    if (a.uo.sor)
+                        v = a.uo.gamma * nw + (1.0 - a.uo.gamma) * a.mu_old[cdim * np + i];
+                    else if (a.uo.esor) {
+                        const double w = exp(-a.uo.gamma * it);
+                        v = (1.0 - w) * nw + w * a.mu_old[cdim * np + i];
+                    }
+                    a.mu[cdim * np + i] = v;
+                }
+            grid.sync();
+        }
+    }
+    if (gtid == 0) {
+        a.out[0] = (double)it;
+        a.out[1] = (double)fail;
+    }
+}
+
+// false -- nothing launched -- when the fused solve does not apply here (no cooperative launch, too many items per CTA)
+bool launch_dipole_fused_solver(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const UpdateOpts& uo,
+                                int max_iter, double allowed, bool precision_mode, bool palmo, const double* es, double* mu,
+                                double* mu_old, double* mu_new, double* eind, double* eic, double* rrms, double* part,
+                                double* mu_palmo, unsigned long long* err2, double* out2, cudaStream_t s) {
+    if (pol.n <= 0) return false;
+    int dev = 0, sms = 0, coop = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (!coop) return false;
+    const DipoleConsts k = make_consts(c, o);
+    FusedArgs a;
+    a.n = pol.n;
+    a.np = pol.n_pad;
+    a.njr = (pol.n + FS_COLS - 1) / FS_COLS;
+    a.x = pol.x, a.y = pol.y, a.z = pol.z, a.aux = pol.aux, a.alpha = pol.alpha, a.es = es, a.mol = pol.mol;
+    a.mu = mu, a.mu_old = mu_old, a.mu_new = mu_new, a.eind = eind, a.eic = eic, a.rrms = rrms;
+    a.part = part;
+    a.mu_palmo = mu_palmo;
+    a.err = err2;
+    a.out = out2;
+    a.max_iter = max_iter;
+    a.precision_mode = precision_mode ? 1 : 0;
+    a.palmo = palmo ? 1 : 0;
+    a.allowed = allowed;
+    a.uo = uo;
+    const int items = ((pol.n + FS_ROWS - 1) / FS_ROWS) * a.njr;
+    Cell cc = c;
+    DipoleConsts kk = k;
+    void* args[] = {&cc, &kk, &a};
+    cudaError_t err = cudaErrorInvalidValue;
+#define LAUNCH(ORTHO, DAMP, WF)                                                                      \
+    {                                                                                                \
+        const void* fn = (const void*)dipole_fused_solver_kernel<ORTHO, DAMP, WF>;                   \
+        int per_sm = 0;                                                                              \
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, FS_THREADS, 0);                   \
+        if (per_sm < 1) return false;                                                                \
+        int gridx = per_sm * sms;                                                                    \
+        if (gridx > items) gridx = items;                                                            \
+        err = cudaLaunchCooperativeKernel(fn, dim3(gridx), dim3(FS_THREADS), args, 0, s);            \
+    }
+#define DISPATCH(ORTHO)                                              \
+    if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                      \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, true)  \
+        else LAUNCH(ORTHO, MPMC_DAMP_EXPONENTIAL, false)             \
+    } else if (o.damp_type == MPMC_DAMP_LINEAR) {                    \
+        LAUNCH(ORTHO, MPMC_DAMP_LINEAR, false)                       \
+    } else {                                                         \
+        if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true)          \
+        else LAUNCH(ORTHO, MPMC_DAMP_OFF, false)                     \
+    }
+    if (ortho) {
+        DISPATCH(true)
+    } else {
+        DISPATCH(false)
+    }
+#undef DISPATCH
+#undef LAUNCH
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return true;
 }
 
 // ------------------------------------------------------------------------------------------------

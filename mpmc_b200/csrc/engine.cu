@@ -112,7 +112,9 @@ enum Slot {
     S_FIELDCNT = 13,
     S_TOTMU = 16,  // 3: sum of the dipoles (full-Ewald polarization)
     S_PEER_TIMEOUT = 20,  // set to 1.0 by a peer-wait kernel whose peer never signalled
-    S_GS_TIMEOUT = 21,    // set to 1.0 by the persistent Gauss-Seidel sweep when one of its CTAs waited 2 s for another
+    S_GS_TIMEOUT = 21,
+    S_FUSED_OUT = 26,     // 2: iterations done / iter_success of the fused small-system solve (decided on the device)
+    S_FUSED_ERR = 28,     // 2 words: its residual, alternating by iteration parity    // set to 1.0 by the persistent Gauss-Seidel sweep when one of its CTAs waited 2 s for another
     S_CRYSTAL = 22,       // 2: rd_crystal image sums of the pairs, pairs counted
     S_COUNT = 24
 };
@@ -306,6 +308,7 @@ struct mpmc_b200_ctx {
     mpmc_b200_counters cnt{};
     int launches = 0;
     int pending_iterations = 0, pending_iter_success = 0;
+    bool iter_from_device = false;  // the fused solve counted its iterations itself: read them with the scalars
     bool pending = false;
     bool last_had_polar = false;
 };
@@ -863,7 +866,8 @@ static int repack(Ctx* c) {
         // Without polarization K1 is the critical path: slice down to one candidate offset per warp (small systems are
         // bound by a warp's serial walk).  With polarization K1 runs beside the solve on the side stream and only has to
         // finish before it does: whole batches of 32 offsets per slice, so that it takes few issue slots from K3 / K4.
-        const bool k1_critical = !(c->P.polarization && !c->P.rd_only);
+        // (small systems: the fused solve is shorter than a warp's walk over whole batches -- K1 0.41-0.90 ms at 1k-4k atoms)
+        const bool k1_critical = !(c->P.polarization && !c->P.rd_only) || n <= 8192;
         const int batches = k1_critical ? nclus / 2 + 1 : (nclus / 2 + 1 + 31) / 32;
         c->pair_kslices = std::max(1, std::min(batches, (8 * sms + ctas_x - 1) / ctas_x));
         const int cols = pair_cluster_columns(c->sorted.n_pad, 0, own, c->pair_kslices);
@@ -1703,8 +1707,27 @@ static int enqueue_polar(Ctx* c) {
             permuted = true;
         }
 
+        // Small systems, Jacobi family: every iteration, the convergence test, the bail-out and the Palmo pass in ONE
+        // cooperative launch (dipole_fused_solver_kernel); the iteration count comes back with the scalars.
+        bool fused = false;
+        {
+            static const int fused_max = [] { const char* v = getenv("MPMC_B200_FUSED_MAX"); return v ? atoi(v) : 4096; }();
+            if (!gs && c->world == 1 && !sym_now(c) && pp <= fused_max && c->epart.cap >= (size_t)((c->pol.n + TILE - 1) / TILE) * 3 * pp) {
+                uo.iteration = 0;
+                fused = launch_dipole_fused_solver(cell, ortho, pol, dop, uo, P.polar_max_iter, allowed, P.polar_precision != 0.0,
+                                                   P.polar_palmo != 0, c->es.p, c->mu.p, c->mu_old.p, c->mu_new.p, c->eind.p,
+                                                   c->eic.p, c->rrms.p, c->epart.p, P.polar_palmo ? c->esum.p : nullptr,
+                                                   reinterpret_cast<unsigned long long*>(c->scalars.p + S_FUSED_ERR),
+                                                   c->scalars.p + S_FUSED_OUT, st);
+                if (fused) {
+                    c->launches++;
+                    c->iter_from_device = true;
+                    if (P.polar_palmo && palmo_nonpolar_rows(c, pol, c->esum.p)) return 10;
+                }
+            }
+        }
         int it = 0;
-        bool keep = true;
+        bool keep = !fused;
         while (keep) {
             it++;
             if (it >= kMAX_ITERATION_COUNT && P.polar_precision != 0.0) {  // divergence bail-out (:199-210)
@@ -1846,6 +1869,7 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
     c->cnt.n_atoms = c->n;
     c->pending_iterations = 0;
     c->pending_iter_success = 0;
+    c->iter_from_device = false;
     CU(cudaMemsetAsync(c->scalars.p, 0, sizeof(double) * 32, st));
     phase_begin(c, PH_TOTAL);
     const Cell cell = make_cell(P);
@@ -2018,6 +2042,12 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
         out->es_recip = P.es_wolf ? 0.0 : h[S_RECIP];
         out->es_self = (lead && !P.es_wolf) ? c->es_self : 0.0;
         out->coulombic = out->es_real + out->es_recip + out->es_self;
+    }
+    if (c->last_had_polar && c->iter_from_device) {
+        c->pending_iterations = (int)h[S_FUSED_OUT];
+        c->pending_iter_success = (int)h[S_FUSED_OUT + 1];
+        if (c->pending_iter_success) c->warm_valid = false;  // the bail-out left alpha E_s, not converged dipoles
+        c->cnt.contractions = c->pending_iterations - (c->pending_iter_success ? 1 : 0) + (P.polar_palmo && !c->pending_iter_success ? 1 : 0);
     }
     if (c->last_had_polar) {
         double pot = h[S_POLAR + 0];

@@ -30,8 +30,31 @@ __device__ __forceinline__ void field_term(const Cell& c, const FieldOpts& o, do
             if (MODE == FIELD_EWALD_REAL && same && dx == 0.0 && dy == 0.0 && dz == 0.0) break;  // the atom itself
             min_image<ORTHO>(c, dx, dy, dz);
             const double r2 = dx * dx + dy * dy + dz * dz;
-            const double r = sqrt(r2);
             double f;  // E_i += q_j * f * d
+            if (MODE == FIELD_NOPBC || MODE == FIELD_WOLF_A0) {
+                // thole_field.c:55 (r - SMALL_dR < cutoff, r != 0) decided on r^2; the square root is only taken inside a
+                // 1e-9 A shell around the cutoff, where the reference's own comparison is evaluated.  1/r from the
+                // rsqrt seed + one third-order step (common.cuh) instead of sqrt + division: ~12 instead of ~45 instructions.
+                if (r2 == 0.0) break;
+                if (r2 >= o.in2) {
+                    if (r2 > o.out2) break;
+                    if (!(sqrt(r2) - kSMALL_dR < c.cutoff)) break;
+                }
+                const double ir = rsqrt_fast(r2);
+                if (MODE == FIELD_NOPBC)
+                    f = ir * ir * ir;
+                else {
+                    const double rR = 1.0 / c.cutoff;
+                    f = (ir * ir - rR * rR) * ir;
+                }
+                const double qf0 = qj * f;
+                ex += qf0 * dx;
+                ey += qf0 * dy;
+                ez += qf0 * dz;
+                cnt++;
+                break;
+            }
+            const double r = sqrt(r2);
             if (MODE == FIELD_EWALD_REAL) {
                 if ((r > c.cutoff) || (r == 0.0)) break;  // polar_ewald.c:51
                 const bool excluded = same || (qi == 0.0);   // pair es_excluded (pairs.c:61-77); q_j != 0 by construction
@@ -124,15 +147,16 @@ struct __align__(16) FieldRec {
     int mol, fl;
 };
 
+constexpr int FC_WARPS = 8;  // warps sharing one i-cluster's passing j-clusters (4 left ~13 warps per SM at 16k atoms)
 template <bool ORTHO, int MODE>
-__global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a, FieldOpts o, BoxLen box, int clus_begin,
+__global__ void __launch_bounds__(32 * FC_WARPS) field_cluster_kernel(Cell c, SubsetDev a, FieldOpts o, BoxLen box, int clus_begin,
                                                              int clus_end, double cull2, int accumulate,
                                                              double* __restrict__ ef, int ef_stride,
                                                              double* __restrict__ count_part) {
-    // One CTA per i-cluster: its four warps scan interleaved batches of j-clusters (a warp's serial scan is the
+    // One CTA per i-cluster: its warps scan interleaved batches of j-clusters (a warp's serial scan is the
     // critical path of this latency-bound kernel) and their partial fields are added in warp order.
-    __shared__ FieldRec rec[4][32];
-    __shared__ double sred[4][4][32];
+    __shared__ FieldRec rec[FC_WARPS][32];
+    __shared__ double sred[FC_WARPS][4][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int ci = clus_begin + blockIdx.x;
     if (ci >= clus_end) return;  // whole CTA
@@ -151,7 +175,7 @@ __global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a
         while (mask) {
             const int bit = __ffs(mask) - 1;
             mask &= mask - 1;
-            if (((pos++) & 3) != w) continue;  // warp-uniform: every fourth passing cluster is this warp's
+            if (((pos++) % FC_WARPS) != w) continue;  // warp-uniform: every FC_WARPS-th passing cluster is this warp's
             const int cj = b * 32 + bit;
             __syncwarp();
             {
@@ -181,10 +205,15 @@ __global__ void __launch_bounds__(TILE) field_cluster_kernel(Cell c, SubsetDev a
     sred[w][3][lane] = (double)cnt;
     __syncthreads();
     if (w != 0) return;
-    ex = ((sred[0][0][lane] + sred[1][0][lane]) + sred[2][0][lane]) + sred[3][0][lane];
-    ey = ((sred[0][1][lane] + sred[1][1][lane]) + sred[2][1][lane]) + sred[3][1][lane];
-    ez = ((sred[0][2][lane] + sred[1][2][lane]) + sred[2][2][lane]) + sred[3][2][lane];
-    const double cntd = ((sred[0][3][lane] + sred[1][3][lane]) + sred[2][3][lane]) + sred[3][3][lane];
+    double cntd = sred[0][3][lane];
+    ex = sred[0][0][lane], ey = sred[0][1][lane], ez = sred[0][2][lane];
+#pragma unroll
+    for (int q = 1; q < FC_WARPS; q++) {  // warp order: fixed association
+        ex += sred[q][0][lane];
+        ey += sred[q][1][lane];
+        ez += sred[q][2][lane];
+        cntd += sred[q][3][lane];
+    }
     if (fli & F_VALID) {
         const int g = a.idx[i];
         if (accumulate) {
@@ -221,8 +250,11 @@ void launch_static_field(const Cell& c, bool ortho, const AtomsDev& a, const Sub
     const int ntiles = charged.n_pad / TILE;
     const int tps = (ntiles + jsplits - 1) / jsplits;
     dim3 grid((rows + TILE - 1) / TILE, jsplits);
-#define LAUNCH(ORTHO, MODE)                                                                                         \
-    static_field_kernel<ORTHO, MODE><<<grid, TILE, 0, s>>>(c, a, charged, o, row_begin, row_end, tps, epart, count_part)
+    FieldOpts fo = o;
+    fo.in2 = (c.cutoff - 1e-9) * (c.cutoff - 1e-9);
+    fo.out2 = (c.cutoff + 1e-9) * (c.cutoff + 1e-9);
+#define LAUNCH(ORTHO, MODE)                                                                                          \
+    static_field_kernel<ORTHO, MODE><<<grid, TILE, 0, s>>>(c, a, charged, fo, row_begin, row_end, tps, epart, count_part)
 #define DISPATCH(ORTHO)                                     \
     switch (o.mode) {                                       \
         case FIELD_NOPBC: LAUNCH(ORTHO, FIELD_NOPBC); break; \
@@ -248,9 +280,12 @@ void launch_static_field_clusters(const Cell& c, bool ortho, const SubsetDev& a,
     const double cull2 = (ortho && cull > 0.0) ? cull * cull : 0.0;
     const BoxLen box = box_len(c);
     const int grid = nown;
-#define LAUNCH(ORTHO, MODE)                                                                                              \
-    field_cluster_kernel<ORTHO, MODE><<<grid, TILE, 0, s>>>(c, a, o, box, clus_begin, clus_end, cull2, accumulate ? 1 : 0, ef, \
-                                                            ef_stride, count_part)
+    FieldOpts fo = o;
+    fo.in2 = (c.cutoff - 1e-9) * (c.cutoff - 1e-9);
+    fo.out2 = (c.cutoff + 1e-9) * (c.cutoff + 1e-9);
+#define LAUNCH(ORTHO, MODE)                                                                                                  \
+    field_cluster_kernel<ORTHO, MODE><<<grid, 32 * FC_WARPS, 0, s>>>(c, a, fo, box, clus_begin, clus_end, cull2, accumulate ? 1 : 0, \
+                                                                     ef, ef_stride, count_part)
 #define DISPATCH(ORTHO)                                     \
     switch (o.mode) {                                       \
         case FIELD_NOPBC: LAUNCH(ORTHO, FIELD_NOPBC); break; \

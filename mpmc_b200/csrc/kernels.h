@@ -106,6 +106,7 @@ struct FieldOpts {
     double cutoffterm;  // wolf: value of the kernel at R_c
     const double* table;
     int table_max;
+    double in2 = 0.0, out2 = 0.0;  // (cutoff -+ 1e-9)^2, filled by the launchers: the range test on r^2 away from the boundary
 };
 void launch_static_field(const Cell& c, bool ortho, const AtomsDev& a, const SubsetDev& charged, const FieldOpts& o,
                          int row_begin, int row_end, int jsplits, double* epart /*[jsplits][3][n_pad]*/,
@@ -204,6 +205,14 @@ void launch_palmo_finish(const SubsetDev& pol, const double* epart, int jsplits,
 void launch_polar_energy(const SubsetDev& pol, const double* mu, const double* es, const double* eic, const double* rrms,
                          int row_begin, int row_end, double* out, cudaStream_t s);
 
+// Small systems: the whole Jacobi-family solve (every iteration, convergence test, bail-out, Palmo pass) in one
+// cooperative launch (dipole_kernel.cu: dipole_fused_solver_kernel).  part [ceil(n/128)][3][n_pad]; err2 two device words;
+// out2[0] = iterations done, out2[1] = iter_success.  mu_palmo (optional) receives the dipoles the Palmo pass saw.
+// false = not launchable here (the caller takes the launch-per-iteration path).
+bool launch_dipole_fused_solver(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const UpdateOpts& uo,
+                                int max_iter, double allowed, bool precision_mode, bool palmo, const double* es, double* mu,
+                                double* mu_old, double* mu_new, double* eind, double* eic, double* rrms, double* part,
+                                double* mu_palmo, unsigned long long* err2, double* out2, cudaStream_t s);
 // Gauss-Seidel sweep (polar_gs / polar_gs_ranked): blocked forward substitution in `order`.
 void launch_gs_sweep(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const int* order,
                      const double* es, double* mu, double* mu_new, double* eind, double* scratch, cudaStream_t s);

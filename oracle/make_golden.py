@@ -275,17 +275,35 @@ TRAJ_SYNTH = {
     "traj_co2_npt": (lambda: systems.co2_fluid(125), "npt", "preset_seeds 31337\nnumsteps 200\nmove_factor 0.05\nrot_factor 0.05\n"
                                                             "pressure 100.0\nvolume_probability 0.2\nvolume_change_factor 0.02",
                      dict(explicit_cutoff=False)),
+    # the remaining relink shapes of the MC driver: cavity-biased insertions (mc_moves.c:577-600, cavity.c) and
+    # insertions of molecules taken from a separate list (`insert_input`: the new molecule is a copy of a template that
+    # was never in the system, mc_moves.c:603-660)
+    "traj_co2_uvt_cavity": (lambda: systems.co2_fluid(125), "uvt", "preset_seeds 2718\nnumsteps 300\nmove_factor 0.05\nrot_factor 0.05\n"
+                                                                   "pressure 200.0\ninsert_probability 0.4\ncavity_bias on\n"
+                                                                   "cavity_grid 5\ncavity_radius 3.0"),
+    "traj_co2_uvt_insert_input": (lambda: systems.co2_fluid(125), "uvt", "preset_seeds 1618\nnumsteps 300\nmove_factor 0.05\n"
+                                                                         "rot_factor 0.05\npressure 200.0\ninsert_probability 0.4\n"
+                                                                         "insert_input insert.pqr", dict(insert_first_molecule=True)),
 }
 
 
 def gen_traj_synth(name):
     build, ensemble, extra = TRAJ_SYNTH[name][:3]
-    kw = TRAJ_SYNTH[name][3] if len(TRAJ_SYNTH[name]) > 3 else {}
+    kw = dict(TRAJ_SYNTH[name][3]) if len(TRAJ_SYNTH[name]) > 3 else {}
+    insert_first = kw.pop("insert_first_molecule", False)
     s = build()
     first = np.r_[True, s.mol_id[1:] != s.mol_id[:-1]]
     s.meta["atom_mass"] = np.where(first, s.mol_mass, 0.0)  # update_com() then recovers molecule_t.mass
     with tempfile.TemporaryDirectory() as td:
         inp = systems.write_reference_case(s, td, ensemble=ensemble, extra=extra, **kw)
+        extra_files = {}
+        if insert_first:  # the template list of `insert_input`: the first molecule of the system, on its own
+            lines = [l for l in open(os.path.join(td, "system.pqr")).read().splitlines() if l.startswith("ATOM")]
+            first = [l for l in lines if l.split()[5] == lines[0].split()[5]]
+            extra_files["insert.pqr"] = "\n".join(first) + "\nEND\n"
+        for fn, text in extra_files.items():
+            with open(os.path.join(td, fn), "w") as f:
+                f.write(text)
         r = subprocess.run([oracle.REF_BINARY, "input"], cwd=td, capture_output=True, text=True, timeout=3600)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         en = [l for l in open(os.path.join(td, "energy.dat")).read().splitlines() if not l.startswith("#")]
@@ -294,7 +312,7 @@ def gen_traj_synth(name):
         pqr = open(os.path.join(td, "system.pqr")).read()
     with open(os.path.join(GOLD, name + ".json"), "w") as f:
         json.dump({"input": inp_text, "pqr_name": "system.pqr", "pqr": pqr, "energy_rows": en, "final_pqr": final,
-                   "energy_file": "energy.dat", "final_file": "final.pqr"}, f, indent=0)
+                   "energy_file": "energy.dat", "final_file": "final.pqr", "extra_files": extra_files}, f, indent=0)
     print(f"{name}: {len(en)} energy rows")
 
 

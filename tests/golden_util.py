@@ -85,6 +85,8 @@ def run_and_check_trajectory(program, name, tmp_path, env=None):
 
     (tmp_path / d["pqr_name"]).write_text(unpack("pqr"))
     (tmp_path / "input").write_text(d["input"])
+    for fn, text in (d.get("extra_files") or {}).items():
+        (tmp_path / fn).write_text(text)
     r = subprocess.run([program, "input"], cwd=str(tmp_path), capture_output=True, text=True, timeout=1800,
                        env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

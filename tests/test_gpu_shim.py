@@ -65,7 +65,8 @@ def test_dropin_energy_matches_reference_fixture(name, tmp_path):
 
 
 @pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "incremental", "warm_start", "threaded"])
-@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt", "traj_co2_uvt", "traj_co2_npt"])
+@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt", "traj_co2_uvt", "traj_co2_npt",
+                                  "traj_co2_uvt_cavity", "traj_co2_uvt_insert_input"])
 def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     """host_path: the shim's one-pass O(N) duties over the cached pointer sequence (default; every relinking of the
     lists -- uVT insert / remove, rejected moves -- must be detected; MPMC_B200_SHIM_CHECK=1 compares the pass with a real

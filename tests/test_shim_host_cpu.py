@@ -27,7 +27,8 @@ def hoststub():
 
 
 @pytest.mark.parametrize("host_path", ["cached_sequence", "list_walks", "threaded"])
-@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt", "traj_co2_uvt", "traj_co2_npt"])
+@pytest.mark.parametrize("name", ["traj_small_nvt", "traj_small_uvt", "traj_co2_nvt", "traj_co2_uvt", "traj_co2_npt",
+                                  "traj_co2_uvt_cavity", "traj_co2_uvt_insert_input"])
 def test_shim_host_logic_reproduces_reference_trajectory(hoststub, name, host_path, tmp_path):
     """traj_co2_npt: volume moves -- every accepted or reverted change of the cell must reach set_params (its GPU run:
     tests/test_gpu_shim.py).  `threaded`: the one pass and the scatter into atom_t with 4 host threads (the default above
