@@ -222,6 +222,14 @@ struct mpmc_b200_ctx {
     bool gs_delta = true;  // delta form of the sweep (symmetric Jacobi part + block pushes); MPMC_B200_GS=panels: panel form
     bool gs_persistent = true;  // one cooperative launch per sweep (resolver + pushers); MPMC_B200_GS=blocks: two launches per block
     DevBuf<double> g_tens, g_pushacc, g_ctab;
+    // Gauss-Seidel: the Jacobi part of a sweep (and the Palmo contraction) does not care about the processing order, so it
+    // runs on a spatially ordered image of the polarizable atoms -- tight cluster boxes, the far-cluster damping skip --
+    // and its result is gathered back into processing order (4.6 -> 3.7 ms per contraction at 63k atoms)
+    Subset gsp;
+    std::vector<int> gsp_packed;        // packed (list-order) index of the s-th atom of the spatial order
+    DevBuf<int> map_s2g, map_g2s;       // spatial index -> processing index and back (rebuilt with the processing order)
+    DevBuf<double> g_mu_sp, g_esum_sp, cbox_sp;
+    bool gs_spatial = true;             // MPMC_B200_GS_JACOBI=order: the Jacobi part in processing order (A/B)
     DevBuf<unsigned> gs_flags;
     unsigned gs_epoch = 0;
     DevBuf<unsigned long long> gs_trace;  // MPMC_B200_GS_TRACE=1: resolver time stamps of the last sweep, summarised on stderr
@@ -826,6 +834,26 @@ static int repack(Ctx* c) {
         return 11;
     if (c->eic_np.ensure((size_t)3 * c->nonpol.n_pad) || c->eind_np.ensure((size_t)3 * c->nonpol.n_pad))
         FAIL(11, "cudaMalloc failed");
+    c->gsp.n = 0;
+    if (c->gs_spatial && c->gs_delta && c->have_params && (c->P.polar_gs || c->P.polar_gs_ranked) && !c->P.polar_ewald_full &&
+        c->pol.n > 0) {
+        std::vector<int> sp = c->pol.idx;  // list order
+        spatial_order(c, sp);
+        if (pack_subset(c, c->gsp, sp, polpad, true)) return 11;
+        std::vector<int> packed_of_atom(n, -1);
+        for (int k = 0; k < c->pol.n; k++) packed_of_atom[c->pol.idx[k]] = k;
+        c->gsp_packed.assign(c->gsp.n_pad, 0);
+        for (int k = 0; k < c->gsp.n_pad; k++) c->gsp_packed[k] = k < c->gsp.n ? packed_of_atom[sp[k]] : k;
+        const size_t gp = (size_t)c->gsp.n_pad;
+        if (c->map_s2g.ensure(gp) || c->map_g2s.ensure(gp) || c->g_mu_sp.ensure(3 * gp) || c->g_esum_sp.ensure(3 * gp) ||
+            c->cbox_sp.ensure(6 * (gp / 32)))
+            FAIL(11, "cudaMalloc failed");
+        if (!c->pol_sorted && !c->use_clusters) {  // the drift check of set_positions needs the sort-time positions
+            c->hx_sort = c->hx;
+            c->hy_sort = c->hy;
+            c->hz_sort = c->hz;
+        }
+    }
     c->hperm.assign(c->pol.n_pad, 0);
     std::iota(c->hperm.begin(), c->hperm.end(), 0);
 
@@ -1012,9 +1040,17 @@ static int refresh_subsets(Ctx* c) {
         c->hy_sort = c->hy;
         c->hz_sort = c->hz;
     }
+    if (c->resort_pending && c->gsp.n > 0) {  // Gauss-Seidel: the spatial image of the Jacobi part follows the atoms too
+        std::vector<int> sp = c->pol.idx;
+        spatial_order(c, sp);
+        if (pack_subset(c, c->gsp, sp, dipole_sym_tile() * std::max(c->world, 1), true)) return 11;
+        std::vector<int> packed_of_atom(c->n, -1);
+        for (int k = 0; k < c->pol.n; k++) packed_of_atom[c->pol.idx[k]] = k;
+        for (int k = 0; k < c->gsp.n_pad; k++) c->gsp_packed[k] = k < c->gsp.n ? packed_of_atom[sp[k]] : k;
+    }
     c->resort_pending = false;
     if (!c->subsets_stale) return 0;
-    for (Subset* s : {&c->charged, &c->recip, &c->pol, &c->nonpol, &c->sorted}) {
+    for (Subset* s : {&c->charged, &c->recip, &c->pol, &c->nonpol, &c->sorted, &c->gsp}) {
         if (s->n <= 0) continue;
         gather_positions_kernel<<<(s->n + 255) / 256, 256, 0, c->stream>>>(c->x.p, c->y.p, c->z.p, s->didx.p, s->n, s->x.p,
                                                                           s->y.p, s->z.p);
@@ -1674,6 +1710,16 @@ static int enqueue_polar(Ctx* c) {
             g.alpha = c->gs.alpha.p;
             g.aux = c->gs.aux.p;
             g.mol = c->gs.mol.p;
+            if (c->gs_delta && c->gsp.n > 0) {  // processing order <-> spatial order of the Jacobi part
+                std::vector<int> inv(pp), s2g(pp), g2s(pp);
+                for (int k = 0; k < pp; k++) inv[c->hperm[k]] = k;            // packed index -> processing index
+                for (int k = 0; k < pp; k++) s2g[k] = inv[c->gsp_packed[k]];  // spatial index -> processing index
+                for (int k = 0; k < pp; k++) g2s[s2g[k]] = k;
+                if (upload(c->map_s2g, s2g, st) || upload(c->map_g2s, g2s, st)) return 11;
+                CU(cudaStreamSynchronize(st));  // the uploads read from locals
+                launch_cluster_boxes(cell, ortho, c->gsp.dev(), c->cbox_sp.p, st);
+                c->launches++;
+            }
             if (c->gs_delta) {  // cluster boxes of the atoms in processing order, for the symmetric Jacobi part of a sweep
                 launch_cluster_boxes(cell, ortho, g, c->cbox.p, st);
                 if (c->gs_persistent)
@@ -1694,6 +1740,24 @@ static int enqueue_polar(Ctx* c) {
             permute_kernel<<<nb, 256, 0, st>>>(c->g_eic.p, c->eic.p, c->perm.p, n, pp, 3, 1);
             permute_kernel<<<nb, 256, 0, st>>>(c->g_rrms.p, c->rrms.p, c->perm.p, n, pp, 1, 1);
             c->launches += 6;
+            CU(cudaGetLastError());
+            return 0;
+        };
+        // Gauss-Seidel, Jacobi part of a sweep / Palmo contraction: esum (processing order) = - sum_{j != i} T_ij mu_j for the
+        // dipoles in g_mu -- evaluated on the spatially ordered image when there is one, gathered back by index maps
+        auto gs_jacobi = [&]() -> int {
+            if (c->gsp.n > 0) {
+                const int nb = (pp + 255) / 256;
+                permute_kernel<<<nb, 256, 0, st>>>(c->g_mu.p, c->g_mu_sp.p, c->map_s2g.p, pp, pp, 3, 0);
+                launch_dipole_contract_sym(cell, ortho, c->gsp.dev(), dop, c->g_mu_sp.p, c->cbox_sp.p, 0, 1, c->sym_ysplits,
+                                           c->sym_partI.p, c->sym_partJ.p, c->g_esum_sp.p, st);
+                permute_kernel<<<nb, 256, 0, st>>>(c->g_esum_sp.p, c->esum.p, c->map_g2s.p, pp, pp, 3, 0);
+                c->launches += 4;
+            } else {
+                launch_dipole_contract_sym(cell, ortho, g, dop, c->g_mu.p, c->cbox.p, 0, 1, c->sym_ysplits, c->sym_partI.p,
+                                           c->sym_partJ.p, c->esum.p, st);
+                c->launches += 2;
+            }
             CU(cudaGetLastError());
             return 0;
         };
@@ -1752,13 +1816,12 @@ static int enqueue_polar(Ctx* c) {
                     if (c->gs_persistent) {
                         // Jacobi part with the dipoles as they are at the start of the sweep, then the whole
                         // lower-triangular part in one cooperative launch (resolver + pushers with look-ahead)
-                        launch_dipole_contract_sym(cell, ortho, g, dop, c->g_mu.p, c->cbox.p, 0, 1, c->sym_ysplits, c->sym_partI.p,
-                                                   c->sym_partJ.p, c->esum.p, st);
+                        if (gs_jacobi()) return 10;
                         one_launch = launch_gs_sweep_persistent(cell, ortho, g, dop, c->esum.p, c->g_es.p, c->g_mu.p, c->g_mu_new.p,
                                                                 c->g_eind.p, c->g_delta.p, c->g_tens.p, c->g_ctab.p, c->g_pushacc.p,
                                                                 c->gs_flags.p, ++c->gs_epoch, c->scalars.p + S_GS_TIMEOUT, st,
                                                                 c->gs_trace.p);
-                        c->launches += 3;
+                        c->launches += 1;
                     }
                     if (!one_launch) {
                         launch_gs_sweep_delta(cell, ortho, g, dop, c->cbox.p, c->sym_ysplits, c->sym_partI.p, c->sym_partJ.p,
@@ -1794,10 +1857,9 @@ static int enqueue_polar(Ctx* c) {
 
             if (P.polar_palmo && !keep) {  // palmo_contraction (:119-141) with the CURRENT mu
                 if (gs && c->gs_delta) {
-                    launch_dipole_contract_sym(cell, ortho, g, dop, c->g_mu.p, c->cbox.p, 0, 1, c->sym_ysplits, c->sym_partI.p,
-                                               c->sym_partJ.p, c->esum.p, st);
+                    if (gs_jacobi()) return 10;
                     launch_palmo_finish(g, c->esum.p, 1, c->g_eind.p, c->g_eic.p, 0, pp, st);
-                    c->launches += 3;
+                    c->launches += 1;
                     c->cnt.contractions += 1;
                     if (palmo_nonpolar_rows(c, g, c->g_mu.p)) return 10;
                 } else if (gs) {
@@ -2341,6 +2403,8 @@ int mpmc_b200_create(mpmc_b200_ctx** out, int device) {
         v = getenv("MPMC_B200_GS");
         c->gs_delta = c->use_sym && !(v && strcmp(v, "panels") == 0);
         c->gs_persistent = !(v && strcmp(v, "blocks") == 0);
+        v = getenv("MPMC_B200_GS_JACOBI");
+        c->gs_spatial = !(v && strcmp(v, "order") == 0);
     }
     for (int p = 0; p < PH_COUNT; p++) {
         CU(cudaEventCreate(&c->ev[p][0]));
@@ -2466,6 +2530,12 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     c->eind_np.release();
     c->wb.release();
     c->gs.release();
+    c->gsp.release();
+    c->map_s2g.release();
+    c->map_g2s.release();
+    c->g_mu_sp.release();
+    c->g_esum_sp.release();
+    c->cbox_sp.release();
     c->sorted.release();
     c->follow.release();
     c->intra_part.release();
