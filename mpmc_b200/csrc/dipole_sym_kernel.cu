@@ -25,6 +25,7 @@
 //     (e^{-lr}(...) < 2^-54 for l r >= 48): then exp() and the damping polynomial are skipped -- the
 //     result is bit-identical to evaluating them.
 //   * minimum image: rint() runs on the conversion pipe (FRND.F64), not on the fp64 FMA pipe.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -112,7 +113,9 @@ __device__ __forceinline__ void tensor_coeffs(const SymConsts& k, double r2, dou
 
 struct SymArgs {
     int n, np, S;    // polarizable atoms, padded, super tiles (np / 256)
-    int Y;           // offset slices: work items (I super tile, slice y), numbered y-major: c = y * S + I
+    int Y;           // offset slices OF THIS LAUNCH: work items (I super tile, slice y0 + y), numbered y-major: c = y * S + I
+    int y0;          // first slice of this launch, jrow0 = first offset whose J-side row it writes (row = kk - jrow0):
+    int jrow0;       // a contraction is split into launches over slice ranges when its J-side rows would not fit the cap
     int rank, world; // this launch owns the items c with c % world == rank (round robin: every rank gets the same mix of
                      // near -- damped, expensive -- and far tile pairs; contiguous shares left the ranks 9 % apart)
     int K;           // S/2: offsets 0..K
@@ -230,7 +233,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
     const int np = a.np, S = a.S, nclus = np >> 5;
     const int cidx = a.rank + (int)blockIdx.x * a.world;  // this rank's blockIdx.x-th item
     if (cidx >= S * a.Y) return;                          // (whole CTA, before any barrier)
-    const int I = cidx % S, yslice = cidx / S;
+    const int I = cidx % S, ylocal = cidx / S, yslice = a.y0 + ylocal;
     // thread t keeps atoms ia and ia + 32: warp w owns the i-clusters 2w and 2w+1 of the super tile
     const int ia = I * STILE + w * 64 + lane;
     double pi[2][6], auxi[2] = {0.0, 0.0}, ei[2][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
@@ -337,14 +340,14 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
             }
             __syncthreads();
             {
-                double* ej = a.epartJ + (size_t)(kk - 1) * 3 * np + (size_t)jb + tid;
+                double* ej = a.epartJ + (size_t)(kk - a.jrow0) * 3 * np + (size_t)jb + tid;
 #pragma unroll
                 for (int cc = 0; cc < 3; cc++)
                     ej[(size_t)cc * np] = ((sej[0][cc][tid] + sej[1][cc][tid]) + sej[2][cc][tid]) + sej[3][cc][tid];
             }
         }
     }
-    double* e = a.epartI + (size_t)(yslice * a.hsplit + blockIdx.z) * 3 * np;
+    double* e = a.epartI + (size_t)(ylocal * a.hsplit + blockIdx.z) * 3 * np;
 #pragma unroll
     for (int u = 0; u < 2; u++) {
         const int i = ia + 32 * u;
@@ -363,7 +366,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
 // One CTA = 32 consecutive atoms x 3 components x 8 lanes over the list; the lanes' sums are combined in lane order.
 __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, const int* __restrict__ offs, const int* __restrict__ rows,
                                                                 const double* __restrict__ epartI,
-                                                                const double* __restrict__ epartJ,
+                                                                const double* __restrict__ epartJ, int accumulate,
                                                                 double* __restrict__ esum) {
     __shared__ double part[8][3][32];
     const int li = threadIdx.x & 31, lk = threadIdx.x >> 5;
@@ -388,7 +391,7 @@ __global__ void __launch_bounds__(256) dipole_sym_reduce_kernel(int np, const in
         double s = part[0][cc][li];
 #pragma unroll
         for (int q = 1; q < 8; q++) s += part[q][cc][li];
-        esum[(size_t)cc * np + i] = s;
+        esum[(size_t)cc * np + i] = accumulate ? esum[(size_t)cc * np + i] + s : s;  // later slice ranges add to the first
     }
 }
 
@@ -490,18 +493,20 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
 // (device, layout): [S + 1] CSR offsets followed by the entries.  The layout changes only with the padded atom count
 // or the shard, so the steady state is a map lookup.
 struct ReduceListKey {
-    int dev, S, K, Y, kper, hsplit, rank, world;
+    int dev, S, K, y0, Y, kper, hsplit, rank, world;
     bool operator<(const ReduceListKey& o) const {
-        return std::tie(dev, S, K, Y, kper, hsplit, rank, world) < std::tie(o.dev, o.S, o.K, o.Y, o.kper, o.hsplit, o.rank, o.world);
+        return std::tie(dev, S, K, y0, Y, kper, hsplit, rank, world) <
+               std::tie(o.dev, o.S, o.K, o.y0, o.Y, o.kper, o.hsplit, o.rank, o.world);
     }
 };
-static const int* sym_reduce_list(int S, int K, int Y, int kper, int hsplit, int rank, int world, cudaStream_t st) {
+// slices [y0, y0 + Y) of a contraction with offsets 0..K in slices of kper
+static const int* sym_reduce_list(int S, int K, int y0, int Y, int kper, int hsplit, int rank, int world, cudaStream_t st) {
     static std::map<ReduceListKey, int*> cache;
     static std::mutex mu;
     std::lock_guard<std::mutex> lock(mu);
     ReduceListKey key;
     cudaGetDevice(&key.dev);
-    key.S = S, key.K = K, key.Y = Y, key.kper = kper, key.hsplit = hsplit, key.rank = rank, key.world = world;
+    key.S = S, key.K = K, key.y0 = y0, key.Y = Y, key.kper = kper, key.hsplit = hsplit, key.rank = rank, key.world = world;
     auto it = cache.find(key);
     if (it != cache.end()) return it->second;
     if (cache.size() > 64) {  // uVT runs walk through many sizes: drop the old layouts (no launch is in flight on them
@@ -514,16 +519,17 @@ static const int* sym_reduce_list(int S, int K, int Y, int kper, int hsplit, int
         cudaSetDevice(key.dev);
     }
     std::vector<int> offs(S + 1, 0), rows;
+    const int jrow0 = std::max(y0 * kper, 1), kend = std::min((y0 + Y) * kper - 1, K);
     for (int J = 0; J < S; J++) {
         offs[J] = (int)rows.size();
-        for (int y = 0; y < Y * hsplit; y++)  // I side: item (J, y / hsplit) wrote row y
+        for (int y = 0; y < Y * hsplit; y++)  // I side: item (J, y0 + y / hsplit) wrote row y
             if (((y / hsplit) * S + J) % world == rank) rows.push_back(y);
-        for (int kk = 1; kk <= K; kk++) {  // J side: item (J - kk, slice of kk) wrote row kk - 1
+        for (int kk = jrow0; kk <= kend; kk++) {  // J side: item (J - kk, slice of kk) wrote row kk - jrow0
             int I = J - kk;
             if (I < 0) I += S;
-            if (((kk / kper) * S + I) % world != rank) continue;
+            if (((kk / kper - y0) * S + I) % world != rank) continue;
             if (2 * kk == S && I >= kk) continue;  // even S: the half-way offset belongs to I < S/2
-            rows.push_back((kk - 1) | (1 << 30));
+            rows.push_back((kk - jrow0) | (1 << 30));
         }
     }
     offs[S] = (int)rows.size();
@@ -554,9 +560,31 @@ void launch_peer_signal(const PeerSignal& sig, cudaStream_t s) {
 
 int dipole_sym_tile() { return STILE; }
 
-int dipole_sym_partial_rows(int n_pad) {
-    const int K = (n_pad / STILE) / 2;
-    return K > 1 ? K : 1;
+// J-side partial rows are one [3][n_pad] row per offset of a launch: N^2/512 doubles for a whole contraction (102 MB at
+// 63k atoms, 2 GB at 256k, 17 GB at 1M).  Above MPMC_B200_SYM_PART_MB (default 1024) a contraction is cut into launches
+// over slice ranges that reuse one buffer of that size, so the resident image stays O(N) + the cap.
+static size_t sym_part_cap_bytes() {
+    static const size_t cap = [] {
+        const char* v = getenv("MPMC_B200_SYM_PART_MB");
+        const double mb = v ? atof(v) : 1024.0;
+        return (size_t)((mb > 0.0 ? mb : 1024.0) * 1048576.0);
+    }();
+    return cap;
+}
+static int sym_slices_per_launch(int n_pad, int kper, int Y) {
+    const size_t row_bytes = (size_t)3 * n_pad * sizeof(double);
+    const size_t rows_cap = std::max<size_t>(sym_part_cap_bytes() / row_bytes, 1);
+    int spr = (int)std::min<size_t>(rows_cap / (size_t)kper, (size_t)Y);
+    return spr < 1 ? 1 : spr;
+}
+int dipole_sym_partial_rows(int n_pad, int ysplits) {
+    const int S = n_pad / STILE, K = S / 2;
+    if (ysplits < 1) ysplits = 1;
+    if (ysplits > K + 1) ysplits = K + 1;
+    const int kper = (K + 1 + ysplits - 1) / ysplits;
+    const int Y = (K + 1 + kper - 1) / kper;
+    const int rows = sym_slices_per_launch(n_pad, kper, Y) * kper;
+    return rows > 1 ? rows : 1;
 }
 
 void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
@@ -602,13 +630,18 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
     // Sharding unit: the work item (I tile, offset slice y) -- every item has the same number of pairs; the items are
     // dealt out round robin over their y-major order, so the ranks differ by at most one item and hold the same mix of
     // damped and far tile pairs.  One CTA per owned item, in that order (heavy near-diagonal slices first).
-    const int items = S * ysplits;
-    a.Y = ysplits;
     a.rank = rank;
     a.world = world;
-    const int mine = items > rank ? (items - rank + world - 1) / world : 0;
-    if (mine > 0) {
-        dim3 grid(mine, 1, a.hsplit);
+    const int spr = sym_slices_per_launch(np, a.kper, ysplits);
+    for (int y0 = 0, round = 0; y0 < ysplits; y0 += spr, round++) {
+        const int Yr = std::min(spr, ysplits - y0);
+        const int items = S * Yr;
+        a.Y = Yr;
+        a.y0 = y0;
+        a.jrow0 = std::max(y0 * a.kper, 1);
+        const int mine = items > rank ? (items - rank + world - 1) / world : 0;
+        if (mine > 0) {
+            dim3 grid(mine, 1, a.hsplit);
 #define LAUNCH(ORTHO, DAMP, WF, FE) dipole_sym_kernel<ORTHO, DAMP, WF, FE><<<grid, TILE, 0, s>>>(c, k, a)
 #define DISPATCH(ORTHO)                                                         \
     if (o.damp_type == MPMC_DAMP_EXPONENTIAL) {                                 \
@@ -625,16 +658,17 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
         if (o.wolf_full) LAUNCH(ORTHO, MPMC_DAMP_OFF, true, false);             \
         else LAUNCH(ORTHO, MPMC_DAMP_OFF, false, false);                        \
     }
-        if (ortho) {
-            DISPATCH(true)
-        } else {
-            DISPATCH(false)
-        }
+            if (ortho) {
+                DISPATCH(true)
+            } else {
+                DISPATCH(false)
+            }
 #undef DISPATCH
 #undef LAUNCH
+        }
+        const int* list = sym_reduce_list(S, K, y0, Yr, a.kper, a.hsplit, rank, world, s);
+        if (list) dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, list, list + S + 1, epartI, epartJ, round > 0 ? 1 : 0, esum);
     }
-    const int* list = sym_reduce_list(S, K, ysplits, a.kper, a.hsplit, rank, world, s);
-    if (list) dipole_sym_reduce_kernel<<<np / 32, 256, 0, s>>>(np, list, list + S + 1, epartI, epartJ, esum);
     if (sig && sig->world > 1) peer_signal_kernel<<<1, 32, 0, s>>>(*sig);
 }
 

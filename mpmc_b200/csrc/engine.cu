@@ -975,7 +975,7 @@ static int repack(Ctx* c) {
         if (const char* v = getenv("MPMC_B200_SYM_CTAS_PER_SM")) per_sm = std::max(1, atoi(v));
         c->sym_ysplits = std::max(1, std::min(K1, (per_sm * sms + own_tiles - 1) / own_tiles));
         if (c->cbox.ensure((size_t)6 * (pp / 32)) || c->sym_partI.ensure((size_t)2 * c->sym_ysplits * 3 * pp) ||
-            c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
+            c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp, c->sym_ysplits) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
             FAIL(11, "cudaMalloc failed");
     }
     CU(cudaMemsetAsync(c->ef_static.p, 0, sizeof(double) * 3 * np, st));

@@ -47,3 +47,39 @@ def test_cuda_matches_pin(engine, name):
     if polar:
         arr2 = engine.atom_arrays()
         assert np.array_equal(arr2["mu"], arr["mu"])
+
+
+def test_contraction_in_rounds_under_a_small_partial_buffer_cap(tmp_path):
+    """MPMC_B200_SYM_PART_MB bounds the J-side partial rows of the symmetric contraction (N^2/512 doubles for a whole
+    contraction): above the cap a contraction is cut into launches over slice ranges that reuse one buffer.  Forced here
+    with a 2 MB cap on the 21k-atom MOF (31 offsets -> several rounds) in a fresh process (the cap is read once), against
+    the pin; on >= 2 GPUs also sharded over a device group."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r"""
+import sys
+sys.path.insert(0, %r)
+import bench
+from mpmc_b200 import Engine
+from tests import pins
+import torch
+pin = pins.load("pin_mof_h2_21k")
+s = bench.build_workload("mof_h2_21k")
+devs = [None] + ([[0, 1]] if torch.cuda.device_count() >= 2 else [])
+for d in devs:
+    eng = Engine(0) if d is None else Engine(devices=d)
+    eng.set_system(s)
+    got = eng.energy()
+    dev = pins.deviation(pin, got.to_dict(), eng.atom_arrays())
+    assert dev["iterations_equal"] and dev["max"] <= 1e-10, (d, dev)
+    again = eng.energy()
+    assert again.polar == got.polar
+    eng.close()
+print("ROUNDS_OK", len(devs))
+""" % root
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, MPMC_B200_SYM_PART_MB="2", MPMC_B200_SYM_MIN="0"))
+    assert r.returncode == 0 and "ROUNDS_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
