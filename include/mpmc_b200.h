@@ -298,6 +298,27 @@ int mpmc_b200_phase_ms(mpmc_b200_ctx *ctx, const char *phase, double *ms);
  * roofline denominator because MEASURED_PEAKS.json carries no fp64 figure. */
 int mpmc_b200_measure_fp64_peak(mpmc_b200_ctx *ctx, double *tflops);
 
+/* No counterpart in the reference.  For callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the reciprocal-space
+ * Ewald energy -- the quantity of coulombic_reciprocal() (src/energy/coulombic.c:42-95) that mpmc_b200_energy()
+ * reports as energies.es_recip -- computed by a variant of the structure-factor kernel K2 whose scratch (per-chunk
+ * partial structure factors and S(k)) is a file-scope `static __device__` array of 4.9 MB instead of context
+ * buffers.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and enqueues three
+ * kernels on `cuda_stream` (a cudaStream_t passed as void*, NULL = the default stream) of the CURRENT device;
+ * it does not synchronise.  The first call on a device resolves the array's address (cudaGetSymbolAddress): make
+ * that call outside any capture.
+ *   DEVICE pointers:  d_pos[3*n] atom_t.pos, d_charge[n] atom_t.charge, d_frozen[n] atom_t.frozen (NULL: none
+ *                     frozen; frozen and uncharged atoms are skipped as coulombic.c:73-74 does), d_energy[1] (K).
+ *   HOST values:      reciprocal_basis[9] = pbc_t.reciprocal_basis[p][q] row-major, volume, ewald_alpha, ewald_kmax.
+ * Limits (the scratch is sized for them; beyond them the call fails with error 3 and a message):
+ *   0 <= n <= 1,048,576 atoms, 1 <= ewald_kmax <= 7 (the reference's default).
+ * Every GPU that loads the library holds the array until exit.  All calls share it and it keeps the last call's
+ * contents (each call writes every slot it reads; nothing has to be cleared by the caller): calls that overlap on
+ * the GPU -- different streams, concurrent graph launches -- race on it and must be serialised by the caller. */
+int mpmc_b200_recip_energy_static(int n, const double *d_pos, const double *d_charge, const int *d_frozen,
+                                  const double *reciprocal_basis, double volume, double ewald_alpha, int ewald_kmax,
+                                  double *d_energy, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

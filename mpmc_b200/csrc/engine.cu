@@ -28,6 +28,10 @@
 using namespace mpmc;
 
 static thread_local std::string g_err = "";
+// for entry points that live in other translation units (recip_static_kernel.cu)
+namespace mpmc {
+void set_last_error(const char* msg) { g_err = msg ? msg : ""; }
+}  // namespace mpmc
 
 #define CU(call)                                                                                      \
     do {                                                                                              \

@@ -8,6 +8,9 @@ namespace mpmc {
 
 enum : int { F_FROZEN = 1, F_VALID = 2 };
 
+// message behind mpmc_b200_last_error() (engine.cu), for entry points defined in other translation units
+void set_last_error(const char* msg);
+
 // All atoms, reference list order, padded to a multiple of TILE (pad atoms have flags == 0).
 struct AtomsDev {
     int n, n_pad;
