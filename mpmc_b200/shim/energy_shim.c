@@ -126,6 +126,12 @@ static int shim_threads(void) {
     }
     return g_threads;
 }
+/* writers.c formats with the same threads, above the same threshold */
+int mpmc_b200_shim_host_threads(int *min_atoms) {
+    const int t = shim_threads();
+    if (min_atoms) *min_atoms = g_threads_min;
+    return t;
+}
 
 static void *xrealloc(void *p, size_t bytes) {
     void *q = realloc(p, bytes ? bytes : 1);
