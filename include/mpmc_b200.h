@@ -29,6 +29,8 @@
  *   mpmc_b200_set_incremental, mpmc_b200_set_warm_start
  *                            no reference counterpart: opt-in accelerations of the same energy() (the
  *                            reference's TODO:2; its pair_t cache src/energy/pairs.c:243-250 is the idea)
+ *   mpmc_b200_mc_steps       the body of mc()'s loop for displacement moves (src/mc/mc.c:294-353): move, energy,
+ *                            Metropolis test, restore -- a batch of steps resident on the device
  *   mpmc_b200_get_atom_arrays  the per-atom fields polar() writes back:
  *                            mu, ef_static, ef_induced, ef_induced_change,
  *                            dipole_rrms (structs.h:47-49), rank_metric
@@ -297,6 +299,53 @@ int mpmc_b200_phase_ms(mpmc_b200_ctx *ctx, const char *phase, double *ms);
 /* fp64 FMA throughput probe (dependent-chain DFMA kernel), TFLOP/s; used as the
  * roofline denominator because MEASURED_PEAKS.json carries no fp64 figure. */
 int mpmc_b200_measure_fp64_peak(mpmc_b200_ctx *ctx, double *tflops);
+
+/*
+ * Resident MC steps: a batch of displacement moves evaluated AND decided on the device, with no host
+ * round trip between steps.  Replaces, for the steps it covers, the loop body of mc() (src/mc/mc.c:294-353):
+ *   make_move() DISPLACE = translate() + rotate()   (src/mc/mc_moves.c:376-464,713-731; the random numbers -- hence the
+ *                                                    translation vector, the rotation quaternion and the Metropolis
+ *                                                    draw -- come from the caller, who keeps the reference's RNG)
+ *   energy()                                         (src/energy/energy.c:67-226)
+ *   boltzmann_factor() NVT + the Metropolis test     (src/mc/mc.c:106-114,320)
+ *   restore() of the coordinates on a reject         (src/mc/mc_moves.c:744-804)
+ * Step j applies move j to the CURRENT device positions exactly as translate() / rotate() do on the host (centre of
+ * mass as update_com() computes it, src/energy/pairs.c:364-385; quaternion products in the reference's operation order,
+ * src/main/quaternion.c:76-86; no fused multiply-add), evaluates the energy, accepts iff
+ * u_accept < exp(-(E_new - E_cur) / temperature) and the solver did not fail, and on a reject puts the old coordinates
+ * back.  The caller replays the same steps on its lists from the returned decisions; the drop-in shim uses this
+ * speculatively -- the unmodified mc() stays in charge and every served step is checked against what make_move() really
+ * did (MPMC_B200_RESIDENT_STEPS).
+ * Single GPU; fixed-iteration solvers (or polarization off); no cavity_autoreject_absolute.  At most
+ * MPMC_B200_MC_MAX_STEPS steps per call and MPMC_B200_MC_MAX_ATOMS atoms per moved molecule.
+ */
+#define MPMC_B200_MC_MAX_ATOMS 16
+#define MPMC_B200_MC_MAX_STEPS 64
+typedef struct mpmc_b200_mc_move {
+    int first, count;        /* the molecule's atoms [first, first+count) in list order */
+    int explicit_positions;  /* 1: new_pos / old_pos are given (a move the caller already made and uploaded) */
+    int reserved;
+    double u_accept;         /* the Metropolis draw of this step (mc.c:320) */
+    double trans[3];         /* translate(): signed displacement (mc_moves.c:380-385) */
+    double quat[4];          /* rotate(): x, y, z, w of quaternion_construct_axis_angle_degree() (mc_moves.c:415-420) */
+    double mass[MPMC_B200_MC_MAX_ATOMS];         /* atom_t.mass, for the centre of mass */
+    double new_pos[3 * MPMC_B200_MC_MAX_ATOMS];  /* explicit_positions only */
+    double old_pos[3 * MPMC_B200_MC_MAX_ATOMS];  /* explicit_positions only: what a reject restores */
+} mpmc_b200_mc_move;
+typedef struct mpmc_b200_mc_result {
+    mpmc_b200_energies e;    /* what mpmc_b200_energy() would have returned for the trial configuration */
+    int accepted;            /* the device's decision */
+    int reserved;
+    double new_pos[3 * MPMC_B200_MC_MAX_ATOMS];  /* the trial coordinates of the moved atoms */
+    double old_pos[3 * MPMC_B200_MC_MAX_ATOMS];  /* their coordinates before the move */
+} mpmc_b200_mc_result;
+int mpmc_b200_mc_steps(mpmc_b200_ctx *ctx, int nsteps, const mpmc_b200_mc_move *moves, double temperature,
+                       double current_energy, mpmc_b200_mc_result *results);
+/* Per-atom results of step `step` of the last mpmc_b200_mc_steps() call (what mpmc_b200_atom_arrays_view() would have
+ * shown after that step's evaluation); pointers into pinned host memory, valid until the next call on this context. */
+int mpmc_b200_mc_step_arrays_view(mpmc_b200_ctx *ctx, int step, const double **mu, const double **ef_static,
+                                  const double **ef_induced, const double **ef_induced_change, const double **dipole_rrms,
+                                  const double **rank_metric);
 
 /* No counterpart in the reference.  For callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the reciprocal-space

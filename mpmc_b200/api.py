@@ -346,7 +346,7 @@ ABI_SYMBOLS = [
     "mpmc_b200_peer_export", "mpmc_b200_peer_connect", "mpmc_b200_peer_active",
     "mpmc_b200_get_counters", "mpmc_b200_phase_ms", "mpmc_b200_measure_fp64_peak", "mpmc_b200_set_incremental",
     "mpmc_b200_set_warm_start", "mpmc_b200_create_group", "mpmc_b200_group_size", "mpmc_b200_atom_arrays_view",
-    "mpmc_b200_recip_energy_static",
+    "mpmc_b200_recip_energy_static", "mpmc_b200_mc_steps", "mpmc_b200_mc_step_arrays_view",
 ]
 
 

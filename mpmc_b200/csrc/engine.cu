@@ -317,6 +317,17 @@ struct mpmc_b200_ctx {
     float contract_ms_sum = 0.f;
     int contract_launches = 0;
 
+    // resident MC steps (mpmc_b200_mc_steps): the batch's moves and per-step records on the device, and a
+    // ring of per-step write-back images (14 n doubles each) with its pinned host copy
+    DevBuf<mpmc_b200_mc_move> mc_moves;
+    DevBuf<McStepDev> mc_res;
+    DevBuf<double> mc_ecur, mc_ring;
+    McStepDev* h_mc_res = nullptr;  // pinned
+    double* h_mc_ring = nullptr;    // pinned
+    size_t h_mc_res_cap = 0, h_mc_ring_cap = 0;
+    int mc_last_steps = 0;
+    bool mc_ring_valid = false;
+
     mpmc_b200_counters cnt{};
     int launches = 0;
     int pending_iterations = 0, pending_iter_success = 0;
@@ -2048,40 +2059,10 @@ static int enqueue_energy(Ctx* c, bool with_pair_part, bool with_polar_part) {
     return 0;
 }
 
-static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
-    if (!c->pending) FAIL(2, "no evaluation pending");
+// The 32 device scalars of one evaluation (+ the host-side analytic terms) -> what energy() reports.  Shared by
+// finish_energy() and the resident MC steps, which keep one scalar set per step.
+static int assemble_energies(Ctx* c, const double* h, mpmc_b200_energies* out) {
     const mpmc_b200_params& P = c->P;
-    cudaStream_t st = c->stream;
-    join_side(c);
-    CU(cudaMemcpyAsync(c->h_scalars, c->scalars.p, sizeof(double) * 32, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    c->pending = false;
-    for (int p = 0; p < PH_COUNT; p++) {
-        c->phase_ms[p] = 0.f;
-        if (c->ev_used[p]) cudaEventElapsedTime(&c->phase_ms[p], c->ev[p][0], c->ev[p][1]);
-    }
-    c->contract_ms_sum = 0.f;
-    c->contract_launches = c->kev_used / 2;
-    for (int k = 0; k + 1 < c->kev_used; k += 2) {
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, c->kev[k], c->kev[k + 1]);
-        c->contract_ms_sum += ms;
-    }
-    const double* h = c->h_scalars;
-    if (c->gs_trace.p && c->last_had_polar && (c->P.polar_gs || c->P.polar_gs_ranked) && c->pol.n > 0) {
-        // profiling aid: where the resolver of the last persistent sweep spent its time, per 128-atom block
-        const int nb = (c->pol.n + TILE - 1) / TILE;
-        std::vector<unsigned long long> t((size_t)nb * 8);
-        if (cudaMemcpy(t.data(), c->gs_trace.p, sizeof(unsigned long long) * t.size(), cudaMemcpyDeviceToHost) == cudaSuccess && nb > 4) {
-            double acc[5] = {0, 0, 0, 0, 0};
-            for (int b = 2; b < nb - 1; b++)
-                for (int k = 0; k < 5; k++) acc[k] += (double)(t[(size_t)b * 8 + k + 1] - t[(size_t)b * 8 + k]);
-            fprintf(stderr, "MPMC_B200_GS_TRACE: %d blocks, sweep %.3f ms; per block (us): wait for pushers %.2f, load %.2f, "
-                            "chains + cross pushes %.2f, publish %.2f, push to next block %.2f\n",
-                    nb, (double)(t[(size_t)(nb - 1) * 8 + 5] - t[0]) * 1e-6, acc[0] / (nb - 3) * 1e-3, acc[1] / (nb - 3) * 1e-3,
-                    acc[2] / (nb - 3) * 1e-3, acc[3] / (nb - 3) * 1e-3, acc[4] / (nb - 3) * 1e-3);
-        }
-    }
     if (h[S_PEER_TIMEOUT] != 0.0) FAIL(12, "peer exchange timed out: a rank never published its induced-field partial sums");
     if (h[S_GS_TIMEOUT] != 0.0) FAIL(12, "Gauss-Seidel sweep timed out: a CTA of the persistent sweep waited 2 s for another");
     memset(out, 0, sizeof(*out));
@@ -2129,6 +2110,43 @@ static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
     }
     out->total = out->rd + out->coulombic + out->polar;  // energy.c:194
     return 0;
+}
+
+static int finish_energy(Ctx* c, mpmc_b200_energies* out) {
+    if (!c->pending) FAIL(2, "no evaluation pending");
+    const mpmc_b200_params& P = c->P;
+    cudaStream_t st = c->stream;
+    join_side(c);
+    CU(cudaMemcpyAsync(c->h_scalars, c->scalars.p, sizeof(double) * 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    c->pending = false;
+    for (int p = 0; p < PH_COUNT; p++) {
+        c->phase_ms[p] = 0.f;
+        if (c->ev_used[p]) cudaEventElapsedTime(&c->phase_ms[p], c->ev[p][0], c->ev[p][1]);
+    }
+    c->contract_ms_sum = 0.f;
+    c->contract_launches = c->kev_used / 2;
+    for (int k = 0; k + 1 < c->kev_used; k += 2) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->kev[k], c->kev[k + 1]);
+        c->contract_ms_sum += ms;
+    }
+    const double* h = c->h_scalars;
+    if (c->gs_trace.p && c->last_had_polar && (c->P.polar_gs || c->P.polar_gs_ranked) && c->pol.n > 0) {
+        // profiling aid: where the resolver of the last persistent sweep spent its time, per 128-atom block
+        const int nb = (c->pol.n + TILE - 1) / TILE;
+        std::vector<unsigned long long> t((size_t)nb * 8);
+        if (cudaMemcpy(t.data(), c->gs_trace.p, sizeof(unsigned long long) * t.size(), cudaMemcpyDeviceToHost) == cudaSuccess && nb > 4) {
+            double acc[5] = {0, 0, 0, 0, 0};
+            for (int b = 2; b < nb - 1; b++)
+                for (int k = 0; k < 5; k++) acc[k] += (double)(t[(size_t)b * 8 + k + 1] - t[(size_t)b * 8 + k]);
+            fprintf(stderr, "MPMC_B200_GS_TRACE: %d blocks, sweep %.3f ms; per block (us): wait for pushers %.2f, load %.2f, "
+                            "chains + cross pushes %.2f, publish %.2f, push to next block %.2f\n",
+                    nb, (double)(t[(size_t)(nb - 1) * 8 + 5] - t[0]) * 1e-6, acc[0] / (nb - 3) * 1e-3, acc[1] / (nb - 3) * 1e-3,
+                    acc[2] / (nb - 3) * 1e-3, acc[3] / (nb - 3) * 1e-3, acc[4] / (nb - 3) * 1e-3);
+        }
+    }
+    return assemble_energies(c, h, out);
 }
 
 // ================================================================================================
@@ -2546,6 +2564,8 @@ void mpmc_b200_destroy(mpmc_b200_ctx* c) {
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->h_wb) cudaFreeHost(c->h_wb);
+    if (c->h_mc_res) cudaFreeHost(c->h_mc_res);
+    if (c->h_mc_ring) cudaFreeHost(c->h_mc_ring);
     peer_teardown(c);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -2885,6 +2905,132 @@ int mpmc_b200_energy_finish(mpmc_b200_ctx* c, mpmc_b200_energies* out) {
     return finish_energy(c, out);
 }
 
+// ================================================================================================
+// Resident MC steps: a batch of displacement moves evaluated and decided on the device.  Per step, on the
+// engine's stream and without any host synchronisation: mc_move_kernel (translate + rotate of one molecule in the
+// list-order coordinates, old coordinates kept), the whole evaluation (enqueue_energy: the subsets and cluster boxes are
+// refreshed from the list-order coordinates), the write-back image of that evaluation into the step's ring slot, and
+// mc_decide_kernel (total, Metropolis test, coordinates put back on a reject).  One D2H of the per-step records and the
+// ring at the end.  The spatial order is left alone during a batch (it is a matter of speed, not of results) and
+// re-examined afterwards from the final coordinates.
+// ================================================================================================
+static int enqueue_writeback(mpmc_b200_ctx* c, double* dst, int kb, int ke);
+int mpmc_b200_mc_steps(mpmc_b200_ctx* c, int nsteps, const mpmc_b200_mc_move* moves, double temperature,
+                       double current_energy, mpmc_b200_mc_result* results) {
+    if (!c || !moves || !results) FAIL(1, "null argument");
+    if (!c->have_params || !c->have_atoms) FAIL(2, "no system");
+    if (nsteps < 1 || nsteps > MPMC_B200_MC_MAX_STEPS) FAIL(1, "mpmc_b200_mc_steps: nsteps outside 1..MPMC_B200_MC_MAX_STEPS");
+    if (c->world > 1 || c->group.size() > 1) FAIL(3, "mpmc_b200_mc_steps: single GPU only");
+    const mpmc_b200_params& P = c->P;
+    const bool polar = P.polarization && !P.rd_only;
+    if (P.cavity_autoreject_absolute) FAIL(3, "mpmc_b200_mc_steps: cavity_autoreject_absolute needs the host between the pair sums and the rest");
+    if (polar && P.polar_precision != 0.0 && !P.polar_zodid) FAIL(3, "mpmc_b200_mc_steps: fixed-iteration solvers only (polar_precision reads a scalar per pass)");
+    if (!(temperature > 0.0)) FAIL(1, "mpmc_b200_mc_steps: temperature must be positive");
+    for (int j = 0; j < nsteps; j++)
+        if (moves[j].count < 1 || moves[j].count > MPMC_B200_MC_MAX_ATOMS || moves[j].first < 0 || moves[j].first + moves[j].count > c->n)
+            FAIL(1, "mpmc_b200_mc_steps: a move's atom range is empty, longer than MPMC_B200_MC_MAX_ATOMS or out of bounds");
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const size_t ring_per_step = polar ? (size_t)14 * c->n : 0;
+    if (c->mc_moves.ensure(MPMC_B200_MC_MAX_STEPS) || c->mc_res.ensure(MPMC_B200_MC_MAX_STEPS) || c->mc_ecur.ensure(1) ||
+        (ring_per_step && c->mc_ring.ensure(ring_per_step * nsteps)))
+        FAIL(11, "cudaMalloc failed");
+    if (c->h_mc_res_cap < (size_t)MPMC_B200_MC_MAX_STEPS) {
+        c->h_mc_res_cap = MPMC_B200_MC_MAX_STEPS;
+        CU(cudaMallocHost(&c->h_mc_res, sizeof(McStepDev) * c->h_mc_res_cap));
+    }
+    if (c->h_mc_ring_cap < ring_per_step * nsteps) {
+        if (c->h_mc_ring) cudaFreeHost(c->h_mc_ring);
+        c->h_mc_ring = nullptr;
+        c->h_mc_ring_cap = ring_per_step * nsteps + ring_per_step;
+        CU(cudaMallocHost(&c->h_mc_ring, sizeof(double) * c->h_mc_ring_cap));
+    }
+    c->mc_ring_valid = false;
+    c->inc_valid = false;
+    inc_clear_moved(c);
+    c->warm_valid = false;
+    CU(cudaMemcpyAsync(c->mc_moves.p, moves, sizeof(mpmc_b200_mc_move) * nsteps, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(c->mc_ecur.p, &current_energy, sizeof(double), cudaMemcpyHostToDevice, st));
+    if (c->kdirty)
+        if (build_kvectors(c)) return 10;
+    if (c->analytic_dirty) compute_analytic(c);
+    McDecide k;
+    k.lrc_pair = c->lrc_pair, k.lrc_self = c->lrc_self, k.es_self = c->es_self, k.crystal_self = c->crystal_self;
+    k.temperature = temperature;
+    k.rd_only = P.rd_only, k.es_wolf = P.es_wolf, k.rd_crystal = P.rd_crystal, k.polar = polar ? 1 : 0, k.palmo = P.polar_palmo;
+    k.s_pair = S_PAIR, k.s_recip = S_RECIP, k.s_polar = S_POLAR, k.s_crystal = S_CRYSTAL, k.s_fused_out = S_FUSED_OUT;
+    int launches = 0;
+    for (int j = 0; j < nsteps; j++) {
+        launch_mc_move(c->mc_moves.p, j, c->x.p, c->y.p, c->z.p, c->mc_res.p, st);
+        c->subsets_stale = true;
+        c->boxes_fresh = false;
+        const bool resort = c->resort_pending;
+        if (j > 0) c->resort_pending = false;  // the host mirror of the coordinates is stale inside a batch
+        const int rc = enqueue_energy(c, true, true);
+        c->resort_pending = c->resort_pending || (j > 0 && resort);
+        if (rc) return rc;
+        if (ring_per_step && enqueue_writeback(c, c->mc_ring.p + ring_per_step * j, 0, c->pol.n)) return 10;
+        k.iter_from_device = c->iter_from_device ? 1 : 0;
+        k.iter_success = c->pending_iter_success;
+        launch_mc_decide(c->mc_moves.p, j, k, c->scalars.p, c->mc_ecur.p, c->x.p, c->y.p, c->z.p, c->mc_res.p, st);
+        launches += c->launches + 2 + (ring_per_step ? 1 : 0);
+    }
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(c->h_mc_res, c->mc_res.p, sizeof(McStepDev) * nsteps, cudaMemcpyDeviceToHost, st));
+    if (ring_per_step)
+        CU(cudaMemcpyAsync(c->h_mc_ring, c->mc_ring.p, sizeof(double) * ring_per_step * nsteps, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    c->pending = false;
+    c->subsets_stale = true;  // the last decision may have put coordinates back after the subsets were gathered
+    c->boxes_fresh = false;
+    const int pend_it = c->pending_iterations, pend_ok = c->pending_iter_success;
+    for (int j = 0; j < nsteps; j++) {
+        const McStepDev& r = c->h_mc_res[j];
+        c->pending_iterations = pend_it;
+        c->pending_iter_success = pend_ok;
+        if (const int rc = assemble_energies(c, r.scalars, &results[j].e)) return rc;
+        results[j].accepted = r.accepted != 0.0 ? 1 : 0;
+        results[j].reserved = 0;
+        memcpy(results[j].new_pos, r.new_pos, sizeof(r.new_pos));
+        memcpy(results[j].old_pos, r.old_pos, sizeof(r.old_pos));
+        // the host mirror follows the decisions
+        const double* fin = results[j].accepted ? r.new_pos : r.old_pos;
+        for (int i = 0; i < moves[j].count; i++) {
+            const int g = moves[j].first + i;
+            c->hx[g] = fin[3 * i], c->hy[g] = fin[3 * i + 1], c->hz[g] = fin[3 * i + 2];
+        }
+    }
+    c->cnt.kernel_launches = launches;
+    if ((c->pol_sorted || c->use_clusters) && !c->resort_pending && c->hx_sort.size() == c->hx.size()) {
+        const double lim2 = 1.5 * 1.5;  // as mpmc_b200_set_positions: clusters stay compact while no atom drifted far
+        for (int j = 0; j < nsteps && !c->resort_pending; j++)
+            for (int i = 0; i < moves[j].count; i++) {
+                const int g = moves[j].first + i;
+                const double dx = c->hx[g] - c->hx_sort[g], dy = c->hy[g] - c->hy_sort[g], dz = c->hz[g] - c->hz_sort[g];
+                if (dx * dx + dy * dy + dz * dz > lim2) c->resort_pending = true;
+            }
+    }
+    c->mc_last_steps = nsteps;
+    c->mc_ring_valid = ring_per_step != 0;
+    return 0;
+}
+
+int mpmc_b200_mc_step_arrays_view(mpmc_b200_ctx* c, int step, const double** mu, const double** ef_static,
+                                  const double** ef_induced, const double** ef_induced_change, const double** dipole_rrms,
+                                  const double** rank_metric) {
+    if (!c) FAIL(1, "null ctx");
+    if (!c->mc_ring_valid || step < 0 || step >= c->mc_last_steps) FAIL(2, "no per-atom results of that step (mpmc_b200_mc_steps with polarization on)");
+    const size_t n = (size_t)c->n;
+    const double* h = c->h_mc_ring + (size_t)14 * n * step;
+    if (mu) *mu = h;
+    if (ef_static) *ef_static = h + 3 * n;
+    if (ef_induced) *ef_induced = h + 6 * n;
+    if (ef_induced_change) *ef_induced_change = h + 9 * n;
+    if (dipole_rrms) *dipole_rrms = h + 12 * n;
+    if (rank_metric) *rank_metric = h + 13 * n;
+    return 0;
+}
+
 int mpmc_b200_polar_stage(mpmc_b200_ctx* c, int stage, int iteration) {
     if (!c) FAIL(1, "null ctx");
     if (!c->have_params || !c->have_atoms) FAIL(2, "no system");
@@ -3027,6 +3173,20 @@ int mpmc_b200_shard_rows(mpmc_b200_ctx* c, int* begin, int* end, int* n_pol, int
 }
 
 // what polar() leaves in atom_t, assembled on the device in the caller's layout -> the pinned host image c->h_wb
+// the write-back image of the evaluation that was just enqueued (writeback_kernel), into `dst` (14 n doubles)
+static int enqueue_writeback(mpmc_b200_ctx* c, double* dst, int kb, int ke) {
+    const int n = c->n, np = c->n_pad, pp = c->pol.n_pad;
+    cudaStream_t st = c->stream;
+    CU(cudaMemsetAsync(dst, 0, sizeof(double) * (size_t)14 * n, st));
+    const int m = std::max(n, std::max(c->pol.n, c->nonpol.n));
+    writeback_kernel<<<(m + 255) / 256, 256, 0, st>>>(
+        n, np, c->ef_static.p, c->pol.n, pp, c->pol.didx.p, c->mu.p, c->eind.p, c->eic.p, c->rrms.p, c->rank_packed.p, kb, ke,
+        c->nonpol.n, c->nonpol.n_pad, c->nonpol.didx.p, c->eind_np_valid ? c->eind_np.p : nullptr,
+        c->eic_np_valid ? c->eic_np.p : nullptr, dst);
+    CU(cudaGetLastError());
+    return 0;
+}
+
 static int fetch_atom_arrays(mpmc_b200_ctx* c) {
     if (!c) FAIL(1, "null ctx");
     if (!c->have_atoms) FAIL(2, "no atoms");
@@ -3067,13 +3227,7 @@ static int fetch_atom_arrays(mpmc_b200_ctx* c) {
                                        sizeof(double) * (size_t)(te - tb) * TILE, st));
         }
     }
-    CU(cudaMemsetAsync(c->wb.p, 0, sizeof(double) * total, st));
-    const int m = std::max(n, std::max(c->pol.n, c->nonpol.n));
-    writeback_kernel<<<(m + 255) / 256, 256, 0, st>>>(
-        n, np, c->ef_static.p, c->pol.n, pp, c->pol.didx.p, c->mu.p, c->eind.p, c->eic.p, c->rrms.p, c->rank_packed.p, kb, ke,
-        c->nonpol.n, c->nonpol.n_pad, c->nonpol.didx.p, c->eind_np_valid ? c->eind_np.p : nullptr,
-        c->eic_np_valid ? c->eic_np.p : nullptr, c->wb.p);
-    CU(cudaGetLastError());
+    if (enqueue_writeback(c, c->wb.p, kb, ke)) return 10;
     CU(cudaMemcpyAsync(c->h_wb, c->wb.p, sizeof(double) * total, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     return 0;

@@ -286,4 +286,21 @@ void launch_ewald_palmo_finish(const SubsetDev& pol, const double* es, const dou
 // fp64 FMA throughput probe
 double measure_fp64_peak_tflops(cudaStream_t s);
 
+// ---- resident MC steps (mc_step_kernel.cu) -----------------------------------------
+// replaces, per step of a batch: make_move() DISPLACE (src/mc/mc_moves.c:376-464,713-731), the Metropolis test
+// (src/mc/mc.c:106-114,320) and restore() of the coordinates (mc_moves.c:744-804)
+struct McStepDev {  // what a step leaves on the device
+    double scalars[32];
+    double total, accepted;
+    double new_pos[3 * MPMC_B200_MC_MAX_ATOMS], old_pos[3 * MPMC_B200_MC_MAX_ATOMS];
+};
+struct McDecide {  // what assemble_energies() (engine.cu) adds on the host, and which slots it reads
+    double lrc_pair, lrc_self, es_self, crystal_self, temperature;
+    int rd_only, es_wolf, rd_crystal, polar, palmo, iter_from_device, iter_success;
+    int s_pair, s_recip, s_polar, s_crystal, s_fused_out;
+};
+void launch_mc_move(const mpmc_b200_mc_move* moves, int j, double* x, double* y, double* z, McStepDev* res, cudaStream_t s);
+void launch_mc_decide(const mpmc_b200_mc_move* moves, int j, const McDecide& k, const double* scalars, double* e_current,
+                      double* x, double* y, double* z, McStepDev* res, cudaStream_t s);
+
 }  // namespace mpmc

@@ -6,6 +6,7 @@
  * cached-sequence pass, change detection, uVT relinking, the observables epilogue, the write-back into atom_t -- is
  * exercised by the CPU test suite against the reference's fixed-seed trajectories (tests/test_shim_host_cpu.py).
  * libmpmc_b200.so itself has no CPU path: mpmc_b200_create() fails without a CUDA device (tests/test_abi_cpu.py). */
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -26,6 +27,8 @@ struct mpmc_b200_ctx {
     double *pos, *q, *alpha, *eps, *sig, *mm;
     int *mol, *frozen;
     double *mu, *es, *ei, *eic, *rrms, *rank;
+    double *ring; /* mpmc_b200_mc_steps: per-step copies of the six per-atom arrays, 14 n doubles each */
+    int ring_steps, ring_n;
 };
 
 static const char *g_err = "";
@@ -49,7 +52,7 @@ int mpmc_b200_group_size(mpmc_b200_ctx *c) { return c ? g_group : 0; }
 void mpmc_b200_destroy(mpmc_b200_ctx *c) {
     if (!c) return;
     free(c->pos), free(c->q), free(c->alpha), free(c->eps), free(c->sig), free(c->mm), free(c->mol), free(c->frozen);
-    free(c->mu), free(c->es), free(c->ei), free(c->eic), free(c->rrms), free(c->rank);
+    free(c->mu), free(c->es), free(c->ei), free(c->eic), free(c->rrms), free(c->rank), free(c->ring);
     free(c);
 }
 
@@ -124,5 +127,102 @@ int mpmc_b200_atom_arrays_view(mpmc_b200_ctx *c, const double **mu, const double
     if (ef_induced_change) *ef_induced_change = c->eic;
     if (dipole_rrms) *dipole_rrms = c->rrms;
     if (rank_metric) *rank_metric = c->rank;
+    return 0;
+}
+
+/* Resident MC steps on the CPU stand-in: the plain-C restatement of what mc_step_kernel.cu does on the device --
+ * translate() / rotate() (src/mc/mc_moves.c:376-464) about the centre of mass of update_com() (src/energy/pairs.c:364-385)
+ * with quaternion_multiplication()'s operation order (src/main/quaternion.c:76-86), the oracle's energy, the NVT
+ * Metropolis test (src/mc/mc.c:106-114,320), coordinates put back on a reject.  gcc on x86-64 without -mfma rounds every
+ * operation separately, as the reference's own objects do. */
+typedef struct {
+    double x, y, z, w;
+} stub_quat;
+static stub_quat stub_qmul(stub_quat a, stub_quat b) {
+    stub_quat r;
+    r.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+    r.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+    r.y = a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x;
+    r.z = a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w;
+    return r;
+}
+
+int mpmc_b200_mc_steps(mpmc_b200_ctx *c, int nsteps, const mpmc_b200_mc_move *moves, double temperature, double current_energy,
+                       mpmc_b200_mc_result *results) {
+    const size_t n = (size_t)c->n;
+    int j, i, p;
+    if (nsteps < 1 || nsteps > MPMC_B200_MC_MAX_STEPS) {
+        g_err = "nsteps out of range";
+        return 1;
+    }
+    c->ring = (double *)realloc(c->ring, sizeof(double) * 14 * n * (size_t)nsteps);
+    c->ring_steps = nsteps;
+    c->ring_n = c->n;
+    for (j = 0; j < nsteps; j++) {
+        const mpmc_b200_mc_move *m = &moves[j];
+        mpmc_b200_mc_result *r = &results[j];
+        double *pos = c->pos + 3 * (size_t)m->first;
+        double *slot = c->ring + 14 * n * (size_t)j;
+        int rc;
+        memset(r, 0, sizeof(*r));
+        if (m->explicit_positions) {
+            memcpy(r->old_pos, m->old_pos, sizeof(double) * 3 * m->count);
+            memcpy(r->new_pos, m->new_pos, sizeof(double) * 3 * m->count);
+            memcpy(pos, m->new_pos, sizeof(double) * 3 * m->count);
+        } else {
+            double mass = 0, com[3] = {0, 0, 0};
+            stub_quat q = {m->quat[0], m->quat[1], m->quat[2], m->quat[3]}, qc = {-m->quat[0], -m->quat[1], -m->quat[2], m->quat[3]};
+            memcpy(r->old_pos, pos, sizeof(double) * 3 * m->count);
+            for (i = 0; i < m->count; i++) {
+                mass += m->mass[i];
+                for (p = 0; p < 3; p++) com[p] += m->mass[i] * pos[3 * i + p];
+            }
+            for (p = 0; p < 3; p++) com[p] = com[p] / mass;
+            for (p = 0; p < 3; p++) com[p] += m->trans[p];
+            for (i = 0; i < m->count; i++)
+                for (p = 0; p < 3; p++) pos[3 * i + p] += m->trans[p];
+            for (i = 0; i < m->count; i++) {
+                stub_quat pv = {pos[3 * i] - com[0], pos[3 * i + 1] - com[1], pos[3 * i + 2] - com[2], 0.}, a;
+                a = stub_qmul(pv, qc);
+                a = stub_qmul(q, a);
+                pos[3 * i] = a.x + com[0];
+                pos[3 * i + 1] = a.y + com[1];
+                pos[3 * i + 2] = a.z + com[2];
+            }
+            memcpy(r->new_pos, pos, sizeof(double) * 3 * m->count);
+        }
+        rc = mpmc_b200_energy(c, &r->e);
+        if (rc) return rc;
+        memcpy(slot, c->mu, sizeof(double) * 3 * n), memcpy(slot + 3 * n, c->es, sizeof(double) * 3 * n);
+        memcpy(slot + 6 * n, c->ei, sizeof(double) * 3 * n), memcpy(slot + 9 * n, c->eic, sizeof(double) * 3 * n);
+        memcpy(slot + 12 * n, c->rrms, sizeof(double) * n), memcpy(slot + 13 * n, c->rank, sizeof(double) * n);
+        {
+            double bf = 0.0;
+            if (isfinite(r->e.total)) bf = exp(-(r->e.total - current_energy) / temperature);
+            r->accepted = (m->u_accept < bf) && r->e.iter_success == 0;
+        }
+        if (r->accepted)
+            current_energy = r->e.total;
+        else
+            memcpy(pos, r->old_pos, sizeof(double) * 3 * m->count);
+    }
+    return 0;
+}
+
+int mpmc_b200_mc_step_arrays_view(mpmc_b200_ctx *c, int step, const double **mu, const double **ef_static, const double **ef_induced,
+                                  const double **ef_induced_change, const double **dipole_rrms, const double **rank_metric) {
+    const size_t n = (size_t)c->ring_n;
+    const double *h;
+    if (!c->ring || step < 0 || step >= c->ring_steps) {
+        g_err = "no per-atom results of that step";
+        return 2;
+    }
+    h = c->ring + 14 * n * (size_t)step;
+    if (mu) *mu = h;
+    if (ef_static) *ef_static = h + 3 * n;
+    if (ef_induced) *ef_induced = h + 6 * n;
+    if (ef_induced_change) *ef_induced_change = h + 9 * n;
+    if (dipole_rrms) *dipole_rrms = h + 12 * n;
+    if (rank_metric) *rank_metric = h + 13 * n;
     return 0;
 }

@@ -87,6 +87,28 @@ def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     gu.run_and_check_trajectory(PROGRAM, name, tmp_path, env)
 
 
+@pytest.mark.parametrize("name,batch", [("traj_small_nvt", 8), ("traj_small_nvt", 64), ("traj_co2_nvt", 16), ("traj_co2_uvt", 8)])
+def test_dropin_resident_steps(name, batch, tmp_path):
+    """SURVEY 8f f3 (opt-in MPMC_B200_RESIDENT_STEPS): batches of NVT displacement steps moved, evaluated and decided on the
+    device (mpmc_b200_mc_steps), served to the unmodified mc() after checking the trial coordinates bit for bit.  The
+    reference's fixed-seed trajectory must come out row for row, and -- the point of running it on the GPU -- the device's
+    move arithmetic and its Metropolis decisions must agree with make_move() / mc() so that no batch is cut short (a cut
+    batch is still correct, it just falls back to the normal path).  uVT is not eligible and must be untouched."""
+    import re
+
+    _need(PROGRAM)
+    env = {"MPMC_B200_RESIDENT_STEPS": str(batch), "MPMC_B200_SHIM_CHECK": "1", "MPMC_B200_SHIM_TIMING": "1", "MPMC_B200_HOST_THREADS": "1"}
+    r = gu.run_and_check_trajectory(PROGRAM, name, tmp_path, env)
+    steps = int(re.findall(r"^numsteps\s+(\d+)", json.load(open(os.path.join(gu.GOLD, name + ".json")))["input"], re.M)[-1])
+    m = re.search(r"MPMC_B200_RESIDENT_STEPS: (\d+) batches, (\d+) steps answered from a batch, (\d+) batches cut short", r.stderr)
+    if "nvt" in name:
+        assert m, r.stderr[-2000:]
+        batches, served, dropped = map(int, m.groups())
+        assert served == steps and dropped == 0 and batches == -(-steps // batch), (batches, served, dropped, steps)
+    else:
+        assert m is None or int(m.group(2)) == 0
+
+
 def test_dropin_energy_no_observables(tmp_path):
     """energy_no_observables() (energy.c:232-318) through the drop-in: same energy, observables_t left alone."""
     from oracle import oracle  # snapshot parser only

@@ -43,6 +43,31 @@ def test_shim_host_logic_reproduces_reference_trajectory(hoststub, name, host_pa
     gu.run_and_check_trajectory(hoststub, name, tmp_path, env)
 
 
+@pytest.mark.parametrize("name,batch", [("traj_small_nvt", 8), ("traj_small_nvt", 64), ("traj_co2_nvt", 16), ("traj_co2_uvt", 8),
+                                        ("traj_co2_npt", 8)])
+def test_resident_steps_reproduce_reference_trajectory(hoststub, name, batch, tmp_path):
+    """SURVEY 8f f3, MPMC_B200_RESIDENT_STEPS: the shim reads the driver's next random numbers ahead, has a batch of NVT
+    displacement steps moved, evaluated and decided behind the C ABI (mpmc_b200_mc_steps; here the CPU stand-in, whose move
+    arithmetic is the plain-C twin of mc_step_kernel.cu) and answers the following energy() calls from the batch after
+    checking the trial coordinates make_move() really produced, bit for bit.  The unmodified mc() must see exactly the
+    reference's trajectory -- every energy row, the final configuration -- and every NVT step after the first of a batch
+    must have been answered from the batch (none dropped); uVT / NPT runs are not eligible and stay on the normal path."""
+    env = {"MPMC_B200_RESIDENT_STEPS": str(batch), "MPMC_B200_SHIM_CHECK": "1", "MPMC_B200_SHIM_TIMING": "1",
+           "MPMC_B200_HOST_THREADS": "1"}
+    r = gu.run_and_check_trajectory(hoststub, name, tmp_path, env)
+    import json
+    import re
+
+    steps = int(re.findall(r"^numsteps\s+(\d+)", json.load(open(os.path.join(gu.GOLD, name + ".json")))["input"], re.M)[-1])
+    m = re.search(r"MPMC_B200_RESIDENT_STEPS: (\d+) batches, (\d+) steps answered from a batch, (\d+) batches cut short", r.stderr)
+    if "nvt" in name:
+        assert m, r.stderr[-2000:]
+        batches, served, dropped = map(int, m.groups())
+        assert served == steps and dropped == 0 and batches == -(-steps // batch), (batches, served, dropped, steps)
+    else:
+        assert m is None or int(m.group(2)) == 0
+
+
 DRIVER = os.path.join(STUB_DIR, "_build", "shim_driver_hoststub")
 
 
