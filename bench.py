@@ -16,6 +16,7 @@ Own arm (default): the CUDA engine behind the C ABI (mpmc_b200/lib/libmpmc_b200.
   config.parity : this run's energies and per-atom arrays against the pin of the workload (tests/golden/pin_*.npz:
            the unmodified reference where it fits, else the reference-pinned oracle), at every N
   config.mc_steps_per_s_dropin : MC steps/s of a short `mpmc_b200 <input>` NVT run (BASELINE's first metric)
+  config.resident_steps : SURVEY 8f f3 -- MC steps/s of the drop-in on a small system, per-step path vs resident MC steps
   roofline: the dominant kernel (K4 symmetric dipole-tensor contraction): EXECUTED fp64 flops per launch (ncu SASS
            counts dadd + dmul + 2 dfma, profiles/k4_executed.json) / mean launch time (CUDA events on the launching
            stream) against the fp64 FMA peak of 148 SMs at the clock sampled under load; the SURVEY 8d algorithmic
@@ -341,6 +342,33 @@ def dropin_mc_steps_per_s(s, n_gpus: int, short: int, long_: int):
     return (long_ - short) / (b - a)
 
 
+def dropin_resident_steps(base: str = "h2_fluid_1000", steps: int = 6000, batch: int = 64):
+    """SURVEY 8f f3 evidence in the driver-run line: MC steps/s of `mpmc_b200 <input>` on a SMALL system (where the host
+    round trip per step costs more than the kernels) on the per-step path and with resident MC steps
+    (MPMC_B200_RESIDENT_STEPS: batches of steps moved, evaluated and decided on the device, the step replayed as a CUDA
+    graph), both read from the shim's own clock between the 2nd and the last energy() call (MPMC_B200_SHIM_TIMING)."""
+    import re
+
+    if not os.path.exists(DROPIN):
+        return None
+    from mpmc_b200 import systems
+
+    s = build_workload(base)
+    out = {"workload": base, "ensemble": "nvt", "steps": steps, "batch": batch}
+    for key, b in (("mc_steps_per_s", 0), ("mc_steps_per_s_resident", batch)):
+        with tempfile.TemporaryDirectory(prefix="mpmc_res_") as td:
+            ex = f"numsteps {steps}\ncorrtime {steps}\npreset_seeds 12345\nmove_factor 0.01\nrot_factor 0.01\n"
+            systems.write_reference_case(s, td, ensemble="nvt", extra=ex)
+            env = dict(dropin_env(1), MPMC_B200_SHIM_TIMING="1", MPMC_B200_RESIDENT_STEPS=str(b))
+            r = subprocess.run([DROPIN, "input"], cwd=td, capture_output=True, text=True, timeout=600, env=env)
+        m = re.search(r"([\d.]+) energy\(\) calls per second", r.stderr)
+        out[key] = float(m.group(1)) if (m and r.returncode == 0) else None
+        if b:
+            m = re.search(r"RESIDENT_STEPS: (\d+) batches, (\d+) steps answered from a batch, (\d+) batches cut short", r.stderr)
+            out["batches_served_cut"] = [int(x) for x in m.groups()] if m else None
+    return out
+
+
 def executed_flops(workload: str, n_gpus: int):
     """fp64 flops ONE launch of the dominant kernel executes on one rank: dadd + dmul + 2 dfma thread-level SASS counts
     of an ncu capture of this workload (profiles/k4_executed.json, written by profiles/capture_k4_executed.py from the
@@ -503,6 +531,7 @@ def own_arm(args):
         est = max(ms_per_step * 1e-3, 2e-3)  # size the long run for ~3 s of stepping
         short = 5
         mc_dropin = dropin_mc_steps_per_s(s, world, short, short + int(min(max(3.0 / est, 20), 4000)))
+    resident = dropin_resident_steps() if (not args.no_mc_dropin and world == 1) else None
 
     # ---- roofline of the dominant kernel (K4): EXECUTED fp64 flops / launch time / fp64 peak ----
     c_ms = float(np.mean([x for x in contract_ms if x > 0])) if any(x > 0 for x in contract_ms) else 0.0
@@ -558,6 +587,7 @@ def own_arm(args):
         "config": {"workload": args.workload, "n_atoms": n, "n_polarizable": int(cnt.n_polarizable),
                    "polar_iterations": int(e.polar_iterations), "pair_interactions_per_step": pairs,
                    "mc_steps_per_s": 1e3 / ms_per_step, "mc_steps_per_s_dropin": mc_dropin,
+                   "resident_steps": resident,
                    "l2": "flushed between timed iterations (256 MiB fill)",
                    "parallelism": f"rows{world}" if world > 1 else "single", "energy_K": energy_timed, "parity": parity,
                    "exchange": ("engine kernels over NVLink peer memory (static-field rows, induced field of every pass, "

@@ -322,6 +322,8 @@ struct mpmc_b200_ctx {
     DevBuf<mpmc_b200_mc_move> mc_moves;
     DevBuf<McStepDev> mc_res;
     DevBuf<double> mc_ecur, mc_ring;
+    DevBuf<int> mc_ctr;             // step counter on the device (read by the replayed graph of a step)
+    int mc_graph = -1;              // MPMC_B200_MC_GRAPH: 1 = steps 2.. of a batch replay a CUDA graph captured from step 1
     McStepDev* h_mc_res = nullptr;  // pinned
     double* h_mc_ring = nullptr;    // pinned
     size_t h_mc_res_cap = 0, h_mc_ring_cap = 0;
@@ -2960,20 +2962,69 @@ int mpmc_b200_mc_steps(mpmc_b200_ctx* c, int nsteps, const mpmc_b200_mc_move* mo
     k.rd_only = P.rd_only, k.es_wolf = P.es_wolf, k.rd_crystal = P.rd_crystal, k.polar = polar ? 1 : 0, k.palmo = P.polar_palmo;
     k.s_pair = S_PAIR, k.s_recip = S_RECIP, k.s_polar = S_POLAR, k.s_crystal = S_CRYSTAL, k.s_fused_out = S_FUSED_OUT;
     int launches = 0;
-    for (int j = 0; j < nsteps; j++) {
-        launch_mc_move(c->mc_moves.p, j, c->x.p, c->y.p, c->z.p, c->mc_res.p, st);
+    if (c->mc_ctr.ensure(1) || (ring_per_step && c->wb.ensure(ring_per_step))) FAIL(11, "cudaMalloc failed");
+    CU(cudaMemsetAsync(c->mc_ctr.p, 0, sizeof(int), st));
+    // one step: j >= 0 names it, j < 0 takes the step the device counter points at
+    auto step = [&](int j) -> int {
+        launch_mc_move(c->mc_moves.p, j, c->mc_ctr.p, c->x.p, c->y.p, c->z.p, c->mc_res.p, st);
         c->subsets_stale = true;
         c->boxes_fresh = false;
         const bool resort = c->resort_pending;
-        if (j > 0) c->resort_pending = false;  // the host mirror of the coordinates is stale inside a batch
+        if (j != 0) c->resort_pending = false;  // the host mirror of the coordinates is stale inside a batch
         const int rc = enqueue_energy(c, true, true);
-        c->resort_pending = c->resort_pending || (j > 0 && resort);
+        c->resort_pending = c->resort_pending || (j != 0 && resort);
         if (rc) return rc;
-        if (ring_per_step && enqueue_writeback(c, c->mc_ring.p + ring_per_step * j, 0, c->pol.n)) return 10;
+        if (ring_per_step) {
+            if (enqueue_writeback(c, c->wb.p, 0, c->pol.n)) return 10;
+            launch_mc_ring_copy(c->wb.p, c->mc_ring.p, ring_per_step, j, c->mc_ctr.p, st);
+        }
         k.iter_from_device = c->iter_from_device ? 1 : 0;
         k.iter_success = c->pending_iter_success;
-        launch_mc_decide(c->mc_moves.p, j, k, c->scalars.p, c->mc_ecur.p, c->x.p, c->y.p, c->z.p, c->mc_res.p, st);
-        launches += c->launches + 2 + (ring_per_step ? 1 : 0);
+        launch_mc_decide(c->mc_moves.p, j, c->mc_ctr.p, k, c->scalars.p, c->mc_ecur.p, c->x.p, c->y.p, c->z.p, c->mc_res.p, st);
+        launches += c->launches + 2 + (ring_per_step ? 2 : 0);
+        return 0;
+    };
+    // Steps 0 and 1 are enqueued launch by launch (step 0 may still re-sort and allocate; step 1 runs every launcher once in
+    // its steady state); from step 2 on a CUDA graph captured from one more plain enqueue of a step is replayed: the ~40
+    // launches of a small system's step become one graph launch, and the GPU no longer idles between tiny kernels.
+    // Gauss-Seidel is left out (its persistent sweep is handed a fresh epoch by the host at every launch).
+    if (c->mc_graph < 0) {
+        const char* v = getenv("MPMC_B200_MC_GRAPH");
+        c->mc_graph = (v && v[0] == '0') ? 0 : 1;
+    }
+    const bool want_graph = c->mc_graph == 1 && nsteps >= 4 && !(polar && (P.polar_gs || P.polar_gs_ranked || P.polar_ewald_full));
+    int j = 0;
+    for (; j < nsteps && (!want_graph || j < 2); j++)
+        if (const int rc = step(j)) return rc;
+    if (j < nsteps) {
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        bool ok = cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+        int rc_step = 0;
+        if (ok) {
+            const int before = launches;
+            rc_step = step(-1);
+            const int per_graph = launches - before;
+            ok = cudaStreamEndCapture(st, &graph) == cudaSuccess && graph && rc_step == 0;
+            if (ok) ok = cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess;
+            launches = before;
+            for (; ok && j < nsteps; j++) {
+                ok = cudaGraphLaunch(exec, st) == cudaSuccess;
+                launches += per_graph;
+            }
+        }
+        if (exec) cudaGraphExecDestroy(exec);
+        if (graph) cudaGraphDestroy(graph);
+        if (!ok) {  // something in the step does not capture on this driver: this context stays on plain launches
+            cudaGetLastError();
+            c->mc_graph = 0;
+            // the device counter says how far the batch got; finish it launch by launch
+            CU(cudaStreamSynchronize(st));
+            int done = 0;
+            CU(cudaMemcpy(&done, c->mc_ctr.p, sizeof(int), cudaMemcpyDeviceToHost));
+            for (j = done; j < nsteps; j++)
+                if (const int rc = step(j)) return rc;
+        }
     }
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(c->h_mc_res, c->mc_res.p, sizeof(McStepDev) * nsteps, cudaMemcpyDeviceToHost, st));

@@ -299,8 +299,11 @@ struct McDecide {  // what assemble_energies() (engine.cu) adds on the host, and
     int rd_only, es_wolf, rd_crystal, polar, palmo, iter_from_device, iter_success;
     int s_pair, s_recip, s_polar, s_crystal, s_fused_out;
 };
-void launch_mc_move(const mpmc_b200_mc_move* moves, int j, double* x, double* y, double* z, McStepDev* res, cudaStream_t s);
-void launch_mc_decide(const mpmc_b200_mc_move* moves, int j, const McDecide& k, const double* scalars, double* e_current,
-                      double* x, double* y, double* z, McStepDev* res, cudaStream_t s);
+// j >= 0: that step; j < 0: the step the device counter points at (a captured graph of one step replayed for the rest)
+void launch_mc_move(const mpmc_b200_mc_move* moves, int j, const int* step_ctr, double* x, double* y, double* z, McStepDev* res,
+                    cudaStream_t s);
+void launch_mc_decide(const mpmc_b200_mc_move* moves, int j, int* step_ctr, const McDecide& k, const double* scalars,
+                      double* e_current, double* x, double* y, double* z, McStepDev* res, cudaStream_t s);
+void launch_mc_ring_copy(const double* wb, double* ring, size_t per_step, int j, const int* step_ctr, cudaStream_t s);
 
 }  // namespace mpmc

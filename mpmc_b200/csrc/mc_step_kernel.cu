@@ -28,9 +28,13 @@ __device__ __forceinline__ Quat qmul(const Quat& a, const Quat& b) {
     return r;
 }
 
-__global__ void mc_move_kernel(const mpmc_b200_mc_move* __restrict__ moves, int j, double* __restrict__ x,
-                               double* __restrict__ y, double* __restrict__ z, McStepDev* __restrict__ res) {
+// The step index is either given (j >= 0) or read from the device counter the decide kernel advances: the second form
+// lets one captured CUDA graph of a step be replayed for every later step of the batch.
+__global__ void mc_move_kernel(const mpmc_b200_mc_move* __restrict__ moves, int j, const int* __restrict__ step_ctr,
+                               double* __restrict__ x, double* __restrict__ y, double* __restrict__ z,
+                               McStepDev* __restrict__ res) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (j < 0) j = *step_ctr;
     const mpmc_b200_mc_move& m = moves[j];
     McStepDev& r = res[j];
     const int n = m.count, f = m.first;
@@ -80,10 +84,12 @@ __global__ void mc_move_kernel(const mpmc_b200_mc_move* __restrict__ moves, int 
 
 // After the evaluation of step j: keep its scalars, assemble the total exactly as engine.cu:assemble_energies() does on
 // the host (same operations, same order), decide, and put the old coordinates back on a reject.
-__global__ void mc_decide_kernel(const mpmc_b200_mc_move* __restrict__ moves, int j, McDecide k,
+__global__ void mc_decide_kernel(const mpmc_b200_mc_move* __restrict__ moves, int j, int* __restrict__ step_ctr, McDecide k,
                                  const double* __restrict__ scalars, double* __restrict__ e_current, double* __restrict__ x,
                                  double* __restrict__ y, double* __restrict__ z, McStepDev* __restrict__ res) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (j < 0) j = *step_ctr;
+    *step_ctr = j + 1;
     const mpmc_b200_mc_move& m = moves[j];
     McStepDev& r = res[j];
     for (int s = 0; s < 32; s++) r.scalars[s] = scalars[s];
@@ -124,12 +130,25 @@ __global__ void mc_decide_kernel(const mpmc_b200_mc_move* __restrict__ moves, in
     }
 }
 
-void launch_mc_move(const mpmc_b200_mc_move* moves, int j, double* x, double* y, double* z, McStepDev* res, cudaStream_t s) {
-    mc_move_kernel<<<1, 32, 0, s>>>(moves, j, x, y, z, res);
+// the write-back image of the step (14 n doubles) into the step's slot of the ring
+__global__ void mc_ring_copy_kernel(const double* __restrict__ wb, double* __restrict__ ring, size_t per_step, int j,
+                                    const int* __restrict__ step_ctr) {
+    if (j < 0) j = *step_ctr;
+    double* dst = ring + per_step * (size_t)j;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < per_step; i += (size_t)gridDim.x * blockDim.x) dst[i] = wb[i];
 }
-void launch_mc_decide(const mpmc_b200_mc_move* moves, int j, const McDecide& k, const double* scalars, double* e_current,
-                      double* x, double* y, double* z, McStepDev* res, cudaStream_t s) {
-    mc_decide_kernel<<<1, 32, 0, s>>>(moves, j, k, scalars, e_current, x, y, z, res);
+
+void launch_mc_move(const mpmc_b200_mc_move* moves, int j, const int* step_ctr, double* x, double* y, double* z, McStepDev* res,
+                    cudaStream_t s) {
+    mc_move_kernel<<<1, 32, 0, s>>>(moves, j, step_ctr, x, y, z, res);
+}
+void launch_mc_decide(const mpmc_b200_mc_move* moves, int j, int* step_ctr, const McDecide& k, const double* scalars,
+                      double* e_current, double* x, double* y, double* z, McStepDev* res, cudaStream_t s) {
+    mc_decide_kernel<<<1, 32, 0, s>>>(moves, j, step_ctr, k, scalars, e_current, x, y, z, res);
+}
+void launch_mc_ring_copy(const double* wb, double* ring, size_t per_step, int j, const int* step_ctr, cudaStream_t s) {
+    const int blocks = (int)((per_step + 255) / 256 < 592 ? (per_step + 255) / 256 : 592);
+    mc_ring_copy_kernel<<<blocks > 0 ? blocks : 1, 256, 0, s>>>(wb, ring, per_step, j, step_ctr);
 }
 
 }  // namespace mpmc
