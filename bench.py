@@ -322,24 +322,25 @@ def dropin_energy_seconds(s, n_gpus: int, steps: int, warmup: int):
 
 
 def dropin_mc_steps_per_s(s, n_gpus: int, short: int, long_: int):
-    """MC steps/s of `mpmc_b200 <input>` (NVT, fixed seed): (long - short) steps / (wall_long - wall_short), so that
-    parsing, the initial energy() and CUDA start-up cancel."""
+    """MC steps/s of `mpmc_b200 <input>` (NVT, fixed seed), read from the shim's own clock (MPMC_B200_SHIM_TIMING: energy()
+    calls per second of wall clock between the 2nd and the last call of ONE run of `long_` steps -- parsing, CUDA start-up and
+    the first allocations lie before the 2nd call; everything the unmodified driver does per step is included).  The earlier
+    form, the wall-clock difference of a short and a long run, carried the start-up jitter of two fresh processes
+    (+-0.5 s against ~3 s of stepping)."""
+    import re
+
     if not os.path.exists(DROPIN):
         return None
     from mpmc_b200 import systems
 
-    def wall(steps):
-        with tempfile.TemporaryDirectory(prefix="mpmc_mc_") as td:
-            ex = f"numsteps {steps}\ncorrtime {steps}\npreset_seeds 12345\nmove_factor 0.01\nrot_factor 0.01\n"
-            systems.write_reference_case(s, td, ensemble="nvt", extra=ex)
-            t0 = time.perf_counter()
-            r = subprocess.run([DROPIN, "input"], cwd=td, capture_output=True, text=True, timeout=1200, env=dropin_env(n_gpus))
-            return (time.perf_counter() - t0) if r.returncode == 0 else None
-
-    a, b = wall(short), wall(long_)
-    if a is None or b is None or b <= a:
-        return None
-    return (long_ - short) / (b - a)
+    steps = max(long_, short + 3)
+    with tempfile.TemporaryDirectory(prefix="mpmc_mc_") as td:
+        ex = f"numsteps {steps}\ncorrtime {steps}\npreset_seeds 12345\nmove_factor 0.01\nrot_factor 0.01\n"
+        systems.write_reference_case(s, td, ensemble="nvt", extra=ex)
+        env = dict(dropin_env(n_gpus), MPMC_B200_SHIM_TIMING="1")
+        r = subprocess.run([DROPIN, "input"], cwd=td, capture_output=True, text=True, timeout=1200, env=env)
+    m = re.search(r"([\d.]+) energy\(\) calls per second", r.stderr)
+    return float(m.group(1)) if (m and r.returncode == 0) else None
 
 
 def dropin_resident_steps(base: str = "h2_fluid_1000", steps: int = 6000, batch: int = 64):
