@@ -27,14 +27,36 @@ struct PairConsts {
     double fh2_pref, fh4_pref;  // M2A2*HBAR2/(24 KB T) and M2A4*HBAR4/(1152 KB2 T^2), before 1/mu_red powers
     double fh4_pref_es;         // coulombic.c:141 spells KB*KB instead of the KB2 constant (differs at 4.7e-10)
     double inv_sqrt_pi;
+    // range tests on r^2: below in2 = (cutoff - 1e-9)^2 a pair is inside, above out2 = (cutoff + 1e-9)^2 outside; only in
+    // the shell between them is the square root taken and the reference's own comparison evaluated
+    double in2, out2;
+    double inv_amu;  // 1 / AMU2KG: 1 / mu_red = (1/m_i + 1/m_j) / AMU2KG
+    double ec[12];   // 1/q!: exp_neg_fast() (common.cuh) for the Gaussian of coulombic_real_FH() and of erfc_fast()
+    double pc[17];   // erfc_fast(): exp(x^2) erfc(x) as a polynomial in (x - 4) / (x + 4), profiles/k1_erfc_coeffs.py
     // coulombic_wolf(): erf(alpha R)/R and 1/R^2 (coulombic.c:275-276,290); only read by the FH == 0 kernels
     double wolf_shift, wolf_ir2;
     int wolf;
     int no_lj;  // rd_crystal: the LJ term comes from crystal_lj_kernel, K1 keeps electrostatics + minimum distance
 };
 
-__device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double ej, double sj, double& eps,
-                                       double& sigma, bool& attractive_only) {
+// Per-atom quantities of the pair terms that the reference re-derives for every pair: sqrt(epsilon) (Lorentz-Berthelot
+// eps_ij = sqrt(eps_i eps_j), pairs.c:200-211, here se_i * se_j: one rounding more, no square root per pair) and the
+// inverse molecular mass (Feynman-Hibbs reduced mass, lj.c:22-23: 1 / mu_red = (1/m_i + 1/m_j) / AMU2KG, no division per pair).
+struct PairAtom {
+    double eps, sig, se, imm;
+};
+template <int FH>
+__device__ __forceinline__ PairAtom pair_atom(double eps, double sig, double mm) {
+    PairAtom a;
+    a.eps = eps;
+    a.sig = sig;
+    a.se = sqrt(fabs(eps));
+    a.imm = FH ? 1.0 / mm : 0.0;
+    return a;
+}
+
+__device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double sei, double ej, double sj, double sej,
+                                       double& eps, double& sigma, bool& attractive_only) {
     attractive_only = false;
     eps = 0.0;
     sigma = 0.0;
@@ -45,16 +67,16 @@ __device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double 
                 attractive_only = true;
                 sigma = pow(0.5 * (si6 + sj6), 1. / 6.);
             } else if (si == 0 || sj == 0) {
-                eps = sqrt(ei * ej);
+                eps = sei * sej;
             } else {
                 sigma = pow(0.5 * (si6 + sj6), 1. / 6.);
-                eps = sqrt(ei * ej) * 2.0 * si3 * sj3 / (si6 + sj6);
+                eps = sei * sej * 2.0 * si3 * sj3 / (si6 + sj6);
             }
         } break;
         case MPMC_MIX_HALGREN:  // pairs.c:104-114
             if (si > 0.0 && sj > 0.0) sigma = (si * si * si + sj * sj * sj) / (si * si + sj * sj);
             if (ei > 0.0 && ej > 0.0) {
-                double t = sqrt(ei) + sqrt(ej);
+                double t = sei + sej;
                 eps = 4 * ei * ej / (t * t);
             }
             break;
@@ -62,7 +84,7 @@ __device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double 
             sigma = 0.5 * (si + sj);
             if (sigma != 0.0) {
                 double sp = si + sj, sp3 = sp * sp * sp;
-                eps = 64.0 * sqrt(ei * ej) * (si * si * si) * (sj * sj * sj) / (sp3 * sp3);
+                eps = 64.0 * (sei * sej) * (si * si * si) * (sj * sj * sj) / (sp3 * sp3);
             }
             break;
         default:  // Lorentz-Berthelot, pairs.c:200-211
@@ -70,22 +92,24 @@ __device__ __forceinline__ void mix_lj(int mixing, double ei, double si, double 
                 attractive_only = true;
                 sigma = 0.5 * (fabs(si) + fabs(sj));
             } else if (si == 0 || sj == 0) {
-                eps = sqrt(ei * ej);
+                eps = sei * sej;
             } else {
                 sigma = 0.5 * (si + sj);
-                eps = sqrt(ei * ej);
+                eps = sei * sej;
             }
     }
 }
 
 struct PairAcc {
-    double rd, es, intra, minr;
+    double rd, es, intra, minr2;  // minr2: smallest squared intermolecular distance (sqrt is monotone: taken once at the end)
     int n_tested, n_lj, n_es;
 };
+constexpr double kMinR2Init = 1.0e80;
+__device__ __forceinline__ double min_r_from(double minr2) { return minr2 >= 1.0e79 ? kMAXVALUE : sqrt(minr2); }
 
 // What is known about a pair before any expensive term: the minimum-image separation and which terms apply.
 struct PairScreen {
-    double r2, r, qq;
+    double r2, r, ir, qq;
     bool do_lj, do_es;
 };
 
@@ -110,29 +134,68 @@ __device__ __forceinline__ bool pair_screen(const Cell& c, const PairConsts& k, 
     }
     min_image<ORTHO>(c, dx, dy, dz);
     g.r2 = dx * dx + dy * dy + dz * dz;
-    g.r = sqrt(g.r2);
     A.n_tested++;
-    A.minr = fmin(A.minr, g.r);
-    g.do_lj = (g.r - kSMALL_dR < k.cutoff) && lj_i && (ej != 0.0) && (sj != 0.0);
-    // coulombic.c:167 skips r > cutoff; coulombic_wolf() keeps r < R only (coulombic.c:288)
-    g.do_es = !rd_only && ((FH == 0 && k.wolf) ? (g.r < k.cutoff) : !(g.r > k.cutoff)) && (g.qq != 0.0);
-    return g.do_lj || g.do_es;
+    A.minr2 = fmin(A.minr2, g.r2);
+    // lj.c:191 keeps r - SMALL_dR < cutoff; coulombic.c:167 skips r > cutoff; coulombic_wolf() keeps r < R only
+    // (coulombic.c:288).  Decided on r^2; the reference's comparisons on sqrt(r^2) only inside the 1e-9 A shell.
+    bool in_lj, in_es;
+    if (g.r2 < k.in2) {
+        in_lj = in_es = true;
+    } else if (g.r2 > k.out2) {
+        in_lj = in_es = false;
+    } else {
+        const double rs = sqrt(g.r2);
+        in_lj = rs - kSMALL_dR < k.cutoff;
+        in_es = (FH == 0 && k.wolf) ? (rs < k.cutoff) : !(rs > k.cutoff);
+    }
+    g.do_lj = in_lj && lj_i && (ej != 0.0) && (sj != 0.0);
+    g.do_es = !rd_only && in_es && (g.qq != 0.0);
+    if (!(g.do_lj || g.do_es)) return false;
+    // 1/r from the rsqrt seed + one third-order step (common.cuh), r = r^2 / r: no square root, no division
+    g.ir = rsqrt_fast(g.r2);
+    g.r = g.r2 * g.ir;
+    if (g.r2 == 0.0) {  // coincident atoms of two molecules: 1/r = inf, and the terms follow as in the reference
+        g.ir = 1.0 / g.r2;
+        g.r = 0.0;
+    }
+    return true;
+}
+
+// erfc(x) and exp(-x^2) for 0 <= x <= 6 without the library's range splits: erfc(x) = exp(-x^2) P((x - 4) / (x + 4)) with a
+// degree-16 polynomial (the mapped variable makes exp(x^2) erfc(x) nearly polynomial on the whole range; coefficients sum
+// to 1 in magnitude, so Horner is well conditioned), the Gaussian from exp_neg_fast() -- which the Feynman-Hibbs terms
+// need anyway -- and 1 / (x + 4) from the reciprocal seed + two Newton steps.  ~45 fp64 instructions, no branch; 7e-15
+// relative against a 50-digit reference.  The library erfc() remains for x > 6 (ewald_alpha * cutoff is 3.5 by default).
+__device__ __forceinline__ double erfc_fast(const PairConsts& k, double x, double& gauss) {
+    gauss = exp_neg_fast(k, x * x);
+    const double d = x + 4.0;
+    double rc;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rc) : "d"(d));
+    double e = fma(-d, rc, 1.0);
+    rc = fma(rc, e, rc);
+    e = fma(-d, rc, 1.0);
+    rc = fma(rc, e, rc);
+    const double y = (x - 4.0) * rc;
+    double p = k.pc[16];
+#pragma unroll
+    for (int q = 15; q >= 0; q--) p = fma(p, y, k.pc[q]);
+    return gauss * p;
 }
 
 // lj() + lj_fh_corr() and coulombic_real() + coulombic_real_FH() / coulombic_wolf() of a screened pair
 template <int FH>
-__device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, double ei, double si, double mi, double ej,
-                                          double sj, double mj, const PairScreen& g, PairAcc& A) {
+__device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, const PairAtom& pi, const PairAtom& pj,
+                                          const PairScreen& g, PairAcc& A) {
     const double r = g.r, r2 = g.r2, qq = g.qq;
     const bool do_lj = g.do_lj, do_es = g.do_es;
-    const double ir = 1.0 / r;
-    double mured = 0.0;
-    if (FH) mured = kAMU2KG * mi * mj / (mi + mj);
+    const double ir = g.ir;
+    double inv_mured = 0.0;  // 1 / (AMU2KG m_i m_j / (m_i + m_j)), lj.c:22-23
+    if (FH) inv_mured = (pi.imm + pj.imm) * k.inv_amu;
 
     if (do_lj) {
         double eps, sigma;
         bool att;
-        mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
+        mix_lj(mixing, pi.eps, pi.sig, pi.se, pj.eps, pj.sig, pj.se, eps, sigma, att);
         const double sor = fabs(sigma) * ir;
         double s6 = sor * sor * sor;
         s6 *= s6;
@@ -142,11 +205,11 @@ __device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, doubl
             const double ir2 = ir * ir, ir3 = ir2 * ir, ir4 = ir3 * ir;
             const double dE = -24.0 * eps * (2.0 * term12 - term6) * ir;
             const double d2E = 24.0 * eps * (26.0 * term12 - 7.0 * term6) * ir2;
-            u += (k.fh2_pref / mured) * (d2E + 2.0 * dE * ir);
+            u += (k.fh2_pref * inv_mured) * (d2E + 2.0 * dE * ir);
             if (FH >= 4) {
                 const double d3E = -1344.0 * eps * (6.0 * term12 - term6) * ir3;
                 const double d4E = 12096.0 * eps * (10.0 * term12 - term6) * ir4;
-                u += (k.fh4_pref / (mured * mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
+                u += (k.fh4_pref * (inv_mured * inv_mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
             }
         }
         A.rd += u;
@@ -158,21 +221,27 @@ __device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, doubl
             A.n_es++;
         }
     } else if (do_es) {
-        const double erfc_term = erfc(k.alpha * r);
+        const double x = k.alpha * r;
+        double erfc_term, gaussian_term = 0.0;
+        if (x <= 6.0) {
+            erfc_term = erfc_fast(k, x, gaussian_term);
+        } else {
+            erfc_term = erfc(x);
+            if (FH) gaussian_term = x < 26.0 ? exp_neg_fast(k, x * x) : 0.0;  // exp(-alpha^2 r^2), valid below 700
+        }
         double u = qq * erfc_term * ir;
         if (FH) {  // coulombic.c:132-141
-            const double gaussian_term = exp(-k.a2 * r2);
             const double ir2 = ir * ir, ir3 = ir * ir2, ir4 = ir2 * ir2;
             const double gg = gaussian_term * k.inv_sqrt_pi;
             const double du = -2.0 * k.alpha * gg * ir - erfc_term * ir2;
             const double d2u = 4.0 * gg * (k.a3 + ir2) + 2.0 * erfc_term * ir3;
-            u += (k.fh2_pref / mured) * (d2u + 2.0 * du * ir);
+            u += (k.fh2_pref * inv_mured) * (d2u + 2.0 * du * ir);
             if (FH >= 4) {
                 const double d3u = gg * (-8.0 * (k.a3 * k.a2) * r - 8.0 * k.a3 * ir - 12.0 * k.alpha * ir3) -
                                    6.0 * erfc_term * ir4;
                 const double d4u = gg * (8.0 * k.a3 * k.a2 + 16.0 * k.a3 * k.a4 * r2 + 32.0 * k.a3 * ir2 + 48.0 * ir4) +
                                    24.0 * erfc_term * (ir4 * ir);
-                u += (k.fh4_pref_es / (mured * mured)) * (15.0 * du * ir3 + 4.0 * d3u * ir + d4u);
+                u += (k.fh4_pref_es * (inv_mured * inv_mured)) * (15.0 * du * ir3 + 4.0 * d3u * ir + d4u);
             }
         }
         A.es += u;
@@ -183,19 +252,19 @@ __device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, doubl
 // all terms of one pair (i in registers, j given): pair_exclusions + minimum_image + lj + coulombic_real
 template <bool ORTHO, int FH>
 __device__ __forceinline__ void pair_terms(const Cell& c, const PairConsts& k, int mixing, int rd_only, double xi, double yi,
-                                           double zi, double qi, double ei, double si, double mi, int moli, int fli,
-                                           bool lj_i, double xj, double yj, double zj, double qj, double ej, double sj,
-                                           double mj, int molj, int fj, PairAcc& A) {
+                                           double zi, double qi, const PairAtom& pi, int moli, int fli, bool lj_i, double xj,
+                                           double yj, double zj, double qj, const PairAtom& pj, int molj, int fj, PairAcc& A) {
     PairScreen g;
-    if (pair_screen<ORTHO, FH>(c, k, rd_only, xi, yi, zi, qi, moli, fli, lj_i, xj, yj, zj, qj, ej, sj, molj, fj, A, g))
-        pair_body<FH>(k, mixing, ei, si, mi, ej, sj, mj, g, A);
+    if (pair_screen<ORTHO, FH>(c, k, rd_only, xi, yi, zi, qi, moli, fli, lj_i, xj, yj, zj, qj, pj.eps, pj.sig, molj, fj, A, g))
+        pair_body<FH>(k, mixing, pi, pj, g, A);
 }
 
 template <bool ORTHO, int FH>
 __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, PairConsts k, int mixing, int rd_only,
                                                            const int2* __restrict__ tiles, double* __restrict__ partial,
                                                            int stride) {
-    __shared__ double sx[TILE], sy[TILE], sz[TILE], sq[TILE], se[TILE], ss[TILE], sm[TILE];
+    __shared__ double sx[TILE], sy[TILE], sz[TILE], sq[TILE];
+    __shared__ PairAtom sp[TILE];
     __shared__ int smol[TILE], sfl[TILE];
     __shared__ double red[32];
 
@@ -208,9 +277,7 @@ __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, P
         sy[tid] = a.y[j];
         sz[tid] = a.z[j];
         sq[tid] = a.q[j];
-        se[tid] = a.eps[j];
-        ss[tid] = a.sig[j];
-        sm[tid] = a.molmass[j];
+        sp[tid] = pair_atom<FH>(a.eps[j], a.sig[j], a.molmass[j]);
         smol[tid] = a.mol[j];
         sfl[tid] = a.flags[j];
     }
@@ -218,15 +285,16 @@ __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, P
     const int moli = a.mol[i], fli = a.flags[i];
     __syncthreads();
 
-    PairAcc A = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
+    PairAcc A = {0.0, 0.0, 0.0, kMinR2Init, 0, 0, 0};
     const bool lj_i = (ei != 0.0) && (si != 0.0) && !k.no_lj;
+    const PairAtom pi = pair_atom<FH>(ei, si, mi);
     const int j0 = (t.x == t.y) ? tid + 1 : 0;
 
     for (int jj = j0; jj < TILE; jj++) {
-        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, ei, si, mi, moli, fli, lj_i, sx[jj], sy[jj], sz[jj], sq[jj],
-                              se[jj], ss[jj], sm[jj], smol[jj], sfl[jj], A);
+        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, pi, moli, fli, lj_i, sx[jj], sy[jj], sz[jj], sq[jj], sp[jj],
+                              smol[jj], sfl[jj], A);
     }
-    const double rd = A.rd, es = A.es, intra = A.intra, minr = A.minr;
+    const double rd = A.rd, es = A.es, intra = A.intra, minr2 = A.minr2;
     const int n_tested = A.n_tested, n_lj = A.n_lj, n_es = A.n_es;
 
     // fixed-order block reduction, one partial row per tile pair
@@ -237,8 +305,8 @@ __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, P
     if (tid == 0) partial[1 * stride + blockIdx.x] = v;
     v = block_reduce<0>(intra, red);
     if (tid == 0) partial[2 * stride + blockIdx.x] = v;
-    v = block_reduce<1>(minr, red);
-    if (tid == 0) partial[3 * stride + blockIdx.x] = v;
+    v = block_reduce<1>(minr2, red);
+    if (tid == 0) partial[3 * stride + blockIdx.x] = min_r_from(v);
     v = block_reduce<0>((double)n_tested, red);
     if (tid == 0) partial[4 * stride + blockIdx.x] = v;
     v = block_reduce<0>((double)n_lj, red);
@@ -258,7 +326,8 @@ __global__ void __launch_bounds__(TILE) pair_energy_kernel(Cell c, AtomsDev a, P
 // No CTA-level synchronisation; one partial column per (slice, cluster), reduced in fixed order.
 // ------------------------------------------------------------------------------------------------
 struct __align__(16) PairRec {
-    double x, y, z, q, eps, sig, mm;
+    double x, y, z, q;
+    PairAtom p;  // eps, sig, sqrt(eps), 1 / molecule mass: the last two formed once per staged atom, not once per pair
     int mol, fl;
 };
 
@@ -284,10 +353,11 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
     const double xi = a.x[i], yi = a.y[i], zi = a.z[i], qi = a.q[i], ei = a.eps[i], si = a.sig[i], mi = a.molmass[i];
     const int moli = a.mol[i], fli = a.flags[i];
     const bool lj_i = (ei != 0.0) && (si != 0.0) && !k.no_lj;
-    PairAcc A = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
+    const PairAtom pi = pair_atom<FH>(ei, si, mi);
+    PairAcc A = {0.0, 0.0, 0.0, kMinR2Init, 0, 0, 0};
     if (COMPACT) {
         PairRec r;
-        r.x = xi, r.y = yi, r.z = zi, r.q = qi, r.eps = ei, r.sig = si, r.mm = mi, r.mol = moli, r.fl = fli;
+        r.x = xi, r.y = yi, r.z = zi, r.q = qi, r.p = pi, r.mol = moli, r.fl = fli;
         irec[w][lane] = r;
     }
 
@@ -319,9 +389,7 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
                 r.y = a.y[j];
                 r.z = a.z[j];
                 r.q = a.q[j];
-                r.eps = a.eps[j];
-                r.sig = a.sig[j];
-                r.mm = a.molmass[j];
+                r.p = pair_atom<FH>(a.eps[j], a.sig[j], a.molmass[j]);
                 r.mol = a.mol[j];
                 r.fl = a.flags[j];
                 rec[w][lane] = r;
@@ -331,8 +399,8 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
             if (!COMPACT || ((inside_mask >> b) & 1u)) {
                 for (int s = s0; s < 32; s++) {
                     const PairRec& r = rec[w][s];
-                    pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, ei, si, mi, moli, fli, lj_i, r.x, r.y, r.z,
-                                          r.q, r.eps, r.sig, r.mm, r.mol, r.fl, A);
+                    pair_terms<ORTHO, FH>(c, k, mixing, rd_only, xi, yi, zi, qi, pi, moli, fli, lj_i, r.x, r.y, r.z, r.q, r.p,
+                                          r.mol, r.fl, A);
                 }
             } else {
                 // screen: one bit per staged atom whose pair with this lane's atom has a body
@@ -340,7 +408,7 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
                 for (int s = s0; s < 32; s++) {
                     const PairRec& r = rec[w][s];
                     PairScreen g;
-                    if (pair_screen<ORTHO, FH>(c, k, rd_only, xi, yi, zi, qi, moli, fli, lj_i, r.x, r.y, r.z, r.q, r.eps, r.sig,
+                    if (pair_screen<ORTHO, FH>(c, k, rd_only, xi, yi, zi, qi, moli, fli, lj_i, r.x, r.y, r.z, r.q, r.p.eps, r.p.sig,
                                                r.mol, r.fl, A, g))
                         bits |= 1u << s;
                 }
@@ -361,22 +429,22 @@ __global__ void __launch_bounds__(TILE) pair_cluster_kernel(Cell c, SubsetDev a,
                 }
                 __syncwarp();
                 // bodies, densely: lane l takes pairs l, l + 32, ...
-                PairAcc scratch = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};  // the screen's side sums were taken above
+                PairAcc scratch = {0.0, 0.0, 0.0, kMinR2Init, 0, 0, 0};  // the screen's side sums were taken above
                 for (int t = lane; t < total; t += 32) {
                     const int pr = plist[w][t];
                     const PairRec& ri = irec[w][pr >> 5];
                     const PairRec& rj = rec[w][pr & 31];
-                    const bool lj_a = (ri.eps != 0.0) && (ri.sig != 0.0) && !k.no_lj;
+                    const bool lj_a = (ri.p.eps != 0.0) && (ri.p.sig != 0.0) && !k.no_lj;
                     PairScreen g;
                     if (pair_screen<ORTHO, FH>(c, k, rd_only, ri.x, ri.y, ri.z, ri.q, ri.mol, ri.fl, lj_a, rj.x, rj.y, rj.z, rj.q,
-                                               rj.eps, rj.sig, rj.mol, rj.fl, scratch, g))
-                        pair_body<FH>(k, mixing, ri.eps, ri.sig, ri.mm, rj.eps, rj.sig, rj.mm, g, A);
+                                               rj.p.eps, rj.p.sig, rj.mol, rj.fl, scratch, g))
+                        pair_body<FH>(k, mixing, ri.p, rj.p, g, A);
                 }
             }
         }
     }
     // same-molecule pairs are handled by intra_erf_kernel (list order): drop what pair_terms collected for them
-    const double rd = warp_sum(A.rd), es = warp_sum(A.es), minr = warp_min(A.minr);
+    const double rd = warp_sum(A.rd), es = warp_sum(A.es), minr = min_r_from(warp_min(A.minr2));
     const double nlj = warp_sum((double)A.n_lj), nes = warp_sum((double)A.n_es);
     if (lane == 0) {
         const int col = blockIdx.y * (clus_end - clus_begin) + (ci - clus_begin);
@@ -508,6 +576,17 @@ void launch_intra_erf(const AtomsDev& a, const int* follow, double ewald_alpha, 
 static PairConsts make_pair_consts(const Cell& c, const PairOpts& o) {
     PairConsts k;
     k.cutoff = c.cutoff;
+    k.in2 = (c.cutoff - 1e-9) * (c.cutoff - 1e-9);
+    k.out2 = (c.cutoff + 1e-9) * (c.cutoff + 1e-9);
+    k.inv_amu = 1.0 / kAMU2KG;
+    fill_exp_coeffs(k.ec);
+    static const double erfc_poly[17] = {  // profiles/k1_erfc_coeffs.py: max relative error 3.5e-15 on 0 <= x <= 6
+        0.13699945762506133,     -0.25906804876015949,    0.21871967891831384,    -0.16425781670012546,
+        0.10896317738612751,     -0.06310781547805365,    0.03129905758162637,    -0.012843947793199894,
+        0.004060233939324147,    -0.00079919577948827682, -2.1624460041698876e-05, 8.0102508503569764e-05,
+        -1.9647828005712331e-05, 2.3461777077804792e-06,  6.6863398646632111e-06,  1.4399022917082169e-06,
+        4.4575205502236814e-08};
+    for (int q = 0; q < 17; q++) k.pc[q] = erfc_poly[q];
     k.alpha = o.ewald_alpha;
     k.a2 = k.alpha * k.alpha;
     k.a3 = k.a2 * k.alpha;
@@ -610,7 +689,7 @@ __global__ void __launch_bounds__(TILE) crystal_lj_kernel(Cell c, AtomsDev a, Pa
         if (!(rimg - kSMALL_dR < rd_cutoff)) continue;  // lj.c:191
         double eps, sigma;
         bool att;
-        mix_lj(mixing, ei, si, ej, sj, eps, sigma, att);
+        mix_lj(mixing, ei, si, sqrt(fabs(ei)), ej, sj, sqrt(fabs(ej)), eps, sigma, att);  // once per pair, images inside
         const double sig2 = sigma * sigma;
         const bool same = (moli == smol[jj]);
         double s6 = 0.0, s12 = 0.0;
@@ -708,6 +787,7 @@ __global__ void __launch_bounds__(TILE) pair_delta_kernel(Cell c, AtomsDev a, Pa
     const int j = blockIdx.x * TILE + tid;
     const double xj = a.x[j], yj = a.y[j], zj = a.z[j], qj = a.q[j], ej = a.eps[j], sj = a.sig[j], mj = a.molmass[j];
     const int molj = a.mol[j], fj = a.flags[j];
+    const PairAtom pj = pair_atom<FH>(ej, sj, mj);
     int mine = -1;  // index of j in the moved list
     for (int m = 0; m < nmoved; m++)
         if (smv[m].idx == j) mine = m;
@@ -718,11 +798,11 @@ __global__ void __launch_bounds__(TILE) pair_delta_kernel(Cell c, AtomsDev a, Pa
         if (mine >= 0 && mine <= m) continue;  // j itself, or a moved pair already taken at the smaller index
         const MovedRec& r = smv[m];
         const bool lj_i = (r.eps != 0.0) && (r.sig != 0.0) && !k.no_lj;
-        PairAcc An = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0}, Ao = {0.0, 0.0, 0.0, kMAXVALUE, 0, 0, 0};
-        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, r.xn, r.yn, r.zn, r.q, r.eps, r.sig, r.mm, r.mol, r.fl, lj_i, xj, yj, zj, qj,
-                              ej, sj, mj, molj, fj, An);
-        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, r.xo, r.yo, r.zo, r.q, r.eps, r.sig, r.mm, r.mol, r.fl, lj_i, xjo, yjo, zjo,
-                              qj, ej, sj, mj, molj, fj, Ao);
+        PairAcc An = {0.0, 0.0, 0.0, kMinR2Init, 0, 0, 0}, Ao = {0.0, 0.0, 0.0, kMinR2Init, 0, 0, 0};
+        const PairAtom pm = pair_atom<FH>(r.eps, r.sig, r.mm);
+        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, r.xn, r.yn, r.zn, r.q, pm, r.mol, r.fl, lj_i, xj, yj, zj, qj, pj, molj, fj, An);
+        pair_terms<ORTHO, FH>(c, k, mixing, rd_only, r.xo, r.yo, r.zo, r.q, pm, r.mol, r.fl, lj_i, xjo, yjo, zjo, qj, pj, molj, fj,
+                              Ao);
         d_rd += An.rd - Ao.rd;
         d_es += An.es - Ao.es;
         d_intra += An.intra - Ao.intra;

@@ -40,8 +40,12 @@ def assert_energies(got: dict, exp: dict, rtol=RTOL, label="", floor=COND_FLOOR)
         tol = rtol * abs(b) + extra
         assert abs(a - b) <= tol, f"{label} {k}: got {a!r} expected {b!r} |diff| {abs(a - b):.3e} > tol {tol:.3e}"
 
-    if exp.get("total", 0) >= 1e40 or got.get("autorejected"):
+    if exp.get("total", 0) == 1e40 or got.get("autorejected"):  # the MAXVALUE sentinel of cavity_autoreject_absolute: exact
         assert got["total"] == exp["total"], f"{label} autoreject: {got['total']} vs {exp['total']}"
+        return
+    if exp.get("total", 0) > 1e40:  # a computed, astronomically large energy (atoms 0.001 A apart): the usual tolerance
+        close(got["total"], exp["total"], k="total")
+        close(got["rd"], exp["rd"], k="rd")
         return
     close(got["rd"], exp["rd"], k="rd")
     close(got["polar"], exp["polar"], k="polar")
