@@ -47,9 +47,13 @@ struct Cell {
 };
 
 __device__ __forceinline__ double rint_magic(double x) {
+#ifdef MPMC_RINT_FRND
+    return rint(x);  // FRND.F64 on the conversion pipe: same value, off the fp64 pipe (A/B: make EXTRA=-DMPMC_RINT_FRND)
+#else
     // round-half-even like rint() for |x| < 2^51; two DADDs instead of a conversion-pipe op
     const double m = 6755399441055744.0;  // 1.5 * 2^52
     return __dadd_rn(__dadd_rn(x, m), -m);
+#endif
 }
 
 template <bool ORTHO>
