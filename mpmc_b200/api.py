@@ -154,6 +154,24 @@ class Counters(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
 
 
+MC_MAX_ATOMS, MC_MAX_STEPS = 16, 64  # MPMC_B200_MC_MAX_ATOMS / MPMC_B200_MC_MAX_STEPS
+
+
+class McMove(C.Structure):
+    """struct mpmc_b200_mc_move (resident MC steps, mpmc_b200_mc_steps)."""
+
+    _fields_ = [("first", C.c_int), ("count", C.c_int), ("explicit_positions", C.c_int), ("reserved", C.c_int),
+                ("u_accept", C.c_double), ("trans", C.c_double * 3), ("quat", C.c_double * 4), ("mass", C.c_double * MC_MAX_ATOMS),
+                ("new_pos", C.c_double * (3 * MC_MAX_ATOMS)), ("old_pos", C.c_double * (3 * MC_MAX_ATOMS))]
+
+
+class McResult(C.Structure):
+    """struct mpmc_b200_mc_result."""
+
+    _fields_ = [("e", Energies), ("accepted", C.c_int), ("reserved", C.c_int), ("new_pos", C.c_double * (3 * MC_MAX_ATOMS)),
+                ("old_pos", C.c_double * (3 * MC_MAX_ATOMS))]
+
+
 def default_params(basis, cutoff: Optional[float] = None) -> Params:
     """Defaults of the reference's ``setdefaults()`` (src/io/input.c:1598-1667) and
     ``pbc()`` (src/energy/pbc.c:65-83): kmax 7, gamma 1, max_iter 10, rd_lrc on,
@@ -429,6 +447,14 @@ class Engine:
         e = Energies()
         self._check(self.lib.mpmc_b200_polar(self._ctx, C.byref(e)))
         return e
+
+    def mc_steps(self, moves, temperature: float, current_energy: float):
+        """Resident MC steps (include/mpmc_b200.h: mpmc_b200_mc_steps): `moves` is a ctypes array of McMove; returns the array
+        of McResult (energies of every trial configuration, the device's decisions, trial / old coordinates)."""
+        n = len(moves)
+        res = (McResult * n)()
+        self._check(self.lib.mpmc_b200_mc_steps(self._ctx, n, moves, C.c_double(temperature), C.c_double(current_energy), res))
+        return res
 
     def energy_enqueue(self):
         self._check(self.lib.mpmc_b200_energy_enqueue(self._ctx))

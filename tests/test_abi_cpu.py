@@ -46,6 +46,13 @@ def test_struct_layouts_match_header(tmp_path):
         body.append(f'printf("%zu\\n", offsetof(mpmc_b200_energies, {f}));')
     for f in fields_c:
         body.append(f'printf("%zu\\n", offsetof(mpmc_b200_counters, {f}));')
+    fields_m = [n for n, _ in api.McMove._fields_]
+    fields_r = [n for n, _ in api.McResult._fields_]
+    body.append('printf("%zu %zu %d %d\\n", sizeof(mpmc_b200_mc_move), sizeof(mpmc_b200_mc_result), MPMC_B200_MC_MAX_ATOMS, MPMC_B200_MC_MAX_STEPS);')
+    for f in fields_m:
+        body.append(f'printf("%zu\\n", offsetof(mpmc_b200_mc_move, {f}));')
+    for f in fields_r:
+        body.append(f'printf("%zu\\n", offsetof(mpmc_b200_mc_result, {f}));')
     body.append("return 0;}")
     src.write_text("\n".join(body))
     exe = tmp_path / "layout"
@@ -53,10 +60,14 @@ def test_struct_layouts_match_header(tmp_path):
     out = subprocess.check_output([str(exe)], text=True).split()
     sizes = [int(x) for x in out[:3]]
     assert sizes == [ctypes.sizeof(api.Params), ctypes.sizeof(api.Energies), ctypes.sizeof(api.Counters)]
-    offs = [int(x) for x in out[3:]]
+    n3 = len(fields_p) + len(fields_e) + len(fields_c)
+    offs = [int(x) for x in out[3:3 + n3]]
     want = [getattr(api.Params, f).offset for f in fields_p] + [getattr(api.Energies, f).offset for f in fields_e] + [
         getattr(api.Counters, f).offset for f in fields_c]
     assert offs == want
+    rest = [int(x) for x in out[3 + n3:]]
+    assert rest[:4] == [ctypes.sizeof(api.McMove), ctypes.sizeof(api.McResult), api.MC_MAX_ATOMS, api.MC_MAX_STEPS]
+    assert rest[4:] == [getattr(api.McMove, f).offset for f in fields_m] + [getattr(api.McResult, f).offset for f in fields_r]
 
 
 def test_no_cpu_fallback(lib):

@@ -9,21 +9,10 @@ import numpy as np
 import pytest
 
 from mpmc_b200 import systems
-from mpmc_b200.api import Energies
+from mpmc_b200.api import McMove, McResult
 
 pytestmark = pytest.mark.gpu
 MAXA, MAXS = 16, 64
-
-
-class McMove(C.Structure):
-    _fields_ = [("first", C.c_int), ("count", C.c_int), ("explicit_positions", C.c_int), ("reserved", C.c_int),
-                ("u_accept", C.c_double), ("trans", C.c_double * 3), ("quat", C.c_double * 4), ("mass", C.c_double * MAXA),
-                ("new_pos", C.c_double * (3 * MAXA)), ("old_pos", C.c_double * (3 * MAXA))]
-
-
-class McResult(C.Structure):
-    _fields_ = [("e", Energies), ("accepted", C.c_int), ("reserved", C.c_int), ("new_pos", C.c_double * (3 * MAXA)),
-                ("old_pos", C.c_double * (3 * MAXA))]
 
 
 def _qmul(a, b):  # quaternion.c:76-86, (x, y, z, w), left to right
