@@ -906,7 +906,7 @@ double polar(system_t *system) {
 /* ------------------------------------------------------------------------------------------------
  * Resident MC steps (opt-in: MPMC_B200_RESIDENT_STEPS=B).  The reference's mc() (src/mc/mc.c:294-353)
  * stays in charge, unmodified: make_move() -> energy() -> Metropolis test -> checkpoint() / restore().  In an NVT run of
- * displacement moves everything the NEXT steps will do follows from random numbers that do not depend on the
+ * displacement moves (or between the volume moves of an NPT run) everything the NEXT steps will do follows from random numbers that do not depend on the
  * configuration: per step one Metropolis draw (mc.c:320), one draw that picks the molecule (checkpoint.c:126), six for
  * translate() and four for rotate() (mc_moves.c:380-385,415-418).  So when energy() is called for step s the shim reads
  * the next draws AHEAD of the driver (get_rand() below serves them to the driver later, in the same order, from the
@@ -972,7 +972,8 @@ static int shim_resident_eligible(const system_t *system, int with_observables) 
         }
     }
     if (!s_batch || !with_observables) return 0;
-    if (system->ensemble != ENSEMBLE_NVT || system->step < 1 || !system->checkpoint) return 0;
+    /* NVT, and the displacement steps of NPT runs (a batch ends where the driver will draw a volume move) */
+    if ((system->ensemble != ENSEMBLE_NVT && system->ensemble != ENSEMBLE_NPT) || system->step < 1 || !system->checkpoint) return 0;
     if (system->checkpoint->movetype != MOVETYPE_DISPLACE || !system->checkpoint->molecule_altered || !system->checkpoint->molecule_backup) return 0;
     if (system->quantum_rotation || system->spectre || system->gwp || system->rd_anharmonic || system->cavity_bias) return 0;
     if (system->parallel_tempering || system->simulated_annealing || system->cavity_autoreject_absolute || system->sg) return 0;
@@ -1119,11 +1120,18 @@ static int shim_resident_start(system_t *system, mpmc_b200_energies *e) {
     }
     if (a) return 0;
     s_move[0].u_accept = shim_peek_rand(system, 0);
-    /* steps 1..B-1: per step the driver will draw u (mc.c:320), the pick (checkpoint.c:126), translate() x6, rotate() x4 */
+    /* steps 1..B-1: per step the driver will draw u (mc.c:320), in NPT the volume-or-displace draw (checkpoint.c:83-97),
+     * the pick (checkpoint.c:126), translate() x6, rotate() x4 */
     for (j = 1, draw = 1; j < B; j++, draw += 12) {
         struct quaternion q;
         mpmc_b200_mc_move *mv = &s_move[j];
-        const int altered = (int)floor(shim_peek_rand(system, draw) * N);
+        int altered;
+        if (system->ensemble == ENSEMBLE_NPT) {
+            const double pv = system->volume_probability == 0.0 ? 1.0 / N : system->volume_probability;
+            if (shim_peek_rand(system, draw) < pv) break; /* a volume move comes next: the batch ends before it */
+            draw++;
+        }
+        altered = (int)floor(shim_peek_rand(system, draw) * N);
         double t[3], sgn[3], ax[3], angle;
         int p;
         if (altered < 0 || altered >= s_nexch) break;

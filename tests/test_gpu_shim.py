@@ -87,7 +87,8 @@ def test_dropin_fixed_seed_trajectory(name, host_path, tmp_path):
     gu.run_and_check_trajectory(PROGRAM, name, tmp_path, env)
 
 
-@pytest.mark.parametrize("name,batch", [("traj_small_nvt", 8), ("traj_small_nvt", 64), ("traj_co2_nvt", 16), ("traj_co2_uvt", 8)])
+@pytest.mark.parametrize("name,batch", [("traj_small_nvt", 8), ("traj_small_nvt", 64), ("traj_co2_nvt", 16), ("traj_co2_uvt", 8),
+                                        ("traj_co2_npt", 8)])
 def test_dropin_resident_steps(name, batch, tmp_path):
     """SURVEY 8f f3 (opt-in MPMC_B200_RESIDENT_STEPS): batches of NVT displacement steps moved, evaluated and decided on the
     device (mpmc_b200_mc_steps), served to the unmodified mc() after checking the trial coordinates bit for bit.  The
@@ -105,6 +106,10 @@ def test_dropin_resident_steps(name, batch, tmp_path):
         assert m, r.stderr[-2000:]
         batches, served, dropped = map(int, m.groups())
         assert served == steps and dropped == 0 and batches == -(-steps // batch), (batches, served, dropped, steps)
+    elif "npt" in name:  # displacement steps between the volume moves; a batch ends where the driver will draw a volume move
+        assert m, r.stderr[-2000:]
+        batches, served, dropped = map(int, m.groups())
+        assert served > steps // 2 and dropped == 0, (batches, served, dropped, steps)
     else:
         assert m is None or int(m.group(2)) == 0
 
