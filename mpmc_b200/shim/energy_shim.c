@@ -1101,7 +1101,12 @@ static int shim_resident_start(system_t *system, mpmc_b200_energies *e) {
     }
     if (k0 < 0 || (double)s_nexch != N) return 0;
     /* a batch keeps one write-back image per step on the device and in pinned memory: bound it */
-    if (system->polarization && (long)B * c_natom * 14 * 8 > (64L << 20)) B = (int)((64L << 20) / ((long)c_natom * 14 * 8));
+    {
+        static long ring_mb = -1; /* MPMC_B200_RESIDENT_RING_MB (default 64) */
+        if (ring_mb < 0) ring_mb = getenv("MPMC_B200_RESIDENT_RING_MB") ? atol(getenv("MPMC_B200_RESIDENT_RING_MB")) : 64;
+        if (ring_mb < 1) ring_mb = 1;
+        if (system->polarization && (long)B * c_natom * 14 * 8 > (ring_mb << 20)) B = (int)((ring_mb << 20) / ((long)c_natom * 14 * 8));
+    }
     if (B < 2) return 0;
     memset(s_move, 0, sizeof(mpmc_b200_mc_move) * (size_t)B);
     /* step 0: the trial coordinates are in the lists (and on the device); a reject restores the backup's */
