@@ -323,8 +323,8 @@ def dropin_energy_seconds(s, n_gpus: int, steps: int, warmup: int):
 
 def dropin_mc_steps_per_s(s, n_gpus: int, short: int, long_: int):
     """MC steps/s of `mpmc_b200 <input>` (NVT, fixed seed), read from the shim's own clock (MPMC_B200_SHIM_TIMING: energy()
-    calls per second of wall clock between the 2nd and the last call of ONE run of `long_` steps -- parsing, CUDA start-up and
-    the first allocations lie before the 2nd call; everything the unmodified driver does per step is included).  The earlier
+    calls per second of wall clock between the 1st and the last call of ONE run of `long_` steps -- parsing, CUDA start-up and
+    the first allocations lie before the end of the 1st call -- the initial energy; everything the unmodified driver does per step is included).  The earlier
     form, the wall-clock difference of a short and a long run, carried the start-up jitter of two fresh processes
     (+-0.5 s against ~3 s of stepping)."""
     import re
@@ -347,7 +347,7 @@ def dropin_resident_steps(base: str = "h2_fluid_1000", steps: int = 6000, batch:
     """SURVEY 8f f3 evidence in the driver-run line: MC steps/s of `mpmc_b200 <input>` on a SMALL system (where the host
     round trip per step costs more than the kernels) on the per-step path and with resident MC steps
     (MPMC_B200_RESIDENT_STEPS: batches of steps moved, evaluated and decided on the device, the step replayed as a CUDA
-    graph), both read from the shim's own clock between the 2nd and the last energy() call (MPMC_B200_SHIM_TIMING)."""
+    graph), both read from the shim's own clock between the 1st and the last energy() call (MPMC_B200_SHIM_TIMING)."""
     import re
 
     if not os.path.exists(DROPIN):
