@@ -31,6 +31,7 @@ struct PairConsts {
     // the shell between them is the square root taken and the reference's own comparison evaluated
     double in2, out2;
     double inv_amu;  // 1 / AMU2KG: 1 / mu_red = (1/m_i + 1/m_j) / AMU2KG
+    double one_m_alpha, a5x24, a7x16, c_ir4;  // 1 - a, 24 a^5, 16 a^7, 48 - 78 a: the collapsed sums of coulombic_real_FH()
     double ec[12];   // 1/q!: exp_neg_fast() (common.cuh) for the Gaussian of coulombic_real_FH() and of erfc_fast()
     double pc[17];   // erfc_fast(): exp(x^2) erfc(x) as a polynomial in (x - 4) / (x + 4), profiles/k1_erfc_coeffs.py
     // coulombic_wolf(): erf(alpha R)/R and 1/R^2 (coulombic.c:275-276,290); only read by the FH == 0 kernels
@@ -199,18 +200,17 @@ __device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, const
         const double sor = fabs(sigma) * ir;
         double s6 = sor * sor * sor;
         s6 *= s6;
-        const double term6 = s6, term12 = att ? 0.0 : s6 * s6;
-        double u = 4.0 * eps * (term12 - term6);
-        if (FH) {  // lj.c:29-50
-            const double ir2 = ir * ir, ir3 = ir2 * ir, ir4 = ir3 * ir;
-            const double dE = -24.0 * eps * (2.0 * term12 - term6) * ir;
-            const double d2E = 24.0 * eps * (26.0 * term12 - 7.0 * term6) * ir2;
-            u += (k.fh2_pref * inv_mured) * (d2E + 2.0 * dE * ir);
-            if (FH >= 4) {
-                const double d3E = -1344.0 * eps * (6.0 * term12 - term6) * ir3;
-                const double d4E = 12096.0 * eps * (10.0 * term12 - term6) * ir4;
-                u += (k.fh4_pref * (inv_mured * inv_mured)) * (15.0 * dE * ir3 + 4.0 * d3E * ir + d4E);
-            }
+        // with A = eps (sigma/r)^12 and B = eps (sigma/r)^6 the derivative sums of lj_fh_corr() (lj.c:29-50) collapse:
+        //   d2E + 2 dE / r                   = (528 A - 120 B) / r^2
+        //   15 dE / r^3 + 4 d3E / r + d4E    = (87984 A - 6360 B) / r^4
+        // (dE = -24 (2A - B)/r, d2E = 24 (26A - 7B)/r^2, d3E = -1344 (6A - B)/r^3, d4E = 12096 (10A - B)/r^4)
+        const double B6 = eps * s6, A12 = att ? 0.0 : B6 * s6;
+        double u = 4.0 * (A12 - B6);
+        if (FH) {
+            const double ir2 = ir * ir;
+            u = fma((k.fh2_pref * inv_mured) * ir2, fma(528.0, A12, -120.0 * B6), u);
+            if (FH >= 4)
+                u = fma((k.fh4_pref * (inv_mured * inv_mured)) * (ir2 * ir2), fma(87984.0, A12, -6360.0 * B6), u);
         }
         A.rd += u;
         A.n_lj++;
@@ -230,18 +230,19 @@ __device__ __forceinline__ void pair_body(const PairConsts& k, int mixing, const
             if (FH) gaussian_term = x < 26.0 ? exp_neg_fast(k, x * x) : 0.0;  // exp(-alpha^2 r^2), valid below 700
         }
         double u = qq * erfc_term * ir;
-        if (FH) {  // coulombic.c:132-141
-            const double ir2 = ir * ir, ir3 = ir * ir2, ir4 = ir2 * ir2;
+        if (FH) {
+            // coulombic_real_FH() (coulombic.c:132-141) with G = exp(-a^2 r^2) / sqrt(pi), E = erfc(a r); its derivative sums
+            // collapse (the erfc terms of the second-order sum cancel identically, those of the fourth-order sum to -15 E / r^5):
+            //   d2u + 2 du / r                 = 4 G (a^3 + (1 - a) / r^2)
+            //   15 du / r^3 + 4 d3u / r + d4u  = G (16 a^7 r^2 - 24 a^5 + (48 - 78 a) / r^4) - 15 E / r^5
+            // (the reference's own mix of powers of alpha is kept; the corrections carry no charge product, as there)
+            const double ir2 = ir * ir;
             const double gg = gaussian_term * k.inv_sqrt_pi;
-            const double du = -2.0 * k.alpha * gg * ir - erfc_term * ir2;
-            const double d2u = 4.0 * gg * (k.a3 + ir2) + 2.0 * erfc_term * ir3;
-            u += (k.fh2_pref * inv_mured) * (d2u + 2.0 * du * ir);
+            u = fma(k.fh2_pref * inv_mured, 4.0 * gg * fma(k.one_m_alpha, ir2, k.a3), u);
             if (FH >= 4) {
-                const double d3u = gg * (-8.0 * (k.a3 * k.a2) * r - 8.0 * k.a3 * ir - 12.0 * k.alpha * ir3) -
-                                   6.0 * erfc_term * ir4;
-                const double d4u = gg * (8.0 * k.a3 * k.a2 + 16.0 * k.a3 * k.a4 * r2 + 32.0 * k.a3 * ir2 + 48.0 * ir4) +
-                                   24.0 * erfc_term * (ir4 * ir);
-                u += (k.fh4_pref_es * (inv_mured * inv_mured)) * (15.0 * du * ir3 + 4.0 * d3u * ir + d4u);
+                const double ir4 = ir2 * ir2;
+                const double poly = fma(k.a7x16, r2, fma(k.c_ir4, ir4, -k.a5x24));
+                u = fma(k.fh4_pref_es * (inv_mured * inv_mured), fma(gg, poly, -15.0 * erfc_term * (ir4 * ir)), u);
             }
         }
         A.es += u;
@@ -591,6 +592,10 @@ static PairConsts make_pair_consts(const Cell& c, const PairOpts& o) {
     k.a2 = k.alpha * k.alpha;
     k.a3 = k.a2 * k.alpha;
     k.a4 = k.a3 * k.alpha;
+    k.one_m_alpha = 1.0 - k.alpha;
+    k.a5x24 = 24.0 * (k.a3 * k.a2);
+    k.a7x16 = 16.0 * k.a3 * k.a4;
+    k.c_ir4 = 48.0 - 78.0 * k.alpha;
     k.inv_sqrt_pi = 1.0 / sqrt(M_PI);
     k.fh2_pref = kM2A2 * (kHBAR2 / (24.0 * kKB * o.temperature));
     k.fh4_pref = kM2A4 * (kHBAR4 / (1152.0 * kKB2 * o.temperature * o.temperature));

@@ -28,13 +28,17 @@ CASES = [("cuda_pol.small (10 atoms)", lambda: fix(gu.load("ref_small")[0]), 200
          ("h2_fluid_2000", lambda: fix(systems.h2_fluid(2000)), 8000),
          ("h2_fluid_4000", lambda: fix(systems.h2_fluid(4000)), 4000),
          ("co2_fluid 3,000 atoms, non-polarizable", lambda: fix(systems.co2_fluid(1000)), 12000),
+         ("co2_fluid_12k (BASELINE config 2)", lambda: fix(bench.build_workload("co2_fluid_12k")), 2049),
          ("mof_h2_7k", lambda: fix(bench.build_workload("mof_h2_7k")), 1537),
          ("mof_h2_21k", lambda: fix(bench.build_workload("mof_h2_21k")), 1025),
          ("mof_h2_63k", lambda: fix(bench.build_workload("mof_h2_63k")), 129)]
 
 if __name__ == "__main__":
+    only = os.environ.get("RESIDENT_AB_ONLY")  # substring filter on the case label
     batches = [int(a) for a in sys.argv[1:]] or [0, 8, 32, 64]
     for label, make, steps in CASES:
+        if only and only not in label:
+            continue
         s = make()
         for B in batches:
             with tempfile.TemporaryDirectory(prefix="mpmc_res_") as td:
