@@ -463,7 +463,14 @@ SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
     // = 5.55e-17: 1.0 - x rounds to 1.0 exactly, so damp1 == damp2 == 1.0 bit for bit.
     k.far2 = 0.0;
     if (ortho && o.damp_type == MPMC_DAMP_EXPONENTIAL && l > 0.0) {
-        const double rf = 48.0 / l * (1.0 + 1e-12);
+        // MPMC_B200_SYM_FAR_LR (A/B): a smaller product trades the bit-exact skip for more far cluster pairs; at l r = 40 the
+        // damping factors differ from 1 by 4.5e-14 at most (e^{-40} 40^3 / 6)
+        static const double far_lr = [] {
+            const char* v = getenv("MPMC_B200_SYM_FAR_LR");
+            const double x = v ? atof(v) : 48.0;
+            return x >= 30.0 && x <= 48.0 ? x : 48.0;
+        }();
+        const double rf = far_lr / l * (1.0 + 1e-12);
         k.far2 = rf * rf;
     }
     {
