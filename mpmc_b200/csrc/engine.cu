@@ -915,6 +915,8 @@ static int repack(Ctx* c) {
         const bool k1_critical = !(c->P.polarization && !c->P.rd_only) || n <= 8192;
         const int batches = k1_critical ? nclus / 2 + 1 : (nclus / 2 + 1 + 31) / 32;
         c->pair_kslices = std::max(1, std::min(batches, (8 * sms + ctas_x - 1) / ctas_x));
+        if (const char* v = getenv("MPMC_B200_K1_SLICES"))  // A/B: slices of the candidate offsets per i-cluster
+            if (atoi(v) > 0) c->pair_kslices = std::min(atoi(v), nclus / 2 + 1);
         const int cols = pair_cluster_columns(c->sorted.n_pad, 0, own, c->pair_kslices);
         c->ntiles = 0;
         c->pair_stride = round_up(std::max(cols, 1), 32);
