@@ -914,7 +914,10 @@ static int repack(Ctx* c) {
         // (small systems: the fused solve is shorter than a warp's walk over whole batches -- K1 0.41-0.90 ms at 1k-4k atoms)
         const bool k1_critical = !(c->P.polarization && !c->P.rd_only) || n <= 8192;
         const int batches = k1_critical ? nclus / 2 + 1 : (nclus / 2 + 1 + 31) / 32;
-        c->pair_kslices = std::max(1, std::min(batches, (8 * sms + ctas_x - 1) / ctas_x));
+        // CTAs aimed at: ~8 per SM beside the solve; ~28 per SM where K1 is the critical path -- the grid is then many waves
+        // of short CTAs instead of 1.4 waves of long ones (co2_fluid_12k: 13 -> 38 slices, K1 0.676 -> 0.585 ms; optimum 39-78)
+        const int per_sm = k1_critical ? 28 : 8;
+        c->pair_kslices = std::max(1, std::min(batches, (per_sm * sms + ctas_x - 1) / ctas_x));
         if (const char* v = getenv("MPMC_B200_K1_SLICES"))  // A/B: slices of the candidate offsets per i-cluster
             if (atoi(v) > 0) c->pair_kslices = std::min(atoi(v), nclus / 2 + 1);
         const int cols = pair_cluster_columns(c->sorted.n_pad, 0, own, c->pair_kslices);
