@@ -628,11 +628,11 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
     // fewer than ~8 waves of resident CTAs -- 4 and 8 GPUs at 63k atoms: 0.978 -> 0.951 and 0.528 -> 0.501 ms per
     // contraction (profiles/r02_multi_gpu.md; in round 1 it lost 8 % because the partial-row reduce then cost twice as
     // much, which the list-driven reduce no longer does) -- and nowhere else.
-    a.hsplit = 1;
-    {
-        const long long items_here = ((long long)S * ysplits + world - 1) / world;
-        if (world > 1 && items_here < 8LL * SYM_MINB * sms) a.hsplit = 2;
-    }
+    // Round 2, end: with the list-driven reduce the half items also pay on ONE GPU -- 9.6k polarizable atoms 0.283 -> 0.253 ms
+    // per contraction (1.3 -> 2.6 waves), 15k -6 %, 31k -3 %, 46k (mof_h2_63k, 9.5 -> 19 waves) 3.674 -> 3.597 ms
+    // (profiles/r02_k4_hsplit.md) -- so they are the default everywhere; MPMC_B200_SYM_HSPLIT=1 restores whole items.
+    a.hsplit = 2;
+    (void)sms;
     if (const char* v = getenv("MPMC_B200_SYM_HSPLIT")) a.hsplit = atoi(v) == 2 ? 2 : 1;
     // Sharding unit: the work item (I tile, offset slice y) -- every item has the same number of pairs; the items are
     // dealt out round robin over their y-major order, so the ranks differ by at most one item and hold the same mix of
