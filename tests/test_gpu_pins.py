@@ -83,3 +83,8 @@ print("ROUNDS_OK", len(devs))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
                        env=dict(os.environ, MPMC_B200_SYM_PART_MB="2", MPMC_B200_SYM_MIN="0"))
     assert r.returncode == 0 and "ROUNDS_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+    # the other launch shape of the symmetric contraction: whole J super tiles per CTA (half tiles are the default since the
+    # end of round 2, MPMC_B200_SYM_HSPLIT); both must meet the pin
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, MPMC_B200_SYM_HSPLIT="1", MPMC_B200_SYM_MIN="0"))
+    assert r.returncode == 0 and "ROUNDS_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
