@@ -10,6 +10,7 @@
 //                                                              (dipole_kernel.cu)
 // The O(N^2) pair_t lists and the 3N x 3N A matrix are never built: device memory is O(N).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <condition_variable>
 #include <functional>
@@ -255,6 +256,13 @@ struct mpmc_b200_ctx {
     bool boxes_fresh = false;  // sorted.cbox matches the current positions
     double pairs_tested_analytic = 0.0;
     std::vector<double> hx_sort, hy_sort, hz_sort;  // positions at the time of the last spatial sort
+    // uVT: an insertion or a removal of a molecule changes the atom set by a few atoms.  The spatial orders (a matter of
+    // speed, never of results) are then carried over instead of being rebuilt: surviving atoms keep their place, new atoms
+    // go to the end; a full sort again after enough edits or when an atom has drifted (resort_pending)
+    std::vector<int> edit_map;     // set_atoms -> repack: old atom index -> new one, -1 = gone; empty = no carry-over
+    int edit_new_begin = 0, edit_new_end = 0;  // the new atoms [begin, end)
+    int order_edits = 0;           // atoms added + removed since the last full sort
+    bool orders_valid = false;     // pol / sorted / gsp hold spatial orders made under the current options
     DevBuf<double> cbox, sym_partI, sym_partJ, esum;
     int sym_ysplits = 1;
     int fb = 0, fe = 0, pb = 0, pe = 0;  // this shard's static-field rows (atom space) and dipole rows (packed space)
@@ -799,8 +807,78 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
     return 0;
 }
 
+// the order `old_idx` of a set of atoms after a small edit of the atom set (edit_map): survivors keep their place, the new
+// atoms that belong to the set (`member`) go in right behind the survivor nearest to them (minimum image) -- at the end
+// of the order they would make one cluster with a box as large as the cell, and the CTA that owns it in the row-owned
+// cutoff kernels would walk every other cluster (a straggler on the critical path: +1.4 ms at 63k atoms)
+template <class Member>
+static std::vector<int> carried_order(const Ctx* c, const std::vector<int>& old_idx, Member member) {
+    const mpmc_b200_params& P = c->P;
+    std::vector<int> fresh;
+    for (int i = c->edit_new_begin; i < c->edit_new_end; i++)
+        if (member(i)) fresh.push_back(i);
+    int anchor = -1;  // new index of the nearest survivor
+    if (!fresh.empty()) {
+        const int a = fresh[0];
+        double best = 1e300;
+        for (int g : old_idx) {
+            const int m = (g >= 0 && g < (int)c->edit_map.size()) ? c->edit_map[g] : -1;
+            if (m < 0) continue;
+            const double d[3] = {c->hx[m] - c->hx[a], c->hy[m] - c->hy[a], c->hz[m] - c->hz[a]};
+            double f[3], w[3] = {0.0, 0.0, 0.0};
+            for (int p = 0; p < 3; p++) {
+                f[p] = P.reciprocal_basis[0][p] * d[0] + P.reciprocal_basis[1][p] * d[1] + P.reciprocal_basis[2][p] * d[2];
+                f[p] -= rint(f[p]);
+            }
+            for (int p = 0; p < 3; p++)
+                for (int q = 0; q < 3; q++) w[q] += P.basis[p][q] * f[p];
+            const double r2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
+            if (r2 < best) {
+                best = r2;
+                anchor = m;
+            }
+        }
+    }
+    std::vector<int> out;
+    out.reserve(old_idx.size() + fresh.size());
+    bool placed = fresh.empty();
+    for (int g : old_idx) {
+        const int m = (g >= 0 && g < (int)c->edit_map.size()) ? c->edit_map[g] : -1;
+        if (m < 0) continue;
+        out.push_back(m);
+        if (!placed && m == anchor) {
+            out.insert(out.end(), fresh.begin(), fresh.end());
+            placed = true;
+        }
+    }
+    if (!placed) out.insert(out.end(), fresh.begin(), fresh.end());
+    return out;
+}
+
 static int repack(Ctx* c) {
     const int n = c->n;
+    // small edit of the atom set: the spatial orders are carried over (see edit_map); anything else sorts afresh
+    const bool carry = !c->edit_map.empty() && c->orders_valid;
+    std::vector<double> sx_old, sy_old, sz_old;
+    if (carry && c->hx_sort.size() == c->edit_map.size()) {
+        sx_old.swap(c->hx_sort), sy_old.swap(c->hy_sort), sz_old.swap(c->hz_sort);
+    }
+    auto sort_positions = [&]() {  // the positions the drift check of set_positions compares with
+        c->hx_sort = c->hx, c->hy_sort = c->hy, c->hz_sort = c->hz;
+        if (carry && !sx_old.empty())
+            for (size_t g = 0; g < c->edit_map.size(); g++) {
+                const int m = c->edit_map[g];
+                if (m >= 0) c->hx_sort[m] = sx_old[g], c->hy_sort[m] = sy_old[g], c->hz_sort[m] = sz_old[g];
+            }
+    };
+    static const bool timing = getenv("MPMC_B200_REPACK_TIMING") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    double t_sort = 0.0;
+    auto timed_sort = [&](std::vector<int>& idx) {
+        const auto t0 = std::chrono::steady_clock::now();
+        spatial_order(c, idx);
+        t_sort += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    };
     c->layout_dirty = true;
     c->inc_valid = false;
     c->inc_moved.clear();
@@ -839,11 +917,12 @@ static int repack(Ctx* c) {
     // atoms in list / rank order and keeps the list order
     c->pol_sorted = false;
     if (c->use_sym && (!(c->P.polar_gs || c->P.polar_gs_ranked) || c->P.polar_ewald_full) && c->have_params) {
-        spatial_order(c, pol);
+        if (carry && !c->pol.idx.empty())
+            pol = carried_order(c, c->pol.idx, [&](int i) { return c->halpha[i] != 0.0; });
+        else
+            timed_sort(pol);
         c->pol_sorted = true;
-        c->hx_sort = c->hx;
-        c->hy_sort = c->hy;
-        c->hz_sort = c->hz;
+        sort_positions();
     }
     const int polpad = dipole_sym_tile() * std::max(c->world, 1);  // super tiles of the symmetric K4, equal shards
     if (pack_subset(c, c->charged, charged, TILE, false) || pack_subset(c, c->recip, recip, TILE, false) ||
@@ -855,7 +934,10 @@ static int repack(Ctx* c) {
     if (c->gs_spatial && c->gs_delta && c->have_params && (c->P.polar_gs || c->P.polar_gs_ranked) && !c->P.polar_ewald_full &&
         c->pol.n > 0) {
         std::vector<int> sp = c->pol.idx;  // list order
-        spatial_order(c, sp);
+        if (carry && !c->gsp.idx.empty())
+            sp = carried_order(c, c->gsp.idx, [&](int i) { return c->halpha[i] != 0.0; });
+        else
+            timed_sort(sp);
         if (pack_subset(c, c->gsp, sp, polpad, true)) return 11;
         std::vector<int> packed_of_atom(n, -1);
         for (int k = 0; k < c->pol.n; k++) packed_of_atom[c->pol.idx[k]] = k;
@@ -865,11 +947,7 @@ static int repack(Ctx* c) {
         if (c->map_s2g.ensure(gp) || c->map_g2s.ensure(gp) || c->g_mu_sp.ensure(3 * gp) || c->g_esum_sp.ensure(3 * gp) ||
             c->cbox_sp.ensure(6 * (gp / 32)))
             FAIL(11, "cudaMalloc failed");
-        if (!c->pol_sorted && !c->use_clusters) {  // the drift check of set_positions needs the sort-time positions
-            c->hx_sort = c->hx;
-            c->hy_sort = c->hy;
-            c->hz_sort = c->hz;
-        }
+        if (!c->pol_sorted && !c->use_clusters) sort_positions();  // the drift check of set_positions needs the sort-time positions
     }
     c->hperm.assign(c->pol.n_pad, 0);
     std::iota(c->hperm.begin(), c->hperm.end(), 0);
@@ -880,13 +958,12 @@ static int repack(Ctx* c) {
         // spatially sorted image of ALL atoms for the cutoff kernels (K1, K3)
         std::vector<int> all(n);
         std::iota(all.begin(), all.end(), 0);
-        spatial_order(c, all);
+        if (carry && !c->sorted.idx.empty())
+            all = carried_order(c, c->sorted.idx, [](int) { return true; });
+        else
+            timed_sort(all);
         if (pack_subset(c, c->sorted, all, 32, false, true)) return 11;
-        if (!c->pol_sorted) {  // the drift check of set_positions needs the sort-time positions in either case
-            c->hx_sort = c->hx;
-            c->hy_sort = c->hy;
-            c->hz_sort = c->hz;
-        }
+        if (!c->pol_sorted) sort_positions();  // the drift check of set_positions needs the sort-time positions in either case
         // intramolecular erf term: list order, molecules are contiguous (pairs.c:28-34)
         std::vector<int> follow(np, 0);
         double same_mol_pairs = 0.0;  // pairs of one molecule that are not frozen-frozen
@@ -1008,6 +1085,13 @@ static int repack(Ctx* c) {
     c->analytic_dirty = true;
     c->subsets_stale = false;
     c->have_atoms = true;
+    if (!carry) c->order_edits = 0;
+    c->orders_valid = c->have_params;
+    c->edit_map.clear();
+    if (timing)
+        fprintf(stderr, "MPMC_B200_REPACK_TIMING: n %d, %s, spatial sorts %.3f ms, whole repack %.3f ms (host work + enqueued uploads)\n", n,
+                carry ? "orders carried over" : "full sort", t_sort,
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
     return 0;
 }
 
@@ -1070,6 +1154,7 @@ static int refresh_subsets(Ctx* c) {
         for (int k = 0; k < c->pol.n; k++) packed_of_atom[c->pol.idx[k]] = k;
         for (int k = 0; k < c->gsp.n_pad; k++) c->gsp_packed[k] = k < c->gsp.n ? packed_of_atom[sp[k]] : k;
     }
+    if (c->resort_pending) c->order_edits = 0;
     c->resort_pending = false;
     if (!c->subsets_stale) return 0;
     for (Subset* s : {&c->charged, &c->recip, &c->pol, &c->nonpol, &c->sorted, &c->gsp}) {
@@ -2615,6 +2700,7 @@ int mpmc_b200_set_params(mpmc_b200_ctx* c, const mpmc_b200_params* p) {
     c->inc_valid = false;
     c->warm_valid = false;
     c->layout_dirty = true;
+    if (repack_needed || !c->have_params || memcmp(p->basis, c->P.basis, sizeof(p->basis)) != 0) c->orders_valid = false;
     c->P = *p;
     c->have_params = true;
     c->kdirty = true;
@@ -2646,6 +2732,35 @@ int mpmc_b200_set_atoms(mpmc_b200_ctx* c, int n, const double* pos, const double
     }
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
+    // a small edit of the atom set (uVT insert / remove / restore): common prefix and suffix with what is held
+    c->edit_map.clear();
+    {
+        static const bool reuse = [] { const char* v = getenv("MPMC_B200_REUSE_ORDER"); return !(v && v[0] == '0'); }();
+        const int no = c->n;
+        if (reuse && c->have_atoms && c->orders_valid && !c->resort_pending && no >= 1024 && n >= 1024) {
+            auto same = [&](int io, int in) {
+                return c->hx[io] == pos[3 * in] && c->hy[io] == pos[3 * in + 1] && c->hz[io] == pos[3 * in + 2] &&
+                       c->hq[io] == charge[in] && c->halpha[io] == polarizability[in] && c->heps[io] == epsilon[in] &&
+                       c->hsig[io] == sigma[in] && c->hfrozen[io] == (frozen[in] ? 1 : 0);
+            };
+            const int lim = std::min(no, n);
+            int pre = 0;
+            while (pre < lim && same(pre, pre)) pre++;
+            int suf = 0;
+            while (suf < lim - pre && same(no - 1 - suf, n - 1 - suf)) suf++;
+            const int gone = no - pre - suf, fresh = n - pre - suf;
+            // every edit shifts the clusters behind it off the bricks the sort made (a few % of K4 / K1 / K3 once many have
+            // piled up): a full sort again after n/128 edited atoms -- its cost, spread over them, is ~0.15 ms per edit
+            if (gone >= 0 && fresh >= 0 && gone + fresh <= 256 && c->order_edits + gone + fresh <= std::max(64, no / 128)) {
+                c->edit_map.assign(no, -1);
+                for (int i = 0; i < pre; i++) c->edit_map[i] = i;
+                for (int i = 0; i < suf; i++) c->edit_map[no - 1 - i] = n - 1 - i;
+                c->edit_new_begin = pre;
+                c->edit_new_end = pre + fresh;
+                c->order_edits += gone + fresh;
+            }
+        }
+    }
     c->n = n;
     c->hx.resize(n), c->hy.resize(n), c->hz.resize(n), c->hq.resize(n), c->halpha.resize(n), c->heps.resize(n);
     c->hsig.resize(n), c->hmm.resize(n), c->hmol.resize(n), c->hfrozen.resize(n);

@@ -307,3 +307,46 @@ def test_edge_cases(engine):
         got = engine.energy()
         exp, _, _ = oracle.energy(sN, nthreads=0)
         gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=f"n={n}")
+
+
+def test_small_edits_of_the_atom_set_keep_parity(engine):
+    """uVT through the ABI: after a removal / an insertion of a molecule set_atoms carries the spatial orders over instead of
+    sorting afresh (surviving atoms keep their place, new atoms go in behind their nearest survivor; engine.cu: edit_map).
+    The orders only re-associate sums: every edited configuration must still meet the oracle at 1e-10, energies and dipoles."""
+    from oracle import oracle
+
+    rng = np.random.default_rng(11)
+    s = systems.mof_h2(cells=(3, 3, 1))  # 2,391 atoms: above the 1,024-atom threshold of the carry-over
+    fields = ("pos", "charge", "polarizability", "epsilon", "sigma", "mol_mass", "mol_id", "frozen")
+    engine.set_system(s)
+    engine.energy()
+    L = np.array([s.params.basis[q][q] for q in range(3)])
+    cur = s
+    for k in range(6):
+        st = np.flatnonzero(np.r_[True, cur.mol_id[1:] != cur.mol_id[:-1]])
+        en = np.r_[st[1:], cur.n]
+        mv = [i for i in range(len(st)) if not cur.frozen[st[i]]]
+        m = mv[int(rng.integers(len(mv)))]
+        a, b = int(st[m]), int(en[m])
+        nxt = cur.copy()
+        if k % 3 != 2:  # two removals ...
+            keep = np.r_[np.arange(0, a), np.arange(b, cur.n)]
+            for f in fields:
+                setattr(nxt, f, getattr(cur, f)[keep].copy())
+        else:  # ... then an insertion in the MIDDLE of the list (a copy of molecule m, displaced, right behind it)
+            for f in fields:
+                v = getattr(cur, f)
+                add = v[a:b].copy()
+                if f == "pos":
+                    add = add + rng.uniform(-0.5, 0.5, 3) * L
+                setattr(nxt, f, np.concatenate([v[:b], add, v[b:]]))
+            nxt.mol_id[b:b + (b - a)] = -1
+        nxt.mol_id = np.cumsum(np.r_[0, (nxt.mol_id[1:] != nxt.mol_id[:-1]).astype(np.int32)]).astype(np.int32)
+        engine.set_system(nxt)
+        got = engine.energy()
+        exp, _, oarr = oracle.energy(nxt, nthreads=0)
+        gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=f"edit {k}")
+        mu = engine.atom_arrays()["mu"]
+        assert np.abs(mu - oarr["mu"]).max() <= 1e-10 * np.abs(oarr["mu"]).max(), f"edit {k}: dipoles"
+        cur = nxt
+
