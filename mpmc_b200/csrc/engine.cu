@@ -362,6 +362,46 @@ __global__ void gather_positions_kernel(const double* __restrict__ x, const doub
     sz[k] = z[g];
 }
 
+// A subset's own SoA copy, filled on the device from the list-order atom arrays and the subset's index list (one
+// upload per subset instead of nine to twelve): entries k < n take atom idx[k]; padding takes zeros, molecule -1, no flags
+// (aux 1.0 under linear damping, where the kernels form its powers).
+__global__ void subset_gather_kernel(int n, int n_pad, const int* __restrict__ idx, const double* __restrict__ ax,
+                                     const double* __restrict__ ay, const double* __restrict__ az,
+                                     const double* __restrict__ aq, const double* __restrict__ aalpha,
+                                     const double* __restrict__ aeps, const double* __restrict__ asig,
+                                     const double* __restrict__ amm, const int* __restrict__ amol,
+                                     const int* __restrict__ aflags, int with_aux, int damp_linear, int with_lj,
+                                     double* __restrict__ x, double* __restrict__ y, double* __restrict__ z,
+                                     double* __restrict__ q, double* __restrict__ alpha, double* __restrict__ aux,
+                                     double* __restrict__ eps, double* __restrict__ sig, double* __restrict__ mm,
+                                     int* __restrict__ mol, int* __restrict__ flags) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_pad) return;
+    if (k < n) {
+        const int g = idx[k];
+        const double qq = aq[g], al = aalpha[g];
+        x[k] = ax[g];
+        y[k] = ay[g];
+        z[k] = az[g];
+        q[k] = qq;
+        alpha[k] = al;
+        aux[k] = with_aux ? (damp_linear ? pow(al, 1.0 / 6.0) : qq) : 0.0;
+        mol[k] = amol[g];
+        flags[k] = aflags[g];
+        if (with_lj) {
+            eps[k] = aeps[g];
+            sig[k] = asig[g];
+            mm[k] = amm[g];
+        }
+    } else {
+        x[k] = y[k] = z[k] = q[k] = alpha[k] = 0.0;
+        aux[k] = (with_aux && damp_linear) ? 1.0 : 0.0;
+        mol[k] = -1;
+        flags[k] = 0;
+        if (with_lj) eps[k] = sig[k] = mm[k] = 0.0;
+    }
+}
+
 // dst[c][k] = src[c][perm[k]] (forward) or dst[c][perm[k]] = src[c][k] (inverse), k < n
 __global__ void permute_kernel(const double* __restrict__ src, double* __restrict__ dst, const int* __restrict__ perm, int n,
                                int np, int ncomp, int inverse) {
@@ -772,38 +812,23 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
     s.idx = idx;
     s.n = (int)idx.size();
     s.n_pad = std::max(round_up(s.n, pad_multiple), pad_multiple);
-    std::vector<double> x(s.n_pad, 0.0), y(s.n_pad, 0.0), z(s.n_pad, 0.0), q(s.n_pad, 0.0), al(s.n_pad, 0.0), aux(s.n_pad, 0.0);
-    std::vector<int> mol(s.n_pad, -1), fl(s.n_pad, 0), di(s.n_pad, 0);
-    for (int k = 0; k < s.n; k++) {
-        const int g = idx[k];
-        x[k] = c->hx[g];
-        y[k] = c->hy[g];
-        z[k] = c->hz[g];
-        q[k] = c->hq[g];
-        al[k] = c->halpha[g];
-        mol[k] = c->hmol[g];
-        fl[k] = F_VALID | (c->hfrozen[g] ? F_FROZEN : 0);
-        di[k] = g;
-        if (with_aux) aux[k] = (P.damp_type == MPMC_DAMP_LINEAR) ? pow(c->halpha[g], 1.0 / 6.0) : c->hq[g];
-    }
-    if (with_aux && P.damp_type == MPMC_DAMP_LINEAR)
-        for (int k = s.n; k < s.n_pad; k++) aux[k] = 1.0;
-    // distinct pad positions far from each other are not needed: pad sources carry mu = 0 / q = 0 and
-    // every loop over a padded tile is bounded by n
+    // the index list goes up; the subset's arrays are gathered on the device from the list-order atom arrays, which
+    // repack() has uploaded before (subset_gather_kernel)
+    std::vector<int> di(s.n_pad, 0);
+    std::copy(idx.begin(), idx.end(), di.begin());
     cudaStream_t st = c->stream;
-    if (upload(s.x, x, st) || upload(s.y, y, st) || upload(s.z, z, st) || upload(s.q, q, st) || upload(s.alpha, al, st) ||
-        upload(s.aux, aux, st) || upload(s.mol, mol, st) || upload(s.flags, fl, st) || upload(s.didx, di, st))
-        return 11;
-    if (with_lj) {
-        std::vector<double> e(s.n_pad, 0.0), sg(s.n_pad, 0.0), mm(s.n_pad, 0.0);
-        for (int k = 0; k < s.n; k++) {
-            e[k] = c->heps[idx[k]];
-            sg[k] = c->hsig[idx[k]];
-            mm[k] = c->hmm[idx[k]];
-        }
-        if (upload(s.eps, e, st) || upload(s.sig, sg, st) || upload(s.mm, mm, st)) return 11;
-        if (s.cbox.ensure((size_t)6 * (s.n_pad / 32))) return 11;
-    }
+    const size_t np = (size_t)s.n_pad;
+    if (upload(s.didx, di, st)) return 11;
+    if (s.x.ensure(np) || s.y.ensure(np) || s.z.ensure(np) || s.q.ensure(np) || s.alpha.ensure(np) || s.aux.ensure(np) ||
+        s.mol.ensure(np) || s.flags.ensure(np))
+        FAIL(11, "cudaMalloc failed");
+    if (with_lj && (s.eps.ensure(np) || s.sig.ensure(np) || s.mm.ensure(np) || s.cbox.ensure((size_t)6 * (s.n_pad / 32))))
+        FAIL(11, "cudaMalloc failed");
+    subset_gather_kernel<<<(s.n_pad + 255) / 256, 256, 0, st>>>(
+        s.n, s.n_pad, s.didx.p, c->x.p, c->y.p, c->z.p, c->q.p, c->alpha.p, c->eps.p, c->sig.p, c->molmass.p, c->mol.p, c->flags.p,
+        with_aux ? 1 : 0, P.damp_type == MPMC_DAMP_LINEAR ? 1 : 0, with_lj ? 1 : 0, s.x.p, s.y.p, s.z.p, s.q.p, s.alpha.p, s.aux.p,
+        with_lj ? s.eps.p : nullptr, with_lj ? s.sig.p : nullptr, with_lj ? s.mm.p : nullptr, s.mol.p, s.flags.p);
+    CU(cudaGetLastError());
     return 0;
 }
 
@@ -820,22 +845,42 @@ static std::vector<int> carried_order(const Ctx* c, const std::vector<int>& old_
     int anchor = -1;  // new index of the nearest survivor
     if (!fresh.empty()) {
         const int a = fresh[0];
+        const double xa = c->hx[a], ya = c->hy[a], za = c->hz[a];
+        const int nmap = (int)c->edit_map.size();
         double best = 1e300;
-        for (int g : old_idx) {
-            const int m = (g >= 0 && g < (int)c->edit_map.size()) ? c->edit_map[g] : -1;
-            if (m < 0) continue;
-            const double d[3] = {c->hx[m] - c->hx[a], c->hy[m] - c->hy[a], c->hz[m] - c->hz[a]};
-            double f[3], w[3] = {0.0, 0.0, 0.0};
-            for (int p = 0; p < 3; p++) {
-                f[p] = P.reciprocal_basis[0][p] * d[0] + P.reciprocal_basis[1][p] * d[1] + P.reciprocal_basis[2][p] * d[2];
-                f[p] -= rint(f[p]);
+        if (is_ortho(P)) {  // the common case: per-axis wrap, no matrix products
+            const double Lx = P.basis[0][0], Ly = P.basis[1][1], Lz = P.basis[2][2];
+            const double ix = 1.0 / Lx, iy = 1.0 / Ly, iz = 1.0 / Lz;
+            for (int g : old_idx) {
+                const int m = (g >= 0 && g < nmap) ? c->edit_map[g] : -1;
+                if (m < 0) continue;
+                double dx = c->hx[m] - xa, dy = c->hy[m] - ya, dz = c->hz[m] - za;
+                dx -= Lx * rint(dx * ix);
+                dy -= Ly * rint(dy * iy);
+                dz -= Lz * rint(dz * iz);
+                const double r2 = dx * dx + dy * dy + dz * dz;
+                if (r2 < best) {
+                    best = r2;
+                    anchor = m;
+                }
             }
-            for (int p = 0; p < 3; p++)
-                for (int q = 0; q < 3; q++) w[q] += P.basis[p][q] * f[p];
-            const double r2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
-            if (r2 < best) {
-                best = r2;
-                anchor = m;
+        } else {
+            for (int g : old_idx) {
+                const int m = (g >= 0 && g < nmap) ? c->edit_map[g] : -1;
+                if (m < 0) continue;
+                const double d[3] = {c->hx[m] - xa, c->hy[m] - ya, c->hz[m] - za};
+                double f[3], w[3] = {0.0, 0.0, 0.0};
+                for (int p = 0; p < 3; p++) {
+                    f[p] = P.reciprocal_basis[0][p] * d[0] + P.reciprocal_basis[1][p] * d[1] + P.reciprocal_basis[2][p] * d[2];
+                    f[p] -= rint(f[p]);
+                }
+                for (int p = 0; p < 3; p++)
+                    for (int q = 0; q < 3; q++) w[q] += P.basis[p][q] * f[p];
+                const double r2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
+                if (r2 < best) {
+                    best = r2;
+                    anchor = m;
+                }
             }
         }
     }
