@@ -260,7 +260,13 @@ struct mpmc_b200_ctx {
     // speed, never of results) are then carried over instead of being rebuilt: surviving atoms keep their place, new atoms
     // go to the end; a full sort again after enough edits or when an atom has drifted (resort_pending)
     std::vector<int> edit_map;     // set_atoms -> repack: old atom index -> new one, -1 = gone; empty = no carry-over
-    int edit_new_begin = 0, edit_new_end = 0;  // the new atoms [begin, end)
+    std::vector<int> edit_fresh;   // the atoms to place: new ones (set_atoms) or drifted ones (refresh_subsets), ascending
+    // atoms that moved further than the drift limit from where they were when the orders were made (set_positions, the end
+    // of a resident batch): refresh_subsets() takes them out of the orders and puts them back behind their nearest
+    // neighbour instead of sorting everything again -- with the reference's default move_factor of 1.0 nearly every trial
+    // move is such a jump (a full sort per step: 19 ms at 63k atoms, 25 -> 17 MC steps/s)
+    std::vector<int> drifted;
+    bool drift_tracked = false;    // `drifted` names every atom that has to be relocated
     int order_edits = 0;           // atoms added + removed since the last full sort
     bool orders_valid = false;     // pol / sorted / gsp hold spatial orders made under the current options
     DevBuf<double> cbox, sym_partI, sym_partJ, esum;
@@ -839,64 +845,71 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
 template <class Member>
 static std::vector<int> carried_order(const Ctx* c, const std::vector<int>& old_idx, Member member) {
     const mpmc_b200_params& P = c->P;
+    const int nmap = (int)c->edit_map.size();
+    // the atoms to place, in runs of consecutive indices (a molecule's atoms are consecutive): one anchor per run
     std::vector<int> fresh;
-    for (int i = c->edit_new_begin; i < c->edit_new_end; i++)
+    for (int i : c->edit_fresh)
         if (member(i)) fresh.push_back(i);
-    int anchor = -1;  // new index of the nearest survivor
-    if (!fresh.empty()) {
-        const int a = fresh[0];
+    struct Run { int b, e, anchor; };
+    std::vector<Run> runs;
+    for (size_t k = 0; k < fresh.size();) {
+        size_t e = k + 1;
+        while (e < fresh.size() && fresh[e] == fresh[e - 1] + 1 && c->hmol[fresh[e]] == c->hmol[fresh[k]]) e++;
+        runs.push_back({(int)k, (int)e, -1});
+        k = e;
+    }
+    const bool ortho = is_ortho(P);
+    const double Lx = P.basis[0][0], Ly = P.basis[1][1], Lz = P.basis[2][2];
+    const double ix = 1.0 / Lx, iy = 1.0 / Ly, iz = 1.0 / Lz;
+    for (Run& r : runs) {  // nearest survivor of the set (minimum image)
+        const int a = fresh[r.b];
         const double xa = c->hx[a], ya = c->hy[a], za = c->hz[a];
-        const int nmap = (int)c->edit_map.size();
         double best = 1e300;
-        if (is_ortho(P)) {  // the common case: per-axis wrap, no matrix products
-            const double Lx = P.basis[0][0], Ly = P.basis[1][1], Lz = P.basis[2][2];
-            const double ix = 1.0 / Lx, iy = 1.0 / Ly, iz = 1.0 / Lz;
-            for (int g : old_idx) {
-                const int m = (g >= 0 && g < nmap) ? c->edit_map[g] : -1;
-                if (m < 0) continue;
-                double dx = c->hx[m] - xa, dy = c->hy[m] - ya, dz = c->hz[m] - za;
+        for (int g : old_idx) {
+            const int m = (g >= 0 && g < nmap) ? c->edit_map[g] : -1;
+            if (m < 0) continue;
+            double dx = c->hx[m] - xa, dy = c->hy[m] - ya, dz = c->hz[m] - za, r2;
+            if (ortho) {  // the common case: per-axis wrap, no matrix products
                 dx -= Lx * rint(dx * ix);
                 dy -= Ly * rint(dy * iy);
                 dz -= Lz * rint(dz * iz);
-                const double r2 = dx * dx + dy * dy + dz * dz;
-                if (r2 < best) {
-                    best = r2;
-                    anchor = m;
-                }
-            }
-        } else {
-            for (int g : old_idx) {
-                const int m = (g >= 0 && g < nmap) ? c->edit_map[g] : -1;
-                if (m < 0) continue;
-                const double d[3] = {c->hx[m] - xa, c->hy[m] - ya, c->hz[m] - za};
+                r2 = dx * dx + dy * dy + dz * dz;
+            } else {
                 double f[3], w[3] = {0.0, 0.0, 0.0};
                 for (int p = 0; p < 3; p++) {
-                    f[p] = P.reciprocal_basis[0][p] * d[0] + P.reciprocal_basis[1][p] * d[1] + P.reciprocal_basis[2][p] * d[2];
+                    f[p] = P.reciprocal_basis[0][p] * dx + P.reciprocal_basis[1][p] * dy + P.reciprocal_basis[2][p] * dz;
                     f[p] -= rint(f[p]);
                 }
                 for (int p = 0; p < 3; p++)
                     for (int q = 0; q < 3; q++) w[q] += P.basis[p][q] * f[p];
-                const double r2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
-                if (r2 < best) {
-                    best = r2;
-                    anchor = m;
-                }
+                r2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
+            }
+            if (r2 < best) {
+                best = r2;
+                r.anchor = m;
             }
         }
     }
+    // runs by anchor: head[anchor] -> first run, next[run] -> the following one with the same anchor
+    std::vector<int> head(c->n > 0 ? c->n : 1, -1), next(runs.size(), -1);
+    std::vector<int> loose;
+    for (int k = (int)runs.size() - 1; k >= 0; k--) {
+        if (runs[k].anchor < 0) {
+            loose.push_back(k);
+            continue;
+        }
+        next[k] = head[runs[k].anchor];
+        head[runs[k].anchor] = k;
+    }
     std::vector<int> out;
     out.reserve(old_idx.size() + fresh.size());
-    bool placed = fresh.empty();
     for (int g : old_idx) {
-        const int m = (g >= 0 && g < (int)c->edit_map.size()) ? c->edit_map[g] : -1;
+        const int m = (g >= 0 && g < nmap) ? c->edit_map[g] : -1;
         if (m < 0) continue;
         out.push_back(m);
-        if (!placed && m == anchor) {
-            out.insert(out.end(), fresh.begin(), fresh.end());
-            placed = true;
-        }
+        for (int k = head[m]; k >= 0; k = next[k]) out.insert(out.end(), fresh.begin() + runs[k].b, fresh.begin() + runs[k].e);
     }
-    if (!placed) out.insert(out.end(), fresh.begin(), fresh.end());
+    for (int k : loose) out.insert(out.end(), fresh.begin() + runs[k].b, fresh.begin() + runs[k].e);
     return out;
 }
 
@@ -1171,6 +1184,43 @@ static void kev_mark(Ctx* c) {
 }
 
 static int refresh_subsets(Ctx* c) {
+    // a few atoms jumped (a large displacement move, or its restore): they leave their place in the orders and go in
+    // again behind their nearest neighbour; everything else stays -- O(n) host work and one index upload + gather per
+    // subset instead of the k-d sorts (16 ms at 63k atoms)
+    static const bool reuse = [] { const char* v = getenv("MPMC_B200_REUSE_ORDER"); return !(v && v[0] == '0'); }();
+    if (c->resort_pending && reuse && c->drift_tracked && c->orders_valid && !c->drifted.empty() && c->n >= 1024 &&
+        c->hx_sort.size() == (size_t)c->n) {
+        std::sort(c->drifted.begin(), c->drifted.end());
+        c->drifted.erase(std::unique(c->drifted.begin(), c->drifted.end()), c->drifted.end());
+        const int nd = (int)c->drifted.size();
+        if (nd <= 256 && c->order_edits + nd <= std::max(64, c->n / 128)) {
+            c->edit_map.resize(c->n);
+            std::iota(c->edit_map.begin(), c->edit_map.end(), 0);
+            for (int g : c->drifted) c->edit_map[g] = -1;
+            c->edit_fresh = c->drifted;
+            const int polpad = dipole_sym_tile() * std::max(c->world, 1);
+            int rc = 0;
+            if (c->use_clusters && !c->sorted.idx.empty())
+                rc = pack_subset(c, c->sorted, carried_order(c, c->sorted.idx, [](int) { return true; }), 32, false, true);
+            if (!rc && c->pol_sorted && !c->pol.idx.empty())
+                rc = pack_subset(c, c->pol, carried_order(c, c->pol.idx, [&](int i) { return c->halpha[i] != 0.0; }), polpad, true);
+            if (!rc && c->gsp.n > 0) {
+                const std::vector<int> sp = carried_order(c, c->gsp.idx, [&](int i) { return c->halpha[i] != 0.0; });
+                rc = pack_subset(c, c->gsp, sp, polpad, true);
+                std::vector<int> packed_of_atom(c->n, -1);
+                for (int k = 0; k < c->pol.n; k++) packed_of_atom[c->pol.idx[k]] = k;
+                for (int k = 0; k < c->gsp.n_pad; k++) c->gsp_packed[k] = k < c->gsp.n ? packed_of_atom[sp[k]] : k;
+            }
+            c->edit_map.clear();
+            if (rc) return 11;
+            for (int g : c->drifted) c->hx_sort[g] = c->hx[g], c->hy_sort[g] = c->hy[g], c->hz_sort[g] = c->hz[g];
+            c->order_edits += nd;
+            c->resort_pending = false;
+            c->subsets_stale = true;  // the other subsets still hold the old coordinates
+        }
+    }
+    c->drifted.clear();
+    c->drift_tracked = false;
     if (c->resort_pending && c->use_clusters) {
         std::vector<int> all(c->n);
         std::iota(all.begin(), all.end(), 0);
@@ -2779,6 +2829,8 @@ int mpmc_b200_set_atoms(mpmc_b200_ctx* c, int n, const double* pos, const double
     CU(cudaStreamSynchronize(c->stream));
     // a small edit of the atom set (uVT insert / remove / restore): common prefix and suffix with what is held
     c->edit_map.clear();
+    c->drifted.clear();
+    c->drift_tracked = false;
     {
         static const bool reuse = [] { const char* v = getenv("MPMC_B200_REUSE_ORDER"); return !(v && v[0] == '0'); }();
         const int no = c->n;
@@ -2800,8 +2852,8 @@ int mpmc_b200_set_atoms(mpmc_b200_ctx* c, int n, const double* pos, const double
                 c->edit_map.assign(no, -1);
                 for (int i = 0; i < pre; i++) c->edit_map[i] = i;
                 for (int i = 0; i < suf; i++) c->edit_map[no - 1 - i] = n - 1 - i;
-                c->edit_new_begin = pre;
-                c->edit_new_end = pre + fresh;
+                c->edit_fresh.resize(fresh);
+                std::iota(c->edit_fresh.begin(), c->edit_fresh.end(), pre);
                 c->order_edits += gone + fresh;
             }
         }
@@ -2882,15 +2934,20 @@ int mpmc_b200_set_positions(mpmc_b200_ctx* c, int first, int count, const double
         sy[k] = c->hy[first + k] = pos[3 * k + 1];
         sz[k] = c->hz[first + k] = pos[3 * k + 2];
     }
-    if ((c->pol_sorted || c->use_clusters) && !c->resort_pending && c->hx_sort.size() == c->hx.size()) {
-        // clusters stay compact as long as no atom has drifted far from where it was sorted
+    if ((c->pol_sorted || c->use_clusters) && c->hx_sort.size() == c->hx.size() && (!c->resort_pending || c->drift_tracked)) {
+        // clusters stay compact as long as no atom has drifted far from where it was when the orders were made; the ones
+        // that have are named, so that refresh_subsets() can relocate them instead of sorting everything again
+        if (!c->resort_pending) {
+            c->drifted.clear();
+            c->drift_tracked = true;
+        }
         const double lim2 = 1.5 * 1.5;
         for (int k = 0; k < count; k++) {
             const int g = first + k;
             const double dx = c->hx[g] - c->hx_sort[g], dy = c->hy[g] - c->hy_sort[g], dz = c->hz[g] - c->hz_sort[g];
             if (dx * dx + dy * dy + dz * dz > lim2) {
                 c->resort_pending = true;
-                break;
+                if (c->drifted.size() <= 512) c->drifted.push_back(g);
             }
         }
     }
@@ -3219,11 +3276,16 @@ int mpmc_b200_mc_steps(mpmc_b200_ctx* c, int nsteps, const mpmc_b200_mc_move* mo
     c->cnt.kernel_launches = launches;
     if ((c->pol_sorted || c->use_clusters) && !c->resort_pending && c->hx_sort.size() == c->hx.size()) {
         const double lim2 = 1.5 * 1.5;  // as mpmc_b200_set_positions: clusters stay compact while no atom drifted far
-        for (int j = 0; j < nsteps && !c->resort_pending; j++)
+        c->drifted.clear();
+        c->drift_tracked = true;
+        for (int j = 0; j < nsteps; j++)
             for (int i = 0; i < moves[j].count; i++) {
                 const int g = moves[j].first + i;
                 const double dx = c->hx[g] - c->hx_sort[g], dy = c->hy[g] - c->hy_sort[g], dz = c->hz[g] - c->hz_sort[g];
-                if (dx * dx + dy * dy + dz * dz > lim2) c->resort_pending = true;
+                if (dx * dx + dy * dy + dz * dz > lim2) {
+                    c->resort_pending = true;
+                    if (c->drifted.size() <= 512) c->drifted.push_back(g);
+                }
             }
     }
     c->mc_last_steps = nsteps;

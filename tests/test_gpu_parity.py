@@ -350,3 +350,42 @@ def test_small_edits_of_the_atom_set_keep_parity(engine):
         assert np.abs(mu - oarr["mu"]).max() <= 1e-10 * np.abs(oarr["mu"]).max(), f"edit {k}: dipoles"
         cur = nxt
 
+
+def test_large_moves_relocate_atoms_in_the_orders(engine):
+    """With the reference's default move_factor (1.0: displacements up to the cutoff) nearly every trial move carries a
+    molecule further than the drift limit of the spatial orders.  The engine then takes the molecule's atoms out of the orders
+    and puts them back behind their nearest neighbour instead of sorting everything again (engine.cu: refresh_subsets).
+    Jumps of several Angstrom, a restore and two molecules moved between evaluations: every configuration against the oracle."""
+    from oracle import oracle
+
+    rng = np.random.default_rng(17)
+    s = systems.mof_h2(cells=(3, 3, 1))  # 2,391 atoms: above the 1,024-atom threshold of the carry-over
+    engine.set_system(s)
+    engine.energy()
+    st = np.flatnonzero(np.r_[True, s.mol_id[1:] != s.mol_id[:-1]])
+    en = np.r_[st[1:], s.n]
+    mv = [(int(a), int(b)) for a, b in zip(st, en) if not s.frozen[a]]
+    cur = s.copy()
+    last = None
+    for k in range(7):
+        nxt = cur.copy()
+        if k == 3 and last is not None:  # a reject: the molecule goes back where it was
+            a, b, old = last
+            nxt.pos[a:b] = old
+            moved = [(a, b)]
+        else:
+            moved = []
+            for _ in range(2 if k == 5 else 1):  # k == 5: two molecules between two evaluations
+                a, b = mv[int(rng.integers(len(mv)))]
+                last = (a, b, cur.pos[a:b].copy())
+                nxt.pos[a:b] = cur.pos[a:b] + rng.uniform(-6.0, 6.0, 3)
+                moved.append((a, b))
+        for a, b in moved:
+            engine.set_positions(a, nxt.pos[a:b])
+        got = engine.energy()
+        exp, _, oarr = oracle.energy(nxt, nthreads=0)
+        gu.assert_energies(got.to_dict(), exp.to_dict(), rtol=1e-10, label=f"jump {k}")
+        mu = engine.atom_arrays()["mu"]
+        assert np.abs(mu - oarr["mu"]).max() <= 1e-10 * np.abs(oarr["mu"]).max(), f"jump {k}: dipoles"
+        cur = nxt
+
