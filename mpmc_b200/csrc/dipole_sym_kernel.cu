@@ -24,7 +24,11 @@
 //     pair is so far apart that the exponential damping factors are exactly 1.0 in fp64
 //     (e^{-lr}(...) < 2^-54 for l r >= 48): then exp() and the damping polynomial are skipped -- the
 //     result is bit-identical to evaluating them.
-//   * minimum image: rint() runs on the conversion pipe (FRND.F64), not on the fp64 FMA pipe.
+//   * minimum image: rint() runs on the conversion pipe (FRND.F64), not on the fp64 FMA pipe.  Where the boxes of an
+//     (i-cluster, j-cluster) pair prove that EVERY atom pair picks the same image n (per axis |centre distance - n L| + half
+//     extents < L/2), the i positions are moved by -n L once per cluster pair and the per-pair image step (3 DMUL + 3 FRND
+//     + 3 DFMA of ~41 fp64 instructions) is left out: about half of the cluster pairs of a MOF cell.  n = 0 gives the same
+//     bits as the per-pair form; n != 0 rounds x_i - n L once where the per-pair form rounds (x_i - x_j) - n L (1 ulp of d).
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -122,10 +126,11 @@ struct SymArgs {
     int kper;        // offsets per gridDim.y slice
     int hsplit;      // 1: a CTA walks both halves of the J super tile; 2: gridDim.z = 2, one half each (finer grain
                      // for the short launches of a sharded run, where the last wave would otherwise cost ~10 %)
+    int unishift;    // 1: cluster pairs with one image for all their atom pairs skip the per-pair minimum image
     const double *x, *y, *z, *aux;
     const int* mol;
     const double* mu;    // [3][np]
-    const double* cbox;  // [6][np/32] centre xyz, half extent xyz
+    const double* cbox;  // [7][np/32] centre xyz, half extent xyz, 1.0 if no atom of the cluster sits in another image than its first
     double* epartI;      // [gridDim.y][3][np]
     double* epartJ;      // [K][3][np]
 };
@@ -137,6 +142,22 @@ struct SymArgs {
 #define SYM_MINB 4
 #endif
 constexpr int kSymUnroll = SYM_UNROLL;
+// unroll factor of the 32-step loop per class of cluster pair (far / damped, with / without one image for all pairs);
+// SYM_UNR_DAMPUNI 0: damped pairs always take the per-pair minimum image.  The kernel is sensitive to the size of its hot
+// loops (instruction cache): with all four classes at 4 the one-image path LOST 6.7 % (39.66 against 37.16 ms per energy()
+// at mof_h2_63k), with the two damped classes at 2 it gains 1.3 % (36.33 against 36.82; profiles/r02_k4_one_image.md)
+#ifndef SYM_UNR_FAR
+#define SYM_UNR_FAR SYM_UNROLL
+#endif
+#ifndef SYM_UNR_FARUNI
+#define SYM_UNR_FARUNI SYM_UNROLL
+#endif
+#ifndef SYM_UNR_DAMP
+#define SYM_UNR_DAMP 2
+#endif
+#ifndef SYM_UNR_DAMPUNI
+#define SYM_UNR_DAMPUNI 2
+#endif
 constexpr int STILE = 256;  // atoms per super tile: 2 per thread
 constexpr int JREC = 6;     // doubles per staged j record: x y z mx my mz
 
@@ -164,17 +185,38 @@ __device__ __forceinline__ void coeffs_exp(const SymConsts& k, double r2, double
     }
 }
 
+// Do all atom pairs of clusters (ca, cb) pick the same periodic image?  Both clusters must hold their atoms in ONE image
+// (row 6 of the boxes: then the box bounds the stored coordinates), and per axis |D - n L| + half extents must stay below
+// L/2 by a margin (1e-6 A: ~1e-8 of the box, nine orders above the rounding of rint(d / L)), D = centre distance,
+// n = rint(D / L): then rint((x_i - x_j) / L) = n for every pair.  Returns bit 30 | (n_x + 512) | (n_y + 512) << 10 |
+// (n_z + 512) << 20, or 0.
+constexpr int kNoImage = 512 | (512 << 10) | (512 << 20);
+__device__ __forceinline__ int uniform_image(const BoxLen& k, const double* __restrict__ cbox, int nclus, int ca, int cb) {
+    if (cbox[6 * nclus + ca] != 1.0 || cbox[6 * nclus + cb] != 1.0) return 0;
+    const double L[3] = {k.Lx, k.Ly, k.Lz}, iL[3] = {k.iLx, k.iLy, k.iLz};
+    int code = 1 << 30;
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+        const double D = cbox[d * nclus + ca] - cbox[d * nclus + cb];
+        const double n = rint(D * iL[d]);
+        const double rem = fabs(fma(-L[d], n, D)) + (cbox[(3 + d) * nclus + ca] + cbox[(3 + d) * nclus + cb]);
+        if (!(rem < 0.5 * L[d] - 1e-6) || !(fabs(n) <= 500.0)) return 0;
+        code |= ((int)n + 512) << (10 * d);
+    }
+    return code;
+}
+
 // One j-cluster of 32 (records staged twice in a row, so lane+s never wraps) against the two i atoms a
 // lane keeps in registers; T once per unordered pair, applied in both directions.
-template <bool ORTHO, int DAMP, bool WF, bool FAR, bool CHECK, bool FASTEXP>
+template <bool ORTHO, int DAMP, bool WF, bool FAR, bool CHECK, bool FASTEXP, bool UNI, int UNR>
 __device__ __forceinline__ void cluster_pair2(const Cell& c, const SymConsts& k, int lane, int ia, int jbase_global, int n,
                                               const double* __restrict__ rec, const double* __restrict__ saux,
                                               const int* __restrict__ smol, const double (&pi)[2][6],
                                               const double (&auxi)[2], const int (&moli)[2], double (&ei)[2][3],
-                                              double& ajx, double& ajy, double& ajz) {
+                                              double& ajx, double& ajy, double& ajz, const bool uni_rt = false) {
     ajx = ajy = ajz = 0.0;
     const double* base = rec + lane * JREC;
-#pragma unroll kSymUnroll
+#pragma unroll UNR
     for (int s = 0; s < 32; s++) {
         const double2 pxy = *reinterpret_cast<const double2*>(base + s * JREC);
         const double2 pzm = *reinterpret_cast<const double2*>(base + s * JREC + 2);
@@ -187,7 +229,7 @@ __device__ __forceinline__ void cluster_pair2(const Cell& c, const SymConsts& k,
 #pragma unroll
         for (int u = 0; u < 2; u++) {
             double dx = pi[u][0] - xj, dy = pi[u][1] - yj, dz = pi[u][2] - zj;
-            min_image_xu<ORTHO>(c, dx, dy, dz);
+            if (!UNI && !uni_rt) min_image_xu<ORTHO>(c, dx, dy, dz);  // UNI: pi is already in the image every pair of this cluster pair picks
             const double r2 = dx * dx + dy * dy + dz * dz;
             double c1, c2;
             if (DAMP == MPMC_DAMP_EXPONENTIAL)
@@ -229,6 +271,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
     __shared__ double saux[4][64];
     __shared__ int smol[4][64];
     __shared__ double sej[4][3][TILE];
+    __shared__ double spi[2][3][TILE];  // the positions as stored; pi[u][0..2] hold them in the image of the current cluster pair
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int np = a.np, S = a.S, nclus = np >> 5;
     const int cidx = a.rank + (int)blockIdx.x * a.world;  // this rank's blockIdx.x-th item
@@ -241,9 +284,9 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
 #pragma unroll
     for (int u = 0; u < 2; u++) {
         const int i = ia + 32 * u;
-        pi[u][0] = a.x[i];
-        pi[u][1] = a.y[i];
-        pi[u][2] = a.z[i];
+        pi[u][0] = spi[u][0][tid] = a.x[i];  // (read back by this thread only: no barrier needed)
+        pi[u][1] = spi[u][1][tid] = a.y[i];
+        pi[u][2] = spi[u][2][tid] = a.z[i];
         pi[u][3] = a.mu[i];
         pi[u][4] = a.mu[np + i];
         pi[u][5] = a.mu[2 * np + i];
@@ -285,6 +328,10 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
                 // diagonal super tile: every ordered pair inside it, I side only
                 const int jn = min(TILE, a.n - jb);
 #pragma unroll
+                for (int u = 0; u < 2; u++)
+#pragma unroll
+                    for (int d = 0; d < 3; d++) pi[u][d] = spi[u][d][tid];
+#pragma unroll
                 for (int u = 0; u < 2; u++) {
                     const int i = ia + 32 * u;
                     if (i >= a.n) continue;
@@ -317,22 +364,57 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
                 farmask = __ballot_sync(0xffffffffu, f);
                 farmask = farmask & (farmask >> 4) & 0xfu;  // both i-clusters far from j-cluster b
             }
+            // one image for all 32 x 32 pairs of (i-cluster, j-cluster)?  bit 30 + the image numbers (10 bits each, +512)
+            int ucode = 0;
+            if (ORTHO && a.unishift && !check && lane < 8)
+                ucode = uniform_image(k.box, a.cbox, nclus, ci + (lane >> 2), (jb >> 5) + (lane & 3));
 #pragma unroll 1
             for (int b = 0; b < 4; b++) {
                 const int jc = b;  // all four warps on the same j-cluster: their i-clusters are neighbours, so the
                                    // far / damped classes coincide and nobody waits long at the barrier
                 double ajx, ajy, ajz;
                 const bool far = (farmask >> jc) & 1u;
-#define CP(FAR, CHECK)                                                                                                     \
-    cluster_pair2<ORTHO, DAMP, WF, FAR, CHECK, FASTEXP>(c, k, lane, ia, jb + jc * 32, a.n, &srec[jc][0][0], &saux[jc][0], \
-                                                        &smol[jc][0], pi, auxi, moli, ei, ajx, ajy, ajz)
-                if (check) {
-                    CP(false, true);
-                } else if (far) {
-                    CP(true, false);
-                } else {
-                    CP(false, false);
+                bool uni = false;
+                if (ORTHO) {
+                    const int cu0 = __shfl_sync(0xffffffffu, ucode, jc), cu1 = __shfl_sync(0xffffffffu, ucode, 4 + jc);
+                    uni = (cu0 & cu1 & (1 << 30)) != 0;  // warp-uniform
+                    if (SYM_UNR_DAMPUNI == 0) uni = uni && far;
+                    const int cu[2] = {uni ? cu0 : kNoImage, uni ? cu1 : kNoImage};
+#pragma unroll
+                    for (int u = 0; u < 2; u++) {  // x - 0 L = x exactly: a cluster pair without a common image keeps the stored positions
+                        pi[u][0] = fma(-k.box.Lx, (double)((cu[u] & 1023) - 512), spi[u][0][tid]);
+                        pi[u][1] = fma(-k.box.Ly, (double)(((cu[u] >> 10) & 1023) - 512), spi[u][1][tid]);
+                        pi[u][2] = fma(-k.box.Lz, (double)(((cu[u] >> 20) & 1023) - 512), spi[u][2][tid]);
+                    }
                 }
+#define CP(FAR, CHECK, UNI, UNR)                                                                                                     \
+    cluster_pair2<ORTHO, DAMP, WF, FAR, CHECK, FASTEXP, UNI, UNR>(c, k, lane, ia, jb + jc * 32, a.n, &srec[jc][0][0], &saux[jc][0], \
+                                                                  &smol[jc][0], pi, auxi, moli, ei, ajx, ajy, ajz)
+#ifdef SYM_UNI_RUNTIME
+#define CPR(FAR)                                                                                                                  \
+    cluster_pair2<ORTHO, DAMP, WF, FAR, false, FASTEXP, false, kSymUnroll>(c, k, lane, ia, jb + jc * 32, a.n, &srec[jc][0][0], &saux[jc][0], \
+                                                               &smol[jc][0], pi, auxi, moli, ei, ajx, ajy, ajz, uni)
+                if (check) {
+                    CP(false, true, false, kSymUnroll);
+                } else if (far) {
+                    CPR(true);
+                } else {
+                    CPR(false);
+                }
+#undef CPR
+#else
+                if (check) {
+                    CP(false, true, false, 2);
+                } else if (ORTHO && uni && far) {
+                    CP(true, false, true, SYM_UNR_FARUNI);
+                } else if (ORTHO && SYM_UNR_DAMPUNI > 0 && uni) {
+                    CP(false, false, true, (SYM_UNR_DAMPUNI > 0 ? SYM_UNR_DAMPUNI : 1));
+                } else if (far) {
+                    CP(true, false, false, SYM_UNR_FAR);
+                } else {
+                    CP(false, false, false, SYM_UNR_DAMP);
+                }
+#endif
 #undef CP
                 sej[w][0][jc * 32 + lane] = ajx;
                 sej[w][1][jc * 32 + lane] = ajy;
@@ -424,11 +506,16 @@ __global__ void __launch_bounds__(256) cluster_box_kernel(int n, int np, double 
     double px[3] = {live ? x[i] : 0.0, live ? y[i] : 0.0, live ? z[i] : 0.0};
     const unsigned any = __ballot_sync(0xffffffffu, live);
     const double L[3] = {Lx, Ly, Lz}, iL[3] = {iLx, iLy, iLz};
+    bool one_image = true;  // every atom in the image of the first: the box bounds the stored coordinates
 #pragma unroll
     for (int d = 0; d < 3; d++) {
         const double p0 = __shfl_sync(0xffffffffu, px[d], 0);  // lane 0 is live whenever any lane is
         double v = px[d] - p0;
-        if (ortho) v = fma(-L[d], rint(v * iL[d]), v);
+        if (ortho) {
+            const double m = rint(v * iL[d]);
+            one_image = one_image && (m == 0.0 || !live);
+            v = fma(-L[d], m, v);
+        }
         double lo = live ? v : 1.0e300, hi = live ? v : -1.0e300;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -441,6 +528,8 @@ __global__ void __launch_bounds__(256) cluster_box_kernel(int n, int np, double 
             cbox[(3 + d) * nclus + cl] = any ? 0.5 * (hi - lo) * (1.0 + 1e-12) + 1e-9 : 1.0e30;
         }
     }
+    const bool all_one = __all_sync(0xffffffffu, one_image);
+    if (lane == 0) cbox[6 * nclus + cl] = (any && ortho && all_one) ? 1.0 : 0.0;
 }
 
 SymConsts make_sym_consts(const Cell& c, bool ortho, const DipoleOpts& o) {
@@ -634,6 +723,8 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
     a.hsplit = 2;
     (void)sms;
     if (const char* v = getenv("MPMC_B200_SYM_HSPLIT")) a.hsplit = atoi(v) == 2 ? 2 : 1;
+    a.unishift = 1;  // MPMC_B200_SYM_UNISHIFT=0: minimum image per pair everywhere (A/B)
+    if (const char* v = getenv("MPMC_B200_SYM_UNISHIFT")) a.unishift = atoi(v) != 0 ? 1 : 0;
     // Sharding unit: the work item (I tile, offset slice y) -- every item has the same number of pairs; the items are
     // dealt out round robin over their y-major order, so the ranks differ by at most one item and hold the same mix of
     // damped and far tile pairs.  One CTA per owned item, in that order (heavy near-diagonal slices first).

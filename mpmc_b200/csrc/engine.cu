@@ -828,7 +828,7 @@ static int pack_subset(Ctx* c, Subset& s, const std::vector<int>& idx, int pad_m
     if (s.x.ensure(np) || s.y.ensure(np) || s.z.ensure(np) || s.q.ensure(np) || s.alpha.ensure(np) || s.aux.ensure(np) ||
         s.mol.ensure(np) || s.flags.ensure(np))
         FAIL(11, "cudaMalloc failed");
-    if (with_lj && (s.eps.ensure(np) || s.sig.ensure(np) || s.mm.ensure(np) || s.cbox.ensure((size_t)6 * (s.n_pad / 32))))
+    if (with_lj && (s.eps.ensure(np) || s.sig.ensure(np) || s.mm.ensure(np) || s.cbox.ensure((size_t)7 * (s.n_pad / 32))))
         FAIL(11, "cudaMalloc failed");
     subset_gather_kernel<<<(s.n_pad + 255) / 256, 256, 0, st>>>(
         s.n, s.n_pad, s.didx.p, c->x.p, c->y.p, c->z.p, c->q.p, c->alpha.p, c->eps.p, c->sig.p, c->molmass.p, c->mol.p, c->flags.p,
@@ -1003,7 +1003,7 @@ static int repack(Ctx* c) {
         for (int k = 0; k < c->gsp.n_pad; k++) c->gsp_packed[k] = k < c->gsp.n ? packed_of_atom[sp[k]] : k;
         const size_t gp = (size_t)c->gsp.n_pad;
         if (c->map_s2g.ensure(gp) || c->map_g2s.ensure(gp) || c->g_mu_sp.ensure(3 * gp) || c->g_esum_sp.ensure(3 * gp) ||
-            c->cbox_sp.ensure(6 * (gp / 32)))
+            c->cbox_sp.ensure(7 * (gp / 32)))
             FAIL(11, "cudaMalloc failed");
         if (!c->pol_sorted && !c->use_clusters) sort_positions();  // the drift check of set_positions needs the sort-time positions
     }
@@ -1131,7 +1131,7 @@ static int repack(Ctx* c) {
         int per_sm = 48;  // measured on M4: 16 -> 48 CTAs per SM removes most of the last-wave tail
         if (const char* v = getenv("MPMC_B200_SYM_CTAS_PER_SM")) per_sm = std::max(1, atoi(v));
         c->sym_ysplits = std::max(1, std::min(K1, (per_sm * sms + own_tiles - 1) / own_tiles));
-        if (c->cbox.ensure((size_t)6 * (pp / 32)) || c->sym_partI.ensure((size_t)2 * c->sym_ysplits * 3 * pp) ||
+        if (c->cbox.ensure((size_t)7 * (pp / 32)) || c->sym_partI.ensure((size_t)2 * c->sym_ysplits * 3 * pp) ||
             c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp, c->sym_ysplits) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
             FAIL(11, "cudaMalloc failed");
     }

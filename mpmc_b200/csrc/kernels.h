@@ -27,7 +27,7 @@ struct SubsetDev {
     int *mol, *flags, *idx;  // idx = index in AtomsDev
     // only in the spatially sorted image of ALL atoms used by the cutoff kernels (else null):
     double *eps, *sig, *molmass;
-    double* cbox;  // [6][n_pad/32] cluster boxes of this evaluation
+    double* cbox;  // [7][n_pad/32] cluster boxes of this evaluation (centre, half extent, one-image flag)
 };
 
 // ---- K1: fused LJ(+FH) + Ewald real(+FH) + intramolecular erf + min distance ------------------
@@ -145,7 +145,7 @@ void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, co
 // `world` takes the r-th contiguous share of the flattened items;
 // partial rows: epartI [2 * ysplits][3][n_pad], epartJ [dipole_sym_partial_rows(n_pad, ysplits)][3][n_pad];
 // esum [3][n_pad] receives this launch's contribution to E_ind for ALL rows (summed over ranks by the
-// caller in sharded runs).  cbox [6][n_pad/32] from launch_cluster_boxes().
+// caller in sharded runs).  cbox [7][n_pad/32] from launch_cluster_boxes().
 // Peer-memory exchange of the induced-field partial sums (multi-GPU, one process per GPU): every rank's reduce
 // kernel leaves its contribution to E_ind of ALL rows in a buffer the other ranks can read over NVLink
 // (CUDA IPC), then raises a flag in every peer's memory; the update kernel of each rank waits for all flags and
