@@ -1343,13 +1343,16 @@ static double* peer_scal(void* base, size_t cap, size_t cap_atoms, int parity) {
 static unsigned long long* peer_flags(void* base, size_t cap, size_t cap_atoms, int ch) {
     return reinterpret_cast<unsigned long long*>(reinterpret_cast<double*>(base) + peer_doubles(cap, cap_atoms)) + ch * PEER_MAX;
 }
-// Which Jacobi contraction runs.  The symmetric kernel's work item is a 256 x 256 tile pair (~130 us of one CTA):
-// below ~8k polarizable atoms its grid does not fill the GPU and an evaluation costs one item per iteration however
-// small the system, while the row form with the j range fully split ((n/128)^2 CTAs of 128 x 128 pairs) finishes in
-// 10-60 us despite doing every pair twice.  Sharded runs always use the symmetric form (its exchange protocol).
+// Which Jacobi contraction runs.  The symmetric kernel's work item is half a 256 x 256 tile pair (~65 us of one CTA):
+// for a small system its grid does not fill the GPU and an evaluation costs one item per iteration however small the
+// system, while the row form with the j range fully split ((n/128)^2 CTAs of 128 x 128 pairs) finishes in 10-60 us
+// despite doing every pair twice.  Crossover on one GPU (profiles/r02_sym_min.md, half-tile items): 3,840 padded
+// polarizable atoms 0.93 (rows) against 0.96 ms (symmetric) per energy(), 4,864: 1.66 against 1.08, 7,296: 2.93 against
+// 1.65 -- so 4,096 (8,192 while the item was a whole tile pair).  Sharded runs always use the symmetric form (its
+// exchange protocol).
 static bool sym_now(const Ctx* c) {
     const char* v = getenv("MPMC_B200_SYM_MIN");  // read per call: the tests switch it inside one process
-    const int min_pad = v ? atoi(v) : 8192;
+    const int min_pad = v ? atoi(v) : 4096;
     return c->use_sym && (c->world > 1 || c->pol.n_pad >= min_pad);
 }
 static bool peer_active(const Ctx* c) {
