@@ -2843,20 +2843,48 @@ int mpmc_b200_set_atoms(mpmc_b200_ctx* c, int n, const double* pos, const double
                        c->hq[io] == charge[in] && c->halpha[io] == polarizability[in] && c->heps[io] == epsilon[in] &&
                        c->hsig[io] == sigma[in] && c->hfrozen[io] == (frozen[in] ? 1 : 0);
             };
-            const int lim = std::min(no, n);
-            int pre = 0;
-            while (pre < lim && same(pre, pre)) pre++;
-            int suf = 0;
-            while (suf < lim - pre && same(no - 1 - suf, n - 1 - suf)) suf++;
-            const int gone = no - pre - suf, fresh = n - pre - suf;
+            // Two-pointer walk over the held and the incoming arrays.  At a mismatch the shortest block (<= 64 atoms: a
+            // molecule) whose removal from the held side, insertion on the incoming side, or replacement makes the next atoms
+            // agree again is taken as one edit.  A uVT step is usually TWO edits at different places of the list -- the
+            // driver's restore of a rejected insertion / removal never reaches the engine on its own, it arrives together
+            // with the next trial -- which a common prefix + suffix would read as one long changed span (every second
+            // step of the PCN-61 sample then sorted afresh).
+            auto agree = [&](int io, int in) {  // the next (up to) 8 atoms agree; both lists ending together counts
+                const int len = std::min(8, std::min(no - io, n - in));
+                if (len == 0) return io == no && in == n;
+                for (int q = 0; q < len; q++)
+                    if (!same(io + q, in + q)) return false;
+                return true;
+            };
+            std::vector<int> map(no, -1), fresh_list;
+            int io = 0, in = 0, gone = 0;
+            bool ok = true;
+            while (ok && (io < no || in < n)) {
+                if (io < no && in < n && same(io, in)) {
+                    map[io++] = in++;
+                    continue;
+                }
+                bool found = false;
+                for (int k = 1; k <= 64 && !found; k++) {
+                    if (io + k <= no && agree(io + k, in)) {  // k held atoms are gone
+                        io += k, gone += k, found = true;
+                    } else if (in + k <= n && agree(io, in + k)) {  // k new atoms
+                        for (int q = 0; q < k; q++) fresh_list.push_back(in + q);
+                        in += k, found = true;
+                    } else if (io + k <= no && in + k <= n && agree(io + k, in + k)) {  // k atoms replaced
+                        for (int q = 0; q < k; q++) fresh_list.push_back(in + q);
+                        io += k, in += k, gone += k, found = true;
+                    }
+                }
+                if (!found || gone + (int)fresh_list.size() > 256) ok = false;
+            }
+            const int fresh = (int)fresh_list.size();
             // every edit shifts the clusters behind it off the bricks the sort made (a few % of K4 / K1 / K3 once many have
             // piled up): a full sort again after n/128 edited atoms -- its cost, spread over them, is ~0.15 ms per edit
-            if (gone >= 0 && fresh >= 0 && gone + fresh <= 256 && c->order_edits + gone + fresh <= std::max(64, no / 128)) {
-                c->edit_map.assign(no, -1);
-                for (int i = 0; i < pre; i++) c->edit_map[i] = i;
-                for (int i = 0; i < suf; i++) c->edit_map[no - 1 - i] = n - 1 - i;
-                c->edit_fresh.resize(fresh);
-                std::iota(c->edit_fresh.begin(), c->edit_fresh.end(), pre);
+            // (small systems: a sort costs ~2 ms at 8k atoms against an evaluation of ~1.3 ms, so up to 256 edited atoms)
+            if (ok && gone + fresh <= 256 && c->order_edits + gone + fresh <= std::max(std::min(256, no / 16), no / 128)) {
+                c->edit_map.swap(map);
+                c->edit_fresh.swap(fresh_list);
                 c->order_edits += gone + fresh;
             }
         }

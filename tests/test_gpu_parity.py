@@ -351,6 +351,73 @@ def test_small_edits_of_the_atom_set_keep_parity(engine):
         cur = nxt
 
 
+def test_two_edits_in_one_call_carry_the_orders():
+    """A uVT step reaches the engine as TWO edits at different places of the list: the driver's restore of a rejected
+    insertion / removal arrives together with the next trial (mc_moves.c:790-799 + :567-741).  set_atoms must read that as
+    two small edits (engine.cu: two-pointer walk), not as one long changed span, and carry the orders over; a displaced
+    molecule in the same call (replacement) as well.  Fresh process with MPMC_B200_REPACK_TIMING, whose stderr line names
+    the path taken; every configuration against the oracle."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r"""
+import sys
+sys.path.insert(0, %r)
+import numpy as np
+from mpmc_b200 import Engine, systems
+from oracle import oracle
+rng = np.random.default_rng(23)
+s = systems.mof_h2(cells=(3, 3, 1))
+fields = ("pos", "charge", "polarizability", "epsilon", "sigma", "mol_mass", "mol_id", "frozen")
+eng = Engine(0)
+eng.set_system(s)
+eng.energy()
+L = np.array([s.params.basis[q][q] for q in range(3)])
+cur = s
+for k in range(4):
+    st = np.flatnonzero(np.r_[True, cur.mol_id[1:] != cur.mol_id[:-1]])
+    en = np.r_[st[1:], cur.n]
+    mv = [i for i in range(len(st)) if not cur.frozen[st[i]]]
+    pick = sorted(rng.choice(len(mv), size=3, replace=False))
+    (a1, b1), (a2, b2), (a3, b3) = [(int(st[mv[i]]), int(en[mv[i]])) for i in pick]
+    nxt = cur.copy()
+    # molecule 1 removed, molecule 2 displaced (k odd), a displaced copy of molecule 3 inserted behind it
+    for f in fields:
+        v = getattr(cur, f)
+        add = v[a3:b3].copy()
+        mid = v[b1:b3].copy()
+        if f == "pos":
+            add = add + rng.uniform(-0.5, 0.5, 3) * L
+            if k %% 2:
+                mid[a2 - b1:b2 - b1] += rng.uniform(-0.3, 0.3, 3)
+        setattr(nxt, f, np.concatenate([v[:a1], mid, add, v[b3:]]))
+    pos_new = b3 - (b1 - a1)
+    nxt.mol_id[pos_new:pos_new + (b3 - a3)] = -1
+    nxt.mol_id = np.cumsum(np.r_[0, (nxt.mol_id[1:] != nxt.mol_id[:-1]).astype(np.int32)]).astype(np.int32)
+    print("EDIT", k, cur.n, "->", nxt.n, file=sys.stderr, flush=True)
+    eng.set_system(nxt)
+    got = eng.energy()
+    exp, _, oarr = oracle.energy(nxt, nthreads=0)
+    for key, want in exp.to_dict().items():
+        have = got.to_dict()[key]
+        if isinstance(want, float) and key not in ("iterations",):
+            assert abs(have - want) <= 1e-10 * max(abs(want), 1.0), (k, key, have, want)
+    mu = eng.atom_arrays()["mu"]
+    assert np.abs(mu - oarr["mu"]).max() <= 1e-10 * np.abs(oarr["mu"]).max(), k
+    cur = nxt
+eng.close()
+print("EDITS_OK")
+""" % root
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=900,
+                       env=dict(os.environ, MPMC_B200_REPACK_TIMING="1"))
+    assert r.returncode == 0 and "EDITS_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+    after = r.stderr.split("EDIT 0")[1]
+    lines = [l for l in after.splitlines() if "MPMC_B200_REPACK_TIMING" in l]
+    assert len(lines) == 4 and all("orders carried over" in l for l in lines), lines
+
+
 def test_large_moves_relocate_atoms_in_the_orders(engine):
     """With the reference's default move_factor (1.0: displacements up to the cutoff) nearly every trial move carries a
     molecule further than the drift limit of the spatial orders.  The engine then takes the molecule's atoms out of the orders
