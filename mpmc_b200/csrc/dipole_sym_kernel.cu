@@ -124,8 +124,9 @@ struct SymArgs {
                      // near -- damped, expensive -- and far tile pairs; contiguous shares left the ranks 9 % apart)
     int K;           // S/2: offsets 0..K
     int kper;        // offsets per gridDim.y slice
-    int hsplit;      // 1: a CTA walks both halves of the J super tile; 2: gridDim.z = 2, one half each (finer grain
-                     // for the short launches of a sharded run, where the last wave would otherwise cost ~10 %)
+    int hsplit;      // gridDim.z.  1: a CTA walks both halves of the J super tile; 2: one half each (finer grain: the last
+                     // wave of a launch costs less); 4 / 8: one half, and 2 / 1 of its four j-clusters (launches of
+                     // less than two waves of CTAs: the single item is then the critical path)
     int unishift;    // 1: cluster pairs with one image for all their atom pairs skip the per-pair minimum image
     const double *x, *y, *z, *aux;
     const int* mol;
@@ -140,6 +141,9 @@ struct SymArgs {
 #endif
 #ifndef SYM_MINB
 #define SYM_MINB 4
+#endif
+#ifndef SYM_HSPLIT_MAX
+#define SYM_HSPLIT_MAX 8
 #endif
 constexpr int kSymUnroll = SYM_UNROLL;
 // unroll factor of the 32-step loop per class of cluster pair (far / damped, with / without one image for all pairs);
@@ -300,7 +304,10 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
         if (kk > 0 && 2 * kk == S && I >= kk) continue;  // even S: the half-way offset belongs to I < S/2
         int J = I + kk;
         if (J >= S) J -= S;
-        const int h0 = a.hsplit == 2 ? (int)blockIdx.z : 0, h1 = a.hsplit == 2 ? (int)blockIdx.z + 1 : 2;
+        // gridDim.z = hsplit slices of the J super tile: halves, then groups of the half's four j-clusters
+        const int zq = a.hsplit >= 2 ? a.hsplit >> 1 : 1, zb = (int)blockIdx.z % zq;
+        const int h0 = a.hsplit >= 2 ? (int)blockIdx.z / zq : 0, h1 = a.hsplit >= 2 ? h0 + 1 : 2;
+        const int b0 = zb * (4 / zq), b1 = b0 + 4 / zq;  // this CTA's j-clusters of the half
 #pragma unroll 1
         for (int half = h0; half < h1; half++) {
             const int jb = J * STILE + half * TILE;  // first atom of this half
@@ -326,7 +333,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
             __syncthreads();
             if (kk == 0) {
                 // diagonal super tile: every ordered pair inside it, I side only
-                const int jn = min(TILE, a.n - jb);
+                const int jn = min(32 * b1, a.n - jb);
 #pragma unroll
                 for (int u = 0; u < 2; u++)
 #pragma unroll
@@ -335,7 +342,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
                 for (int u = 0; u < 2; u++) {
                     const int i = ia + 32 * u;
                     if (i >= a.n) continue;
-                    for (int jj = 0; jj < jn; jj++) {
+                    for (int jj = 32 * b0; jj < jn; jj++) {
                         if (jb + jj == i) continue;
                         const double* r = &srec[jj >> 5][jj & 31][0];
                         double dx = pi[u][0] - r[0], dy = pi[u][1] - r[1], dz = pi[u][2] - r[2];
@@ -369,7 +376,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
             if (ORTHO && a.unishift && !check && lane < 8)
                 ucode = uniform_image(k.box, a.cbox, nclus, ci + (lane >> 2), (jb >> 5) + (lane & 3));
 #pragma unroll 1
-            for (int b = 0; b < 4; b++) {
+            for (int b = b0; b < b1; b++) {
                 const int jc = b;  // all four warps on the same j-cluster: their i-clusters are neighbours, so the
                                    // far / damped classes coincide and nobody waits long at the barrier
                 double ajx, ajy, ajz;
@@ -421,7 +428,7 @@ __global__ void __launch_bounds__(TILE, SYM_MINB) dipole_sym_kernel(Cell c, SymC
                 sej[w][2][jc * 32 + lane] = ajz;
             }
             __syncthreads();
-            {
+            if ((tid >> 5) >= b0 && (tid >> 5) < b1) {  // the j atoms of this CTA's clusters (the other slices write the rest of the row)
                 double* ej = a.epartJ + (size_t)(kk - a.jrow0) * 3 * np + (size_t)jb + tid;
 #pragma unroll
                 for (int cc = 0; cc < 3; cc++)
@@ -683,6 +690,31 @@ int dipole_sym_partial_rows(int n_pad, int ysplits) {
     return rows > 1 ? rows : 1;
 }
 
+// gridDim.z of a contraction's launches (see SymArgs::hsplit); the I-side partial rows are [hsplit * ysplits][3][n_pad]
+int dipole_sym_hsplit(int n_pad, int ysplits, int world) {
+    static const int forced = [] {
+        const char* v = getenv("MPMC_B200_SYM_HSPLIT");
+        const int h = v ? atoi(v) : 0;
+        return (h == 1 || h == 2 || h == 4 || h == 8) ? h : 0;
+    }();
+    if (forced) return forced;
+    const int S = n_pad / STILE, K = S / 2;
+    if (S <= 0) return 2;
+    ysplits = std::max(1, std::min(ysplits, K + 1));
+    const int kper = (K + 1 + ysplits - 1) / ysplits, Y = (K + 1 + kper - 1) / kper;
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long mine = ((long)S * Y + std::max(world, 1) - 1) / std::max(world, 1);
+    // measured on one GPU (call 73, ms per energy() with gridDim.z 2 / 4 / 8): 4.8k polarizable atoms 1.66 / 1.54 / 1.49, 5.2k
+    // 1.44 / 1.30 / 1.25, 7.2k 2.70 / 2.67 / 2.69, 9.6k 4.23 / 4.11 / 4.13, 15k 2.36 / 2.35 / 2.45: finer while the launch is
+    // below ~2.75 waves of resident CTAs
+    const long limit = 11L * sms * SYM_MINB / 4;
+    int h = 2;
+    while (h < SYM_HSPLIT_MAX && mine * h < limit) h *= 2;
+    return h;
+}
+
 void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,
                                 const double* cbox, int rank, int world, int ysplits, double* epartI,
                                 double* epartJ, double* esum, cudaStream_t s, const PeerSignal* sig) {
@@ -720,9 +752,10 @@ void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol,
     // Round 2, end: with the list-driven reduce the half items also pay on ONE GPU -- 9.6k polarizable atoms 0.283 -> 0.253 ms
     // per contraction (1.3 -> 2.6 waves), 15k -6 %, 31k -3 %, 46k (mof_h2_63k, 9.5 -> 19 waves) 3.674 -> 3.597 ms
     // (profiles/r02_k4_hsplit.md) -- so they are the default everywhere; MPMC_B200_SYM_HSPLIT=1 restores whole items.
-    a.hsplit = 2;
+    // Last change of round 2: launches of less than two waves of half items (4k-12k polarizable atoms on one GPU) are
+    // bound by the single item; there the half is cut further into groups of its j-clusters (profiles/r02_sym_min.md).
+    a.hsplit = dipole_sym_hsplit(np, ysplits, world);
     (void)sms;
-    if (const char* v = getenv("MPMC_B200_SYM_HSPLIT")) a.hsplit = atoi(v) == 2 ? 2 : 1;
     a.unishift = 1;  // MPMC_B200_SYM_UNISHIFT=0: minimum image per pair everywhere (A/B)
     if (const char* v = getenv("MPMC_B200_SYM_UNISHIFT")) a.unishift = atoi(v) != 0 ? 1 : 0;
     // Sharding unit: the work item (I tile, offset slice y) -- every item has the same number of pairs; the items are

@@ -1131,7 +1131,7 @@ static int repack(Ctx* c) {
         int per_sm = 48;  // measured on M4: 16 -> 48 CTAs per SM removes most of the last-wave tail
         if (const char* v = getenv("MPMC_B200_SYM_CTAS_PER_SM")) per_sm = std::max(1, atoi(v));
         c->sym_ysplits = std::max(1, std::min(K1, (per_sm * sms + own_tiles - 1) / own_tiles));
-        if (c->cbox.ensure((size_t)7 * (pp / 32)) || c->sym_partI.ensure((size_t)2 * c->sym_ysplits * 3 * pp) ||
+        if (c->cbox.ensure((size_t)7 * (pp / 32)) || c->sym_partI.ensure((size_t)std::max(2, dipole_sym_hsplit(pp, c->sym_ysplits, c->world)) * c->sym_ysplits * 3 * pp) ||
             c->sym_partJ.ensure((size_t)dipole_sym_partial_rows(pp, c->sym_ysplits) * 3 * pp) || c->esum.ensure((size_t)3 * pp))
             FAIL(11, "cudaMalloc failed");
     }

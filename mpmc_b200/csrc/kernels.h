@@ -143,7 +143,7 @@ void launch_dipole_field_at(const Cell& c, bool ortho, const SubsetDev& rows, co
 // Symmetric form of the contraction (dipole_sym_kernel.cu): T_ij computed once per unordered pair and
 // applied in both directions.  Work items = (I super tile of 256 atoms) x (slice of the offsets 0..S/2, `ysplits` slices); rank r of
 // `world` takes the r-th contiguous share of the flattened items;
-// partial rows: epartI [2 * ysplits][3][n_pad], epartJ [dipole_sym_partial_rows(n_pad, ysplits)][3][n_pad];
+// partial rows: epartI [dipole_sym_hsplit() * ysplits][3][n_pad], epartJ [dipole_sym_partial_rows(n_pad, ysplits)][3][n_pad];
 // esum [3][n_pad] receives this launch's contribution to E_ind for ALL rows (summed over ranks by the
 // caller in sharded runs).  cbox [7][n_pad/32] from launch_cluster_boxes().
 // Peer-memory exchange of the induced-field partial sums (multi-GPU, one process per GPU): every rank's reduce
@@ -171,6 +171,7 @@ void launch_peer_sum(const PeerWait& pw, size_t n, double* out, cudaStream_t s);
 // the evaluation's device scalars: sums over ranks, slot min_slot the minimum; n <= 64
 void launch_peer_scalars(const PeerWait& pw, int n, int min_slot, double* out, cudaStream_t s);
 int dipole_sym_tile();  // atoms per super tile (256): n_pad of the polarizable subset must be a multiple
+int dipole_sym_hsplit(int n_pad, int ysplits, int world);  // gridDim.z of a contraction: I-side partial rows = hsplit * ysplits
 int dipole_sym_partial_rows(int n_pad, int ysplits);  // J-side partial rows one launch writes (capped: MPMC_B200_SYM_PART_MB)
 void launch_cluster_boxes(const Cell& c, bool ortho, const SubsetDev& pol, double* cbox, cudaStream_t s);
 void launch_dipole_contract_sym(const Cell& c, bool ortho, const SubsetDev& pol, const DipoleOpts& o, const double* mu,

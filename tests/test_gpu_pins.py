@@ -88,6 +88,10 @@ print("ROUNDS_OK", len(devs))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
                        env=dict(os.environ, MPMC_B200_SYM_HSPLIT="1", MPMC_B200_SYM_MIN="0"))
     assert r.returncode == 0 and "ROUNDS_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+    # the finest items (one j-cluster of a half tile per CTA; chosen automatically only for launches below ~3 waves)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, MPMC_B200_SYM_HSPLIT="8", MPMC_B200_SYM_MIN="0"))
+    assert r.returncode == 0 and "ROUNDS_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
     # and the minimum image taken per pair everywhere (by default a cluster pair whose boxes prove one image for all its
     # atom pairs moves the i atoms once instead, MPMC_B200_SYM_UNISHIFT)
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
