@@ -1348,11 +1348,12 @@ static unsigned long long* peer_flags(void* base, size_t cap, size_t cap_atoms, 
 // system, while the row form with the j range fully split ((n/128)^2 CTAs of 128 x 128 pairs) finishes in 10-60 us
 // despite doing every pair twice.  Crossover on one GPU (profiles/r02_sym_min.md, half-tile items): 3,840 padded
 // polarizable atoms 0.93 (rows) against 0.96 ms (symmetric) per energy(), 4,864: 1.66 against 1.08, 7,296: 2.93 against
-// 1.65 -- so 4,096 (8,192 while the item was a whole tile pair).  Sharded runs always use the symmetric form (its
-// exchange protocol).
+// 1.65; with the items cut down to single j-clusters for short launches (dipole_sym_hsplit) also 3,072: 0.99 against 0.91,
+// 3,840: 1.31 against 1.09, while 2,560 stays with the rows (0.73 against 1.13 with half items) -- so 3,072 (8,192 while
+// the item was a whole tile pair).  Sharded runs always use the symmetric form (its exchange protocol).
 static bool sym_now(const Ctx* c) {
     const char* v = getenv("MPMC_B200_SYM_MIN");  // read per call: the tests switch it inside one process
-    const int min_pad = v ? atoi(v) : 4096;
+    const int min_pad = v ? atoi(v) : 3072;
     return c->use_sym && (c->world > 1 || c->pol.n_pad >= min_pad);
 }
 static bool peer_active(const Ctx* c) {

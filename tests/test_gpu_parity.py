@@ -113,7 +113,7 @@ def test_es_wolf_with_feynman_hibbs_is_refused(engine):
 
 @pytest.mark.parametrize("name", SYM_SMALL)
 def test_symmetric_contraction_on_small_fixtures(engine, name, monkeypatch):
-    """Below 4,096 padded polarizable atoms a single GPU uses the row form of K4 (latency); MPMC_B200_SYM_MIN=0 forces
+    """Below 3,072 padded polarizable atoms a single GPU uses the row form of K4 (latency); MPMC_B200_SYM_MIN=0 forces
     the symmetric kernel so that its damping / wolf / triclinic / padding variants stay pinned to the reference fixtures."""
     monkeypatch.setenv("MPMC_B200_SYM_MIN", "0")
     s, exp = gu.load(name)
@@ -125,6 +125,7 @@ def test_symmetric_contraction_on_small_fixtures(engine, name, monkeypatch):
 
 @pytest.mark.parametrize("builder,kw", [
     (systems.h2_fluid, dict(n_atoms=4000)),
+    (systems.h2_fluid, dict(n_atoms=5500)),  # 3,300 polarizable atoms: just above the size where the symmetric K4 takes over
     (systems.co2_fluid, dict(n_mol=1500)),
     (systems.mof_h2, dict(cells=(3, 3, 1))),
 ])

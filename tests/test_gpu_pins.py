@@ -38,7 +38,7 @@ def test_cuda_matches_pin(engine, name):
     if "rd_vs_reference" in dev:  # reference-made pin: see tests/pins.py on the rounding of lj()'s running sum
         assert dev["rd_vs_reference"] <= 1e-10 + 1.01 * dev["reference_rd_noise"], dev
     if polar and pin["meta"]["workload"] == "mof_h2_63k":
-        # the dispatch the bench line is quoted on: symmetric contraction (>= 4,096 padded polarizable atoms)
+        # the dispatch the bench line is quoted on: symmetric contraction (>= 3,072 padded polarizable atoms)
         c = engine.counters()
         assert c.n_polarizable >= 8192 and engine.uses_symmetric_contraction()
     # a second evaluation of the resident system reproduces the first bit for bit (fixed-order sums, no atomics)
